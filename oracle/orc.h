@@ -1,0 +1,121 @@
+/*
+ * orc.h — CPU ORACLE for the ORB front-end hot path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * Plain-C restatement of the reference's algorithm (Wangkkkkkkkk/ORB-SLAM3, CPU, OpenCV based):
+ *   src/ORBextractor.cc, src/ORBmatcher.cc, src/Frame.cc  (file:line cited at every function).
+ * The OpenCV primitives the reference calls (resize, copyMakeBorder, FAST, GaussianBlur,
+ * fastAtan2, cvRound, norm L1, BFMatcher) are NOT in /root/reference (un-vendored, unpinned
+ * dependency, CMakeLists.txt:37-43); they are restated here from their published algorithms and
+ * PINNED against cv2 4.13.0 (tests/test_oracle_vs_cv2.py, tests/golden/ built by
+ * oracle/make_golden.py which runs the real cv2 primitives).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+ * link or call this.  The product (orb-slam3_b200/) never does.
+ *
+ * Canonicalisations (documented in DESIGN.md):
+ *   - quadtree tie-break: (size, creation sequence) instead of (size, heap pointer)
+ *     (src/ORBextractor.cc:927 sorts pair<int,ExtractorNode*>);
+ *   - cosf/sinf: glibc's generic C algorithm evaluated without FMA contraction (orc_sinf/orc_cosf);
+ *   - tap rotation x*b+y*a: no FMA contraction (build uses -ffp-contract=off).
+ */
+#ifndef ORC_H
+#define ORC_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* cv::KeyPoint memory layout (28 bytes). */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orc_keypoint;
+
+/* candidate / selected keypoint inside one level (coordinates relative to minBorder=16). */
+typedef struct {
+    int32_t x, y, score;
+} orc_cand;
+
+typedef struct orc_extractor orc_extractor;
+
+enum { ORC_TIE_CANONICAL = 0, ORC_TIE_REVERSED = 1 };
+enum { ORC_TRIG_CANONICAL = 0, ORC_TRIG_LIBM = 1 };
+
+/* ---- OpenCV primitive restatements (orc_prims.c) ---- */
+int   orc_cvround_f(float v);                       /* cvRound(float): round-half-even      */
+int   orc_cvround_d(double v);                      /* cvRound(double)                      */
+float orc_fast_atan2(float y, float x);             /* cv::fastAtan2, degrees [0,360)       */
+float orc_sinf(float x);                            /* glibc generic sinf, no FMA           */
+float orc_cosf(float x);
+void  orc_resize_linear_u8(const uint8_t* src, int srows, int scols, size_t sstep,
+                           uint8_t* dst, int drows, int dcols, size_t dstep);
+void  orc_border_reflect101(uint8_t* plane, int rows, int cols, size_t step, int border);
+/* cv::FAST(img, kps, threshold, nms=true) TYPE_9_16; returns count, writes raster-ordered (x,y,score) */
+int   orc_fast9_16(const uint8_t* img, int rows, int cols, size_t step, int threshold,
+                   int nonmax, orc_cand* out, int cap);
+void  orc_gaussian7x7_s2(const uint8_t* src, int rows, int cols, size_t sstep,
+                         uint8_t* dst, size_t dstep);    /* BORDER_REFLECT_101, fixed point */
+int   orc_hamming256(const void* a, const void* b);      /* ORBmatcher::DescriptorDistance  */
+/* BFMatcher(NORM_HAMMING).knnMatch(k=2): out_idx/out_dist are [nq][2]; missing = -1 */
+void  orc_bf_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* out_idx, int32_t* out_dist);
+
+/* ---- ORBextractor (orc_extractor.c) ---- */
+orc_extractor* orc_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);
+void  orc_destroy(orc_extractor* e);
+void  orc_set_modes(orc_extractor* e, int tie_mode, int trig_mode);
+/* ORBextractor::operator(): returns monoIndex, -1 on empty image, -2 if cap too small. */
+int   orc_extract(orc_extractor* e, const uint8_t* img, int rows, int cols, size_t step,
+                  int lap0, int lap1, orc_keypoint* kps, uint8_t* desc, int cap, int* nkp);
+/* getters */
+int   orc_levels(const orc_extractor* e);
+const float* orc_scale_factors(const orc_extractor* e);
+const float* orc_inv_scale_factors(const orc_extractor* e);
+const float* orc_level_sigma2(const orc_extractor* e);
+const float* orc_inv_level_sigma2(const orc_extractor* e);
+const int*   orc_features_per_level(const orc_extractor* e);
+const int*   orc_umax(const orc_extractor* e);
+/* stage accessors (valid after orc_extract) */
+void  orc_level_dims(const orc_extractor* e, int level, int* rows, int* cols);
+const uint8_t* orc_level_plane(const orc_extractor* e, int level, size_t* step);   /* padded origin */
+const uint8_t* orc_level_blurred(const orc_extractor* e, int level, size_t* step); /* unpadded      */
+int   orc_level_candidates(const orc_extractor* e, int level, const orc_cand** out);
+int   orc_level_selected(const orc_extractor* e, int level, const orc_cand** out, const float** angles);
+/* stand-alone pieces for unit parity */
+int   orc_distribute_octree(const orc_cand* keys, int nkeys, int minX, int maxX, int minY, int maxY,
+                            int N, int tie_mode, orc_cand* out, int cap);
+float orc_ic_angle(const uint8_t* center, size_t step, const int* umax);
+void  orc_orb_descriptor(const uint8_t* center, size_t step, float angle_deg, int trig_mode, uint8_t* desc);
+
+/* ---- matching (orc_match.c) ---- */
+/* Frame::ComputeStereoMatches (src/Frame.cc:1027-1276). best_dist/best_sad optional (may be NULL). */
+void  orc_stereo_match(const orc_extractor* eL, const orc_extractor* eR,
+                       const orc_keypoint* kpL, int nL, const uint8_t* descL,
+                       const orc_keypoint* kpR, int nR, const uint8_t* descR,
+                       float mb, float mbf, float* uRight, float* depth,
+                       int32_t* best_dist, int32_t* best_sad);
+
+/* Frame grid (include/Frame.h:37-38, src/Frame.cc:446-480, 784-899) */
+typedef struct orc_grid orc_grid;
+orc_grid* orc_grid_build(const orc_keypoint* kps, int n, float minX, float maxX, float minY, float maxY);
+void  orc_grid_destroy(orc_grid* g);
+int   orc_grid_query(const orc_grid* g, const orc_keypoint* kps, float x, float y, float r,
+                     int minLevel, int maxLevel, int32_t* out, int cap);
+
+/* ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th, bFar, thFar) mono/rectified-stereo
+ * branch (F.Nleft == -1), src/ORBmatcher.cc:45-168.  SoA map-point inputs; assign[n] in/out:
+ * -1 = free, >=0 = index of the map point already held (treated as "Observations()>0").
+ * uRight may be NULL (mono).  Returns nmatches. */
+int   orc_search_by_projection(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n,
+                               const float* uRight, const float* scaleFactors,
+                               int nmp, const uint8_t* mp_desc, const float* mp_projx, const float* mp_projy,
+                               const float* mp_projxr, const int32_t* mp_level, const float* mp_viewcos,
+                               const float* mp_depth, const uint8_t* mp_inview,
+                               float th, float nnratio, int bFarPoints, float thFarPoints,
+                               int32_t* assign);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,285 @@
+"""ctypes binding of the CPU ORACLE (oracle/liborc.so).  TEST INFRASTRUCTURE ONLY.
+
+May be imported from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs — never from the product package.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import pathlib
+import subprocess
+
+import numpy as np
+
+_DIR = pathlib.Path(__file__).resolve().parent
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+CAND_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("score", "<i4")])
+assert KP_DTYPE.itemsize == 28 and CAND_DTYPE.itemsize == 12
+
+u8p = C.POINTER(C.c_uint8)
+i32p = C.POINTER(C.c_int32)
+f32p = C.POINTER(C.c_float)
+
+
+def build(force: bool = False) -> None:
+    """Compile the C restatement (gcc, a second or two)."""
+    if force:
+        subprocess.run(["make", "-C", str(_DIR), "clean"], check=True, capture_output=True)
+    subprocess.run(["make", "-C", str(_DIR)], check=True, capture_output=True)
+
+
+def _ptr(a, t):
+    return a.ctypes.data_as(t)
+
+
+class Oracle:
+    def __init__(self, fma: bool = False):
+        path = _DIR / "_build" / ("liborc_fma.so" if fma else "liborc.so")
+        if not path.exists():
+            build()
+        L = self.L = C.CDLL(str(path))
+        L.orc_create.restype = C.c_void_p
+        L.orc_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_destroy.argtypes = [C.c_void_p]
+        L.orc_set_modes.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.orc_extract.restype = C.c_int
+        L.orc_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int,
+                                  C.c_void_p, C.c_void_p, C.c_int, i32p]
+        for name in ("orc_scale_factors", "orc_inv_scale_factors", "orc_level_sigma2", "orc_inv_level_sigma2"):
+            getattr(L, name).restype = f32p
+            getattr(L, name).argtypes = [C.c_void_p]
+        for name in ("orc_features_per_level", "orc_umax"):
+            getattr(L, name).restype = i32p
+            getattr(L, name).argtypes = [C.c_void_p]
+        L.orc_levels.argtypes = [C.c_void_p]
+        L.orc_level_dims.argtypes = [C.c_void_p, C.c_int, i32p, i32p]
+        L.orc_level_plane.restype = C.c_void_p
+        L.orc_level_plane.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_size_t)]
+        L.orc_level_blurred.restype = C.c_void_p
+        L.orc_level_blurred.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_size_t)]
+        L.orc_level_candidates.restype = C.c_int
+        L.orc_level_candidates.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.orc_level_selected.restype = C.c_int
+        L.orc_level_selected.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.orc_fast_atan2.restype = C.c_float
+        L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orc_sinf.restype = C.c_float
+        L.orc_sinf.argtypes = [C.c_float]
+        L.orc_cosf.restype = C.c_float
+        L.orc_cosf.argtypes = [C.c_float]
+        L.orc_cvround_f.argtypes = [C.c_float]
+        L.orc_resize_linear_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_int, C.c_int, C.c_size_t]
+        L.orc_border_reflect101.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int]
+        L.orc_fast9_16.restype = C.c_int
+        L.orc_fast9_16.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_gaussian7x7_s2.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_size_t]
+        L.orc_hamming256.restype = C.c_int
+        L.orc_hamming256.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_bf_knn2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_distribute_octree.restype = C.c_int
+        L.orc_distribute_octree.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_ic_angle.restype = C.c_float
+        L.orc_ic_angle.argtypes = [C.c_void_p, C.c_size_t, i32p]
+        L.orc_orb_descriptor.argtypes = [C.c_void_p, C.c_size_t, C.c_float, C.c_int, C.c_void_p]
+        L.orc_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                       C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_grid_build.restype = C.c_void_p
+        L.orc_grid_build.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
+        L.orc_grid_destroy.argtypes = [C.c_void_p]
+        L.orc_grid_query.restype = C.c_int
+        L.orc_grid_query.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_search_by_projection.restype = C.c_int
+        L.orc_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                               C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_float, C.c_float, C.c_int, C.c_float, C.c_void_p]
+
+    # ---- primitives ----
+    def resize(self, src: np.ndarray, drows: int, dcols: int) -> np.ndarray:
+        src = np.ascontiguousarray(src, np.uint8)
+        dst = np.empty((drows, dcols), np.uint8)
+        self.L.orc_resize_linear_u8(src.ctypes.data, src.shape[0], src.shape[1], src.strides[0],
+                                    dst.ctypes.data, drows, dcols, dst.strides[0])
+        return dst
+
+    def border101(self, img: np.ndarray, border: int) -> np.ndarray:
+        h, w = img.shape
+        out = np.zeros((h + 2 * border, w + 2 * border), np.uint8)
+        out[border:border + h, border:border + w] = img
+        self.L.orc_border_reflect101(out.ctypes.data, h, w, out.strides[0], border)
+        return out
+
+    def fast(self, img: np.ndarray, threshold: int, nonmax: bool = True) -> np.ndarray:
+        img = np.ascontiguousarray(img, np.uint8)
+        cap = img.size
+        out = np.empty(cap, CAND_DTYPE)
+        n = self.L.orc_fast9_16(img.ctypes.data, img.shape[0], img.shape[1], img.strides[0], threshold,
+                                int(nonmax), out.ctypes.data, cap)
+        return out[:n].copy()
+
+    def gaussian(self, img: np.ndarray) -> np.ndarray:
+        img = np.ascontiguousarray(img, np.uint8)
+        dst = np.empty_like(img)
+        self.L.orc_gaussian7x7_s2(img.ctypes.data, img.shape[0], img.shape[1], img.strides[0], dst.ctypes.data, dst.strides[0])
+        return dst
+
+    def knn2(self, q: np.ndarray, t: np.ndarray):
+        q = np.ascontiguousarray(q, np.uint8); t = np.ascontiguousarray(t, np.uint8)
+        idx = np.empty((q.shape[0], 2), np.int32); dist = np.empty((q.shape[0], 2), np.int32)
+        self.L.orc_bf_knn2(q.ctypes.data, q.shape[0], t.ctypes.data, t.shape[0], idx.ctypes.data, dist.ctypes.data)
+        return idx, dist
+
+    def hamming(self, a: np.ndarray, b: np.ndarray) -> int:
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        return self.L.orc_hamming256(a.ctypes.data, b.ctypes.data)
+
+    def distribute(self, cands: np.ndarray, minX, maxX, minY, maxY, N, tie_mode=0) -> np.ndarray:
+        cands = np.ascontiguousarray(cands, CAND_DTYPE)
+        out = np.empty(len(cands) + 8, CAND_DTYPE)
+        n = self.L.orc_distribute_octree(cands.ctypes.data, len(cands), minX, maxX, minY, maxY, N, tie_mode,
+                                         out.ctypes.data, len(out))
+        if n < 0:
+            raise ValueError("orc_distribute_octree failed")
+        return out[:n].copy()
+
+
+class Extractor:
+    """Mirror of ORB_SLAM3::ORBextractor on the oracle (include/ORBextractor.h:49-83)."""
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7,
+                 oracle: Oracle | None = None, tie_mode=0, trig_mode=0):
+        self.o = oracle or Oracle()
+        self.L = self.o.L
+        self.h = self.L.orc_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+        if not self.h:
+            raise ValueError("orc_create failed")
+        self.nlevels = nlevels
+        self.nfeatures = nfeatures
+        self.L.orc_set_modes(self.h, tie_mode, trig_mode)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_destroy(self.h)
+            self.h = None
+
+    def _farr(self, fn):
+        return np.ctypeslib.as_array(fn(self.h), shape=(self.nlevels,)).copy()
+
+    @property
+    def scale_factors(self): return self._farr(self.L.orc_scale_factors)
+    @property
+    def inv_scale_factors(self): return self._farr(self.L.orc_inv_scale_factors)
+    @property
+    def level_sigma2(self): return self._farr(self.L.orc_level_sigma2)
+    @property
+    def inv_level_sigma2(self): return self._farr(self.L.orc_inv_level_sigma2)
+    @property
+    def features_per_level(self): return np.ctypeslib.as_array(self.L.orc_features_per_level(self.h), shape=(self.nlevels,)).copy()
+    @property
+    def umax(self): return np.ctypeslib.as_array(self.L.orc_umax(self.h), shape=(16,)).copy()
+
+    def __call__(self, image: np.ndarray, lapping=(0, 0)):
+        """Returns (monoIndex, keypoints[KP_DTYPE], descriptors[n,32])."""
+        if image is None or image.size == 0:
+            return -1, np.empty(0, KP_DTYPE), np.empty((0, 32), np.uint8)
+        assert image.dtype == np.uint8 and image.ndim == 2 and image.strides[1] == 1
+        cap = self.nfeatures + 4 * self.nlevels + 64
+        while True:
+            kps = np.empty(cap, KP_DTYPE); desc = np.empty((cap, 32), np.uint8)
+            n = C.c_int32(0)
+            ret = self.L.orc_extract(self.h, image.ctypes.data, image.shape[0], image.shape[1], image.strides[0],
+                                     int(lapping[0]), int(lapping[1]), kps.ctypes.data, desc.ctypes.data, cap, C.byref(n))
+            if ret == -2:
+                cap = n.value + 16
+                continue
+            if ret < 0:
+                raise RuntimeError(f"orc_extract failed: {ret}")
+            return ret, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def level_dims(self, l):
+        r = C.c_int32(); c = C.c_int32()
+        self.L.orc_level_dims(self.h, l, C.byref(r), C.byref(c))
+        return r.value, c.value
+
+    def level_plane(self, l) -> np.ndarray:
+        """Padded plane (rows+38, cols+38) of mvImagePyramid[l]'s backing buffer."""
+        st = C.c_size_t()
+        p = self.L.orc_level_plane(self.h, l, C.byref(st))
+        r, c = self.level_dims(l)
+        buf = (C.c_uint8 * ((r + 38) * st.value)).from_address(p)
+        return np.frombuffer(buf, np.uint8).reshape(r + 38, st.value)[:, :c + 38].copy()
+
+    def level_blurred(self, l):
+        st = C.c_size_t()
+        p = self.L.orc_level_blurred(self.h, l, C.byref(st))
+        if not p:
+            return None
+        r, c = self.level_dims(l)
+        buf = (C.c_uint8 * (r * c)).from_address(p)
+        return np.frombuffer(buf, np.uint8).reshape(r, c).copy()
+
+    def level_candidates(self, l) -> np.ndarray:
+        p = C.c_void_p()
+        n = self.L.orc_level_candidates(self.h, l, C.byref(p))
+        if n == 0:
+            return np.empty(0, CAND_DTYPE)
+        buf = (C.c_uint8 * (n * 12)).from_address(p.value)
+        return np.frombuffer(buf, CAND_DTYPE).copy()
+
+    def level_selected(self, l):
+        p = C.c_void_p(); a = C.c_void_p()
+        n = self.L.orc_level_selected(self.h, l, C.byref(p), C.byref(a))
+        if n == 0:
+            return np.empty(0, CAND_DTYPE), np.empty(0, np.float32)
+        buf = (C.c_uint8 * (n * 12)).from_address(p.value)
+        abuf = (C.c_float * n).from_address(a.value)
+        return np.frombuffer(buf, CAND_DTYPE).copy(), np.frombuffer(abuf, np.float32).copy()
+
+
+def stereo_match(eL: Extractor, eR: Extractor, kpL, descL, kpR, descR, mb: float, mbf: float):
+    """Frame::ComputeStereoMatches on the pyramids left in eL/eR by their last __call__."""
+    kpL = np.ascontiguousarray(kpL, KP_DTYPE); kpR = np.ascontiguousarray(kpR, KP_DTYPE)
+    descL = np.ascontiguousarray(descL, np.uint8); descR = np.ascontiguousarray(descR, np.uint8)
+    n = len(kpL)
+    uR = np.empty(n, np.float32); depth = np.empty(n, np.float32)
+    bd = np.empty(n, np.int32); bs = np.empty(n, np.int32)
+    eL.L.orc_stereo_match(eL.h, eR.h, kpL.ctypes.data, n, descL.ctypes.data, kpR.ctypes.data, len(kpR),
+                          descR.ctypes.data, mb, mbf, uR.ctypes.data, depth.ctypes.data, bd.ctypes.data, bs.ctypes.data)
+    return uR, depth, bd, bs
+
+
+class Grid:
+    def __init__(self, o: Oracle, kps, minX, maxX, minY, maxY):
+        self.L = o.L
+        self.kps = np.ascontiguousarray(kps, KP_DTYPE)
+        self.g = self.L.orc_grid_build(self.kps.ctypes.data, len(self.kps), minX, maxX, minY, maxY)
+
+    def __del__(self):
+        if getattr(self, "g", None):
+            self.L.orc_grid_destroy(self.g)
+            self.g = None
+
+    def query(self, x, y, r, minLevel=-1, maxLevel=-1):
+        out = np.empty(len(self.kps) + 1, np.int32)
+        n = self.L.orc_grid_query(self.g, self.kps.ctypes.data, x, y, r, minLevel, maxLevel, out.ctypes.data, len(out))
+        return out[:n].copy()
+
+
+def search_by_projection(grid: Grid, desc, uRight, scale_factors, mp: dict, th: float, nnratio: float,
+                         far: bool = False, th_far: float = 0.0, assign=None):
+    desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(grid.kps)
+    assign = np.full(n, -1, np.int32) if assign is None else np.ascontiguousarray(assign, np.int32).copy()
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    ur = None if uRight is None else np.ascontiguousarray(uRight, np.float32)
+    f = lambda k, t: np.ascontiguousarray(mp[k], t)
+    md, px, py, pxr = f("desc", np.uint8), f("projx", np.float32), f("projy", np.float32), f("projxr", np.float32)
+    lv, vc, dp, iv = f("level", np.int32), f("viewcos", np.float32), f("depth", np.float32), f("inview", np.uint8)
+    nm = grid.L.orc_search_by_projection(grid.g, grid.kps.ctypes.data, desc.ctypes.data, n,
+                                         None if ur is None else ur.ctypes.data, sf.ctypes.data,
+                                         len(px), md.ctypes.data, px.ctypes.data, py.ctypes.data, pxr.ctypes.data,
+                                         lv.ctypes.data, vc.ctypes.data, dp.ctypes.data, iv.ctypes.data,
+                                         th, nnratio, int(far), th_far, assign.ctypes.data)
+    return nm, assign
