@@ -1,0 +1,173 @@
+/*
+ * orbx.h — C ABI of the B200-native ORB front-end (liborbx.so, CUDA sm_100a).
+ *
+ * This is the drop-in boundary for the reference's hot path (Wangkkkkkkkk/ORB-SLAM3).  The
+ * reference has no FFI: its "operator API" is the C++ class surface of ORBextractor / ORBmatcher /
+ * Frame inside libORB_SLAM3.so.  Each entry point below names the reference interface it replaces
+ * (file:line relative to the reference tree); orb-slam3_b200/cpp/ holds header-only C++ shims with
+ * the reference's own class names and signatures on top of this ABI, and INTEGRATION.md shows the
+ * change a maintainer makes.
+ *
+ * Conventions: plain pointers and sizes only; no exceptions cross the boundary; functions return
+ * >= 0 on success and a negative orbx_status on failure, with a thread-local message available from
+ * orbx_last_error().  There is NO CPU fallback: without a CUDA device every compute entry point
+ * fails with ORBX_ERR_CUDA.
+ *
+ * Threading (same contract as the reference): one extractor handle = one CUDA
+ * stream + buffers; different handles may be used from different threads concurrently; calls on the
+ * same handle must be serialised by the caller (the reference never shares an ORBextractor).
+ */
+#ifndef ORBX_H
+#define ORBX_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBX_MAX_LEVELS 16
+
+typedef enum {
+    ORBX_OK = 0,
+    ORBX_EMPTY_IMAGE = -1,   /* operator() returns -1 for an empty image, src/ORBextractor.cc:1538 */
+    ORBX_ERR_CAPACITY = -2,  /* caller's keypoint/descriptor buffers too small; *nkp holds the need */
+    ORBX_ERR_GEOMETRY = -3,  /* image too small for the 35-px cell grid (reference divides by zero) */
+    ORBX_ERR_ARG = -4,
+    ORBX_ERR_CUDA = -5,
+    ORBX_ERR_STATE = -6      /* e.g. stereo match before both extractions */
+} orbx_status;
+
+/* cv::KeyPoint memory layout (28 bytes): the shim reinterprets std::vector<cv::KeyPoint> storage. */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orbx_keypoint;
+
+typedef struct orbx_extractor orbx_extractor;
+
+const char* orbx_last_error(void);
+int orbx_version(void);
+/* number of visible CUDA devices (0 when none / no driver); never fails */
+int orbx_device_count(void);
+
+/* ---- ORBextractor -------------------------------------------------------------------------- */
+
+/* ORBextractor::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+ * include/ORBextractor.h:49-50, src/ORBextractor.cc:468-571.  `device` = CUDA ordinal. */
+int orbx_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+                int device, orbx_extractor** out);
+void orbx_destroy(orbx_extractor* e);
+
+/* GetLevels / GetScaleFactor / GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares /
+ * GetInverseScaleSigmaSquares, include/ORBextractor.h:61-81.  Returned arrays have nlevels entries
+ * and live as long as the handle. */
+int          orbx_levels(const orbx_extractor* e);
+float        orbx_scale_factor(const orbx_extractor* e);
+const float* orbx_scale_factors(const orbx_extractor* e);
+const float* orbx_inv_scale_factors(const orbx_extractor* e);
+const float* orbx_level_sigma2(const orbx_extractor* e);
+const float* orbx_inv_level_sigma2(const orbx_extractor* e);
+const int*   orbx_features_per_level(const orbx_extractor* e);   /* mnFeaturesPerLevel */
+
+/* int ORBextractor::operator()(image, mask, keypoints, descriptors, vLappingArea)
+ * include/ORBextractor.h:57-59, src/ORBextractor.cc:1534-1659.  The mask is ignored by the
+ * reference (include/ORBextractor.h:56) and has no parameter here.  `img` is a HOST CV_8UC1 image
+ * (rows x cols, `step` bytes per row).  kps/desc are caller-owned with room for `cap` keypoints
+ * (desc: cap x 32 bytes); *nkp receives the keypoint count.  Returns monoIndex (>= 0), or
+ * ORBX_EMPTY_IMAGE, or an error.  The image pyramid stays resident on the device (mvImagePyramid,
+ * include/ORBextractor.h:83) for orbx_stereo_match / orbx_get_pyramid_level. */
+int orbx_extract(orbx_extractor* e, const uint8_t* img, int rows, int cols, size_t step,
+                 int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp);
+
+/* Throughput twin of operator() (no reference analogue; identical per-frame results): nframes
+ * HOST images of equal size, frame f at imgs + f*frame_stride.  Frame f's outputs are written at
+ * kps + f*cap, desc + f*cap*32; nkp[f], mono[f] receive the count and the monoIndex. */
+int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t* imgs, int rows, int cols,
+                       size_t step, size_t frame_stride, int lap0, int lap1,
+                       orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono);
+
+/* Upper bound on the keypoints one frame can yield (quota + quadtree overshoot per level). */
+int orbx_max_keypoints(const orbx_extractor* e, int rows, int cols);
+
+/* Size the device buffers for `max_batch` frames of rows x cols ahead of time (otherwise done
+ * lazily by the first extract call). */
+int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch);
+
+/* Device-resident staging for kernel-only timing: upload once, run many times, download. */
+int orbx_upload(orbx_extractor* e, int nframes, const uint8_t* imgs, int rows, int cols,
+                size_t step, size_t frame_stride);
+int orbx_run_resident(orbx_extractor* e, int lap0, int lap1);          /* async on the handle's stream */
+int orbx_sync(orbx_extractor* e);
+int orbx_download(orbx_extractor* e, orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono);
+
+/* mvImagePyramid[level] of frame `frame` of the last extract (include/ORBextractor.h:83): copies
+ * the unpadded rows x cols level image (padded=0) or the (rows+38) x (cols+38) buffer with its
+ * reflect-101 border (padded=1) to dst (dst_step bytes per row).  *rows/*cols get the copied size. */
+int orbx_get_pyramid_level(orbx_extractor* e, int frame, int level, int padded,
+                           uint8_t* dst, size_t dst_step, int* rows, int* cols);
+
+/* Stage dumps for parity tests (no reference analogue).  stage: 0 = FAST candidates of `level` in
+ * reference order (vToDistributeKeys, src/ORBextractor.cc:1131-1140), 1 = quadtree selection in
+ * list order (:1150).  out receives (x, y, score) int32 triplets, coordinates relative to
+ * minBorder=16; angles (stage 1, may be NULL) the IC_Angle of each selected keypoint. */
+int orbx_debug_level_keys(orbx_extractor* e, int frame, int level, int stage,
+                          int32_t* out, float* angles, int cap);
+/* blurred level image (GaussianBlur 7x7 sigma 2 of the level, src/ORBextractor.cc:1606-1614) */
+int orbx_debug_blurred_level(orbx_extractor* e, int frame, int level, uint8_t* dst, size_t dst_step);
+
+/* timing of the most recent orbx_run_resident / extract on this handle, CUDA events on the handle's
+ * stream, milliseconds; stage < 0 = whole pipeline.  Stages: 0 pyramid, 1 FAST, 2 quadtree,
+ * 3 assemble, 4 blur, 5 orientation+descriptor. */
+float orbx_last_stage_ms(orbx_extractor* e, int stage);
+/* enable per-stage event recording (off by default: events serialise nothing but cost launches) */
+void orbx_set_profiling(orbx_extractor* e, int on);
+/* number of kernel launches issued by this handle since creation */
+long long orbx_launch_count(const orbx_extractor* e);
+
+/* ---- ORBmatcher / Frame -------------------------------------------------------------------- */
+
+/* static int ORBmatcher::DescriptorDistance(const cv::Mat&, const cv::Mat&)
+ * include/ORBmatcher.h:42, src/ORBmatcher.cc:2911-2931: 256-bit Hamming distance (host inline). */
+int orbx_hamming256(const void* a, const void* b);
+
+/* void Frame::ComputeStereoMatches()  include/Frame.h:114, src/Frame.cc:1027-1276.
+ * Uses the keypoints, descriptors and pyramids left on the device by the preceding extract calls on
+ * eL and eR (frame slot `frame` of each).  uRight/depth: N_left floats (mvuRight, mvDepth). */
+int orbx_stereo_match(orbx_extractor* eL, orbx_extractor* eR, int frame, float mb, float mbf,
+                      float* uRight, float* depth, int cap);
+/* batch twin: all frames of the last extract; outputs at uRight + f*cap, depth + f*cap. */
+int orbx_stereo_match_batch(orbx_extractor* eL, orbx_extractor* eR, float mb, float mbf,
+                            float* uRight, float* depth, int cap);
+/* resident variant (results stay on device; for kernel timing) */
+int orbx_stereo_match_resident(orbx_extractor* eL, orbx_extractor* eR, float mb, float mbf);
+
+/* cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, k=2) as used by Frame::ComputeStereoFishEyeMatches
+ * src/Frame.cc:1440-1480 (matcher at src/Frame.cc:48).  HOST descriptors in, out_idx/out_dist
+ * [nq][2] out (missing neighbour = -1); ties by ascending train index. */
+int orbx_knn2_hamming(int device, const uint8_t* q, int nq, const uint8_t* t, int nt,
+                      int32_t* out_idx, int32_t* out_dist);
+
+/* int ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints)
+ * include/ORBmatcher.h:46, src/ORBmatcher.cc:45-168 (F.Nleft == -1 branch: mono / rectified stereo).
+ * Frame side: n keypoints (undistorted, mvKeysUn), descriptors, optional uRight (NULL for mono),
+ * image bounds [minX,maxX]x[minY,maxY] (Frame::ComputeImageBounds src/Frame.cc:978-1009), scale
+ * factors.  Map-point side (SoA, filled by Frame::isInFrustum src/Frame.cc:603-711): descriptor,
+ * mTrackProjX/Y/XR, mnTrackScaleLevel, mTrackViewCos, mTrackDepth, mbTrackInView.
+ * assign[n] in/out: -1 = keypoint free, >= 0 = already holds a map point (F.mvpMapPoints[idx] with
+ * Observations() > 0, src/ORBmatcher.cc:102-104); on return newly matched keypoints hold the index
+ * of their map point.  Returns nmatches. */
+int orbx_search_by_projection(int device,
+                              const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+                              float minX, float maxX, float minY, float maxY,
+                              const float* scaleFactors, int nlevels,
+                              int nmp, const uint8_t* mp_desc, const float* mp_projx, const float* mp_projy,
+                              const float* mp_projxr, const int32_t* mp_level, const float* mp_viewcos,
+                              const float* mp_depth, const uint8_t* mp_inview,
+                              float th, float nnratio, int bFarPoints, float thFarPoints,
+                              int32_t* assign);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H */

@@ -1,0 +1,423 @@
+// capi.cu — C ABI of the extractor (include/orbx.h): handle life cycle, device buffers, the
+// extraction pipeline and host<->device transfers.  No CPU fallback: every compute entry point needs
+// a CUDA device and fails with ORBX_ERR_CUDA otherwise.
+#include "orbx_host.h"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+static thread_local char g_err[512] = "";
+
+void orbx_set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+#define CUDA_TRY(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            orbx_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return ORBX_ERR_CUDA;                                                              \
+        }                                                                                      \
+    } while (0)
+
+extern "C" const char* orbx_last_error(void) { return g_err; }
+extern "C" int orbx_version(void) { return 100; }
+extern "C" int orbx_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int orbx_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+                           int device, orbx_extractor** out)
+{
+    if (!out) { orbx_set_error("out is NULL"); return ORBX_ERR_ARG; }
+    *out = nullptr;
+    if (nlevels < 1 || nlevels > ORBX_MAX_LEVELS || nfeatures < 0 || !(scaleFactor > 1.0f)) {
+        orbx_set_error("bad parameters: nfeatures=%d scaleFactor=%g nlevels=%d (1..%d)", nfeatures, scaleFactor, nlevels, ORBX_MAX_LEVELS);
+        return ORBX_ERR_ARG;
+    }
+    int ndev = orbx_device_count();
+    if (device < 0 || device >= ndev) {
+        orbx_set_error("CUDA device %d not available (%d visible); this library has no CPU path", device, ndev);
+        return ORBX_ERR_CUDA;
+    }
+    orbx_extractor* e = new orbx_extractor();
+    e->nfeatures = nfeatures; e->nlevels = nlevels; e->iniTh = iniThFAST; e->minTh = minThFAST;
+    e->scaleFactorF = scaleFactor;
+    e->device = device; e->reserved = false; e->profiling = false; e->launches = 0; e->last_nframes = 0;
+    e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr;
+    memset(&e->G, 0, sizeof(e->G)); memset(&e->D, 0, sizeof(e->D));
+    memset(e->stage_ms, 0, sizeof(e->stage_ms));
+    orbx_init_tables(e);
+    cudaError_t ce = cudaSetDevice(device);
+    if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    for (int i = 0; i <= ORBX_NSTAGES && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->ev[i]);
+    if (ce != cudaSuccess) {
+        orbx_set_error("CUDA init failed: %s", cudaGetErrorString(ce));
+        delete e;
+        return ORBX_ERR_CUDA;
+    }
+    *out = e;
+    return ORBX_OK;
+}
+
+static void free_device(orbx_extractor* e)
+{
+    cudaSetDevice(e->device);
+    for (void* p : e->allocs) cudaFree(p);
+    e->allocs.clear();
+    e->reserved = false;
+    e->last_nframes = 0;
+    e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr;
+}
+
+extern "C" void orbx_destroy(orbx_extractor* e)
+{
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    free_device(e);
+    for (int i = 0; i <= ORBX_NSTAGES; i++) cudaEventDestroy(e->ev[i]);
+    cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+extern "C" int orbx_levels(const orbx_extractor* e) { return e->nlevels; }
+extern "C" float orbx_scale_factor(const orbx_extractor* e) { return (float)e->scaleFactorD; }
+extern "C" const float* orbx_scale_factors(const orbx_extractor* e) { return e->sf; }
+extern "C" const float* orbx_inv_scale_factors(const orbx_extractor* e) { return e->isf; }
+extern "C" const float* orbx_level_sigma2(const orbx_extractor* e) { return e->sig2; }
+extern "C" const float* orbx_inv_level_sigma2(const orbx_extractor* e) { return e->isig2; }
+extern "C" const int* orbx_features_per_level(const orbx_extractor* e) { return e->nper; }
+
+extern "C" int orbx_max_keypoints(const orbx_extractor* e, int rows, int cols)
+{
+    FrameGeom G;
+    std::vector<std::vector<ResizeTapX>> tx;
+    std::vector<std::vector<ResizeTapY>> ty;
+    int r = orbx_compute_geometry(e, rows, cols, 1, &G, &tx, &ty);
+    if (r != 0) { orbx_set_error("image %dx%d too small for %d pyramid levels", cols, rows, e->nlevels); return r; }
+    return G.out_cap;
+}
+
+template <typename T>
+static int dev_alloc(orbx_extractor* e, T** p, size_t count)
+{
+    void* q = nullptr;
+    CUDA_TRY(cudaMalloc(&q, count * sizeof(T) + 256));
+    e->allocs.push_back(q);
+    *p = (T*)q;
+    return 0;
+}
+
+extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch)
+{
+    if (!e || rows <= 0 || cols <= 0 || max_batch <= 0) { orbx_set_error("bad reserve arguments"); return ORBX_ERR_ARG; }
+    if (e->reserved && e->G.rows == rows && e->G.cols == cols && e->G.batch >= max_batch) return ORBX_OK;
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    free_device(e);
+    FrameGeom G;
+    std::vector<std::vector<ResizeTapX>> tx;
+    std::vector<std::vector<ResizeTapY>> ty;
+    int r = orbx_compute_geometry(e, rows, cols, max_batch, &G, &tx, &ty);
+    if (r != 0) { orbx_set_error("image %dx%d too small for %d pyramid levels (35-px cell grid)", cols, rows, e->nlevels); return r; }
+    DevBuffers D;
+    memset(&D, 0, sizeof(D));
+    const size_t B = (size_t)max_batch;
+    D.in_pitch = (cols + 127) / 128 * 128;
+    int rc = 0;
+    rc |= dev_alloc(e, &D.input, B * rows * D.in_pitch);
+    for (int l = 0; l < G.nlevels && !rc; l++) {
+        rc |= dev_alloc(e, &G.L[l].pyr, B * G.L[l].plane_bytes);
+        rc |= dev_alloc(e, &G.L[l].blur, B * G.L[l].plane_bytes);
+        if (!rc) {
+            // zero once: bytes outside the padded image are never written by the kernels
+            if (cudaMemsetAsync(G.L[l].pyr, 0, B * G.L[l].plane_bytes, e->stream) != cudaSuccess) rc = ORBX_ERR_CUDA;
+            if (cudaMemsetAsync(G.L[l].blur, 0, B * G.L[l].plane_bytes, e->stream) != cudaSuccess) rc = ORBX_ERR_CUDA;
+        }
+        if (l > 0 && !rc) {
+            ResizeTapX* dx; ResizeTapY* dy;
+            rc |= dev_alloc(e, &dx, tx[l].size());
+            rc |= dev_alloc(e, &dy, ty[l].size());
+            if (!rc) {
+                CUDA_TRY(cudaMemcpy(dx, tx[l].data(), tx[l].size() * sizeof(ResizeTapX), cudaMemcpyHostToDevice));
+                CUDA_TRY(cudaMemcpy(dy, ty[l].data(), ty[l].size() * sizeof(ResizeTapY), cudaMemcpyHostToDevice));
+                G.L[l].tapx = dx; G.L[l].tapy = dy;
+            }
+        }
+    }
+    D.nodetab_per_frame = (long long)octree_nodetab_ints(G);
+    if (!rc) rc |= dev_alloc(e, &D.cellcnt, B * G.cells_per_frame);
+    if (!rc) rc |= dev_alloc(e, &D.celloff, B * G.cells_per_frame);
+    if (!rc) rc |= dev_alloc(e, &D.cellkey, B * G.keys_per_frame);
+    if (!rc) rc |= dev_alloc(e, &D.cand, B * G.cand_per_frame);
+    if (!rc) rc |= dev_alloc(e, &D.candnode, B * G.cand_per_frame);
+    if (!rc) rc |= dev_alloc(e, &D.nodetab, B * G.nlevels * D.nodetab_per_frame);
+    if (!rc) rc |= dev_alloc(e, &D.sel, B * G.sel_per_frame);
+    if (!rc) rc |= dev_alloc(e, &D.selcnt, B * G.nlevels);
+    if (!rc) rc |= dev_alloc(e, &D.candcnt, B * G.nlevels);
+    if (!rc) rc |= dev_alloc(e, &D.angle, B * G.sel_per_frame);
+    if (!rc) rc |= dev_alloc(e, &D.outidx, B * G.sel_per_frame);
+    if (!rc) rc |= dev_alloc(e, &D.kps, B * G.out_cap);
+    if (!rc) rc |= dev_alloc(e, &D.desc, B * G.out_cap * 32);
+    if (!rc) rc |= dev_alloc(e, &D.counts, B * 2);
+    if (!rc) rc |= dev_alloc(e, &e->d_uright, B * G.out_cap);
+    if (!rc) rc |= dev_alloc(e, &e->d_depth, B * G.out_cap);
+    if (rc) { free_device(e); return ORBX_ERR_CUDA; }
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->G = G; e->D = D; e->reserved = true;
+    return ORBX_OK;
+}
+
+static int upload_frames(orbx_extractor* e, int slot0, int nframes, const uint8_t* imgs, size_t step, size_t frame_stride)
+{
+    const FrameGeom& G = e->G;
+    if (frame_stride == step * (size_t)G.rows) {
+        // frames are back to back: one 2-D copy of nframes*rows rows
+        CUDA_TRY(cudaMemcpy2DAsync(e->D.input + (size_t)slot0 * G.rows * e->D.in_pitch, e->D.in_pitch, imgs, step,
+                                   G.cols, (size_t)nframes * G.rows, cudaMemcpyHostToDevice, e->stream));
+    } else {
+        for (int f = 0; f < nframes; f++)
+            CUDA_TRY(cudaMemcpy2DAsync(e->D.input + (size_t)(slot0 + f) * G.rows * e->D.in_pitch, e->D.in_pitch,
+                                       imgs + (size_t)f * frame_stride, step, G.cols, G.rows, cudaMemcpyHostToDevice, e->stream));
+    }
+    return 0;
+}
+
+// the whole extraction pipeline on frame slots [0, nframes), asynchronous on the handle's stream
+static int run_pipeline(orbx_extractor* e, int nframes, int lap0, int lap1)
+{
+    const FrameGeom& G = e->G;
+    const DevBuffers& D = e->D;
+    cudaStream_t s = e->stream;
+    const bool prof = e->profiling;
+    if (prof) cudaEventRecord(e->ev[0], s);
+    e->launches += launch_pyramid(G, D, nframes, s);
+    if (prof) cudaEventRecord(e->ev[1], s);
+    e->launches += launch_fast(G, D, nframes, s);
+    if (prof) cudaEventRecord(e->ev[2], s);
+    e->launches += launch_octree(G, D, nframes, s);
+    if (prof) cudaEventRecord(e->ev[3], s);
+    e->launches += launch_assemble(G, D, nframes, lap0, lap1, s);
+    if (prof) cudaEventRecord(e->ev[4], s);
+    e->launches += launch_blur(G, D, nframes, s);
+    if (prof) cudaEventRecord(e->ev[5], s);
+    e->launches += launch_describe(G, D, nframes, s);
+    if (prof) cudaEventRecord(e->ev[6], s);
+    e->last_nframes = nframes;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+static void collect_stage_times(orbx_extractor* e)
+{
+    if (!e->profiling) return;
+    for (int i = 0; i < ORBX_NSTAGES; i++) cudaEventElapsedTime(&e->stage_ms[i], e->ev[i], e->ev[i + 1]);
+    cudaEventElapsedTime(&e->stage_ms[ORBX_NSTAGES], e->ev[0], e->ev[ORBX_NSTAGES]);
+}
+
+extern "C" int orbx_upload(orbx_extractor* e, int nframes, const uint8_t* imgs, int rows, int cols,
+                           size_t step, size_t frame_stride)
+{
+    if (!e || !imgs || nframes <= 0) { orbx_set_error("bad upload arguments"); return ORBX_ERR_ARG; }
+    int r = orbx_reserve(e, rows, cols, nframes);
+    if (r) return r;
+    CUDA_TRY(cudaSetDevice(e->device));
+    r = upload_frames(e, 0, nframes, imgs, step, frame_stride);
+    if (r) return r;
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->last_nframes = -nframes;     // uploaded, not yet run
+    return ORBX_OK;
+}
+
+extern "C" int orbx_run_resident(orbx_extractor* e, int lap0, int lap1)
+{
+    if (!e || !e->reserved || e->last_nframes == 0) { orbx_set_error("run_resident before upload"); return ORBX_ERR_STATE; }
+    CUDA_TRY(cudaSetDevice(e->device));
+    return run_pipeline(e, e->last_nframes < 0 ? -e->last_nframes : e->last_nframes, lap0, lap1);
+}
+
+extern "C" int orbx_sync(orbx_extractor* e)
+{
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    collect_stage_times(e);
+    return ORBX_OK;
+}
+
+static int download_results(orbx_extractor* e, int slot0, int nframes, orbx_keypoint* kps, uint8_t* desc, int cap,
+                            int* counts_host /* 2*nframes */)
+{
+    const FrameGeom& G = e->G;
+    const int ncopy = cap < G.out_cap ? cap : G.out_cap;
+    CUDA_TRY(cudaMemcpyAsync(counts_host, e->D.counts + 2 * slot0, sizeof(int) * 2 * nframes, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbx_keypoint), e->D.kps + (size_t)slot0 * G.out_cap,
+                               (size_t)G.out_cap * sizeof(orbx_keypoint), (size_t)ncopy * sizeof(orbx_keypoint), nframes,
+                               cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaMemcpy2DAsync(desc, (size_t)cap * 32, e->D.desc + (size_t)slot0 * G.out_cap * 32, (size_t)G.out_cap * 32,
+                               (size_t)ncopy * 32, nframes, cudaMemcpyDeviceToHost, e->stream));
+    return 0;
+}
+
+extern "C" int orbx_download(orbx_extractor* e, orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono)
+{
+    if (!e || !e->reserved || e->last_nframes <= 0) { orbx_set_error("download before run"); return ORBX_ERR_STATE; }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const int n = e->last_nframes;
+    std::vector<int> counts(2 * (size_t)n);
+    int r = download_results(e, 0, n, kps, desc, cap, counts.data());
+    if (r) return r;
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    collect_stage_times(e);
+    int rc = ORBX_OK;
+    for (int f = 0; f < n; f++) {
+        if (nkp) nkp[f] = counts[2 * f];
+        if (mono) mono[f] = counts[2 * f + 1];
+        if (counts[2 * f] > cap) rc = ORBX_ERR_CAPACITY;
+    }
+    if (rc) orbx_set_error("keypoint capacity %d too small", cap);
+    return rc;
+}
+
+extern "C" int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t* imgs, int rows, int cols,
+                                  size_t step, size_t frame_stride, int lap0, int lap1,
+                                  orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono)
+{
+    if (!e) { orbx_set_error("null handle"); return ORBX_ERR_ARG; }
+    if (!imgs || rows <= 0 || cols <= 0 || nframes <= 0) { orbx_set_error("empty image"); return ORBX_EMPTY_IMAGE; }
+    if (!kps || !desc || cap <= 0 || step < (size_t)cols) { orbx_set_error("bad output buffers / step"); return ORBX_ERR_ARG; }
+    int r;
+    if (!(e->reserved && e->G.rows == rows && e->G.cols == cols)) {
+        // lazy sizing: bound the device footprint to ~8 GB
+        FrameGeom G;
+        std::vector<std::vector<ResizeTapX>> tx; std::vector<std::vector<ResizeTapY>> ty;
+        r = orbx_compute_geometry(e, rows, cols, 1, &G, &tx, &ty);
+        if (r) { orbx_set_error("image %dx%d too small for %d pyramid levels (35-px cell grid)", cols, rows, e->nlevels); return r; }
+        long long per = (long long)rows * ((cols + 127) / 128 * 128) + G.keys_per_frame * 12;
+        for (int l = 0; l < G.nlevels; l++) per += 2 * G.L[l].plane_bytes;
+        long long b = (8LL << 30) / per;
+        if (b < 1) b = 1;
+        if (b > nframes) b = nframes;
+        if (b > 512) b = 512;
+        r = orbx_reserve(e, rows, cols, (int)b);
+        if (r) return r;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const int B = e->G.batch;
+    std::vector<int> counts(2 * (size_t)B);
+    int rc = ORBX_OK;
+    for (int f0 = 0; f0 < nframes; f0 += B) {
+        const int nb = nframes - f0 < B ? nframes - f0 : B;
+        r = upload_frames(e, 0, nb, imgs + (size_t)f0 * frame_stride, step, frame_stride);
+        if (r) return r;
+        r = run_pipeline(e, nb, lap0, lap1);
+        if (r) return r;
+        r = download_results(e, 0, nb, kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, counts.data());
+        if (r) return r;
+        CUDA_TRY(cudaStreamSynchronize(e->stream));
+        collect_stage_times(e);
+        for (int f = 0; f < nb; f++) {
+            if (nkp) nkp[f0 + f] = counts[2 * f];
+            if (mono) mono[f0 + f] = counts[2 * f + 1];
+            if (counts[2 * f] > cap) rc = ORBX_ERR_CAPACITY;
+        }
+    }
+    if (rc) orbx_set_error("keypoint capacity %d too small", cap);
+    return rc;
+}
+
+extern "C" int orbx_extract(orbx_extractor* e, const uint8_t* img, int rows, int cols, size_t step,
+                            int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp)
+{
+    int n = 0, mono = 0;
+    if (nkp) *nkp = 0;
+    int r = orbx_extract_batch(e, 1, img, rows, cols, step, step * (size_t)(rows > 0 ? rows : 0), lap0, lap1, kps, desc, cap, &n, &mono);
+    if (nkp) *nkp = n;
+    if (r < 0) return r;
+    return mono;
+}
+
+extern "C" int orbx_get_pyramid_level(orbx_extractor* e, int frame, int level, int padded,
+                                      uint8_t* dst, size_t dst_step, int* rows, int* cols)
+{
+    if (!e || !e->reserved || e->last_nframes <= 0 || frame < 0 || frame >= e->last_nframes || level < 0 || level >= e->nlevels) {
+        orbx_set_error("pyramid level not available"); return ORBX_ERR_STATE;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const LevelGeom& L = e->G.L[level];
+    const int r = padded ? L.h + 2 * ORBX_EDGE : L.h, c = padded ? L.w + 2 * ORBX_EDGE : L.w;
+    if (rows) *rows = r;
+    if (cols) *cols = c;
+    if (!dst) return ORBX_OK;
+    const uint8_t* src = L.pyr + (size_t)frame * L.plane_bytes +
+                         (padded ? (size_t)(ORBX_XOFF - ORBX_EDGE) : (size_t)ORBX_YOFF * L.pitch + ORBX_XOFF);
+    CUDA_TRY(cudaMemcpy2DAsync(dst, dst_step, src, L.pitch, c, r, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return ORBX_OK;
+}
+
+extern "C" int orbx_debug_blurred_level(orbx_extractor* e, int frame, int level, uint8_t* dst, size_t dst_step)
+{
+    if (!e || !e->reserved || e->last_nframes <= 0 || frame < 0 || frame >= e->last_nframes || level < 0 || level >= e->nlevels) {
+        orbx_set_error("blurred level not available"); return ORBX_ERR_STATE;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const LevelGeom& L = e->G.L[level];
+    const uint8_t* src = L.blur + (size_t)frame * L.plane_bytes + (size_t)ORBX_YOFF * L.pitch + ORBX_XOFF;
+    CUDA_TRY(cudaMemcpy2DAsync(dst, dst_step, src, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return ORBX_OK;
+}
+
+extern "C" int orbx_debug_level_keys(orbx_extractor* e, int frame, int level, int stage,
+                                     int32_t* out, float* angles, int cap)
+{
+    if (!e || !e->reserved || e->last_nframes <= 0 || frame < 0 || frame >= e->last_nframes || level < 0 || level >= e->nlevels) {
+        orbx_set_error("level keys not available"); return ORBX_ERR_STATE;
+    }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const FrameGeom& G = e->G;
+    const LevelGeom& L = G.L[level];
+    int n = 0;
+    const int* cntp = (stage == 0 ? e->D.candcnt : e->D.selcnt) + frame * G.nlevels + level;
+    CUDA_TRY(cudaMemcpyAsync(&n, cntp, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    if (!out) return n;
+    const int m = n < cap ? n : cap;
+    std::vector<uint32_t> keys((size_t)m);
+    const uint32_t* src = stage == 0 ? e->D.cand + (size_t)frame * G.cand_per_frame + L.cand_base
+                                     : e->D.sel + (size_t)frame * G.sel_per_frame + L.sel_base;
+    if (m > 0) CUDA_TRY(cudaMemcpyAsync(keys.data(), src, sizeof(uint32_t) * m, cudaMemcpyDeviceToHost, e->stream));
+    if (m > 0 && stage == 1 && angles)
+        CUDA_TRY(cudaMemcpyAsync(angles, e->D.angle + (size_t)frame * G.sel_per_frame + L.sel_base, sizeof(float) * m,
+                                 cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    for (int i = 0; i < m; i++) {
+        out[3 * i] = (int32_t)KEY_X(keys[i]); out[3 * i + 1] = (int32_t)KEY_Y(keys[i]); out[3 * i + 2] = (int32_t)KEY_S(keys[i]);
+    }
+    return n;
+}
+
+extern "C" float orbx_last_stage_ms(orbx_extractor* e, int stage)
+{
+    if (!e || stage >= ORBX_NSTAGES) return -1.f;
+    return e->stage_ms[stage < 0 ? ORBX_NSTAGES : stage];
+}
+extern "C" void orbx_set_profiling(orbx_extractor* e, int on) { if (e) e->profiling = on != 0; }
+extern "C" long long orbx_launch_count(const orbx_extractor* e) { return e ? e->launches : 0; }
+
+extern "C" int orbx_hamming256(const void* a, const void* b)
+{
+    uint64_t x[4], y[4];
+    memcpy(x, a, 32); memcpy(y, b, 32);
+    return __builtin_popcountll(x[0] ^ y[0]) + __builtin_popcountll(x[1] ^ y[1]) +
+           __builtin_popcountll(x[2] ^ y[2]) + __builtin_popcountll(x[3] ^ y[3]);
+}

@@ -1,0 +1,35 @@
+// orbx_host.h — host-side extractor handle.
+#pragma once
+#include "orbx_internal.h"
+#include <vector>
+
+#define ORBX_NSTAGES 6
+
+struct orbx_extractor {
+    // ORBextractor members (include/ORBextractor.h:93-112)
+    int nfeatures, nlevels, iniTh, minTh;
+    float scaleFactorF;
+    double scaleFactorD;
+    float sf[ORBX_MAX_LEVELS], isf[ORBX_MAX_LEVELS], sig2[ORBX_MAX_LEVELS], isig2[ORBX_MAX_LEVELS];
+    int nper[ORBX_MAX_LEVELS];
+    // device state
+    int device;
+    cudaStream_t stream;
+    bool reserved;
+    FrameGeom G;
+    DevBuffers D;
+    std::vector<void*> allocs;           // every cudaMalloc of this handle
+    cudaEvent_t ev[ORBX_NSTAGES + 1];
+    bool profiling;
+    float stage_ms[ORBX_NSTAGES + 1];    // [ORBX_NSTAGES] = total
+    long long launches;
+    int last_nframes;                    // frames processed by the last run (valid pyramids / outputs)
+    // stereo-match outputs (device), sized out_cap per frame slot
+    float* d_uright; float* d_depth;
+    int* d_st_scratch;
+};
+
+void orbx_init_tables(orbx_extractor* e);
+int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch, FrameGeom* G,
+                          std::vector<std::vector<ResizeTapX>>* tapx, std::vector<std::vector<ResizeTapY>>* tapy);
+void orbx_set_error(const char* fmt, ...);

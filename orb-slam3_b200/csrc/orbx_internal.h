@@ -1,0 +1,103 @@
+// orbx_internal.h — device data layout and kernel launchers of the B200 ORB front-end.
+//
+// HBM layout (all per extractor handle, sized for `batch` frame slots):
+//   pyr[l]   : batch planes of level l, each `prow x pitch` bytes; interior pixel (0,0) at byte
+//              ORBX_YOFF*pitch + ORBX_XOFF (XOFF=32 keeps interior rows 32B-sector aligned, pitch is a
+//              multiple of 128); the 19-px reflect-101 border of mvImagePyramid sits around it.
+//   blur[l]  : same geometry, GaussianBlur(7x7, s=2) of the level (interior only).
+//   cellcnt  : per frame, per cell (all levels flattened) number of FAST keypoints kept by the cell.
+//   cellkey  : per frame, per cell `cell_cap[l]` packed keys  (y<<20 | x<<8 | score), cell raster order.
+//   cand     : per frame, per level compacted candidate list in reference order (vToDistributeKeys).
+//   sel      : per frame, per level quadtree selection in std::list order (+ count), packed keys.
+//   out      : per frame `out_cap` cv::KeyPoint records + 32-byte descriptors + {nkp, mono}.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/orbx.h"
+
+#define ORBX_EDGE 19
+#define ORBX_XOFF 32
+#define ORBX_YOFF 19
+#define ORBX_MINB 16          // EDGE_THRESHOLD-3, src/ORBextractor.cc:1053
+#define ORBX_HALF_PATCH 15
+#define ORBX_PATCH 31
+
+#define KEY_X(k) (((k) >> 8) & 0xFFFu)
+#define KEY_Y(k) ((k) >> 20)
+#define KEY_S(k) ((k) & 0xFFu)
+#define MAKE_KEY(x, y, s) (((uint32_t)(y) << 20) | ((uint32_t)(x) << 8) | (uint32_t)(s))
+
+struct ResizeTapX { short s0, s1, a0, a1; };   // source cols (clipped) and 11-bit coefficients
+struct ResizeTapY { short s0, s1, b0, b1; };
+
+struct LevelGeom {
+    int w, h;                 // level image size (cols, rows)
+    int pitch, prow;          // plane row pitch (bytes) and padded row count (h + 38)
+    long long plane_bytes;    // pitch * prow
+    uint8_t* pyr;             // level planes of all frame slots
+    uint8_t* blur;
+    // FAST cell grid, src/ORBextractor.cc:1053-1072
+    int maxBX, maxBY;         // maxBorderX/Y (minBorder = 16)
+    int nCols, nRows, wCell, hCell;
+    int cell_base;            // first cell of this level in a frame's flattened cell list
+    int cell_cap;             // key slots per cell
+    long long key_base;       // first slot of this level in a frame's cellkey array
+    // quadtree
+    int N;                    // mnFeaturesPerLevel[level]
+    int nIni;                 // root nodes, :695
+    float hX;                 // :698
+    int cand_cap;             // capacity of compact candidate list
+    long long cand_base;      // offset in a frame's cand array
+    int node_cap;             // capacity of node tables
+    int sel_cap;              // capacity of selection list
+    int sel_base;             // offset in a frame's sel arrays
+    // descriptor stage
+    float scale;              // mvScaleFactor[level]
+    float patch_size;         // (float)(int)(31*scale), :1161
+    // resize taps producing THIS level from level-1, indexed by padded coordinate (border folded in)
+    const ResizeTapX* tapx;   // w + 38 entries
+    const ResizeTapY* tapy;   // h + 38 entries
+};
+
+struct FrameGeom {
+    int nlevels;
+    int rows, cols;           // input image size
+    int batch;                // frame slots
+    int cells_per_frame;
+    long long keys_per_frame; // cellkey slots per frame
+    long long cand_per_frame;
+    int sel_per_frame;        // == out_cap
+    int out_cap;
+    int iniTh, minTh;
+    LevelGeom L[ORBX_MAX_LEVELS];
+};
+
+struct DevBuffers {
+    uint8_t* input;           // batch x rows x in_pitch staging of the uploaded frames
+    int in_pitch;
+    uint32_t* cellcnt;        // [batch][cells_per_frame]
+    uint32_t* cellkey;        // [batch][keys_per_frame]
+    int* celloff;             // [batch][cells_per_frame] quadtree scratch: prefix of cellcnt per level
+    uint32_t* cand;           // [batch][cand_per_frame]
+    uint32_t* candnode;       // [batch][cand_per_frame]  quadtree scratch: node of each candidate
+    int* nodetab;             // quadtree scratch: node tables
+    long long nodetab_per_frame;
+    uint32_t* sel;            // [batch][sel_per_frame]
+    int* selcnt;              // [batch][nlevels]
+    int* candcnt;             // [batch][nlevels]
+    float* angle;             // [batch][sel_per_frame]
+    int* outidx;              // [batch][sel_per_frame] final row of each selected keypoint
+    orbx_keypoint* kps;       // [batch][out_cap]
+    uint8_t* desc;            // [batch][out_cap][32]
+    int* counts;              // [batch][2] = {nkp, mono}
+};
+
+// kernel launchers (each returns the number of kernel launches it issued)
+int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
+int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
+int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
+int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int lap0, int lap1, cudaStream_t s);
+int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
+int launch_describe(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
+size_t octree_nodetab_ints(const FrameGeom& G);   // ints of node scratch per frame
+void octree_assign_node_offsets(FrameGeom& G);

@@ -1,0 +1,106 @@
+"""GPU parity of the extraction path (through the C ABI) against the CPU oracle, stage by stage.
+
+Bars (BASELINE.json north_star): pyramid pixels, FAST keypoint sets, quadtree selection bit-exact;
+angles within 1e-3 deg (we demand bit-exact); descriptors bit-exact.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+CASES = [
+    # name, rows, cols, nfeatures, lapping, seed
+    ("C1-mono", 480, 752, 1000, (0, 1000), 0),
+    ("C2-eye", 480, 752, 1200, (0, 0), 3),
+    ("C3-fisheye-partial", 512, 512, 1000, (128, 383), 5),
+    ("C3-fisheye-full", 512, 512, 1000, (0, 511), 6),
+    ("C4-kitti", 376, 1241, 2000, (0, 0), 7),
+    ("ini-5x", 480, 752, 5000, (0, 1000), 8),
+    ("small", 256, 320, 300, (0, 0), 9),
+]
+
+
+def _cand_arr(c):
+    return np.stack([c["x"], c["y"], c["score"]], axis=1).astype(np.int32) if len(c) else np.empty((0, 3), np.int32)
+
+
+@pytest.mark.parametrize("name,rows,cols,nf,lap,seed", CASES)
+def test_extract_stages_match_oracle(pkg, orc, oracle, name, rows, cols, nf, lap, seed):
+    img = pkg.synth.synth_frame(rows, cols, seed)
+    E = orc.Extractor(nf, oracle=oracle)
+    mono_o, kps_o, desc_o = E(img, lap)
+    X = pkg.ORBextractor(nf)
+    mono_g, kps_g, desc_g = X(img, lap)
+    # constructor tables
+    assert np.array_equal(X.GetScaleFactors(), E.scale_factors)
+    assert np.array_equal(X.GetInverseScaleFactors(), E.inv_scale_factors)
+    assert np.array_equal(X.GetScaleSigmaSquares(), E.level_sigma2)
+    assert np.array_equal(X.GetInverseScaleSigmaSquares(), E.inv_level_sigma2)
+    assert np.array_equal(X.features_per_level(), E.features_per_level)
+    for l in range(8):
+        assert np.array_equal(X.pyramid_level(l, padded=True), E.level_plane(l)), f"pyramid level {l}"
+        assert np.array_equal(X.level_keys(l, 0), _cand_arr(E.level_candidates(l))), f"FAST candidates level {l}"
+        sel_g, ang_g = X.level_keys(l, 1)
+        sel_o, ang_o = E.level_selected(l)
+        assert np.array_equal(sel_g, _cand_arr(sel_o)), f"quadtree selection level {l}"
+        assert np.array_equal(ang_g, ang_o), f"angles level {l}: max diff {np.abs(ang_g - ang_o).max() if len(ang_o) else 0}"
+        b = E.level_blurred(l)
+        if b is not None:
+            assert np.array_equal(X.blurred_level(l), b), f"blur level {l}"
+    assert mono_g == mono_o
+    assert len(kps_g) == len(kps_o)
+    for fld in kps_o.dtype.names:
+        assert np.array_equal(kps_g[fld], kps_o[fld]), fld
+    assert np.array_equal(desc_g, desc_o)
+    X.close()
+
+
+def test_batch_equals_single(pkg, orc, oracle):
+    rows, cols, nf = 480, 752, 1000
+    frames = np.stack([pkg.synth.synth_frame(rows, cols, 100 + s, bands=(s % 2 == 0)) for s in range(6)])
+    X = pkg.ORBextractor(nf)
+    mono, nkp, kps, desc = X.extract_batch(frames, (0, 0))
+    E = orc.Extractor(nf, oracle=oracle)
+    for f in range(len(frames)):
+        m, k, d = E(frames[f], (0, 0))
+        assert mono[f] == m and nkp[f] == len(k)
+        assert np.array_equal(kps[f, :nkp[f]], k)
+        assert np.array_equal(desc[f, :nkp[f]], d)
+    # a second call on the same handle with fewer frames and a non-contiguous row step
+    big = np.zeros((2, rows, cols + 40), np.uint8)
+    big[:, :, :cols] = frames[:2]
+    m2, k2, d2 = X(big[1, :, :cols], (0, 0))
+    m, k, d = E(frames[1], (0, 0))
+    assert m2 == m and np.array_equal(k2, k) and np.array_equal(d2, d)
+    X.close()
+
+
+def test_flat_and_low_texture_frames(pkg, orc, oracle):
+    """Empty cells, minThFAST retries and levels with no keypoints at all."""
+    rows, cols = 480, 752
+    flat = np.full((rows, cols), 77, np.uint8)
+    rng = np.random.default_rng(4)
+    sparse = flat.copy()
+    for _ in range(12):
+        y, x = int(rng.integers(40, rows - 40)), int(rng.integers(40, cols - 40))
+        sparse[y:y + 9, x:x + 9] = 200
+    grad = np.tile(np.linspace(0, 255, cols).astype(np.uint8), (rows, 1))
+    X = pkg.ORBextractor(1000)
+    E = orc.Extractor(1000, oracle=oracle)
+    for img in (flat, sparse, grad):
+        mg, kg, dg = X(img, (0, 0))
+        mo, ko, do = E(img, (0, 0))
+        assert mg == mo and np.array_equal(kg, ko) and np.array_equal(dg, do)
+    X.close()
+
+
+def test_error_conventions(pkg):
+    X = pkg.ORBextractor(1000)
+    r, k, d = X(np.empty((0, 0), np.uint8))
+    assert r == -1 and len(k) == 0          # operator() returns -1 for an empty image (src/ORBextractor.cc:1538)
+    with pytest.raises(pkg.OrbxError) as ei:
+        X(np.zeros((60, 60), np.uint8))     # top pyramid level narrower than one 35-px cell
+    assert ei.value.code == pkg.binding.ORBX_ERR_GEOMETRY
+    with pytest.raises(pkg.OrbxError):
+        pkg.ORBextractor(1000, nlevels=99)
+    X.close()

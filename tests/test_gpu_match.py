@@ -1,0 +1,105 @@
+"""GPU parity of the matching path (stereo row search + SAD, brute-force 2-NN, SearchByProjection)
+against the CPU oracle.  Integer results bit-exact; mvuRight/mvDepth bit-exact floats."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _stereo_case(pkg, orc, oracle, cfg, seed, nframes=1):
+    c = pkg.synth.CONFIGS[cfg]
+    rows, cols, nf = c["rows"], c["cols"], c["nfeatures"]
+    mbf = c["mbf"]; mb = mbf / c["fx"]
+    pairs = [pkg.synth.synth_stereo_pair(rows, cols, seed + i) for i in range(nframes)]
+    L = np.stack([p[0] for p in pairs]); R = np.stack([p[1] for p in pairs])
+    XL, XR = pkg.ORBextractor(nf), pkg.ORBextractor(nf)
+    _, nL, kL, dL = XL.extract_batch(L, (0, 0))
+    _, nR, kR, dR = XR.extract_batch(R, (0, 0))
+    uR, depth = pkg.ComputeStereoMatches(XL, XR, mb, mbf, frame=None)
+    EL, ER = orc.Extractor(nf, oracle=oracle), orc.Extractor(nf, oracle=oracle)
+    matched = 0
+    for f in range(nframes):
+        _, kl, dl = EL(L[f], (0, 0)); _, kr, dr = ER(R[f], (0, 0))
+        assert np.array_equal(kL[f, :nL[f]], kl) and np.array_equal(kR[f, :nR[f]], kr)
+        u_o, d_o, _, _ = orc.stereo_match(EL, ER, kl, dl, kr, dr, mb, mbf)
+        assert np.array_equal(uR[f, :nL[f]], u_o), f"mvuRight frame {f}: {np.sum(uR[f, :nL[f]] != u_o)} differ"
+        assert np.array_equal(depth[f, :nL[f]], d_o), f"mvDepth frame {f}"
+        matched += int((u_o >= 0).sum())
+    XL.close(); XR.close()
+    return matched
+
+
+def test_stereo_euroc(pkg, orc, oracle):
+    assert _stereo_case(pkg, orc, oracle, "C2", 11, nframes=3) > 300     # the synthetic pairs do match
+
+
+def test_stereo_kitti(pkg, orc, oracle):
+    assert _stereo_case(pkg, orc, oracle, "C4", 21, nframes=2) > 300
+
+
+def test_stereo_single_frame_api(pkg, orc, oracle):
+    c = pkg.synth.CONFIGS["C2"]
+    l, r = pkg.synth.synth_stereo_pair(c["rows"], c["cols"], 5)
+    XL, XR = pkg.ORBextractor(1200), pkg.ORBextractor(1200)
+    _, kl, dl = XL(l); _, kr, dr = XR(r)
+    mb = c["mbf"] / c["fx"]
+    uR, depth = pkg.ComputeStereoMatches(XL, XR, mb, c["mbf"], frame=0)
+    EL, ER = orc.Extractor(1200, oracle=oracle), orc.Extractor(1200, oracle=oracle)
+    _, ko, do = EL(l); _, kro, dro = ER(r)
+    u_o, d_o, _, _ = orc.stereo_match(EL, ER, ko, do, kro, dro, mb, c["mbf"])
+    assert np.array_equal(uR[:len(kl)], u_o) and np.array_equal(depth[:len(kl)], d_o)
+    XL.close(); XR.close()
+
+
+def test_stereo_state_errors(pkg):
+    XL, XR = pkg.ORBextractor(1200), pkg.ORBextractor(1200)
+    XL._last_shape = (1, 480, 752)
+    with pytest.raises(pkg.OrbxError) as ei:
+        pkg.ComputeStereoMatches(XL, XR, 0.11, 47.9)
+    assert ei.value.code == pkg.binding.ORBX_ERR_STATE
+    XL.close(); XR.close()
+
+
+@pytest.mark.parametrize("nq,nt", [(1000, 1000), (517, 733), (1, 1), (3, 2), (5, 0), (1300, 129)])
+def test_knn2(pkg, oracle, nq, nt):
+    rng = np.random.default_rng(nq * 7 + nt)
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    if nt > 4:      # forced duplicates / near-duplicates: tie-break by ascending train index
+        t[nt // 2] = t[1]; t[nt - 1] = t[1]
+        q[0] = t[1]
+        q[nq // 2] = t[1] ^ np.uint8(1)
+    gi, gd = pkg.knn2_hamming(q, t)
+    oi, od = oracle.knn2(q, t) if nt > 0 else (np.full((nq, 2), -1, np.int32), np.full((nq, 2), -1, np.int32))
+    assert np.array_equal(gi, oi) and np.array_equal(gd, od)
+
+
+def test_descriptor_distance(pkg, oracle):
+    rng = np.random.default_rng(1)
+    for _ in range(200):
+        a = rng.integers(0, 256, 32, dtype=np.uint8); b = rng.integers(0, 256, 32, dtype=np.uint8)
+        assert pkg.DescriptorDistance(a, b) == oracle.hamming(a, b) == int(np.unpackbits(a ^ b).sum())
+
+
+@pytest.mark.parametrize("th,stereo,far", [(1.0, False, False), (3.0, False, False), (3.0, True, False), (1.0, True, True)])
+def test_search_by_projection(pkg, orc, oracle, th, stereo, far):
+    """C3: 512x512 fisheye-sized frame vs 5000 synthetic map points."""
+    rows, cols = 512, 512
+    img = pkg.synth.synth_frame(rows, cols, 31)
+    X = pkg.ORBextractor(1000)
+    _, kps, desc = X(img, (0, 0))
+    sf = X.GetScaleFactors()
+    mp = pkg.synth.synth_map_points(desc, np.stack([kps["x"], kps["y"]], 1), kps["octave"], 5000, 77, rows, cols)
+    rng = np.random.default_rng(5)
+    uR = None
+    if stereo:
+        uR = np.where(rng.random(len(kps)) < 0.6, kps["x"] - rng.uniform(0, 30, len(kps)), -1).astype(np.float32)
+    pre = np.full(len(kps), -1, np.int32)
+    pre[rng.choice(len(kps), 50, replace=False)] = 9999          # keypoints that already hold a map point
+    g = orc.Grid(oracle, kps, 0.0, float(cols), 0.0, float(rows))
+    nm_o, as_o = orc.search_by_projection(g, desc, uR, sf, mp, th, 0.8, far, 30.0, pre)
+    nm_g, as_g = pkg.SearchByProjection(kps, desc, uR, (0.0, float(cols), 0.0, float(rows)), sf, mp, th, 0.8, far, 30.0, pre)
+    assert nm_o > 100
+    assert nm_g == nm_o
+    assert np.array_equal(as_g, as_o), f"{np.sum(as_g != as_o)} assignments differ"
+    X.close()
