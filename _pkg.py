@@ -24,3 +24,16 @@ def load_oracle():
         sys.path.insert(0, p)
     import orc_py
     return orc_py
+
+
+def load_synth_only():
+    """The synthetic-input generator without touching liborbx.so (reference arm / CPU-only paths)."""
+    import types
+    if "orbslam3_b200" in sys.modules:
+        return sys.modules["orbslam3_b200"]
+    d = ROOT / "orb-slam3_b200"
+    spec = importlib.util.spec_from_file_location("orbslam3_b200_synth", d / "synth.py")
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    ns = types.SimpleNamespace(synth=m)
+    return ns

@@ -1,0 +1,342 @@
+#!/usr/bin/env python3
+"""bench.py — ORB extract+describe frames/s on B200 (BASELINE.json metric), one JSON line.
+
+  python bench.py --gpus N --steps K --warmup W            our arm (CUDA, liborbx.so)
+  python bench.py --impl reference --gpus N --steps K ...  reference arm: the reference's CPU path
+                                                           (oracle port, all host cores), rank 0 only
+
+A step = one pass of the extraction hot path over one batch of synthetic frames.
+  value : frames/s with the batch already resident in HBM (orbx_upload once, orbx_run_resident per
+          step), CUDA events on the extractor's stream, max over ranks.
+  e2e   : the same metric through the C-ABI call a user makes (orbx_extract_batch) with pinned HOST
+          buffers: H2D of the frames and D2H of keypoints+descriptors inside the timed region.
+  roofline : dominant stage's algorithmic bytes / its CUDA-event time, against MEASURED_PEAKS.json.
+  cpu_baseline : the oracle (C port of the reference's ORBextractor) on the box's host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import pathlib
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = pathlib.Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+import _pkg  # noqa: E402
+
+STAGES = ["pyramid", "fast", "quadtree", "assemble", "blur", "describe"]
+N_DISTINCT = 32      # distinct synthetic frames, tiled to the batch
+
+
+def level_dims(rows, cols, isf):
+    return [(int(np.rint(np.float32(rows) * s)), int(np.rint(np.float32(cols) * s))) for s in isf]
+
+
+def algorithmic_bytes(rows, cols, isf, nkp_mean):
+    """SURVEY.md 8(d) primary figure, per frame and per stage (compulsory stage-wise HBM traffic)."""
+    px = [h * w for h, w in level_dims(rows, cols, isf)]
+    return {
+        "pyramid": sum(px[:-1]) + sum(px[1:]),       # read L0..L6, write L1..L7
+        "fast": sum(px),                             # read L0..L7
+        "blur": 2 * sum(px),                         # read + write L0..L7
+        "outputs": int(round(nkp_mean * 60)),        # 28 B keypoint + 32 B descriptor
+    }
+
+
+def make_frames(pkg, rows, cols, batch, seed0=0):
+    base = np.stack([pkg.synth.synth_frame(rows, cols, seed0 + s) for s in range(min(N_DISTINCT, batch))])
+    reps = (batch + len(base) - 1) // len(base)
+    return np.ascontiguousarray(np.tile(base, (reps, 1, 1))[:batch])
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for l in self.lines:
+            p = [x.strip() for x in l.split(",")]
+            if len(p) < 8:
+                continue
+            try:
+                sm.append(float(p[1])); mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_oracle_throughput(pkg, rows, cols, nfeatures, lapping, target_seconds, threads=None):
+    """Reference CPU path (oracle port) on the host cores: one independent extractor per thread."""
+    orc = _pkg.load_oracle()
+    orc.build()
+    o = orc.Oracle()
+    cores = threads or (os.cpu_count() or 1)
+    frames = make_frames(pkg, rows, cols, min(N_DISTINCT, 8))
+    E0 = orc.Extractor(nfeatures, oracle=o)
+    t0 = time.perf_counter(); E0(frames[0], lapping); t1 = time.perf_counter() - t0
+    n = int(max(cores, min(4000, target_seconds * cores / max(t1, 1e-4))))
+    n = (n + cores - 1) // cores * cores
+    exts = [orc.Extractor(nfeatures, oracle=o) for _ in range(cores)]
+    per = n // cores
+
+    def work(i):
+        for k in range(per):
+            exts[i](frames[(i + k) % len(frames)], lapping)
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(cores)]
+    t0 = time.perf_counter()
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    dt = time.perf_counter() - t0
+    return {"value": n / dt, "unit": "frames/s", "cores": cores, "kind": "port",
+            "sample": f"{n} frames {cols}x{rows} ({nfeatures} features) over {cores} threads in {dt:.1f} s; "
+                      f"oracle/liborc.so (C restatement of ORBextractor::operator(), -O3 -ffp-contract=off); "
+                      f"single-thread latency {t1 * 1e3:.1f} ms/frame"}
+
+
+def run_reference(args, cfg, rank, world):
+    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    pkg = _pkg.load_synth_only()
+    rows, cols, nf = cfg["rows"], cfg["cols"], cfg["nfeatures"]
+    lap = (0, 1000) if args.workload == "C1" else (0, 0)
+    orc = _pkg.load_oracle(); orc.build(); o = orc.Oracle()
+    cores = os.cpu_count() or 1
+    frames = make_frames(pkg, rows, cols, N_DISTINCT)
+    exts = [orc.Extractor(nf, oracle=o) for _ in range(cores)]
+    per = max(1, args.ref_frames_per_core)
+
+    def step():
+        def work(i):
+            for k in range(per):
+                exts[i](frames[(i * per + k) % len(frames)], lap)
+        th = [threading.Thread(target=work, args=(i,)) for i in range(cores)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    nframes = per * cores * args.steps
+    v = nframes / dt
+    line = {"impl": "reference", "metric": "ORB extract+describe frames/s @752x480,1000kp", "value": v, "unit": "frames/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": workload_name(args.workload, cfg), "frames_per_step": per * cores},
+            "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": f"{per * cores} frames/step x {args.steps} steps, one oracle extractor per host thread "
+                                       f"(reference src/ORBextractor.cc cannot be compiled here: no OpenCV C++ headers)"},
+            "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(w, cfg):
+    return (f"{w}: synthetic {cfg['cols']}x{cfg['rows']} grayscale frames, {cfg['nfeatures']} features, 8 levels, "
+            f"scale 1.2, FAST 20/7, ORBextractor::operator() (extract+describe)")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C1", choices=["C1", "C2", "C3", "C4", "C5"])
+    ap.add_argument("--batch", type=int, default=0, help="frames per step per GPU (0 = auto, > L2)")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="bounded CPU-baseline sample")
+    ap.add_argument("--ref-frames-per-core", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    synth = _pkg.load_synth_only()
+    cfg = synth.synth.CONFIGS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, cfg, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
+    pkg = _pkg.load()
+    rows, cols, nf = cfg["rows"], cfg["cols"], cfg["nfeatures"]
+    lap = (0, 1000) if args.workload == "C1" else (0, 0)      # mono passes vLappingArea={0,1000} (src/Frame.cc:361)
+    B = args.batch or {"C1": 512, "C2": 512, "C3": 512, "C4": 384, "C5": 24}[args.workload]
+
+    X = pkg.ORBextractor(nf, device=local_rank)
+    isf = X.GetInverseScaleFactors()
+    frames = make_frames(pkg, rows, cols, B, seed0=1000 * rank)
+    # pinned host staging for the e2e leg
+    cap = X.max_keypoints(rows, cols)
+    t_frames = torch.from_numpy(frames).pin_memory()
+    t_kps = torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory()
+    t_desc = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    h_frames = t_frames.numpy()
+    h_kps = t_kps.numpy().view(pkg.KP_DTYPE).reshape(B, cap)
+    h_desc = t_desc.numpy()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- resident leg (value) ----------------
+    X.upload(h_frames)
+    for _ in range(args.warmup):
+        X.run_resident(lap)
+    X.sync()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    l0 = X.launch_count()
+    w0 = time.perf_counter()
+    X.timer_start()
+    for _ in range(args.steps):
+        X.run_resident(lap)
+    ms = X.timer_stop()
+    wall_ms = (time.perf_counter() - w0) * 1e3
+    launches = X.launch_count() - l0
+    barrier()
+    clocks = sampler.stop()
+    ms = max_over_ranks(ms)
+    mono, nkp, _, _ = X.download()
+    nkp_mean = float(nkp.mean())
+    value = world * args.steps * B / (ms * 1e-3)
+
+    # ---------------- per-stage times (profiling events, outside the timed region) ----------------
+    X.set_profiling(True)
+    stage = np.zeros(len(STAGES)); nprof = 5
+    for _ in range(nprof):
+        X.run_resident(lap); X.sync()
+        stage += np.array([X.stage_ms(i) for i in range(len(STAGES))])
+    stage /= nprof
+    X.set_profiling(False)
+    ab = algorithmic_bytes(rows, cols, isf, nkp_mean)
+    peaks = {}
+    pk = ROOT / "MEASURED_PEAKS.json"
+    if pk.exists():
+        peaks = json.loads(pk.read_text())
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    hbm_stages = {"pyramid": 0, "fast": 1, "blur": 4}
+    stage_gbs = {k: ab[k] * B / (stage[i] * 1e-3) / 1e9 for k, i in hbm_stages.items() if stage[i] > 0}
+    dom = max(hbm_stages, key=lambda k: stage[hbm_stages[k]])
+    whole = sum(ab.values()) * B / (ms / args.steps * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": stage_gbs[dom], "peak": peak_gbs, "unit": "GB/s",
+                "frac": stage_gbs[dom] / peak_gbs, "traffic": None, "peak_source": peak_src,
+                "bytes_per_launch": ab[dom] * B,
+                "stage_ms": {k: float(stage[i]) for i, k in enumerate(STAGES)},
+                "stage_gbs": stage_gbs,
+                "pipeline_achieved_gbs": whole, "pipeline_frac": whole / peak_gbs,
+                "algorithmic_bytes_per_frame": ab}
+
+    # ---------------- end-to-end leg (host buffers through the C ABI) ----------------
+    nkp_h = np.empty(B, np.int32); mono_h = np.empty(B, np.int32)
+    lib = pkg.binding.load()
+
+    def e2e_step():
+        pkg.binding.check(lib.orbx_extract_batch(X.h, B, h_frames.ctypes.data, rows, cols, h_frames.strides[1], h_frames.strides[0],
+                                                 lap[0], lap[1], h_kps.ctypes.data, h_desc.ctypes.data, cap,
+                                                 nkp_h.ctypes.data, mono_h.ctypes.data))
+    for _ in range(max(1, min(args.warmup, 3))):
+        e2e_step()
+    barrier()
+    ksteps = max(1, min(args.steps, 10))
+    t0 = time.perf_counter()
+    X.timer_start()
+    for _ in range(ksteps):
+        e2e_step()
+    e2e_ms = X.timer_stop()
+    e2e_wall = (time.perf_counter() - t0) * 1e3
+    barrier()
+    e2e_ms = max_over_ranks(max(e2e_ms, e2e_wall))
+    e2e = {"value": world * ksteps * B / (e2e_ms * 1e-3), "unit": "frames/s",
+           "h2d_bytes_per_step": int(B * rows * cols), "d2h_bytes_per_step": int(B * (cap * 60 + 8)),
+           "steps": ksteps, "api": "orbx_extract_batch (pinned host frames -> pinned host keypoints+descriptors)"}
+    assert np.array_equal(nkp_h, nkp), "e2e and resident legs disagree"
+
+    # ---------------- CPU baseline (rank 0, N=1 only) ----------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_oracle_throughput(pkg, rows, cols, nf, lap, args.cpu_seconds)
+
+    if rank == 0:
+        line = {"metric": "ORB extract+describe frames/s @752x480,1000kp", "value": value, "unit": "frames/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": workload_name(args.workload, cfg), "frames_per_step_per_gpu": B,
+                           "distinct_frames": min(N_DISTINCT, B), "mean_keypoints_per_frame": nkp_mean,
+                           "l2": f"inputs larger than L2: {B * rows * cols / 1e6:.0f} MB of frames + "
+                                 f"{B * sum(h * w for h, w in level_dims(rows, cols, isf)) * 2 / 1e6:.0f} MB of pyramid/blur planes per step vs 126 MB L2",
+                           "partition": "frames sharded across ranks, no collective"},
+                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+                "cpu_baseline": cpu, "wall_ms_per_step": wall_ms / args.steps}
+        print(json.dumps(line), flush=True)
+    X.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -120,6 +120,12 @@ int orbx_debug_blurred_level(orbx_extractor* e, int frame, int level, uint8_t* d
  * stream, milliseconds; stage < 0 = whole pipeline.  Stages: 0 pyramid, 1 FAST, 2 quadtree,
  * 3 assemble, 4 blur, 5 orientation+descriptor. */
 float orbx_last_stage_ms(orbx_extractor* e, int stage);
+/* CUDA-event stopwatch on the handle's stream: start records an event, stop records a second one,
+ * waits for it and returns the elapsed milliseconds (everything queued on the handle in between). */
+int   orbx_timer_start(orbx_extractor* e);
+float orbx_timer_stop(orbx_extractor* e);
+/* unit-test entry: FAST-9/16 score map (no NMS) of a HOST image at threshold th -> out[rows*cols] */
+int   orbx_debug_fast_score_map(int device, const uint8_t* img, int rows, int cols, size_t step, int th, uint8_t* out);
 /* enable per-stage event recording (off by default: events serialise nothing but cost launches) */
 void orbx_set_profiling(orbx_extractor* e, int on);
 /* number of kernel launches issued by this handle since creation */

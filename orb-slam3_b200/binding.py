@@ -49,6 +49,9 @@ SYMBOLS = {
     "orbx_debug_blurred_level": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t]),
     "orbx_last_stage_ms": (C.c_float, [C.c_void_p, C.c_int]),
     "orbx_set_profiling": (None, [C.c_void_p, C.c_int]),
+    "orbx_timer_start": (C.c_int, [C.c_void_p]),
+    "orbx_timer_stop": (C.c_float, [C.c_void_p]),
+    "orbx_debug_fast_score_map": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_void_p]),
     "orbx_launch_count": (C.c_longlong, [C.c_void_p]),
     "orbx_hamming256": (C.c_int, [C.c_void_p, C.c_void_p]),
     "orbx_stereo_match": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int]),

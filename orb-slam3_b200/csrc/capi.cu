@@ -59,6 +59,7 @@ extern "C" int orbx_create(int nfeatures, float scaleFactor, int nlevels, int in
     cudaError_t ce = cudaSetDevice(device);
     if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     for (int i = 0; i <= ORBX_NSTAGES && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->ev[i]);
+    for (int i = 0; i < 2 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->tev[i]);
     if (ce != cudaSuccess) {
         orbx_set_error("CUDA init failed: %s", cudaGetErrorString(ce));
         delete e;
@@ -85,6 +86,7 @@ extern "C" void orbx_destroy(orbx_extractor* e)
     cudaStreamSynchronize(e->stream);
     free_device(e);
     for (int i = 0; i <= ORBX_NSTAGES; i++) cudaEventDestroy(e->ev[i]);
+    for (int i = 0; i < 2; i++) cudaEventDestroy(e->tev[i]);
     cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -410,6 +412,24 @@ extern "C" float orbx_last_stage_ms(orbx_extractor* e, int stage)
 {
     if (!e || stage >= ORBX_NSTAGES) return -1.f;
     return e->stage_ms[stage < 0 ? ORBX_NSTAGES : stage];
+}
+// CUDA-event stopwatch on the handle's stream (bench.py times K steps with it)
+extern "C" int orbx_timer_start(orbx_extractor* e)
+{
+    if (!e) return ORBX_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaEventRecord(e->tev[0], e->stream));
+    return ORBX_OK;
+}
+extern "C" float orbx_timer_stop(orbx_extractor* e)
+{
+    if (!e) return -1.f;
+    float ms = -1.f;
+    if (cudaSetDevice(e->device) != cudaSuccess) return -1.f;
+    if (cudaEventRecord(e->tev[1], e->stream) != cudaSuccess) return -1.f;
+    if (cudaEventSynchronize(e->tev[1]) != cudaSuccess) return -1.f;
+    if (cudaEventElapsedTime(&ms, e->tev[0], e->tev[1]) != cudaSuccess) return -1.f;
+    return ms;
 }
 extern "C" void orbx_set_profiling(orbx_extractor* e, int on) { if (e) e->profiling = on != 0; }
 extern "C" long long orbx_launch_count(const orbx_extractor* e) { return e ? e->launches : 0; }

@@ -20,6 +20,7 @@ struct orbx_extractor {
     DevBuffers D;
     std::vector<void*> allocs;           // every cudaMalloc of this handle
     cudaEvent_t ev[ORBX_NSTAGES + 1];
+    cudaEvent_t tev[2];                  // stopwatch (orbx_timer_start/stop)
     bool profiling;
     float stage_ms[ORBX_NSTAGES + 1];    // [ORBX_NSTAGES] = total
     long long launches;

@@ -101,6 +101,8 @@ class ORBextractor:
         check(self.lib.orbx_download(self.h, kps.ctypes.data, desc.ctypes.data, cap, nkp.ctypes.data, mono.ctypes.data))
         return mono, nkp, kps, desc
 
+    def timer_start(self): check(self.lib.orbx_timer_start(self.h))
+    def timer_stop(self): return float(self.lib.orbx_timer_stop(self.h))
     def set_profiling(self, on=True): self.lib.orbx_set_profiling(self.h, int(on))
     def stage_ms(self, stage=-1): return float(self.lib.orbx_last_stage_ms(self.h, stage))
     def launch_count(self): return int(self.lib.orbx_launch_count(self.h))
