@@ -103,7 +103,7 @@ int orbx_download(orbx_extractor* e, orbx_keypoint* kps, uint8_t* desc, int cap,
 
 /* mvImagePyramid[level] of frame `frame` of the last extract (include/ORBextractor.h:83): copies
  * the unpadded rows x cols level image (padded=0) or the (rows+38) x (cols+38) buffer with its
- * reflect-101 border (padded=1) to dst (dst_step bytes per row).  *rows/*cols get the copied size. */
+ * reflect-101 border (padded=1) to dst (dst_step bytes per row).  rows / cols receive the copied size. */
 int orbx_get_pyramid_level(orbx_extractor* e, int frame, int level, int padded,
                            uint8_t* dst, size_t dst_step, int* rows, int* cols);
 

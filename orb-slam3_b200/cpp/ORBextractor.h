@@ -1,0 +1,121 @@
+// ORBextractor.h — drop-in replacement of the reference's include/ORBextractor.h:28-114 on top of the
+// C ABI (include/orbx.h).  Same namespace, class name, constructor, operator() and getters, so that
+// src/Frame.cc / src/Tracking.cc compile unchanged against it.
+//
+// With OpenCV headers available define ORBX_WITH_OPENCV (the real cv::Mat / cv::KeyPoint are used).
+// Without them (this build image has no OpenCV C++ headers) a minimal layout-compatible stand-in
+// (`cv::Mat`, `cv::KeyPoint`, 28 bytes) is provided so the shim and its example still compile.
+#pragma once
+#include <cassert>
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/orbx.h"
+
+#ifdef ORBX_WITH_OPENCV
+#include <opencv2/core.hpp>
+#else
+namespace cv {
+struct Point2f { float x, y; };
+struct KeyPoint {                   // memory layout of cv::KeyPoint (28 bytes)
+    Point2f pt; float size, angle, response; int octave, class_id;
+};
+struct Mat {                        // CV_8UC1 only: what the hot path exchanges
+    int rows = 0, cols = 0; size_t step = 0; uint8_t* data = nullptr;
+    std::vector<uint8_t> storage;
+    Mat() {}
+    Mat(int r, int c) { create(r, c); }
+    Mat(int r, int c, uint8_t* ext, size_t st) : rows(r), cols(c), step(st), data(ext) {}
+    void create(int r, int c) { rows = r; cols = c; step = (size_t)c; storage.assign((size_t)r * c, 0); data = storage.data(); }
+    void release() { rows = cols = 0; step = 0; data = nullptr; storage.clear(); }
+    bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
+    uint8_t* ptr(int r) { return data + (size_t)r * step; }
+    const uint8_t* ptr(int r) const { return data + (size_t)r * step; }
+};
+}  // namespace cv
+#endif
+
+#ifdef ORBX_WITH_OPENCV
+#define ORBX_MAT_CREATE(m, r, c) (m).create((r), (c), CV_8U)
+#else
+#define ORBX_MAT_CREATE(m, r, c) (m).create((r), (c))
+#endif
+
+static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint layout");
+
+namespace ORB_SLAM3 {
+
+class ORBextractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    // include/ORBextractor.h:49-50
+    ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device = 0)
+    {
+        if (orbx_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device, &h_) != ORBX_OK)
+            throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        const int n = orbx_levels(h_);
+        mvScaleFactor.assign(orbx_scale_factors(h_), orbx_scale_factors(h_) + n);
+        mvInvScaleFactor.assign(orbx_inv_scale_factors(h_), orbx_inv_scale_factors(h_) + n);
+        mvLevelSigma2.assign(orbx_level_sigma2(h_), orbx_level_sigma2(h_) + n);
+        mvInvLevelSigma2.assign(orbx_inv_level_sigma2(h_), orbx_inv_level_sigma2(h_) + n);
+    }
+    ~ORBextractor() { orbx_destroy(h_); }
+    ORBextractor(const ORBextractor&) = delete;
+    ORBextractor& operator=(const ORBextractor&) = delete;
+
+    // include/ORBextractor.h:57-59, src/ORBextractor.cc:1534-1659.  The mask is ignored (as in the
+    // reference); outputs are resized by the callee; returns monoIndex, -1 for an empty image.
+    int operator()(const cv::Mat& image, const cv::Mat& /*mask*/, std::vector<cv::KeyPoint>& keypoints,
+                   cv::Mat& descriptors, std::vector<int>& vLappingArea)
+    {
+        if (image.empty()) return -1;                                       // :1538
+        assert(vLappingArea.size() >= 2);
+        const int cap = orbx_max_keypoints(h_, image.rows, image.cols);
+        if (cap < 0) throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        keypoints.resize((size_t)cap);
+        scratch_.resize((size_t)cap * 32);
+        int n = 0;
+        const int mono = orbx_extract(h_, image.data, image.rows, image.cols, image.step, vLappingArea[0], vLappingArea[1],
+                                      reinterpret_cast<orbx_keypoint*>(keypoints.data()), scratch_.data(), cap, &n);
+        if (mono < 0) throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        keypoints.resize((size_t)n);                                        // :1587
+        if (n == 0) descriptors.release();                                  // :1570-1572
+        else {
+            ORBX_MAT_CREATE(descriptors, n, 32);                            // :1577 (CV_8U)
+            for (int i = 0; i < n; i++) std::memcpy(descriptors.ptr(i), scratch_.data() + (size_t)i * 32, 32);
+        }
+        return mono;
+    }
+
+    // include/ORBextractor.h:61-81
+    int GetLevels() { return orbx_levels(h_); }
+    float GetScaleFactor() { return orbx_scale_factor(h_); }
+    std::vector<float> GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+
+    // mvImagePyramid (include/ORBextractor.h:83) lives on the device; copy a level out on demand.
+    cv::Mat GetPyramidLevel(int level, bool padded = false)
+    {
+        int r = 0, c = 0;
+        if (orbx_get_pyramid_level(h_, 0, level, padded, nullptr, 0, &r, &c) != ORBX_OK)
+            throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        cv::Mat m; ORBX_MAT_CREATE(m, r, c);
+        orbx_get_pyramid_level(h_, 0, level, padded, m.data, m.step, &r, &c);
+        return m;
+    }
+
+    orbx_extractor* handle() { return h_; }
+
+protected:
+    orbx_extractor* h_ = nullptr;
+    std::vector<uint8_t> scratch_;
+    std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
+};
+
+}  // namespace ORB_SLAM3

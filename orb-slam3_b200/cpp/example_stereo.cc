@@ -1,0 +1,60 @@
+// example_stereo.cc — what the reference's stereo Frame constructor (src/Frame.cc:103-225) does with the
+// extractor and matcher, written against the shims (no OpenCV needed).  Build + run on a GPU box:
+//   g++ -O2 -std=c++17 orb-slam3_b200/cpp/example_stereo.cc -Lorb-slam3_b200 -lorbx -Wl,-rpath,$PWD/orb-slam3_b200 -o example_stereo
+#include <cstdio>
+#include <cstdlib>
+#include <thread>
+
+#include "ORBmatcher.h"
+
+static cv::Mat synth(int rows, int cols, unsigned seed, int shift)
+{
+    cv::Mat m(rows, cols);
+    std::vector<uint8_t> base((size_t)rows * (cols + 64));
+    srand(seed);
+    for (auto& v : base) v = (uint8_t)(rand() & 0xFF);
+    for (int y = 0; y < rows; y++)
+        for (int x = 0; x < cols; x++) {
+            // 3x3 box of the noise = band-limited texture; the right image is the left shifted by `shift`
+            int s = 0;
+            for (int dy = -1; dy <= 1; dy++)
+                for (int dx = -1; dx <= 1; dx++) {
+                    int yy = y + dy < 0 ? 0 : (y + dy >= rows ? rows - 1 : y + dy);
+                    s += base[(size_t)yy * (cols + 64) + x + shift + 1 + dx];
+                }
+            m.ptr(y)[x] = (uint8_t)(s / 9);
+        }
+    return m;
+}
+
+int main()
+{
+    using namespace ORB_SLAM3;
+    const int rows = 480, cols = 752;
+    try {
+        // src/Tracking.cc:1106-1110: mpORBextractorLeft / mpORBextractorRight
+        ORBextractor left(1200, 1.2f, 8, 20, 7), right(1200, 1.2f, 8, 20, 7);
+        cv::Mat imLeft = synth(rows, cols, 1, 20), imRight = synth(rows, cols, 1, 0);
+        std::vector<cv::KeyPoint> mvKeys, mvKeysRight;
+        cv::Mat mDescriptors, mDescriptorsRight;
+        std::vector<int> vLapping = {0, 0};
+        // src/Frame.cc:132-137: two threads, one extractor each
+        int monoLeft = 0, monoRight = 0;
+        std::thread tl([&] { monoLeft = left(imLeft, cv::Mat(), mvKeys, mDescriptors, vLapping); });
+        std::thread tr([&] { monoRight = right(imRight, cv::Mat(), mvKeysRight, mDescriptorsRight, vLapping); });
+        tl.join(); tr.join();
+        // src/Frame.cc:159: ComputeStereoMatches (EuRoC: bf = 47.90639, fx = 435.2047)
+        std::vector<float> mvuRight, mvDepth;
+        const float mbf = 47.90639f, mb = mbf / 435.2047f;
+        ORBmatcherGPU::ComputeStereoMatches(left, right, (int)mvKeys.size(), mb, mbf, mvuRight, mvDepth);
+        int matched = 0;
+        for (float u : mvuRight) matched += u >= 0;
+        std::printf("left %zu kps (mono %d), right %zu kps (mono %d), stereo matches %d, d(0,1) = %d\n", mvKeys.size(), monoLeft,
+                    mvKeysRight.size(), monoRight, matched,
+                    mvKeys.size() > 1 ? ORBmatcherGPU::DescriptorDistance(cv::Mat(1, 32, mDescriptors.ptr(0), 32), cv::Mat(1, 32, mDescriptors.ptr(1), 32)) : -1);
+        return matched > 0 ? 0 : 2;
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "error: %s\n", e.what());
+        return 1;
+    }
+}

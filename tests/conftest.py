@@ -13,9 +13,26 @@ def pytest_configure(config):
 
 
 @pytest.fixture(scope="session")
-def pkg():
+def built_lib():
+    """liborbx.so built in-tree (nvcc cross-compiles without a GPU)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_orbx_build", ROOT / "orb-slam3_b200" / "build.py")
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    return b.build()
+
+
+@pytest.fixture(scope="session")
+def pkg(built_lib):
     import _pkg
     return _pkg.load()
+
+
+@pytest.fixture(scope="session")
+def pkg_synth():
+    """Synthetic-input generator only (no CUDA library involved)."""
+    import _pkg
+    return _pkg.load_synth_only().synth
 
 
 @pytest.fixture(scope="session")

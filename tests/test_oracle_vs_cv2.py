@@ -1,0 +1,65 @@
+"""CPU suite: the oracle's OpenCV-primitive restatements against the live cv2 wheel (4.13.0 in this
+image) on fresh random inputs — resize, copyMakeBorder, FAST, GaussianBlur, fastAtan2, BFMatcher —
+plus one full operator() against oracle A (oracle/ref_cv2.py, real cv2 calls)."""
+import sys
+import pathlib
+
+import numpy as np
+import pytest
+
+cv2 = pytest.importorskip("cv2")
+ROOT = pathlib.Path(__file__).resolve().parents[1]
+
+
+def cand_arr(c):
+    return np.stack([c["x"], c["y"], c["score"]], axis=1).astype(np.int32) if len(c) else np.empty((0, 3), np.int32)
+
+
+@pytest.mark.parametrize("shape,seed", [((97, 131), 1), ((240, 376), 2), ((64, 64), 3)])
+def test_pixel_primitives(pkg_synth, oracle, shape, seed):
+    rng = np.random.default_rng(seed)
+    img = pkg_synth.synth_frame(shape[0], shape[1], seed) if shape[0] > 64 else rng.integers(0, 256, shape, dtype=np.uint8)
+    for s in (1.2, 1.44, 2.5):
+        dh, dw = int(round(shape[0] / s)), int(round(shape[1] / s))
+        assert np.array_equal(oracle.resize(img, dh, dw), cv2.resize(img, (dw, dh), interpolation=cv2.INTER_LINEAR))
+    assert np.array_equal(oracle.border101(img, 19), cv2.copyMakeBorder(img, 19, 19, 19, 19, cv2.BORDER_REFLECT_101))
+    assert np.array_equal(oracle.gaussian(img), cv2.GaussianBlur(img, (7, 7), 2, None, 2, cv2.BORDER_REFLECT_101))
+    for t in (20, 7):
+        k = cv2.FastFeatureDetector_create(t, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16).detect(img, None)
+        ref = np.array([(int(p.pt[0]), int(p.pt[1]), int(p.response)) for p in k], np.int32).reshape(-1, 3)
+        assert np.array_equal(cand_arr(oracle.fast(img, t)), ref)
+
+
+def test_fast_on_tiny_and_degenerate_images(oracle):
+    for shape in [(6, 40), (40, 6), (7, 7), (8, 9)]:
+        img = np.random.default_rng(1).integers(0, 256, shape, dtype=np.uint8)
+        k = cv2.FastFeatureDetector_create(7, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16).detect(img, None)
+        assert len(oracle.fast(img, 7)) == len(k)
+
+
+def test_fast_atan2(oracle):
+    rng = np.random.default_rng(0)
+    ys = rng.integers(-1_900_000, 1_900_000, 3000).astype(np.float32)
+    xs = rng.integers(-1_900_000, 1_900_000, 3000).astype(np.float32)
+    for y, x in zip(ys, xs):
+        assert oracle.L.orc_fast_atan2(float(y), float(x)) == np.float32(cv2.fastAtan2(float(y), float(x)))
+
+
+def test_bf_knn(oracle):
+    rng = np.random.default_rng(5)
+    q = rng.integers(0, 256, (90, 32), dtype=np.uint8); t = rng.integers(0, 256, (70, 32), dtype=np.uint8)
+    t[10] = t[60]; q[5] = t[10]
+    m = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q, t, 2)
+    idx, dist = oracle.knn2(q, t)
+    assert np.array_equal(idx, np.array([[a.trainIdx, b.trainIdx] for a, b in m], np.int32))
+    assert np.array_equal(dist, np.array([[int(a.distance), int(b.distance)] for a, b in m], np.int32))
+
+
+def test_full_operator_against_cv2_oracle(pkg_synth, orc, oracle):
+    sys.path.insert(0, str(ROOT / "oracle"))
+    import ref_cv2
+    img = pkg_synth.synth_frame(300, 400, 21)
+    P = ref_cv2.Params(600)
+    R = ref_cv2.extract(img, P, (100, 250))
+    mono, kps, desc = orc.Extractor(600, oracle=oracle)(img, (100, 250))
+    assert mono == R["mono"] and kps.tobytes() == R["kps"].tobytes() and np.array_equal(desc, R["desc"])
