@@ -34,7 +34,7 @@ int main()
     try {
         // src/Tracking.cc:1106-1110: mpORBextractorLeft / mpORBextractorRight
         ORBextractor left(1200, 1.2f, 8, 20, 7), right(1200, 1.2f, 8, 20, 7);
-        cv::Mat imLeft = synth(rows, cols, 1, 20), imRight = synth(rows, cols, 1, 0);
+        cv::Mat imLeft = synth(rows, cols, 1, 0), imRight = synth(rows, cols, 1, 20);   // uR = uL - 20
         std::vector<cv::KeyPoint> mvKeys, mvKeysRight;
         cv::Mat mDescriptors, mDescriptorsRight;
         std::vector<int> vLapping = {0, 0};

@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
 
 static thread_local char g_err[512] = "";
 
@@ -157,9 +158,15 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
         }
     }
     D.nodetab_per_frame = (long long)octree_nodetab_ints(G);
-    if (!rc) rc |= dev_alloc(e, &D.cellcnt, B * G.cells_per_frame);
-    if (!rc) rc |= dev_alloc(e, &D.celloff, B * G.cells_per_frame);
-    if (!rc) rc |= dev_alloc(e, &D.cellkey, B * G.keys_per_frame);
+    {
+        std::vector<BandDesc> bands;
+        G.fast_smem = fast_build_bands(G, &bands);
+        G.bands_per_frame = (int)bands.size();
+        BandDesc* db = nullptr;
+        if (!rc) rc |= dev_alloc(e, &db, bands.size());
+        if (!rc) CUDA_TRY(cudaMemcpy(db, bands.data(), bands.size() * sizeof(BandDesc), cudaMemcpyHostToDevice));
+        D.bands = db;
+    }
     if (!rc) rc |= dev_alloc(e, &D.cand, B * G.cand_per_frame);
     if (!rc) rc |= dev_alloc(e, &D.candnode, B * G.cand_per_frame);
     if (!rc) rc |= dev_alloc(e, &D.nodetab, B * G.nlevels * D.nodetab_per_frame);
@@ -402,6 +409,16 @@ extern "C" int orbx_debug_level_keys(orbx_extractor* e, int frame, int level, in
         CUDA_TRY(cudaMemcpyAsync(angles, e->D.angle + (size_t)frame * G.sel_per_frame + L.sel_base, sizeof(float) * m,
                                  cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(cudaStreamSynchronize(e->stream));
+    if (stage == 0) {
+        // the device list is unordered; present it in the reference's vToDistributeKeys order
+        // (cell row-major, raster inside a cell) = ascending canonical rank, as the quadtree sees it
+        auto rank = [&L](uint32_t k) {
+            const int X3 = (int)KEY_X(k) - 3, Y3 = (int)KEY_Y(k) - 3;
+            const int cj = X3 / L.wCell, ci = Y3 / L.hCell;
+            return ((ci * L.nCols + cj) << 14) | ((Y3 - ci * L.hCell) << 7) | (X3 - cj * L.wCell);
+        };
+        std::sort(keys.begin(), keys.end(), [&](uint32_t a, uint32_t b) { return rank(a) < rank(b); });
+    }
     for (int i = 0; i < m; i++) {
         out[3 * i] = (int32_t)KEY_X(keys[i]); out[3 * i + 1] = (int32_t)KEY_Y(keys[i]); out[3 * i + 2] = (int32_t)KEY_S(keys[i]);
     }

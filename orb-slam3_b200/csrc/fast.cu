@@ -2,19 +2,311 @@
 // (ORBextractor::ComputeKeyPointsOctTree cell loop, reference src/ORBextractor.cc:1038-1143, and the
 // cv::FAST / cornerScore<16> / 3x3 non-max suppression it calls, restated in oracle/orc_prims.c).
 //
-// One CTA per 35-px cell: the (wCell+6)x(hCell+6) sub-image is staged in shared memory once, the
-// score map of its interior is computed at iniThFAST; only if NMS leaves nothing the cell is redone
-// at minThFAST (exactly the reference's per-cell semantics: NMS sees zero scores outside the cell).
-// Survivors are compacted in raster order into the cell's slot range; the quadtree kernel later
-// concatenates cells in row-major order, which reproduces vToDistributeKeys' order.
-// Integer/byte work, HBM-bound in the limit: algorithmic bytes per frame = read sum(L0..L7).
+// Work unit ("band"): the interiors of up to 768 px worth of cells of one cell row.  The interiors of
+// the reference's overlapping cell sub-images tile the level without overlap, so every pixel is scored
+// once.  Three phases per CTA:
+//   A  threshold-free score S = max(A, Bn) - 1 of every pixel (A = v - min_arcs max_arc ring,
+//      Bn = max_arcs min_arc ring - v; pixel is a corner at threshold t  <=>  S >= t, and its OpenCV
+//      score is S).  Each thread owns 4 adjacent pixels and slides down the band with a 7-row register
+//      window; the ring is evaluated two pixels per instruction on u16x2 lanes (VIMNMX3.U16x2): a lane
+//      is the raw byte pair (garbage, pixel) so the byte-shifted row words are used as they are —
+//      lexicographic min/max keeps the exact pixel value in the high byte.
+//   B1 3x3 non-max suppression on the shared-memory score tile, again on u16x2 lanes; neighbours
+//      outside the pixel's own cell interior count as 0 (the reference runs cv::FAST per cell).  The
+//      strict-maximum test does not depend on the threshold, so one pass serves both thresholds;
+//      per cell the survivors >= iniThFAST and those in [minThFAST, iniThFAST) are counted.
+//   B2 survivors >= iniThFAST are emitted; a cell without any emits its >= minThFAST survivors
+//      (the retry of :1118-1125).  Emission order is arbitrary: the quadtree breaks ties by the
+//      candidate's canonical rank (cell row, cell col, y, x), i.e. the reference's vector order.
+// Integer work on the ALU pipe (~55 lane-ops per pixel); HBM traffic = one read of the level.
 #include "orbx_internal.h"
+#include <vector>
 
-#define FAST_THREADS 128
-#define TILE_MAXW 80      // >= wCell+6 (wCell < 70)
-#define TILE_MAXH 76
-#define SC_MAXW 72        // interior + 1-px zero ring
+#define FAST_WARPS 6
+#define FAST_THREADS (FAST_WARPS * 32)
+#define FAST_MAXSPAN (FAST_THREADS * 4)
+#define FAST_MAXCELLS 24
 
+// ring offsets of cv::FAST 9_16 (oracle/orc_prims.c)
+#define RING_DX {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1}
+#define RING_DY {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3}
+
+// Score of two pixels.  r[k]: u16x2 lanes (low byte garbage, high byte ring pixel k), c: centre lanes.
+// Returns the two scores (0..254) in the low bytes of the two lanes.
+__device__ __forceinline__ uint32_t fast_score_pair(const uint32_t (&r)[16], uint32_t c)
+{
+    uint32_t t3[16];
+    uint32_t P, Q;
+    // P: min over the 16 arcs of (max of the arc's 9 ring pixels)
+#pragma unroll
+    for (int k = 0; k < 16; k++) t3[k] = __vimax3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
+    {
+        uint32_t a[16];
+#pragma unroll
+        for (int k = 0; k < 16; k++) a[k] = __vimax3_u16x2(t3[k], t3[(k + 3) & 15], t3[(k + 6) & 15]);
+        P = __vimin3_u16x2(a[0], a[1], a[2]);
+#pragma unroll
+        for (int k = 3; k < 15; k += 2) P = __vimin3_u16x2(P, a[k], a[k + 1]);
+        P = __vminu2(P, a[15]);
+    }
+    // Q: max over the arcs of (min of the arc)
+#pragma unroll
+    for (int k = 0; k < 16; k++) t3[k] = __vimin3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
+    {
+        uint32_t a[16];
+#pragma unroll
+        for (int k = 0; k < 16; k++) a[k] = __vimin3_u16x2(t3[k], t3[(k + 3) & 15], t3[(k + 6) & 15]);
+        Q = __vimax3_u16x2(a[0], a[1], a[2]);
+#pragma unroll
+        for (int k = 3; k < 15; k += 2) Q = __vimax3_u16x2(Q, a[k], a[k + 1]);
+        Q = __vmaxu2(Q, a[15]);
+    }
+    // clean lanes (high byte -> value), biased by 0x100 so that plain 32-bit adds never borrow across lanes
+    const uint32_t Pc = __byte_perm(P, 0u, 0x4341), Qc = __byte_perm(Q, 0u, 0x4341), Vc = __byte_perm(c, 0u, 0x4341);
+    const uint32_t Ab = Vc + 0x01000100u - Pc;        // 0x100 + (v - P)  per lane, in [1, 0x1FF]
+    const uint32_t Bb = Qc + 0x01000100u - Vc;        // 0x100 + (Q - v)
+    const uint32_t Mb = __vmaxu2(Ab, Bb);
+    return __viaddmax_s16x2(Mb, 0xFEFFFEFFu, 0u);     // max(M - 1, 0): add -0x101 per lane
+}
+
+// window row: the 8 byte-shifted words starting at x-4 .. x+3 (x = first pixel of the thread's word)
+__device__ __forceinline__ void fast_fill_row(uint32_t (&w)[8], uint32_t l, uint32_t m, uint32_t r)
+{
+    w[0] = l;
+    w[1] = __funnelshift_r(l, m, 8);
+    w[2] = __funnelshift_r(l, m, 16);
+    w[3] = __funnelshift_r(l, m, 24);
+    w[4] = m;
+    w[5] = __funnelshift_r(m, r, 8);
+    w[6] = __funnelshift_r(m, r, 16);
+    w[7] = __funnelshift_r(m, r, 24);
+}
+
+// scores of the thread's 4 pixels of the row whose window slots are (PH + dy + 3) % 7, dy = -3..3
+template <int PH>
+__device__ __forceinline__ uint32_t fast_score_word(const uint32_t (&W)[7][8])
+{
+    constexpr int DX[16] = RING_DX;
+    constexpr int DY[16] = RING_DY;
+    uint32_t re[16], ro[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        re[k] = W[(PH + DY[k] + 3) % 7][DX[k] + 3];     // lanes: pixels x+dx, x+dx+2   (ring of px 0 and 2)
+        ro[k] = W[(PH + DY[k] + 3) % 7][DX[k] + 4];     // lanes: pixels x+dx+1, x+dx+3 (ring of px 1 and 3)
+    }
+    const uint32_t se = fast_score_pair(re, W[(PH + 3) % 7][3]);
+    const uint32_t so = fast_score_pair(ro, W[(PH + 3) % 7][4]);
+    return se + (so << 8);                               // bytes S0 S1 S2 S3
+}
+
+// 3x3 NMS row step.  R[slot][0..3]: score words starting at x-2, x-1, x, x+1 of rows r-1, r, r+1 at slots
+// (PH, PH+1, PH+2) % 3.  Returns non-zero lanes for the survivors: te = px 0,2 ; to = px 1,3.
+template <int PH>
+__device__ __forceinline__ void nms_row(const uint32_t (&R)[3][4], uint32_t thr, uint32_t ML_e, uint32_t MR_e,
+                                        uint32_t ML_o, uint32_t MR_o, uint32_t V_e, uint32_t V_o,
+                                        uint32_t& te, uint32_t& to)
+{
+    const uint32_t (&U)[4] = R[PH % 3];
+    const uint32_t (&C)[4] = R[(PH + 1) % 3];
+    const uint32_t (&D)[4] = R[(PH + 2) % 3];
+    // even pixels (x, x+2): left neighbours = lanes of word x-2, centre column = word x-1, right = word x
+    uint32_t cl = __vimax3_u16x2(U[0], C[0], D[0]) & ML_e;
+    uint32_t cr = __vimax3_u16x2(U[2], C[2], D[2]) & MR_e;
+    uint32_t cm = __vimax3_u16x2(U[1], D[1], thr);
+    uint32_t nb = __vimax3_u16x2(cl, cr, cm) | 0x00FF00FFu;
+    te = __vmaxu2(C[1] & V_e, nb) ^ nb;
+    // odd pixels (x+1, x+3): left = word x-1, centre = word x, right = word x+1
+    cl = __vimax3_u16x2(U[1], C[1], D[1]) & ML_o;
+    cr = __vimax3_u16x2(U[3], C[3], D[3]) & MR_o;
+    cm = __vimax3_u16x2(U[2], D[2], thr);
+    nb = __vimax3_u16x2(cl, cr, cm) | 0x00FF00FFu;
+    to = __vmaxu2(C[2] & V_o, nb) ^ nb;
+}
+
+__device__ __forceinline__ void nms_fill(uint32_t (&w)[4], uint32_t l, uint32_t m, uint32_t r)
+{
+    w[0] = __funnelshift_r(l, m, 16);
+    w[1] = __funnelshift_r(l, m, 24);
+    w[2] = m;
+    w[3] = __funnelshift_r(m, r, 8);
+}
+
+__global__ void __launch_bounds__(FAST_THREADS)
+fast_band_kernel(FrameGeom G, DevBuffers D)
+{
+    extern __shared__ uint32_t s_tile[];              // S words [ih][nw], then keep nibbles (bytes) [ih][nw]
+    __shared__ int s_cnt[2 * FAST_MAXCELLS];          // per cell: survivors >= iniTh, survivors in [minTh, iniTh)
+    __shared__ int s_base, s_pos;
+
+    const BandDesc bd = D.bands[blockIdx.x];
+    const int f = blockIdx.y;
+    const LevelGeom& L = G.L[bd.lvl];
+    const int Wr = L.maxBX - ORBX_MINB, Hr = L.maxBY - ORBX_MINB;     // region size, :1053-1059
+    // interior rows / columns of the band in level coordinates (cell sub-image minus its 3-px FAST border)
+    const int ys = ORBX_MINB + bd.ci * L.hCell + 3;
+    const int ye = ORBX_MINB + min(bd.ci * L.hCell + L.hCell + 6, Hr) - 3;
+    const int xs = ORBX_MINB + bd.cj0 * L.wCell + 3;
+    const int xe = ORBX_MINB + min((bd.cj1 - 1) * L.wCell + L.wCell + 6, Wr) - 3;
+    const int ih = ye - ys;
+    const int xa = xs & ~3;                           // word aligned (XOFF and the pitch are multiples of 4)
+    const int nw = (xe - xa + 3) >> 2;                // words per tile row
+    const int tid = threadIdx.x;
+    const bool active = tid < nw;
+    const int wi = active ? tid : nw - 1;
+    const int x = xa + 4 * wi;
+    uint8_t* s_keep = reinterpret_cast<uint8_t*>(s_tile + ih * nw);
+
+    if (tid < 2 * FAST_MAXCELLS) s_cnt[tid] = 0;
+    if (tid == 0) s_pos = 0;
+
+    // ---------------- phase A: score tile ----------------
+    if ((tid & ~31) < nw) {                            // warps without any column skip
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(
+            L.pyr + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + ys - 3) * L.pitch + ORBX_XOFF + x);
+        const int pw = L.pitch >> 2;
+        uint32_t W[7][8];
+#pragma unroll
+        for (int i = 0; i < 6; i++) { fast_fill_row(W[i], __ldg(p - 1), __ldg(p), __ldg(p + 1)); p += pw; }
+        uint32_t nl = __ldg(p - 1), nm = __ldg(p), nr = __ldg(p + 1);      // row ys+3
+        uint32_t* out = s_tile + wi;
+#define FAST_STEP(PH)                                                                              \
+        if (rb + PH < ih) {                                                                        \
+            const int r = rb + PH;                                                                 \
+            fast_fill_row(W[(PH + 6) % 7], nl, nm, nr);                                            \
+            if (r + 1 < ih) { p += pw; nl = __ldg(p - 1); nm = __ldg(p); nr = __ldg(p + 1); }      \
+            const uint32_t sw = fast_score_word<PH>(W);                                            \
+            if (active) out[r * nw] = sw;                                                          \
+        }
+#pragma unroll 1
+        for (int rb = 0; rb < ih; rb += 7) {
+            FAST_STEP(0) FAST_STEP(1) FAST_STEP(2) FAST_STEP(3) FAST_STEP(4) FAST_STEP(5) FAST_STEP(6)
+        }
+#undef FAST_STEP
+    }
+    __syncthreads();
+
+    // ---------------- phase B1: 3x3 NMS inside each cell, per-cell counts ----------------
+    // per-pixel cell bookkeeping of this thread's 4 pixels
+    int lc[4];                                        // cell index inside the band (0..)
+    uint32_t ML_e = 0, MR_e = 0, ML_o = 0, MR_o = 0, V_e = 0, V_o = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const int xp = x + q;
+        const bool valid = active && xp >= xs && xp < xe;
+        const int X3 = xp - ORBX_MINB - 3;
+        const int j = valid ? X3 / L.wCell : bd.cj0;
+        const int xin = X3 - j * L.wCell;
+        const int cend = ORBX_MINB + min(j * L.wCell + L.wCell + 6, Wr) - 3;      // end of cell j's interior
+        const bool lok = valid && xin > 0, rok = valid && xp + 1 < cend;
+        lc[q] = j - bd.cj0;
+        const uint32_t lane = (q & 2) ? 0xFFFF0000u : 0x0000FFFFu;
+        if (q & 1) { if (lok) ML_o |= lane; if (rok) MR_o |= lane; if (valid) V_o |= lane & 0xFF00FF00u; }
+        else       { if (lok) ML_e |= lane; if (rok) MR_e |= lane; if (valid) V_e |= lane & 0xFF00FF00u; }
+    }
+    const int iniTh = G.iniTh, minTh = min(G.minTh, G.iniTh);
+    const uint32_t thr = (uint32_t)(((minTh - 1) << 8) | 0xFF) * 0x00010001u;
+    if (active) {
+        const uint32_t* sp = s_tile + wi;
+        const bool hasl = wi > 0, hasr = wi + 1 < nw;
+        uint32_t R[3][4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) R[0][k] = 0;
+        nms_fill(R[1], hasl ? sp[-1] : 0u, sp[0], hasr ? sp[1] : 0u);
+#define NMS_STEP(PH)                                                                                        \
+        if (rb + PH < ih) {                                                                                 \
+            const int r = rb + PH;                                                                          \
+            if (r + 1 < ih) { const uint32_t* q = sp + (r + 1) * nw;                                        \
+                              nms_fill(R[(PH + 2) % 3], hasl ? q[-1] : 0u, q[0], hasr ? q[1] : 0u); }       \
+            else { R[(PH + 2) % 3][0] = R[(PH + 2) % 3][1] = R[(PH + 2) % 3][2] = R[(PH + 2) % 3][3] = 0; } \
+            uint32_t te, to;                                                                                \
+            nms_row<PH>(R, thr, ML_e, MR_e, ML_o, MR_o, V_e, V_o, te, to);                                  \
+            uint32_t nib = 0;                                                                               \
+            if (te | to) {                                                                                  \
+                const uint32_t sw = R[(PH + 1) % 3][2];                                                     \
+                if (te & 0xFFFFu) { nib |= 1; atomicAdd(&s_cnt[2 * lc[0] + ((int)(sw & 0xFF) >= iniTh ? 0 : 1)], 1); }          \
+                if (to & 0xFFFFu) { nib |= 2; atomicAdd(&s_cnt[2 * lc[1] + ((int)((sw >> 8) & 0xFF) >= iniTh ? 0 : 1)], 1); }   \
+                if (te >> 16)     { nib |= 4; atomicAdd(&s_cnt[2 * lc[2] + ((int)((sw >> 16) & 0xFF) >= iniTh ? 0 : 1)], 1); }  \
+                if (to >> 16)     { nib |= 8; atomicAdd(&s_cnt[2 * lc[3] + ((int)(sw >> 24) >= iniTh ? 0 : 1)], 1); }           \
+            }                                                                                               \
+            s_keep[r * nw + wi] = (uint8_t)nib;                                                             \
+        }
+#pragma unroll 1
+        for (int rb = 0; rb < ih; rb += 3) { NMS_STEP(0) NMS_STEP(1) NMS_STEP(2) }
+#undef NMS_STEP
+    }
+    __syncthreads();
+
+    // ---------------- phase B2: reserve a range of the level's candidate list and emit ----------------
+    const int ncell = bd.cj1 - bd.cj0;
+    if (tid == 0) {
+        int total = 0;
+        for (int c = 0; c < ncell; c++) total += s_cnt[2 * c] > 0 ? s_cnt[2 * c] : s_cnt[2 * c + 1];   // retry, :1118
+        s_base = total > 0 ? atomicAdd(&D.candcnt[f * G.nlevels + bd.lvl], total) : 0;
+    }
+    __syncthreads();
+    if (active) {
+        uint32_t* cand = D.cand + (long long)f * G.cand_per_frame + L.cand_base + s_base;
+        const uint32_t ybase = (uint32_t)(ys - ORBX_MINB), xbase = (uint32_t)(x - ORBX_MINB);
+        for (int r = 0; r < ih; r++) {
+            const uint32_t nib = s_keep[r * nw + wi];
+            if (nib) {
+                const uint32_t sw = s_tile[r * nw + wi];
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    if (nib & (1u << q)) {
+                        const int s = (sw >> (8 * q)) & 0xFF;
+                        if (s >= iniTh || s_cnt[2 * lc[q]] == 0)
+                            cand[atomicAdd(&s_pos, 1)] = MAKE_KEY(xbase + q, ybase + r, s);
+                    }
+                }
+            }
+        }
+    }
+}
+
+// FAST work units of one frame: per level and cell row, segments of whole cells <= FAST_MAXSPAN px wide.
+// Cells the reference skips (:1085,1102: iniX >= maxBorderX-6, iniY >= maxBorderY-3, or narrower than the
+// 7-px FAST footprint) are left out.  Returns the dynamic shared memory the kernel needs.
+int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out)
+{
+    int smem = 0;
+    out->clear();
+    for (int l = 0; l < G.nlevels; l++) {
+        const LevelGeom& L = G.L[l];
+        const int Wr = L.maxBX - ORBX_MINB, Hr = L.maxBY - ORBX_MINB;
+        int ncv = 0, nrv = 0;
+        while (ncv < L.nCols && ncv * L.wCell <= Wr - 7) ncv++;
+        while (nrv < L.nRows && nrv * L.hCell <= Hr - 7) nrv++;
+        int per = (FAST_MAXSPAN - 3) / L.wCell;
+        if (per > FAST_MAXCELLS) per = FAST_MAXCELLS;
+        for (int i = 0; i < nrv; i++) {
+            const int ih = (L.hCell + 6 < Hr - i * L.hCell ? L.hCell + 6 : Hr - i * L.hCell) - 6;
+            for (int j0 = 0; j0 < ncv; j0 += per) {
+                const int j1 = j0 + per < ncv ? j0 + per : ncv;
+                BandDesc b; b.lvl = (short)l; b.ci = (short)i; b.cj0 = (short)j0; b.cj1 = (short)j1;
+                out->push_back(b);
+                const int xs = ORBX_MINB + j0 * L.wCell + 3;
+                const int xe = ORBX_MINB + ((j1 - 1) * L.wCell + L.wCell + 6 < Wr ? (j1 - 1) * L.wCell + L.wCell + 6 : Wr) - 3;
+                const int nw = (xe - (xs & ~3) + 3) >> 2;
+                const int need = ih * nw * 5 + 16;
+                if (need > smem) smem = need;
+            }
+        }
+    }
+    return smem;
+}
+
+int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
+{
+    cudaMemsetAsync(D.candcnt, 0, sizeof(int) * (size_t)nframes * G.nlevels, s);
+    if (G.fast_smem > 48 * 1024)
+        cudaFuncSetAttribute(fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G.fast_smem);
+    const dim3 grid(G.bands_per_frame, nframes);
+    fast_band_kernel<<<grid, FAST_THREADS, G.fast_smem, s>>>(G, D);
+    return 1;
+}
+
+// scalar restatement kept for the unit-test entry below
 __device__ __forceinline__ int fast_score(const uint8_t* p, int pitch, int t)
 {
     const int v = p[0];
@@ -52,105 +344,6 @@ __device__ __forceinline__ int fast_score(const uint8_t* p, int pitch, int t)
     }
     if (!(A > t || Bn > t)) return 0;
     return max(max(A, Bn), t) - 1;
-}
-
-__global__ void __launch_bounds__(FAST_THREADS)
-fast_cells_kernel(FrameGeom G, DevBuffers D)
-{
-    __shared__ uint8_t tile[TILE_MAXH * TILE_MAXW];
-    __shared__ uint8_t sc[(SC_MAXW) * (SC_MAXW)];
-    __shared__ uint8_t keep[70 * 70];
-    __shared__ int warp_tot[FAST_THREADS / 32];
-    __shared__ int s_total;
-
-    const int f = blockIdx.y;
-    int c = blockIdx.x;
-    int lvl = 0;
-#pragma unroll 1
-    for (int l = 1; l < G.nlevels; l++) if (c >= G.L[l].cell_base) lvl = l;
-    const LevelGeom& L = G.L[lvl];
-    c -= L.cell_base;
-    const int ci = c / L.nCols, cj = c - ci * L.nCols;
-    uint32_t* cnt_out = D.cellcnt + (long long)f * G.cells_per_frame + L.cell_base + c;
-    uint32_t* key_out = D.cellkey + (long long)f * G.keys_per_frame + L.key_base + (long long)c * L.cell_cap;
-
-    // cell geometry, src/ORBextractor.cc:1078-1106 (all values are small integers, float math is exact)
-    const int y0 = ORBX_MINB + ci * L.hCell, x0 = ORBX_MINB + cj * L.wCell;
-    const int y1 = min(y0 + L.hCell + 6, L.maxBY), x1 = min(x0 + L.wCell + 6, L.maxBX);
-    const int sw = x1 - x0, sh = y1 - y0;
-    if (y0 >= L.maxBY - 3 || x0 >= L.maxBX - 6 || sw < 7 || sh < 7) {
-        if (threadIdx.x == 0) *cnt_out = 0;
-        return;
-    }
-    const int iw = sw - 6, ih = sh - 6;      // tested interior
-    const int scp = iw + 2;
-
-    const uint8_t* src = L.pyr + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + y0) * L.pitch + ORBX_XOFF + x0;
-    for (int i = threadIdx.x; i < sw * sh; i += FAST_THREADS) {
-        const int r = i / sw, cc = i - r * sw;
-        tile[r * TILE_MAXW + cc] = __ldg(src + (long long)r * L.pitch + cc);
-    }
-    for (int i = threadIdx.x; i < scp * (ih + 2); i += FAST_THREADS) sc[i] = 0;
-    __syncthreads();
-
-    const int P = iw * ih;
-    const int chunk = (P + FAST_THREADS - 1) / FAST_THREADS;
-    const int p0 = min(P, (int)threadIdx.x * chunk), p1 = min(P, p0 + chunk);
-    int th = G.iniTh;
-#pragma unroll 1
-    for (int pass = 0; pass < 2; pass++) {
-        for (int i = threadIdx.x; i < P; i += FAST_THREADS) {
-            const int y = i / iw, x = i - y * iw;
-            sc[(y + 1) * scp + x + 1] = (uint8_t)fast_score(tile + (y + 3) * TILE_MAXW + x + 3, TILE_MAXW, th);
-        }
-        __syncthreads();
-        int mycount = 0;
-        for (int i = p0; i < p1; i++) {
-            const int y = i / iw, x = i - y * iw;
-            const uint8_t* q = sc + (y + 1) * scp + x + 1;
-            const int s = q[0];
-            const bool k = s != 0 && s > q[-1] && s > q[1] && s > q[-scp - 1] && s > q[-scp] && s > q[-scp + 1] &&
-                           s > q[scp - 1] && s > q[scp] && s > q[scp + 1];
-            keep[i] = k;
-            mycount += k;
-        }
-        // block exclusive scan of mycount
-        int incl = mycount;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int n = __shfl_up_sync(0xffffffffu, incl, o);
-            if ((threadIdx.x & 31) >= o) incl += n;
-        }
-        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = incl;
-        __syncthreads();
-        int base = 0, total = 0;
-#pragma unroll
-        for (int wv = 0; wv < FAST_THREADS / 32; wv++) {
-            if (wv < (int)(threadIdx.x >> 5)) base += warp_tot[wv];
-            total += warp_tot[wv];
-        }
-        if (total > 0 || pass == 1) {
-            int o = base + incl - mycount;
-            for (int i = p0; i < p1; i++) {
-                if (keep[i]) {
-                    const int y = i / iw, x = i - y * iw;
-                    key_out[o++] = MAKE_KEY(x + 3 + cj * L.wCell, y + 3 + ci * L.hCell, sc[(y + 1) * scp + x + 1]);
-                }
-            }
-            if (threadIdx.x == 0) *cnt_out = (uint32_t)total;
-            return;
-        }
-        th = G.minTh;          // cell empty at iniThFAST -> retry, src/ORBextractor.cc:1118-1125
-        __syncthreads();       // everyone done with sc/keep/warp_tot before the second pass
-    }
-    (void)s_total;
-}
-
-int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
-{
-    const dim3 grid(G.cells_per_frame, nframes);
-    fast_cells_kernel<<<grid, FAST_THREADS, 0, s>>>(G, D);
-    return 1;
 }
 
 // ---- unit-test entry: plain per-pixel score map of a host image (no cells, no NMS) ----

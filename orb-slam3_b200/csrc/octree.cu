@@ -59,6 +59,14 @@ __device__ __forceinline__ int child_of(int x, int y, int x0, int y0, int x1, in
     return (x < mx) ? ((y < my) ? 0 : 2) : ((y < my) ? 1 : 3);   // :651-661
 }
 
+// position of a candidate in the reference's vToDistributeKeys order (cell row-major, raster inside a cell)
+__device__ __forceinline__ int cand_rank(uint32_t key, const LevelGeom& L)
+{
+    const int X3 = (int)KEY_X(key) - 3, Y3 = (int)KEY_Y(key) - 3;
+    const int cj = X3 / L.wCell, ci = Y3 / L.hCell;
+    return ((ci * L.nCols + cj) << 14) | ((Y3 - ci * L.hCell) << 7) | (X3 - cj * L.wCell);
+}
+
 __global__ void __launch_bounds__(OCT_THREADS)
 octree_kernel(FrameGeom G, DevBuffers D, int use_smem)
 {
@@ -87,20 +95,8 @@ octree_kernel(FrameGeom G, DevBuffers D, int use_smem)
     int* headoff = T + 17 * cap;      // new list position of a split node's first child slot
     int* tailpos = T + 18 * cap;      // new list position of an unsplit node
 
-    // ---- gather the cells' keypoints in reference order (cell row-major, raster inside a cell) ----
-    const int ncell = L.nCols * L.nRows;
-    const uint32_t* ccnt = D.cellcnt + (long long)f * G.cells_per_frame + L.cell_base;
-    int* coff = D.celloff + (long long)f * G.cells_per_frame + L.cell_base;
-    const int n = block_scan_excl((const int*)ccnt, coff, ncell, s_warp);
-    {
-        const uint32_t* ckey = D.cellkey + (long long)f * G.keys_per_frame + L.key_base;
-        const int warp = tid >> 5, lane = tid & 31;
-        for (int c = warp; c < ncell; c += OCT_THREADS / 32) {
-            const int cn = (int)ccnt[c], o = coff[c];
-            for (int k = lane; k < cn; k += 32) cand[o + k] = ckey[(long long)c * L.cell_cap + k];
-        }
-    }
-    if (tid == 0) D.candcnt[f * G.nlevels + lvl] = n;
+    // candidates were compacted (in arbitrary order) by fast_band_kernel
+    const int n = min(D.candcnt[f * G.nlevels + lvl], L.cand_cap);
     const int N = L.N;
     const int H = L.maxBY - ORBX_MINB;
 
@@ -272,16 +268,27 @@ octree_kernel(FrameGeom G, DevBuffers D, int use_smem)
         __syncthreads();
     }
 
-    // ---- best response per node, first in candidate order on ties (:1005-1030) ----
+    // ---- best response per node; ties go to the first keypoint in the reference's vector order
+    // (:1005-1030), i.e. the smallest canonical rank (cell row, cell col, y, x) ----
     int* best = tmpA;
-    for (int i = tid; i < size; i += OCT_THREADS) best[i] = 0;
+    int* bestrank = tmpB;
+    for (int i = tid; i < size; i += OCT_THREADS) { best[i] = 0; bestrank[i] = 0x7FFFFFFF; }
     __syncthreads();
-    for (int i = tid; i < n; i += OCT_THREADS)
-        atomicMax((unsigned int*)&best[knode[i]], (KEY_S(cand[i]) << 24) | (0xFFFFFFu - (uint32_t)i));
+    for (int i = tid; i < n; i += OCT_THREADS) atomicMax(&best[knode[i]], (int)KEY_S(cand[i]));
+    __syncthreads();
+    for (int i = tid; i < n; i += OCT_THREADS) {
+        const uint32_t k = cand[i];
+        const int nd = knode[i];
+        if ((int)KEY_S(k) == best[nd]) atomicMin(&bestrank[nd], cand_rank(k, L));
+    }
     __syncthreads();
     uint32_t* sel = D.sel + (long long)f * G.sel_per_frame + L.sel_base;
     const int nout = min(size, L.sel_cap);
-    for (int i = tid; i < nout; i += OCT_THREADS) sel[i] = cand[0xFFFFFFu - ((uint32_t)best[i] & 0xFFFFFFu)];
+    for (int i = tid; i < n; i += OCT_THREADS) {
+        const uint32_t k = cand[i];
+        const int nd = knode[i];
+        if (nd < nout && (int)KEY_S(k) == best[nd] && cand_rank(k, L) == bestrank[nd]) sel[nd] = k;
+    }
     if (tid == 0) D.selcnt[f * G.nlevels + lvl] = nout;
 }
 

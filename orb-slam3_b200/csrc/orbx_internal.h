@@ -59,8 +59,13 @@ struct LevelGeom {
     const ResizeTapY* tapy;   // h + 38 entries
 };
 
+// one FAST work unit: the interiors of cells [cj0, cj1) of cell row ci of level lvl (<= 768 px wide)
+struct BandDesc { short lvl, ci, cj0, cj1; };
+
 struct FrameGeom {
     int nlevels;
+    int bands_per_frame;      // FAST band segments per frame (DevBuffers::bands)
+    int fast_smem;            // dynamic shared memory of fast_band_kernel (bytes)
     int rows, cols;           // input image size
     int batch;                // frame slots
     int cells_per_frame;
@@ -75,9 +80,7 @@ struct FrameGeom {
 struct DevBuffers {
     uint8_t* input;           // batch x rows x in_pitch staging of the uploaded frames
     int in_pitch;
-    uint32_t* cellcnt;        // [batch][cells_per_frame]
-    uint32_t* cellkey;        // [batch][keys_per_frame]
-    int* celloff;             // [batch][cells_per_frame] quadtree scratch: prefix of cellcnt per level
+    const BandDesc* bands;    // [bands_per_frame] FAST work units (same for every frame)
     uint32_t* cand;           // [batch][cand_per_frame]
     uint32_t* candnode;       // [batch][cand_per_frame]  quadtree scratch: node of each candidate
     int* nodetab;             // quadtree scratch: node tables
@@ -99,5 +102,9 @@ int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStre
 int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int lap0, int lap1, cudaStream_t s);
 int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
 int launch_describe(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
+#ifdef __cplusplus
+#include <vector>
+int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out);   // returns the kernel's dynamic smem bytes
+#endif
 size_t octree_nodetab_ints(const FrameGeom& G);   // ints of node scratch per frame
 void octree_assign_node_offsets(FrameGeom& G);
