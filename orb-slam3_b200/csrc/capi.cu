@@ -160,7 +160,7 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     D.nodetab_per_frame = (long long)octree_nodetab_ints(G);
     {
         std::vector<BandDesc> bands;
-        G.fast_smem = fast_build_bands(G, &bands);
+        G.fast_smem = fast_build_bands(G, &bands, &G.fast_warp_words);
         G.bands_per_frame = (int)bands.size();
         BandDesc* db = nullptr;
         if (!rc) rc |= dev_alloc(e, &db, bands.size());

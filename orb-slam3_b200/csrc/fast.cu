@@ -22,10 +22,10 @@
 #include "orbx_internal.h"
 #include <vector>
 
-#define FAST_WARPS 6
+#define FAST_WARPS 4
 #define FAST_THREADS (FAST_WARPS * 32)
-#define FAST_MAXSPAN (FAST_THREADS * 4)
-#define FAST_MAXCELLS 24
+#define FAST_MAXSPAN 128               // pixels per work item: one warp, 4 px per lane
+#define FAST_MAXCELLS 4
 
 // ring offsets of cv::FAST 9_16 (oracle/orc_prims.c)
 #define RING_DX {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1}
@@ -131,14 +131,14 @@ __device__ __forceinline__ void nms_fill(uint32_t (&w)[4], uint32_t l, uint32_t 
     w[3] = __funnelshift_r(m, r, 8);
 }
 
-__global__ void __launch_bounds__(FAST_THREADS)
+__global__ void __launch_bounds__(FAST_THREADS, 5)
 fast_band_kernel(FrameGeom G, DevBuffers D)
 {
-    extern __shared__ uint32_t s_tile[];              // S words [ih][nw], then keep nibbles (bytes) [ih][nw]
-    __shared__ int s_cnt[2 * FAST_MAXCELLS];          // per cell: survivors >= iniTh, survivors in [minTh, iniTh)
-    __shared__ int s_base, s_pos;
-
-    const BandDesc bd = D.bands[blockIdx.x];
+    extern __shared__ uint32_t s_dyn[];               // per warp: S words [ihmax][32], then u16 survivor list
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int item = blockIdx.x * FAST_WARPS + warp;
+    if (item >= G.bands_per_frame) return;            // warps are independent: no block-level barrier below
+    const BandDesc bd = D.bands[item];
     const int f = blockIdx.y;
     const LevelGeom& L = G.L[bd.lvl];
     const int Wr = L.maxBX - ORBX_MINB, Hr = L.maxBY - ORBX_MINB;     // region size, :1053-1059
@@ -149,33 +149,36 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
     const int xe = ORBX_MINB + min((bd.cj1 - 1) * L.wCell + L.wCell + 6, Wr) - 3;
     const int ih = ye - ys;
     const int xa = xs & ~3;                           // word aligned (XOFF and the pitch are multiples of 4)
-    const int nw = (xe - xa + 3) >> 2;                // words per tile row
-    const int tid = threadIdx.x;
-    const bool active = tid < nw;
-    const int wi = active ? tid : nw - 1;
+    const int nw = (xe - xa + 3) >> 2;                // words per row, <= 32
+    const bool active = lane < nw;
+    const int wi = active ? lane : nw - 1;
     const int x = xa + 4 * wi;
-    uint8_t* s_keep = reinterpret_cast<uint8_t*>(s_tile + ih * nw);
-
-    if (tid < 2 * FAST_MAXCELLS) s_cnt[tid] = 0;
-    if (tid == 0) s_pos = 0;
+    uint32_t* s_tile = s_dyn + warp * G.fast_warp_words;
+    uint16_t* s_list = reinterpret_cast<uint16_t*>(s_tile + ih * 32);
 
     // ---------------- phase A: score tile ----------------
-    if ((tid & ~31) < nw) {                            // warps without any column skip
-        const uint32_t* p = reinterpret_cast<const uint32_t*>(
+    {
+        const uint32_t* p0 = reinterpret_cast<const uint32_t*>(
             L.pyr + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + ys - 3) * L.pitch + ORBX_XOFF + x);
         const int pw = L.pitch >> 2;
+        const int klast = ih + 5;                     // last window row (ye + 2) relative to ys - 3
         uint32_t W[7][8];
 #pragma unroll
-        for (int i = 0; i < 6; i++) { fast_fill_row(W[i], __ldg(p - 1), __ldg(p), __ldg(p + 1)); p += pw; }
-        uint32_t nl = __ldg(p - 1), nm = __ldg(p), nr = __ldg(p + 1);      // row ys+3
+        for (int i = 0; i < 6; i++) { const uint32_t* p = p0 + i * pw; fast_fill_row(W[i], __ldg(p - 1), __ldg(p), __ldg(p + 1)); }
+        // two rows in flight ahead of the window
+        const uint32_t* pa = p0 + 6 * pw;
+        uint32_t al = __ldg(pa - 1), am = __ldg(pa), ar = __ldg(pa + 1);
+        const uint32_t* pb = p0 + min(7, klast) * pw;
+        uint32_t bl = __ldg(pb - 1), bm = __ldg(pb), br = __ldg(pb + 1);
         uint32_t* out = s_tile + wi;
 #define FAST_STEP(PH)                                                                              \
         if (rb + PH < ih) {                                                                        \
             const int r = rb + PH;                                                                 \
-            fast_fill_row(W[(PH + 6) % 7], nl, nm, nr);                                            \
-            if (r + 1 < ih) { p += pw; nl = __ldg(p - 1); nm = __ldg(p); nr = __ldg(p + 1); }      \
+            fast_fill_row(W[(PH + 6) % 7], al, am, ar);                                            \
+            al = bl; am = bm; ar = br;                                                             \
+            { const uint32_t* pn = p0 + min(r + 8, klast) * pw; bl = __ldg(pn - 1); bm = __ldg(pn); br = __ldg(pn + 1); } \
             const uint32_t sw = fast_score_word<PH>(W);                                            \
-            if (active) out[r * nw] = sw;                                                          \
+            if (active) out[r * 32] = sw;                                                          \
         }
 #pragma unroll 1
         for (int rb = 0; rb < ih; rb += 7) {
@@ -183,11 +186,10 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
         }
 #undef FAST_STEP
     }
-    __syncthreads();
+    __syncwarp();
 
-    // ---------------- phase B1: 3x3 NMS inside each cell, per-cell counts ----------------
-    // per-pixel cell bookkeeping of this thread's 4 pixels
-    int lc[4];                                        // cell index inside the band (0..)
+    // ---------------- phase B1: 3x3 NMS inside each cell, survivors appended to the list ----------------
+    int lc[4];                                        // cell of each of the thread's 4 pixels (0.. inside the item)
     uint32_t ML_e = 0, MR_e = 0, ML_o = 0, MR_o = 0, V_e = 0, V_o = 0;
 #pragma unroll
     for (int q = 0; q < 4; q++) {
@@ -199,15 +201,17 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
         const int cend = ORBX_MINB + min(j * L.wCell + L.wCell + 6, Wr) - 3;      // end of cell j's interior
         const bool lok = valid && xin > 0, rok = valid && xp + 1 < cend;
         lc[q] = j - bd.cj0;
-        const uint32_t lane = (q & 2) ? 0xFFFF0000u : 0x0000FFFFu;
-        if (q & 1) { if (lok) ML_o |= lane; if (rok) MR_o |= lane; if (valid) V_o |= lane & 0xFF00FF00u; }
-        else       { if (lok) ML_e |= lane; if (rok) MR_e |= lane; if (valid) V_e |= lane & 0xFF00FF00u; }
+        const uint32_t ln = (q & 2) ? 0xFFFF0000u : 0x0000FFFFu;
+        if (q & 1) { if (lok) ML_o |= ln; if (rok) MR_o |= ln; if (valid) V_o |= ln & 0xFF00FF00u; }
+        else       { if (lok) ML_e |= ln; if (rok) MR_e |= ln; if (valid) V_e |= ln & 0xFF00FF00u; }
     }
     const int iniTh = G.iniTh, minTh = min(G.minTh, G.iniTh);
     const uint32_t thr = (uint32_t)(((minTh - 1) << 8) | 0xFF) * 0x00010001u;
-    if (active) {
+    const uint32_t lt = (1u << lane) - 1u;
+    int cnt = 0;                                      // list length (warp-uniform)
+    {
         const uint32_t* sp = s_tile + wi;
-        const bool hasl = wi > 0, hasr = wi + 1 < nw;
+        const bool hasl = active && wi > 0, hasr = active && wi + 1 < nw;
         uint32_t R[3][4];
 #pragma unroll
         for (int k = 0; k < 4; k++) R[0][k] = 0;
@@ -215,61 +219,85 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
 #define NMS_STEP(PH)                                                                                        \
         if (rb + PH < ih) {                                                                                 \
             const int r = rb + PH;                                                                          \
-            if (r + 1 < ih) { const uint32_t* q = sp + (r + 1) * nw;                                        \
+            if (r + 1 < ih) { const uint32_t* q = sp + (r + 1) * 32;                                        \
                               nms_fill(R[(PH + 2) % 3], hasl ? q[-1] : 0u, q[0], hasr ? q[1] : 0u); }       \
             else { R[(PH + 2) % 3][0] = R[(PH + 2) % 3][1] = R[(PH + 2) % 3][2] = R[(PH + 2) % 3][3] = 0; } \
             uint32_t te, to;                                                                                \
             nms_row<PH>(R, thr, ML_e, MR_e, ML_o, MR_o, V_e, V_o, te, to);                                  \
-            uint32_t nib = 0;                                                                               \
-            if (te | to) {                                                                                  \
-                const uint32_t sw = R[(PH + 1) % 3][2];                                                     \
-                if (te & 0xFFFFu) { nib |= 1; atomicAdd(&s_cnt[2 * lc[0] + ((int)(sw & 0xFF) >= iniTh ? 0 : 1)], 1); }          \
-                if (to & 0xFFFFu) { nib |= 2; atomicAdd(&s_cnt[2 * lc[1] + ((int)((sw >> 8) & 0xFF) >= iniTh ? 0 : 1)], 1); }   \
-                if (te >> 16)     { nib |= 4; atomicAdd(&s_cnt[2 * lc[2] + ((int)((sw >> 16) & 0xFF) >= iniTh ? 0 : 1)], 1); }  \
-                if (to >> 16)     { nib |= 8; atomicAdd(&s_cnt[2 * lc[3] + ((int)(sw >> 24) >= iniTh ? 0 : 1)], 1); }           \
+            if (__ballot_sync(0xffffffffu, (te | to) != 0u)) {                                              \
+                const bool k0 = (te & 0xFFFFu) != 0u, k1 = (to & 0xFFFFu) != 0u, k2 = (te >> 16) != 0u, k3 = (to >> 16) != 0u; \
+                const int c = (int)k0 + (int)k1 + (int)k2 + (int)k3;       /* <= 3: one cell boundary per word at most */ \
+                const uint32_t m0 = __ballot_sync(0xffffffffu, c & 1), m1 = __ballot_sync(0xffffffffu, c & 2); \
+                int o = cnt + __popc(m0 & lt) + 2 * __popc(m1 & lt);                                        \
+                cnt += __popc(m0) + 2 * __popc(m1);                                                         \
+                const int e = (r << 7) | (4 * wi);                                                          \
+                if (k0) s_list[o++] = (uint16_t)e;                                                          \
+                if (k1) s_list[o++] = (uint16_t)(e + 1);                                                    \
+                if (k2) s_list[o++] = (uint16_t)(e + 2);                                                    \
+                if (k3) s_list[o++] = (uint16_t)(e + 3);                                                    \
             }                                                                                               \
-            s_keep[r * nw + wi] = (uint8_t)nib;                                                             \
         }
 #pragma unroll 1
         for (int rb = 0; rb < ih; rb += 3) { NMS_STEP(0) NMS_STEP(1) NMS_STEP(2) }
 #undef NMS_STEP
     }
-    __syncthreads();
+    __syncwarp();
 
-    // ---------------- phase B2: reserve a range of the level's candidate list and emit ----------------
+    // ---------------- phase B2: per-cell retry rule (:1118-1125) and emission ----------------
     const int ncell = bd.cj1 - bd.cj0;
-    if (tid == 0) {
-        int total = 0;
-        for (int c = 0; c < ncell; c++) total += s_cnt[2 * c] > 0 ? s_cnt[2 * c] : s_cnt[2 * c + 1];   // retry, :1118
-        s_base = total > 0 ? atomicAdd(&D.candcnt[f * G.nlevels + bd.lvl], total) : 0;
-    }
-    __syncthreads();
-    if (active) {
-        uint32_t* cand = D.cand + (long long)f * G.cand_per_frame + L.cand_base + s_base;
-        const uint32_t ybase = (uint32_t)(ys - ORBX_MINB), xbase = (uint32_t)(x - ORBX_MINB);
-        for (int r = 0; r < ih; r++) {
-            const uint32_t nib = s_keep[r * nw + wi];
-            if (nib) {
-                const uint32_t sw = s_tile[r * nw + wi];
+    const uint8_t* s_score = reinterpret_cast<const uint8_t*>(s_tile);
+    const int xrel = xa - ORBX_MINB, yrel = ys - ORBX_MINB;
+    int nhi[FAST_MAXCELLS], nlo[FAST_MAXCELLS];        // survivors >= iniTh / in [minTh, iniTh) per cell (uniform)
 #pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    if (nib & (1u << q)) {
-                        const int s = (sw >> (8 * q)) & 0xFF;
-                        if (s >= iniTh || s_cnt[2 * lc[q]] == 0)
-                            cand[atomicAdd(&s_pos, 1)] = MAKE_KEY(xbase + q, ybase + r, s);
-                    }
-                }
+    for (int c = 0; c < FAST_MAXCELLS; c++) nhi[c] = nlo[c] = 0;
+    for (int i0 = 0; i0 < cnt; i0 += 32) {
+        const int i = i0 + lane;
+        const bool valid = i < cnt;
+        const int e = valid ? s_list[i] : 0;
+        const int px = e & 127, r = e >> 7;
+        const int sc = s_score[r * 128 + px];
+        const int cell = (xrel + px - 3) / L.wCell - bd.cj0;
+        const bool hi = valid && sc >= iniTh;
+#pragma unroll
+        for (int c = 0; c < FAST_MAXCELLS; c++) {
+            if (c < ncell) {
+                nhi[c] += __popc(__ballot_sync(0xffffffffu, hi && cell == c));
+                nlo[c] += __popc(__ballot_sync(0xffffffffu, valid && !hi && cell == c));
             }
         }
     }
+    int total = 0;
+#pragma unroll
+    for (int c = 0; c < FAST_MAXCELLS; c++) total += nhi[c] > 0 ? nhi[c] : nlo[c];
+    if (total == 0) return;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(&D.candcnt[f * G.nlevels + bd.lvl], total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    uint32_t* cand = D.cand + (long long)f * G.cand_per_frame + L.cand_base;
+    for (int i0 = 0; i0 < cnt; i0 += 32) {
+        const int i = i0 + lane;
+        const bool valid = i < cnt;
+        const int e = valid ? s_list[i] : 0;
+        const int px = e & 127, r = e >> 7;
+        const int sc = s_score[r * 128 + px];
+        const int cell = (xrel + px - 3) / L.wCell - bd.cj0;
+        int ch = nhi[0];
+#pragma unroll
+        for (int c = 1; c < FAST_MAXCELLS; c++) if (cell == c) ch = nhi[c];
+        const bool emit = valid && (sc >= iniTh || ch == 0);
+        const uint32_t m = __ballot_sync(0xffffffffu, emit);
+        if (emit) cand[base + __popc(m & lt)] = MAKE_KEY(xrel + px, yrel + r, sc);
+        base += __popc(m);
+    }
 }
 
-// FAST work units of one frame: per level and cell row, segments of whole cells <= FAST_MAXSPAN px wide.
-// Cells the reference skips (:1085,1102: iniX >= maxBorderX-6, iniY >= maxBorderY-3, or narrower than the
-// 7-px FAST footprint) are left out.  Returns the dynamic shared memory the kernel needs.
-int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out)
+// FAST work items of one frame: per level and cell row, runs of whole cells spanning <= 128 px (one warp,
+// 4 px per lane).  Cells the reference skips (:1085,1102: iniX >= maxBorderX-6, iniY >= maxBorderY-3, or
+// narrower than the 7-px FAST footprint) are left out.  Returns the kernel's dynamic shared memory and
+// sets *warp_words (32-bit words of shared memory per warp).
+int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out, int* warp_words)
 {
-    int smem = 0;
+    int ihmax = 1;
     out->clear();
     for (int l = 0; l < G.nlevels; l++) {
         const LevelGeom& L = G.L[l];
@@ -279,21 +307,22 @@ int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out)
         while (nrv < L.nRows && nrv * L.hCell <= Hr - 7) nrv++;
         int per = (FAST_MAXSPAN - 3) / L.wCell;
         if (per > FAST_MAXCELLS) per = FAST_MAXCELLS;
+        if (per < 1 || ncv < 1) continue;
+        const int nseg = (ncv + per - 1) / per, q = ncv / nseg, rem = ncv % nseg;   // balanced split
         for (int i = 0; i < nrv; i++) {
             const int ih = (L.hCell + 6 < Hr - i * L.hCell ? L.hCell + 6 : Hr - i * L.hCell) - 6;
-            for (int j0 = 0; j0 < ncv; j0 += per) {
-                const int j1 = j0 + per < ncv ? j0 + per : ncv;
+            if (ih > ihmax) ihmax = ih;
+            int j0 = 0;
+            for (int sgm = 0; sgm < nseg; sgm++) {
+                const int j1 = j0 + q + (sgm < rem ? 1 : 0);
                 BandDesc b; b.lvl = (short)l; b.ci = (short)i; b.cj0 = (short)j0; b.cj1 = (short)j1;
                 out->push_back(b);
-                const int xs = ORBX_MINB + j0 * L.wCell + 3;
-                const int xe = ORBX_MINB + ((j1 - 1) * L.wCell + L.wCell + 6 < Wr ? (j1 - 1) * L.wCell + L.wCell + 6 : Wr) - 3;
-                const int nw = (xe - (xs & ~3) + 3) >> 2;
-                const int need = ih * nw * 5 + 16;
-                if (need > smem) smem = need;
+                j0 = j1;
             }
         }
     }
-    return smem;
+    *warp_words = ihmax * 32 + (ihmax + 1) * 16;      // S tile + u16 list of <= 32*(ih+1) survivors
+    return FAST_WARPS * *warp_words * 4;
 }
 
 int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
@@ -301,7 +330,7 @@ int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream
     cudaMemsetAsync(D.candcnt, 0, sizeof(int) * (size_t)nframes * G.nlevels, s);
     if (G.fast_smem > 48 * 1024)
         cudaFuncSetAttribute(fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G.fast_smem);
-    const dim3 grid(G.bands_per_frame, nframes);
+    const dim3 grid((G.bands_per_frame + FAST_WARPS - 1) / FAST_WARPS, nframes);
     fast_band_kernel<<<grid, FAST_THREADS, G.fast_smem, s>>>(G, D);
     return 1;
 }

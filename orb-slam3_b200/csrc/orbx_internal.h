@@ -59,13 +59,14 @@ struct LevelGeom {
     const ResizeTapY* tapy;   // h + 38 entries
 };
 
-// one FAST work unit: the interiors of cells [cj0, cj1) of cell row ci of level lvl (<= 768 px wide)
+// one FAST work item (one warp): the interiors of cells [cj0, cj1) of cell row ci of level lvl (<= 128 px wide)
 struct BandDesc { short lvl, ci, cj0, cj1; };
 
 struct FrameGeom {
     int nlevels;
     int bands_per_frame;      // FAST band segments per frame (DevBuffers::bands)
     int fast_smem;            // dynamic shared memory of fast_band_kernel (bytes)
+    int fast_warp_words;      // ... of which 32-bit words per warp
     int rows, cols;           // input image size
     int batch;                // frame slots
     int cells_per_frame;
@@ -104,7 +105,7 @@ int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream
 int launch_describe(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
 #ifdef __cplusplus
 #include <vector>
-int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out);   // returns the kernel's dynamic smem bytes
+int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out, int* warp_words);   // returns the kernel's dynamic smem bytes
 #endif
 size_t octree_nodetab_ints(const FrameGeom& G);   // ints of node scratch per frame
 void octree_assign_node_offsets(FrameGeom& G);
