@@ -79,63 +79,64 @@ int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int la
 // Reads the padded pyramid plane (its reflect-101 border IS the blur's BORDER_REFLECT_101), writes the
 // interior of the blur plane.  HBM-bound: algorithmic bytes per frame = read + write sum(L0..L7).
 // ------------------------------------------------------------------------------------------------
-#define BL_TW 128
-#define BL_TH 16
-#define BL_THREADS 256
+// A thread owns one 32-bit word (4 px) of a 32-row strip and slides down it.  Horizontal pass per row:
+// two IDP.4A (u8 x u8 dot products) per pixel on byte-shifted copies of the three words around the
+// pixel; the 7 most recent horizontal rows stay in registers and the vertical pass is 4 IMAD per pixel
+// on the symmetric kernel.  No shared memory, no barriers.
+#define BL_RT 32
+#define BL_BX 64
+#define BL_BY 2
 
-__global__ void __launch_bounds__(BL_THREADS)
+__device__ __forceinline__ void blur_hrow(int (&h)[4], const uint32_t* __restrict__ p)
+{
+    const uint32_t l = __ldg(p - 1), m = __ldg(p), r = __ldg(p + 1);
+    const uint32_t kA = 18u | (34u << 8) | (48u << 16) | (56u << 24);   // taps -3..0
+    const uint32_t kB = 48u | (34u << 8) | (18u << 16);                 // taps +1..+3
+    // word starting at byte x+d: funnel shifts of (l, m) / (m, r)
+    h[0] = __dp4a(__funnelshift_r(l, m, 8), kA, __dp4a(__funnelshift_r(m, r, 8), kB, 0u));    // px x  : x-3..x | x+1..x+4
+    h[1] = __dp4a(__funnelshift_r(l, m, 16), kA, __dp4a(__funnelshift_r(m, r, 16), kB, 0u));  // px x+1
+    h[2] = __dp4a(__funnelshift_r(l, m, 24), kA, __dp4a(__funnelshift_r(m, r, 24), kB, 0u));  // px x+2
+    h[3] = __dp4a(m, kA, __dp4a(r, kB, 0u));                                                   // px x+3
+}
+
+template <int PH>
+__device__ __forceinline__ uint32_t blur_vword(const int (&H)[7][4])
+{
+    uint32_t word = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t acc = 18u * (uint32_t)(H[PH % 7][k] + H[(PH + 6) % 7][k]) + 34u * (uint32_t)(H[(PH + 1) % 7][k] + H[(PH + 5) % 7][k]) +
+                             48u * (uint32_t)(H[(PH + 2) % 7][k] + H[(PH + 4) % 7][k]) + 56u * (uint32_t)H[(PH + 3) % 7][k] + 32768u;
+        word |= ((acc >> 16) & 0xFFu) << (8 * k);
+    }
+    return word;
+}
+
+__global__ void __launch_bounds__(BL_BX * BL_BY)
 blur_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, int pitch, long long plane_bytes, int w, int h)
 {
-    __shared__ uint32_t s_in[(BL_TH + 6)][(BL_TW + 8) / 4];      // bytes x0-4 .. x0+131
-    __shared__ uint16_t s_h[(BL_TH + 6)][BL_TW];
+    const int wi = blockIdx.x * BL_BX + threadIdx.x;
+    const int y0 = (blockIdx.y * BL_BY + threadIdx.y) * BL_RT;
+    if (wi * 4 >= w || y0 >= h) return;
     const int f = blockIdx.z;
-    const int x0 = blockIdx.x * BL_TW, y0 = blockIdx.y * BL_TH;
-    const uint8_t* src = pyr + (long long)f * plane_bytes;
-    const int tid = threadIdx.x;
-    // stage rows y0-3 .. y0+TH+2, byte columns XOFF+x0-4 .. (word aligned)
-    for (int i = tid; i < (BL_TH + 6) * ((BL_TW + 8) / 4); i += BL_THREADS) {
-        const int r = i / ((BL_TW + 8) / 4), c = i - r * ((BL_TW + 8) / 4);
-        const int yy = ORBX_YOFF + y0 - 3 + r;                    // padded row
-        const int bx = ORBX_XOFF + x0 - 4 + 4 * c;                // byte in row
-        uint32_t v = 0;
-        if (yy < h + 2 * ORBX_EDGE && bx + 4 <= pitch)
-            v = __ldg(reinterpret_cast<const uint32_t*>(src + (long long)yy * pitch + bx));
-        s_in[r][c] = v;
+    const int pw = pitch >> 2;
+    // word of pixel (4*wi, y0-3)
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(pyr + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y0 - 3) * pitch + ORBX_XOFF) + wi;
+    uint32_t* q = reinterpret_cast<uint32_t*>(blur + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y0) * pitch + ORBX_XOFF) + wi;
+    int H[7][4];
+#pragma unroll
+    for (int i = 0; i < 6; i++) { blur_hrow(H[i], p); p += pw; }
+    const int nr = min(BL_RT, h - y0);
+#define BLUR_STEP(PH)                                                   \
+    if (rb + PH < nr) {                                                 \
+        blur_hrow(H[(PH + 6) % 7], p); p += pw;                         \
+        *q = blur_vword<PH>(H); q += pw;                                \
     }
-    __syncthreads();
-    // horizontal pass: 4 outputs per work item
-    for (int i = tid; i < (BL_TH + 6) * (BL_TW / 4); i += BL_THREADS) {
-        const int r = i / (BL_TW / 4), c = i - r * (BL_TW / 4);
-        const uint32_t w0 = s_in[r][c], w1 = s_in[r][c + 1], w2 = s_in[r][c + 2];
-        // bytes b[0..11] = columns x-4 .. x+7 for x = x0+4c ; output j uses b[j+1 .. j+7]
-        int b[12];
-#pragma unroll
-        for (int k = 0; k < 4; k++) { b[k] = (w0 >> (8 * k)) & 0xFF; b[4 + k] = (w1 >> (8 * k)) & 0xFF; b[8 + k] = (w2 >> (8 * k)) & 0xFF; }
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int acc = 18 * (b[j + 1] + b[j + 7]) + 34 * (b[j + 2] + b[j + 6]) + 48 * (b[j + 3] + b[j + 5]) + 56 * b[j + 4];
-            s_h[r][4 * c + j] = (uint16_t)acc;
-        }
+#pragma unroll 1
+    for (int rb = 0; rb < nr; rb += 7) {
+        BLUR_STEP(0) BLUR_STEP(1) BLUR_STEP(2) BLUR_STEP(3) BLUR_STEP(4) BLUR_STEP(5) BLUR_STEP(6)
     }
-    __syncthreads();
-    // vertical pass: thread -> 4 columns x 2 rows
-    const int tx = tid & 31, ty = tid >> 5;
-#pragma unroll
-    for (int rr = 0; rr < 2; rr++) {
-        const int r = ty + 8 * rr, y = y0 + r, x = x0 + 4 * tx;
-        if (y < h && x < w) {
-            uint32_t word = 0;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const int cx = 4 * tx + j;
-                const uint32_t acc = 18u * (s_h[r][cx] + s_h[r + 6][cx]) + 34u * (s_h[r + 1][cx] + s_h[r + 5][cx]) +
-                                     48u * (s_h[r + 2][cx] + s_h[r + 4][cx]) + 56u * s_h[r + 3][cx];
-                word |= (((acc + 32768u) >> 16) & 0xFFu) << (8 * j);
-            }
-            // columns beyond w inside the last word land in the (unused) right margin of the blur plane
-            *reinterpret_cast<uint32_t*>(blur + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y) * pitch + ORBX_XOFF + x) = word;
-        }
-    }
+#undef BLUR_STEP
 }
 
 int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
@@ -143,8 +144,9 @@ int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream
     int launches = 0;
     for (int l = 0; l < G.nlevels; l++) {
         const LevelGeom& L = G.L[l];
-        const dim3 grid((L.w + BL_TW - 1) / BL_TW, (L.h + BL_TH - 1) / BL_TH, nframes);
-        blur_kernel<<<grid, BL_THREADS, 0, s>>>(L.pyr, L.blur, L.pitch, L.plane_bytes, L.w, L.h);
+        const int ww = (L.w + 3) / 4;
+        const dim3 grid((ww + BL_BX - 1) / BL_BX, (L.h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT), nframes);
+        blur_kernel<<<grid, dim3(BL_BX, BL_BY), 0, s>>>(L.pyr, L.blur, L.pitch, L.plane_bytes, L.w, L.h);
         launches++;
     }
     return launches;

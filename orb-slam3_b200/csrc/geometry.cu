@@ -81,7 +81,9 @@ int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch
             const LevelGeom& P = G->L[l - 1];
             const double sx = (double)P.w / L.w, sy = (double)P.h / L.h;
             auto& TX = (*tapx)[l]; auto& TY = (*tapy)[l];
-            TX.resize(L.w + 2 * ORBX_EDGE); TY.resize(L.h + 2 * ORBX_EDGE);
+            // TX is indexed by the BYTE of the padded row (padded column X = byte - (XOFF - EDGE)); bytes that
+            // are not image columns get an all-zero tap, which makes the kernel write 0 there.
+            TX.assign(L.pitch, ResizeTapX{0, 0, 0, 0}); TY.resize(L.h + 2 * ORBX_EDGE);
             for (int X = 0; X < L.w + 2 * ORBX_EDGE; X++) {
                 const int dx = reflect101(X - ORBX_EDGE, L.w);
                 float fx = (float)((dx + 0.5) * sx - 0.5);
@@ -92,7 +94,7 @@ int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch
                 ResizeTapX t;
                 t.s0 = (short)s; t.s1 = (short)(s + 1 < P.w ? s + 1 : P.w - 1);
                 t.a0 = (short)cv_round_f((1.f - fx) * 2048.f); t.a1 = (short)cv_round_f(fx * 2048.f);
-                TX[X] = t;
+                TX[X + ORBX_XOFF - ORBX_EDGE] = t;
             }
             for (int Y = 0; Y < L.h + 2 * ORBX_EDGE; Y++) {
                 const int dy = reflect101(Y - ORBX_EDGE, L.h);

@@ -55,7 +55,7 @@ struct LevelGeom {
     float scale;              // mvScaleFactor[level]
     float patch_size;         // (float)(int)(31*scale), :1161
     // resize taps producing THIS level from level-1, indexed by padded coordinate (border folded in)
-    const ResizeTapX* tapx;   // w + 38 entries
+    const ResizeTapX* tapx;   // pitch entries, indexed by byte of the padded row
     const ResizeTapY* tapy;   // h + 38 entries
 };
 

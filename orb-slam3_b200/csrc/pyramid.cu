@@ -37,33 +37,67 @@ pyr_level0_kernel(const uint8_t* __restrict__ in, int in_pitch, long long in_fra
 
 // level l>0 from level l-1.  OpenCV HResizeLinear/VResizeLinear u8 arithmetic (see oracle/orc_prims.c):
 //   H = S[s0]*a0 + S[s1]*a1 ;  dst = (((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2
-__global__ void __launch_bounds__(256)
+// A thread owns one 32-bit word (4 px) of PYR_ROWS consecutive padded rows: the 4 horizontal taps are
+// loaded once, and a horizontal row result is reused when the next output row's upper source row is
+// this row's lower one (scale 1.2: most of the time), i.e. ~1.2 horizontal passes per output row.
+#define PYR_ROWS 8
+#define PYR_BX 64
+#define PYR_BY 4
+
+struct HRow { int h[4]; };     // (S[s0]*a0 + S[s1]*a1) >> 4 of the thread's 4 pixels
+
+__device__ __forceinline__ HRow pyr_hrow(const uint8_t* __restrict__ S, const int (&s0)[4], const int (&s1)[4],
+                                         const int (&a0)[4], const int (&a1)[4])
+{
+    HRow r;
+#pragma unroll
+    for (int k = 0; k < 4; k++) r.h[k] = ((int)__ldg(S + s0[k]) * a0[k] + (int)__ldg(S + s1[k]) * a1[k]) >> 4;
+    return r;
+}
+
+__global__ void __launch_bounds__(PYR_BX * PYR_BY)
 pyr_resize_kernel(const uint8_t* __restrict__ prev, int ppitch, long long pplane_bytes,
-                  uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h,
+                  uint8_t* __restrict__ out, int pitch, long long plane_bytes, int prow,
                   const ResizeTapX* __restrict__ tapx, const ResizeTapY* __restrict__ tapy)
 {
-    const int wi = blockIdx.x * blockDim.x + threadIdx.x;
-    const int Y = blockIdx.y * blockDim.y + threadIdx.y;
-    if (Y >= h + 2 * ORBX_EDGE || wi * 4 >= pitch) return;
+    const int wi = blockIdx.x * PYR_BX + threadIdx.x;
+    if (wi * 4 >= pitch) return;
+    const int Y0 = (blockIdx.y * PYR_BY + threadIdx.y) * PYR_ROWS;
+    if (Y0 >= prow) return;
     const int f = blockIdx.z;
-    const ResizeTapY ty = tapy[Y];
-    const uint8_t* base = prev + (long long)f * pplane_bytes + ORBX_XOFF;
-    const uint8_t* S0 = base + (long long)(ORBX_YOFF + ty.s0) * ppitch;
-    const uint8_t* S1 = base + (long long)(ORBX_YOFF + ty.s1) * ppitch;
-    const int b0 = ty.b0, b1 = ty.b1;
-    uint32_t word = 0;
+    int s0[4], s1[4], a0[4], a1[4];
+    {
+        const uint4 t01 = __ldg(reinterpret_cast<const uint4*>(tapx + wi * 4));
+        const uint4 t23 = __ldg(reinterpret_cast<const uint4*>(tapx + wi * 4) + 1);
+        const uint32_t w[8] = {t01.x, t01.y, t01.z, t01.w, t23.x, t23.y, t23.z, t23.w};
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const int X = wi * 4 + k - (ORBX_XOFF - ORBX_EDGE);
-        if (X >= 0 && X < w + 2 * ORBX_EDGE) {
-            const ResizeTapX tx = tapx[X];
-            const int h0 = (int)__ldg(S0 + tx.s0) * tx.a0 + (int)__ldg(S0 + tx.s1) * tx.a1;
-            const int h1 = (int)__ldg(S1 + tx.s0) * tx.a0 + (int)__ldg(S1 + tx.s1) * tx.a1;
-            const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-            word |= (uint32_t)(v & 0xFF) << (8 * k);
+        for (int k = 0; k < 4; k++) {
+            s0[k] = (int)(w[2 * k] & 0xFFFF); s1[k] = (int)(w[2 * k] >> 16);
+            a0[k] = (int)(w[2 * k + 1] & 0xFFFF); a1[k] = (int)(w[2 * k + 1] >> 16);
         }
     }
-    *reinterpret_cast<uint32_t*>(out + (long long)f * plane_bytes + (long long)Y * pitch + wi * 4) = word;
+    const uint8_t* base = prev + (long long)f * pplane_bytes + (long long)ORBX_YOFF * ppitch + ORBX_XOFF;
+    uint8_t* dst = out + (long long)f * plane_bytes + (long long)Y0 * pitch + wi * 4;
+    int have = -1;              // source row whose horizontal pass is held in hl
+    HRow hl;
+#pragma unroll
+    for (int k = 0; k < 4; k++) hl.h[k] = 0;
+    const int nr = min(PYR_ROWS, prow - Y0);
+#pragma unroll 2
+    for (int rr = 0; rr < nr; rr++) {
+        const ResizeTapY ty = tapy[Y0 + rr];
+        const HRow h0 = (ty.s0 == have) ? hl : pyr_hrow(base + (long long)ty.s0 * ppitch, s0, s1, a0, a1);
+        const HRow h1 = (ty.s1 == ty.s0) ? h0 : pyr_hrow(base + (long long)ty.s1 * ppitch, s0, s1, a0, a1);
+        const int b0 = ty.b0, b1 = ty.b1;
+        uint32_t word = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int v = (((b0 * h0.h[k]) >> 16) + ((b1 * h1.h[k]) >> 16) + 2) >> 2;
+            word |= (uint32_t)v << (8 * k);        // v <= 255 by construction
+        }
+        *reinterpret_cast<uint32_t*>(dst + (long long)rr * pitch) = word;
+        hl = h1; have = ty.s1;
+    }
 }
 
 int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
@@ -78,8 +112,10 @@ int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStr
                                                      L.pyr, L.pitch, L.plane_bytes, L.w, L.h);
         } else {
             const LevelGeom& P = G.L[l - 1];
-            pyr_resize_kernel<<<grid, block, 0, s>>>(P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch, L.plane_bytes,
-                                                     L.w, L.h, L.tapx, L.tapy);
+            const dim3 rblock(PYR_BX, PYR_BY);
+            const dim3 rgrid((L.pitch / 4 + PYR_BX - 1) / PYR_BX, (L.prow + PYR_BY * PYR_ROWS - 1) / (PYR_BY * PYR_ROWS), nframes);
+            pyr_resize_kernel<<<rgrid, rblock, 0, s>>>(P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch, L.plane_bytes,
+                                                       L.prow, L.tapx, L.tapy);
         }
         launches++;
     }
