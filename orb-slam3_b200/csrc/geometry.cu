@@ -73,6 +73,7 @@ int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch
         const int mx = (L.N + 3 > 4 * L.nIni ? L.N + 3 : 4 * L.nIni);
         L.sel_cap = mx;
         L.node_cap = align_up(mx + 1, 4);
+        if (L.node_cap > 4096) return ORBX_ERR_GEOMETRY;              // quadtree sort key holds a 12-bit list position
         L.sel_base = sel;
         sel += L.sel_cap;
         L.scale = e->sf[l];

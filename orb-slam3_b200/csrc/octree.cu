@@ -2,25 +2,24 @@
 // (reference src/ORBextractor.cc:688-1034, ExtractorNode::DivideNode :602-674).
 //
 // The reference walks a std::list of nodes holding std::vector<KeyPoint> copies.  Here one CTA owns
-// one (frame, level): every candidate carries the list POSITION of its node, and a round of the
-// reference's loop becomes  (1) a key pass that histograms candidates into the 4 children of every
-// node about to be split,  (2) scans over the node table that compute where each child / surviving
-// node lands in the new list (children are push_front'ed in the order n1..n4, so the last split node's
-// n4 ends up first),  (3) a key pass that relabels candidates.  The ordered final phase (:909-992:
-// sort by size, split largest first, stop the moment the list reaches N) is a rank-by-counting sort
-// plus a prefix cut.  Tie-break among equal-size nodes is the canonical (size, creation order) rule
-// of the oracle (the reference compares heap pointers, :927): among the just-created nodes, creation
-// order descending == list position ascending.  Winner per node = max response, first in candidate
-// order (:1005-1030), via a packed atomicMax.
+// one (frame, level): node = list POSITION, every candidate carries `4*node + child` (the child of
+// its node it would fall into).  One round of the reference's loop =
+//   node step   : from the per-child counts decide which nodes split (all expandable ones, or — in
+//                 the ordered final phase :909-992 — the largest first until the list reaches N),
+//                 compute by scans where children / surviving nodes land in the new list (children
+//                 are push_front'ed n1..n4, so the last split node's n4 ends up first), build the new
+//                 node table and a (node, child) -> new position map;
+//   candidate step (ONE pass per round): relabel through that map, find the child inside the new
+//                 node and add it to the next round's per-child counts.
+// The ordered phase sorts (count desc, creation desc == position asc): the canonical tie-break of
+// the oracle (the reference compares heap pointers, :927).  Winner per node = max response, ties to
+// the first keypoint in the reference's vector order = smallest canonical rank (cell row, cell col,
+// y, x) since the FAST kernel emits candidates unordered.
 // Latency-bound integer work (no roofline); reported as a share of the step.
 #include "orbx_internal.h"
 
-#define OCT_THREADS 512
-#define OCT_TABLES 19     // int arrays of node_cap entries in the per-CTA node scratch
-
-struct Scan {
-    int* warp;            // shared: OCT_THREADS/32 + 1 ints
-};
+#define OCT_THREADS 256
+#define OCT_TABLES 23     // int arrays of node_cap entries in the per-CTA node scratch
 
 // exclusive scan of in[0..m) into out[0..m) (out may alias in); returns the total to all threads.
 __device__ int block_scan_excl(const int* in, int* out, int m, int* s_warp)
@@ -52,8 +51,10 @@ __device__ int block_scan_excl(const int* in, int* out, int m, int* s_warp)
     return total;
 }
 
-__device__ __forceinline__ int child_of(int x, int y, int x0, int y0, int x1, int y1)
+// node bounds are packed lo | hi << 16 (coordinates relative to minBorder, < 4096)
+__device__ __forceinline__ int child_of(int x, int y, int bx, int by)
 {
+    const int x0 = bx & 0xFFFF, x1 = bx >> 16, y0 = by & 0xFFFF, y1 = by >> 16;
     const int mx = x0 + ((x1 - x0 + 1) >> 1);     // ceil(float(w)/2), :608
     const int my = y0 + ((y1 - y0 + 1) >> 1);     // :609
     return (x < mx) ? ((y < my) ? 0 : 2) : ((y < my) ? 1 : 3);   // :651-661
@@ -67,8 +68,9 @@ __device__ __forceinline__ int cand_rank(uint32_t key, const LevelGeom& L)
     return ((ci * L.nCols + cj) << 14) | ((Y3 - ci * L.hCell) << 7) | (X3 - cj * L.wCell);
 }
 
+template <bool SMEM>
 __global__ void __launch_bounds__(OCT_THREADS)
-octree_kernel(FrameGeom G, DevBuffers D, int use_smem)
+octree_kernel(FrameGeom G, DevBuffers D)
 {
     extern __shared__ int dyn_smem[];
     __shared__ int s_warp[OCT_THREADS / 32 + 1];
@@ -79,189 +81,172 @@ octree_kernel(FrameGeom G, DevBuffers D, int use_smem)
     const int tid = threadIdx.x;
     const int cap = L.node_cap;
 
-    uint32_t* cand = D.cand + (long long)f * G.cand_per_frame + L.cand_base;
-    uint32_t* knode = D.candnode + (long long)f * G.cand_per_frame + L.cand_base;
-    int* T = use_smem ? dyn_smem : (D.nodetab + ((long long)f * G.nlevels + lvl) * D.nodetab_per_frame);
-    // node tables (double-buffered bounds+count), per-round temporaries
-    int* bx0[2] = {T + 0 * cap, T + 5 * cap};
-    int* by0[2] = {T + 1 * cap, T + 6 * cap};
-    int* bx1[2] = {T + 2 * cap, T + 7 * cap};
-    int* by1[2] = {T + 3 * cap, T + 8 * cap};
-    int* ncnt[2] = {T + 4 * cap, T + 9 * cap};
-    int* childcnt = T + 10 * cap;     // 4*cap
-    int* tmpA = T + 14 * cap;         // flags / ne / gains
-    int* tmpB = T + 15 * cap;         // scan results
-    int* rnk = T + 16 * cap;          // processing rank of a node (or -1)
-    int* headoff = T + 17 * cap;      // new list position of a split node's first child slot
-    int* tailpos = T + 18 * cap;      // new list position of an unsplit node
+    const uint32_t* __restrict__ cand = D.cand + (long long)f * G.cand_per_frame + L.cand_base;
+    uint32_t* kcode = D.candnode + (long long)f * G.cand_per_frame + L.cand_base;     // 4*node + child
+    int* T = SMEM ? dyn_smem : (D.nodetab + ((long long)f * G.nlevels + lvl) * D.nodetab_per_frame);
+    int* BX[2] = {T, T + 3 * cap};               // x0 | x1 << 16
+    int* BY[2] = {T + cap, T + 4 * cap};         // y0 | y1 << 16
+    int* CN[2] = {T + 2 * cap, T + 5 * cap};     // keypoints in the node
+    int* CC[2] = {T + 6 * cap, T + 10 * cap};    // keypoints per child (4 per node)
+    int* NP4 = T + 14 * cap;                     // (old node, child) -> new list position
+    int* aA = T + 18 * cap; int* aB = T + 19 * cap; int* aC = T + 20 * cap; int* aD = T + 21 * cap; int* aE = T + 22 * cap;
 
-    // candidates were compacted (in arbitrary order) by fast_band_kernel
-    const int n = min(D.candcnt[f * G.nlevels + lvl], L.cand_cap);
+    const int n = min(D.candcnt[f * G.nlevels + lvl], L.cand_cap);   // compacted (unordered) by fast_band_kernel
     const int N = L.N;
     const int H = L.maxBY - ORBX_MINB;
 
     // ---- roots, :695-763 ----
-    int cur = 0;
     for (int i = tid; i < L.nIni; i += OCT_THREADS) {
-        bx0[0][i] = (int)__fmul_rn(L.hX, (float)i);
-        bx1[0][i] = (int)__fmul_rn(L.hX, (float)(i + 1));
-        by0[0][i] = 0; by1[0][i] = H;
-        ncnt[0][i] = 0;
+        const int x0 = (int)__fmul_rn(L.hX, (float)i), x1 = (int)__fmul_rn(L.hX, (float)(i + 1));
+        BX[0][i] = x0 | (x1 << 16); BY[0][i] = H << 16; CN[0][i] = 0;
     }
     __syncthreads();
     for (int i = tid; i < n; i += OCT_THREADS) {
-        int r = (int)__fdiv_rn((float)KEY_X(cand[i]), L.hX);     // vpIniNodes[kp.pt.x/hX], :740
+        int r = (int)__fdiv_rn((float)KEY_X(cand[i]), L.hX);         // vpIniNodes[kp.pt.x/hX], :740
         r = min(r, L.nIni - 1);
-        knode[i] = r;
-        atomicAdd(&ncnt[0][r], 1);
+        kcode[i] = 4 * r;
+        atomicAdd(&CN[0][r], 1);
     }
     __syncthreads();
-    for (int i = tid; i < L.nIni; i += OCT_THREADS) tmpA[i] = ncnt[0][i] > 0;
+    for (int i = tid; i < L.nIni; i += OCT_THREADS) aA[i] = CN[0][i] > 0;
     __syncthreads();
-    int size = block_scan_excl(tmpA, tmpB, L.nIni, s_warp);
+    int size = block_scan_excl(aA, aB, L.nIni, s_warp);              // empty roots are erased, :746-763
     for (int i = tid; i < L.nIni; i += OCT_THREADS) {
-        if (ncnt[0][i] > 0) {
-            const int p = tmpB[i];
-            bx0[1][p] = bx0[0][i]; by0[1][p] = by0[0][i]; bx1[1][p] = bx1[0][i]; by1[1][p] = by1[0][i];
-            ncnt[1][p] = ncnt[0][i];
+        const int p = aB[i];
+        if (CN[0][i] > 0) {
+            BX[1][p] = BX[0][i]; BY[1][p] = BY[0][i]; CN[1][p] = CN[0][i];
+            *reinterpret_cast<int4*>(CC[1] + 4 * p) = make_int4(0, 0, 0, 0);
         }
+        *reinterpret_cast<int4*>(NP4 + 4 * i) = make_int4(p, p, p, p);
     }
-    for (int i = tid; i < n; i += OCT_THREADS) knode[i] = tmpB[knode[i]];
-    cur = 1;
-    __syncthreads();
-
+    int cur = 1;
     bool final_phase = false;
     bool finish = (n == 0);        // empty list: first iteration leaves size == prevSize, :889
+    bool more = !finish;
+    __syncthreads();
+
 #pragma unroll 1
-    while (!finish) {
-        const int prevSize = size;
-        int *X0 = bx0[cur], *Y0 = by0[cur], *X1 = bx1[cur], *Y1 = by1[cur], *CN = ncnt[cur];
-        int *NX0 = bx0[cur ^ 1], *NY0 = by0[cur ^ 1], *NX1 = bx1[cur ^ 1], *NY1 = by1[cur ^ 1], *NCN = ncnt[cur ^ 1];
-        // (1) histogram candidates of expandable nodes into their four children
-        for (int i = tid; i < 4 * size; i += OCT_THREADS) childcnt[i] = 0;
-        __syncthreads();
-        for (int i = tid; i < n; i += OCT_THREADS) {
-            const int nd = knode[i];
-            if (CN[nd] > 1) {
-                const uint32_t k = cand[i];
-                const int c = child_of(KEY_X(k), KEY_Y(k), X0[nd], Y0[nd], X1[nd], Y1[nd]);
-                atomicAdd(&childcnt[4 * nd + c], 1);
+    while (more) {
+        // ---- candidate step: relabel, child inside the new node, next round's per-child counts ----
+        {
+            const int* bx = BX[cur]; const int* by = BY[cur]; const int* cn = CN[cur]; int* cc = CC[cur];
+            for (int i = tid; i < n; i += OCT_THREADS) {
+                const int p = NP4[kcode[i]];
+                int c = 0;
+                if (!finish && cn[p] > 1) {
+                    const uint32_t k = cand[i];
+                    c = child_of(KEY_X(k), KEY_Y(k), bx[p], by[p]);
+                    atomicAdd(&cc[4 * p + c], 1);
+                }
+                kcode[i] = 4 * p + c;
             }
         }
         __syncthreads();
-        // (2) processing order of the nodes to split
+        if (finish) break;
+        // ---- node step ----
+        const int prevSize = size;
+        const int nxt = cur ^ 1;
+        const int* cn = CN[cur]; const int* cc = CC[cur];
         int nsplit, totalNe;
+        // on exit of either branch: aB[i] = first child slot of a node that splits (else -1),
+        //                           aC[i] = number of non-splitting nodes before i
         if (!final_phase) {
-            // all expandable nodes, in list order (:800-886)
-            for (int i = tid; i < size; i += OCT_THREADS) tmpA[i] = CN[i] > 1;
-            __syncthreads();
-            nsplit = block_scan_excl(tmpA, rnk, size, s_warp);       // rnk = #expandable nodes before i
+            // every expandable node splits, in list order (:800-886); e << 16 | ne scanned in one go
             for (int i = tid; i < size; i += OCT_THREADS) {
-                int ne = 0;
-                tailpos[i] = i - rnk[i];                                // #unsplit nodes before i
-                if (CN[i] > 1) {
-                    ne = (childcnt[4 * i] > 0) + (childcnt[4 * i + 1] > 0) + (childcnt[4 * i + 2] > 0) + (childcnt[4 * i + 3] > 0);
-                } else rnk[i] = -1;
-                tmpA[i] = ne;
+                int v = 0;
+                if (cn[i] > 1) {
+                    const int4 c4 = *reinterpret_cast<const int4*>(cc + 4 * i);
+                    v = 0x10000 | ((c4.x > 0) + (c4.y > 0) + (c4.z > 0) + (c4.w > 0));
+                }
+                aA[i] = v;
             }
             __syncthreads();
-            totalNe = block_scan_excl(tmpA, tmpB, size, s_warp);       // tmpB = exclusive prefix of ne in list order
+            const int tot = block_scan_excl(aA, aD, size, s_warp);
+            nsplit = tot >> 16; totalNe = tot & 0xFFFF;
             for (int i = tid; i < size; i += OCT_THREADS) {
-                // later-processed nodes sit in front: offset = sum of ne over the nodes after i
-                headoff[i] = totalNe - tmpB[i] - tmpA[i];
-                tailpos[i] += totalNe;
+                const int v = aA[i], pre = aD[i];
+                // later-processed nodes sit in front: slot = sum of ne over the nodes after i
+                aB[i] = (v >> 16) ? totalNe - (pre & 0xFFFF) - (v & 0xFFFF) : -1;
+                aC[i] = i - (pre >> 16);
             }
             __syncthreads();
         } else {
-            // ordered phase (:909-992): sort expandable nodes by (size desc, creation desc == position asc)
-            for (int i = tid; i < size; i += OCT_THREADS) {
-                int r = -1;
-                const int ci = CN[i];
-                if (ci > 1) {
-                    r = 0;
-                    for (int j = 0; j < size; j++) {
-                        const int cj = CN[j];
-                        r += (cj > 1) && (cj > ci || (cj == ci && j < i));
-                    }
+            // ordered phase (:909-992): expandable nodes by (size desc, creation desc == position asc)
+            for (int i = tid; i < size; i += OCT_THREADS) { aA[i] = cn[i] > 1; aB[i] = -1; }
+            __syncthreads();
+            const int E = block_scan_excl(aA, aD, size, s_warp);
+            for (int i = tid; i < size; i += OCT_THREADS)
+                if (cn[i] > 1) aC[aD[i]] = (min(cn[i], 0x7FFFF) << 12) | (4095 - i);      // sort key
+            __syncthreads();
+            for (int e = tid; e < E; e += OCT_THREADS) {
+                const int my = aC[e];
+                int r = 0, j = 0;
+                for (; j + 4 <= E; j += 4) {
+                    const int4 k4 = *reinterpret_cast<const int4*>(aC + j);
+                    r += (k4.x > my) + (k4.y > my) + (k4.z > my) + (k4.w > my);
                 }
-                rnk[i] = r;
+                for (; j < E; j++) r += aC[j] > my;
+                const int i = 4095 - (my & 4095);
+                const int4 c4 = *reinterpret_cast<const int4*>(cc + 4 * i);
+                aD[r] = i;                                                   // node processed r-th
+                aE[r] = (c4.x > 0) + (c4.y > 0) + (c4.z > 0) + (c4.w > 0);  // its non-empty children
             }
+            if (tid == 0) s_val[0] = E;                                      // default: split everything
             __syncthreads();
-            int* order = tmpB;     // order[r] = node
-            int E;
-            for (int i = tid; i < size; i += OCT_THREADS) tmpA[i] = CN[i] > 1;
-            __syncthreads();
-            E = block_scan_excl(tmpA, headoff, size, s_warp);   // headoff used as throwaway here
-            for (int i = tid; i < size; i += OCT_THREADS) if (rnk[i] >= 0) order[rnk[i]] = i;
-            __syncthreads();
-            // ne in rank order -> tmpA ; inclusive prefix -> tailpos (temporary)
-            for (int r = tid; r < E; r += OCT_THREADS) {
-                const int i = order[r];
-                tmpA[r] = (childcnt[4 * i] > 0) + (childcnt[4 * i + 1] > 0) + (childcnt[4 * i + 2] > 0) + (childcnt[4 * i + 3] > 0);
-            }
-            __syncthreads();
-            block_scan_excl(tmpA, tailpos, E, s_warp);          // tailpos[r] = exclusive prefix of ne (rank order)
-            if (tid == 0) s_val[0] = E;                          // default: split everything
-            __syncthreads();
+            block_scan_excl(aE, aA, E, s_warp);                              // aA[r] = sum of ne before rank r
             for (int r = tid; r < E; r += OCT_THREADS) {
                 // list size after splitting ranks 0..r : prevSize + sum(ne) - (r+1)
-                const int after = prevSize + tailpos[r] + tmpA[r] - (r + 1);
-                const int before = prevSize + tailpos[r] - r;
-                if (after >= N && before < N) s_val[0] = r + 1;  // break right after this split, :983
+                const int after = prevSize + aA[r] + aE[r] - (r + 1);
+                const int before = prevSize + aA[r] - r;
+                if (after >= N && before < N) s_val[0] = r + 1;              // break right after this split, :983
             }
             __syncthreads();
             nsplit = s_val[0];
-            totalNe = (nsplit > 0) ? tailpos[nsplit - 1] + tmpA[nsplit - 1] : 0;
+            totalNe = (nsplit > 0) ? aA[nsplit - 1] + aE[nsplit - 1] : 0;
             __syncthreads();
-            for (int r = tid; r < E; r += OCT_THREADS) {
-                const int i = order[r];
-                if (r < nsplit) headoff[i] = totalNe - tailpos[r] - tmpA[r];
-                else rnk[i] = -1;                                // not split in this round
-            }
+            for (int r = tid; r < nsplit; r += OCT_THREADS) aB[aD[r]] = totalNe - aA[r] - aE[r];
             __syncthreads();
-            for (int i = tid; i < size; i += OCT_THREADS) tmpA[i] = rnk[i] >= 0;
+            for (int i = tid; i < size; i += OCT_THREADS) aC[i] = aB[i] < 0;
             __syncthreads();
-            block_scan_excl(tmpA, tmpB, size, s_warp);
-            for (int i = tid; i < size; i += OCT_THREADS) tailpos[i] = totalNe + i - tmpB[i];
-            __syncthreads();
+            block_scan_excl(aC, aC, size, s_warp);
         }
         const int newSize = totalNe + size - nsplit;
-        // (3) build the next node table
+        // ---- build the next node table and the relabel map ----
         if (tid == 0) s_val[1] = 0;
         __syncthreads();
-        int myexp = 0;
-        for (int i = tid; i < size; i += OCT_THREADS) {
-            if (rnk[i] >= 0) {
-                const int x0 = X0[i], y0 = Y0[i], x1 = X1[i], y1 = Y1[i];
-                const int mx = x0 + ((x1 - x0 + 1) >> 1), my = y0 + ((y1 - y0 + 1) >> 1);
-                const int c0 = childcnt[4 * i], c1 = childcnt[4 * i + 1], c2 = childcnt[4 * i + 2], c3 = childcnt[4 * i + 3];
-                int p = headoff[i];
-                if (c3 > 0) { NX0[p] = mx; NY0[p] = my; NX1[p] = x1; NY1[p] = y1; NCN[p] = c3; p++; myexp += c3 > 1; }
-                if (c2 > 0) { NX0[p] = x0; NY0[p] = my; NX1[p] = mx; NY1[p] = y1; NCN[p] = c2; p++; myexp += c2 > 1; }
-                if (c1 > 0) { NX0[p] = mx; NY0[p] = y0; NX1[p] = x1; NY1[p] = my; NCN[p] = c1; p++; myexp += c1 > 1; }
-                if (c0 > 0) { NX0[p] = x0; NY0[p] = y0; NX1[p] = mx; NY1[p] = my; NCN[p] = c0; p++; myexp += c0 > 1; }
-            } else {
-                const int p = tailpos[i];
-                NX0[p] = X0[i]; NY0[p] = Y0[i]; NX1[p] = X1[i]; NY1[p] = Y1[i]; NCN[p] = CN[i];
+        {
+            const int* bxo = BX[cur]; const int* byo = BY[cur];
+            int* bxn = BX[nxt]; int* byn = BY[nxt]; int* cnn = CN[nxt]; int* ccn = CC[nxt];
+            int myexp = 0;
+            for (int i = tid; i < size; i += OCT_THREADS) {
+                const int bx = bxo[i], by = byo[i];
+                int p = aB[i];
+                if (p >= 0) {
+                    const int x0 = bx & 0xFFFF, x1 = bx >> 16, y0 = by & 0xFFFF, y1 = by >> 16;
+                    const int mx = x0 + ((x1 - x0 + 1) >> 1), my = y0 + ((y1 - y0 + 1) >> 1);
+                    const int4 c4 = *reinterpret_cast<const int4*>(cc + 4 * i);
+                    int4 np = make_int4(0, 0, 0, 0);
+                    if (c4.w > 0) { bxn[p] = mx | (x1 << 16); byn[p] = my | (y1 << 16); cnn[p] = c4.w; np.w = p;
+                                    *reinterpret_cast<int4*>(ccn + 4 * p) = make_int4(0, 0, 0, 0); p++; myexp += c4.w > 1; }
+                    if (c4.z > 0) { bxn[p] = x0 | (mx << 16); byn[p] = my | (y1 << 16); cnn[p] = c4.z; np.z = p;
+                                    *reinterpret_cast<int4*>(ccn + 4 * p) = make_int4(0, 0, 0, 0); p++; myexp += c4.z > 1; }
+                    if (c4.y > 0) { bxn[p] = mx | (x1 << 16); byn[p] = y0 | (my << 16); cnn[p] = c4.y; np.y = p;
+                                    *reinterpret_cast<int4*>(ccn + 4 * p) = make_int4(0, 0, 0, 0); p++; myexp += c4.y > 1; }
+                    if (c4.x > 0) { bxn[p] = x0 | (mx << 16); byn[p] = y0 | (my << 16); cnn[p] = c4.x; np.x = p;
+                                    *reinterpret_cast<int4*>(ccn + 4 * p) = make_int4(0, 0, 0, 0); p++; myexp += c4.x > 1; }
+                    *reinterpret_cast<int4*>(NP4 + 4 * i) = np;
+                } else {
+                    p = totalNe + aC[i];
+                    bxn[p] = bx; byn[p] = by; cnn[p] = cn[i];
+                    *reinterpret_cast<int4*>(ccn + 4 * p) = make_int4(0, 0, 0, 0);
+                    *reinterpret_cast<int4*>(NP4 + 4 * i) = make_int4(p, p, p, p);
+                }
             }
-        }
-        if (myexp) atomicAdd(&s_val[1], myexp);
-        // (4) relabel candidates
-        for (int i = tid; i < n; i += OCT_THREADS) {
-            const int nd = knode[i];
-            if (rnk[nd] >= 0) {
-                const uint32_t k = cand[i];
-                const int c = child_of(KEY_X(k), KEY_Y(k), X0[nd], Y0[nd], X1[nd], Y1[nd]);
-                int p = headoff[nd];
-                for (int cc = 3; cc > c; cc--) p += childcnt[4 * nd + cc] > 0;
-                knode[i] = p;
-            } else {
-                knode[i] = tailpos[nd];
-            }
+            if (myexp) atomicAdd(&s_val[1], myexp);
         }
         __syncthreads();
         const int nToExpand = s_val[1];
-        cur ^= 1;
+        cur = nxt;
         size = newSize;
         if (size >= N || size == prevSize) finish = true;                  // :889 / :990
         else if (!final_phase && size + nToExpand * 3 > N) final_phase = true;   // :909
@@ -270,15 +255,15 @@ octree_kernel(FrameGeom G, DevBuffers D, int use_smem)
 
     // ---- best response per node; ties go to the first keypoint in the reference's vector order
     // (:1005-1030), i.e. the smallest canonical rank (cell row, cell col, y, x) ----
-    int* best = tmpA;
-    int* bestrank = tmpB;
+    int* best = aA;
+    int* bestrank = aB;
     for (int i = tid; i < size; i += OCT_THREADS) { best[i] = 0; bestrank[i] = 0x7FFFFFFF; }
     __syncthreads();
-    for (int i = tid; i < n; i += OCT_THREADS) atomicMax(&best[knode[i]], (int)KEY_S(cand[i]));
+    for (int i = tid; i < n; i += OCT_THREADS) atomicMax(&best[kcode[i] >> 2], (int)KEY_S(cand[i]));
     __syncthreads();
     for (int i = tid; i < n; i += OCT_THREADS) {
         const uint32_t k = cand[i];
-        const int nd = knode[i];
+        const int nd = kcode[i] >> 2;
         if ((int)KEY_S(k) == best[nd]) atomicMin(&bestrank[nd], cand_rank(k, L));
     }
     __syncthreads();
@@ -286,7 +271,7 @@ octree_kernel(FrameGeom G, DevBuffers D, int use_smem)
     const int nout = min(size, L.sel_cap);
     for (int i = tid; i < n; i += OCT_THREADS) {
         const uint32_t k = cand[i];
-        const int nd = knode[i];
+        const int nd = kcode[i] >> 2;
         if (nd < nout && (int)KEY_S(k) == best[nd] && cand_rank(k, L) == bestrank[nd]) sel[nd] = k;
     }
     if (tid == 0) D.selcnt[f * G.nlevels + lvl] = nout;
@@ -302,10 +287,13 @@ size_t octree_nodetab_ints(const FrameGeom& G)
 int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
     const size_t need = octree_nodetab_ints(G) * sizeof(int);
-    const int use_smem = need <= 96 * 1024;
-    if (use_smem && need > 48 * 1024)
-        cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     const dim3 grid(G.nlevels, nframes);
-    octree_kernel<<<grid, OCT_THREADS, use_smem ? need : 0, s>>>(G, D, use_smem);
+    if (need <= 64 * 1024) {
+        if (need > 48 * 1024)
+            cudaFuncSetAttribute(octree_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+        octree_kernel<true><<<grid, OCT_THREADS, need, s>>>(G, D);
+    } else {
+        octree_kernel<false><<<grid, OCT_THREADS, 0, s>>>(G, D);
+    }
     return 1;
 }
