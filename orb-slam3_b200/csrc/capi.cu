@@ -154,6 +154,13 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
                 CUDA_TRY(cudaMemcpy(dx, tx[l].data(), tx[l].size() * sizeof(ResizeTapX), cudaMemcpyHostToDevice));
                 CUDA_TRY(cudaMemcpy(dy, ty[l].data(), ty[l].size() * sizeof(ResizeTapY), cudaMemcpyHostToDevice));
                 G.L[l].tapx = dx; G.L[l].tapy = dy;
+                std::vector<ResizeWord> tw;
+                if (orbx_build_word_taps(tx[l], G.L[l].w, G.L[l].pitch, &tw)) {
+                    ResizeWord* dw;
+                    rc |= dev_alloc(e, &dw, tw.size());
+                    if (!rc) CUDA_TRY(cudaMemcpy(dw, tw.data(), tw.size() * sizeof(ResizeWord), cudaMemcpyHostToDevice));
+                    G.L[l].tapw = dw;
+                }
             }
         }
     }

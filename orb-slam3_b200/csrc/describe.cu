@@ -224,11 +224,15 @@ __device__ __forceinline__ void sincosf_glibc(float y, float* sn, float* cs)
 }
 
 #define DESC_WARPS 8
+#define DESC_R 18                  // max |rotated tap| : the pattern lies inside radius 18.4
+#define DESC_ROWS (2 * DESC_R + 1)
+#define DESC_PW 11                 // words per patch row: 37 bytes at any alignment
 
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 describe_kernel(FrameGeom G, DevBuffers D)
 {
     __shared__ signed char s_pat[1024];
+    __shared__ uint32_t s_patch[DESC_WARPS][DESC_ROWS * DESC_PW];
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_pat[i] = c_pattern[i];
     __syncthreads();
     const int f = blockIdx.y;
@@ -264,12 +268,27 @@ describe_kernel(FrameGeom G, DevBuffers D)
     m01 = __reduce_add_sync(0xffffffffu, m01);
     const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-    // computeOrbDescriptor (:150-203)
+    // computeOrbDescriptor (:150-203).  The 37x37 neighbourhood of the blurred level that the rotated
+    // taps can reach (|tap| <= 18) is staged in shared memory with coalesced word loads; the 16 taps of
+    // each lane are then byte gathers from shared memory instead of 512 scattered sectors per keypoint.
     float a = 0.f, b = 0.f;
     if (lane == 0) sincosf_glibc(__fmul_rn(angle, 0.017453292519943295f), &b, &a);   // factorPI = (float)(CV_PI/180.f)
     a = __shfl_sync(0xffffffffu, a, 0);
     b = __shfl_sync(0xffffffffu, b, 0);
-    const uint8_t* bc = L.blur + off;
+    uint32_t* patch = s_patch[threadIdx.x >> 5];
+    const int xoff = (ORBX_XOFF + x - DESC_R) & 3;                 // byte of the first patch column inside its word
+    {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(
+            L.blur + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + y - DESC_R) * L.pitch + ((ORBX_XOFF + x - DESC_R) & ~3));
+        const int pw = L.pitch >> 2;
+#pragma unroll 4
+        for (int i = lane; i < DESC_ROWS * DESC_PW; i += 32) {
+            const int r = i / DESC_PW, c = i - r * DESC_PW;
+            patch[i] = __ldg(src + r * pw + c);
+        }
+    }
+    __syncwarp();
+    const uint8_t* bc = reinterpret_cast<const uint8_t*>(patch) + DESC_R * (DESC_PW * 4) + DESC_R + xoff;
     const signed char* pat = s_pat + 32 * lane;
     int val = 0;
 #pragma unroll
@@ -280,7 +299,7 @@ describe_kernel(FrameGeom G, DevBuffers D)
             const float px = (float)pat[4 * k + 2 * e], py = (float)pat[4 * k + 2 * e + 1];
             const int ry = __float2int_rn(__fadd_rn(__fmul_rn(px, b), __fmul_rn(py, a)));
             const int rx = __float2int_rn(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, b)));
-            t[e] = bc[ry * L.pitch + rx];
+            t[e] = bc[ry * (DESC_PW * 4) + rx];
         }
         val |= (t[0] < t[1]) << k;
     }

@@ -34,6 +34,28 @@ void orbx_init_tables(orbx_extractor* e)
 }
 
 // Fills G (without device pointers) for an image of rows x cols.  Returns 0 or ORBX_ERR_GEOMETRY.
+// Fast-path word taps of a level from its byte-indexed tap table; false if some word's taps do not fit
+// the 8-byte window (scale factors > ~2) -> the level uses the generic kernel.
+bool orbx_build_word_taps(const std::vector<ResizeTapX>& TX, int w, int pitch, std::vector<ResizeWord>* out)
+{
+    out->assign(pitch / 4, ResizeWord{0, 0, 0, {0, 0, 0, 0}, 0});
+    for (int wi = ORBX_XOFF / 4; wi * 4 < ORBX_XOFF + w; wi++) {
+        ResizeWord rw{};
+        const ResizeTapX& t0 = TX[wi * 4];
+        rw.wb = t0.s0 & ~3; rw.shift = (uint32_t)(t0.s0 & 3) * 8;
+        for (int k = 0; k < 4; k++) {
+            const int x = wi * 4 - ORBX_XOFF + k;
+            const ResizeTapX& t = TX[ORBX_XOFF + (x < w ? x : w - 1)];
+            const int n0 = t.s0 - t0.s0, n1 = t.s1 - t0.s0;
+            if (n0 < 0 || n0 > 7 || n1 < 0 || n1 > 7) return false;
+            rw.sels |= (uint32_t)(n0 | (n1 << 4)) << (8 * k);
+            rw.a01[k] = (uint32_t)(uint16_t)t.a0 | ((uint32_t)(uint16_t)t.a1 << 16);
+        }
+        (*out)[wi] = rw;
+    }
+    return true;
+}
+
 int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch, FrameGeom* G,
                           std::vector<std::vector<ResizeTapX>>* tapx, std::vector<std::vector<ResizeTapY>>* tapy)
 {

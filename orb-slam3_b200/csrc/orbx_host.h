@@ -33,4 +33,5 @@ struct orbx_extractor {
 void orbx_init_tables(orbx_extractor* e);
 int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch, FrameGeom* G,
                           std::vector<std::vector<ResizeTapX>>* tapx, std::vector<std::vector<ResizeTapY>>* tapy);
+bool orbx_build_word_taps(const std::vector<ResizeTapX>& TX, int w, int pitch, std::vector<ResizeWord>* out);
 void orbx_set_error(const char* fmt, ...);

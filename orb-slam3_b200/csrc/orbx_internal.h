@@ -30,6 +30,16 @@
 struct ResizeTapX { short s0, s1, a0, a1; };   // source cols (clipped) and 11-bit coefficients
 struct ResizeTapY { short s0, s1, b0, b1; };
 
+// horizontal taps of one output word (4 px) of the fast resize path: the 8 source bytes starting at
+// the first pixel's left tap hold every tap of the 4 pixels
+struct ResizeWord {
+    int wb;                   // byte offset (multiple of 4) of the aligned source word holding the first tap
+    uint32_t shift;           // bit shift that brings the first tap to byte 0 of the 8-byte window
+    uint32_t sels;            // per pixel one byte: PRMT selector (left tap | right tap << 4) into the window
+    uint32_t a01[4];          // per pixel the 11-bit coefficients a0 | a1 << 16
+    uint32_t pad;
+};
+
 struct LevelGeom {
     int w, h;                 // level image size (cols, rows)
     int pitch, prow;          // plane row pitch (bytes) and padded row count (h + 38)
@@ -57,6 +67,7 @@ struct LevelGeom {
     // resize taps producing THIS level from level-1, indexed by padded coordinate (border folded in)
     const ResizeTapX* tapx;   // pitch entries, indexed by byte of the padded row
     const ResizeTapY* tapy;   // h + 38 entries
+    const ResizeWord* tapw;   // pitch/4 entries (interior words only are meaningful); NULL: generic path
 };
 
 // one FAST work item (one warp): the interiors of cells [cj0, cj1) of cell row ci of level lvl (<= 128 px wide)
