@@ -15,24 +15,89 @@ __device__ __forceinline__ int reflect101(int i, int n)
     return i;
 }
 
-// level 0: input frame -> padded plane
+// level 0: input frame -> interior words of every padded row (rows reflect about the image edges;
+// the 19 columns left and right of the image are filled by pyr_border_kernel for all levels at once)
 __global__ void __launch_bounds__(256)
 pyr_level0_kernel(const uint8_t* __restrict__ in, int in_pitch, long long in_frame_bytes,
                   uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h)
 {
-    const int wi = blockIdx.x * blockDim.x + threadIdx.x;     // 32-bit word of the row
+    const int wi = blockIdx.x * blockDim.x + threadIdx.x;     // 32-bit word of the image row
     const int Y = blockIdx.y * blockDim.y + threadIdx.y;      // padded row
-    if (Y >= h + 2 * ORBX_EDGE || wi * 4 >= pitch) return;
+    if (Y >= h + 2 * ORBX_EDGE || wi * 4 >= w) return;
     const int f = blockIdx.z;
-    const uint8_t* src = in + (long long)f * in_frame_bytes + (long long)reflect101(Y - ORBX_EDGE, h) * in_pitch;
-    uint32_t word = 0;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(in + (long long)f * in_frame_bytes + (long long)reflect101(Y - ORBX_EDGE, h) * in_pitch);
+    reinterpret_cast<uint32_t*>(out + (long long)f * plane_bytes + (long long)Y * pitch + ORBX_XOFF)[wi] = __ldg(src + wi);
+}
+
+// reflect-101 columns of every level: out[-k] = out[k], out[w-1+k] = out[w-1-k], k = 1..19
+// (copyMakeBorder BORDER_REFLECT_101 of the level image, :1689-1693,1711-1713)
+__global__ void __launch_bounds__(256)
+pyr_border_kernel(FrameGeom G)
+{
+    const int lvl = blockIdx.y, f = blockIdx.z;
+    const LevelGeom& L = G.L[lvl];
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int Y = idx / (2 * ORBX_EDGE), j = idx - Y * (2 * ORBX_EDGE);
+    if (Y >= L.prow) return;
+    uint8_t* row = L.pyr + (long long)f * L.plane_bytes + (long long)Y * L.pitch + ORBX_XOFF;
+    if (j < ORBX_EDGE) row[-(j + 1)] = row[j + 1];
+    else { const int k = j - ORBX_EDGE + 1; row[L.w - 1 + k] = row[L.w - 1 - k]; }
+}
+
+// fast path of the resize: interior words only, taps from the 8 source bytes starting at the first
+// pixel's left tap (3 aligned word loads + 2 funnel shifts per source row, PRMT + IDP.2A per pixel)
+struct HRow4 { int h[4]; };
+__device__ __forceinline__ HRow4 pyr_hrow_fast(const uint8_t* __restrict__ S, const ResizeWord& t)
+{
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(S + t.wb);
+    const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+    const uint32_t lo = __funnelshift_r(w0, w1, t.shift), hi = __funnelshift_r(w1, w2, t.shift);
+    HRow4 r;
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const int X = wi * 4 + k - (ORBX_XOFF - ORBX_EDGE);   // padded column
-        if (X >= 0 && X < w + 2 * ORBX_EDGE)
-            word |= (uint32_t)__ldg(src + reflect101(X - ORBX_EDGE, w)) << (8 * k);
+    for (int k = 0; k < 4; k++)
+        r.h[k] = (int)(__dp2a_lo(t.a01[k], __byte_perm(lo, hi, (t.sels >> (8 * k)) & 0xFFu), 0u) >> 4);
+    return r;
+}
+
+#define PYRF_ROWS 8
+__global__ void __launch_bounds__(256)
+pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long pplane_bytes,
+                       uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int prow,
+                       const ResizeWord* __restrict__ tapw, const ResizeTapY* __restrict__ tapy)
+{
+    const int wi = ORBX_XOFF / 4 + blockIdx.x * blockDim.x + threadIdx.x;      // interior words only
+    if (wi * 4 >= ORBX_XOFF + w) return;
+    const int Y0 = (blockIdx.y * blockDim.y + threadIdx.y) * PYRF_ROWS;
+    if (Y0 >= prow) return;
+    const int f = blockIdx.z;
+    ResizeWord t;
+    {
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(tapw + wi)), b = __ldg(reinterpret_cast<const uint4*>(tapw + wi) + 1);
+        t.wb = (int)a.x; t.shift = a.y; t.sels = a.z; t.a01[0] = a.w; t.a01[1] = b.x; t.a01[2] = b.y; t.a01[3] = b.z;
     }
-    *reinterpret_cast<uint32_t*>(out + (long long)f * plane_bytes + (long long)Y * pitch + wi * 4) = word;
+    const uint8_t* base = prev + (long long)f * pplane_bytes + (long long)ORBX_YOFF * ppitch + ORBX_XOFF;
+    uint32_t* dst = reinterpret_cast<uint32_t*>(out + (long long)f * plane_bytes + (long long)Y0 * pitch) + wi;
+    const int pw = pitch >> 2;
+    int have = -1;
+    HRow4 hl;
+#pragma unroll
+    for (int k = 0; k < 4; k++) hl.h[k] = 0;
+    const int nr = min(PYRF_ROWS, prow - Y0);
+#pragma unroll 2
+    for (int rr = 0; rr < nr; rr++) {
+        const ResizeTapY ty = tapy[Y0 + rr];
+        const HRow4 h0 = (ty.s0 == have) ? hl : pyr_hrow_fast(base + (long long)ty.s0 * ppitch, t);
+        const HRow4 h1 = (ty.s1 == ty.s0) ? h0 : pyr_hrow_fast(base + (long long)ty.s1 * ppitch, t);
+        const int b0 = ty.b0, b1 = ty.b1;
+        uint32_t word = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int v = (((b0 * h0.h[k]) >> 16) + ((b1 * h1.h[k]) >> 16) + 2) >> 2;
+            word |= (uint32_t)v << (8 * k);
+        }
+        dst[rr * pw] = word;
+        hl = h1; have = ty.s1;
+    }
 }
 
 // level l>0 from level l-1.  OpenCV HResizeLinear/VResizeLinear u8 arithmetic (see oracle/orc_prims.c):
@@ -103,20 +168,37 @@ pyr_resize_kernel(const uint8_t* __restrict__ prev, int ppitch, long long pplane
 int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
     int launches = 0;
-    const dim3 block(64, 4);
+    bool all_fast = true;
     for (int l = 0; l < G.nlevels; l++) {
         const LevelGeom& L = G.L[l];
-        const dim3 grid((L.pitch / 4 + block.x - 1) / block.x, (L.prow + block.y - 1) / block.y, nframes);
         if (l == 0) {
+            const dim3 block(64, 4);
+            const dim3 grid(((L.w + 3) / 4 + block.x - 1) / block.x, (L.prow + block.y - 1) / block.y, nframes);
             pyr_level0_kernel<<<grid, block, 0, s>>>(D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
                                                      L.pyr, L.pitch, L.plane_bytes, L.w, L.h);
+        } else if (L.tapw) {
+            const LevelGeom& P = G.L[l - 1];
+            const dim3 block(64, 4);
+            const dim3 grid(((L.w + 3) / 4 + block.x - 1) / block.x, (L.prow + block.y * PYRF_ROWS - 1) / (block.y * PYRF_ROWS), nframes);
+            pyr_resize_fast_kernel<<<grid, block, 0, s>>>(P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch, L.plane_bytes,
+                                                          L.w, L.prow, L.tapw, L.tapy);
         } else {
+            // generic path (taps of a word do not fit 8 source bytes): writes the border columns itself
             const LevelGeom& P = G.L[l - 1];
             const dim3 rblock(PYR_BX, PYR_BY);
             const dim3 rgrid((L.pitch / 4 + PYR_BX - 1) / PYR_BX, (L.prow + PYR_BY * PYR_ROWS - 1) / (PYR_BY * PYR_ROWS), nframes);
             pyr_resize_kernel<<<rgrid, rblock, 0, s>>>(P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch, L.plane_bytes,
                                                        L.prow, L.tapx, L.tapy);
+            all_fast = false;
         }
+        launches++;
+    }
+    (void)all_fast;
+    {
+        int maxrows = 0;
+        for (int l = 0; l < G.nlevels; l++) maxrows = G.L[l].prow > maxrows ? G.L[l].prow : maxrows;
+        const dim3 grid((maxrows * 2 * ORBX_EDGE + 255) / 256, G.nlevels, nframes);
+        pyr_border_kernel<<<grid, 256, 0, s>>>(G);
         launches++;
     }
     return launches;
