@@ -373,6 +373,7 @@ extern "C" int orbx_get_pyramid_level(orbx_extractor* e, int frame, int level, i
     if (rows) *rows = r;
     if (cols) *cols = c;
     if (!dst) return ORBX_OK;
+    if (padded) pyramid_fill_border(L, frame, e->stream);     // the hot path leaves the reflect-101 border unwritten
     const uint8_t* src = L.pyr + (size_t)frame * L.plane_bytes +
                          (padded ? (size_t)(ORBX_XOFF - ORBX_EDGE) : (size_t)ORBX_YOFF * L.pitch + ORBX_XOFF);
     CUDA_TRY(cudaMemcpy2DAsync(dst, dst_step, src, L.pitch, c, r, cudaMemcpyDeviceToHost, e->stream));

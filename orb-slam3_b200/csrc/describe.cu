@@ -76,7 +76,7 @@ int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int la
 // ------------------------------------------------------------------------------------------------
 // GaussianBlur(7x7, sigma 2) in OpenCV 4.x fixed point: kernel [18,34,48,56,48,34,18]/256, horizontal
 // pass in 8.8 (u16), vertical in 16.16, +0.5 rounding (oracle/orc_prims.c orc_gaussian7x7_s2).
-// Reads the padded pyramid plane (its reflect-101 border IS the blur's BORDER_REFLECT_101), writes the
+// Reads the interior of the pyramid plane (BORDER_REFLECT_101 is applied on the fly), writes the
 // interior of the blur plane.  HBM-bound: algorithmic bytes per frame = read + write sum(L0..L7).
 // ------------------------------------------------------------------------------------------------
 // A thread owns one 32-bit word (4 px) of a 32-row strip and slides down it.  Horizontal pass per row:
@@ -87,9 +87,41 @@ int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int la
 #define BL_BX 64
 #define BL_BY 2
 
-__device__ __forceinline__ void blur_hrow(int (&h)[4], const uint32_t* __restrict__ p)
+// The pyramid planes carry no materialised border: BORDER_REFLECT_101 is applied while loading.  Every
+// thread rebuilds its three words with PRMT selectors computed once per thread (identity for all but
+// the first and the last two word threads of a row): the first word thread mirrors columns 1..3 to the
+// left, the last two replace every byte right of column w-1 by its mirror image.
+struct BlurEdge { uint32_t selL, selM, selR; bool rFromLM; };
+
+__device__ __forceinline__ BlurEdge blur_edge(int wi, int w)
 {
-    const uint32_t l = __ldg(p - 1), m = __ldg(p), r = __ldg(p + 1);
+    BlurEdge e;
+    e.selL = wi == 0 ? 0x5670u : 0x3210u;         // over (l, m): bytes -3,-2,-1 = columns 3,2,1
+    e.selM = 0x7654u;                             // over (l, m): m itself
+    e.selR = 0x7654u;                             // over (m, r): r itself
+    e.rFromLM = false;
+    const int last = w - 1;
+    if (4 * wi + 7 > last) {
+        // position q of m | r (column 4wi+q): right of the image -> byte idx of l | m | r holding its mirror
+        uint32_t sm = 0, sr = 0;
+        bool lm = (4 * wi + 3 >= last);           // last word thread: mirrors of r's bytes lie in l | m
+        for (int q = 0; q < 8; q++) {
+            const int pos = 4 * wi + q;
+            int idx = q + 4;                      // itself
+            if (pos > last) { idx = 2 * last - pos - (4 * wi - 4); if (idx < 0) idx = 0; }
+            if (q < 4) sm |= (uint32_t)idx << (4 * q);                       // idx < 8: over (l, m)
+            else sr |= (uint32_t)(lm ? (idx > 7 ? 7 : idx) : idx - 4) << (4 * (q - 4));
+        }
+        e.selM = sm; e.selR = sr; e.rFromLM = lm;
+    }
+    return e;
+}
+
+__device__ __forceinline__ void blur_hrow(int (&h)[4], const uint32_t* __restrict__ p, const BlurEdge& e)
+{
+    const uint32_t l0 = __ldg(p - 1), m0 = __ldg(p), r0 = __ldg(p + 1);
+    const uint32_t l = __byte_perm(l0, m0, e.selL), m = __byte_perm(l0, m0, e.selM);
+    const uint32_t r = e.rFromLM ? __byte_perm(l0, m0, e.selR) : __byte_perm(m0, r0, e.selR);
     const uint32_t kA = 18u | (34u << 8) | (48u << 16) | (56u << 24);   // taps -3..0
     const uint32_t kB = 48u | (34u << 8) | (18u << 16);                 // taps +1..+3
     // word starting at byte x+d: funnel shifts of (l, m) / (m, r)
@@ -120,16 +152,18 @@ blur_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, int pit
     if (wi * 4 >= w || y0 >= h) return;
     const int f = blockIdx.z;
     const int pw = pitch >> 2;
-    // word of pixel (4*wi, y0-3)
-    const uint32_t* p = reinterpret_cast<const uint32_t*>(pyr + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y0 - 3) * pitch + ORBX_XOFF) + wi;
+    // row y of the level (reflect-101 outside [0, h)), word wi
+    const uint32_t* base = reinterpret_cast<const uint32_t*>(pyr + (long long)f * plane_bytes + (long long)ORBX_YOFF * pitch + ORBX_XOFF) + wi;
+    auto rowp = [&](int y) { y = y < 0 ? -y : y; y = y >= h ? 2 * (h - 1) - y : y; return base + y * pw; };
     uint32_t* q = reinterpret_cast<uint32_t*>(blur + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y0) * pitch + ORBX_XOFF) + wi;
+    const BlurEdge edge = blur_edge(wi, w);
     int H[7][4];
 #pragma unroll
-    for (int i = 0; i < 6; i++) { blur_hrow(H[i], p); p += pw; }
+    for (int i = 0; i < 6; i++) blur_hrow(H[i], rowp(y0 - 3 + i), edge);
     const int nr = min(BL_RT, h - y0);
 #define BLUR_STEP(PH)                                                   \
     if (rb + PH < nr) {                                                 \
-        blur_hrow(H[(PH + 6) % 7], p); p += pw;                         \
+        blur_hrow(H[(PH + 6) % 7], rowp(y0 + rb + PH + 3), edge);      \
         *q = blur_vword<PH>(H); q += pw;                                \
     }
 #pragma unroll 1

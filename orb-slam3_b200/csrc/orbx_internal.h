@@ -109,6 +109,7 @@ struct DevBuffers {
 
 // kernel launchers (each returns the number of kernel launches it issued)
 int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
+void pyramid_fill_border(const LevelGeom& L, int frame, cudaStream_t s);   // mvImagePyramid border on demand
 int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
 int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
 int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int lap0, int lap1, cudaStream_t s);

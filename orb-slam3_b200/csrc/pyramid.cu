@@ -1,10 +1,9 @@
 // pyramid.cu — image pyramid (ORBextractor::ComputePyramid, reference src/ORBextractor.cc:1664-1715).
 //
 // Level 0 = copyMakeBorder(image, 19, BORDER_REFLECT_101); level l>0 = cv::resize(level l-1,
-// INTER_LINEAR) in OpenCV's 11-bit fixed point followed by the same reflect-101 border.  The border
-// is folded into the tap tables (indexed by PADDED coordinate), so each level is one streaming pass:
-// every thread produces 4 consecutive bytes of one padded row and stores them as one 32-bit word
-// (rows are 128-byte pitched, interior starts on a 32-byte sector boundary).
+// INTER_LINEAR) in OpenCV's 11-bit fixed point followed by the same reflect-101 border.  Planes keep
+// room for the border (rows are 128-byte pitched, interior starts on a 32-byte sector boundary) but the
+// hot path only writes the interior; the border is produced on demand (orbx_get_pyramid_level).
 // HBM-bound: algorithmic bytes per frame = read sum(L0..L6) + write sum(L1..L7).
 #include "orbx_internal.h"
 
@@ -15,33 +14,51 @@ __device__ __forceinline__ int reflect101(int i, int n)
     return i;
 }
 
-// level 0: input frame -> interior words of every padded row (rows reflect about the image edges;
-// the 19 columns left and right of the image are filled by pyr_border_kernel for all levels at once)
+// level 0: input frame -> interior of the level-0 plane, 16 bytes per thread.  The 19-px reflect-101
+// border of mvImagePyramid is NOT materialised on the hot path (nothing downstream reads it: the blur
+// mirrors on the fly); orbx_get_pyramid_level(padded) fills it on demand with the two kernels below.
 __global__ void __launch_bounds__(256)
 pyr_level0_kernel(const uint8_t* __restrict__ in, int in_pitch, long long in_frame_bytes,
                   uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h)
 {
-    const int wi = blockIdx.x * blockDim.x + threadIdx.x;     // 32-bit word of the image row
-    const int Y = blockIdx.y * blockDim.y + threadIdx.y;      // padded row
-    if (Y >= h + 2 * ORBX_EDGE || wi * 4 >= w) return;
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;     // 16-byte group of the image row
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (y >= h || qi * 16 >= w) return;
     const int f = blockIdx.z;
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(in + (long long)f * in_frame_bytes + (long long)reflect101(Y - ORBX_EDGE, h) * in_pitch);
-    reinterpret_cast<uint32_t*>(out + (long long)f * plane_bytes + (long long)Y * pitch + ORBX_XOFF)[wi] = __ldg(src + wi);
+    const uint4* src = reinterpret_cast<const uint4*>(in + (long long)f * in_frame_bytes + (long long)y * in_pitch);
+    reinterpret_cast<uint4*>(out + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y) * pitch + ORBX_XOFF)[qi] = __ldg(src + qi);
 }
 
-// reflect-101 columns of every level: out[-k] = out[k], out[w-1+k] = out[w-1-k], k = 1..19
-// (copyMakeBorder BORDER_REFLECT_101 of the level image, :1689-1693,1711-1713)
+// on-demand border, step 1: rows above / below the image = reflect-101 rows (interior columns)
 __global__ void __launch_bounds__(256)
-pyr_border_kernel(FrameGeom G)
+pyr_border_rows_kernel(uint8_t* __restrict__ plane, int pitch, int w, int h)
 {
-    const int lvl = blockIdx.y, f = blockIdx.z;
-    const LevelGeom& L = G.L[lvl];
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;                                 // 0..37: 19 rows above, 19 below
+    if (x >= w) return;
+    const int Y = j < ORBX_EDGE ? j : h + j;                  // padded row
+    const int sy = j < ORBX_EDGE ? ORBX_EDGE - j : h - 2 - (j - ORBX_EDGE);
+    plane[(long long)Y * pitch + ORBX_XOFF + x] = plane[(long long)(ORBX_YOFF + sy) * pitch + ORBX_XOFF + x];
+}
+
+// on-demand border, step 2: columns left / right of every padded row: out[-k] = out[k],
+// out[w-1+k] = out[w-1-k], k = 1..19 (copyMakeBorder BORDER_REFLECT_101, :1689-1693,1711-1713)
+__global__ void __launch_bounds__(256)
+pyr_border_cols_kernel(uint8_t* __restrict__ plane, int pitch, int w, int prow)
+{
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int Y = idx / (2 * ORBX_EDGE), j = idx - Y * (2 * ORBX_EDGE);
-    if (Y >= L.prow) return;
-    uint8_t* row = L.pyr + (long long)f * L.plane_bytes + (long long)Y * L.pitch + ORBX_XOFF;
+    if (Y >= prow) return;
+    uint8_t* row = plane + (long long)Y * pitch + ORBX_XOFF;
     if (j < ORBX_EDGE) row[-(j + 1)] = row[j + 1];
-    else { const int k = j - ORBX_EDGE + 1; row[L.w - 1 + k] = row[L.w - 1 - k]; }
+    else { const int k = j - ORBX_EDGE + 1; row[w - 1 + k] = row[w - 1 - k]; }
+}
+
+void pyramid_fill_border(const LevelGeom& L, int frame, cudaStream_t s)
+{
+    uint8_t* plane = L.pyr + (long long)frame * L.plane_bytes;
+    pyr_border_rows_kernel<<<dim3((L.w + 255) / 256, 2 * ORBX_EDGE), 256, 0, s>>>(plane, L.pitch, L.w, L.h);
+    pyr_border_cols_kernel<<<(L.prow * 2 * ORBX_EDGE + 255) / 256, 256, 0, s>>>(plane, L.pitch, L.w, L.prow);
 }
 
 // fast path of the resize: interior words only, taps from the 8 source bytes starting at the first
@@ -62,13 +79,13 @@ __device__ __forceinline__ HRow4 pyr_hrow_fast(const uint8_t* __restrict__ S, co
 #define PYRF_ROWS 8
 __global__ void __launch_bounds__(256)
 pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long pplane_bytes,
-                       uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int prow,
+                       uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h,
                        const ResizeWord* __restrict__ tapw, const ResizeTapY* __restrict__ tapy)
 {
     const int wi = ORBX_XOFF / 4 + blockIdx.x * blockDim.x + threadIdx.x;      // interior words only
     if (wi * 4 >= ORBX_XOFF + w) return;
-    const int Y0 = (blockIdx.y * blockDim.y + threadIdx.y) * PYRF_ROWS;
-    if (Y0 >= prow) return;
+    const int Y0 = (blockIdx.y * blockDim.y + threadIdx.y) * PYRF_ROWS;       // image row (interior rows only)
+    if (Y0 >= h) return;
     const int f = blockIdx.z;
     ResizeWord t;
     {
@@ -76,16 +93,16 @@ pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long p
         t.wb = (int)a.x; t.shift = a.y; t.sels = a.z; t.a01[0] = a.w; t.a01[1] = b.x; t.a01[2] = b.y; t.a01[3] = b.z;
     }
     const uint8_t* base = prev + (long long)f * pplane_bytes + (long long)ORBX_YOFF * ppitch + ORBX_XOFF;
-    uint32_t* dst = reinterpret_cast<uint32_t*>(out + (long long)f * plane_bytes + (long long)Y0 * pitch) + wi;
+    uint32_t* dst = reinterpret_cast<uint32_t*>(out + (long long)f * plane_bytes + (long long)(ORBX_YOFF + Y0) * pitch) + wi;
     const int pw = pitch >> 2;
     int have = -1;
     HRow4 hl;
 #pragma unroll
     for (int k = 0; k < 4; k++) hl.h[k] = 0;
-    const int nr = min(PYRF_ROWS, prow - Y0);
+    const int nr = min(PYRF_ROWS, h - Y0);
 #pragma unroll 2
     for (int rr = 0; rr < nr; rr++) {
-        const ResizeTapY ty = tapy[Y0 + rr];
+        const ResizeTapY ty = tapy[ORBX_EDGE + Y0 + rr];       // the tap table is indexed by padded row
         const HRow4 h0 = (ty.s0 == have) ? hl : pyr_hrow_fast(base + (long long)ty.s0 * ppitch, t);
         const HRow4 h1 = (ty.s1 == ty.s0) ? h0 : pyr_hrow_fast(base + (long long)ty.s1 * ppitch, t);
         const int b0 = ty.b0, b1 = ty.b1;
@@ -168,37 +185,27 @@ pyr_resize_kernel(const uint8_t* __restrict__ prev, int ppitch, long long pplane
 int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
     int launches = 0;
-    bool all_fast = true;
     for (int l = 0; l < G.nlevels; l++) {
         const LevelGeom& L = G.L[l];
         if (l == 0) {
             const dim3 block(64, 4);
-            const dim3 grid(((L.w + 3) / 4 + block.x - 1) / block.x, (L.prow + block.y - 1) / block.y, nframes);
+            const dim3 grid(((L.w + 15) / 16 + block.x - 1) / block.x, (L.h + block.y - 1) / block.y, nframes);
             pyr_level0_kernel<<<grid, block, 0, s>>>(D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
                                                      L.pyr, L.pitch, L.plane_bytes, L.w, L.h);
         } else if (L.tapw) {
             const LevelGeom& P = G.L[l - 1];
             const dim3 block(64, 4);
-            const dim3 grid(((L.w + 3) / 4 + block.x - 1) / block.x, (L.prow + block.y * PYRF_ROWS - 1) / (block.y * PYRF_ROWS), nframes);
+            const dim3 grid(((L.w + 3) / 4 + block.x - 1) / block.x, (L.h + block.y * PYRF_ROWS - 1) / (block.y * PYRF_ROWS), nframes);
             pyr_resize_fast_kernel<<<grid, block, 0, s>>>(P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch, L.plane_bytes,
-                                                          L.w, L.prow, L.tapw, L.tapy);
+                                                          L.w, L.h, L.tapw, L.tapy);
         } else {
-            // generic path (taps of a word do not fit 8 source bytes): writes the border columns itself
+            // generic path (taps of a word do not fit 8 source bytes); it also writes the border
             const LevelGeom& P = G.L[l - 1];
             const dim3 rblock(PYR_BX, PYR_BY);
             const dim3 rgrid((L.pitch / 4 + PYR_BX - 1) / PYR_BX, (L.prow + PYR_BY * PYR_ROWS - 1) / (PYR_BY * PYR_ROWS), nframes);
             pyr_resize_kernel<<<rgrid, rblock, 0, s>>>(P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch, L.plane_bytes,
                                                        L.prow, L.tapx, L.tapy);
-            all_fast = false;
         }
-        launches++;
-    }
-    (void)all_fast;
-    {
-        int maxrows = 0;
-        for (int l = 0; l < G.nlevels; l++) maxrows = G.L[l].prow > maxrows ? G.L[l].prow : maxrows;
-        const dim3 grid((maxrows * 2 * ORBX_EDGE + 255) / 256, G.nlevels, nframes);
-        pyr_border_kernel<<<grid, 256, 0, s>>>(G);
         launches++;
     }
     return launches;
