@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <algorithm>
 
 static thread_local char g_err[512] = "";
@@ -54,11 +55,19 @@ extern "C" int orbx_create(int nfeatures, float scaleFactor, int nlevels, int in
     e->scaleFactorF = scaleFactor;
     e->device = device; e->reserved = false; e->profiling = false; e->launches = 0; e->last_nframes = 0;
     e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr;
+    e->h_counts = nullptr; e->h_counts_cap = 0;
     memset(&e->G, 0, sizeof(e->G)); memset(&e->D, 0, sizeof(e->D));
     memset(e->stage_ms, 0, sizeof(e->stage_ms));
     orbx_init_tables(e);
     cudaError_t ce = cudaSetDevice(device);
     if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    for (int i = 0; i < ORBX_NCSTREAMS && ce == cudaSuccess; i++) {
+        ce = cudaStreamCreateWithFlags(&e->cstream[i], cudaStreamNonBlocking);
+        if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_join[i], cudaEventDisableTiming);
+    }
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming);
+    if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->stream_h2d, cudaStreamNonBlocking);
+    if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->stream_d2h, cudaStreamNonBlocking);
     for (int i = 0; i <= ORBX_NSTAGES && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->ev[i]);
     for (int i = 0; i < 2 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->tev[i]);
     if (ce != cudaSuccess) {
@@ -88,6 +97,13 @@ extern "C" void orbx_destroy(orbx_extractor* e)
     free_device(e);
     for (int i = 0; i <= ORBX_NSTAGES; i++) cudaEventDestroy(e->ev[i]);
     for (int i = 0; i < 2; i++) cudaEventDestroy(e->tev[i]);
+    for (cudaEvent_t ev : e->ev_up) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : e->ev_done) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : e->ev_down) cudaEventDestroy(ev);
+    for (int i = 0; i < ORBX_NCSTREAMS; i++) { cudaStreamDestroy(e->cstream[i]); cudaEventDestroy(e->ev_join[i]); }
+    cudaEventDestroy(e->ev_fork);
+    if (e->h_counts) cudaFreeHost(e->h_counts);
+    cudaStreamDestroy(e->stream_h2d); cudaStreamDestroy(e->stream_d2h);
     cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -135,7 +151,7 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     DevBuffers D;
     memset(&D, 0, sizeof(D));
     const size_t B = (size_t)max_batch;
-    D.in_pitch = (cols + 127) / 128 * 128;
+    D.in_pitch = (cols + 15) / 16 * 16;       // rows 16-byte aligned for the level-0 copy; == cols for the usual widths
     int rc = 0;
     rc |= dev_alloc(e, &D.input, B * rows * D.in_pitch);
     for (int l = 0; l < G.nlevels && !rc; l++) {
@@ -193,28 +209,46 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     return ORBX_OK;
 }
 
-static int upload_frames(orbx_extractor* e, int slot0, int nframes, const uint8_t* imgs, size_t step, size_t frame_stride)
+static int upload_frames(orbx_extractor* e, int slot0, int nframes, const uint8_t* imgs, size_t step, size_t frame_stride,
+                         cudaStream_t st)
 {
     const FrameGeom& G = e->G;
-    if (frame_stride == step * (size_t)G.rows) {
+    uint8_t* dst = e->D.input + (size_t)slot0 * G.rows * e->D.in_pitch;
+    if (step == (size_t)e->D.in_pitch && frame_stride == step * (size_t)G.rows) {
+        // densely packed frames with the device pitch: one linear copy
+        CUDA_TRY(cudaMemcpyAsync(dst, imgs, (size_t)nframes * G.rows * step, cudaMemcpyHostToDevice, st));
+    } else if (frame_stride == step * (size_t)G.rows) {
         // frames are back to back: one 2-D copy of nframes*rows rows
-        CUDA_TRY(cudaMemcpy2DAsync(e->D.input + (size_t)slot0 * G.rows * e->D.in_pitch, e->D.in_pitch, imgs, step,
-                                   G.cols, (size_t)nframes * G.rows, cudaMemcpyHostToDevice, e->stream));
+        CUDA_TRY(cudaMemcpy2DAsync(dst, e->D.in_pitch, imgs, step, G.cols, (size_t)nframes * G.rows, cudaMemcpyHostToDevice, st));
     } else {
         for (int f = 0; f < nframes; f++)
-            CUDA_TRY(cudaMemcpy2DAsync(e->D.input + (size_t)(slot0 + f) * G.rows * e->D.in_pitch, e->D.in_pitch,
-                                       imgs + (size_t)f * frame_stride, step, G.cols, G.rows, cudaMemcpyHostToDevice, e->stream));
+            CUDA_TRY(cudaMemcpy2DAsync(dst + (size_t)f * G.rows * e->D.in_pitch, e->D.in_pitch,
+                                       imgs + (size_t)f * frame_stride, step, G.cols, G.rows, cudaMemcpyHostToDevice, st));
     }
     return 0;
 }
 
-// the whole extraction pipeline on frame slots [0, nframes), asynchronous on the handle's stream
-static int run_pipeline(orbx_extractor* e, int nframes, int lap0, int lap1)
+// views of the geometry / buffers that start at frame slot s0 (kernels index frames from 0)
+static void slot_view(const orbx_extractor* e, int s0, FrameGeom* Go, DevBuffers* Do)
 {
+    *Go = e->G; *Do = e->D;
     const FrameGeom& G = e->G;
-    const DevBuffers& D = e->D;
-    cudaStream_t s = e->stream;
-    const bool prof = e->profiling;
+    const size_t s = (size_t)s0;
+    for (int l = 0; l < G.nlevels; l++) { Go->L[l].pyr += s * G.L[l].plane_bytes; Go->L[l].blur += s * G.L[l].plane_bytes; }
+    Do->input += s * G.rows * e->D.in_pitch;
+    Do->cand += s * G.cand_per_frame; Do->candnode += s * G.cand_per_frame;
+    Do->nodetab += s * G.nlevels * e->D.nodetab_per_frame;
+    Do->sel += s * G.sel_per_frame; Do->selcnt += s * G.nlevels; Do->candcnt += s * G.nlevels;
+    Do->angle += s * G.sel_per_frame; Do->outidx += s * G.sel_per_frame;
+    Do->kps += s * G.out_cap; Do->desc += s * G.out_cap * 32; Do->counts += 2 * s;
+}
+
+// the whole extraction pipeline on frame slots [0, nframes), asynchronous on the handle's stream
+static int run_pipeline(orbx_extractor* e, int slot0, int nframes, int lap0, int lap1, cudaStream_t s)
+{
+    FrameGeom G; DevBuffers D;
+    slot_view(e, slot0, &G, &D);
+    const bool prof = e->profiling && s == e->stream;
     if (prof) cudaEventRecord(e->ev[0], s);
     e->launches += launch_pyramid(G, D, nframes, s);
     if (prof) cudaEventRecord(e->ev[1], s);
@@ -228,7 +262,6 @@ static int run_pipeline(orbx_extractor* e, int nframes, int lap0, int lap1)
     if (prof) cudaEventRecord(e->ev[5], s);
     e->launches += launch_describe(G, D, nframes, s);
     if (prof) cudaEventRecord(e->ev[6], s);
-    e->last_nframes = nframes;
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -247,7 +280,7 @@ extern "C" int orbx_upload(orbx_extractor* e, int nframes, const uint8_t* imgs, 
     int r = orbx_reserve(e, rows, cols, nframes);
     if (r) return r;
     CUDA_TRY(cudaSetDevice(e->device));
-    r = upload_frames(e, 0, nframes, imgs, step, frame_stride);
+    r = upload_frames(e, 0, nframes, imgs, step, frame_stride, e->stream);
     if (r) return r;
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     e->last_nframes = -nframes;     // uploaded, not yet run
@@ -258,7 +291,24 @@ extern "C" int orbx_run_resident(orbx_extractor* e, int lap0, int lap1)
 {
     if (!e || !e->reserved || e->last_nframes == 0) { orbx_set_error("run_resident before upload"); return ORBX_ERR_STATE; }
     CUDA_TRY(cudaSetDevice(e->device));
-    return run_pipeline(e, e->last_nframes < 0 ? -e->last_nframes : e->last_nframes, lap0, lap1);
+    const int n = e->last_nframes < 0 ? -e->last_nframes : e->last_nframes;
+    e->last_nframes = n;
+    int ns = ORBX_NCSTREAMS;
+    if (const char* cs = getenv("ORBX_STREAMS")) { const int v = atoi(cs); if (v >= 1 && v <= ORBX_NCSTREAMS) ns = v; }
+    if (e->profiling || ns == 1 || n < 4 * ns) return run_pipeline(e, 0, n, lap0, lap1, e->stream);
+    // fork: sub-batches on the compute streams (ordered after everything queued on the handle's stream), join back
+    CUDA_TRY(cudaEventRecord(e->ev_fork, e->stream));
+    const int per = (n + ns - 1) / ns;
+    for (int i = 0; i < ns; i++) {
+        const int s0 = i * per, m = n - s0 < per ? n - s0 : per;
+        if (m <= 0) break;
+        CUDA_TRY(cudaStreamWaitEvent(e->cstream[i], e->ev_fork, 0));
+        int r = run_pipeline(e, s0, m, lap0, lap1, e->cstream[i]);
+        if (r) return r;
+        CUDA_TRY(cudaEventRecord(e->ev_join[i], e->cstream[i]));
+        CUDA_TRY(cudaStreamWaitEvent(e->stream, e->ev_join[i], 0));
+    }
+    return ORBX_OK;
 }
 
 extern "C" int orbx_sync(orbx_extractor* e)
@@ -270,16 +320,21 @@ extern "C" int orbx_sync(orbx_extractor* e)
 }
 
 static int download_results(orbx_extractor* e, int slot0, int nframes, orbx_keypoint* kps, uint8_t* desc, int cap,
-                            int* counts_host /* 2*nframes */)
+                            int* counts_host /* 2*nframes */, cudaStream_t st)
 {
     const FrameGeom& G = e->G;
     const int ncopy = cap < G.out_cap ? cap : G.out_cap;
-    CUDA_TRY(cudaMemcpyAsync(counts_host, e->D.counts + 2 * slot0, sizeof(int) * 2 * nframes, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(counts_host, e->D.counts + 2 * slot0, sizeof(int) * 2 * nframes, cudaMemcpyDeviceToHost, st));
+    if (cap == G.out_cap) {       // caller's per-frame capacity equals the device layout: two linear copies
+        CUDA_TRY(cudaMemcpyAsync(kps, e->D.kps + (size_t)slot0 * G.out_cap, (size_t)nframes * cap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(desc, e->D.desc + (size_t)slot0 * G.out_cap * 32, (size_t)nframes * cap * 32, cudaMemcpyDeviceToHost, st));
+        return 0;
+    }
     CUDA_TRY(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbx_keypoint), e->D.kps + (size_t)slot0 * G.out_cap,
                                (size_t)G.out_cap * sizeof(orbx_keypoint), (size_t)ncopy * sizeof(orbx_keypoint), nframes,
-                               cudaMemcpyDeviceToHost, e->stream));
+                               cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaMemcpy2DAsync(desc, (size_t)cap * 32, e->D.desc + (size_t)slot0 * G.out_cap * 32, (size_t)G.out_cap * 32,
-                               (size_t)ncopy * 32, nframes, cudaMemcpyDeviceToHost, e->stream));
+                               (size_t)ncopy * 32, nframes, cudaMemcpyDeviceToHost, st));
     return 0;
 }
 
@@ -289,7 +344,7 @@ extern "C" int orbx_download(orbx_extractor* e, orbx_keypoint* kps, uint8_t* des
     CUDA_TRY(cudaSetDevice(e->device));
     const int n = e->last_nframes;
     std::vector<int> counts(2 * (size_t)n);
-    int r = download_results(e, 0, n, kps, desc, cap, counts.data());
+    int r = download_results(e, 0, n, kps, desc, cap, counts.data(), e->stream);
     if (r) return r;
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     collect_stage_times(e);
@@ -328,23 +383,69 @@ extern "C" int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t*
     }
     CUDA_TRY(cudaSetDevice(e->device));
     const int B = e->G.batch;
-    std::vector<int> counts(2 * (size_t)B);
     int rc = ORBX_OK;
-    for (int f0 = 0; f0 < nframes; f0 += B) {
-        const int nb = nframes - f0 < B ? nframes - f0 : B;
-        r = upload_frames(e, 0, nb, imgs + (size_t)f0 * frame_stride, step, frame_stride);
+    // Chunked three-stream ring pipeline: the frames are cut into chunks that cycle through the R chunk
+    // slots of the device buffers; upload of chunk k+1, kernels of chunk k and download of chunk k-1
+    // overlap.  Hazards of slot reuse: upload(k) waits for kernels(k-R) (input consumed), kernels(k) wait
+    // for upload(k) and download(k-R) (outputs of the slot copied out), download(k) waits for kernels(k).
+    int chunk = 128;
+    if (const char* cs = getenv("ORBX_CHUNK")) { const int v = atoi(cs); if (v > 0) chunk = v; }
+    if (chunk > B) chunk = B;
+    const int R = B / chunk > 0 ? B / chunk : 1;             // chunk slots in the ring
+    int ncs = ORBX_NCSTREAMS;
+    if (const char* cs_ = getenv("ORBX_STREAMS")) { const int v = atoi(cs_); if (v >= 1 && v <= ORBX_NCSTREAMS) ncs = v; }
+    while (R % ncs) ncs--;                                   // a slot must always be served by the same compute stream
+    const int nchunks = (nframes + chunk - 1) / chunk;
+    const bool multi = nchunks > 1;
+    while ((int)e->ev_up.size() < R) {
+        cudaEvent_t a, b, c;
+        CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&c, cudaEventDisableTiming));
+        e->ev_up.push_back(a); e->ev_done.push_back(b); e->ev_down.push_back(c);
+    }
+    if (e->h_counts_cap < 2 * (size_t)nframes) {
+        if (e->h_counts) cudaFreeHost(e->h_counts);
+        e->h_counts = nullptr; e->h_counts_cap = 0;
+        CUDA_TRY(cudaHostAlloc((void**)&e->h_counts, sizeof(int) * 2 * (size_t)nframes, cudaHostAllocDefault));
+        e->h_counts_cap = 2 * (size_t)nframes;
+    }
+    int* counts = e->h_counts;
+    cudaStream_t up = multi ? e->stream_h2d : e->stream, dn = multi ? e->stream_d2h : e->stream;
+    for (int k = 0; k < nchunks; k++) {
+        const int fr0 = k * chunk, n = nframes - fr0 < chunk ? nframes - fr0 : chunk;
+        const int slot = k % R, s0 = slot * chunk;
+        cudaStream_t cs = (multi && !e->profiling) ? e->cstream[k % ncs] : e->stream;   // chunk slot k%R is always served by the same stream
+        if (multi && k >= R) CUDA_TRY(cudaStreamWaitEvent(up, e->ev_done[slot], 0));
+        r = upload_frames(e, s0, n, imgs + (size_t)fr0 * frame_stride, step, frame_stride, up);
         if (r) return r;
-        r = run_pipeline(e, nb, lap0, lap1);
-        if (r) return r;
-        r = download_results(e, 0, nb, kps + (size_t)f0 * cap, desc + (size_t)f0 * cap * 32, cap, counts.data());
-        if (r) return r;
-        CUDA_TRY(cudaStreamSynchronize(e->stream));
-        collect_stage_times(e);
-        for (int f = 0; f < nb; f++) {
-            if (nkp) nkp[f0 + f] = counts[2 * f];
-            if (mono) mono[f0 + f] = counts[2 * f + 1];
-            if (counts[2 * f] > cap) rc = ORBX_ERR_CAPACITY;
+        if (multi) {
+            CUDA_TRY(cudaEventRecord(e->ev_up[slot], up));
+            CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_up[slot], 0));
+            if (k >= R) CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_down[slot], 0));
         }
+        r = run_pipeline(e, s0, n, lap0, lap1, cs);
+        if (r) return r;
+        if (multi) {
+            CUDA_TRY(cudaEventRecord(e->ev_done[slot], cs));
+            CUDA_TRY(cudaStreamWaitEvent(dn, e->ev_done[slot], 0));
+        }
+        r = download_results(e, s0, n, kps + (size_t)fr0 * cap, desc + (size_t)fr0 * cap * 32, cap, counts + 2 * (size_t)fr0, dn);
+        if (r) return r;
+        if (multi) CUDA_TRY(cudaEventRecord(e->ev_down[slot], dn));
+    }
+    if (multi) {
+        // callers (timer, stereo match) order against the handle's stream: join the copy streams into it
+        CUDA_TRY(cudaStreamWaitEvent(e->stream, e->ev_down[(nchunks - 1) % R], 0));
+        CUDA_TRY(cudaStreamSynchronize(e->stream_d2h));
+    }
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    collect_stage_times(e);
+    e->last_nframes = nframes < B ? nframes : B;           // resident pyramids / outputs: the last pass over the slots
+    for (int f = 0; f < nframes; f++) {
+        if (nkp) nkp[f] = counts[2 * f];
+        if (mono) mono[f] = counts[2 * f + 1];
+        if (counts[2 * f] > cap) rc = ORBX_ERR_CAPACITY;
     }
     if (rc) orbx_set_error("keypoint capacity %d too small", cap);
     return rc;

@@ -4,6 +4,7 @@
 #include <vector>
 
 #define ORBX_NSTAGES 6
+#define ORBX_NCSTREAMS 4
 
 struct orbx_extractor {
     // ORBextractor members (include/ORBextractor.h:93-112)
@@ -15,6 +16,11 @@ struct orbx_extractor {
     // device state
     int device;
     cudaStream_t stream;
+    cudaStream_t cstream[ORBX_NCSTREAMS];  // compute streams: sub-batches run concurrently so kernel tails overlap
+    cudaEvent_t ev_fork, ev_join[ORBX_NCSTREAMS];
+    cudaStream_t stream_h2d, stream_d2h;   // copy engines of the chunked extract_batch pipeline
+    std::vector<cudaEvent_t> ev_up, ev_done, ev_down;
+    int* h_counts; size_t h_counts_cap;    // pinned {nkp, mono} staging (a pageable target would make the D2H copy synchronous)
     bool reserved;
     FrameGeom G;
     DevBuffers D;
