@@ -26,7 +26,9 @@ def build(force: bool = False, verbose: bool = False) -> pathlib.Path:
     if not force and not needs_build():
         return lib
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    cmd = [nvcc, *NVCC_FLAGS, "-o", str(lib), *[str(CSRC / s) for s in SOURCES]]
+    import os
+    extra = os.environ.get("ORBX_NVCC_EXTRA", "").split()
+    cmd = [nvcc, *NVCC_FLAGS, *extra, "-o", str(lib), *[str(CSRC / s) for s in SOURCES]]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     r = subprocess.run(cmd, capture_output=True, text=True)

@@ -35,32 +35,35 @@
 // Returns the two scores (0..254) in the low bytes of the two lanes.
 __device__ __forceinline__ uint32_t fast_score_pair(const uint32_t (&r)[16], uint32_t c)
 {
-    uint32_t t3[16];
+    // arcs k and k+3 share two of their three triples:  min(arc_k, arc_k+3) =
+    // max(t3[k+3], t3[k+6], min(t3[k], t3[k+9]));  the 16 arcs pair up as (k, k+3) for these 8 starts
+    constexpr int PK[8] = {0, 6, 12, 2, 8, 14, 4, 10};
+    uint32_t t3[16], w[8];
     uint32_t P, Q;
     // P: min over the 16 arcs of (max of the arc's 9 ring pixels)
 #pragma unroll
     for (int k = 0; k < 16; k++) t3[k] = __vimax3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
-    {
-        uint32_t a[16];
 #pragma unroll
-        for (int k = 0; k < 16; k++) a[k] = __vimax3_u16x2(t3[k], t3[(k + 3) & 15], t3[(k + 6) & 15]);
-        P = __vimin3_u16x2(a[0], a[1], a[2]);
-#pragma unroll
-        for (int k = 3; k < 15; k += 2) P = __vimin3_u16x2(P, a[k], a[k + 1]);
-        P = __vminu2(P, a[15]);
+    for (int i = 0; i < 8; i++) {
+        const int k = PK[i];
+        w[i] = __vimax3_u16x2(t3[(k + 3) & 15], t3[(k + 6) & 15], __vminu2(t3[k], t3[(k + 9) & 15]));
     }
+    P = __vimin3_u16x2(w[0], w[1], w[2]);
+    P = __vimin3_u16x2(P, w[3], w[4]);
+    P = __vimin3_u16x2(P, w[5], w[6]);
+    P = __vminu2(P, w[7]);
     // Q: max over the arcs of (min of the arc)
 #pragma unroll
     for (int k = 0; k < 16; k++) t3[k] = __vimin3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
-    {
-        uint32_t a[16];
 #pragma unroll
-        for (int k = 0; k < 16; k++) a[k] = __vimin3_u16x2(t3[k], t3[(k + 3) & 15], t3[(k + 6) & 15]);
-        Q = __vimax3_u16x2(a[0], a[1], a[2]);
-#pragma unroll
-        for (int k = 3; k < 15; k += 2) Q = __vimax3_u16x2(Q, a[k], a[k + 1]);
-        Q = __vmaxu2(Q, a[15]);
+    for (int i = 0; i < 8; i++) {
+        const int k = PK[i];
+        w[i] = __vimin3_u16x2(t3[(k + 3) & 15], t3[(k + 6) & 15], __vmaxu2(t3[k], t3[(k + 9) & 15]));
     }
+    Q = __vimax3_u16x2(w[0], w[1], w[2]);
+    Q = __vimax3_u16x2(Q, w[3], w[4]);
+    Q = __vimax3_u16x2(Q, w[5], w[6]);
+    Q = __vmaxu2(Q, w[7]);
     // clean lanes (high byte -> value), biased by 0x100 so that plain 32-bit adds never borrow across lanes
     const uint32_t Pc = __byte_perm(P, 0u, 0x4341), Qc = __byte_perm(Q, 0u, 0x4341), Vc = __byte_perm(c, 0u, 0x4341);
     const uint32_t Ab = Vc + 0x01000100u - Pc;        // 0x100 + (v - P)  per lane, in [1, 0x1FF]
@@ -131,10 +134,13 @@ __device__ __forceinline__ void nms_fill(uint32_t (&w)[4], uint32_t l, uint32_t 
     w[3] = __funnelshift_r(m, r, 8);
 }
 
-__global__ void __launch_bounds__(FAST_THREADS, 5)
+#ifndef FAST_MINBLOCKS
+#define FAST_MINBLOCKS 4
+#endif
+__global__ void __launch_bounds__(FAST_THREADS, FAST_MINBLOCKS)
 fast_band_kernel(FrameGeom G, DevBuffers D)
 {
-    extern __shared__ uint32_t s_dyn[];               // per warp: S words [ihmax][32], then u16 survivor list
+    extern __shared__ uint32_t s_dyn[];               // per warp: S words [ihmax][32], then 32 lane-private u16 survivor lists
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int item = blockIdx.x * FAST_WARPS + warp;
     if (item >= G.bands_per_frame) return;            // warps are independent: no block-level barrier below
@@ -165,18 +171,21 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
         uint32_t W[7][8];
 #pragma unroll
         for (int i = 0; i < 6; i++) { const uint32_t* p = p0 + i * pw; fast_fill_row(W[i], __ldg(p - 1), __ldg(p), __ldg(p + 1)); }
-        // two rows in flight ahead of the window
-        const uint32_t* pa = p0 + 6 * pw;
-        uint32_t al = __ldg(pa - 1), am = __ldg(pa), ar = __ldg(pa + 1);
-        const uint32_t* pb = p0 + min(7, klast) * pw;
-        uint32_t bl = __ldg(pb - 1), bm = __ldg(pb), br = __ldg(pb + 1);
+        // three rows in flight ahead of the window, in statically indexed slots (no register moves that
+        // would wait for the loads): slot k % 7 holds window row k = r + 6 .. r + 8 at step r
+        uint32_t pf[7][3];
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            const uint32_t* pn = p0 + min(6 + i, klast) * pw;
+            pf[(6 + i) % 7][0] = __ldg(pn - 1); pf[(6 + i) % 7][1] = __ldg(pn); pf[(6 + i) % 7][2] = __ldg(pn + 1);
+        }
         uint32_t* out = s_tile + wi;
 #define FAST_STEP(PH)                                                                              \
         if (rb + PH < ih) {                                                                        \
             const int r = rb + PH;                                                                 \
-            fast_fill_row(W[(PH + 6) % 7], al, am, ar);                                            \
-            al = bl; am = bm; ar = br;                                                             \
-            { const uint32_t* pn = p0 + min(r + 8, klast) * pw; bl = __ldg(pn - 1); bm = __ldg(pn); br = __ldg(pn + 1); } \
+            fast_fill_row(W[(PH + 6) % 7], pf[(PH + 6) % 7][0], pf[(PH + 6) % 7][1], pf[(PH + 6) % 7][2]); \
+            { const uint32_t* pn = p0 + min(r + 9, klast) * pw;                                    \
+              pf[(PH + 9) % 7][0] = __ldg(pn - 1); pf[(PH + 9) % 7][1] = __ldg(pn); pf[(PH + 9) % 7][2] = __ldg(pn + 1); } \
             const uint32_t sw = fast_score_word<PH>(W);                                            \
             if (active) out[r * 32] = sw;                                                          \
         }
@@ -208,7 +217,9 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
     const int iniTh = G.iniTh, minTh = min(G.minTh, G.iniTh);
     const uint32_t thr = (uint32_t)(((minTh - 1) << 8) | 0xFF) * 0x00010001u;
     const uint32_t lt = (1u << lane) - 1u;
-    int cnt = 0;                                      // list length (warp-uniform)
+    int cnt = 0;                                      // survivors of this lane
+    const int lcap = (3 * ih) / 2 + 2;                // <= 3 strict maxima per 2 rows of a 4-px column strip (one cell boundary)
+    uint16_t* mylist = s_list + lane * lcap;
     {
         const uint32_t* sp = s_tile + wi;
         const bool hasl = active && wi > 0, hasr = active && wi + 1 < nw;
@@ -224,17 +235,12 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
             else { R[(PH + 2) % 3][0] = R[(PH + 2) % 3][1] = R[(PH + 2) % 3][2] = R[(PH + 2) % 3][3] = 0; } \
             uint32_t te, to;                                                                                \
             nms_row<PH>(R, thr, ML_e, MR_e, ML_o, MR_o, V_e, V_o, te, to);                                  \
-            if (__ballot_sync(0xffffffffu, (te | to) != 0u)) {                                              \
-                const bool k0 = (te & 0xFFFFu) != 0u, k1 = (to & 0xFFFFu) != 0u, k2 = (te >> 16) != 0u, k3 = (to >> 16) != 0u; \
-                const int c = (int)k0 + (int)k1 + (int)k2 + (int)k3;       /* <= 3: one cell boundary per word at most */ \
-                const uint32_t m0 = __ballot_sync(0xffffffffu, c & 1), m1 = __ballot_sync(0xffffffffu, c & 2); \
-                int o = cnt + __popc(m0 & lt) + 2 * __popc(m1 & lt);                                        \
-                cnt += __popc(m0) + 2 * __popc(m1);                                                         \
+            if ((te | to) != 0u) {                             /* survivors go to the lane's private list */          \
                 const int e = (r << 7) | (4 * wi);                                                          \
-                if (k0) s_list[o++] = (uint16_t)e;                                                          \
-                if (k1) s_list[o++] = (uint16_t)(e + 1);                                                    \
-                if (k2) s_list[o++] = (uint16_t)(e + 2);                                                    \
-                if (k3) s_list[o++] = (uint16_t)(e + 3);                                                    \
+                if (te & 0xFFFFu) mylist[cnt++] = (uint16_t)e;                                              \
+                if (to & 0xFFFFu) mylist[cnt++] = (uint16_t)(e + 1);                                        \
+                if (te >> 16)     mylist[cnt++] = (uint16_t)(e + 2);                                        \
+                if (to >> 16)     mylist[cnt++] = (uint16_t)(e + 3);                                        \
             }                                                                                               \
         }
 #pragma unroll 1
@@ -250,10 +256,10 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
     int nhi[FAST_MAXCELLS], nlo[FAST_MAXCELLS];        // survivors >= iniTh / in [minTh, iniTh) per cell (uniform)
 #pragma unroll
     for (int c = 0; c < FAST_MAXCELLS; c++) nhi[c] = nlo[c] = 0;
-    for (int i0 = 0; i0 < cnt; i0 += 32) {
-        const int i = i0 + lane;
+    const int maxcnt = __reduce_max_sync(0xffffffffu, cnt);
+    for (int i = 0; i < maxcnt; i++) {                 // entry i of every lane's list
         const bool valid = i < cnt;
-        const int e = valid ? s_list[i] : 0;
+        const int e = valid ? mylist[i] : 0;
         const int px = e & 127, r = e >> 7;
         const int sc = s_score[r * 128 + px];
         const int cell = (xrel + px - 3) / L.wCell - bd.cj0;
@@ -274,10 +280,9 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
     if (lane == 0) base = atomicAdd(&D.candcnt[f * G.nlevels + bd.lvl], total);
     base = __shfl_sync(0xffffffffu, base, 0);
     uint32_t* cand = D.cand + (long long)f * G.cand_per_frame + L.cand_base;
-    for (int i0 = 0; i0 < cnt; i0 += 32) {
-        const int i = i0 + lane;
+    for (int i = 0; i < maxcnt; i++) {
         const bool valid = i < cnt;
-        const int e = valid ? s_list[i] : 0;
+        const int e = valid ? mylist[i] : 0;
         const int px = e & 127, r = e >> 7;
         const int sc = s_score[r * 128 + px];
         const int cell = (xrel + px - 3) / L.wCell - bd.cj0;
@@ -321,7 +326,7 @@ int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out, int* warp_w
             }
         }
     }
-    *warp_words = ihmax * 32 + (ihmax + 1) * 16;      // S tile + u16 list of <= 32*(ih+1) survivors
+    *warp_words = ihmax * 32 + 16 * ((3 * ihmax) / 2 + 2);      // S tile + 32 lane-private u16 lists of 3*ih/2+2 survivors
     return FAST_WARPS * *warp_words * 4;
 }
 
