@@ -3,9 +3,6 @@
 // GaussianBlur call :1606-1614, computeOrbDescriptor :150-203.
 #include "orbx_internal.h"
 
-__constant__ signed char c_pattern[1024] = {
-#include "../../include/orb_pattern_31.inc"
-};
 // umax of the 31x31 circular patch (src/ORBextractor.cc:542-570); depends only on HALF_PATCH_SIZE=15
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
@@ -258,96 +255,168 @@ __device__ __forceinline__ void sincosf_glibc(float y, float* sn, float* cs)
 }
 
 #define DESC_WARPS 8
+#ifndef DESC_KPW
+#define DESC_KPW 1
+#endif
+#ifndef DESC_MINB
+#define DESC_MINB 6
+#endif
+//#define DESC_KPW_                 // keypoint slots per warp (pattern registers and masks are set up once)
 #define DESC_R 18                  // max |rotated tap| : the pattern lies inside radius 18.4
 #define DESC_ROWS (2 * DESC_R + 1)
 #define DESC_PW 11                 // words per patch row: 37 bytes at any alignment
 
-__global__ void __launch_bounds__(DESC_WARPS * 32)
+__device__ __align__(16) signed char g_pattern[1024] = {
+#include "../../include/orb_pattern_31.inc"
+};
+
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c)      // sum of u8(a) * s8(b) + c
+{
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// One warp per keypoint, DESC_KPW keypoints per warp.
+//  IC_Angle (:91-138): lane = patch row v = lane - 15; the row's 31 bytes are 8 aligned-by-funnel-shift
+//    words, masked to |u| <= umax[|v|], and reduced with two IDP.4A per word (sum of u*I with constant
+//    s8 weights, sum of I with ones); m_10 / m_01 by warp reductions.
+//  computeOrbDescriptor (:150-203): the lane's 16 tap pairs live in registers as floats; the 37x37
+//    neighbourhood of the blurred level is staged in shared memory; cvRound = add 1.5 * 2^23 (round half
+//    even, exact for |v| < 2^22); lane i builds byte i.
+__global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB)
 describe_kernel(FrameGeom G, DevBuffers D)
 {
-    __shared__ signed char s_pat[1024];
     __shared__ uint32_t s_patch[DESC_WARPS][DESC_ROWS * DESC_PW];
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_pat[i] = c_pattern[i];
-    __syncthreads();
+    __shared__ uint32_t s_raw[DESC_WARPS][ORBX_PATCH * 9];
     const int f = blockIdx.y;
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);
-    if (slot >= G.sel_per_frame) return;
-    int lvl = 0;
-#pragma unroll 1
-    for (int l = 1; l < G.nlevels; l++) if (slot >= G.L[l].sel_base) lvl = l;
-    const LevelGeom& L = G.L[lvl];
-    const int i = slot - L.sel_base;
-    if (i >= D.selcnt[f * G.nlevels + lvl]) return;
-    const uint32_t key = D.sel[(long long)f * G.sel_per_frame + slot];
-    const int x = KEY_X(key) + ORBX_MINB, y = KEY_Y(key) + ORBX_MINB;
-    const long long off = (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + y) * L.pitch + ORBX_XOFF + x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slot0 = (blockIdx.x * DESC_WARPS + warp) * DESC_KPW;
+    if (slot0 >= G.sel_per_frame) return;
 
-    // IC_Angle (:91-138): lane = u + 15
-    const uint8_t* center = L.pyr + off;
-    int m10 = 0, m01 = 0;
-    const int u = lane - ORBX_HALF_PATCH;
-    if (lane < 31) {
-        m10 = u * (int)center[u];
+    // per-lane constants: tap pattern (floats) and the disc mask of this lane's patch row
+    float pat[32];
+    {
+        const uint4* gp = reinterpret_cast<const uint4*>(g_pattern) + 2 * lane;
+        const uint4 a = gp[0], b = gp[1];
+        const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 #pragma unroll
-        for (int v = 1; v <= ORBX_HALF_PATCH; v++) {
-            if (abs(u) <= c_umax[v]) {
-                const int vp = center[u + v * L.pitch], vm = center[u - v * L.pitch];
-                m01 += v * (vp - vm);
-                m10 += u * (vp + vm);
+        for (int k = 0; k < 32; k++) pat[k] = (float)(signed char)((w[k >> 2] >> (8 * (k & 3))) & 0xFF);
+    }
+    const int v = lane - ORBX_HALF_PATCH;
+    uint32_t rmask[8];
+    {
+        const int d = lane < 31 ? c_umax[abs(v)] : -1;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            uint32_t m = 0;
+#pragma unroll
+            for (int b = 0; b < 4; b++) { const int u = -15 + 4 * j + b; if (abs(u) <= d) m |= 0xFFu << (8 * b); }
+            rmask[j] = m;
+        }
+    }
+    uint32_t* patch = s_patch[warp];
+    uint32_t* raw = s_raw[warp];
+
+#pragma unroll 1
+    for (int kk = 0; kk < DESC_KPW; kk++) {
+        const int slot = slot0 + kk;
+        if (slot >= G.sel_per_frame) break;
+        int lvl = 0;
+#pragma unroll 1
+        for (int l = 1; l < G.nlevels; l++) if (slot >= G.L[l].sel_base) lvl = l;
+        const LevelGeom& L = G.L[lvl];
+        if (slot - L.sel_base >= D.selcnt[f * G.nlevels + lvl]) continue;
+        const uint32_t key = D.sel[(long long)f * G.sel_per_frame + slot];
+        const int x = KEY_X(key) + ORBX_MINB, y = KEY_Y(key) + ORBX_MINB;
+        const int pw = L.pitch >> 2;
+
+        // ---- stage the 31x31 patch of the level (rows of 9 words) and the 37x37 patch of the blurred level
+        // (rows of 11 words) in shared memory with row-major coalesced loads: the L1 wavefront count of a
+        // keypoint is then ~1-2 per patch row instead of one per lane ----
+        const int xr = ORBX_XOFF + x - ORBX_HALF_PATCH;           // byte of u = -15 in the row
+        __syncwarp();                                             // previous keypoint's reads are done
+        {
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(
+                L.pyr + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + y - ORBX_HALF_PATCH) * L.pitch + (xr & ~3));
+            const int g = lane / 9, c = lane - g * 9;             // lanes 0..26: 3 rows of 9 words per iteration
+            if (lane < 27) {
+                const uint32_t* sp = src + g * pw + c;
+                uint32_t* dp = raw + g * 9 + c;
+#pragma unroll
+                for (int t = 0; t < 11; t++) if (3 * t + g < ORBX_PATCH) dp[3 * t * 9] = __ldg(sp + 3 * t * pw);
             }
         }
-    }
-    m10 = __reduce_add_sync(0xffffffffu, m10);
-    m01 = __reduce_add_sync(0xffffffffu, m01);
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
-
-    // computeOrbDescriptor (:150-203).  The 37x37 neighbourhood of the blurred level that the rotated
-    // taps can reach (|tap| <= 18) is staged in shared memory with coalesced word loads; the 16 taps of
-    // each lane are then byte gathers from shared memory instead of 512 scattered sectors per keypoint.
-    float a = 0.f, b = 0.f;
-    if (lane == 0) sincosf_glibc(__fmul_rn(angle, 0.017453292519943295f), &b, &a);   // factorPI = (float)(CV_PI/180.f)
-    a = __shfl_sync(0xffffffffu, a, 0);
-    b = __shfl_sync(0xffffffffu, b, 0);
-    uint32_t* patch = s_patch[threadIdx.x >> 5];
-    const int xoff = (ORBX_XOFF + x - DESC_R) & 3;                 // byte of the first patch column inside its word
-    {
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(
-            L.blur + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + y - DESC_R) * L.pitch + ((ORBX_XOFF + x - DESC_R) & ~3));
-        const int pw = L.pitch >> 2;
-#pragma unroll 4
-        for (int i = lane; i < DESC_ROWS * DESC_PW; i += 32) {
-            const int r = i / DESC_PW, c = i - r * DESC_PW;
-            patch[i] = __ldg(src + r * pw + c);
-        }
-    }
-    __syncwarp();
-    const uint8_t* bc = reinterpret_cast<const uint8_t*>(patch) + DESC_R * (DESC_PW * 4) + DESC_R + xoff;
-    const signed char* pat = s_pat + 32 * lane;
-    int val = 0;
+        {
+            const int xb = ORBX_XOFF + x - DESC_R;
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(
+                L.blur + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + y - DESC_R) * L.pitch + (xb & ~3));
+            // lanes 0..10 -> even rows, 11..21 -> odd rows; 19 iterations cover the 37 rows
+            const int g = lane >= DESC_PW ? 1 : 0, c = lane - g * DESC_PW;
+            if (lane < 2 * DESC_PW) {
+                const uint32_t* sp = src + g * pw + c;
+                uint32_t* dp = patch + g * DESC_PW + c;
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        int t[2];
-#pragma unroll
-        for (int e = 0; e < 2; e++) {
-            const float px = (float)pat[4 * k + 2 * e], py = (float)pat[4 * k + 2 * e + 1];
-            const int ry = __float2int_rn(__fadd_rn(__fmul_rn(px, b), __fmul_rn(py, a)));
-            const int rx = __float2int_rn(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, b)));
-            t[e] = bc[ry * (DESC_PW * 4) + rx];
+                for (int t = 0; t < (DESC_ROWS + 1) / 2; t++) {
+                    if (2 * t + g < DESC_ROWS) dp[2 * t * DESC_PW] = __ldg(sp + 2 * t * pw);
+                }
+            }
         }
-        val |= (t[0] < t[1]) << k;
-    }
-    const int dst = D.outidx[(long long)f * G.sel_per_frame + slot];
-    D.desc[((long long)f * G.out_cap + dst) * 32 + lane] = (uint8_t)val;
-    if (lane == 0) {
-        D.kps[(long long)f * G.out_cap + dst].angle = angle;
-        D.angle[(long long)f * G.sel_per_frame + slot] = angle;
+        __syncwarp();
+        // this lane's patch row: 9 conflict-free word reads (row pitch 9 words)
+        uint32_t rw[9];
+        {
+            const uint32_t* rp = raw + (lane < 31 ? lane : 0) * 9;
+#pragma unroll
+            for (int j = 0; j < 9; j++) rw[j] = rp[j];
+        }
+        // ---- IC_Angle ----
+        const int sh = (xr & 3) * 8;
+        int sI = 0, sUI = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const uint32_t a = __funnelshift_r(rw[j], rw[j + 1], sh) & rmask[j];     // bytes u = -15+4j .. -12+4j
+            const uint32_t uw = (uint32_t)((-15 + 4 * j) & 0xFF) | ((uint32_t)((-14 + 4 * j) & 0xFF) << 8) |
+                                ((uint32_t)((-13 + 4 * j) & 0xFF) << 16) | ((uint32_t)((-12 + 4 * j) & 0xFF) << 24);
+            sUI = dp4a_us(a, uw, sUI);
+            sI = (int)__dp4a(a, 0x01010101u, (uint32_t)sI);
+        }
+        const int m10 = __reduce_add_sync(0xffffffffu, sUI);
+        const int m01 = __reduce_add_sync(0xffffffffu, v * sI);
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
+        float a, b;
+        sincosf_glibc(__fmul_rn(angle, 0.017453292519943295f), &b, &a);   // factorPI = (float)(CV_PI/180.f)
+        // ---- descriptor byte of this lane ----
+        const int xoff = (ORBX_XOFF + x - DESC_R) & 3;
+        const uint8_t* bc = reinterpret_cast<const uint8_t*>(patch) + DESC_R * (DESC_PW * 4) + DESC_R + xoff;
+        const float MAGIC = 12582912.f;                           // 1.5 * 2^23
+        // tap address = ry * 44 + rx with r = bits(v + MAGIC) - bits(MAGIC)
+        const uint32_t abias = 0x4B400000u * (uint32_t)(DESC_PW * 4 + 1);    // wraps; the difference below is exact
+        int val = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            int t[2];
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const float px = pat[4 * k + 2 * e], py = pat[4 * k + 2 * e + 1];
+                const float fy = __fadd_rn(__fadd_rn(__fmul_rn(px, b), __fmul_rn(py, a)), MAGIC);
+                const float fx = __fadd_rn(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, b)), MAGIC);
+                t[e] = bc[(int)(__float_as_uint(fy) * (uint32_t)(DESC_PW * 4) + __float_as_uint(fx) - abias)];
+            }
+            val |= (t[0] < t[1]) << k;
+        }
+        const int dst = D.outidx[(long long)f * G.sel_per_frame + slot];
+        D.desc[((long long)f * G.out_cap + dst) * 32 + lane] = (uint8_t)val;
+        if (lane == 0) {
+            D.kps[(long long)f * G.out_cap + dst].angle = angle;
+            D.angle[(long long)f * G.sel_per_frame + slot] = angle;
+        }
     }
 }
 
 int launch_describe(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
-    const dim3 grid((G.sel_per_frame + DESC_WARPS - 1) / DESC_WARPS, nframes);
+    const dim3 grid((G.sel_per_frame + DESC_WARPS * DESC_KPW - 1) / (DESC_WARPS * DESC_KPW), nframes);
     describe_kernel<<<grid, DESC_WARPS * 32, 0, s>>>(G, D);
     return 1;
 }
