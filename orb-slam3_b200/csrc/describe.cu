@@ -131,14 +131,13 @@ __device__ __forceinline__ void blur_hrow(int (&h)[4], const uint32_t* __restric
 template <int PH>
 __device__ __forceinline__ uint32_t blur_vword(const int (&H)[7][4])
 {
-    uint32_t word = 0;
+    uint32_t acc[4];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const uint32_t acc = 18u * (uint32_t)(H[PH % 7][k] + H[(PH + 6) % 7][k]) + 34u * (uint32_t)(H[(PH + 1) % 7][k] + H[(PH + 5) % 7][k]) +
-                             48u * (uint32_t)(H[(PH + 2) % 7][k] + H[(PH + 4) % 7][k]) + 56u * (uint32_t)H[(PH + 3) % 7][k] + 32768u;
-        word |= ((acc >> 16) & 0xFFu) << (8 * k);
-    }
-    return word;
+    for (int k = 0; k < 4; k++)
+        acc[k] = 18u * (uint32_t)(H[PH % 7][k] + H[(PH + 6) % 7][k]) + 34u * (uint32_t)(H[(PH + 1) % 7][k] + H[(PH + 5) % 7][k]) +
+                 48u * (uint32_t)(H[(PH + 2) % 7][k] + H[(PH + 4) % 7][k]) + 56u * (uint32_t)H[(PH + 3) % 7][k] + 32768u;
+    // (acc >> 16) <= 255 is byte 2 of each accumulator
+    return __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
 }
 
 __global__ void __launch_bounds__(BL_BX * BL_BY)

@@ -64,7 +64,7 @@ void pyramid_fill_border(const LevelGeom& L, int frame, cudaStream_t s)
 // fast path of the resize: interior words only, taps from the 8 source bytes starting at the first
 // pixel's left tap (3 aligned word loads + 2 funnel shifts per source row, PRMT + IDP.2A per pixel)
 struct HRow4 { int h[4]; };
-__device__ __forceinline__ HRow4 pyr_hrow_fast(const uint8_t* __restrict__ S, const ResizeWord& t)
+__device__ __forceinline__ HRow4 pyr_hrow_fast(const uint8_t* __restrict__ S, const ResizeWord& t, const uint32_t (&sel)[4])
 {
     const uint32_t* p = reinterpret_cast<const uint32_t*>(S + t.wb);
     const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
@@ -72,7 +72,7 @@ __device__ __forceinline__ HRow4 pyr_hrow_fast(const uint8_t* __restrict__ S, co
     HRow4 r;
 #pragma unroll
     for (int k = 0; k < 4; k++)
-        r.h[k] = (int)(__dp2a_lo(t.a01[k], __byte_perm(lo, hi, (t.sels >> (8 * k)) & 0xFFu), 0u) >> 4);
+        r.h[k] = (int)(__dp2a_lo(t.a01[k], __byte_perm(lo, hi, sel[k]), 0u) >> 4);
     return r;
 }
 
@@ -92,6 +92,9 @@ pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long p
         const uint4 a = __ldg(reinterpret_cast<const uint4*>(tapw + wi)), b = __ldg(reinterpret_cast<const uint4*>(tapw + wi) + 1);
         t.wb = (int)a.x; t.shift = a.y; t.sels = a.z; t.a01[0] = a.w; t.a01[1] = b.x; t.a01[2] = b.y; t.a01[3] = b.z;
     }
+    uint32_t sel[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) sel[k] = (t.sels >> (8 * k)) & 0xFFu;
     const uint8_t* base = prev + (long long)f * pplane_bytes + (long long)ORBX_YOFF * ppitch + ORBX_XOFF;
     uint32_t* dst = reinterpret_cast<uint32_t*>(out + (long long)f * plane_bytes + (long long)(ORBX_YOFF + Y0) * pitch) + wi;
     const int pw = pitch >> 2;
@@ -103,16 +106,17 @@ pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long p
 #pragma unroll 2
     for (int rr = 0; rr < nr; rr++) {
         const ResizeTapY ty = tapy[ORBX_EDGE + Y0 + rr];       // the tap table is indexed by padded row
-        const HRow4 h0 = (ty.s0 == have) ? hl : pyr_hrow_fast(base + (long long)ty.s0 * ppitch, t);
-        const HRow4 h1 = (ty.s1 == ty.s0) ? h0 : pyr_hrow_fast(base + (long long)ty.s1 * ppitch, t);
-        const int b0 = ty.b0, b1 = ty.b1;
-        uint32_t word = 0;
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int v = (((b0 * h0.h[k]) >> 16) + ((b1 * h1.h[k]) >> 16) + 2) >> 2;
-            word |= (uint32_t)v << (8 * k);
-        }
-        dst[rr * pw] = word;
+        const HRow4 h0 = (ty.s0 == have) ? hl : pyr_hrow_fast(base + (long long)ty.s0 * ppitch, t, sel);
+        const HRow4 h1 = (ty.s1 == ty.s0) ? h0 : pyr_hrow_fast(base + (long long)ty.s1 * ppitch, t, sel);
+        const uint32_t b0 = (uint32_t)ty.b0, b1 = (uint32_t)ty.b1;
+        // ((b0*h0)>>16) + ((b1*h1)>>16) + 2 for two pixels per register: PRMT gathers the upper halves of
+        // the products (each < 2^27), the sums stay below 2^11 per 16-bit lane; result byte = bits 2..9
+        const uint32_t A01 = __byte_perm(b0 * (uint32_t)h0.h[0], b0 * (uint32_t)h0.h[1], 0x7632);
+        const uint32_t A23 = __byte_perm(b0 * (uint32_t)h0.h[2], b0 * (uint32_t)h0.h[3], 0x7632);
+        const uint32_t B01 = __byte_perm(b1 * (uint32_t)h1.h[0], b1 * (uint32_t)h1.h[1], 0x7632);
+        const uint32_t B23 = __byte_perm(b1 * (uint32_t)h1.h[2], b1 * (uint32_t)h1.h[3], 0x7632);
+        const uint32_t S01 = A01 + B01 + 0x00020002u, S23 = A23 + B23 + 0x00020002u;
+        dst[rr * pw] = __byte_perm(S01 >> 2, S23 >> 2, 0x6420);
         hl = h1; have = ty.s1;
     }
 }
