@@ -82,7 +82,7 @@ int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int la
 // on the symmetric kernel.  No shared memory, no barriers.
 #define BL_RT 32
 #define BL_BX 64
-#define BL_BY 2
+#define BL_BY 4
 
 // The pyramid planes carry no materialised border: BORDER_REFLECT_101 is applied while loading.  Every
 // thread rebuilds its three words with PRMT selectors computed once per thread (identity for all but
@@ -114,9 +114,8 @@ __device__ __forceinline__ BlurEdge blur_edge(int wi, int w)
     return e;
 }
 
-__device__ __forceinline__ void blur_hrow(int (&h)[4], const uint32_t* __restrict__ p, const BlurEdge& e)
+__device__ __forceinline__ void blur_hrow(int (&h)[4], uint32_t l0, uint32_t m0, uint32_t r0, const BlurEdge& e)
 {
-    const uint32_t l0 = __ldg(p - 1), m0 = __ldg(p), r0 = __ldg(p + 1);
     const uint32_t l = __byte_perm(l0, m0, e.selL), m = __byte_perm(l0, m0, e.selM);
     const uint32_t r = e.rFromLM ? __byte_perm(l0, m0, e.selR) : __byte_perm(m0, r0, e.selR);
     const uint32_t kA = 18u | (34u << 8) | (48u << 16) | (56u << 24);   // taps -3..0
@@ -140,46 +139,106 @@ __device__ __forceinline__ uint32_t blur_vword(const int (&H)[7][4])
     return __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
 }
 
-__global__ void __launch_bounds__(BL_BX * BL_BY)
-blur_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, int pitch, long long plane_bytes, int w, int h)
+__device__ __forceinline__ void cp_async4(uint32_t* smem_dst, const uint32_t* gsrc)
 {
-    const int wi = blockIdx.x * BL_BX + threadIdx.x;
-    const int y0 = (blockIdx.y * BL_BY + threadIdx.y) * BL_RT;
-    if (wi * 4 >= w || y0 >= h) return;
-    const int f = blockIdx.z;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+// One warp per (128-px column block, 32-row strip).  The rows of the strip stream through a per-warp
+// shared-memory ring filled with cp.async (LDGSTS) BL_DEPTH rows ahead: the loads need no registers and
+// never stall the issuing warp, so the memory latency overlaps the arithmetic of the rows in between.
+#define BL_RING 8
+#define BL_DEPTH 5
+#define BL_ROWW 36            // ring row: word -1, the warp's 32 words, word +32 (+ padding)
+
+__global__ void __launch_bounds__(32 * BL_BY)
+blur_kernel(FrameGeom G)
+{
+    __shared__ uint32_t s_ring[BL_BY][BL_RING][BL_ROWW];
+    const int lane = threadIdx.x, warp = threadIdx.y;
+    // all levels in one launch: blockIdx.x enumerates (level, row-strip group, 128-px column block)
+    int lvl = 0, bid = blockIdx.x;
+#pragma unroll 1
+    for (; lvl < G.nlevels - 1; lvl++) {
+        const int nb = ((G.L[lvl].w + 127) / 128) * ((G.L[lvl].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
+        if (bid < nb) break;
+        bid -= nb;
+    }
+    const LevelGeom& L = G.L[lvl];
+    const uint8_t* __restrict__ pyr = L.pyr; uint8_t* __restrict__ blur = L.blur;
+    const int pitch = L.pitch, w = L.w, h = L.h;
+    const long long plane_bytes = L.plane_bytes;
+    const int nbx = (w + 127) / 128;
+    const int by = bid / nbx, bx = bid - by * nbx;
+    const int wi0 = bx * 32, wi = wi0 + lane;
+    const int y0 = (by * BL_BY + warp) * BL_RT;
+    if (wi0 * 4 >= w || y0 >= h) return;                       // warp-uniform
+    const int f = blockIdx.y;
     const int pw = pitch >> 2;
-    // row y of the level (reflect-101 outside [0, h)), word wi
-    const uint32_t* base = reinterpret_cast<const uint32_t*>(pyr + (long long)f * plane_bytes + (long long)ORBX_YOFF * pitch + ORBX_XOFF) + wi;
-    auto rowp = [&](int y) { y = y < 0 ? -y : y; y = y >= h ? 2 * (h - 1) - y : y; return base + y * pw; };
-    uint32_t* q = reinterpret_cast<uint32_t*>(blur + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y0) * pitch + ORBX_XOFF) + wi;
-    const BlurEdge edge = blur_edge(wi, w);
-    int H[7][4];
-#pragma unroll
-    for (int i = 0; i < 6; i++) blur_hrow(H[i], rowp(y0 - 3 + i), edge);
     const int nr = min(BL_RT, h - y0);
+    const int nstream = nr + 6;                                // stream row s = image row y0 - 3 + s
+    const uint32_t* base = reinterpret_cast<const uint32_t*>(pyr + (long long)f * plane_bytes + (long long)ORBX_YOFF * pitch + ORBX_XOFF) + wi0;
+    uint32_t (*ring)[BL_ROWW] = s_ring[warp];
+    // per-lane copy addresses: every lane copies its own word, lanes 0 / 1 also the words left / right of the warp
+    const uint32_t sm_own = (uint32_t)__cvta_generic_to_shared(&ring[0][1 + lane]);
+    const uint32_t sm_halo = (uint32_t)__cvta_generic_to_shared(&ring[0][lane ? 33 : 0]);
+    const int g_halo = lane ? 32 : -1;
+    const bool reflects = (y0 < 3) || (y0 + nr + 3 > h);      // only the first / last strips leave [0, h)
+    const uint32_t* srow = base + (long long)(y0 - 3) * pw;   // running row pointer (interior strips)
+    auto issue = [&](int sr) {
+        if (sr < nstream) {
+            const uint32_t* src = srow;
+            if (reflects) {
+                int y = y0 - 3 + sr;
+                y = y < 0 ? -y : y; y = y >= h ? 2 * (h - 1) - y : y;      // reflect-101 rows
+                src = base + y * pw;
+            }
+            const uint32_t so = (uint32_t)(sr & (BL_RING - 1)) * (BL_ROWW * 4);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(sm_own + so), "l"(src + lane) : "memory");
+            if (lane < 2) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(sm_halo + so), "l"(src + g_halo) : "memory");
+            srow += pw;
+        }
+        cp_async_commit();
+    };
+    uint32_t* q = reinterpret_cast<uint32_t*>(blur + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y0) * pitch + ORBX_XOFF) + wi;
+    const bool colvalid = wi * 4 < w;
+    const BlurEdge edge = blur_edge(wi, w);
+#pragma unroll
+    for (int i = 0; i < BL_DEPTH; i++) issue(i);
+    int H[7][4];
+    int sr = 0;                                                // next stream row to consume
+#define BLUR_ROW(SLOT)                                                                    \
+    {   cp_async_wait<BL_DEPTH - 1>(); __syncwarp();                                      \
+        const uint32_t* rr = ring[sr & (BL_RING - 1)] + lane;                             \
+        const uint32_t l0 = rr[0], m0 = rr[1], r0 = rr[2];                                \
+        issue(sr + BL_DEPTH); sr++;                                                       \
+        blur_hrow(H[SLOT], l0, m0, r0, edge); }
+    BLUR_ROW(0) BLUR_ROW(1) BLUR_ROW(2) BLUR_ROW(3) BLUR_ROW(4) BLUR_ROW(5)
 #define BLUR_STEP(PH)                                                   \
     if (rb + PH < nr) {                                                 \
-        blur_hrow(H[(PH + 6) % 7], rowp(y0 + rb + PH + 3), edge);      \
-        *q = blur_vword<PH>(H); q += pw;                                \
+        BLUR_ROW((PH + 6) % 7)                                          \
+        const uint32_t vw = blur_vword<PH>(H);                          \
+        if (colvalid) *q = vw;                                          \
+        q += pw;                                                        \
     }
 #pragma unroll 1
     for (int rb = 0; rb < nr; rb += 7) {
         BLUR_STEP(0) BLUR_STEP(1) BLUR_STEP(2) BLUR_STEP(3) BLUR_STEP(4) BLUR_STEP(5) BLUR_STEP(6)
     }
 #undef BLUR_STEP
+#undef BLUR_ROW
 }
 
 int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
-    int launches = 0;
-    for (int l = 0; l < G.nlevels; l++) {
-        const LevelGeom& L = G.L[l];
-        const int ww = (L.w + 3) / 4;
-        const dim3 grid((ww + BL_BX - 1) / BL_BX, (L.h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT), nframes);
-        blur_kernel<<<grid, dim3(BL_BX, BL_BY), 0, s>>>(L.pyr, L.blur, L.pitch, L.plane_bytes, L.w, L.h);
-        launches++;
-    }
-    return launches;
+    int nblocks = 0;
+    for (int l = 0; l < G.nlevels; l++)
+        nblocks += ((G.L[l].w + 127) / 128) * ((G.L[l].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
+    blur_kernel<<<dim3(nblocks, nframes), dim3(32, BL_BY), 0, s>>>(G);
+    (void)D;
+    return 1;
 }
 
 // ------------------------------------------------------------------------------------------------
