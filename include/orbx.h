@@ -173,6 +173,68 @@ int orbx_search_by_projection(int device,
                               float th, float nnratio, int bFarPoints, float thFarPoints,
                               int32_t* assign);
 
+/* std::vector<size_t> Frame::GetFeaturesInArea(x, y, r, minLevel, maxLevel) include/Frame.h:101,
+ * src/Frame.cc:784-871 for nq windows at once, with ORBmatcher::DescriptorDistance
+ * (src/ORBmatcher.cc:2911-2931) of every hit against the query's descriptor: the candidate core shared
+ * by the windowed searches of src/ORBmatcher.cc (:831, :2533-2538).  q_r[i] < 0 skips query i.
+ * out_start[nq+1] (CSR offsets), out_idx/out_dist[cap] in the reference's visiting order.
+ * Returns the total number of candidates (ORBX_ERR_CAPACITY if it exceeds cap). */
+int orbx_window_candidates(int device, const orbx_keypoint* kps, const uint8_t* desc, int n,
+                           float minX, float maxX, float minY, float maxY,
+                           int nq, const uint8_t* q_desc, const float* q_x, const float* q_y, const float* q_r,
+                           const int32_t* q_minLevel, const int32_t* q_maxLevel,
+                           int32_t* out_start, int32_t* out_idx, int32_t* out_dist, int cap);
+
+/* int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th,
+ * const bool bMono) include/ORBmatcher.h:50, src/ORBmatcher.cc:2469-2711 (CurrentFrame.Nleft == -1).
+ * Current frame: kps/desc/uRight (NULL = mono), bounds, scale factors.  Last frame, one row per keypoint
+ * i (SoA): descriptor of its map point, the projection uv and invzc of that point in the current camera
+ * (:2508-2518, host geometry), mvKeys[i].octave, the angle used at :2584, last_valid = pMP &&
+ * !mvbOutlier[i], last_obs = pMP->Observations() > 0.  bForward/bBackward as at :2495-2496.
+ * cur_held (may be NULL): current keypoints already holding a map point with observations (:2552-2554).
+ * assign[n] out: index of the last-frame row each current keypoint is given, -1 = none.  Returns nmatches. */
+int orbx_search_by_projection_frame(int device,
+                                    const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+                                    float minX, float maxX, float minY, float maxY,
+                                    const float* scaleFactors, int nlevels,
+                                    int nlast, const uint8_t* last_desc, const float* last_u, const float* last_v,
+                                    const float* last_invz, const int32_t* last_octave, const float* last_angle,
+                                    const uint8_t* last_valid, const uint8_t* last_obs,
+                                    float th, float mbf, int bForward, int bBackward, int checkOrientation,
+                                    const uint8_t* cur_held, int32_t* assign);
+
+/* int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched,
+ * vector<int>& vnMatches12, int windowSize) include/ORBmatcher.h:71, src/ORBmatcher.cc:799-943.
+ * prev_matched[2*n1] in/out, matches12[n1] out.  Bounds are frame 2's.  Returns nmatches. */
+int orbx_search_for_initialization(int device,
+                                   const orbx_keypoint* kps1, const uint8_t* desc1, int n1,
+                                   const orbx_keypoint* kps2, const uint8_t* desc2, int n2,
+                                   float minX, float maxX, float minY, float maxY,
+                                   float* prev_matched, int windowSize, float nnratio, int checkOrientation,
+                                   int32_t* matches12);
+
+/* int ORBmatcher::SearchForTriangulation(KeyFrame*, KeyFrame*, cv::Mat F12, vector<pair<size_t,size_t>>&,
+ * bOnlyStereo, bCoarse) include/ORBmatcher.h:74, src/ORBmatcher.cc:1107-1386 (variant 0) and
+ * SearchForTriangulation_ (include/ORBmatcher.h:77, src/ORBmatcher.cc:1388-1630, variant 1: histogram factor 1/HISTO_LENGTH and no vbMatched2
+ * marking), pinhole branch (mpCamera2 == NULL).  DBoW2 FeatureVectors as CSR (fv_node ascending ids,
+ * fv_start[nn+1], fv_idx).  has_mp = GetMapPoint(idx) != NULL; uRight NULL = mono.  sf2 / sigma2_2 are
+ * pKF2's mvScaleFactors / mvLevelSigma2; ep the epipole (:1120); F12 row-major 3x3 as formed inside
+ * Pinhole::epipolarConstrain (src/CameraModels/Pinhole.cpp:243).  matches12[n1] out.  Returns nmatches. */
+int orbx_search_for_triangulation(int device,
+                                  const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
+                                  const float* uRight1,
+                                  const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                                  const orbx_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* has_mp2,
+                                  const float* uRight2,
+                                  const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                                  const float* sf2, const float* sigma2_2, int nlevels, const float* ep, const float* F12,
+                                  int bOnlyStereo, int bCoarse, int checkOrientation, int variant,
+                                  int32_t* matches12);
+
+/* void ORBmatcher::ComputeThreeMaxima(vector<int>* histo, const int L, int&, int&, int&)
+ * include/ORBmatcher.h:107, src/ORBmatcher.cc:2863-2905 on the bin sizes (host, no device work). */
+void orbx_three_maxima(const int32_t* sizes, int L, int32_t* ind1, int32_t* ind2, int32_t* ind3);
+
 #ifdef __cplusplus
 }
 #endif

@@ -115,6 +115,36 @@ int   orc_search_by_projection(const orc_grid* g, const orc_keypoint* kps, const
                                float th, float nnratio, int bFarPoints, float thFarPoints,
                                int32_t* assign);
 
+/* ORBmatcher::ComputeThreeMaxima, src/ORBmatcher.cc:2863-2905 (sizes[i] = histo[i].size()) */
+void  orc_three_maxima(const int* sizes, int L, int* ind1, int* ind2, int* ind3);
+
+/* ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th, bMono), src/ORBmatcher.cc:2469-2711,
+ * Nleft == -1 branch; see orc_match.c for the argument meaning.  Returns nmatches. */
+int   orc_search_by_projection_frame(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n,
+                                     const float* uRight, const float* scaleFactors,
+                                     int nlast, const uint8_t* last_desc, const float* last_u, const float* last_v,
+                                     const float* last_invz, const int32_t* last_octave, const float* last_angle,
+                                     const uint8_t* last_valid, const uint8_t* last_obs,
+                                     float th, float mbf, int bForward, int bBackward, int checkOrientation,
+                                     const uint8_t* cur_held, int32_t* assign);
+
+/* ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:799-943 */
+int   orc_search_for_initialization(const orc_keypoint* kps1, const uint8_t* desc1, int n1,
+                                    const orc_grid* g2, const orc_keypoint* kps2, const uint8_t* desc2, int n2,
+                                    float* prev_matched, int windowSize, float nnratio, int checkOrientation,
+                                    int32_t* matches12);
+
+/* ORBmatcher::SearchForTriangulation (:1107-1386, variant 0) / SearchForTriangulation_ (:1388-1630, variant 1) */
+int   orc_search_for_triangulation(const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
+                                   const float* uRight1,
+                                   const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                                   const orc_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* has_mp2,
+                                   const float* uRight2,
+                                   const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                                   const float* sf2, const float* sigma2_2, const float* ep, const float* F12,
+                                   int bOnlyStereo, int bCoarse, int checkOrientation, int variant,
+                                   int32_t* matches12);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,7 +1,9 @@
 /*
  * orc_match.c — ORACLE (test infrastructure): Frame::ComputeStereoMatches (src/Frame.cc:1027-1276),
  * the 64x48 frame grid (include/Frame.h:37-38, src/Frame.cc:446-480, 784-899) and
- * ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, ...) (src/ORBmatcher.cc:45-249).
+ * ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, ...) (src/ORBmatcher.cc:45-249),
+ * SearchByProjection(Frame&, const Frame&, th, bMono) (:2469-2711), SearchForInitialization (:799-943),
+ * SearchForTriangulation / SearchForTriangulation_ (:1107-1630) and ComputeThreeMaxima (:2863-2905).
  * Build with -ffp-contract=off.
  */
 #include "orc_internal.h"
@@ -12,6 +14,7 @@
 
 #define TH_HIGH 100 /* src/ORBmatcher.cc:36 */
 #define TH_LOW 50   /* :37 */
+#define HISTO_LENGTH 30 /* :38 */
 
 typedef struct { int dist, idx; } distidx;
 static int cmp_distidx(const void* a, const void* b)
@@ -138,7 +141,7 @@ void orc_stereo_match(const orc_extractor* eL, const orc_extractor* eR,
 #define GRID_COLS 64 /* include/Frame.h:38 */
 #define GRID_ROWS 48 /* include/Frame.h:37 */
 struct orc_grid {
-    float minX, minY, winv, hinv;
+    float minX, minY, maxX, maxY, winv, hinv;
     int start[GRID_COLS * GRID_ROWS + 1]; /* cell id = ix*GRID_ROWS + iy (mGrid[ix][iy]) */
     int* idx;
 };
@@ -156,7 +159,7 @@ static int pos_in_grid(const orc_grid* g, const orc_keypoint* kp, int* px, int* 
 orc_grid* orc_grid_build(const orc_keypoint* kps, int n, float minX, float maxX, float minY, float maxY)
 {
     orc_grid* g = (orc_grid*)calloc(1, sizeof(orc_grid));
-    g->minX = minX; g->minY = minY;
+    g->minX = minX; g->minY = minY; g->maxX = maxX; g->maxY = maxY;
     g->winv = (float)GRID_COLS / (float)(maxX - minX);                        /* src/Frame.cc:292 */
     g->hinv = (float)GRID_ROWS / (float)(maxY - minY);                        /* :294 */
     g->idx = (int*)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));
@@ -252,5 +255,246 @@ int orc_search_by_projection(const orc_grid* g, const orc_keypoint* kps, const u
         }
     }
     free(vIndices);
+    return nmatches;
+}
+
+/* ---- rotation histogram ---- */
+typedef struct { int* v[HISTO_LENGTH]; int n[HISTO_LENGTH], cap[HISTO_LENGTH]; } rot_hist;
+static void hist_init(rot_hist* h) { memset(h, 0, sizeof(*h)); }
+static void hist_free(rot_hist* h) { for (int i = 0; i < HISTO_LENGTH; i++) free(h->v[i]); }
+static void hist_push(rot_hist* h, int bin, int val)
+{
+    if (h->n[bin] == h->cap[bin]) {
+        h->cap[bin] = h->cap[bin] ? 2 * h->cap[bin] : 64;
+        h->v[bin] = (int*)realloc(h->v[bin], sizeof(int) * (size_t)h->cap[bin]);
+    }
+    h->v[bin][h->n[bin]++] = val;
+}
+/* the bin of one accepted pair, e.g. src/ORBmatcher.cc:895-906 (factor is each caller's own) */
+static int hist_bin(float angle1, float angle2, float factor)
+{
+    float rot = angle1 - angle2;
+    if (rot < 0.0) rot += 360.0f;
+    int bin = (int)roundf(rot * factor);
+    if (bin == HISTO_LENGTH) bin = 0;
+    return bin;
+}
+
+/* ORBmatcher::ComputeThreeMaxima, src/ORBmatcher.cc:2863-2905 */
+void orc_three_maxima(const int* sizes, int L, int* ind1, int* ind2, int* ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    *ind1 = *ind2 = *ind3 = -1;
+    for (int i = 0; i < L; i++) {
+        const int s = sizes[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; *ind3 = *ind2; *ind2 = *ind1; *ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; *ind3 = *ind2; *ind2 = i; }
+        else if (s > max3) { max3 = s; *ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { *ind2 = -1; *ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { *ind3 = -1; }
+}
+
+/* ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono),
+ * src/ORBmatcher.cc:2469-2711, branch CurrentFrame.Nleft == -1.  The projection of the last frame's map
+ * points into the current camera (:2501-2520) is the caller's: last_u/last_v = uv, last_invz = invzc.
+ * last_valid = pMP && !mvbOutlier; last_obs = pMP->Observations() > 0.  cur_held (may be NULL) marks
+ * current keypoints that already hold a map point with observations; assign[n] out = index of the last
+ * frame point each current keypoint ends with (-1 = none).  bForward/bBackward as computed at :2495-2496. */
+int orc_search_by_projection_frame(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n,
+                                   const float* uRight, const float* sf,
+                                   int nlast, const uint8_t* last_desc, const float* last_u, const float* last_v,
+                                   const float* last_invz, const int32_t* last_octave, const float* last_angle,
+                                   const uint8_t* last_valid, const uint8_t* last_obs,
+                                   float th, float mbf, int bForward, int bBackward, int checkOrientation,
+                                   const uint8_t* cur_held, int32_t* assign)
+{
+    int nmatches = 0;
+    rot_hist H; hist_init(&H);
+    const float factor = HISTO_LENGTH / 360.0f;                               /* :2480 */
+    uint8_t* held = (uint8_t*)calloc((size_t)(n > 0 ? n : 1), 1);
+    int32_t* vIndices2 = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; i++) { assign[i] = -1; if (cur_held) held[i] = cur_held[i] != 0; }
+    for (int i = 0; i < nlast; i++) {
+        if (!last_valid[i]) continue;                                         /* :2503-2506 */
+        const float invzc = last_invz[i];
+        if (invzc < 0) continue;                                              /* :2515 */
+        const float u = last_u[i], v = last_v[i];
+        if (u < g->minX || u > g->maxX) continue;                             /* :2520-2523 */
+        if (v < g->minY || v > g->maxY) continue;
+        const int nLastOctave = last_octave[i];
+        const float radius = th * sf[nLastOctave];                            /* :2529 */
+        int nc;
+        if (bForward) nc = orc_grid_query(g, kps, u, v, radius, nLastOctave, -1, vIndices2, n);
+        else if (bBackward) nc = orc_grid_query(g, kps, u, v, radius, 0, nLastOctave, vIndices2, n);
+        else nc = orc_grid_query(g, kps, u, v, radius, nLastOctave - 1, nLastOctave + 1, vIndices2, n);
+        if (nc == 0) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int k = 0; k < nc; k++) {                                        /* :2548-2574 */
+            const int i2 = vIndices2[k];
+            if (held[i2]) continue;
+            if (uRight && uRight[i2] > 0) {
+                const float ur = u - mbf * invzc;
+                const float er = fabsf(ur - uRight[i2]);
+                if (er > radius) continue;
+            }
+            const int dist = orc_hamming256(last_desc + 32 * (size_t)i, desc + 32 * (size_t)i2);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {                                            /* :2576-2601 */
+            assign[bestIdx2] = i;
+            held[bestIdx2] = last_obs[i] != 0;
+            nmatches++;
+            if (checkOrientation) hist_push(&H, hist_bin(last_angle[i], kps[bestIdx2].angle, factor), bestIdx2);
+        }
+    }
+    if (checkOrientation) {                                                   /* :2686-2708 */
+        int ind1, ind2, ind3;
+        orc_three_maxima(H.n, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int b = 0; b < HISTO_LENGTH; b++)
+            if (b != ind1 && b != ind2 && b != ind3)
+                for (int j = 0; j < H.n[b]; j++) { assign[H.v[b][j]] = -1; nmatches--; }
+    }
+    hist_free(&H); free(held); free(vIndices2);
+    return nmatches;
+}
+
+/* ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:799-943.  g2 is the grid of frame 2.
+ * prev_matched[2*n1] (x,y) in/out (vbPrevMatched), matches12[n1] out.  Returns nmatches. */
+int orc_search_for_initialization(const orc_keypoint* kps1, const uint8_t* desc1, int n1,
+                                  const orc_grid* g2, const orc_keypoint* kps2, const uint8_t* desc2, int n2,
+                                  float* prev_matched, int windowSize, float nnratio, int checkOrientation,
+                                  int32_t* matches12)
+{
+    int nmatches = 0;
+    rot_hist H; hist_init(&H);
+    const float factor = HISTO_LENGTH / 360.0f;                               /* :812 */
+    const size_t m2 = (size_t)(n2 > 0 ? n2 : 1);
+    int* vMatchedDistance = (int*)malloc(sizeof(int) * m2);
+    int* vnMatches21 = (int*)malloc(sizeof(int) * m2);
+    int32_t* vIndices2 = (int32_t*)malloc(sizeof(int32_t) * m2);
+    for (int i = 0; i < n2; i++) { vMatchedDistance[i] = INT_MAX; vnMatches21[i] = -1; }
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    for (int i1 = 0; i1 < n1; i1++) {
+        const int level1 = kps1[i1].octave;
+        if (level1 > 0) continue;                                             /* :825 */
+        const int nc = orc_grid_query(g2, kps2, prev_matched[2 * i1], prev_matched[2 * i1 + 1], (float)windowSize,
+                                      level1, level1, vIndices2, n2);         /* :831 */
+        if (nc == 0) continue;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int k = 0; k < nc; k++) {                                        /* :845-866 */
+            const int i2 = vIndices2[k];
+            const int dist = orc_hamming256(desc1 + 32 * (size_t)i1, desc2 + 32 * (size_t)i2);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= TH_LOW) {                                             /* :870-908 */
+            if (bestDist < (float)bestDist2 * nnratio) {
+                if (vnMatches21[bestIdx2] >= 0) { matches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+                matches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (checkOrientation) hist_push(&H, hist_bin(kps1[i1].angle, kps2[bestIdx2].angle, factor), i1);
+            }
+        }
+    }
+    if (checkOrientation) {                                                   /* :914-935 */
+        int ind1, ind2, ind3;
+        orc_three_maxima(H.n, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int b = 0; b < HISTO_LENGTH; b++) {
+            if (b == ind1 || b == ind2 || b == ind3) continue;
+            for (int j = 0; j < H.n[b]; j++) {
+                const int idx1 = H.v[b][j];
+                if (matches12[idx1] >= 0) { matches12[idx1] = -1; nmatches--; }
+            }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)                                           /* :939-941 */
+        if (matches12[i1] >= 0) { prev_matched[2 * i1] = kps2[matches12[i1]].x; prev_matched[2 * i1 + 1] = kps2[matches12[i1]].y; }
+    hist_free(&H); free(vMatchedDistance); free(vnMatches21); free(vIndices2);
+    return nmatches;
+}
+
+/* Pinhole::epipolarConstrain, src/CameraModels/Pinhole.cpp:237-260, with F12 (row-major 3x3) formed by the
+ * caller (K1^-T [t12]x R12 K2^-1, :243) */
+static int epipolar_ok(const float* F12, float x1, float y1, float x2, float y2, float unc)
+{
+    const float a = x1 * F12[0] + y1 * F12[3] + F12[6];
+    const float b = x1 * F12[1] + y1 * F12[4] + F12[7];
+    const float c = x1 * F12[2] + y1 * F12[5] + F12[8];
+    const float num = a * x2 + b * y2 + c;
+    const float den = a * a + b * b;
+    if (den == 0) return 0;
+    const float dsqr = num * num / den;
+    return dsqr < 3.84 * unc;
+}
+
+/* ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:1107-1386, variant 0) and SearchForTriangulation_
+ * (:1388-1630, variant 1: factor 1/HISTO_LENGTH :1441 and no vbMatched2 bookkeeping), pinhole branch
+ * (mpCamera2 == NULL).  FeatureVectors as CSR: fvN_node[nnN] ascending node ids, fvN_start[nnN+1],
+ * fvN_idx[].  has_mpN = GetMapPoint(idx) != NULL; uRightN may be NULL (all < 0 = mono).  ep = epipole in
+ * image 2 (:1120), F12 row-major.  matches12[n1] out (vMatchedPairs = the >=0 entries, ascending idx1). */
+int orc_search_for_triangulation(const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
+                                 const float* uRight1,
+                                 const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                                 const orc_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* has_mp2,
+                                 const float* uRight2,
+                                 const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                                 const float* sf2, const float* sigma2_2, const float* ep, const float* F12,
+                                 int bOnlyStereo, int bCoarse, int checkOrientation, int variant,
+                                 int32_t* matches12)
+{
+    int nmatches = 0;
+    rot_hist H; hist_init(&H);
+    const float factor = variant ? 1.0f / HISTO_LENGTH : HISTO_LENGTH / 360.0f; /* :1166 / :1441 */
+    uint8_t* vbMatched2 = (uint8_t*)calloc((size_t)(n2 > 0 ? n2 : 1), 1);
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    int a = 0, b = 0;
+    while (a < nn1 && b < nn2) {                                              /* :1176-1330 */
+        if (fv1_node[a] < fv2_node[b]) { a++; continue; }                     /* lower_bound on sorted keys */
+        if (fv1_node[a] > fv2_node[b]) { b++; continue; }
+        for (int p1 = fv1_start[a]; p1 < fv1_start[a + 1]; p1++) {
+            const int idx1 = fv1_idx[p1];
+            if (has_mp1[idx1]) continue;                                      /* :1188-1192 */
+            const int bStereo1 = uRight1 && uRight1[idx1] >= 0;               /* :1194 */
+            if (bOnlyStereo && !bStereo1) continue;
+            const orc_keypoint* kp1 = &kps1[idx1];
+            int bestDist = TH_LOW, bestIdx2 = -1;
+            for (int p2 = fv2_start[b]; p2 < fv2_start[b + 1]; p2++) {
+                const int idx2 = fv2_idx[p2];
+                if (vbMatched2[idx2] || has_mp2[idx2]) continue;              /* :1218 */
+                const int bStereo2 = uRight2 && uRight2[idx2] >= 0;
+                if (bOnlyStereo && !bStereo2) continue;
+                const int dist = orc_hamming256(desc1 + 32 * (size_t)idx1, desc2 + 32 * (size_t)idx2);
+                if (dist > TH_LOW || dist > bestDist) continue;               /* :1231 */
+                const orc_keypoint* kp2 = &kps2[idx2];
+                if (!bStereo1 && !bStereo2) {                                 /* :1241-1250 */
+                    const float distex = ep[0] - kp2->x, distey = ep[1] - kp2->y;
+                    if (distex * distex + distey * distey < 100 * sf2[kp2->octave]) continue;
+                }
+                if (epipolar_ok(F12, kp1->x, kp1->y, kp2->x, kp2->y, sigma2_2[kp2->octave]) || bCoarse) { /* :1282 */
+                    bestIdx2 = idx2; bestDist = dist;
+                }
+            }
+            if (bestIdx2 >= 0) {                                              /* :1289-1313 */
+                matches12[idx1] = bestIdx2;
+                if (!variant) vbMatched2[bestIdx2] = 1;
+                nmatches++;
+                if (checkOrientation) hist_push(&H, hist_bin(kp1->angle, kps2[bestIdx2].angle, factor), idx1);
+            }
+        }
+        a++; b++;
+    }
+    if (checkOrientation) {                                                   /* :1332-1355 */
+        int ind1, ind2, ind3;
+        orc_three_maxima(H.n, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int bi = 0; bi < HISTO_LENGTH; bi++) {
+            if (bi == ind1 || bi == ind2 || bi == ind3) continue;
+            for (int j = 0; j < H.n[bi]; j++) { matches12[H.v[bi][j]] = -1; nmatches--; }
+        }
+    }
+    hist_free(&H); free(vbMatched2);
     return nmatches;
 }

@@ -95,6 +95,17 @@ class Oracle:
                                                C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                                C.c_void_p, C.c_void_p, C.c_void_p,
                                                C.c_float, C.c_float, C.c_int, C.c_float, C.c_void_p]
+        L.orc_three_maxima.restype = None
+        L.orc_three_maxima.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_search_by_projection_frame.restype = C.c_int
+        L.orc_search_by_projection_frame.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_void_p, C.c_void_p, C.c_int] + \
+            [C.c_void_p] * 8 + [C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_search_for_initialization.restype = C.c_int
+        L.orc_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                    C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.orc_search_for_triangulation.restype = C.c_int
+        L.orc_search_for_triangulation.argtypes = ([C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int]) * 2 + \
+            [C.c_void_p] * 4 + [C.c_int] * 4 + [C.c_void_p]
 
     # ---- primitives ----
     def resize(self, src: np.ndarray, drows: int, dcols: int) -> np.ndarray:
@@ -283,3 +294,70 @@ def search_by_projection(grid: Grid, desc, uRight, scale_factors, mp: dict, th: 
                                          lv.ctypes.data, vc.ctypes.data, dp.ctypes.data, iv.ctypes.data,
                                          th, nnratio, int(far), th_far, assign.ctypes.data)
     return nm, assign
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data
+
+
+def three_maxima(o: Oracle, sizes):
+    sizes = np.ascontiguousarray(sizes, np.int32)
+    out = np.zeros(3, np.int32)
+    o.L.orc_three_maxima(sizes.ctypes.data, len(sizes), out[0:].ctypes.data, out[1:].ctypes.data, out[2:].ctypes.data)
+    return tuple(int(v) for v in out)
+
+
+def search_by_projection_frame(grid: Grid, desc, uRight, scale_factors, last: dict, th: float, mbf: float,
+                               forward: bool, backward: bool, check_orientation: bool = True, cur_held=None):
+    """last: dict of SoA arrays desc,u,v,invz,octave,angle,valid,obs (see orc_match.c)."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(grid.kps)
+    assign = np.full(n, -1, np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    ur = None if uRight is None else np.ascontiguousarray(uRight, np.float32)
+    held = None if cur_held is None else np.ascontiguousarray(cur_held, np.uint8)
+    f = lambda k, t: np.ascontiguousarray(last[k], t)
+    ld, lu, lv, lz = f("desc", np.uint8), f("u", np.float32), f("v", np.float32), f("invz", np.float32)
+    lo, la, lval, lobs = f("octave", np.int32), f("angle", np.float32), f("valid", np.uint8), f("obs", np.uint8)
+    nm = grid.L.orc_search_by_projection_frame(grid.g, grid.kps.ctypes.data, desc.ctypes.data, n, _p(ur), sf.ctypes.data,
+                                               len(lu), ld.ctypes.data, lu.ctypes.data, lv.ctypes.data, lz.ctypes.data,
+                                               lo.ctypes.data, la.ctypes.data, lval.ctypes.data, lobs.ctypes.data,
+                                               th, mbf, int(forward), int(backward), int(check_orientation),
+                                               _p(held), assign.ctypes.data)
+    return nm, assign
+
+
+def search_for_initialization(o: Oracle, kps1, desc1, grid2: Grid, desc2, prev_matched, window: int = 100,
+                              nnratio: float = 0.9, check_orientation: bool = True):
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE)
+    desc1 = np.ascontiguousarray(desc1, np.uint8)
+    desc2 = np.ascontiguousarray(desc2, np.uint8)
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.full(len(kps1), -1, np.int32)
+    nm = o.L.orc_search_for_initialization(kps1.ctypes.data, desc1.ctypes.data, len(kps1), grid2.g,
+                                           grid2.kps.ctypes.data, desc2.ctypes.data, len(grid2.kps),
+                                           pm.ctypes.data, window, nnratio, int(check_orientation), m12.ctypes.data)
+    return nm, m12, pm
+
+
+def search_for_triangulation(o: Oracle, kf1: dict, kf2: dict, sf2, sigma2_2, ep, F12, only_stereo=False, coarse=False,
+                             check_orientation=True, variant=0):
+    """kfN: dict kps, desc, has_mp, uRight (or None), fv_node, fv_start, fv_idx."""
+    def prep(k):
+        return (np.ascontiguousarray(k["kps"], KP_DTYPE), np.ascontiguousarray(k["desc"], np.uint8),
+                np.ascontiguousarray(k["has_mp"], np.uint8),
+                None if k.get("uRight") is None else np.ascontiguousarray(k["uRight"], np.float32),
+                np.ascontiguousarray(k["fv_node"], np.int32), np.ascontiguousarray(k["fv_start"], np.int32),
+                np.ascontiguousarray(k["fv_idx"], np.int32))
+    a, b = prep(kf1), prep(kf2)
+    sf2 = np.ascontiguousarray(sf2, np.float32); sg = np.ascontiguousarray(sigma2_2, np.float32)
+    ep = np.ascontiguousarray(ep, np.float32); F = np.ascontiguousarray(F12, np.float32).reshape(9)
+    m12 = np.full(len(a[0]), -1, np.int32)
+    args = []
+    for k in (a, b):
+        args += [k[0].ctypes.data, k[1].ctypes.data, len(k[0]), k[2].ctypes.data, _p(k[3]),
+                 k[4].ctypes.data, k[5].ctypes.data, k[6].ctypes.data, len(k[4])]
+    nm = o.L.orc_search_for_triangulation(*args, sf2.ctypes.data, sg.ctypes.data, ep.ctypes.data, F.ctypes.data,
+                                          int(only_stereo), int(coarse), int(check_orientation), int(variant),
+                                          m12.ctypes.data)
+    return nm, m12

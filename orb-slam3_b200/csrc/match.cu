@@ -3,7 +3,7 @@
 // ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, ...) (src/ORBmatcher.cc:45-168) over the
 // 64x48 frame grid (Frame::AssignFeaturesToGrid / GetFeaturesInArea, src/Frame.cc:446-480, 784-899).
 // Integer pipe work (XOR + POPC); no tensor cores: nothing here is a dense contraction.
-#include "orbx_host.h"
+#include "match_internal.h"
 #include <climits>
 #include <vector>
 
@@ -15,12 +15,6 @@
             rc = ORBX_ERR_CUDA; goto done;                                                     \
         }                                                                                      \
     } while (0)
-
-__device__ __forceinline__ int ham256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
-{
-    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
-}
 
 // ---- brute-force 2-NN: one thread per query, train rows broadcast from shared memory ----
 #define KNN_THREADS 128
@@ -78,11 +72,7 @@ done:
 }
 
 // ---- frame grid + SearchByProjection ----
-#define GRID_COLS 64
-#define GRID_ROWS 48
-#define GRID_CELLS (GRID_COLS * GRID_ROWS)
 #define PROJ_KMAX 256
-#define TH_HIGH 100
 
 struct ProjArgs {
     const orbx_keypoint* kps; const uint4* desc; int n; const float* uRight;
@@ -103,7 +93,7 @@ struct ProjArgs {
 
 // Frame::AssignFeaturesToGrid (src/Frame.cc:446-480) + PosInGrid (:883-899): CSR, insertion order kept
 __global__ void __launch_bounds__(1024)
-grid_build_kernel(ProjArgs A)
+grid_build_kernel(GridArgs A)
 {
     __shared__ int s_cnt[GRID_CELLS + 1];
     __shared__ int s_warp[32];
@@ -147,6 +137,8 @@ grid_build_kernel(ProjArgs A)
         }
     }
 }
+
+void orbx_launch_grid_build(const GridArgs& g, cudaStream_t stream) { grid_build_kernel<<<1, 1024, 0, stream>>>(g); }
 
 // candidate lists in the reference's visiting order (GetFeaturesInArea, src/Frame.cc:784-871) with the
 // gates that do not depend on earlier assignments (src/ORBmatcher.cc:57-117) and the Hamming distance.
@@ -327,7 +319,12 @@ extern "C" int orbx_search_by_projection(int device,
     A.hinv = (float)GRID_ROWS / (float)(maxY - minY);                     // :294
     for (int l = 0; l < nlevels; l++) A.sf[l] = scaleFactors[l];
     A.th = th; A.nnratio = nnratio; A.bFar = bFarPoints; A.thFar = thFarPoints;
-    grid_build_kernel<<<1, 1024, 0, s>>>(A);
+    {
+        GridArgs g;
+        g.kps = A.kps; g.n = n; g.minX = A.minX; g.minY = A.minY; g.winv = A.winv; g.hinv = A.hinv;
+        g.cell_start = A.cell_start; g.cell_idx = A.cell_idx;
+        orbx_launch_grid_build(g, s);
+    }
     proj_candidates_kernel<<<(nmp + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32, 0, s>>>(A);
     proj_resolve_kernel<<<1, 1024, 0, s>>>(A);
     CUDA_TRYM(cudaGetLastError());

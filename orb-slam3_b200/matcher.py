@@ -1,4 +1,5 @@
-"""Python mirrors of Frame::ComputeStereoMatches, BFMatcher kNN and ORBmatcher::SearchByProjection
+"""Python mirrors of Frame::ComputeStereoMatches, BFMatcher kNN and the ORBmatcher searches
+(SearchByProjection x2, SearchForInitialization, SearchForTriangulation[_], ComputeThreeMaxima)
 on the C ABI (include/orbx.h).  All compute happens in liborbx.so on the GPU."""
 from __future__ import annotations
 
@@ -57,3 +58,90 @@ def SearchByProjection(kps, desc, uRight, bounds, scale_factors, mp: dict, th: f
         len(px), md.ctypes.data, px.ctypes.data, py.ctypes.data, pxr.ctypes.data, lv.ctypes.data, vc.ctypes.data,
         dp.ctypes.data, iv.ctypes.data, th, nnratio, int(far), th_far, assign.ctypes.data))
     return nm, assign
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data
+
+
+def GetFeaturesInArea(kps, desc, bounds, q_desc, q_x, q_y, q_r, q_min, q_max, cap: int | None = None, device: int = 0):
+    """Frame::GetFeaturesInArea (src/Frame.cc:784-871) for many windows + DescriptorDistance of every hit.
+    Returns (start[nq+1], idx, dist)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE); desc = np.ascontiguousarray(desc, np.uint8)
+    qd = np.ascontiguousarray(q_desc, np.uint8)
+    qx, qy, qr = (np.ascontiguousarray(a, np.float32) for a in (q_x, q_y, q_r))
+    qmin, qmax = (np.ascontiguousarray(a, np.int32) for a in (q_min, q_max))
+    nq = len(qx)
+    cap = max(1, nq * max(1, len(kps))) if cap is None else cap
+    start = np.zeros(nq + 1, np.int32); idx = np.empty(cap, np.int32); dist = np.empty(cap, np.int32)
+    tot = check(binding.load().orbx_window_candidates(
+        device, kps.ctypes.data, desc.ctypes.data, len(kps), bounds[0], bounds[1], bounds[2], bounds[3],
+        nq, qd.ctypes.data, qx.ctypes.data, qy.ctypes.data, qr.ctypes.data, qmin.ctypes.data, qmax.ctypes.data,
+        start.ctypes.data, idx.ctypes.data, dist.ctypes.data, cap))
+    return start, idx[:tot].copy(), dist[:tot].copy()
+
+
+def SearchByProjectionFrame(kps, desc, uRight, bounds, scale_factors, last: dict, th: float, mbf: float,
+                            forward: bool, backward: bool, check_orientation: bool = True, cur_held=None, device: int = 0):
+    """ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th, bMono) (src/ORBmatcher.cc:2469).
+    last: SoA dict desc,u,v,invz,octave,angle,valid,obs.  Returns (nmatches, assign)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE); desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(kps)
+    assign = np.full(n, -1, np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    ur = None if uRight is None else np.ascontiguousarray(uRight, np.float32)
+    held = None if cur_held is None else np.ascontiguousarray(cur_held, np.uint8)
+    f = lambda k, t: np.ascontiguousarray(last[k], t)
+    ld, lu, lv, lz = f("desc", np.uint8), f("u", np.float32), f("v", np.float32), f("invz", np.float32)
+    lo, la, lval, lobs = f("octave", np.int32), f("angle", np.float32), f("valid", np.uint8), f("obs", np.uint8)
+    nm = check(binding.load().orbx_search_by_projection_frame(
+        device, kps.ctypes.data, desc.ctypes.data, n, _p(ur), bounds[0], bounds[1], bounds[2], bounds[3],
+        sf.ctypes.data, len(sf), len(lu), ld.ctypes.data, lu.ctypes.data, lv.ctypes.data, lz.ctypes.data,
+        lo.ctypes.data, la.ctypes.data, lval.ctypes.data, lobs.ctypes.data,
+        th, mbf, int(forward), int(backward), int(check_orientation), _p(held), assign.ctypes.data))
+    return nm, assign
+
+
+def SearchForInitialization(kps1, desc1, kps2, desc2, bounds, prev_matched, window: int = 100, nnratio: float = 0.9,
+                            check_orientation: bool = True, device: int = 0):
+    """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:799).  Returns (nmatches, matches12, prev_matched)."""
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); desc1 = np.ascontiguousarray(desc1, np.uint8)
+    kps2 = np.ascontiguousarray(kps2, KP_DTYPE); desc2 = np.ascontiguousarray(desc2, np.uint8)
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.full(len(kps1), -1, np.int32)
+    nm = check(binding.load().orbx_search_for_initialization(
+        device, kps1.ctypes.data, desc1.ctypes.data, len(kps1), kps2.ctypes.data, desc2.ctypes.data, len(kps2),
+        bounds[0], bounds[1], bounds[2], bounds[3], pm.ctypes.data, window, nnratio, int(check_orientation), m12.ctypes.data))
+    return nm, m12, pm
+
+
+def SearchForTriangulation(kf1: dict, kf2: dict, sf2, sigma2_2, ep, F12, only_stereo: bool = False, coarse: bool = False,
+                           check_orientation: bool = True, variant: int = 0, device: int = 0):
+    """ORBmatcher::SearchForTriangulation (variant 0, src/ORBmatcher.cc:1107) / SearchForTriangulation_ (variant 1,
+    :1388).  kfN: dict kps, desc, has_mp, uRight (or None), fv_node, fv_start, fv_idx.  Returns (nmatches, matches12)."""
+    def prep(k):
+        return (np.ascontiguousarray(k["kps"], KP_DTYPE), np.ascontiguousarray(k["desc"], np.uint8),
+                np.ascontiguousarray(k["has_mp"], np.uint8),
+                None if k.get("uRight") is None else np.ascontiguousarray(k["uRight"], np.float32),
+                np.ascontiguousarray(k["fv_node"], np.int32), np.ascontiguousarray(k["fv_start"], np.int32),
+                np.ascontiguousarray(k["fv_idx"], np.int32))
+    a, b = prep(kf1), prep(kf2)
+    sf2 = np.ascontiguousarray(sf2, np.float32); sg = np.ascontiguousarray(sigma2_2, np.float32)
+    ep = np.ascontiguousarray(ep, np.float32); F = np.ascontiguousarray(F12, np.float32).reshape(9)
+    m12 = np.full(len(a[0]), -1, np.int32)
+    args = []
+    for k in (a, b):
+        args += [k[0].ctypes.data, k[1].ctypes.data, len(k[0]), k[2].ctypes.data, _p(k[3]),
+                 k[4].ctypes.data, k[5].ctypes.data, k[6].ctypes.data, len(k[4])]
+    nm = check(binding.load().orbx_search_for_triangulation(
+        device, *args, sf2.ctypes.data, sg.ctypes.data, len(sf2), ep.ctypes.data, F.ctypes.data,
+        int(only_stereo), int(coarse), int(check_orientation), int(variant), m12.ctypes.data))
+    return nm, m12
+
+
+def ComputeThreeMaxima(sizes):
+    """ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:2863) on the bin sizes."""
+    sizes = np.ascontiguousarray(sizes, np.int32)
+    out = np.zeros(3, np.int32)
+    binding.load().orbx_three_maxima(sizes.ctypes.data, len(sizes), out[0:].ctypes.data, out[1:].ctypes.data, out[2:].ctypes.data)
+    return tuple(int(v) for v in out)

@@ -1,0 +1,194 @@
+"""GPU parity (through the C ABI) for the guided searches of src/ORBmatcher.cc:
+GetFeaturesInArea windows, SearchByProjection(Frame,Frame), SearchForInitialization and
+SearchForTriangulation[_], each against the oracle restatement on the same seeded inputs.  Bar: identical
+match vectors and counts (integer work; the float gates are evaluated operation by operation)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SF = np.cumprod(np.concatenate([[1.0], np.full(7, 1.2)])).astype(np.float32)
+SIGMA2 = (SF * SF).astype(np.float32)
+
+
+def _flip(rng, d, lo, hi):
+    bits = np.unpackbits(d, axis=1)
+    for i in range(len(d)):
+        k = int(rng.integers(lo, hi + 1))
+        bits[i, rng.choice(256, k, replace=False)] ^= 1
+    return np.packbits(bits, axis=1)
+
+
+def _frame(pkg, rng, n, rows, cols, pool=None, quant=1.0):
+    """n random keypoints; descriptors drawn from a small pool (+ a few flipped bits) so that equal
+    distances and repeated best candidates occur."""
+    kps = np.zeros(n, pkg.KP_DTYPE)
+    kps["x"] = np.round(rng.uniform(0, cols, n) / quant) * quant
+    kps["y"] = np.round(rng.uniform(0, rows, n) / quant) * quant
+    kps["octave"] = rng.choice(8, n, p=[.3, .22, .16, .12, .08, .06, .04, .02])
+    kps["angle"] = rng.uniform(0, 360, n).astype(np.float32)
+    kps["size"] = 31.0 * SF[kps["octave"]]
+    kps["class_id"] = -1
+    if pool is None:
+        pool = rng.integers(0, 256, (max(8, n // 6), 32), dtype=np.uint8)
+    src = rng.integers(0, len(pool), n)
+    desc = _flip(rng, pool[src].copy(), 0, 12)
+    return kps, desc, pool, src
+
+
+def _moved(pkg, rng, kps, desc, rows, cols, shift=(4.0, -3.0), jitter=2.0, flips=(0, 40)):
+    """A second view of the same points: shifted and jittered positions, noisy descriptors/angles."""
+    n = len(kps)
+    k2 = kps.copy()
+    k2["x"] = np.clip(kps["x"] + shift[0] + rng.normal(0, jitter, n), 0, cols - 1).astype(np.float32)
+    k2["y"] = np.clip(kps["y"] + shift[1] + rng.normal(0, jitter, n), 0, rows - 1).astype(np.float32)
+    k2["octave"] = np.clip(kps["octave"] + rng.choice([-1, 0, 0, 0, 1], n), 0, 7)
+    ang = kps["angle"] + np.where(rng.random(n) < 0.8, rng.normal(0, 4, n), rng.uniform(0, 360, n))
+    k2["angle"] = np.mod(ang, 360).astype(np.float32)
+    d2 = _flip(rng, desc.copy(), *flips)
+    perm = rng.permutation(n)
+    return k2[perm], d2[perm], perm
+
+
+@pytest.mark.parametrize("n,nq,seed", [(1200, 900, 1), (3000, 64, 2), (40, 500, 3), (0, 10, 4)])
+def test_window_candidates(pkg, orc, oracle, n, nq, seed):
+    rng = np.random.default_rng(seed)
+    rows, cols = 480, 752
+    kps, desc, _, _ = _frame(pkg, rng, n, rows, cols)
+    qd = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    qx = rng.uniform(-40, cols + 40, nq).astype(np.float32); qy = rng.uniform(-40, rows + 40, nq).astype(np.float32)
+    qr = rng.choice([3.0, 7.5, 15.0, 100.0, -1.0, 0.0, 2000.0], nq).astype(np.float32)
+    qmin = rng.integers(-1, 6, nq).astype(np.int32)
+    qmax = np.where(rng.random(nq) < 0.3, -1, qmin + rng.integers(0, 3, nq)).astype(np.int32)
+    start, idx, dist = pkg.GetFeaturesInArea(kps, desc, (0.0, float(cols), 0.0, float(rows)), qd, qx, qy, qr, qmin, qmax)
+    g = orc.Grid(oracle, kps, 0.0, float(cols), 0.0, float(rows))
+    tot = 0
+    for q in range(nq):
+        ref = g.query(float(qx[q]), float(qy[q]), float(qr[q]), int(qmin[q]), int(qmax[q])) if qr[q] >= 0 else np.zeros(0, np.int32)
+        got = idx[start[q]:start[q + 1]]
+        assert np.array_equal(got, ref), f"query {q}"
+        for k, i2 in enumerate(ref):
+            assert dist[start[q] + k] == oracle.hamming(qd[q], desc[i2])
+        tot += len(ref)
+    assert start[nq] == tot
+    if n >= 1000:
+        assert tot > 1000
+
+
+def test_window_candidates_capacity(pkg):
+    rng = np.random.default_rng(0)
+    kps, desc, _, _ = _frame(pkg, rng, 500, 480, 752)
+    one = np.ones(4, np.float32)
+    with pytest.raises(pkg.OrbxError):
+        pkg.GetFeaturesInArea(kps, desc, (0.0, 752.0, 0.0, 480.0), desc[:4], 300 * one, 200 * one, 500 * one,
+                              -np.ones(4, np.int32), -np.ones(4, np.int32), cap=16)
+
+
+@pytest.mark.parametrize("stereo,direction,orient,seed", [(True, "none", True, 11), (True, "forward", True, 12),
+                                                          (True, "backward", False, 13), (False, "none", True, 14)])
+def test_search_by_projection_frame(pkg, orc, oracle, stereo, direction, orient, seed):
+    """TrackWithMotionModel's matcher (th = 15 mono / 7 stereo, src/Tracking.cc)."""
+    rng = np.random.default_rng(seed)
+    rows, cols = 480, 752
+    n = 1500
+    lkps, ldesc, _, _ = _frame(pkg, rng, n, rows, cols)
+    ckps, cdesc, perm = _moved(pkg, rng, lkps, ldesc, rows, cols)
+    uR = None
+    if stereo:
+        uR = np.where(rng.random(n) < 0.7, ckps["x"] - rng.uniform(1, 40, n), -1).astype(np.float32)
+    invz = np.where(rng.random(n) < 0.97, rng.uniform(0.02, 0.5, n), -0.1).astype(np.float32)
+    last = dict(desc=_flip(rng, ldesc.copy(), 0, 10),
+                u=(lkps["x"] + 4.0 + rng.normal(0, 3, n)).astype(np.float32),
+                v=(lkps["y"] - 3.0 + rng.normal(0, 3, n)).astype(np.float32),
+                invz=invz, octave=lkps["octave"].astype(np.int32), angle=lkps["angle"],
+                valid=(rng.random(n) < 0.85).astype(np.uint8), obs=(rng.random(n) < 0.9).astype(np.uint8))
+    held = (rng.random(n) < 0.03).astype(np.uint8)
+    th, mbf = (7.0, 40.0) if stereo else (15.0, 0.0)
+    fwd, bwd = direction == "forward", direction == "backward"
+    bounds = (0.0, float(cols), 0.0, float(rows))
+    g = orc.Grid(oracle, ckps, *bounds)
+    nm_o, as_o = orc.search_by_projection_frame(g, cdesc, uR, SF, last, th, mbf, fwd, bwd, orient, held)
+    nm_g, as_g = pkg.SearchByProjectionFrame(ckps, cdesc, uR, bounds, SF, last, th, mbf, fwd, bwd, orient, held)
+    assert nm_o > 150
+    assert nm_g == nm_o
+    assert np.array_equal(as_g, as_o), f"{np.sum(as_g != as_o)} assignments differ"
+
+
+@pytest.mark.parametrize("window,orient,seed", [(100, True, 21), (100, False, 22), (30, True, 23)])
+def test_search_for_initialization(pkg, orc, oracle, window, orient, seed):
+    rng = np.random.default_rng(seed)
+    rows, cols = 480, 752
+    n = 2000
+    k1, d1, _, _ = _frame(pkg, rng, n, rows, cols, quant=1.0)
+    k2, d2, perm = _moved(pkg, rng, k1, d1, rows, cols, shift=(12.0, 5.0), flips=(0, 30))
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    bounds = (0.0, float(cols), 0.0, float(rows))
+    g2 = orc.Grid(oracle, k2, *bounds)
+    nm_o, m_o, pm_o = orc.search_for_initialization(oracle, k1, d1, g2, d2, prev, window, 0.9, orient)
+    nm_g, m_g, pm_g = pkg.SearchForInitialization(k1, d1, k2, d2, bounds, prev, window, 0.9, orient)
+    assert nm_o > 50
+    assert nm_g == nm_o == int(np.sum(m_o >= 0))
+    assert np.array_equal(m_g, m_o)
+    assert np.array_equal(pm_g, pm_o)
+    # second round feeds the updated vbPrevMatched back, as Tracking::MonocularInitialization does
+    nm_o2, m_o2, pm_o2 = orc.search_for_initialization(oracle, k1, d1, g2, d2, pm_o, window, 0.9, orient)
+    nm_g2, m_g2, pm_g2 = pkg.SearchForInitialization(k1, d1, k2, d2, bounds, pm_g, window, 0.9, orient)
+    assert nm_g2 == nm_o2 and np.array_equal(m_g2, m_o2) and np.array_equal(pm_g2, pm_o2)
+
+
+def _feature_vector(rng, node_of, drop=0.0):
+    """CSR FeatureVector: node id -> keypoint indices in ascending index order (DBoW2 push_back order)."""
+    keep = rng.random(len(node_of)) >= drop
+    nodes = np.unique(node_of[keep])
+    start = [0]; idx = []
+    for nd in nodes:
+        m = np.nonzero((node_of == nd) & keep)[0]
+        idx.extend(m.tolist()); start.append(len(idx))
+    return nodes.astype(np.int32), np.array(start, np.int32), np.array(idx, np.int32)
+
+
+@pytest.mark.parametrize("variant,only_stereo,coarse,stereo,seed", [(0, False, False, False, 31), (0, False, False, True, 32),
+                                                                  (1, False, False, True, 33), (0, True, False, True, 34),
+                                                                  (0, False, True, False, 35), (1, False, True, False, 36)])
+def test_search_for_triangulation(pkg, orc, oracle, variant, only_stereo, coarse, stereo, seed):
+    rng = np.random.default_rng(seed)
+    rows, cols = 480, 752
+    n = 1800
+    k1, d1, pool, src = _frame(pkg, rng, n, rows, cols)
+    # second keyframe: pure sideways translation -> horizontal epipolar lines, F12 = [t]x up to K
+    k2, d2, perm = _moved(pkg, rng, k1, d1, rows, cols, shift=(-18.0, 0.0), jitter=0.8, flips=(0, 45))
+    fx = fy = 458.0; cx, cy = 367.0, 248.0
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1.0]])
+    t12 = np.array([0.11, 0.002, -0.004]); tx = np.array([[0, -t12[2], t12[1]], [t12[2], 0, -t12[0]], [-t12[1], t12[0], 0]])
+    F12 = (np.linalg.inv(K).T @ tx @ np.eye(3) @ np.linalg.inv(K)).astype(np.float32)
+    ep = np.array([cx + 120.0, cy - 15.0], np.float32)            # an epipole inside the image exercises :1241-1250
+    node1 = (src % 97).astype(np.int32); node2 = node1[perm]
+    wrong = rng.random(n) < 0.05
+    node2 = np.where(wrong, rng.integers(0, 97, n), node2).astype(np.int32)
+    kf1 = dict(kps=k1, desc=d1, has_mp=(rng.random(n) < 0.35).astype(np.uint8), uRight=None)
+    kf2 = dict(kps=k2, desc=d2, has_mp=(rng.random(n) < 0.35).astype(np.uint8), uRight=None)
+    if stereo:
+        kf1["uRight"] = np.where(rng.random(n) < 0.5, k1["x"] - 10, -1).astype(np.float32)
+        kf2["uRight"] = np.where(rng.random(n) < 0.5, k2["x"] - 10, -1).astype(np.float32)
+    kf1["fv_node"], kf1["fv_start"], kf1["fv_idx"] = _feature_vector(rng, node1, 0.02)
+    kf2["fv_node"], kf2["fv_start"], kf2["fv_idx"] = _feature_vector(rng, node2, 0.02)
+    nm_o, m_o = orc.search_for_triangulation(oracle, kf1, kf2, SF, SIGMA2, ep, F12, only_stereo, coarse, True, variant)
+    nm_g, m_g = pkg.SearchForTriangulation(kf1, kf2, SF, SIGMA2, ep, F12, only_stereo, coarse, True, variant)
+    assert nm_o > (5 if only_stereo else 40), nm_o
+    assert nm_g == nm_o
+    assert np.array_equal(m_g, m_o), f"{np.sum(m_g != m_o)} matches differ"
+    nm_o2, m_o2 = orc.search_for_triangulation(oracle, kf1, kf2, SF, SIGMA2, ep, F12, only_stereo, coarse, False, variant)
+    nm_g2, m_g2 = pkg.SearchForTriangulation(kf1, kf2, SF, SIGMA2, ep, F12, only_stereo, coarse, False, variant)
+    assert nm_g2 == nm_o2 and np.array_equal(m_g2, m_o2)
+
+
+def test_search_empty_inputs(pkg):
+    z = np.zeros(0, pkg.KP_DTYPE); zd = np.zeros((0, 32), np.uint8)
+    rng = np.random.default_rng(1)
+    k, d, _, _ = _frame(pkg, rng, 50, 480, 752)
+    b = (0.0, 752.0, 0.0, 480.0)
+    last = dict(desc=zd, u=[], v=[], invz=[], octave=[], angle=[], valid=[], obs=[])
+    assert pkg.SearchByProjectionFrame(k, d, None, b, SF, last, 15.0, 0.0, False, False)[0] == 0
+    assert pkg.SearchForInitialization(z, zd, k, d, b, np.zeros((0, 2), np.float32))[0] == 0
+    nm, m12, _ = pkg.SearchForInitialization(k, d, z, zd, b, np.zeros((50, 2), np.float32))
+    assert nm == 0 and np.all(m12 == -1)
