@@ -4,6 +4,7 @@
 #pragma once
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "ORBextractor.h"
@@ -14,6 +15,11 @@ struct ORBmatcherGPU {
     static const int TH_LOW = 50;       // src/ORBmatcher.cc:37
     static const int TH_HIGH = 100;     // src/ORBmatcher.cc:36
     static const int HISTO_LENGTH = 30; // src/ORBmatcher.cc:38
+
+    // ORBmatcher::ORBmatcher(float nnratio = 0.6, bool checkOri = true), include/ORBmatcher.h:39, src/ORBmatcher.cc:40
+    explicit ORBmatcherGPU(float nnratio = 0.6f, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+    float mfNNratio;
+    bool mbCheckOrientation;
 
     // static int ORBmatcher::DescriptorDistance(const cv::Mat&, const cv::Mat&), include/ORBmatcher.h:42
     static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return orbx_hamming256(a.data, b.data); }
@@ -66,6 +72,117 @@ struct ORBmatcherGPU {
             bFarPoints ? 1 : 0, thFarPoints, assign.data());
         if (r < 0) throw std::runtime_error(std::string("SearchByProjection: ") + orbx_last_error());
         return r;
+    }
+
+    // View of the frame fields the guided searches read (mono / rectified stereo, Nleft == -1).
+    struct FrameView {
+        const std::vector<cv::KeyPoint>* mvKeysUn; const cv::Mat* mDescriptors;
+        const std::vector<float>* mvuRight;            // nullptr = monocular
+        float mnMinX, mnMaxX, mnMinY, mnMaxY;          // Frame::ComputeImageBounds, src/Frame.cc:978-1009
+        const std::vector<float>* mvScaleFactors;
+        int N() const { return (int)mvKeysUn->size(); }
+        const orbx_keypoint* kps() const { return reinterpret_cast<const orbx_keypoint*>(mvKeysUn->data()); }
+    };
+
+    // Rows of the last frame as SearchByProjection(Frame&, const Frame&, ...) visits them: map point
+    // descriptor, projection into the current camera (src/ORBmatcher.cc:2508-2518), octave, angle, flags.
+    struct LastFrameSoA {
+        std::vector<uint8_t> desc;                     // n x 32
+        std::vector<float> u, v, invz, angle;
+        std::vector<int32_t> octave;
+        std::vector<uint8_t> valid, obs;               // pMP && !mvbOutlier[i] ; pMP->Observations() > 0
+    };
+
+    // int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono)
+    // include/ORBmatcher.h:50, src/ORBmatcher.cc:2469-2711.  assign[i] = row of `last` now held by keypoint i.
+    int SearchByProjection(const FrameView& CurrentFrame, const LastFrameSoA& last, float th, float mbf,
+                           bool bForward, bool bBackward, const std::vector<uint8_t>* curHeld,
+                           std::vector<int32_t>& assign, int device = 0) const
+    {
+        const int n = CurrentFrame.N();
+        assign.assign((size_t)n, -1);
+        const int r = orbx_search_by_projection_frame(
+            device, CurrentFrame.kps(), CurrentFrame.mDescriptors->data, n,
+            CurrentFrame.mvuRight ? CurrentFrame.mvuRight->data() : nullptr,
+            CurrentFrame.mnMinX, CurrentFrame.mnMaxX, CurrentFrame.mnMinY, CurrentFrame.mnMaxY,
+            CurrentFrame.mvScaleFactors->data(), (int)CurrentFrame.mvScaleFactors->size(),
+            (int)last.u.size(), last.desc.data(), last.u.data(), last.v.data(), last.invz.data(), last.octave.data(),
+            last.angle.data(), last.valid.data(), last.obs.data(), th, mbf, bForward ? 1 : 0, bBackward ? 1 : 0,
+            mbCheckOrientation ? 1 : 0, curHeld ? curHeld->data() : nullptr, assign.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchByProjection(Frame,Frame): ") + orbx_last_error());
+        return r;
+    }
+
+    // int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched,
+    // vector<int>& vnMatches12, int windowSize = 10)  include/ORBmatcher.h:71, src/ORBmatcher.cc:799-943
+    int SearchForInitialization(const FrameView& F1, const FrameView& F2, std::vector<cv::Point2f>& vbPrevMatched,
+                                std::vector<int>& vnMatches12, int windowSize = 10, int device = 0) const
+    {
+        static_assert(sizeof(cv::Point2f) == 8, "Point2f is two floats");
+        vnMatches12.assign((size_t)F1.N(), -1);
+        const int r = orbx_search_for_initialization(
+            device, F1.kps(), F1.mDescriptors->data, F1.N(), F2.kps(), F2.mDescriptors->data, F2.N(),
+            F2.mnMinX, F2.mnMaxX, F2.mnMinY, F2.mnMaxY, reinterpret_cast<float*>(vbPrevMatched.data()), windowSize,
+            mfNNratio, mbCheckOrientation ? 1 : 0, vnMatches12.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchForInitialization: ") + orbx_last_error());
+        return r;
+    }
+
+    // View of a keyframe for SearchForTriangulation: the DBoW2::FeatureVector flattened to CSR.
+    struct KeyFrameView {
+        const std::vector<cv::KeyPoint>* mvKeysUn; const cv::Mat* mDescriptors;
+        const std::vector<float>* mvuRight;            // nullptr = monocular
+        std::vector<uint8_t> hasMapPoint;              // GetMapPoint(idx) != NULL
+        std::vector<int32_t> fvNode, fvStart, fvIdx;   // mFeatVec: ascending node ids, CSR offsets, keypoint indices
+        const std::vector<float>* mvScaleFactors; const std::vector<float>* mvLevelSigma2;
+        // flatten any ordered map<node id, vector<unsigned>> (DBoW2::FeatureVector)
+        template <class FeatVec> void SetFeatVec(const FeatVec& fv)
+        {
+            fvNode.clear(); fvIdx.clear(); fvStart.assign(1, 0);
+            for (const auto& kv : fv) {
+                fvNode.push_back((int32_t)kv.first);
+                for (auto i : kv.second) fvIdx.push_back((int32_t)i);
+                fvStart.push_back((int32_t)fvIdx.size());
+            }
+        }
+    };
+
+    // int ORBmatcher::SearchForTriangulation(KeyFrame*, KeyFrame*, cv::Mat F12, vector<pair<size_t,size_t>>&,
+    // bOnlyStereo, bCoarse) include/ORBmatcher.h:74, src/ORBmatcher.cc:1107-1386; underscore = true selects
+    // SearchForTriangulation_ (include/ORBmatcher.h:77, :1388-1630).  ep = epipole of KF1 in KF2 (:1120),
+    // F12 = the matrix Pinhole::epipolarConstrain forms (src/CameraModels/Pinhole.cpp:243), row-major.
+    int SearchForTriangulation(const KeyFrameView& KF1, const KeyFrameView& KF2, const float F12[9], const float ep[2],
+                               std::vector<std::pair<size_t, size_t>>& vMatchedPairs, bool bOnlyStereo, bool bCoarse = false,
+                               bool underscore = false, int device = 0) const
+    {
+        const int n1 = (int)KF1.mvKeysUn->size(), n2 = (int)KF2.mvKeysUn->size();
+        std::vector<int32_t> m12((size_t)n1, -1);
+        const int r = orbx_search_for_triangulation(
+            device, reinterpret_cast<const orbx_keypoint*>(KF1.mvKeysUn->data()), KF1.mDescriptors->data, n1,
+            KF1.hasMapPoint.data(), KF1.mvuRight ? KF1.mvuRight->data() : nullptr,
+            KF1.fvNode.data(), KF1.fvStart.data(), KF1.fvIdx.data(), (int)KF1.fvNode.size(),
+            reinterpret_cast<const orbx_keypoint*>(KF2.mvKeysUn->data()), KF2.mDescriptors->data, n2,
+            KF2.hasMapPoint.data(), KF2.mvuRight ? KF2.mvuRight->data() : nullptr,
+            KF2.fvNode.data(), KF2.fvStart.data(), KF2.fvIdx.data(), (int)KF2.fvNode.size(),
+            KF2.mvScaleFactors->data(), KF2.mvLevelSigma2->data(), (int)KF2.mvScaleFactors->size(), ep, F12,
+            bOnlyStereo ? 1 : 0, bCoarse ? 1 : 0, mbCheckOrientation ? 1 : 0, underscore ? 1 : 0, m12.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchForTriangulation: ") + orbx_last_error());
+        vMatchedPairs.clear();                                              // :1358-1367
+        vMatchedPairs.reserve((size_t)r);
+        for (int i = 0; i < n1; i++)
+            if (m12[(size_t)i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m12[(size_t)i]));
+        return r;
+    }
+
+    // void ORBmatcher::ComputeThreeMaxima(vector<int>* histo, const int L, int&, int&, int&)
+    // include/ORBmatcher.h:107, src/ORBmatcher.cc:2863-2905
+    static void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3)
+    {
+        std::vector<int32_t> sz((size_t)L);
+        for (int i = 0; i < L; i++) sz[(size_t)i] = (int32_t)histo[i].size();
+        int32_t a, b, c;
+        orbx_three_maxima(sz.data(), L, &a, &b, &c);
+        ind1 = a; ind2 = b; ind3 = c;
     }
 };
 

@@ -52,7 +52,45 @@ int main()
         std::printf("left %zu kps (mono %d), right %zu kps (mono %d), stereo matches %d, d(0,1) = %d\n", mvKeys.size(), monoLeft,
                     mvKeysRight.size(), monoRight, matched,
                     mvKeys.size() > 1 ? ORBmatcherGPU::DescriptorDistance(cv::Mat(1, 32, mDescriptors.ptr(0), 32), cv::Mat(1, 32, mDescriptors.ptr(1), 32)) : -1);
-        return matched > 0 ? 0 : 2;
+        // --- the tracking-side searches on a second view (the scene moved 6 px to the left) ---
+        cv::Mat imNext = synth(rows, cols, 1, 6);
+        std::vector<cv::KeyPoint> mvKeys2;
+        cv::Mat mDescriptors2;
+        left(imNext, cv::Mat(), mvKeys2, mDescriptors2, vLapping);
+        std::vector<float> sf = left.GetScaleFactors(), sigma2 = left.GetScaleSigmaSquares();
+        ORBmatcherGPU::FrameView F1 = {&mvKeys, &mDescriptors, &mvuRight, 0.f, (float)cols, 0.f, (float)rows, &sf};
+        ORBmatcherGPU::FrameView F2 = {&mvKeys2, &mDescriptors2, nullptr, 0.f, (float)cols, 0.f, (float)rows, &sf};
+        // Tracking::MonocularInitialization, src/Tracking.cc: matcher(0.9, true).SearchForInitialization(..., 100)
+        ORBmatcherGPU matcherIni(0.9f, true);
+        std::vector<cv::Point2f> vbPrevMatched(mvKeys.size());
+        for (size_t i = 0; i < mvKeys.size(); i++) vbPrevMatched[i] = mvKeys[i].pt;
+        std::vector<int> vnMatches12;
+        const int nIni = matcherIni.SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, 100);
+        // Tracking::TrackWithMotionModel: matcher(0.9, true).SearchByProjection(mCurrentFrame, mLastFrame, th, bMono)
+        ORBmatcherGPU::LastFrameSoA last;
+        last.desc.assign(mDescriptors.data, mDescriptors.data + (size_t)mDescriptors.rows * 32);
+        for (const cv::KeyPoint& kp : mvKeys) {
+            last.u.push_back(kp.pt.x - 6.f); last.v.push_back(kp.pt.y); last.invz.push_back(0.2f);
+            last.angle.push_back(kp.angle); last.octave.push_back(kp.octave); last.valid.push_back(1); last.obs.push_back(1);
+        }
+        std::vector<int32_t> assign;
+        const int nProj = matcherIni.SearchByProjection(F2, last, 15.f, 0.f, false, false, nullptr, assign);
+        // LocalMapping::CreateNewMapPoints: matcher(0.6, false).SearchForTriangulation(pKF1, pKF2, F12, pairs, false)
+        ORBmatcherGPU matcherTri(0.6f, false);
+        ORBmatcherGPU::KeyFrameView K1 = {&mvKeys, &mDescriptors, nullptr, std::vector<uint8_t>(mvKeys.size(), 0), {}, {}, {}, &sf, &sigma2};
+        ORBmatcherGPU::KeyFrameView K2 = {&mvKeys2, &mDescriptors2, nullptr, std::vector<uint8_t>(mvKeys2.size(), 0), {}, {}, {}, &sf, &sigma2};
+        for (int k = 0; k < 2; k++) {           // one vocabulary node holding every keypoint
+            ORBmatcherGPU::KeyFrameView& K = k ? K2 : K1;
+            K.fvNode = {0}; K.fvStart = {0, (int32_t)K.mvKeysUn->size()};
+            for (size_t i = 0; i < K.mvKeysUn->size(); i++) K.fvIdx.push_back((int32_t)i);
+        }
+        const float F12[9] = {0, 0, 0, 0, 0, -1, 0, 1, 0};   // sideways motion: epipolar lines are the image rows
+        const float ep[2] = {-1e6f, 0.f};
+        std::vector<std::pair<size_t, size_t>> vMatchedPairs;
+        const int nTri = matcherTri.SearchForTriangulation(K1, K2, F12, ep, vMatchedPairs, false);
+        std::printf("second view: %zu kps; SearchForInitialization %d, SearchByProjection(Frame,Frame) %d, SearchForTriangulation %d\n",
+                    mvKeys2.size(), nIni, nProj, nTri);
+        return (matched > 0 && nIni > 0 && nProj > 0 && nTri > 0 && (int)vMatchedPairs.size() == nTri) ? 0 : 2;
     } catch (const std::exception& e) {
         std::fprintf(stderr, "error: %s\n", e.what());
         return 1;
