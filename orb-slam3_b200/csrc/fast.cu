@@ -126,6 +126,13 @@ __device__ __forceinline__ void nms_row(const uint32_t (&R)[3][4], uint32_t thr,
     to = __vmaxu2(C[2] & V_o, nb) ^ nb;
 }
 
+// append e to the u16 list at shared address wa when flag != 0: predicated store + bump, no divergent region
+__device__ __forceinline__ void list_push(uint32_t& wa, uint32_t flag, uint32_t e)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p st.shared.u16 [%0], %2;\n\t@p add.u32 %0, %0, 2;\n\t}"
+                 : "+r"(wa) : "r"(flag), "h"((unsigned short)e) : "memory");
+}
+
 __device__ __forceinline__ void nms_fill(uint32_t (&w)[4], uint32_t l, uint32_t m, uint32_t r)
 {
     w[0] = __funnelshift_r(l, m, 16);
@@ -224,6 +231,8 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
         const uint32_t* sp = s_tile + wi;
         const bool hasl = active && wi > 0, hasr = active && wi + 1 < nw;
         uint32_t R[3][4];
+        const uint32_t wa0 = (uint32_t)__cvta_generic_to_shared(mylist);
+        uint32_t wa = wa0;
 #pragma unroll
         for (int k = 0; k < 4; k++) R[0][k] = 0;
         nms_fill(R[1], hasl ? sp[-1] : 0u, sp[0], hasr ? sp[1] : 0u);
@@ -235,17 +244,18 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
             else { R[(PH + 2) % 3][0] = R[(PH + 2) % 3][1] = R[(PH + 2) % 3][2] = R[(PH + 2) % 3][3] = 0; } \
             uint32_t te, to;                                                                                \
             nms_row<PH>(R, thr, ML_e, MR_e, ML_o, MR_o, V_e, V_o, te, to);                                  \
-            if ((te | to) != 0u) {                             /* survivors go to the lane's private list */          \
-                const int e = (r << 7) | (4 * wi);                                                          \
-                if (te & 0xFFFFu) mylist[cnt++] = (uint16_t)e;                                              \
-                if (to & 0xFFFFu) mylist[cnt++] = (uint16_t)(e + 1);                                        \
-                if (te >> 16)     mylist[cnt++] = (uint16_t)(e + 2);                                        \
-                if (to >> 16)     mylist[cnt++] = (uint16_t)(e + 3);                                        \
+            {                                                  /* survivors go to the lane's private list */         \
+                const uint32_t e = (uint32_t)((r << 7) | (4 * wi));                                          \
+                list_push(wa, te & 0xFFFFu, e);                                                             \
+                list_push(wa, to & 0xFFFFu, e + 1);                                                         \
+                list_push(wa, te >> 16, e + 2);                                                             \
+                list_push(wa, to >> 16, e + 3);                                                             \
             }                                                                                               \
         }
 #pragma unroll 1
         for (int rb = 0; rb < ih; rb += 3) { NMS_STEP(0) NMS_STEP(1) NMS_STEP(2) }
 #undef NMS_STEP
+        cnt = (int)((wa - wa0) >> 1);
     }
     __syncwarp();
 

@@ -1,14 +1,20 @@
 // orbx_internal.h — device data layout and kernel launchers of the B200 ORB front-end.
 //
 // HBM layout (all per extractor handle, sized for `batch` frame slots):
+//   input    : batch frames, rows x in_pitch (in_pitch = cols rounded up to 16: uint4 row copies).
 //   pyr[l]   : batch planes of level l, each `prow x pitch` bytes; interior pixel (0,0) at byte
 //              ORBX_YOFF*pitch + ORBX_XOFF (XOFF=32 keeps interior rows 32B-sector aligned, pitch is a
-//              multiple of 128); the 19-px reflect-101 border of mvImagePyramid sits around it.
+//              multiple of 128).  The hot path writes interiors only; the 19-px reflect-101 border of
+//              mvImagePyramid is filled on demand (pyramid_fill_border) when a padded level is read
+//              back.  Consumers reflect on the fly (blur) or never leave the interior (FAST, IC_Angle).
 //   blur[l]  : same geometry, GaussianBlur(7x7, s=2) of the level (interior only).
-//   cellcnt  : per frame, per cell (all levels flattened) number of FAST keypoints kept by the cell.
-//   cellkey  : per frame, per cell `cell_cap[l]` packed keys  (y<<20 | x<<8 | score), cell raster order.
-//   cand     : per frame, per level compacted candidate list in reference order (vToDistributeKeys).
+//   bands    : FAST work items (BandDesc): runs of whole cells of one cell row, <= 128 px wide.
+//   cand     : per frame, per level FAST keypoints that survive the cell's NMS, packed keys
+//              (y<<20 | x<<8 | score), UNORDERED (one atomic bump per work item); candcnt = counts.
+//              The reference's order (vToDistributeKeys) is recovered where it matters by a canonical
+//              rank computed from the coordinates (cand_rank in octree.cu).
 //   sel      : per frame, per level quadtree selection in std::list order (+ count), packed keys.
+//   nodetab  : quadtree node tables for levels whose tables do not fit 64 KB of shared memory.
 //   out      : per frame `out_cap` cv::KeyPoint records + 32-byte descriptors + {nkp, mono}.
 #pragma once
 #include <cuda_runtime.h>
