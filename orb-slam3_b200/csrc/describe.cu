@@ -76,151 +76,116 @@ int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int la
 // Reads the interior of the pyramid plane (BORDER_REFLECT_101 is applied on the fly), writes the
 // interior of the blur plane.  HBM-bound: algorithmic bytes per frame = read + write sum(L0..L7).
 // ------------------------------------------------------------------------------------------------
-// A thread owns one 32-bit word (4 px) of a 32-row strip and slides down it.  Horizontal pass per row:
-// two IDP.4A (u8 x u8 dot products) per pixel on byte-shifted copies of the three words around the
-// pixel; the 7 most recent horizontal rows stay in registers and the vertical pass is 4 IMAD per pixel
-// on the symmetric kernel.  No shared memory, no barriers.
+// The two passes are exact integer sums without intermediate rounding, so they commute: the VERTICAL
+// pass runs first, on raw bytes.  A thread owns one 32-bit word (4 px) of a 32-row strip; the word is
+// split into its even / odd pixels as u16x2 lanes (E = px 0,2; O = px 1,3) and the 7-tap column sum
+// (<= 255*256, fits 16 bits) is 7 IMAD per lane PAIR (SWAR).  The horizontal pass then needs the column
+// sums of the neighbouring words (4 SHFL) and is 18 IDP.2A (u16 x u8 dot products) per word; byte 2 of
+// each 32-bit accumulator (started at 32768) is the rounded result.  A warp produces 30 words per row:
+// lanes 0 and 31 only supply the halo column sums.
 #define BL_RT 32
-#define BL_BX 64
 #define BL_BY 4
+#define BL_OUTW 30            // output words per warp row
 
-// The pyramid planes carry no materialised border: BORDER_REFLECT_101 is applied while loading.  Every
-// thread rebuilds its three words with PRMT selectors computed once per thread (identity for all but
-// the first and the last two word threads of a row): the first word thread mirrors columns 1..3 to the
-// left, the last two replace every byte right of column w-1 by its mirror image.
-struct BlurEdge { uint32_t selL, selM, selR; bool rFromLM; };
+// BORDER_REFLECT_101 without a materialised border: every lane (halo lanes included) fetches the word
+// pair (A, A+1) that holds the mirror images of its 4 pixels and a PRMT selector picks them; for all
+// interior lanes that is the identity on its own word and the second fetch is skipped.
+struct BlurCol { int a; uint32_t sel; bool needB; };
 
-__device__ __forceinline__ BlurEdge blur_edge(int wi, int w)
+__device__ __forceinline__ BlurCol blur_col(int wi, int w)
 {
-    BlurEdge e;
-    e.selL = wi == 0 ? 0x5670u : 0x3210u;         // over (l, m): bytes -3,-2,-1 = columns 3,2,1
-    e.selM = 0x7654u;                             // over (l, m): m itself
-    e.selR = 0x7654u;                             // over (m, r): r itself
-    e.rFromLM = false;
-    const int last = w - 1;
-    if (4 * wi + 7 > last) {
-        // position q of m | r (column 4wi+q): right of the image -> byte idx of l | m | r holding its mirror
-        uint32_t sm = 0, sr = 0;
-        bool lm = (4 * wi + 3 >= last);           // last word thread: mirrors of r's bytes lie in l | m
-        for (int q = 0; q < 8; q++) {
-            const int pos = 4 * wi + q;
-            int idx = q + 4;                      // itself
-            if (pos > last) { idx = 2 * last - pos - (4 * wi - 4); if (idx < 0) idx = 0; }
-            if (q < 4) sm |= (uint32_t)idx << (4 * q);                       // idx < 8: over (l, m)
-            else sr |= (uint32_t)(lm ? (idx > 7 ? 7 : idx) : idx - 4) << (4 * (q - 4));
-        }
-        e.selM = sm; e.selR = sr; e.rFromLM = lm;
+    const int last = w - 1, nwords = (w + 3) >> 2;
+    int pr[4], lo = 1 << 30;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        int p = 4 * wi + q;
+        p = p < 0 ? -p : p;
+        p = p > last ? 2 * last - p : p;
+        p = max(0, min(p, last));                  // lanes far outside the image: any valid byte (unused)
+        pr[q] = p; lo = min(lo, p);
     }
-    return e;
-}
-
-__device__ __forceinline__ void blur_hrow(int (&h)[4], uint32_t l0, uint32_t m0, uint32_t r0, const BlurEdge& e)
-{
-    const uint32_t l = __byte_perm(l0, m0, e.selL), m = __byte_perm(l0, m0, e.selM);
-    const uint32_t r = e.rFromLM ? __byte_perm(l0, m0, e.selR) : __byte_perm(m0, r0, e.selR);
-    const uint32_t kA = 18u | (34u << 8) | (48u << 16) | (56u << 24);   // taps -3..0
-    const uint32_t kB = 48u | (34u << 8) | (18u << 16);                 // taps +1..+3
-    // word starting at byte x+d: funnel shifts of (l, m) / (m, r)
-    h[0] = __dp4a(__funnelshift_r(l, m, 8), kA, __dp4a(__funnelshift_r(m, r, 8), kB, 0u));    // px x  : x-3..x | x+1..x+4
-    h[1] = __dp4a(__funnelshift_r(l, m, 16), kA, __dp4a(__funnelshift_r(m, r, 16), kB, 0u));  // px x+1
-    h[2] = __dp4a(__funnelshift_r(l, m, 24), kA, __dp4a(__funnelshift_r(m, r, 24), kB, 0u));  // px x+2
-    h[3] = __dp4a(m, kA, __dp4a(r, kB, 0u));                                                   // px x+3
+    BlurCol c;
+    c.a = min(lo >> 2, nwords - 1);
+    c.sel = 0; c.needB = false;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const int idx = min(pr[q] - 4 * c.a, 7);
+        c.sel |= (uint32_t)idx << (4 * q);
+        c.needB |= idx >= 4;
+    }
+    return c;
 }
 
 template <int PH>
-__device__ __forceinline__ uint32_t blur_vword(const int (&H)[7][4])
+__device__ __forceinline__ void blur_vcol(const uint32_t (&WE)[7], const uint32_t (&WO)[7], uint32_t& VE, uint32_t& VO)
 {
-    uint32_t acc[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++)
-        acc[k] = 18u * (uint32_t)(H[PH % 7][k] + H[(PH + 6) % 7][k]) + 34u * (uint32_t)(H[(PH + 1) % 7][k] + H[(PH + 5) % 7][k]) +
-                 48u * (uint32_t)(H[(PH + 2) % 7][k] + H[(PH + 4) % 7][k]) + 56u * (uint32_t)H[(PH + 3) % 7][k] + 32768u;
+    VE = 18u * WE[PH % 7] + 34u * WE[(PH + 1) % 7] + 48u * WE[(PH + 2) % 7] + 56u * WE[(PH + 3) % 7] +
+         48u * WE[(PH + 4) % 7] + 34u * WE[(PH + 5) % 7] + 18u * WE[(PH + 6) % 7];
+    VO = 18u * WO[PH % 7] + 34u * WO[(PH + 1) % 7] + 48u * WO[(PH + 2) % 7] + 56u * WO[(PH + 3) % 7] +
+         48u * WO[(PH + 4) % 7] + 34u * WO[(PH + 5) % 7] + 18u * WO[(PH + 6) % 7];
+}
+
+// E = (V[x], V[x+2]), O = (V[x+1], V[x+3]) of the thread's word, l / r suffix: the words left / right of it.
+__device__ __forceinline__ uint32_t blur_hword(uint32_t El, uint32_t Ol, uint32_t E, uint32_t O, uint32_t Er, uint32_t Or)
+{
+#define KK(lo, hi) ((uint32_t)(lo) | ((uint32_t)(hi) << 8))
+    const uint32_t rnd = 32768u;
+    const uint32_t a0 = __dp2a_lo(Ol, KK(18, 48), __dp2a_lo(El, KK(0, 34), __dp2a_lo(E, KK(56, 34), __dp2a_lo(O, KK(48, 18), rnd))));
+    const uint32_t a1 = __dp2a_lo(El, KK(0, 18), __dp2a_lo(Ol, KK(0, 34), __dp2a_lo(E, KK(48, 48), __dp2a_lo(O, KK(56, 34), __dp2a_lo(Er, KK(18, 0), rnd)))));
+    const uint32_t a2 = __dp2a_lo(Ol, KK(0, 18), __dp2a_lo(E, KK(34, 56), __dp2a_lo(O, KK(48, 48), __dp2a_lo(Er, KK(34, 0), __dp2a_lo(Or, KK(18, 0), rnd)))));
+    const uint32_t a3 = __dp2a_lo(E, KK(18, 48), __dp2a_lo(O, KK(34, 56), __dp2a_lo(Er, KK(48, 18), __dp2a_lo(Or, KK(34, 0), rnd))));
+#undef KK
     // (acc >> 16) <= 255 is byte 2 of each accumulator
-    return __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
+    return __byte_perm(__byte_perm(a0, a1, 0x0062), __byte_perm(a2, a3, 0x0062), 0x5410);
 }
 
-__device__ __forceinline__ void cp_async4(uint32_t* smem_dst, const uint32_t* gsrc)
+// One strip: REFLECT = the strip touches the first / last 3 image rows (row indices are mirrored),
+// FIX = some lane of the warp needs the PRMT edge fix-up (and possibly its second word).  Rows are
+// fetched 7 stream rows ahead into statically indexed registers (slot = stream row % 7, the same
+// rotation as the E/O window).  A slot's old value is fully consumed (unpacked) BEFORE the load that
+// refills it is issued, so the load can land in the same physical register and nothing waits for it
+// until 7 rows later.
+template <bool REFLECT, bool FIX>
+__device__ __forceinline__ void blur_strip(const uint32_t* __restrict__ base, uint32_t* __restrict__ q, int pw, int y0, int nr, int h,
+                                           const BlurCol col, bool colvalid)
 {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
-
-// One warp per (128-px column block, 32-row strip).  The rows of the strip stream through a per-warp
-// shared-memory ring filled with cp.async (LDGSTS) BL_DEPTH rows ahead: the loads need no registers and
-// never stall the issuing warp, so the memory latency overlaps the arithmetic of the rows in between.
-#define BL_RING 8
-#define BL_DEPTH 5
-#define BL_ROWW 36            // ring row: word -1, the warp's 32 words, word +32 (+ padding)
-
-__global__ void __launch_bounds__(32 * BL_BY)
-blur_kernel(FrameGeom G)
-{
-    __shared__ uint32_t s_ring[BL_BY][BL_RING][BL_ROWW];
-    const int lane = threadIdx.x, warp = threadIdx.y;
-    // all levels in one launch: blockIdx.x enumerates (level, row-strip group, 128-px column block)
-    int lvl = 0, bid = blockIdx.x;
-#pragma unroll 1
-    for (; lvl < G.nlevels - 1; lvl++) {
-        const int nb = ((G.L[lvl].w + 127) / 128) * ((G.L[lvl].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
-        if (bid < nb) break;
-        bid -= nb;
-    }
-    const LevelGeom& L = G.L[lvl];
-    const uint8_t* __restrict__ pyr = L.pyr; uint8_t* __restrict__ blur = L.blur;
-    const int pitch = L.pitch, w = L.w, h = L.h;
-    const long long plane_bytes = L.plane_bytes;
-    const int nbx = (w + 127) / 128;
-    const int by = bid / nbx, bx = bid - by * nbx;
-    const int wi0 = bx * 32, wi = wi0 + lane;
-    const int y0 = (by * BL_BY + warp) * BL_RT;
-    if (wi0 * 4 >= w || y0 >= h) return;                       // warp-uniform
-    const int f = blockIdx.y;
-    const int pw = pitch >> 2;
-    const int nr = min(BL_RT, h - y0);
     const int nstream = nr + 6;                                // stream row s = image row y0 - 3 + s
-    const uint32_t* base = reinterpret_cast<const uint32_t*>(pyr + (long long)f * plane_bytes + (long long)ORBX_YOFF * pitch + ORBX_XOFF) + wi0;
-    uint32_t (*ring)[BL_ROWW] = s_ring[warp];
-    // per-lane copy addresses: every lane copies its own word, lanes 0 / 1 also the words left / right of the warp
-    const uint32_t sm_own = (uint32_t)__cvta_generic_to_shared(&ring[0][1 + lane]);
-    const uint32_t sm_halo = (uint32_t)__cvta_generic_to_shared(&ring[0][lane ? 33 : 0]);
-    const int g_halo = lane ? 32 : -1;
-    const bool reflects = (y0 < 3) || (y0 + nr + 3 > h);      // only the first / last strips leave [0, h)
-    const uint32_t* srow = base + (long long)(y0 - 3) * pw;   // running row pointer (interior strips)
-    auto issue = [&](int sr) {
-        if (sr < nstream) {
-            const uint32_t* src = srow;
-            if (reflects) {
-                int y = y0 - 3 + sr;
-                y = y < 0 ? -y : y; y = y >= h ? 2 * (h - 1) - y : y;      // reflect-101 rows
-                src = base + y * pw;
-            }
-            const uint32_t so = (uint32_t)(sr & (BL_RING - 1)) * (BL_ROWW * 4);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(sm_own + so), "l"(src + lane) : "memory");
-            if (lane < 2) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(sm_halo + so), "l"(src + g_halo) : "memory");
-            srow += pw;
-        }
-        cp_async_commit();
+    const uint32_t* nxt = base + (long long)(y0 - 3) * pw;    // next row to fetch (!REFLECT: running pointer;
+    int sf = 0;                                                //  it may run a few rows past the strip, inside the plane)
+    uint32_t RA[7], RB[7];
+    auto fetch = [&](int slot, uint32_t dep) {
+        const uint32_t* src = nxt + dep;
+        if (REFLECT) {
+            int y = y0 - 3 + min(sf, nstream - 1);
+            y = y < 0 ? -y : y; y = y >= h ? 2 * (h - 1) - y : y;          // reflect-101 rows
+            src = base + (long long)y * pw + dep;
+            sf++;
+        } else nxt += pw;
+        RA[slot] = __ldg(src);
+        if (FIX) RB[slot] = col.needB ? __ldg(src + 1) : 0u;
     };
-    uint32_t* q = reinterpret_cast<uint32_t*>(blur + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y0) * pitch + ORBX_XOFF) + wi;
-    const bool colvalid = wi * 4 < w;
-    const BlurEdge edge = blur_edge(wi, w);
+    uint32_t WE[7], WO[7];
 #pragma unroll
-    for (int i = 0; i < BL_DEPTH; i++) issue(i);
-    int H[7][4];
-    int sr = 0;                                                // next stream row to consume
+    for (int i = 0; i < 7; i++) fetch(i, 0u);
 #define BLUR_ROW(SLOT)                                                                    \
-    {   cp_async_wait<BL_DEPTH - 1>(); __syncwarp();                                      \
-        const uint32_t* rr = ring[sr & (BL_RING - 1)] + lane;                             \
-        const uint32_t l0 = rr[0], m0 = rr[1], r0 = rr[2];                                \
-        issue(sr + BL_DEPTH); sr++;                                                       \
-        blur_hrow(H[SLOT], l0, m0, r0, edge); }
+    {   uint32_t m = RA[SLOT];                                                            \
+        if (FIX) m = __byte_perm(m, RB[SLOT], col.sel);                                   \
+        /* opaque unpack: the refill's address is made to depend on it (dep == 0), so the  \
+           load cannot be scheduled above the last read of the slot it overwrites */      \
+        uint32_t e, o;                                                                    \
+        asm("prmt.b32 %0, %2, 0, 0x4240;\n\tprmt.b32 %1, %2, 0, 0x4341;" : "=r"(e), "=r"(o) : "r"(m)); \
+        WE[SLOT] = e; WO[SLOT] = o;                                                       \
+        fetch(SLOT, o >> 24); }
     BLUR_ROW(0) BLUR_ROW(1) BLUR_ROW(2) BLUR_ROW(3) BLUR_ROW(4) BLUR_ROW(5)
 #define BLUR_STEP(PH)                                                   \
-    if (rb + PH < nr) {                                                 \
+    {   /* unguarded: rows past nr are computed and dropped, so the body is straight-line code */ \
         BLUR_ROW((PH + 6) % 7)                                          \
-        const uint32_t vw = blur_vword<PH>(H);                          \
-        if (colvalid) *q = vw;                                          \
+        uint32_t VE, VO;                                                \
+        blur_vcol<PH>(WE, WO, VE, VO);                                  \
+        const uint32_t El = __shfl_up_sync(0xffffffffu, VE, 1), Ol = __shfl_up_sync(0xffffffffu, VO, 1);     \
+        const uint32_t Er = __shfl_down_sync(0xffffffffu, VE, 1), Or = __shfl_down_sync(0xffffffffu, VO, 1); \
+        const uint32_t vw = blur_hword(El, Ol, VE, VO, Er, Or);         \
+        if (colvalid && rb + PH < nr) *q = vw;                          \
         q += pw;                                                        \
     }
 #pragma unroll 1
@@ -231,11 +196,50 @@ blur_kernel(FrameGeom G)
 #undef BLUR_ROW
 }
 
+// One warp per (120-px column block, 32-row strip); no shared memory, no barriers.
+__global__ void __launch_bounds__(32 * BL_BY)
+blur_kernel(FrameGeom G)
+{
+    const int lane = threadIdx.x, warp = threadIdx.y;
+    // all levels in one launch: blockIdx.x enumerates (level, row-strip group, column block)
+    int lvl = 0, bid = blockIdx.x;
+#pragma unroll 1
+    for (; lvl < G.nlevels - 1; lvl++) {
+        const int nb = ((G.L[lvl].w + 4 * BL_OUTW - 1) / (4 * BL_OUTW)) * ((G.L[lvl].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
+        if (bid < nb) break;
+        bid -= nb;
+    }
+    const LevelGeom& L = G.L[lvl];
+    const int pitch = L.pitch, w = L.w, h = L.h;
+    const long long plane_bytes = L.plane_bytes;
+    const int nbx = (w + 4 * BL_OUTW - 1) / (4 * BL_OUTW);
+    const int by = bid / nbx, bx = bid - by * nbx;
+    const int wi = bx * BL_OUTW - 1 + lane;                    // lane 0 / 31: halo words
+    const int y0 = (by * BL_BY + warp) * BL_RT;
+    if (y0 >= h) return;                                       // warp-uniform
+    const int f = blockIdx.y;
+    const int pw = pitch >> 2;
+    const int nr = min(BL_RT, h - y0);
+    const BlurCol col = blur_col(wi, w);
+    const bool fix = __any_sync(0xffffffffu, col.sel != 0x3210u);
+    const uint32_t* base = reinterpret_cast<const uint32_t*>(L.pyr + (long long)f * plane_bytes + (long long)ORBX_YOFF * pitch + ORBX_XOFF) + col.a;
+    uint32_t* q = reinterpret_cast<uint32_t*>(L.blur + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y0) * pitch + ORBX_XOFF) + wi;
+    const bool colvalid = lane >= 1 && lane <= BL_OUTW && wi * 4 < w;
+    const bool reflects = (y0 < 3) || (y0 + nr + 3 > h);      // only the first / last strips leave [0, h)
+    if (reflects) {
+        if (fix) blur_strip<true, true>(base, q, pw, y0, nr, h, col, colvalid);
+        else blur_strip<true, false>(base, q, pw, y0, nr, h, col, colvalid);
+    } else {
+        if (fix) blur_strip<false, true>(base, q, pw, y0, nr, h, col, colvalid);
+        else blur_strip<false, false>(base, q, pw, y0, nr, h, col, colvalid);
+    }
+}
+
 int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
     int nblocks = 0;
     for (int l = 0; l < G.nlevels; l++)
-        nblocks += ((G.L[l].w + 127) / 128) * ((G.L[l].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
+        nblocks += ((G.L[l].w + 4 * BL_OUTW - 1) / (4 * BL_OUTW)) * ((G.L[l].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
     blur_kernel<<<dim3(nblocks, nframes), dim3(32, BL_BY), 0, s>>>(G);
     (void)D;
     return 1;
