@@ -181,6 +181,7 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
         }
     }
     D.nodetab_per_frame = (long long)octree_nodetab_ints(G);
+    blur_plan(G);
     {
         std::vector<BandDesc> bands;
         G.fast_smem = fast_build_bands(G, &bands, &G.fast_warp_words);

@@ -73,7 +73,7 @@ int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int la
 // ------------------------------------------------------------------------------------------------
 // GaussianBlur(7x7, sigma 2) in OpenCV 4.x fixed point: kernel [18,34,48,56,48,34,18]/256, horizontal
 // pass in 8.8 (u16), vertical in 16.16, +0.5 rounding (oracle/orc_prims.c orc_gaussian7x7_s2).
-// Reads the interior of the pyramid plane (BORDER_REFLECT_101 is applied on the fly), writes the
+// Reads the pyramid plane with its thin reflect-101 halo (written by the pyramid kernels), writes the
 // interior of the blur plane.  HBM-bound: algorithmic bytes per frame = read + write sum(L0..L7).
 // ------------------------------------------------------------------------------------------------
 // The two passes are exact integer sums without intermediate rounding, so they commute: the VERTICAL
@@ -86,35 +86,7 @@ int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int la
 #define BL_RT 32
 #define BL_BY 4
 #define BL_OUTW 30            // output words per warp row
-
-// BORDER_REFLECT_101 without a materialised border: every lane (halo lanes included) fetches the word
-// pair (A, A+1) that holds the mirror images of its 4 pixels and a PRMT selector picks them; for all
-// interior lanes that is the identity on its own word and the second fetch is skipped.
-struct BlurCol { int a; uint32_t sel; bool needB; };
-
-__device__ __forceinline__ BlurCol blur_col(int wi, int w)
-{
-    const int last = w - 1, nwords = (w + 3) >> 2;
-    int pr[4], lo = 1 << 30;
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-        int p = 4 * wi + q;
-        p = p < 0 ? -p : p;
-        p = p > last ? 2 * last - p : p;
-        p = max(0, min(p, last));                  // lanes far outside the image: any valid byte (unused)
-        pr[q] = p; lo = min(lo, p);
-    }
-    BlurCol c;
-    c.a = min(lo >> 2, nwords - 1);
-    c.sel = 0; c.needB = false;
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-        const int idx = min(pr[q] - 4 * c.a, 7);
-        c.sel |= (uint32_t)idx << (4 * q);
-        c.needB |= idx >= 4;
-    }
-    return c;
-}
+#define HALO_ROWS_BLUR 3      // rows of reflect-101 halo the pyramid planes carry (written by the pyramid kernels)
 
 template <int PH>
 __device__ __forceinline__ void blur_vcol(const uint32_t (&WE)[7], const uint32_t (&WO)[7], uint32_t& VE, uint32_t& VO)
@@ -139,43 +111,43 @@ __device__ __forceinline__ uint32_t blur_hword(uint32_t El, uint32_t Ol, uint32_
     return __byte_perm(__byte_perm(a0, a1, 0x0062), __byte_perm(a2, a3, 0x0062), 0x5410);
 }
 
-// One strip: REFLECT = the strip touches the first / last 3 image rows (row indices are mirrored),
-// FIX = some lane of the warp needs the PRMT edge fix-up (and possibly its second word).  Rows are
-// fetched 7 stream rows ahead into statically indexed registers (slot = stream row % 7, the same
-// rotation as the E/O window).  A slot's old value is fully consumed (unpacked) BEFORE the load that
-// refills it is issued, so the load can land in the same physical register and nothing waits for it
-// until 7 rows later.
-template <bool REFLECT, bool FIX>
-__device__ __forceinline__ void blur_strip(const uint32_t* __restrict__ base, uint32_t* __restrict__ q, int pw, int y0, int nr, int h,
-                                           const BlurCol col, bool colvalid)
+// One warp per (120-px column block, 32-row strip); no shared memory, no barriers, one straight code
+// path: BORDER_REFLECT_101 is already in the plane (the 3-row / one-word halo written by
+// the pyramid kernels), so the first / last strips and the edge column blocks read like any other.
+// Rows are fetched 7 stream rows ahead into statically indexed registers (slot = stream row % 7, the
+// same rotation as the E/O window).  A slot's old value is consumed (unpacked) BEFORE the load that
+// refills it is issued — the refill's address carries a fake dependency on the unpacked value — so the
+// load lands in the slot's own register and nothing waits for it until 7 rows later.
+__global__ void __launch_bounds__(32 * BL_BY)
+blur_kernel(FrameGeom G)
 {
-    const int nstream = nr + 6;                                // stream row s = image row y0 - 3 + s
-    const uint32_t* nxt = base + (long long)(y0 - 3) * pw;    // next row to fetch (!REFLECT: running pointer;
-    int sf = 0;                                                //  it may run a few rows past the strip, inside the plane)
-    uint32_t RA[7], RB[7];
-    auto fetch = [&](int slot, uint32_t dep) {
-        const uint32_t* src = nxt + dep;
-        if (REFLECT) {
-            int y = y0 - 3 + min(sf, nstream - 1);
-            y = y < 0 ? -y : y; y = y >= h ? 2 * (h - 1) - y : y;          // reflect-101 rows
-            src = base + (long long)y * pw + dep;
-            sf++;
-        } else nxt += pw;
-        RA[slot] = __ldg(src);
-        if (FIX) RB[slot] = col.needB ? __ldg(src + 1) : 0u;
-    };
-    uint32_t WE[7], WO[7];
+    const int lane = threadIdx.x, warp = threadIdx.y;
+    // all levels in one launch: blockIdx.x enumerates (level, row-strip group, column block)
+    int lvl = 0, bid = blockIdx.x;
+    while (bid >= G.blur_end[lvl]) lvl++;
+    if (lvl > 0) bid -= G.blur_end[lvl - 1];
+    const LevelGeom& L = G.L[lvl];
+    const int pitch = L.pitch, w = L.w, h = L.h;
+    const int nbx = (w + 4 * BL_OUTW - 1) / (4 * BL_OUTW);
+    const int by = bid / nbx, bx = bid - by * nbx;
+    const int wi = bx * BL_OUTW - 1 + lane;                    // lane 0 / 31: halo words
+    const int y0 = (by * BL_BY + warp) * BL_RT;
+    if (y0 >= h) return;                                       // warp-uniform
+    const int pw = pitch >> 2;
+    const int nr = min(BL_RT, h - y0);
+    const long long plane = (long long)blockIdx.y * L.plane_bytes + (long long)ORBX_YOFF * pitch + ORBX_XOFF;
+    // lanes past the right halo word read a valid word and drop the result
+    const uint32_t* nxt = reinterpret_cast<const uint32_t*>(L.pyr + plane) + (long long)(y0 - HALO_ROWS_BLUR) * pw + min(wi, (w + 3) >> 2);
+    uint32_t* q = reinterpret_cast<uint32_t*>(L.blur + plane) + (long long)y0 * pw + wi;
+    const bool colvalid = lane >= 1 && lane <= BL_OUTW && wi * 4 < w;
+    uint32_t RA[7], WE[7], WO[7];
 #pragma unroll
-    for (int i = 0; i < 7; i++) fetch(i, 0u);
+    for (int i = 0; i < 7; i++) { RA[i] = __ldg(nxt); nxt += pw; }     // may run a few rows past the strip, inside the plane
 #define BLUR_ROW(SLOT)                                                                    \
-    {   uint32_t m = RA[SLOT];                                                            \
-        if (FIX) m = __byte_perm(m, RB[SLOT], col.sel);                                   \
-        /* opaque unpack: the refill's address is made to depend on it (dep == 0), so the  \
-           load cannot be scheduled above the last read of the slot it overwrites */      \
-        uint32_t e, o;                                                                    \
-        asm("prmt.b32 %0, %2, 0, 0x4240;\n\tprmt.b32 %1, %2, 0, 0x4341;" : "=r"(e), "=r"(o) : "r"(m)); \
+    {   uint32_t e, o;                                                                    \
+        asm("prmt.b32 %0, %2, 0, 0x4240;\n\tprmt.b32 %1, %2, 0, 0x4341;" : "=r"(e), "=r"(o) : "r"(RA[SLOT])); \
         WE[SLOT] = e; WO[SLOT] = o;                                                       \
-        fetch(SLOT, o >> 24); }
+        RA[SLOT] = __ldg(nxt + (o >> 24)); nxt += pw; }
     BLUR_ROW(0) BLUR_ROW(1) BLUR_ROW(2) BLUR_ROW(3) BLUR_ROW(4) BLUR_ROW(5)
 #define BLUR_STEP(PH)                                                   \
     {   /* unguarded: rows past nr are computed and dropped, so the body is straight-line code */ \
@@ -196,51 +168,18 @@ __device__ __forceinline__ void blur_strip(const uint32_t* __restrict__ base, ui
 #undef BLUR_ROW
 }
 
-// One warp per (120-px column block, 32-row strip); no shared memory, no barriers.
-__global__ void __launch_bounds__(32 * BL_BY)
-blur_kernel(FrameGeom G)
+void blur_plan(FrameGeom& G)
 {
-    const int lane = threadIdx.x, warp = threadIdx.y;
-    // all levels in one launch: blockIdx.x enumerates (level, row-strip group, column block)
-    int lvl = 0, bid = blockIdx.x;
-#pragma unroll 1
-    for (; lvl < G.nlevels - 1; lvl++) {
-        const int nb = ((G.L[lvl].w + 4 * BL_OUTW - 1) / (4 * BL_OUTW)) * ((G.L[lvl].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
-        if (bid < nb) break;
-        bid -= nb;
-    }
-    const LevelGeom& L = G.L[lvl];
-    const int pitch = L.pitch, w = L.w, h = L.h;
-    const long long plane_bytes = L.plane_bytes;
-    const int nbx = (w + 4 * BL_OUTW - 1) / (4 * BL_OUTW);
-    const int by = bid / nbx, bx = bid - by * nbx;
-    const int wi = bx * BL_OUTW - 1 + lane;                    // lane 0 / 31: halo words
-    const int y0 = (by * BL_BY + warp) * BL_RT;
-    if (y0 >= h) return;                                       // warp-uniform
-    const int f = blockIdx.y;
-    const int pw = pitch >> 2;
-    const int nr = min(BL_RT, h - y0);
-    const BlurCol col = blur_col(wi, w);
-    const bool fix = __any_sync(0xffffffffu, col.sel != 0x3210u);
-    const uint32_t* base = reinterpret_cast<const uint32_t*>(L.pyr + (long long)f * plane_bytes + (long long)ORBX_YOFF * pitch + ORBX_XOFF) + col.a;
-    uint32_t* q = reinterpret_cast<uint32_t*>(L.blur + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y0) * pitch + ORBX_XOFF) + wi;
-    const bool colvalid = lane >= 1 && lane <= BL_OUTW && wi * 4 < w;
-    const bool reflects = (y0 < 3) || (y0 + nr + 3 > h);      // only the first / last strips leave [0, h)
-    if (reflects) {
-        if (fix) blur_strip<true, true>(base, q, pw, y0, nr, h, col, colvalid);
-        else blur_strip<true, false>(base, q, pw, y0, nr, h, col, colvalid);
-    } else {
-        if (fix) blur_strip<false, true>(base, q, pw, y0, nr, h, col, colvalid);
-        else blur_strip<false, false>(base, q, pw, y0, nr, h, col, colvalid);
+    int run = 0;
+    for (int l = 0; l < G.nlevels; l++) {
+        run += ((G.L[l].w + 4 * BL_OUTW - 1) / (4 * BL_OUTW)) * ((G.L[l].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
+        G.blur_end[l] = run;
     }
 }
 
 int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
-    int nblocks = 0;
-    for (int l = 0; l < G.nlevels; l++)
-        nblocks += ((G.L[l].w + 4 * BL_OUTW - 1) / (4 * BL_OUTW)) * ((G.L[l].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
-    blur_kernel<<<dim3(nblocks, nframes), dim3(32, BL_BY), 0, s>>>(G);
+    blur_kernel<<<dim3(G.blur_end[G.nlevels - 1], nframes), dim3(32, BL_BY), 0, s>>>(G);
     (void)D;
     return 1;
 }

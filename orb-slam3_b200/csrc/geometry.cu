@@ -4,6 +4,7 @@
 #include "orbx_host.h"
 #include <cmath>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 
 static inline int cv_round_f(float v) { return (int)lrintf(v); }   // cvRound: round-half-even
@@ -39,14 +40,17 @@ void orbx_init_tables(orbx_extractor* e)
 bool orbx_build_word_taps(const std::vector<ResizeTapX>& TX, int w, int pitch, std::vector<ResizeWord>* out)
 {
     out->assign(pitch / 4, ResizeWord{0, 0, 0, {0, 0, 0, 0}, 0});
-    for (int wi = ORBX_XOFF / 4; wi * 4 < ORBX_XOFF + w; wi++) {
+    // interior words plus one halo word on each side; TX holds the reflect-101 taps for the bytes outside
+    // the image, so the halo words (and the pixels of the last word past column w-1) come out mirrored
+    for (int wi = ORBX_XOFF / 4 - 1; wi <= (ORBX_XOFF + w + 3) / 4; wi++) {
         ResizeWord rw{};
-        const ResizeTapX& t0 = TX[wi * 4];
-        rw.wb = t0.s0 & ~3; rw.shift = (uint32_t)(t0.s0 & 3) * 8;
+        int base = 1 << 30;
+        for (int k = 0; k < 4; k++) base = std::min(base, (int)TX[wi * 4 + k].s0);
+        rw.wb = base & ~3; rw.shift = (uint32_t)(base & 3) * 8;
         for (int k = 0; k < 4; k++) {
-            const int x = wi * 4 - ORBX_XOFF + k;
-            const ResizeTapX& t = TX[ORBX_XOFF + (x < w ? x : w - 1)];
-            const int n0 = t.s0 - t0.s0, n1 = t.s1 - t0.s0;
+            const ResizeTapX& t = TX[wi * 4 + k];
+            // window byte n = source column (base & ~3) + shift/8 + n
+            const int n0 = t.s0 - base, n1 = t.s1 - base;
             if (n0 < 0 || n0 > 7 || n1 < 0 || n1 > 7) return false;
             rw.sels |= (uint32_t)(n0 | (n1 << 4)) << (8 * k);
             rw.a01[k] = (uint32_t)(uint16_t)t.a0 | ((uint32_t)(uint16_t)t.a1 << 16);

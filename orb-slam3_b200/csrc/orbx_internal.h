@@ -4,9 +4,10 @@
 //   input    : batch frames, rows x in_pitch (in_pitch = cols rounded up to 16: uint4 row copies).
 //   pyr[l]   : batch planes of level l, each `prow x pitch` bytes; interior pixel (0,0) at byte
 //              ORBX_YOFF*pitch + ORBX_XOFF (XOFF=32 keeps interior rows 32B-sector aligned, pitch is a
-//              multiple of 128).  The hot path writes interiors only; the 19-px reflect-101 border of
-//              mvImagePyramid is filled on demand (pyramid_fill_border) when a padded level is read
-//              back.  Consumers reflect on the fly (blur) or never leave the interior (FAST, IC_Angle).
+//              multiple of 128).  The hot path writes the interior plus a thin reflect-101 halo (3 rows
+//              above / below, one 4-px word left / right, written by the pyramid kernels) for the 7x7 blur; the full
+//              19-px border of mvImagePyramid is filled on demand (pyramid_fill_border) when a padded
+//              level is read back.  FAST, IC_Angle and the descriptor taps never leave the interior.
 //   blur[l]  : same geometry, GaussianBlur(7x7, s=2) of the level (interior only).
 //   bands    : FAST work items (BandDesc): runs of whole cells of one cell row, <= 128 px wide.
 //   cand     : per frame, per level FAST keypoints that survive the cell's NMS, packed keys
@@ -92,6 +93,7 @@ struct FrameGeom {
     int sel_per_frame;        // == out_cap
     int out_cap;
     int iniTh, minTh;
+    int blur_end[ORBX_MAX_LEVELS];   // cumulative blur CTAs per frame up to and including level l
     LevelGeom L[ORBX_MAX_LEVELS];
 };
 
@@ -115,6 +117,7 @@ struct DevBuffers {
 
 // kernel launchers (each returns the number of kernel launches it issued)
 int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
+void blur_plan(FrameGeom& G);           // fills blur_end[]
 void pyramid_fill_border(const LevelGeom& L, int frame, cudaStream_t s);   // mvImagePyramid border on demand
 int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
 int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);

@@ -14,19 +14,32 @@ __device__ __forceinline__ int reflect101(int i, int n)
     return i;
 }
 
-// level 0: input frame -> interior of the level-0 plane, 16 bytes per thread.  The 19-px reflect-101
-// border of mvImagePyramid is NOT materialised on the hot path (nothing downstream reads it: the blur
-// mirrors on the fly); orbx_get_pyramid_level(padded) fills it on demand with the two kernels below.
+// level 0: input frame -> interior of the level-0 plane, 16 bytes per thread, plus the thin reflect-101
+// halo the blur reads (PYR_HALO rows above / below, one 4-px word left / right; the pixels of the last
+// word past column w-1 are mirrored too).  The full 19-px border of mvImagePyramid is NOT materialised
+// on the hot path; orbx_get_pyramid_level(padded) fills it on demand with the two kernels below.
+#define PYR_HALO 3
 __global__ void __launch_bounds__(256)
 pyr_level0_kernel(const uint8_t* __restrict__ in, int in_pitch, long long in_frame_bytes,
                   uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h)
 {
     const int qi = blockIdx.x * blockDim.x + threadIdx.x;     // 16-byte group of the image row
-    const int y = blockIdx.y * blockDim.y + threadIdx.y;
-    if (y >= h || qi * 16 >= w) return;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y - PYR_HALO;
+    if (y >= h + PYR_HALO || qi * 16 >= w) return;
     const int f = blockIdx.z;
-    const uint4* src = reinterpret_cast<const uint4*>(in + (long long)f * in_frame_bytes + (long long)y * in_pitch);
-    reinterpret_cast<uint4*>(out + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y) * pitch + ORBX_XOFF)[qi] = __ldg(src + qi);
+    const uint8_t* srow = in + (long long)f * in_frame_bytes + (long long)reflect101(y, h) * in_pitch;
+    uint8_t* drow = out + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y) * pitch + ORBX_XOFF;
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(srow) + qi);
+    reinterpret_cast<uint4*>(drow)[qi] = v;
+    if (qi == 0) *reinterpret_cast<uint32_t*>(drow - 4) = __byte_perm(v.x, v.y, 0x1234);      // columns 4,3,2,1
+    if (qi * 16 + 16 >= w) {                                  // last group: words nw-1 and nw
+        const int p0 = ((w + 3) / 4 - 1) * 4;
+        uint32_t t[2] = {0u, 0u};
+#pragma unroll
+        for (int q = 0; q < 8; q++) t[q >> 2] |= (uint32_t)srow[reflect101(p0 + q, w)] << (8 * (q & 3));
+        *reinterpret_cast<uint32_t*>(drow + p0) = t[0];
+        *reinterpret_cast<uint32_t*>(drow + p0 + 4) = t[1];
+    }
 }
 
 // on-demand border, step 1: rows above / below the image = reflect-101 rows (interior columns)
@@ -61,7 +74,7 @@ void pyramid_fill_border(const LevelGeom& L, int frame, cudaStream_t s)
     pyr_border_cols_kernel<<<(L.prow * 2 * ORBX_EDGE + 255) / 256, 256, 0, s>>>(plane, L.pitch, L.w, L.prow);
 }
 
-// fast path of the resize: interior words only, taps from the 8 source bytes starting at the first
+// fast path of the resize: interior words and the thin halo (PYR_HALO rows, one word per side), taps from the 8 source bytes starting at the first
 // pixel's left tap (3 aligned word loads + 2 funnel shifts per source row, PRMT + IDP.2A per pixel)
 struct HRow4 { int h[4]; };
 __device__ __forceinline__ HRow4 pyr_hrow_fast(const uint8_t* __restrict__ S, const ResizeWord& t, const uint32_t (&sel)[4])
@@ -82,10 +95,10 @@ pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long p
                        uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h,
                        const ResizeWord* __restrict__ tapw, const ResizeTapY* __restrict__ tapy)
 {
-    const int wi = ORBX_XOFF / 4 + blockIdx.x * blockDim.x + threadIdx.x;      // interior words only
-    if (wi * 4 >= ORBX_XOFF + w) return;
-    const int Y0 = (blockIdx.y * blockDim.y + threadIdx.y) * PYRF_ROWS;       // image row (interior rows only)
-    if (Y0 >= h) return;
+    const int wi = ORBX_XOFF / 4 - 1 + blockIdx.x * blockDim.x + threadIdx.x; // interior words + one halo word per side
+    if (wi > (ORBX_XOFF + w + 3) / 4) return;
+    const int Y0 = (blockIdx.y * blockDim.y + threadIdx.y) * PYRF_ROWS - PYR_HALO;   // image row (interior + halo rows)
+    if (Y0 >= h + PYR_HALO) return;
     const int f = blockIdx.z;
     ResizeWord t;
     {
@@ -102,7 +115,7 @@ pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long p
     HRow4 hl;
 #pragma unroll
     for (int k = 0; k < 4; k++) hl.h[k] = 0;
-    const int nr = min(PYRF_ROWS, h - Y0);
+    const int nr = min(PYRF_ROWS, h + PYR_HALO - Y0);
 #pragma unroll 2
     for (int rr = 0; rr < nr; rr++) {
         const ResizeTapY ty = tapy[ORBX_EDGE + Y0 + rr];       // the tap table is indexed by padded row
@@ -193,13 +206,14 @@ int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStr
         const LevelGeom& L = G.L[l];
         if (l == 0) {
             const dim3 block(64, 4);
-            const dim3 grid(((L.w + 15) / 16 + block.x - 1) / block.x, (L.h + block.y - 1) / block.y, nframes);
+            const dim3 grid(((L.w + 15) / 16 + block.x - 1) / block.x, (L.h + 2 * PYR_HALO + block.y - 1) / block.y, nframes);
             pyr_level0_kernel<<<grid, block, 0, s>>>(D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
                                                      L.pyr, L.pitch, L.plane_bytes, L.w, L.h);
         } else if (L.tapw) {
             const LevelGeom& P = G.L[l - 1];
             const dim3 block(64, 4);
-            const dim3 grid(((L.w + 3) / 4 + block.x - 1) / block.x, (L.h + block.y * PYRF_ROWS - 1) / (block.y * PYRF_ROWS), nframes);
+            const dim3 grid(((L.w + 3) / 4 + 2 + block.x - 1) / block.x,
+                            (L.h + 2 * PYR_HALO + block.y * PYRF_ROWS - 1) / (block.y * PYRF_ROWS), nframes);
             pyr_resize_fast_kernel<<<grid, block, 0, s>>>(P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch, L.plane_bytes,
                                                           L.w, L.h, L.tapw, L.tapy);
         } else {
