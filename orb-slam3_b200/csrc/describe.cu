@@ -86,6 +86,9 @@ int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int la
 #define BL_RT 32
 #define BL_BY 4
 #define BL_OUTW 30            // output words per warp row
+#ifndef BL_MINB
+#define BL_MINB 8              // CTAs per SM the register allocation is held to (64 registers)
+#endif
 #define HALO_ROWS_BLUR 3      // rows of reflect-101 halo the pyramid planes carry (written by the pyramid kernels)
 
 template <int PH>
@@ -118,7 +121,7 @@ __device__ __forceinline__ uint32_t blur_hword(uint32_t El, uint32_t Ol, uint32_
 // same rotation as the E/O window).  A slot's old value is consumed (unpacked) BEFORE the load that
 // refills it is issued — the refill's address carries a fake dependency on the unpacked value — so the
 // load lands in the slot's own register and nothing waits for it until 7 rows later.
-__global__ void __launch_bounds__(32 * BL_BY)
+__global__ void __launch_bounds__(32 * BL_BY, BL_MINB)
 blur_kernel(FrameGeom G)
 {
     const int lane = threadIdx.x, warp = threadIdx.y;
