@@ -38,6 +38,38 @@ def level_dims(rows, cols, isf):
     return [(int(np.rint(np.float32(rows) * s)), int(np.rint(np.float32(cols) * s))) for s in isf]
 
 
+STAGE_KERNEL = {"pyramid": "pyr_resize_fast_kernel", "fast": "fast_band_kernel", "blur": "blur_kernel"}
+UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+
+def profiled_traffic(stage, frames_per_launch):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the stage's kernel from the newest committed full-set
+    ncu summary (profiles/*_full_summary.csv, captured at 512 frames per launch), scaled to this launch."""
+    import csv
+    files = sorted((ROOT / "profiles").glob("*_full_summary.csv"))
+    if not files:
+        return None, None
+    f = files[-1]
+    rows = list(csv.reader(open(f)))
+    hdr = rows[0]
+    cols = {}
+    for i, h in enumerate(hdr):
+        for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            if h.startswith(key):
+                cols[key] = (i, UNIT.get(h[h.index("[") + 1:h.index("]")], None))
+    if len(cols) != 2 or any(u is None for _, u in cols.values()):
+        return None, None
+    tot = 0.0; frames = None
+    for r in rows[1:]:
+        if r[1].strip() == STAGE_KERNEL[stage]:
+            tot += sum(float(r[i]) * u for i, u in cols.values())
+            g = [int(x) for x in r[2].strip("()").split(",")]
+            frames = max(g[1], g[2]) if stage != "pyramid" else g[2]
+    if tot == 0.0 or not frames:
+        return None, None
+    return tot * frames_per_launch / frames, f"{f.name} ({frames} frames per launch, scaled to {frames_per_launch})"
+
+
 def algorithmic_bytes(rows, cols, isf, nkp_mean):
     """SURVEY.md 8(d) primary figure, per frame and per stage (compulsory stage-wise HBM traffic)."""
     px = [h * w for h, w in level_dims(rows, cols, isf)]
@@ -286,8 +318,9 @@ def main():
     stage_gbs = {k: ab[k] * B / (stage[i] * 1e-3) / 1e9 for k, i in hbm_stages.items() if stage[i] > 0}
     dom = max(hbm_stages, key=lambda k: stage[hbm_stages[k]])
     whole = sum(ab.values()) * B / (ms / args.steps * 1e-3) / 1e9
+    traffic, traffic_src = profiled_traffic(dom, B)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": stage_gbs[dom], "peak": peak_gbs, "unit": "GB/s",
-                "frac": stage_gbs[dom] / peak_gbs, "traffic": None, "peak_source": peak_src,
+                "frac": stage_gbs[dom] / peak_gbs, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "bytes_per_launch": ab[dom] * B,
                 "stage_ms": {k: float(stage[i]) for i, k in enumerate(STAGES)},
                 "stage_gbs": stage_gbs,
