@@ -68,6 +68,28 @@ __device__ __forceinline__ int cand_rank(uint32_t key, const LevelGeom& L)
     return ((ci * L.nCols + cj) << 14) | ((Y3 - ci * L.hCell) << 7) | (X3 - cj * L.wCell);
 }
 
+// Candidate passes are chains of dependent lookups (global label -> shared tables -> shared atomic); four
+// candidates per thread are fetched before any of them is processed so that their global loads overlap.
+#define OCT_UNROLL 4
+template <class F>
+__device__ __forceinline__ void for_cands(const uint32_t* __restrict__ cand, const uint32_t* kcode, int n, F body)
+{
+    for (int i0 = threadIdx.x; i0 < n; i0 += OCT_UNROLL * OCT_THREADS) {
+        uint32_t key[OCT_UNROLL], code[OCT_UNROLL];
+#pragma unroll
+        for (int u = 0; u < OCT_UNROLL; u++) {
+            const int i = i0 + u * OCT_THREADS;
+            key[u] = i < n ? cand[i] : 0u;
+            code[u] = (kcode && i < n) ? kcode[i] : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < OCT_UNROLL; u++) {
+            const int i = i0 + u * OCT_THREADS;
+            if (i < n) body(i, key[u], (int)code[u]);
+        }
+    }
+}
+
 template <bool SMEM>
 __global__ void __launch_bounds__(OCT_THREADS)
 octree_kernel(FrameGeom G, DevBuffers D)
@@ -101,12 +123,12 @@ octree_kernel(FrameGeom G, DevBuffers D)
         BX[0][i] = x0 | (x1 << 16); BY[0][i] = H << 16; CN[0][i] = 0;
     }
     __syncthreads();
-    for (int i = tid; i < n; i += OCT_THREADS) {
-        int r = (int)__fdiv_rn((float)KEY_X(cand[i]), L.hX);         // vpIniNodes[kp.pt.x/hX], :740
+    for_cands(cand, nullptr, n, [&](int i, uint32_t k, int) {
+        int r = (int)__fdiv_rn((float)KEY_X(k), L.hX);               // vpIniNodes[kp.pt.x/hX], :740
         r = min(r, L.nIni - 1);
         kcode[i] = 4 * r;
         atomicAdd(&CN[0][r], 1);
-    }
+    });
     __syncthreads();
     for (int i = tid; i < L.nIni; i += OCT_THREADS) aA[i] = CN[0][i] > 0;
     __syncthreads();
@@ -130,16 +152,15 @@ octree_kernel(FrameGeom G, DevBuffers D)
         // ---- candidate step: relabel, child inside the new node, next round's per-child counts ----
         {
             const int* bx = BX[cur]; const int* by = BY[cur]; const int* cn = CN[cur]; int* cc = CC[cur];
-            for (int i = tid; i < n; i += OCT_THREADS) {
-                const int p = NP4[kcode[i]];
+            for_cands(cand, kcode, n, [&](int i, uint32_t k, int code) {
+                const int p = NP4[code];
                 int c = 0;
                 if (!finish && cn[p] > 1) {
-                    const uint32_t k = cand[i];
                     c = child_of(KEY_X(k), KEY_Y(k), bx[p], by[p]);
                     atomicAdd(&cc[4 * p + c], 1);
                 }
                 kcode[i] = 4 * p + c;
-            }
+            });
         }
         __syncthreads();
         if (finish) break;
@@ -259,21 +280,19 @@ octree_kernel(FrameGeom G, DevBuffers D)
     int* bestrank = aB;
     for (int i = tid; i < size; i += OCT_THREADS) { best[i] = 0; bestrank[i] = 0x7FFFFFFF; }
     __syncthreads();
-    for (int i = tid; i < n; i += OCT_THREADS) atomicMax(&best[kcode[i] >> 2], (int)KEY_S(cand[i]));
+    for_cands(cand, kcode, n, [&](int, uint32_t k, int code) { atomicMax(&best[code >> 2], (int)KEY_S(k)); });
     __syncthreads();
-    for (int i = tid; i < n; i += OCT_THREADS) {
-        const uint32_t k = cand[i];
-        const int nd = kcode[i] >> 2;
+    for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
+        const int nd = code >> 2;
         if ((int)KEY_S(k) == best[nd]) atomicMin(&bestrank[nd], cand_rank(k, L));
-    }
+    });
     __syncthreads();
     uint32_t* sel = D.sel + (long long)f * G.sel_per_frame + L.sel_base;
     const int nout = min(size, L.sel_cap);
-    for (int i = tid; i < n; i += OCT_THREADS) {
-        const uint32_t k = cand[i];
-        const int nd = kcode[i] >> 2;
+    for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
+        const int nd = code >> 2;
         if (nd < nout && (int)KEY_S(k) == best[nd] && cand_rank(k, L) == bestrank[nd]) sel[nd] = k;
-    }
+    });
     if (tid == 0) D.selcnt[f * G.nlevels + lvl] = nout;
 }
 
