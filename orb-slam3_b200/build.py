@@ -17,7 +17,7 @@ def needs_build() -> bool:
     if not lib.exists():
         return True
     t = lib.stat().st_mtime
-    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.h")) + list((PKG.parent / "include").glob("*"))
+    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.h")) + list(CSRC.glob("*.inc")) + list((PKG.parent / "include").glob("*"))
     return any(d.stat().st_mtime > t for d in deps)
 
 
