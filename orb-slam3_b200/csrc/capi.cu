@@ -151,9 +151,12 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     DevBuffers D;
     memset(&D, 0, sizeof(D));
     const size_t B = (size_t)max_batch;
-    D.in_pitch = (cols + 15) / 16 * 16;       // rows 16-byte aligned for the level-0 copy; == cols for the usual widths
+    // device rows keep the caller's stride when the frames are packed back to back (one linear H2D copy, also
+    // for odd widths such as KITTI's 1241); otherwise rows are 16-byte aligned.  Room for strides up to +64 bytes.
+    D.in_pitch = (cols + 15) / 16 * 16;
+    D.in_pitch_cap = D.in_pitch + 64;
     int rc = 0;
-    rc |= dev_alloc(e, &D.input, B * rows * D.in_pitch);
+    rc |= dev_alloc(e, &D.input, B * rows * D.in_pitch_cap + 64);
     for (int l = 0; l < G.nlevels && !rc; l++) {
         rc |= dev_alloc(e, &G.L[l].pyr, B * G.L[l].plane_bytes);
         rc |= dev_alloc(e, &G.L[l].blur, B * G.L[l].plane_bytes);
@@ -214,9 +217,12 @@ static int upload_frames(orbx_extractor* e, int slot0, int nframes, const uint8_
                          cudaStream_t st)
 {
     const FrameGeom& G = e->G;
+    const bool packed = frame_stride == step * (size_t)G.rows && step <= (size_t)e->D.in_pitch_cap;
+    // all frames resident at one time share one row stride: the caller's when packed, else the aligned one
+    e->D.in_pitch = packed ? (int)step : (G.cols + 15) / 16 * 16;
     uint8_t* dst = e->D.input + (size_t)slot0 * G.rows * e->D.in_pitch;
-    if (step == (size_t)e->D.in_pitch && frame_stride == step * (size_t)G.rows) {
-        // densely packed frames with the device pitch: one linear copy
+    if (packed) {
+        // frames back to back: one linear copy, whatever the alignment of the rows (the level-0 kernel copes)
         CUDA_TRY(cudaMemcpyAsync(dst, imgs, (size_t)nframes * G.rows * step, cudaMemcpyHostToDevice, st));
     } else if (frame_stride == step * (size_t)G.rows) {
         // frames are back to back: one 2-D copy of nframes*rows rows

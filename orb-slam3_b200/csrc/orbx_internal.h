@@ -1,7 +1,8 @@
 // orbx_internal.h — device data layout and kernel launchers of the B200 ORB front-end.
 //
 // HBM layout (all per extractor handle, sized for `batch` frame slots):
-//   input    : batch frames, rows x in_pitch (in_pitch = cols rounded up to 16: uint4 row copies).
+//   input    : batch frames, rows x in_pitch (the caller's row stride when its frames are packed back to back,
+//              else cols rounded up to 16).
 //   pyr[l]   : batch planes of level l, each `prow x pitch` bytes; interior pixel (0,0) at byte
 //              ORBX_YOFF*pitch + ORBX_XOFF (XOFF=32 keeps interior rows 32B-sector aligned, pitch is a
 //              multiple of 128).  The hot path writes the interior plus a thin reflect-101 halo (3 rows
@@ -99,7 +100,8 @@ struct FrameGeom {
 
 struct DevBuffers {
     uint8_t* input;           // batch x rows x in_pitch staging of the uploaded frames
-    int in_pitch;
+    int in_pitch;             // row stride of the frames currently resident (the caller's stride when packed)
+    int in_pitch_cap;         // largest row stride the staging buffer is sized for
     const BandDesc* bands;    // [bands_per_frame] FAST work units (same for every frame)
     uint32_t* cand;           // [batch][cand_per_frame]
     uint32_t* candnode;       // [batch][cand_per_frame]  quadtree scratch: node of each candidate

@@ -19,6 +19,8 @@ __device__ __forceinline__ int reflect101(int i, int n)
 // word past column w-1 are mirrored too).  The full 19-px border of mvImagePyramid is NOT materialised
 // on the hot path; orbx_get_pyramid_level(padded) fills it on demand with the two kernels below.
 #define PYR_HALO 3
+// ALIGNED: source rows start on 16-byte boundaries (uint4 loads); otherwise five aligned words + funnel shifts
+template <bool ALIGNED>
 __global__ void __launch_bounds__(256)
 pyr_level0_kernel(const uint8_t* __restrict__ in, int in_pitch, long long in_frame_bytes,
                   uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h)
@@ -29,7 +31,15 @@ pyr_level0_kernel(const uint8_t* __restrict__ in, int in_pitch, long long in_fra
     const int f = blockIdx.z;
     const uint8_t* srow = in + (long long)f * in_frame_bytes + (long long)reflect101(y, h) * in_pitch;
     uint8_t* drow = out + (long long)f * plane_bytes + (long long)(ORBX_YOFF + y) * pitch + ORBX_XOFF;
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(srow) + qi);
+    uint4 v;
+    if (ALIGNED) v = __ldg(reinterpret_cast<const uint4*>(srow) + qi);
+    else {
+        const uint8_t* sp = srow + 16 * qi;
+        const uint32_t sh = ((uint32_t)(uintptr_t)sp & 3u) * 8u;
+        const uint32_t* ap = reinterpret_cast<const uint32_t*>(sp - (sh >> 3));
+        const uint32_t w0 = __ldg(ap), w1 = __ldg(ap + 1), w2 = __ldg(ap + 2), w3 = __ldg(ap + 3), w4 = __ldg(ap + 4);
+        v = make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh));
+    }
     reinterpret_cast<uint4*>(drow)[qi] = v;
     if (qi == 0) *reinterpret_cast<uint32_t*>(drow - 4) = __byte_perm(v.x, v.y, 0x1234);      // columns 4,3,2,1
     if (qi * 16 + 16 >= w) {                                  // last group: words nw-1 and nw
@@ -207,8 +217,12 @@ int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStr
         if (l == 0) {
             const dim3 block(64, 4);
             const dim3 grid(((L.w + 15) / 16 + block.x - 1) / block.x, (L.h + 2 * PYR_HALO + block.y - 1) / block.y, nframes);
-            pyr_level0_kernel<<<grid, block, 0, s>>>(D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
-                                                     L.pyr, L.pitch, L.plane_bytes, L.w, L.h);
+            if ((D.in_pitch & 15) == 0 && ((uintptr_t)D.input & 15) == 0)
+                pyr_level0_kernel<true><<<grid, block, 0, s>>>(D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
+                                                               L.pyr, L.pitch, L.plane_bytes, L.w, L.h);
+            else
+                pyr_level0_kernel<false><<<grid, block, 0, s>>>(D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
+                                                                L.pyr, L.pitch, L.plane_bytes, L.w, L.h);
         } else if (L.tapw) {
             const LevelGeom& P = G.L[l - 1];
             const dim3 block(64, 4);
