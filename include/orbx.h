@@ -231,6 +231,21 @@ int orbx_search_for_triangulation(int device,
                                   int bOnlyStereo, int bCoarse, int checkOrientation, int variant,
                                   int32_t* matches12);
 
+/* int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches)
+ * include/ORBmatcher.h:67, src/ORBmatcher.cc:314-547 (F.Nleft == -1 branch; mode 0) and
+ * int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12)
+ * include/ORBmatcher.h:68, src/ORBmatcher.cc:955-1105 (mode 1).  Side 1 = the keyframe whose map points are
+ * matched: valid1 = map point present and !isBad().  Side 2 = the Frame (mode 0: valid2 may be NULL) or the
+ * second keyframe (mode 1: valid2 = map point present and !isBad()).  FeatureVectors as CSR (see
+ * orbx_search_for_triangulation).  matches out: mode 0 -> [n2], index of the side-1 keypoint whose map point
+ * each Frame keypoint receives; mode 1 -> [n1], index of the matched side-2 keypoint.  Returns nmatches. */
+int orbx_search_by_bow(int device, int mode,
+                       const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,
+                       const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                       const orbx_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* valid2,
+                       const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                       float nnratio, int checkOrientation, int32_t* matches);
+
 /* void ORBmatcher::ComputeThreeMaxima(vector<int>* histo, const int L, int&, int&, int&)
  * include/ORBmatcher.h:107, src/ORBmatcher.cc:2863-2905 on the bin sizes (host, no device work). */
 void orbx_three_maxima(const int32_t* sizes, int L, int32_t* ind1, int32_t* ind2, int32_t* ind3);

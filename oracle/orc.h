@@ -145,6 +145,14 @@ int   orc_search_for_triangulation(const orc_keypoint* kps1, const uint8_t* desc
                                    int bOnlyStereo, int bCoarse, int checkOrientation, int variant,
                                    int32_t* matches12);
 
+/* ORBmatcher::SearchByBoW (KF,Frame: mode 0, src/ORBmatcher.cc:314-547; KF,KF: mode 1, :955-1105) */
+int   orc_search_by_bow(int mode,
+                        const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,
+                        const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                        const orc_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* valid2,
+                        const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                        float nnratio, int checkOrientation, int32_t* matches);
+
 #ifdef __cplusplus
 }
 #endif

@@ -498,3 +498,59 @@ int orc_search_for_triangulation(const orc_keypoint* kps1, const uint8_t* desc1,
     hist_free(&H); free(vbMatched2);
     return nmatches;
 }
+
+/* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (src/ORBmatcher.cc:314-547, F.Nleft == -1;
+ * mode 0) and SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&) (:955-1105; mode 1).  valid1 / valid2 =
+ * map point present and not bad (valid2 may be NULL in mode 0: a Frame keypoint only needs to be unmatched).
+ * matches out: mode 0 -> [n2] side-1 index per Frame keypoint, mode 1 -> [n1] side-2 index per KF1 keypoint. */
+int orc_search_by_bow(int mode,
+                      const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,
+                      const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                      const orc_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* valid2,
+                      const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                      float nnratio, int checkOrientation, int32_t* matches)
+{
+    int nmatches = 0;
+    rot_hist H; hist_init(&H);
+    const float factor = HISTO_LENGTH / 360.0f;                               /* :334 / :978 */
+    uint8_t* matched2 = (uint8_t*)calloc((size_t)(n2 > 0 ? n2 : 1), 1);
+    const int nout = mode == 0 ? n2 : n1;
+    for (int i = 0; i < nout; i++) matches[i] = -1;
+    int a = 0, b = 0;
+    while (a < nn1 && b < nn2) {
+        if (fv1_node[a] < fv2_node[b]) { a++; continue; }
+        if (fv1_node[a] > fv2_node[b]) { b++; continue; }
+        for (int p1 = fv1_start[a]; p1 < fv1_start[a + 1]; p1++) {
+            const int idx1 = fv1_idx[p1];
+            if (!valid1[idx1]) continue;                                      /* :343-349 / :1006-1011 */
+            int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+            for (int p2 = fv2_start[b]; p2 < fv2_start[b + 1]; p2++) {
+                const int idx2 = fv2_idx[p2];
+                if (matched2[idx2]) continue;                                 /* :365 / :1038 */
+                if (valid2 && !valid2[idx2]) continue;                        /* :1038-1045 */
+                const int dist = orc_hamming256(desc1 + 32 * (size_t)idx1, desc2 + 32 * (size_t)idx2);
+                if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+                else if (dist < bestDist2) bestDist2 = dist;
+            }
+            const int low = mode == 0 ? bestDist1 <= TH_LOW : bestDist1 < TH_LOW;   /* :431 / :1064 */
+            if (low && (float)bestDist1 < nnratio * (float)bestDist2) {       /* :433 / :1066 */
+                matched2[bestIdx2] = 1;
+                if (mode == 0) matches[bestIdx2] = idx1; else matches[idx1] = bestIdx2;
+                if (checkOrientation)
+                    hist_push(&H, hist_bin(kps1[idx1].angle, kps2[bestIdx2].angle, factor), mode == 0 ? bestIdx2 : idx1);
+                nmatches++;
+            }
+        }
+        a++; b++;
+    }
+    if (checkOrientation) {                                                   /* :520-544 / :1090-1110 */
+        int ind1, ind2, ind3;
+        orc_three_maxima(H.n, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int bi = 0; bi < HISTO_LENGTH; bi++) {
+            if (bi == ind1 || bi == ind2 || bi == ind3) continue;
+            for (int j = 0; j < H.n[bi]; j++) { matches[H.v[bi][j]] = -1; nmatches--; }
+        }
+    }
+    hist_free(&H); free(matched2);
+    return nmatches;
+}

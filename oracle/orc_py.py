@@ -103,6 +103,9 @@ class Oracle:
         L.orc_search_for_initialization.restype = C.c_int
         L.orc_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                                     C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.orc_search_by_bow.restype = C.c_int
+        L.orc_search_by_bow.argtypes = [C.c_int] + ([C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_int]) * 2 + \
+            [C.c_float, C.c_int, C.c_void_p]
         L.orc_search_for_triangulation.restype = C.c_int
         L.orc_search_for_triangulation.argtypes = ([C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int]) * 2 + \
             [C.c_void_p] * 4 + [C.c_int] * 4 + [C.c_void_p]
@@ -361,3 +364,20 @@ def search_for_triangulation(o: Oracle, kf1: dict, kf2: dict, sf2, sigma2_2, ep,
                                           int(only_stereo), int(coarse), int(check_orientation), int(variant),
                                           m12.ctypes.data)
     return nm, m12
+
+
+def search_by_bow(o: Oracle, mode: int, kf1: dict, kf2: dict, nnratio: float, check_orientation: bool = True):
+    """kfN: dict kps, desc, valid (or None for side 2 in mode 0), fv_node, fv_start, fv_idx."""
+    def prep(k):
+        return (np.ascontiguousarray(k["kps"], KP_DTYPE), np.ascontiguousarray(k["desc"], np.uint8),
+                None if k.get("valid") is None else np.ascontiguousarray(k["valid"], np.uint8),
+                np.ascontiguousarray(k["fv_node"], np.int32), np.ascontiguousarray(k["fv_start"], np.int32),
+                np.ascontiguousarray(k["fv_idx"], np.int32))
+    a, b = prep(kf1), prep(kf2)
+    out = np.full(len(b[0]) if mode == 0 else len(a[0]), -1, np.int32)
+    args = []
+    for k in (a, b):
+        args += [k[0].ctypes.data, k[1].ctypes.data, len(k[0]), _p(k[2]), k[3].ctypes.data, k[4].ctypes.data,
+                 k[5].ctypes.data, len(k[3])]
+    nm = o.L.orc_search_by_bow(int(mode), *args, nnratio, int(check_orientation), out.ctypes.data)
+    return nm, out

@@ -9,4 +9,5 @@ from . import binding, synth  # noqa: F401
 from .binding import KP_DTYPE, OrbxError  # noqa: F401
 from .extractor import ORBextractor, DescriptorDistance  # noqa: F401
 from .matcher import (ComputeStereoMatches, knn2_hamming, SearchByProjection, SearchByProjectionFrame,  # noqa: F401
-                      SearchForInitialization, SearchForTriangulation, GetFeaturesInArea, ComputeThreeMaxima)
+                      SearchForInitialization, SearchForTriangulation, SearchByBoW, GetFeaturesInArea,
+                      ComputeThreeMaxima)

@@ -76,6 +76,8 @@ SYMBOLS = {
                                                  C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]),
     "orbx_search_for_triangulation": (C.c_int, [C.c_int] + ([C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int]) * 2 +
                                       [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] + [C.c_int] * 4 + [C.c_void_p]),
+    "orbx_search_by_bow": (C.c_int, [C.c_int, C.c_int] + ([C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_int]) * 2 +
+                           [C.c_float, C.c_int, C.c_void_p]),
     "orbx_three_maxima": (None, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 

@@ -174,6 +174,27 @@ struct ORBmatcherGPU {
         return r;
     }
 
+    // int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches) include/ORBmatcher.h:67,
+    // src/ORBmatcher.cc:314-547 (bKeyFrames = false) and SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&)
+    // include/ORBmatcher.h:68, :955-1105 (bKeyFrames = true).  For side 1 (and side 2 of the KF-KF form)
+    // hasMapPoint must mean "map point present and !isBad()".  matches: KF-Frame -> per Frame keypoint the index of
+    // the KF keypoint whose map point it receives; KF-KF -> per KF1 keypoint the matched KF2 keypoint.
+    int SearchByBoW(const KeyFrameView& KF1, const KeyFrameView& KF2, bool bKeyFrames, std::vector<int32_t>& matches, int device = 0) const
+    {
+        const int n1 = (int)KF1.mvKeysUn->size(), n2 = (int)KF2.mvKeysUn->size();
+        matches.assign((size_t)(bKeyFrames ? n1 : n2), -1);
+        const int r = orbx_search_by_bow(
+            device, bKeyFrames ? 1 : 0,
+            reinterpret_cast<const orbx_keypoint*>(KF1.mvKeysUn->data()), KF1.mDescriptors->data, n1, KF1.hasMapPoint.data(),
+            KF1.fvNode.data(), KF1.fvStart.data(), KF1.fvIdx.data(), (int)KF1.fvNode.size(),
+            reinterpret_cast<const orbx_keypoint*>(KF2.mvKeysUn->data()), KF2.mDescriptors->data, n2,
+            bKeyFrames ? KF2.hasMapPoint.data() : nullptr,
+            KF2.fvNode.data(), KF2.fvStart.data(), KF2.fvIdx.data(), (int)KF2.fvNode.size(),
+            mfNNratio, mbCheckOrientation ? 1 : 0, matches.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchByBoW: ") + orbx_last_error());
+        return r;
+    }
+
     // void ORBmatcher::ComputeThreeMaxima(vector<int>* histo, const int L, int&, int&, int&)
     // include/ORBmatcher.h:107, src/ORBmatcher.cc:2863-2905
     static void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3)

@@ -88,9 +88,14 @@ int main()
         const float ep[2] = {-1e6f, 0.f};
         std::vector<std::pair<size_t, size_t>> vMatchedPairs;
         const int nTri = matcherTri.SearchForTriangulation(K1, K2, F12, ep, vMatchedPairs, false);
-        std::printf("second view: %zu kps; SearchForInitialization %d, SearchByProjection(Frame,Frame) %d, SearchForTriangulation %d\n",
-                    mvKeys2.size(), nIni, nProj, nTri);
-        return (matched > 0 && nIni > 0 && nProj > 0 && nTri > 0 && (int)vMatchedPairs.size() == nTri) ? 0 : 2;
+        // Tracking::TrackReferenceKeyFrame: matcher(0.7, true).SearchByBoW(mpReferenceKF, mCurrentFrame, vpMapPointMatches)
+        ORBmatcherGPU matcherBoW(0.7f, true);
+        K1.hasMapPoint.assign(mvKeys.size(), 1);
+        std::vector<int32_t> bowMatches;
+        const int nBoW = matcherBoW.SearchByBoW(K1, K2, false, bowMatches);
+        std::printf("second view: %zu kps; SearchForInitialization %d, SearchByProjection(Frame,Frame) %d, SearchForTriangulation %d, "
+                    "SearchByBoW %d\n", mvKeys2.size(), nIni, nProj, nTri, nBoW);
+        return (matched > 0 && nIni > 0 && nProj > 0 && nTri > 0 && nBoW > 0 && (int)vMatchedPairs.size() == nTri) ? 0 : 2;
     } catch (const std::exception& e) {
         std::fprintf(stderr, "error: %s\n", e.what());
         return 1;

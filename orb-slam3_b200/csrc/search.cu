@@ -162,6 +162,8 @@ struct TriArgs {
     float sf2[ORBX_MAX_LEVELS], sigma2_2[ORBX_MAX_LEVELS];
     float epx, epy, F[9];
     int bOnlyStereo, bCoarse;
+    int mode;                        // 0: SearchForTriangulation gates, 1: SearchByBoW (ratio-bounded distances)
+    float nnratio;
     int* it_base; int* it_cnt;
     int2* cand; int cap;             // (idx2 | epi_ok << 30, dist)
     int* total;
@@ -197,14 +199,17 @@ tri_candidates_kernel(TriArgs A)
             int idx2 = 0, dist = 0, epi = 0;
             if (ok) {
                 idx2 = A.fv2_idx[j];
-                if (A.has_mp2[idx2]) ok = false;                                             // :1218
+                if (A.has_mp2[idx2]) ok = false;                                             // :1218 (BoW: keypoint 2 not usable)
                 const bool bStereo2 = A.uRight2 && A.uRight2[idx2] >= 0;
                 if (A.bOnlyStereo && !bStereo2) ok = false;                                  // :1224-1226
                 if (ok) {
                     dist = ham256(a0, a1, A.desc2[2 * idx2], A.desc2[2 * idx2 + 1]);
-                    if (dist > TH_LOW) ok = false;                                           // :1231
+                    if (A.mode == 0) { if (dist > TH_LOW) ok = false; }                      // :1231
+                    // SearchByBoW accepts best1 <= TH_LOW when best1 < ratio * best2 (:431-433): a distance with
+                    // ratio * d > TH_LOW can neither win nor make that test fail, so it need not be reported
+                    else { epi = 1; if (__fmul_rn(A.nnratio, (float)dist) > (float)TH_LOW) ok = false; }
                 }
-                if (ok) {
+                if (ok && A.mode == 0) {
                     const orbx_keypoint kp2 = A.kps2[idx2];
                     if (!bStereo1 && !bStereo2) {                                            // :1241-1250
                         const float ex = __fsub_rn(A.epx, kp2.x), ey = __fsub_rn(A.epy, kp2.y);
@@ -506,6 +511,92 @@ extern "C" int orbx_search_for_initialization(int device,
     return nmatches;
 }
 
+
+// ---- host: run the pair kernel over caller (pageable) arrays through the workspace ----
+namespace {
+struct PairHost {
+    const orbx_keypoint* kps1; const uint8_t* desc1; int n1; const float* uRight1;
+    const orbx_keypoint* kps2; const uint8_t* desc2; int n2; const float* uRight2; const uint8_t* skip2;
+    const int32_t* fv2_idx; int len2; const int4* items; int nitems;
+    const float* sf2; const float* sigma2_2; int nlevels; const float* ep; const float* F12;
+    int bOnlyStereo, bCoarse, mode; float nnratio;
+};
+struct PairResult { const int* base; const int* cnt; const int2* cand; int total; };
+
+int run_pairs(int device, const PairHost& in, PairResult* out)
+{
+    Workspace& W = t_ws;
+    int rc = W.bind(device);
+    if (rc != ORBX_OK) return rc;
+    const size_t m1 = (size_t)in.n1, m2 = (size_t)in.n2;
+    const int nitems = in.nitems, len2 = in.len2;
+    int cap = t_tri_cap;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        Carver c;
+        const size_t o_k1 = c.take(m1 * sizeof(orbx_keypoint)), o_d1 = c.take(m1 * 32), o_u1 = c.take(in.uRight1 ? m1 * 4 : 0);
+        const size_t o_k2 = c.take(m2 * sizeof(orbx_keypoint)), o_d2 = c.take(m2 * 32), o_u2 = c.take(in.uRight2 ? m2 * 4 : 0);
+        const size_t o_h2 = c.take(m2), o_f2 = c.take((size_t)len2 * 4), o_it = c.take((size_t)nitems * 16);
+        const size_t o_total = c.take(4);
+        const size_t in_bytes = c.off;
+        const size_t o_base = c.take((size_t)nitems * 4), o_cnt = c.take((size_t)nitems * 4);
+        const size_t small_end = c.off;
+        const size_t o_cand = c.take((size_t)cap * 8);
+        rc = W.reserve(c.off, small_end + (size_t)cap * 8 + 256);
+        if (rc != ORBX_OK) return rc;
+        char* h = W.h; char* d = W.d;
+        memcpy(h + o_k1, in.kps1, m1 * sizeof(orbx_keypoint)); memcpy(h + o_d1, in.desc1, m1 * 32);
+        memcpy(h + o_k2, in.kps2, m2 * sizeof(orbx_keypoint)); memcpy(h + o_d2, in.desc2, m2 * 32);
+        if (in.uRight1) memcpy(h + o_u1, in.uRight1, m1 * 4);
+        if (in.uRight2) memcpy(h + o_u2, in.uRight2, m2 * 4);
+        memcpy(h + o_h2, in.skip2, m2); memcpy(h + o_f2, in.fv2_idx, (size_t)len2 * 4); memcpy(h + o_it, in.items, (size_t)nitems * 16);
+        *(int*)(h + o_total) = 0;
+        CUDA_TRYS(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, W.s));
+        TriArgs A;
+        A.kps1 = (const orbx_keypoint*)(d + o_k1); A.desc1 = (const uint4*)(d + o_d1); A.uRight1 = in.uRight1 ? (const float*)(d + o_u1) : nullptr;
+        A.kps2 = (const orbx_keypoint*)(d + o_k2); A.desc2 = (const uint4*)(d + o_d2); A.uRight2 = in.uRight2 ? (const float*)(d + o_u2) : nullptr;
+        A.has_mp2 = (const uint8_t*)(d + o_h2); A.fv2_idx = (const int*)(d + o_f2);
+        A.nitems = nitems; A.items = (const int4*)(d + o_it);
+        for (int l = 0; l < ORBX_MAX_LEVELS; l++) {
+            A.sf2[l] = (in.sf2 && l < in.nlevels) ? in.sf2[l] : 0.f;
+            A.sigma2_2[l] = (in.sigma2_2 && l < in.nlevels) ? in.sigma2_2[l] : 0.f;
+        }
+        A.epx = in.ep ? in.ep[0] : 0.f; A.epy = in.ep ? in.ep[1] : 0.f;
+        for (int k = 0; k < 9; k++) A.F[k] = in.F12 ? in.F12[k] : 0.f;
+        A.bOnlyStereo = in.bOnlyStereo; A.bCoarse = in.bCoarse; A.mode = in.mode; A.nnratio = in.nnratio;
+        A.it_base = (int*)(d + o_base); A.it_cnt = (int*)(d + o_cnt); A.cand = (int2*)(d + o_cand); A.cap = cap; A.total = (int*)(d + o_total);
+        tri_candidates_kernel<<<(nitems + TRI_WARPS - 1) / TRI_WARPS, TRI_WARPS * 32, 0, W.s>>>(A);
+        CUDA_TRYS(cudaGetLastError());
+        CUDA_TRYS(cudaMemcpyAsync(h + o_total, d + o_total, small_end - o_total, cudaMemcpyDeviceToHost, W.s));
+        CUDA_TRYS(cudaStreamSynchronize(W.s));
+        const int total = *(const int*)(h + o_total);
+        if (total > cap) { cap = total + total / 4; t_tri_cap = cap; continue; }
+        if (total > 0) {
+            CUDA_TRYS(cudaMemcpyAsync(h + small_end, d + o_cand, (size_t)total * 8, cudaMemcpyDeviceToHost, W.s));
+            CUDA_TRYS(cudaStreamSynchronize(W.s));
+        }
+        out->base = (const int*)(h + o_base); out->cnt = (const int*)(h + o_cnt); out->cand = (const int2*)(h + small_end); out->total = total;
+        return ORBX_OK;
+    }
+    orbx_set_error("pair candidate lists did not fit after regrowing");
+    return ORBX_ERR_CAPACITY;
+}
+
+// merge of two sorted FeatureVectors (e.g. src/ORBmatcher.cc:1176-1178, 1316-1329): one work item per keypoint
+// of the first keyframe that passes `take`, in the reference's visiting order
+template <class Take>
+void merge_feature_vectors(const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                           const int32_t* fv2_node, const int32_t* fv2_start, int nn2, Take take, std::vector<int4>* items)
+{
+    for (int a = 0, b = 0; a < nn1 && b < nn2;) {
+        if (fv1_node[a] < fv2_node[b]) { a++; continue; }
+        if (fv1_node[a] > fv2_node[b]) { b++; continue; }
+        for (int p1 = fv1_start[a]; p1 < fv1_start[a + 1]; p1++)
+            if (take(fv1_idx[p1])) items->push_back(make_int4(fv1_idx[p1], fv2_start[b], fv2_start[b + 1], 0));
+        a++; b++;
+    }
+}
+}  // namespace
+
 extern "C" int orbx_search_for_triangulation(int device,
                                              const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
                                              const float* uRight1,
@@ -532,70 +623,21 @@ extern "C" int orbx_search_for_triangulation(int device,
     // merge of the two sorted FeatureVectors (:1176-1178, 1316-1329) -> one work item per eligible KF1 keypoint
     std::vector<int4> items;
     items.reserve(len1);
-    for (int a = 0, b = 0; a < nn1 && b < nn2;) {
-        if (fv1_node[a] < fv2_node[b]) { a++; continue; }
-        if (fv1_node[a] > fv2_node[b]) { b++; continue; }
-        for (int p1 = fv1_start[a]; p1 < fv1_start[a + 1]; p1++) {
-            const int idx1 = fv1_idx[p1];
-            if (has_mp1[idx1]) continue;                                          // :1188-1192
-            if (bOnlyStereo && !(uRight1 && uRight1[idx1] >= 0)) continue;        // :1194-1198
-            items.push_back(make_int4(idx1, fv2_start[b], fv2_start[b + 1], 0));
-        }
-        a++; b++;
-    }
+    merge_feature_vectors(fv1_node, fv1_start, fv1_idx, nn1, fv2_node, fv2_start, nn2, [&](int idx1) {
+        if (has_mp1[idx1]) return false;                                          // :1188-1192
+        return !(bOnlyStereo && !(uRight1 && uRight1[idx1] >= 0));                // :1194-1198
+    }, &items);
     const int nitems = (int)items.size();
     if (nitems == 0) return 0;
 
-    Workspace& W = t_ws;
-    int rc = W.bind(device);
-    if (rc != ORBX_OK) return rc;
-    const size_t m1 = (size_t)n1, m2 = (size_t)n2;
-    int cap = t_tri_cap, total = 0;
-    const int* h_base = nullptr; const int* h_cnt = nullptr; const int2* h_cand = nullptr;
-    for (int attempt = 0;; attempt++) {
-        if (attempt == 2) { orbx_set_error("triangulation candidate lists did not fit after regrowing"); return ORBX_ERR_CAPACITY; }
-        Carver c;
-        const size_t o_k1 = c.take(m1 * sizeof(orbx_keypoint)), o_d1 = c.take(m1 * 32), o_u1 = c.take(uRight1 ? m1 * 4 : 0);
-        const size_t o_k2 = c.take(m2 * sizeof(orbx_keypoint)), o_d2 = c.take(m2 * 32), o_u2 = c.take(uRight2 ? m2 * 4 : 0);
-        const size_t o_h2 = c.take(m2), o_f2 = c.take((size_t)len2 * 4), o_it = c.take((size_t)nitems * 16);
-        const size_t o_total = c.take(4);
-        const size_t in_bytes = c.off;
-        const size_t o_base = c.take((size_t)nitems * 4), o_cnt = c.take((size_t)nitems * 4);
-        const size_t small_end = c.off;
-        const size_t o_cand = c.take((size_t)cap * 8);
-        rc = W.reserve(c.off, small_end + (size_t)cap * 8 + 256);
+    PairHost in = {kps1, desc1, n1, uRight1, kps2, desc2, n2, uRight2, has_mp2, fv2_idx, len2, items.data(), nitems,
+                   sf2, sigma2_2, nlevels, ep, F12, bOnlyStereo, bCoarse, 0, 0.f};
+    PairResult R;
+    {
+        const int rc = run_pairs(device, in, &R);
         if (rc != ORBX_OK) return rc;
-        char* h = W.h; char* d = W.d;
-        memcpy(h + o_k1, kps1, m1 * sizeof(orbx_keypoint)); memcpy(h + o_d1, desc1, m1 * 32);
-        memcpy(h + o_k2, kps2, m2 * sizeof(orbx_keypoint)); memcpy(h + o_d2, desc2, m2 * 32);
-        if (uRight1) memcpy(h + o_u1, uRight1, m1 * 4);
-        if (uRight2) memcpy(h + o_u2, uRight2, m2 * 4);
-        memcpy(h + o_h2, has_mp2, m2); memcpy(h + o_f2, fv2_idx, (size_t)len2 * 4); memcpy(h + o_it, items.data(), (size_t)nitems * 16);
-        *(int*)(h + o_total) = 0;
-        CUDA_TRYS(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, W.s));
-        TriArgs A;
-        A.kps1 = (const orbx_keypoint*)(d + o_k1); A.desc1 = (const uint4*)(d + o_d1); A.uRight1 = uRight1 ? (const float*)(d + o_u1) : nullptr;
-        A.kps2 = (const orbx_keypoint*)(d + o_k2); A.desc2 = (const uint4*)(d + o_d2); A.uRight2 = uRight2 ? (const float*)(d + o_u2) : nullptr;
-        A.has_mp2 = (const uint8_t*)(d + o_h2); A.fv2_idx = (const int*)(d + o_f2);
-        A.nitems = nitems; A.items = (const int4*)(d + o_it);
-        for (int l = 0; l < ORBX_MAX_LEVELS; l++) { A.sf2[l] = l < nlevels ? sf2[l] : 0.f; A.sigma2_2[l] = l < nlevels ? sigma2_2[l] : 0.f; }
-        A.epx = ep[0]; A.epy = ep[1];
-        for (int k = 0; k < 9; k++) A.F[k] = F12[k];
-        A.bOnlyStereo = bOnlyStereo; A.bCoarse = bCoarse;
-        A.it_base = (int*)(d + o_base); A.it_cnt = (int*)(d + o_cnt); A.cand = (int2*)(d + o_cand); A.cap = cap; A.total = (int*)(d + o_total);
-        tri_candidates_kernel<<<(nitems + TRI_WARPS - 1) / TRI_WARPS, TRI_WARPS * 32, 0, W.s>>>(A);
-        CUDA_TRYS(cudaGetLastError());
-        CUDA_TRYS(cudaMemcpyAsync(h + o_total, d + o_total, small_end - o_total, cudaMemcpyDeviceToHost, W.s));
-        CUDA_TRYS(cudaStreamSynchronize(W.s));
-        total = *(const int*)(h + o_total);
-        if (total > cap) { cap = total + total / 4; t_tri_cap = cap; continue; }
-        if (total > 0) {
-            CUDA_TRYS(cudaMemcpyAsync(h + small_end, d + o_cand, (size_t)total * 8, cudaMemcpyDeviceToHost, W.s));
-            CUDA_TRYS(cudaStreamSynchronize(W.s));
-        }
-        h_base = (const int*)(h + o_base); h_cnt = (const int*)(h + o_cnt); h_cand = (const int2*)(h + small_end);
-        break;
     }
+    const int* h_base = R.base; const int* h_cnt = R.cnt; const int2* h_cand = R.cand;
     // sequential part, :1210-1313
     int nmatches = 0;
     RotHist H(variant ? 1.0f / HISTO_LENGTH : HISTO_LENGTH / 360.0f);             // :1166 / :1441
@@ -623,6 +665,72 @@ extern "C" int orbx_search_for_triangulation(int device,
         for (int b = 0; b < HISTO_LENGTH; b++) {
             if (b == i1 || b == i2 || b == i3) continue;
             for (int idx1 : H.bin[b]) { matches12[idx1] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+extern "C" int orbx_search_by_bow(int device, int mode,
+                                  const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,
+                                  const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                                  const orbx_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* valid2,
+                                  const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                                  float nnratio, int checkOrientation, int32_t* matches)
+{
+    if ((mode != 0 && mode != 1) || n1 < 0 || n2 < 0 || nn1 < 0 || nn2 < 0 || !matches ||
+        (n1 > 0 && (!kps1 || !desc1 || !valid1)) || (n2 > 0 && (!kps2 || !desc2)) || (mode == 1 && n2 > 0 && !valid2) ||
+        (nn1 > 0 && (!fv1_node || !fv1_start || !fv1_idx)) || (nn2 > 0 && (!fv2_node || !fv2_start || !fv2_idx))) {
+        orbx_set_error("bad search_by_bow arguments"); return ORBX_ERR_ARG;
+    }
+    const int nout = mode == 0 ? n2 : n1;            // per Frame keypoint (KF,F) / per KF1 keypoint (KF,KF)
+    for (int i = 0; i < nout; i++) matches[i] = -1;
+    if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
+    if (n1 == 0 || n2 == 0 || nn1 == 0 || nn2 == 0) return 0;
+    const int len1 = fv1_start[nn1], len2 = fv2_start[nn2];
+    for (int i = 0; i < len1; i++) if (fv1_idx[i] < 0 || fv1_idx[i] >= n1) { orbx_set_error("fv1_idx[%d] out of range", i); return ORBX_ERR_ARG; }
+    for (int i = 0; i < len2; i++) if (fv2_idx[i] < 0 || fv2_idx[i] >= n2) { orbx_set_error("fv2_idx[%d] out of range", i); return ORBX_ERR_ARG; }
+    std::vector<int4> items;
+    items.reserve(len1);
+    merge_feature_vectors(fv1_node, fv1_start, fv1_idx, nn1, fv2_node, fv2_start, nn2,
+                          [&](int idx1) { return valid1[idx1] != 0; }, &items);   // :343-349 / :1006-1011: pMP && !pMP->isBad()
+    const int nitems = (int)items.size();
+    if (nitems == 0) return 0;
+    std::vector<uint8_t> skip2((size_t)n2, 0);
+    if (valid2) for (int i = 0; i < n2; i++) skip2[i] = valid2[i] == 0;           // :1038-1045
+    PairHost in = {kps1, desc1, n1, nullptr, kps2, desc2, n2, nullptr, skip2.data(), fv2_idx, len2, items.data(), nitems,
+                   nullptr, nullptr, 0, nullptr, nullptr, 0, 0, 1, nnratio};
+    PairResult R;
+    {
+        const int rc = run_pairs(device, in, &R);
+        if (rc != ORBX_OK) return rc;
+    }
+    int nmatches = 0;
+    RotHist H(HISTO_LENGTH / 360.0f);                                             // :334 / :978
+    std::vector<uint8_t> taken2((size_t)n2, 0);                                   // vpMapPointMatches[idxF] != NULL / vbMatched2
+    for (int it = 0; it < nitems; it++) {
+        const int idx1 = items[it].x;
+        const int2* c = R.cand + R.base[it];
+        int bestDist1 = 256, bestDist2 = 256, bestIdx2 = -1;
+        for (int k = 0; k < R.cnt[it]; k++) {                                     // :361-384 / :1028-1062
+            const int idx2 = c[k].x & 0x3FFFFFFF, dist = c[k].y;
+            if (taken2[idx2]) continue;
+            if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        const bool low = mode == 0 ? bestDist1 <= TH_LOW : bestDist1 < TH_LOW;    // :431 (<=) / :1064 (<)
+        if (low && (float)bestDist1 < nnratio * (float)bestDist2) {               // :433 / :1066
+            taken2[bestIdx2] = 1;
+            if (mode == 0) matches[bestIdx2] = idx1; else matches[idx1] = bestIdx2;
+            if (checkOrientation) H.push(kps1[idx1].angle, kps2[bestIdx2].angle, mode == 0 ? bestIdx2 : idx1);
+            nmatches++;
+        }
+    }
+    if (checkOrientation) {                                                       // :520-544 / :1090-1110
+        int i1, i2, i3;
+        H.top3(&i1, &i2, &i3);
+        for (int b = 0; b < HISTO_LENGTH; b++) {
+            if (b == i1 || b == i2 || b == i3) continue;
+            for (int v : H.bin[b]) { matches[v] = -1; nmatches--; }
         }
     }
     return nmatches;

@@ -139,6 +139,25 @@ def SearchForTriangulation(kf1: dict, kf2: dict, sf2, sigma2_2, ep, F12, only_st
     return nm, m12
 
 
+def SearchByBoW(mode: int, kf1: dict, kf2: dict, nnratio: float, check_orientation: bool = True, device: int = 0):
+    """ORBmatcher::SearchByBoW — mode 0: (KeyFrame, Frame) src/ORBmatcher.cc:314, mode 1: (KeyFrame, KeyFrame) :955.
+    kfN: dict kps, desc, valid (None allowed for the Frame side of mode 0), fv_node, fv_start, fv_idx.
+    Returns (nmatches, matches) — mode 0: per Frame keypoint the KF keypoint index, mode 1: per KF1 keypoint the KF2 one."""
+    def prep(k):
+        return (np.ascontiguousarray(k["kps"], KP_DTYPE), np.ascontiguousarray(k["desc"], np.uint8),
+                None if k.get("valid") is None else np.ascontiguousarray(k["valid"], np.uint8),
+                np.ascontiguousarray(k["fv_node"], np.int32), np.ascontiguousarray(k["fv_start"], np.int32),
+                np.ascontiguousarray(k["fv_idx"], np.int32))
+    a, b = prep(kf1), prep(kf2)
+    out = np.full(len(b[0]) if mode == 0 else len(a[0]), -1, np.int32)
+    args = []
+    for k in (a, b):
+        args += [k[0].ctypes.data, k[1].ctypes.data, len(k[0]), _p(k[2]), k[3].ctypes.data, k[4].ctypes.data,
+                 k[5].ctypes.data, len(k[3])]
+    nm = check(binding.load().orbx_search_by_bow(device, int(mode), *args, nnratio, int(check_orientation), out.ctypes.data))
+    return nm, out
+
+
 def ComputeThreeMaxima(sizes):
     """ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:2863) on the bin sizes."""
     sizes = np.ascontiguousarray(sizes, np.int32)

@@ -192,3 +192,24 @@ def test_search_empty_inputs(pkg):
     assert pkg.SearchForInitialization(z, zd, k, d, b, np.zeros((0, 2), np.float32))[0] == 0
     nm, m12, _ = pkg.SearchForInitialization(k, d, z, zd, b, np.zeros((50, 2), np.float32))
     assert nm == 0 and np.all(m12 == -1)
+
+
+@pytest.mark.parametrize("mode,nnratio,orient,seed", [(0, 0.7, True, 41), (0, 0.9, False, 42), (1, 0.8, True, 43), (1, 0.6, True, 44)])
+def test_search_by_bow(pkg, orc, oracle, mode, nnratio, orient, seed):
+    """TrackReferenceKeyFrame / Relocalization (mode 0: matcher(0.7|0.75,true)) and the loop-closing KF-KF search (mode 1)."""
+    rng = np.random.default_rng(seed)
+    rows, cols = 480, 752
+    n = 1600
+    k1, d1, pool, src = _frame(pkg, rng, n, rows, cols)
+    k2, d2, perm = _moved(pkg, rng, k1, d1, rows, cols, flips=(0, 50))
+    node1 = (src % 89).astype(np.int32); node2 = node1[perm]
+    node2 = np.where(rng.random(n) < 0.05, rng.integers(0, 89, n), node2).astype(np.int32)
+    kf1 = dict(kps=k1, desc=d1, valid=(rng.random(n) < 0.7).astype(np.uint8))
+    kf2 = dict(kps=k2, desc=d2, valid=None if mode == 0 else (rng.random(n) < 0.7).astype(np.uint8))
+    kf1["fv_node"], kf1["fv_start"], kf1["fv_idx"] = _feature_vector(rng, node1, 0.02)
+    kf2["fv_node"], kf2["fv_start"], kf2["fv_idx"] = _feature_vector(rng, node2, 0.02)
+    nm_o, m_o = orc.search_by_bow(oracle, mode, kf1, kf2, nnratio, orient)
+    nm_g, m_g = pkg.SearchByBoW(mode, kf1, kf2, nnratio, orient)
+    assert nm_o > 40, nm_o
+    assert nm_g == nm_o == int(np.sum(m_o >= 0))
+    assert np.array_equal(m_g, m_o), f"{np.sum(m_g != m_o)} matches differ"

@@ -105,3 +105,23 @@ def test_oracle_triangulation_identity(orc, oracle):
     kf2 = dict(kf); kf2["has_mp"] = np.ones(n, np.uint8)
     assert orc.search_for_triangulation(oracle, kf, kf2, SF, SF * SF, ep, F, False, True, True, 0)[0] == 0
     assert orc.search_for_triangulation(oracle, kf, kf, SF, SF * SF, ep, F, True, True, True, 0)[0] == 0   # bOnlyStereo, mono frames
+
+
+def test_oracle_bow_identity(orc, oracle):
+    rng = np.random.default_rng(4)
+    n = 200
+    kps, desc = _unique_frame(orc, rng, n)
+    node = (np.arange(n) % 13).astype(np.int32)
+    nodes = np.unique(node); start = [0]; idx = []
+    for nd in nodes:
+        idx += np.nonzero(node == nd)[0].tolist(); start.append(len(idx))
+    kf = dict(kps=kps, desc=desc, valid=np.ones(n, np.uint8), fv_node=nodes, fv_start=np.array(start, np.int32),
+              fv_idx=np.array(idx, np.int32))
+    for mode in (0, 1):
+        nm, m = orc.search_by_bow(oracle, mode, kf, kf, 0.7, True)
+        assert nm == n and np.array_equal(m, np.arange(n))
+    half = dict(kf); half["valid"] = (np.arange(n) % 2).astype(np.uint8)
+    nm, m = orc.search_by_bow(oracle, 0, half, kf, 0.7, True)         # only valid side-1 keypoints are matched
+    assert nm == n // 2 and np.array_equal(np.nonzero(m >= 0)[0], np.arange(1, n, 2))
+    nm, m = orc.search_by_bow(oracle, 1, kf, half, 0.7, True)         # mode 1 also needs a valid side-2 keypoint
+    assert nm == n // 2 and np.all(m[::2] == -1)
