@@ -203,6 +203,21 @@ int orbx_search_by_projection_frame(int device,
                                     float th, float mbf, int bForward, int bBackward, int checkOrientation,
                                     const uint8_t* cur_held, int32_t* assign);
 
+/* int ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound,
+ * const float th, const int ORBdist) include/ORBmatcher.h:54, src/ORBmatcher.cc:2723-2862 (relocalisation).
+ * One row per keyframe keypoint i: descriptor of its map point, projection uv into the current camera
+ * (:2756-2758), predicted level (MapPoint::PredictScale, :2778), pKF->mvKeysUn[i].angle, and mp_valid = pMP &&
+ * !isBad() && !sAlreadyFound.count(pMP) && the distance-invariance gate (:2768-2776).  cur_held (may be NULL):
+ * CurrentFrame.mvpMapPoints[i2] != NULL.  assign[n] out as above.  Returns nmatches. */
+int orbx_search_by_projection_keyframe(int device,
+                                       const orbx_keypoint* kps, const uint8_t* desc, int n,
+                                       float minX, float maxX, float minY, float maxY,
+                                       const float* scaleFactors, int nlevels,
+                                       int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                       const int32_t* mp_level, const float* mp_angle, const uint8_t* mp_valid,
+                                       float th, int ORBdist, int checkOrientation,
+                                       const uint8_t* cur_held, int32_t* assign);
+
 /* int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched,
  * vector<int>& vnMatches12, int windowSize) include/ORBmatcher.h:71, src/ORBmatcher.cc:799-943.
  * prev_matched[2*n1] in/out, matches12[n1] out.  Bounds are frame 2's.  Returns nmatches. */

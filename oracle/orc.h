@@ -145,6 +145,12 @@ int   orc_search_for_triangulation(const orc_keypoint* kps1, const uint8_t* desc
                                    int bOnlyStereo, int bCoarse, int checkOrientation, int variant,
                                    int32_t* matches12);
 
+/* ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:2723-2862 */
+int   orc_search_by_projection_keyframe(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* sf,
+                                        int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                        const int32_t* mp_level, const float* mp_angle, const uint8_t* mp_valid,
+                                        float th, int ORBdist, int checkOrientation, const uint8_t* cur_held, int32_t* assign);
+
 /* ORBmatcher::SearchByBoW (KF,Frame: mode 0, src/ORBmatcher.cc:314-547; KF,KF: mode 1, :955-1105) */
 int   orc_search_by_bow(int mode,
                         const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,

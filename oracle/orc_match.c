@@ -554,3 +554,50 @@ int orc_search_by_bow(int mode,
     hist_free(&H); free(matched2);
     return nmatches;
 }
+
+/* ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound, th,
+ * ORBdist), src/ORBmatcher.cc:2723-2862.  Rows = keyframe keypoints: mp_valid folds pMP && !isBad() &&
+ * !sAlreadyFound.count(pMP) and the distance-invariance gate (:2768-2776); mp_level = PredictScale (:2778). */
+int orc_search_by_projection_keyframe(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* sf,
+                                      int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                      const int32_t* mp_level, const float* mp_angle, const uint8_t* mp_valid,
+                                      float th, int ORBdist, int checkOrientation, const uint8_t* cur_held, int32_t* assign)
+{
+    int nmatches = 0;
+    rot_hist H; hist_init(&H);
+    const float factor = HISTO_LENGTH / 360.0f;                               /* :2735 */
+    uint8_t* held = (uint8_t*)calloc((size_t)(n > 0 ? n : 1), 1);
+    int32_t* vIndices2 = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; i++) { assign[i] = -1; if (cur_held) held[i] = cur_held[i] != 0; }
+    for (int i = 0; i < nmp; i++) {
+        if (!mp_valid[i]) continue;
+        const float u = mp_u[i], v = mp_v[i];
+        if (u < g->minX || u > g->maxX) continue;                             /* :2761-2764 */
+        if (v < g->minY || v > g->maxY) continue;
+        const int lvl = mp_level[i];
+        const float radius = th * sf[lvl];                                    /* :2781 */
+        const int nc = orc_grid_query(g, kps, u, v, radius, lvl - 1, lvl + 1, vIndices2, n);   /* :2784 */
+        if (nc == 0) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int k = 0; k < nc; k++) {                                        /* :2795-2811 */
+            const int i2 = vIndices2[k];
+            if (held[i2]) continue;
+            const int dist = orc_hamming256(mp_desc + 32 * (size_t)i, desc + 32 * (size_t)i2);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= ORBdist) {                                            /* :2813-2831 */
+            assign[bestIdx2] = i; held[bestIdx2] = 1;
+            nmatches++;
+            if (checkOrientation) hist_push(&H, hist_bin(mp_angle[i], kps[bestIdx2].angle, factor), bestIdx2);
+        }
+    }
+    if (checkOrientation) {                                                   /* :2834-2857 */
+        int ind1, ind2, ind3;
+        orc_three_maxima(H.n, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int b = 0; b < HISTO_LENGTH; b++)
+            if (b != ind1 && b != ind2 && b != ind3)
+                for (int j = 0; j < H.n[b]; j++) { assign[H.v[b][j]] = -1; nmatches--; }
+    }
+    hist_free(&H); free(held); free(vIndices2);
+    return nmatches;
+}

@@ -103,6 +103,9 @@ class Oracle:
         L.orc_search_for_initialization.restype = C.c_int
         L.orc_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                                     C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.orc_search_by_projection_keyframe.restype = C.c_int
+        L.orc_search_by_projection_keyframe.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 6 + \
+            [C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_search_by_bow.restype = C.c_int
         L.orc_search_by_bow.argtypes = [C.c_int] + ([C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_int]) * 2 + \
             [C.c_float, C.c_int, C.c_void_p]
@@ -381,3 +384,21 @@ def search_by_bow(o: Oracle, mode: int, kf1: dict, kf2: dict, nnratio: float, ch
                  k[5].ctypes.data, len(k[3])]
     nm = o.L.orc_search_by_bow(int(mode), *args, nnratio, int(check_orientation), out.ctypes.data)
     return nm, out
+
+
+def search_by_projection_keyframe(grid: Grid, desc, scale_factors, mp: dict, th: float, orb_dist: int,
+                                  check_orientation: bool = True, cur_held=None):
+    """mp: SoA dict desc,u,v,level,angle,valid."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(grid.kps)
+    assign = np.full(n, -1, np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    held = None if cur_held is None else np.ascontiguousarray(cur_held, np.uint8)
+    f = lambda k, t: np.ascontiguousarray(mp[k], t)
+    md, mu, mv = f("desc", np.uint8), f("u", np.float32), f("v", np.float32)
+    ml, ma, mval = f("level", np.int32), f("angle", np.float32), f("valid", np.uint8)
+    nm = grid.L.orc_search_by_projection_keyframe(grid.g, grid.kps.ctypes.data, desc.ctypes.data, n, sf.ctypes.data,
+                                                  len(mu), md.ctypes.data, mu.ctypes.data, mv.ctypes.data, ml.ctypes.data,
+                                                  ma.ctypes.data, mval.ctypes.data, th, int(orb_dist), int(check_orientation),
+                                                  _p(held), assign.ctypes.data)
+    return nm, assign

@@ -9,5 +9,6 @@ from . import binding, synth  # noqa: F401
 from .binding import KP_DTYPE, OrbxError  # noqa: F401
 from .extractor import ORBextractor, DescriptorDistance  # noqa: F401
 from .matcher import (ComputeStereoMatches, knn2_hamming, SearchByProjection, SearchByProjectionFrame,  # noqa: F401
+                      SearchByProjectionKeyFrame,
                       SearchForInitialization, SearchForTriangulation, SearchByBoW, GetFeaturesInArea,
                       ComputeThreeMaxima)

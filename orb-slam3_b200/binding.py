@@ -71,6 +71,9 @@ SYMBOLS = {
                                                   C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int,
                                                   C.c_int] + [C.c_void_p] * 8 +
                                         [C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "orbx_search_by_projection_keyframe": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                                     C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int,
+                                                     C.c_int] + [C.c_void_p] * 6 + [C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "orbx_search_for_initialization": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                                  C.c_float, C.c_float, C.c_float, C.c_float,
                                                  C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]),

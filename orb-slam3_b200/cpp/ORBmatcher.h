@@ -113,6 +113,31 @@ struct ORBmatcherGPU {
         return r;
     }
 
+    // Rows of a keyframe as SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) visits them.
+    struct KeyFramePointsSoA {
+        std::vector<uint8_t> desc;                     // n x 32: pMP->GetDescriptor()
+        std::vector<float> u, v, angle;                // projection into the current camera, pKF->mvKeysUn[i].angle
+        std::vector<int32_t> level;                    // pMP->PredictScale(dist3D, &CurrentFrame)
+        std::vector<uint8_t> valid;                    // pMP && !isBad() && !sAlreadyFound.count(pMP) && distance gate
+    };
+
+    // int ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound,
+    // const float th, const int ORBdist)  include/ORBmatcher.h:54, src/ORBmatcher.cc:2723-2862
+    int SearchByProjection(const FrameView& CurrentFrame, const KeyFramePointsSoA& kf, float th, int ORBdist,
+                           const std::vector<uint8_t>* curHeld, std::vector<int32_t>& assign, int device = 0) const
+    {
+        const int n = CurrentFrame.N();
+        assign.assign((size_t)n, -1);
+        const int r = orbx_search_by_projection_keyframe(
+            device, CurrentFrame.kps(), CurrentFrame.mDescriptors->data, n,
+            CurrentFrame.mnMinX, CurrentFrame.mnMaxX, CurrentFrame.mnMinY, CurrentFrame.mnMaxY,
+            CurrentFrame.mvScaleFactors->data(), (int)CurrentFrame.mvScaleFactors->size(),
+            (int)kf.u.size(), kf.desc.data(), kf.u.data(), kf.v.data(), kf.level.data(), kf.angle.data(), kf.valid.data(),
+            th, ORBdist, mbCheckOrientation ? 1 : 0, curHeld ? curHeld->data() : nullptr, assign.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchByProjection(Frame,KeyFrame): ") + orbx_last_error());
+        return r;
+    }
+
     // int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched,
     // vector<int>& vnMatches12, int windowSize = 10)  include/ORBmatcher.h:71, src/ORBmatcher.cc:799-943
     int SearchForInitialization(const FrameView& F1, const FrameView& F2, std::vector<cv::Point2f>& vbPrevMatched,

@@ -376,6 +376,51 @@ extern "C" int orbx_window_candidates(int device, const orbx_keypoint* kps, cons
     return run;
 }
 
+
+// Windows + sequential acceptance shared by SearchByProjection(Frame,Frame) (src/ORBmatcher.cc:2545-2601, 2686-2708)
+// and SearchByProjection(Frame,KeyFrame,...) (:2790-2857): best unheld candidate per row, accepted when its
+// distance is <= maxDist; row_obs == NULL means every accepted keypoint becomes held.
+static int projection_replay(int device, const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+                             float minX, float maxX, float minY, float maxY,
+                             int nrows, const uint8_t* row_desc, const float* row_u, const float* row_v,
+                             const float* q_r, const float* q_ur, const int32_t* q_min, const int32_t* q_max,
+                             const float* row_angle, const uint8_t* row_obs, int maxDist, int checkOrientation,
+                             const uint8_t* cur_held, int32_t* assign)
+{
+    WinHost in = {kps, desc, n, uRight, minX, maxX, minY, maxY, nrows, row_desc, row_u, row_v, q_r, q_ur, q_min, q_max};
+    WinResult R;
+    const int rc = run_windows(device, in, &R);
+    if (rc != ORBX_OK) return rc;
+    int nmatches = 0;
+    RotHist H(HISTO_LENGTH / 360.0f);                                             // :2480 / :2735
+    std::vector<uint8_t> held(n, 0);
+    if (cur_held) for (int i = 0; i < n; i++) held[i] = cur_held[i] != 0;
+    for (int i = 0; i < nrows; i++) {
+        const int nc = R.cnt[i];
+        if (nc == 0) continue;
+        const int2* c = R.cand + R.base[i];
+        int bestDist = 256, bestIdx2 = -1;
+        for (int k = 0; k < nc; k++) {
+            if (held[c[k].x]) continue;                                           // :2552-2554 / :2800
+            if (c[k].y < bestDist) { bestDist = c[k].y; bestIdx2 = c[k].x; }
+        }
+        if (bestDist <= maxDist) {
+            assign[bestIdx2] = i;
+            held[bestIdx2] = row_obs ? row_obs[i] != 0 : 1;
+            nmatches++;
+            if (checkOrientation) H.push(row_angle[i], kps[bestIdx2].angle, bestIdx2);
+        }
+    }
+    if (checkOrientation) {                                                       // :2686-2708 / :2834-2857
+        int i1, i2, i3;
+        H.top3(&i1, &i2, &i3);
+        for (int b = 0; b < HISTO_LENGTH; b++)
+            if (b != i1 && b != i2 && b != i3)
+                for (int v : H.bin[b]) { assign[v] = -1; nmatches--; }
+    }
+    return nmatches;
+}
+
 extern "C" int orbx_search_by_projection_frame(int device,
                                                const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
                                                float minX, float maxX, float minY, float maxY,
@@ -413,40 +458,43 @@ extern "C" int orbx_search_by_projection_frame(int device,
         else if (bBackward) { q_min[i] = 0; q_max[i] = oct; }                     // :2535
         else { q_min[i] = oct - 1; q_max[i] = oct + 1; }                          // :2537
     }
-    WinHost in = {kps, desc, n, uRight, minX, maxX, minY, maxY, nlast, last_desc, last_u, last_v, q_r.data(),
-                  uRight ? q_ur.data() : nullptr, q_min.data(), q_max.data()};
-    WinResult R;
-    const int rc = run_windows(device, in, &R);
-    if (rc != ORBX_OK) return rc;
-    // sequential acceptance, :2545-2601
-    int nmatches = 0;
-    RotHist H(HISTO_LENGTH / 360.0f);                                             // :2480
-    std::vector<uint8_t> held(n, 0);
-    if (cur_held) for (int i = 0; i < n; i++) held[i] = cur_held[i] != 0;
-    for (int i = 0; i < nlast; i++) {
-        const int nc = R.cnt[i];
-        if (nc == 0) continue;
-        const int2* c = R.cand + R.base[i];
-        int bestDist = 256, bestIdx2 = -1;
-        for (int k = 0; k < nc; k++) {
-            if (held[c[k].x]) continue;                                           // :2552-2554
-            if (c[k].y < bestDist) { bestDist = c[k].y; bestIdx2 = c[k].x; }
-        }
-        if (bestDist <= TH_HIGH) {
-            assign[bestIdx2] = i;
-            held[bestIdx2] = last_obs[i] != 0;
-            nmatches++;
-            if (checkOrientation) H.push(last_angle[i], kps[bestIdx2].angle, bestIdx2);
-        }
+    return projection_replay(device, kps, desc, n, uRight, minX, maxX, minY, maxY, nlast, last_desc, last_u, last_v,
+                             q_r.data(), uRight ? q_ur.data() : nullptr, q_min.data(), q_max.data(), last_angle, last_obs,
+                             TH_HIGH, checkOrientation, cur_held, assign);
+}
+
+extern "C" int orbx_search_by_projection_keyframe(int device,
+                                                  const orbx_keypoint* kps, const uint8_t* desc, int n,
+                                                  float minX, float maxX, float minY, float maxY,
+                                                  const float* scaleFactors, int nlevels,
+                                                  int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                                  const int32_t* mp_level, const float* mp_angle, const uint8_t* mp_valid,
+                                                  float th, int ORBdist, int checkOrientation,
+                                                  const uint8_t* cur_held, int32_t* assign)
+{
+    if (bad_frame(kps, desc, n, minX, maxX, minY, maxY) || nmp < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors ||
+        (n > 0 && !assign) || (nmp > 0 && (!mp_desc || !mp_u || !mp_v || !mp_level || !mp_angle || !mp_valid))) {
+        orbx_set_error("bad search_by_projection_keyframe arguments"); return ORBX_ERR_ARG;
     }
-    if (checkOrientation) {                                                       // :2686-2708
-        int i1, i2, i3;
-        H.top3(&i1, &i2, &i3);
-        for (int b = 0; b < HISTO_LENGTH; b++)
-            if (b != i1 && b != i2 && b != i3)
-                for (int v : H.bin[b]) { assign[v] = -1; nmatches--; }
+    for (int i = 0; i < n; i++) assign[i] = -1;
+    if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
+    if (n == 0 || nmp == 0) return 0;
+    std::vector<float> q_r(nmp);
+    std::vector<int32_t> q_min(nmp), q_max(nmp);
+    for (int i = 0; i < nmp; i++) {
+        q_r[i] = -1.f; q_min[i] = -1; q_max[i] = -1;
+        if (!mp_valid[i]) continue;                                               // :2749-2753, 2772-2776 (caller's gates)
+        if (mp_u[i] < minX || mp_u[i] > maxX) continue;                           // :2761-2764
+        if (mp_v[i] < minY || mp_v[i] > maxY) continue;
+        const int lvl = mp_level[i];
+        if (lvl < 0 || lvl >= nlevels) { orbx_set_error("map point %d: level %d out of range", i, lvl); return ORBX_ERR_ARG; }
+        q_r[i] = th * scaleFactors[lvl];                                          // :2781
+        if (!(q_r[i] >= 0.f)) { q_r[i] = -1.f; continue; }
+        q_min[i] = lvl - 1; q_max[i] = lvl + 1;                                   // :2784
     }
-    return nmatches;
+    return projection_replay(device, kps, desc, n, nullptr, minX, maxX, minY, maxY, nmp, mp_desc, mp_u, mp_v,
+                             q_r.data(), nullptr, q_min.data(), q_max.data(), mp_angle, nullptr,
+                             ORBdist, checkOrientation, cur_held, assign);
 }
 
 extern "C" int orbx_search_for_initialization(int device,

@@ -102,6 +102,25 @@ def SearchByProjectionFrame(kps, desc, uRight, bounds, scale_factors, last: dict
     return nm, assign
 
 
+def SearchByProjectionKeyFrame(kps, desc, bounds, scale_factors, mp: dict, th: float, orb_dist: int,
+                               check_orientation: bool = True, cur_held=None, device: int = 0):
+    """ORBmatcher::SearchByProjection(Frame& Current, KeyFrame*, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2723).
+    mp: SoA dict desc,u,v,level,angle,valid.  Returns (nmatches, assign)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE); desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(kps)
+    assign = np.full(n, -1, np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    held = None if cur_held is None else np.ascontiguousarray(cur_held, np.uint8)
+    f = lambda k, t: np.ascontiguousarray(mp[k], t)
+    md, mu, mv = f("desc", np.uint8), f("u", np.float32), f("v", np.float32)
+    ml, ma, mval = f("level", np.int32), f("angle", np.float32), f("valid", np.uint8)
+    nm = check(binding.load().orbx_search_by_projection_keyframe(
+        device, kps.ctypes.data, desc.ctypes.data, n, bounds[0], bounds[1], bounds[2], bounds[3], sf.ctypes.data, len(sf),
+        len(mu), md.ctypes.data, mu.ctypes.data, mv.ctypes.data, ml.ctypes.data, ma.ctypes.data, mval.ctypes.data,
+        th, int(orb_dist), int(check_orientation), _p(held), assign.ctypes.data))
+    return nm, assign
+
+
 def SearchForInitialization(kps1, desc1, kps2, desc2, bounds, prev_matched, window: int = 100, nnratio: float = 0.9,
                             check_orientation: bool = True, device: int = 0):
     """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:799).  Returns (nmatches, matches12, prev_matched)."""

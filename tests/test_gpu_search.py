@@ -213,3 +213,25 @@ def test_search_by_bow(pkg, orc, oracle, mode, nnratio, orient, seed):
     assert nm_o > 40, nm_o
     assert nm_g == nm_o == int(np.sum(m_o >= 0))
     assert np.array_equal(m_g, m_o), f"{np.sum(m_g != m_o)} matches differ"
+
+
+@pytest.mark.parametrize("th,orb_dist,orient,seed", [(10.0, 100, True, 51), (3.0, 64, True, 52), (10.0, 100, False, 53)])
+def test_search_by_projection_keyframe(pkg, orc, oracle, th, orb_dist, orient, seed):
+    """Tracking::Relocalization: matcher2(0.9,true).SearchByProjection(mCurrentFrame, vpCandidateKFs[i], sFound, 10, 100) / (…, 3, 64)."""
+    rng = np.random.default_rng(seed)
+    rows, cols = 480, 752
+    n = 1500
+    kkps, kdesc, _, _ = _frame(pkg, rng, n, rows, cols)
+    ckps, cdesc, perm = _moved(pkg, rng, kkps, kdesc, rows, cols)
+    mp = dict(desc=_flip(rng, kdesc.copy(), 0, 10),
+              u=(kkps["x"] + 4.0 + rng.normal(0, 2, n)).astype(np.float32), v=(kkps["y"] - 3.0 + rng.normal(0, 2, n)).astype(np.float32),
+              level=np.clip(kkps["octave"] + rng.choice([-1, 0, 0, 1], n), 0, 7).astype(np.int32), angle=kkps["angle"],
+              valid=(rng.random(n) < 0.8).astype(np.uint8))
+    held = (rng.random(n) < 0.1).astype(np.uint8)
+    bounds = (0.0, float(cols), 0.0, float(rows))
+    g = orc.Grid(oracle, ckps, *bounds)
+    nm_o, as_o = orc.search_by_projection_keyframe(g, cdesc, SF, mp, th, orb_dist, orient, held)
+    nm_g, as_g = pkg.SearchByProjectionKeyFrame(ckps, cdesc, bounds, SF, mp, th, orb_dist, orient, held)
+    assert nm_o > 100, nm_o
+    assert nm_g == nm_o
+    assert np.array_equal(as_g, as_o), f"{np.sum(as_g != as_o)} assignments differ"
