@@ -188,6 +188,7 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     {
         std::vector<BandDesc> bands;
         G.fast_smem = fast_build_bands(G, &bands, &G.fast_warp_words);
+        if (G.fast_smem < 0) { orbx_set_error("cell rows taller than 127 px are not supported"); rc |= ORBX_ERR_GEOMETRY; G.fast_smem = 0; }
         G.bands_per_frame = (int)bands.size();
         BandDesc* db = nullptr;
         if (!rc) rc |= dev_alloc(e, &db, bands.size());

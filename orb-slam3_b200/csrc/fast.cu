@@ -126,11 +126,13 @@ __device__ __forceinline__ void nms_row(const uint32_t (&R)[3][4], uint32_t thr,
     to = __vmaxu2(C[2] & V_o, nb) ^ nb;
 }
 
-// append e to the u16 list at shared address wa when flag != 0: predicated store + bump, no divergent region
+// append the 32-bit entry e to the lane's list at shared address wa when flag != 0: predicated store + bump,
+// no divergent region.  Entry i of lane l lives at word i * 32 + l of the list area, so a push never
+// meets a bank conflict.
 __device__ __forceinline__ void list_push(uint32_t& wa, uint32_t flag, uint32_t e)
 {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p st.shared.u16 [%0], %2;\n\t@p add.u32 %0, %0, 2;\n\t}"
-                 : "+r"(wa) : "r"(flag), "h"((unsigned short)e) : "memory");
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p st.shared.u32 [%0], %2;\n\t@p add.u32 %0, %0, 128;\n\t}"
+                 : "+r"(wa) : "r"(flag), "r"(e) : "memory");
 }
 
 __device__ __forceinline__ void nms_fill(uint32_t (&w)[4], uint32_t l, uint32_t m, uint32_t r)
@@ -167,7 +169,6 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
     const int wi = active ? lane : nw - 1;
     const int x = xa + 4 * wi;
     uint32_t* s_tile = s_dyn + warp * G.fast_warp_words;
-    uint16_t* s_list = reinterpret_cast<uint16_t*>(s_tile + ih * 32);
 
     // ---------------- phase A: score tile ----------------
     {
@@ -204,8 +205,13 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
     }
     __syncwarp();
 
+    // two zero rows under the tile: the NMS loop below runs whole 3-row steps without a row guard
+    s_tile[ih * 32 + lane] = 0;
+    s_tile[(ih + 1) * 32 + lane] = 0;
+    __syncwarp();
+
     // ---------------- phase B1: 3x3 NMS inside each cell, survivors appended to the list ----------------
-    int lc[4];                                        // cell of each of the thread's 4 pixels (0.. inside the item)
+    uint32_t sh[4];                                   // 8 * (cell of each of the thread's 4 pixels, 0.. inside the item)
     uint32_t ML_e = 0, MR_e = 0, ML_o = 0, MR_o = 0, V_e = 0, V_o = 0;
 #pragma unroll
     for (int q = 0; q < 4; q++) {
@@ -216,93 +222,91 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
         const int xin = X3 - j * L.wCell;
         const int cend = ORBX_MINB + min(j * L.wCell + L.wCell + 6, Wr) - 3;      // end of cell j's interior
         const bool lok = valid && xin > 0, rok = valid && xp + 1 < cend;
-        lc[q] = j - bd.cj0;
+        sh[q] = 8u * (uint32_t)(j - bd.cj0);
         const uint32_t ln = (q & 2) ? 0xFFFF0000u : 0x0000FFFFu;
         if (q & 1) { if (lok) ML_o |= ln; if (rok) MR_o |= ln; if (valid) V_o |= ln & 0xFF00FF00u; }
         else       { if (lok) ML_e |= ln; if (rok) MR_e |= ln; if (valid) V_e |= ln & 0xFF00FF00u; }
     }
     const int iniTh = G.iniTh, minTh = min(G.minTh, G.iniTh);
     const uint32_t thr = (uint32_t)(((minTh - 1) << 8) | 0xFF) * 0x00010001u;
-    const uint32_t lt = (1u << lane) - 1u;
-    int cnt = 0;                                      // survivors of this lane
-    const int lcap = (3 * ih) / 2 + 2;                // <= 3 strict maxima per 2 rows of a 4-px column strip (one cell boundary)
-    uint16_t* mylist = s_list + lane * lcap;
+    // one entry per (lane, row) holding a survivor: bits 0,1,16,17 = px 0,1,2,3 survive, bits 8.. = row
+    const uint32_t* mylist = s_tile + (ih + 2) * 32 + lane;
+    int cnt = 0;                                      // entries of this lane
     {
-        const uint32_t* sp = s_tile + wi;
-        const bool hasl = active && wi > 0, hasr = active && wi + 1 < nw;
+        // the first word's left and the last word's right neighbour lie outside every cell interior and
+        // are masked by ML/MR: those lanes re-read their own word instead of a guarded load
+        const uint32_t* pm = s_tile + wi;
+        const uint32_t* pl = pm - (wi > 0 ? 1 : 0);
+        const uint32_t* pr = pm + (wi + 1 < nw ? 1 : 0);
         uint32_t R[3][4];
         const uint32_t wa0 = (uint32_t)__cvta_generic_to_shared(mylist);
-        uint32_t wa = wa0;
+        uint32_t wa = wa0, rr = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++) R[0][k] = 0;
-        nms_fill(R[1], hasl ? sp[-1] : 0u, sp[0], hasr ? sp[1] : 0u);
+        nms_fill(R[1], pl[0], pm[0], pr[0]);
 #define NMS_STEP(PH)                                                                                        \
-        if (rb + PH < ih) {                                                                                 \
-            const int r = rb + PH;                                                                          \
-            if (r + 1 < ih) { const uint32_t* q = sp + (r + 1) * 32;                                        \
-                              nms_fill(R[(PH + 2) % 3], hasl ? q[-1] : 0u, q[0], hasr ? q[1] : 0u); }       \
-            else { R[(PH + 2) % 3][0] = R[(PH + 2) % 3][1] = R[(PH + 2) % 3][2] = R[(PH + 2) % 3][3] = 0; } \
+        {                                                                                                   \
+            nms_fill(R[(PH + 2) % 3], pl[(PH + 1) * 32], pm[(PH + 1) * 32], pr[(PH + 1) * 32]);             \
             uint32_t te, to;                                                                                \
             nms_row<PH>(R, thr, ML_e, MR_e, ML_o, MR_o, V_e, V_o, te, to);                                  \
-            {                                                  /* survivors go to the lane's private list */         \
-                const uint32_t e = (uint32_t)((r << 7) | (4 * wi));                                          \
-                list_push(wa, te & 0xFFFFu, e);                                                             \
-                list_push(wa, to & 0xFFFFu, e + 1);                                                         \
-                list_push(wa, te >> 16, e + 2);                                                             \
-                list_push(wa, to >> 16, e + 3);                                                             \
-            }                                                                                               \
+            const uint32_t fl = __vminu2(te, 0x00010001u) + 2u * __vminu2(to, 0x00010001u);                 \
+            list_push(wa, fl, fl | (rr + PH * 256u));                                                       \
         }
 #pragma unroll 1
-        for (int rb = 0; rb < ih; rb += 3) { NMS_STEP(0) NMS_STEP(1) NMS_STEP(2) }
+        for (int rb = 0; rb < ih; rb += 3) {          // rows >= ih are zero: no survivors there
+            NMS_STEP(0) NMS_STEP(1) NMS_STEP(2)
+            pl += 96; pm += 96; pr += 96; rr += 768u;
+        }
 #undef NMS_STEP
-        cnt = (int)((wa - wa0) >> 1);
+        cnt = (int)((wa - wa0) >> 7);
     }
     __syncwarp();
 
     // ---------------- phase B2: per-cell retry rule (:1118-1125) and emission ----------------
-    const int ncell = bd.cj1 - bd.cj0;
-    const uint8_t* s_score = reinterpret_cast<const uint8_t*>(s_tile);
-    const int xrel = xa - ORBX_MINB, yrel = ys - ORBX_MINB;
-    int nhi[FAST_MAXCELLS], nlo[FAST_MAXCELLS];        // survivors >= iniTh / in [minTh, iniTh) per cell (uniform)
+    // every lane walks its own entries; a pixel's cell is a per-lane constant (sh[q]), so the per-cell
+    // counts are byte fields of one register per class, summed over the warp afterwards
+    const int xrel = xa - ORBX_MINB + 4 * wi, yrel = ys - ORBX_MINB;
+    const uint32_t* srow = s_tile + wi;
+    uint32_t hic = 0, loc = 0;                         // per-cell byte counters: >= iniTh / in [minTh, iniTh)
+    for (int i = 0; i < cnt; i++) {
+        const uint32_t e = mylist[i * 32];
+        const uint32_t sw = srow[((e >> 8) & 127u) * 32];
 #pragma unroll
-    for (int c = 0; c < FAST_MAXCELLS; c++) nhi[c] = nlo[c] = 0;
-    const int maxcnt = __reduce_max_sync(0xffffffffu, cnt);
-    for (int i = 0; i < maxcnt; i++) {                 // entry i of every lane's list
-        const bool valid = i < cnt;
-        const int e = valid ? mylist[i] : 0;
-        const int px = e & 127, r = e >> 7;
-        const int sc = s_score[r * 128 + px];
-        const int cell = (xrel + px - 3) / L.wCell - bd.cj0;
-        const bool hi = valid && sc >= iniTh;
-#pragma unroll
-        for (int c = 0; c < FAST_MAXCELLS; c++) {
-            if (c < ncell) {
-                nhi[c] += __popc(__ballot_sync(0xffffffffu, hi && cell == c));
-                nlo[c] += __popc(__ballot_sync(0xffffffffu, valid && !hi && cell == c));
-            }
+        for (int q = 0; q < 4; q++) {
+            const uint32_t bit = (e >> ((q & 1) + (q & 2) * 8)) & 1u;
+            const uint32_t hi = ((sw >> (8 * q)) & 255u) >= (uint32_t)iniTh ? bit : 0u;
+            hic += hi << sh[q];
+            loc += (bit ^ hi) << sh[q];
         }
     }
-    int total = 0;
+    // a lane holds <= 4 * ih < 256 survivors per cell; the warp sums need 16-bit fields
+    const uint32_t h02 = __reduce_add_sync(0xffffffffu, hic & 0x00FF00FFu);
+    const uint32_t h13 = __reduce_add_sync(0xffffffffu, (hic >> 8) & 0x00FF00FFu);
+    uint32_t zm = 0;                                   // byte c = 0xFF when cell c has no survivor >= iniTh
+    if ((h02 & 0xFFFFu) == 0) zm |= 0x000000FFu;
+    if ((h13 & 0xFFFFu) == 0) zm |= 0x0000FF00u;
+    if ((h02 >> 16) == 0)     zm |= 0x00FF0000u;
+    if ((h13 >> 16) == 0)     zm |= 0xFF000000u;
+    const int mine = __dp4a(hic + (loc & zm), 0x01010101u, 0u);      // emitted by this lane
+    int incl = mine;
 #pragma unroll
-    for (int c = 0; c < FAST_MAXCELLS; c++) total += nhi[c] > 0 ? nhi[c] : nlo[c];
+    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
     if (total == 0) return;
     int base = 0;
     if (lane == 0) base = atomicAdd(&D.candcnt[f * G.nlevels + bd.lvl], total);
     base = __shfl_sync(0xffffffffu, base, 0);
-    uint32_t* cand = D.cand + (long long)f * G.cand_per_frame + L.cand_base;
-    for (int i = 0; i < maxcnt; i++) {
-        const bool valid = i < cnt;
-        const int e = valid ? mylist[i] : 0;
-        const int px = e & 127, r = e >> 7;
-        const int sc = s_score[r * 128 + px];
-        const int cell = (xrel + px - 3) / L.wCell - bd.cj0;
-        int ch = nhi[0];
+    uint32_t* out = D.cand + (long long)f * G.cand_per_frame + L.cand_base + base + (incl - mine);
+    for (int i = 0; i < cnt; i++) {
+        const uint32_t e = mylist[i * 32];
+        const uint32_t r = (e >> 8) & 63u;
+        const uint32_t sw = srow[r * 32];
 #pragma unroll
-        for (int c = 1; c < FAST_MAXCELLS; c++) if (cell == c) ch = nhi[c];
-        const bool emit = valid && (sc >= iniTh || ch == 0);
-        const uint32_t m = __ballot_sync(0xffffffffu, emit);
-        if (emit) cand[base + __popc(m & lt)] = MAKE_KEY(xrel + px, yrel + r, sc);
-        base += __popc(m);
+        for (int q = 0; q < 4; q++) {
+            const uint32_t sc = (sw >> (8 * q)) & 255u;
+            const bool bit = (e >> ((q & 1) + (q & 2) * 8)) & 1u;
+            if (bit && (sc >= (uint32_t)iniTh || ((zm >> sh[q]) & 1u))) *out++ = MAKE_KEY(xrel + q, yrel + r, sc);
+        }
     }
 }
 
@@ -336,7 +340,8 @@ int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out, int* warp_w
             }
         }
     }
-    *warp_words = ihmax * 32 + 16 * ((3 * ihmax) / 2 + 2);      // S tile + 32 lane-private u16 lists of 3*ih/2+2 survivors
+    if (ihmax > 127) return -1;                    // row field of a list entry, byte counters of phase B2
+    *warp_words = (ihmax + 2) * 32 + ihmax * 32;   // S tile + 2 zero rows, then one 32-bit list entry per (lane, row)
     return FAST_WARPS * *warp_words * 4;
 }
 
