@@ -288,25 +288,38 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
     if ((h02 >> 16) == 0)     zm |= 0x00FF0000u;
     if ((h13 >> 16) == 0)     zm |= 0xFF000000u;
     const int mine = __dp4a(hic + (loc & zm), 0x01010101u, 0u);      // emitted by this lane
-    int incl = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
-    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    const int total = __reduce_add_sync(0xffffffffu, mine);
     if (total == 0) return;
     int base = 0;
     if (lane == 0) base = atomicAdd(&D.candcnt[f * G.nlevels + bd.lvl], total);
     base = __shfl_sync(0xffffffffu, base, 0);
-    uint32_t* out = D.cand + (long long)f * G.cand_per_frame + L.cand_base + base + (incl - mine);
-    for (int i = 0; i < cnt; i++) {
-        const uint32_t e = mylist[i * 32];
-        const uint32_t r = (e >> 8) & 63u;
+    // entry i of every lane is written side by side (neighbouring candidates then fall into different
+    // quadtree nodes more often than a lane-major order would give).  Up to three pixels of a 4-px row can be
+    // strict 3x3 maxima of their cells (two on either side of a cell boundary plus one two pixels away):
+    // three ballots rank the lanes.
+    uint32_t* out = D.cand + (long long)f * G.cand_per_frame + L.cand_base + base;
+    const uint32_t lt = (1u << lane) - 1u;
+    const int maxcnt = __reduce_max_sync(0xffffffffu, cnt);
+    for (int i = 0; i < maxcnt; i++) {
+        const uint32_t e = i < cnt ? mylist[i * 32] : 0u;
+        const uint32_t r = (e >> 8) & 127u;
         const uint32_t sw = srow[r * 32];
+        bool em[4];
+        int c = 0;
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const uint32_t sc = (sw >> (8 * q)) & 255u;
             const bool bit = (e >> ((q & 1) + (q & 2) * 8)) & 1u;
-            if (bit && (sc >= (uint32_t)iniTh || ((zm >> sh[q]) & 1u))) *out++ = MAKE_KEY(xrel + q, yrel + r, sc);
+            em[q] = bit && (sc >= (uint32_t)iniTh || ((zm >> sh[q]) & 1u));
+            c += em[q];
         }
+        const uint32_t b1 = __ballot_sync(0xffffffffu, c >= 1), b2 = __ballot_sync(0xffffffffu, c >= 2),
+                       b3 = __ballot_sync(0xffffffffu, c >= 3);
+        int pos = __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+            if (em[q]) out[pos++] = MAKE_KEY(xrel + q, yrel + r, (sw >> (8 * q)) & 255u);
+        out += __popc(b1) + __popc(b2) + __popc(b3);
     }
 }
 
