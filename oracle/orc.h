@@ -61,6 +61,15 @@ int   orc_hamming256(const void* a, const void* b);      /* ORBmatcher::Descript
 /* BFMatcher(NORM_HAMMING).knnMatch(k=2): out_idx/out_dist are [nq][2]; missing = -1 */
 void  orc_bf_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* out_idx, int32_t* out_dist);
 
+/* ---- frame preparation in front of operator() (orc_prepare.c) ---- */
+/* cv::remap(src, dst, mapx, mapy, INTER_LINEAR) with CV_32FC1 maps, BORDER_CONSTANT 0; 1, 3 or 4 channels */
+void  orc_remap_linear_u8(const uint8_t* src, int srows, int scols, size_t sstep, int channels,
+                          const float* mapx, const float* mapy, size_t mstep_floats,
+                          uint8_t* dst, int drows, int dcols, size_t dstep);
+/* cvtColor(COLOR_{RGB,BGR,RGBA,BGRA}2GRAY): channels 3 or 4, rgb != 0 when the first channel is R */
+void  orc_cvt_gray_u8(const uint8_t* src, int rows, int cols, size_t sstep, int channels, int rgb,
+                      uint8_t* dst, size_t dstep);
+
 /* ---- ORBextractor (orc_extractor.c) ---- */
 orc_extractor* orc_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);
 void  orc_destroy(orc_extractor* e);

@@ -53,6 +53,11 @@ class Oracle:
         for name in ("orc_features_per_level", "orc_umax"):
             getattr(L, name).restype = i32p
             getattr(L, name).argtypes = [C.c_void_p]
+        L.orc_remap_linear_u8.restype = None
+        L.orc_remap_linear_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p,
+                                          C.c_size_t, C.c_void_p, C.c_int, C.c_int, C.c_size_t]
+        L.orc_cvt_gray_u8.restype = None
+        L.orc_cvt_gray_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
         L.orc_levels.argtypes = [C.c_void_p]
         L.orc_level_dims.argtypes = [C.c_void_p, C.c_int, i32p, i32p]
         L.orc_level_plane.restype = C.c_void_p
@@ -141,6 +146,35 @@ class Oracle:
         dst = np.empty_like(img)
         self.L.orc_gaussian7x7_s2(img.ctypes.data, img.shape[0], img.shape[1], img.strides[0], dst.ctypes.data, dst.strides[0])
         return dst
+
+    def remap(self, src: np.ndarray, mapx: np.ndarray, mapy: np.ndarray) -> np.ndarray:
+        """cv2.remap(src, mapx, mapy, INTER_LINEAR); src HxW or HxWxC u8, maps float32 of the output size."""
+        src = np.ascontiguousarray(src, np.uint8)
+        ch = 1 if src.ndim == 2 else src.shape[2]
+        mapx = np.ascontiguousarray(mapx, np.float32); mapy = np.ascontiguousarray(mapy, np.float32)
+        dr, dc = mapx.shape
+        dst = np.empty((dr, dc) if src.ndim == 2 else (dr, dc, ch), np.uint8)
+        self.L.orc_remap_linear_u8(_ptr(src, C.c_void_p), src.shape[0], src.shape[1], src.strides[0], ch,
+                                   _ptr(mapx, C.c_void_p), _ptr(mapy, C.c_void_p), dc,
+                                   _ptr(dst, C.c_void_p), dr, dc, dst.strides[0])
+        return dst
+
+    def gray(self, src: np.ndarray, rgb: bool) -> np.ndarray:
+        """cv2.cvtColor(src, COLOR_{RGB,BGR}[A]2GRAY)."""
+        src = np.ascontiguousarray(src, np.uint8)
+        dst = np.empty(src.shape[:2], np.uint8)
+        self.L.orc_cvt_gray_u8(_ptr(src, C.c_void_p), src.shape[0], src.shape[1], src.strides[0], src.shape[2],
+                               int(bool(rgb)), _ptr(dst, C.c_void_p), dst.strides[0])
+        return dst
+
+    def prepare(self, src: np.ndarray, mapx=None, mapy=None, rgb: bool = False) -> np.ndarray:
+        """The frame the extractor sees: remap (stereo_euroc.cc:168) then cvtColor (Tracking.cc:1264-1290)."""
+        out = np.ascontiguousarray(src, np.uint8)
+        if mapx is not None:
+            out = self.remap(out, mapx, mapy)
+        if out.ndim == 3:
+            out = self.gray(out, rgb)
+        return out
 
     def knn2(self, q: np.ndarray, t: np.ndarray):
         q = np.ascontiguousarray(q, np.uint8); t = np.ascontiguousarray(t, np.uint8)

@@ -63,3 +63,38 @@ def test_full_operator_against_cv2_oracle(pkg_synth, orc, oracle):
     R = ref_cv2.extract(img, P, (100, 250))
     mono, kps, desc = orc.Extractor(600, oracle=oracle)(img, (100, 250))
     assert mono == R["mono"] and kps.tobytes() == R["kps"].tobytes() and np.array_equal(desc, R["desc"])
+
+
+def rectify_maps(rows, cols, seed=0):
+    """EuRoC-like undistort+rectify maps through the real cv2.initUndistortRectifyMap (stereo_euroc.cc:117)."""
+    K = np.array([[0.61 * cols, 0, 0.49 * cols], [0, 0.95 * rows, 0.52 * rows], [0, 0, 1]], np.float64)
+    D = np.array([-0.2834, 0.0739, 0.00019, 1.76e-05, 0.0], np.float64)
+    rng = np.random.default_rng(seed)
+    rv = rng.normal(0, 0.01, 3)
+    R, _ = cv2.Rodrigues(rv)
+    P = K.copy(); P[0, 0] *= 0.95; P[1, 1] *= 0.95
+    return cv2.initUndistortRectifyMap(K, D, R, P, (cols, rows), cv2.CV_32F)
+
+
+@pytest.mark.parametrize("channels", [1, 3, 4])
+def test_prepare_primitives(oracle, channels):
+    """remap(INTER_LINEAR, CV_32FC1 maps) and cvtColor(..2GRAY) restatements, incl. taps that leave the source."""
+    rng = np.random.default_rng(10 + channels)
+    H, W = 120, 168
+    shape = (H, W) if channels == 1 else (H, W, channels)
+    src = rng.integers(0, 256, shape, dtype=np.uint8)
+    m1, m2 = rectify_maps(H, W)
+    assert np.array_equal(oracle.remap(src, m1, m2), cv2.remap(src, m1, m2, cv2.INTER_LINEAR))
+    # maps of a different size than the source, wild coordinates, exact half fractions
+    mx = rng.uniform(-4, W + 4, (77, 93)).astype(np.float32)
+    my = rng.uniform(-4, H + 4, (77, 93)).astype(np.float32)
+    mx[0, :6] = [-0.5, -1.0, -1.015625, W - 1, W - 0.5, 0.515625]
+    my[0, :6] = [0.0, 0.5, H - 1, H - 0.984375, -0.015625, 0.015625]
+    assert np.array_equal(oracle.remap(src, mx, my), cv2.remap(src, mx, my, cv2.INTER_LINEAR))
+    if channels > 1:
+        codes = {(3, True): cv2.COLOR_RGB2GRAY, (3, False): cv2.COLOR_BGR2GRAY,
+                 (4, True): cv2.COLOR_RGBA2GRAY, (4, False): cv2.COLOR_BGRA2GRAY}
+        for rgb in (True, False):
+            assert np.array_equal(oracle.gray(src, rgb), cv2.cvtColor(src, codes[(channels, rgb)]))
+            ref = cv2.cvtColor(cv2.remap(src, m1, m2, cv2.INTER_LINEAR), codes[(channels, rgb)])
+            assert np.array_equal(oracle.prepare(src, m1, m2, rgb), ref)
