@@ -87,6 +87,33 @@ int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t* imgs, int 
                        size_t step, size_t frame_stride, int lap0, int lap1,
                        orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono);
 
+/* ---- frame preparation in front of operator() ------------------------- */
+
+/* cv::initUndistortRectifyMap(..., CV_32F, M1, M2) maps of this extractor's camera
+ * (Examples/Stereo/stereo_euroc.cc:117-118): HOST CV_32FC1 mapx / mapy of the RECTIFIED size
+ * rows x cols, `map_step` bytes per row.  Converted once to remap's internal fixed point and kept on
+ * the device.  mapx == mapy == NULL clears the maps (frames are used as they come). */
+int orbx_set_rectify_maps(orbx_extractor* e, const float* mapx, const float* mapy, int rows, int cols, size_t map_step);
+
+/* cv::remap(im, imRect, M1, M2, cv::INTER_LINEAR) (Examples/Stereo/stereo_euroc.cc:168-169; skipped when
+ * no maps are set), then cvtColor(.., COLOR_{RGB,BGR,RGBA,BGRA}2GRAY) (src/Tracking.cc:1264-1290; skipped for
+ * channels == 1; rgb != 0 <=> mbRGB, the first channel is R), then operator() on the result, all on the
+ * device in one call.  `img`: HOST u8 image src_rows x src_cols x channels (1, 3 or 4), `step` bytes per
+ * row.  Outputs and return value as orbx_extract; the prepared frame has the maps' size (or the source's). */
+int orbx_prepare_extract(orbx_extractor* e, const uint8_t* img, int src_rows, int src_cols, int channels, int rgb,
+                         size_t step, int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp);
+/* batch twin (cf. orbx_extract_batch): frame f at imgs + f*frame_stride */
+int orbx_prepare_extract_batch(orbx_extractor* e, int nframes, const uint8_t* imgs, int src_rows, int src_cols,
+                               int channels, int rgb, size_t step, size_t frame_stride, int lap0, int lap1,
+                               orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono);
+/* resident twins (kernel timing): raw frames -> device, prepared into the frame slots (then
+ * orbx_run_resident); orbx_prepare_resident re-runs the prepare kernel alone on the resident raw frames */
+int orbx_prepare_upload(orbx_extractor* e, int nframes, const uint8_t* imgs, int src_rows, int src_cols,
+                        int channels, int rgb, size_t step, size_t frame_stride);
+int orbx_prepare_resident(orbx_extractor* e);
+/* imLeftRect / mImGray of frame slot `frame`: the frame operator() saw (rows x cols of the extractor geometry) */
+int orbx_get_prepared(orbx_extractor* e, int frame, uint8_t* dst, size_t dst_step);
+
 /* Upper bound on the keypoints one frame can yield (quota + quadtree overshoot per level). */
 int orbx_max_keypoints(const orbx_extractor* e, int rows, int cols);
 

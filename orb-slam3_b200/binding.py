@@ -37,6 +37,14 @@ SYMBOLS = {
                                C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]),
     "orbx_extract_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_size_t,
                                      C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "orbx_set_rectify_maps": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t]),
+    "orbx_prepare_extract": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int,
+                                       C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]),
+    "orbx_prepare_extract_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t,
+                                             C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "orbx_prepare_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t]),
+    "orbx_prepare_resident": (C.c_int, [C.c_void_p]),
+    "orbx_get_prepared": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "orbx_max_keypoints": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "orbx_reserve": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "orbx_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_size_t]),

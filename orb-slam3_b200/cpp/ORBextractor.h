@@ -110,11 +110,66 @@ public:
         return m;
     }
 
+    // ---- frame preparation on the device (no reference member: replaces the caller-side cv::remap of
+    // Examples/Stereo/stereo_euroc.cc:168-169 and the cvtColor of src/Tracking.cc:1264-1290) ----
+    // M1 / M2 of cv::initUndistortRectifyMap(..., CV_32F, M1, M2) (stereo_euroc.cc:117-118) for this camera.
+    void SetRectifyMaps(const float* mapx, const float* mapy, int rows, int cols, size_t step_bytes)
+    {
+        if (orbx_set_rectify_maps(h_, mapx, mapy, rows, cols, step_bytes) != ORBX_OK)
+            throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        rect_rows_ = mapx ? rows : 0; rect_cols_ = mapx ? cols : 0;
+    }
+#ifdef ORBX_WITH_OPENCV
+    void SetRectifyMaps(const cv::Mat& M1, const cv::Mat& M2)
+    {
+        assert(M1.type() == CV_32FC1 && M2.type() == CV_32FC1 && M1.size() == M2.size() && M1.step == M2.step);
+        SetRectifyMaps(M1.ptr<float>(), M2.ptr<float>(), M1.rows, M1.cols, M1.step);
+    }
+    // raw camera image (CV_8UC1 / 8UC3 / 8UC4, unrectified) -> remap -> gray -> operator()
+    int ExtractRaw(const cv::Mat& im, bool bRGB, std::vector<cv::KeyPoint>& keypoints, cv::Mat& descriptors, std::vector<int>& vLappingArea)
+    {
+        if (im.empty()) return -1;
+        return ExtractRaw(im.data, im.rows, im.cols, im.channels(), im.step, bRGB, keypoints, descriptors, vLappingArea);
+    }
+#endif
+    int ExtractRaw(const uint8_t* data, int rows, int cols, int channels, size_t step, bool bRGB,
+                   std::vector<cv::KeyPoint>& keypoints, cv::Mat& descriptors, std::vector<int>& vLappingArea)
+    {
+        if (!data || rows <= 0 || cols <= 0) return -1;
+        assert(vLappingArea.size() >= 2);
+        const int prow = rect_rows_ ? rect_rows_ : rows, pcol = rect_cols_ ? rect_cols_ : cols;
+        const int cap = orbx_max_keypoints(h_, prow, pcol);
+        if (cap < 0) throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        keypoints.resize((size_t)cap);
+        scratch_.resize((size_t)cap * 32);
+        int n = 0;
+        const int mono = orbx_prepare_extract(h_, data, rows, cols, channels, bRGB ? 1 : 0, step, vLappingArea[0], vLappingArea[1],
+                                              reinterpret_cast<orbx_keypoint*>(keypoints.data()), scratch_.data(), cap, &n);
+        if (mono < 0) throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        keypoints.resize((size_t)n);
+        if (n == 0) descriptors.release();
+        else {
+            ORBX_MAT_CREATE(descriptors, n, 32);
+            for (int i = 0; i < n; i++) std::memcpy(descriptors.ptr(i), scratch_.data() + (size_t)i * 32, 32);
+        }
+        prep_rows_ = prow; prep_cols_ = pcol;
+        return mono;
+    }
+    // imLeftRect / mImGray: the frame the last ExtractRaw call extracted from (for the viewer, Tracking::mImGray)
+    cv::Mat GetPreparedImage()
+    {
+        cv::Mat m; ORBX_MAT_CREATE(m, prep_rows_, prep_cols_);
+        if (orbx_get_prepared(h_, 0, m.data, m.step) != ORBX_OK)
+            throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        return m;
+    }
+
     orbx_extractor* handle() { return h_; }
 
 protected:
     orbx_extractor* h_ = nullptr;
     std::vector<uint8_t> scratch_;
+    int rect_rows_ = 0, rect_cols_ = 0, prep_rows_ = 0, prep_cols_ = 0;
     std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
 };
 

@@ -54,8 +54,10 @@ extern "C" int orbx_create(int nfeatures, float scaleFactor, int nlevels, int in
     e->nfeatures = nfeatures; e->nlevels = nlevels; e->iniTh = iniThFAST; e->minTh = minThFAST;
     e->scaleFactorF = scaleFactor;
     e->device = device; e->reserved = false; e->profiling = false; e->launches = 0; e->last_nframes = 0;
-    e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr;
+    e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr; e->d_st_rows = nullptr;
     e->h_counts = nullptr; e->h_counts_cap = 0;
+    e->d_map = nullptr; e->map_rows = e->map_cols = 0;
+    e->d_raw = nullptr; e->raw_bytes = 0; e->raw_rows = e->raw_cols = e->raw_ch = e->raw_rgb = e->raw_pitch = 0;
     memset(&e->G, 0, sizeof(e->G)); memset(&e->D, 0, sizeof(e->D));
     memset(e->stage_ms, 0, sizeof(e->stage_ms));
     orbx_init_tables(e);
@@ -86,7 +88,7 @@ static void free_device(orbx_extractor* e)
     e->allocs.clear();
     e->reserved = false;
     e->last_nframes = 0;
-    e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr;
+    e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr; e->d_st_rows = nullptr;
 }
 
 extern "C" void orbx_destroy(orbx_extractor* e)
@@ -95,6 +97,8 @@ extern "C" void orbx_destroy(orbx_extractor* e)
     cudaSetDevice(e->device);
     cudaStreamSynchronize(e->stream);
     free_device(e);
+    if (e->d_map) cudaFree(e->d_map);
+    if (e->d_raw) cudaFree(e->d_raw);
     for (int i = 0; i <= ORBX_NSTAGES; i++) cudaEventDestroy(e->ev[i]);
     for (int i = 0; i < 2; i++) cudaEventDestroy(e->tev[i]);
     for (cudaEvent_t ev : e->ev_up) cudaEventDestroy(ev);
@@ -366,13 +370,61 @@ extern "C" int orbx_download(orbx_extractor* e, orbx_keypoint* kps, uint8_t* des
     return rc;
 }
 
-extern "C" int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t* imgs, int rows, int cols,
-                                  size_t step, size_t frame_stride, int lap0, int lap1,
-                                  orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono)
+// raw frame slots for the prepare path: room for `batch` frames of raw_rows x raw_pitch bytes
+static int reserve_raw(orbx_extractor* e, int batch)
+{
+    const size_t need = (size_t)batch * e->raw_rows * e->raw_pitch + 64;
+    if (e->d_raw && e->raw_bytes >= need) return 0;
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    if (e->d_raw) cudaFree(e->d_raw);
+    e->d_raw = nullptr; e->raw_bytes = 0;
+    CUDA_TRY(cudaMalloc((void**)&e->d_raw, need));
+    e->raw_bytes = need;
+    return 0;
+}
+
+static int upload_raw(orbx_extractor* e, int slot0, int nframes, const uint8_t* imgs, size_t step, size_t frame_stride,
+                      cudaStream_t st)
+{
+    const size_t fbytes = (size_t)e->raw_rows * e->raw_pitch;
+    uint8_t* dst = e->d_raw + (size_t)slot0 * fbytes;
+    if (frame_stride == step * (size_t)e->raw_rows && step == (size_t)e->raw_pitch) {
+        CUDA_TRY(cudaMemcpyAsync(dst, imgs, (size_t)nframes * fbytes, cudaMemcpyHostToDevice, st));
+    } else {
+        for (int f = 0; f < nframes; f++)
+            CUDA_TRY(cudaMemcpy2DAsync(dst + (size_t)f * fbytes, e->raw_pitch, imgs + (size_t)f * frame_stride, step,
+                                       (size_t)e->raw_cols * e->raw_ch, e->raw_rows, cudaMemcpyHostToDevice, st));
+    }
+    return 0;
+}
+
+// validates a prepare call and fixes the raw layout in the handle; *rows/*cols = size of the prepared (gray,
+// rectified) frame = the frame operator() sees.  Returns 1 when the frames need no preparation at all.
+static int prepare_begin(orbx_extractor* e, const uint8_t* imgs, int src_rows, int src_cols, int channels, int rgb,
+                         size_t step, size_t frame_stride, int nframes, int* rows, int* cols)
+{
+    if (!e) { orbx_set_error("null handle"); return ORBX_ERR_ARG; }
+    if (!imgs || src_rows <= 0 || src_cols <= 0 || nframes <= 0) { orbx_set_error("empty image"); return ORBX_EMPTY_IMAGE; }
+    if (channels != 1 && channels != 3 && channels != 4) {          // src/Tracking.cc:1264-1290 handles 3 and 4
+        orbx_set_error("prepare: %d channels (1, 3 or 4 expected)", channels); return ORBX_ERR_ARG;
+    }
+    if (step < (size_t)src_cols * channels) { orbx_set_error("prepare: step smaller than a row"); return ORBX_ERR_ARG; }
+    *rows = e->d_map ? e->map_rows : src_rows;
+    *cols = e->d_map ? e->map_cols : src_cols;
+    if (!e->d_map && channels == 1) return 1;
+    e->raw_rows = src_rows; e->raw_cols = src_cols; e->raw_ch = channels; e->raw_rgb = rgb != 0;
+    const bool packed = frame_stride == step * (size_t)src_rows || nframes == 1;
+    e->raw_pitch = packed ? (int)step : (src_cols * channels + 15) / 16 * 16;
+    return 0;
+}
+
+static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* imgs, int rows, int cols,
+                              size_t step, size_t frame_stride, int lap0, int lap1,
+                              orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono, bool raw)
 {
     if (!e) { orbx_set_error("null handle"); return ORBX_ERR_ARG; }
     if (!imgs || rows <= 0 || cols <= 0 || nframes <= 0) { orbx_set_error("empty image"); return ORBX_EMPTY_IMAGE; }
-    if (!kps || !desc || cap <= 0 || step < (size_t)cols) { orbx_set_error("bad output buffers / step"); return ORBX_ERR_ARG; }
+    if (!kps || !desc || cap <= 0 || (!raw && step < (size_t)cols)) { orbx_set_error("bad output buffers / step"); return ORBX_ERR_ARG; }
     int r;
     if (!(e->reserved && e->G.rows == rows && e->G.cols == cols)) {
         // lazy sizing: bound the device footprint to ~8 GB
@@ -392,6 +444,11 @@ extern "C" int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t*
     CUDA_TRY(cudaSetDevice(e->device));
     const int B = e->G.batch;
     int rc = ORBX_OK;
+    if (raw) {
+        r = reserve_raw(e, B);
+        if (r) return r;
+        e->D.in_pitch = (cols + 15) / 16 * 16;               // the prepare kernel writes whole words
+    }
     // Chunked three-stream ring pipeline: the frames are cut into chunks that cycle through the R chunk
     // slots of the device buffers; upload of chunk k+1, kernels of chunk k and download of chunk k-1
     // overlap.  Hazards of slot reuse: upload(k) waits for kernels(k-R) (input consumed), kernels(k) wait
@@ -425,13 +482,15 @@ extern "C" int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t*
         const int slot = k % R, s0 = slot * chunk;
         cudaStream_t cs = (multi && !e->profiling) ? e->cstream[k % ncs] : e->stream;   // chunk slot k%R is always served by the same stream
         if (multi && k >= R) CUDA_TRY(cudaStreamWaitEvent(up, e->ev_done[slot], 0));
-        r = upload_frames(e, s0, n, imgs + (size_t)fr0 * frame_stride, step, frame_stride, up);
+        r = raw ? upload_raw(e, s0, n, imgs + (size_t)fr0 * frame_stride, step, frame_stride, up)
+                : upload_frames(e, s0, n, imgs + (size_t)fr0 * frame_stride, step, frame_stride, up);
         if (r) return r;
         if (multi) {
             CUDA_TRY(cudaEventRecord(e->ev_up[slot], up));
             CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_up[slot], 0));
             if (k >= R) CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_down[slot], 0));
         }
+        if (raw) e->launches += launch_prepare(e, s0, n, cs);   // remap + gray into the slot's frames
         r = run_pipeline(e, s0, n, lap0, lap1, cs);
         if (r) return r;
         if (multi) {
@@ -457,6 +516,113 @@ extern "C" int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t*
     }
     if (rc) orbx_set_error("keypoint capacity %d too small", cap);
     return rc;
+}
+
+extern "C" int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t* imgs, int rows, int cols,
+                                  size_t step, size_t frame_stride, int lap0, int lap1,
+                                  orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono)
+{
+    return extract_batch_impl(e, nframes, imgs, rows, cols, step, frame_stride, lap0, lap1, kps, desc, cap, nkp, mono, false);
+}
+
+// ---- frame preparation in front of operator(): remap + cvtColor on the device (prepare.cu) ----
+
+extern "C" int orbx_set_rectify_maps(orbx_extractor* e, const float* mapx, const float* mapy, int rows, int cols, size_t map_step)
+{
+    if (!e) { orbx_set_error("null handle"); return ORBX_ERR_ARG; }
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    if (e->d_map) { cudaFree(e->d_map); e->d_map = nullptr; e->map_rows = e->map_cols = 0; }
+    if (!mapx && !mapy) return ORBX_OK;                       // cleared: frames are used as they come
+    if (!mapx || !mapy || rows <= 0 || cols <= 0 || map_step < sizeof(float) * (size_t)cols || map_step % sizeof(float)) {
+        orbx_set_error("bad rectification maps (CV_32FC1 mapx and mapy of the rectified size expected)"); return ORBX_ERR_ARG;
+    }
+    float* tmp = nullptr;
+    const size_t plane = map_step * (size_t)rows;
+    CUDA_TRY(cudaMalloc((void**)&tmp, 2 * plane));
+    cudaError_t ce = cudaMemcpyAsync(tmp, mapx, plane, cudaMemcpyHostToDevice, e->stream);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync((char*)tmp + plane, mapy, plane, cudaMemcpyHostToDevice, e->stream);
+    if (ce == cudaSuccess) ce = cudaMalloc((void**)&e->d_map, sizeof(int2) * (size_t)rows * cols);
+    if (ce == cudaSuccess) {
+        e->launches += launch_rectify_pack(tmp, (const float*)((char*)tmp + plane), rows, cols, (int)(map_step / sizeof(float)), e->d_map, e->stream);
+        ce = cudaGetLastError();
+    }
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->stream);
+    cudaFree(tmp);
+    if (ce != cudaSuccess) {
+        if (e->d_map) { cudaFree(e->d_map); e->d_map = nullptr; }
+        orbx_set_error("rectification map upload failed: %s", cudaGetErrorString(ce)); return ORBX_ERR_CUDA;
+    }
+    e->map_rows = rows; e->map_cols = cols;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_prepare_extract_batch(orbx_extractor* e, int nframes, const uint8_t* imgs, int src_rows, int src_cols,
+                                          int channels, int rgb, size_t step, size_t frame_stride, int lap0, int lap1,
+                                          orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono)
+{
+    int rows = 0, cols = 0;
+    const int p = prepare_begin(e, imgs, src_rows, src_cols, channels, rgb, step, frame_stride, nframes, &rows, &cols);
+    if (p < 0) return p;
+    return extract_batch_impl(e, nframes, imgs, rows, cols, step, frame_stride, lap0, lap1, kps, desc, cap, nkp, mono, p == 0);
+}
+
+extern "C" int orbx_prepare_extract(orbx_extractor* e, const uint8_t* img, int src_rows, int src_cols, int channels, int rgb,
+                                    size_t step, int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp)
+{
+    int n = 0, mono = 0;
+    if (nkp) *nkp = 0;
+    int r = orbx_prepare_extract_batch(e, 1, img, src_rows, src_cols, channels, rgb, step, step * (size_t)(src_rows > 0 ? src_rows : 0),
+                                       lap0, lap1, kps, desc, cap, &n, &mono);
+    if (nkp) *nkp = n;
+    if (r < 0) return r;
+    return mono;
+}
+
+// resident twin of orbx_upload: raw frames -> raw slots -> prepare kernel -> frame slots (then orbx_run_resident)
+extern "C" int orbx_prepare_upload(orbx_extractor* e, int nframes, const uint8_t* imgs, int src_rows, int src_cols,
+                                   int channels, int rgb, size_t step, size_t frame_stride)
+{
+    int rows = 0, cols = 0;
+    const int p = prepare_begin(e, imgs, src_rows, src_cols, channels, rgb, step, frame_stride, nframes, &rows, &cols);
+    if (p < 0) return p;
+    if (p == 1) return orbx_upload(e, nframes, imgs, rows, cols, step, frame_stride);
+    int r = orbx_reserve(e, rows, cols, nframes);
+    if (r) return r;
+    CUDA_TRY(cudaSetDevice(e->device));
+    r = reserve_raw(e, e->G.batch);
+    if (r) return r;
+    e->D.in_pitch = (cols + 15) / 16 * 16;
+    r = upload_raw(e, 0, nframes, imgs, step, frame_stride, e->stream);
+    if (r) return r;
+    e->launches += launch_prepare(e, 0, nframes, e->stream);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->last_nframes = -nframes;
+    return ORBX_OK;
+}
+
+// the prepare kernel alone over the resident raw frames (kernel timing)
+extern "C" int orbx_prepare_resident(orbx_extractor* e)
+{
+    if (!e || !e->reserved || !e->d_raw || e->last_nframes == 0) { orbx_set_error("prepare_resident before prepare_upload"); return ORBX_ERR_STATE; }
+    CUDA_TRY(cudaSetDevice(e->device));
+    const int n = e->last_nframes < 0 ? -e->last_nframes : e->last_nframes;
+    e->launches += launch_prepare(e, 0, n, e->stream);
+    CUDA_TRY(cudaGetLastError());
+    return ORBX_OK;
+}
+
+extern "C" int orbx_get_prepared(orbx_extractor* e, int frame, uint8_t* dst, size_t dst_step)
+{
+    if (!e || !e->reserved || e->last_nframes == 0) { orbx_set_error("no frame resident"); return ORBX_ERR_STATE; }
+    const int n = e->last_nframes < 0 ? -e->last_nframes : e->last_nframes;
+    if (frame < 0 || frame >= n || !dst || dst_step < (size_t)e->G.cols) { orbx_set_error("bad frame / destination"); return ORBX_ERR_ARG; }
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaMemcpy2DAsync(dst, dst_step, e->D.input + (size_t)frame * e->G.rows * e->D.in_pitch, e->D.in_pitch,
+                               e->G.cols, e->G.rows, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return ORBX_OK;
 }
 
 extern "C" int orbx_extract(orbx_extractor* e, const uint8_t* img, int rows, int cols, size_t step,

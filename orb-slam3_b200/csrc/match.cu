@@ -5,6 +5,7 @@
 // Integer pipe work (XOR + POPC); no tensor cores: nothing here is a dense contraction.
 #include "match_internal.h"
 #include <climits>
+#include <cstring>
 #include <vector>
 
 #define CUDA_TRYM(expr)                                                                        \
@@ -16,33 +17,58 @@
         }                                                                                      \
     } while (0)
 
-// ---- brute-force 2-NN: one thread per query, train rows broadcast from shared memory ----
+// ---- brute-force 2-NN ----
+// Grid = (query tiles of 128, train splits): one thread per query, the split's train rows broadcast from
+// shared memory; every (split, query) leaves its partial best / second best, knn2_merge_kernel folds the
+// splits in ascending train order (strict '<' keeps the lower train index on ties, as BFMatcher does).
+// The split count is chosen so that the grid covers the 148 SMs about twice even for 1000 x 1000.
 #define KNN_THREADS 128
 #define KNN_TILE 128
 
 __global__ void __launch_bounds__(KNN_THREADS)
-knn2_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ t, int nt, int* __restrict__ out_idx, int* __restrict__ out_dist)
+knn2_partial_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ t, int nt, int per_split, int4* __restrict__ part)
 {
     __shared__ uint4 s_t[KNN_TILE * 2];
     const int i = blockIdx.x * KNN_THREADS + threadIdx.x;
+    const int jb = blockIdx.y * per_split, je = min(nt, jb + per_split);
     uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
     if (i < nq) { a0 = q[2 * i]; a1 = q[2 * i + 1]; }
     int b0 = 1 << 30, b1 = 1 << 30, i0 = -1, i1 = -1;
-    for (int j0 = 0; j0 < nt; j0 += KNN_TILE) {
-        const int m = min(KNN_TILE, nt - j0);
+    for (int j0 = jb; j0 < je; j0 += KNN_TILE) {
+        const int m = min(KNN_TILE, je - j0);
         __syncthreads();
         for (int k = threadIdx.x; k < 2 * m; k += KNN_THREADS) s_t[k] = t[2 * j0 + k];
         __syncthreads();
+#pragma unroll 4
         for (int j = 0; j < m; j++) {
             const int d = ham256(a0, a1, s_t[2 * j], s_t[2 * j + 1]);
             if (d < b0) { b1 = b0; i1 = i0; b0 = d; i0 = j0 + j; }     // ties keep the lower train index
             else if (d < b1) { b1 = d; i1 = j0 + j; }
         }
     }
-    if (i < nq) {
-        out_idx[2 * i] = i0; out_idx[2 * i + 1] = i1;
-        out_dist[2 * i] = i0 >= 0 ? b0 : -1; out_dist[2 * i + 1] = i1 >= 0 ? b1 : -1;
+    if (i < nq) part[(size_t)blockIdx.y * nq + i] = make_int4(b0, i0, b1, i1);
+}
+
+__global__ void __launch_bounds__(KNN_THREADS)
+knn2_merge_kernel(const int4* __restrict__ part, int nq, int nsplit, int* __restrict__ out_idx, int* __restrict__ out_dist)
+{
+    const int i = blockIdx.x * KNN_THREADS + threadIdx.x;
+    if (i >= nq) return;
+    int b0 = 1 << 30, b1 = 1 << 30, i0 = -1, i1 = -1;
+    for (int s = 0; s < nsplit; s++) {
+        const int4 p = part[(size_t)s * nq + i];
+        // a split's pair is in (distance, index) order; splits ascend in index
+        if (p.y >= 0) {
+            if (p.x < b0) { b1 = b0; i1 = i0; b0 = p.x; i0 = p.y; }
+            else if (p.x < b1) { b1 = p.x; i1 = p.y; }
+        }
+        if (p.w >= 0) {
+            if (p.z < b0) { b1 = b0; i1 = i0; b0 = p.z; i0 = p.w; }
+            else if (p.z < b1) { b1 = p.z; i1 = p.w; }
+        }
     }
+    out_idx[2 * i] = i0; out_idx[2 * i + 1] = i1;
+    out_dist[2 * i] = i0 >= 0 ? b0 : -1; out_dist[2 * i + 1] = i1 >= 0 ? b1 : -1;
 }
 
 extern "C" int orbx_knn2_hamming(int device, const uint8_t* q, int nq, const uint8_t* t, int nt,
@@ -50,25 +76,36 @@ extern "C" int orbx_knn2_hamming(int device, const uint8_t* q, int nq, const uin
 {
     if (nq < 0 || nt < 0 || (nq > 0 && (!q || !out_idx || !out_dist)) || (nt > 0 && !t)) { orbx_set_error("bad knn2 arguments"); return ORBX_ERR_ARG; }
     if (nq == 0) return ORBX_OK;
-    int rc = ORBX_OK;
-    uint8_t *dq = nullptr, *dt = nullptr; int *di = nullptr, *dd = nullptr;
-    cudaStream_t s = nullptr;
-    if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
-    CUDA_TRYM(cudaSetDevice(device));
-    CUDA_TRYM(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-    CUDA_TRYM(cudaMalloc(&dq, (size_t)nq * 32)); CUDA_TRYM(cudaMalloc(&dt, (size_t)(nt > 0 ? nt : 1) * 32));
-    CUDA_TRYM(cudaMalloc(&di, (size_t)nq * 8)); CUDA_TRYM(cudaMalloc(&dd, (size_t)nq * 8));
-    CUDA_TRYM(cudaMemcpyAsync(dq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
-    if (nt > 0) CUDA_TRYM(cudaMemcpyAsync(dt, t, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
-    knn2_kernel<<<(nq + KNN_THREADS - 1) / KNN_THREADS, KNN_THREADS, 0, s>>>((const uint4*)dq, nq, (const uint4*)dt, nt, di, dd);
-    CUDA_TRYM(cudaGetLastError());
-    CUDA_TRYM(cudaMemcpyAsync(out_idx, di, (size_t)nq * 8, cudaMemcpyDeviceToHost, s));
-    CUDA_TRYM(cudaMemcpyAsync(out_dist, dd, (size_t)nq * 8, cudaMemcpyDeviceToHost, s));
-    CUDA_TRYM(cudaStreamSynchronize(s));
-done:
-    cudaFree(dq); cudaFree(dt); cudaFree(di); cudaFree(dd);
-    if (s) cudaStreamDestroy(s);
-    return rc;
+    OrbxWorkspace& W = orbx_workspace();
+    int rc = W.bind(device);
+    if (rc != ORBX_OK) return rc;
+    const int tiles = (nq + KNN_THREADS - 1) / KNN_THREADS;
+    int nsplit = (2 * 148 + tiles - 1) / tiles;                       // cover the SMs about twice
+    const int max_split = nt > 0 ? (nt + 63) / 64 : 1;                // at least 64 train rows per split
+    if (nsplit > max_split) nsplit = max_split;
+    if (nsplit < 1) nsplit = 1;
+    const int per_split = nt > 0 ? (nt + nsplit - 1) / nsplit : 1;
+    nsplit = nt > 0 ? (nt + per_split - 1) / per_split : 1;
+    OrbxCarver c;
+    const size_t o_q = c.take((size_t)nq * 32), o_t = c.take((size_t)nt * 32);
+    const size_t in_bytes = c.off;
+    const size_t o_idx = c.take((size_t)nq * 8), o_dist = c.take((size_t)nq * 8);
+    const size_t out_end = c.off;
+    const size_t o_part = c.take((size_t)nsplit * nq * sizeof(int4));
+    rc = W.reserve(c.off, out_end);
+    if (rc != ORBX_OK) return rc;
+    memcpy(W.h + o_q, q, (size_t)nq * 32);
+    if (nt > 0) memcpy(W.h + o_t, t, (size_t)nt * 32);
+    CUDA_TRYW(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.s));
+    knn2_partial_kernel<<<dim3(tiles, nsplit), KNN_THREADS, 0, W.s>>>((const uint4*)(W.d + o_q), nq, (const uint4*)(W.d + o_t), nt, per_split,
+                                                                     (int4*)(W.d + o_part));
+    knn2_merge_kernel<<<tiles, KNN_THREADS, 0, W.s>>>((const int4*)(W.d + o_part), nq, nsplit, (int*)(W.d + o_idx), (int*)(W.d + o_dist));
+    CUDA_TRYW(cudaGetLastError());
+    CUDA_TRYW(cudaMemcpyAsync(W.h + o_idx, W.d + o_idx, out_end - o_idx, cudaMemcpyDeviceToHost, W.s));
+    CUDA_TRYW(cudaStreamSynchronize(W.s));
+    memcpy(out_idx, W.h + o_idx, (size_t)nq * 8);
+    memcpy(out_dist, W.h + o_dist, (size_t)nq * 8);
+    return ORBX_OK;
 }
 
 // ---- frame grid + SearchByProjection ----
@@ -274,45 +311,42 @@ extern "C" int orbx_search_by_projection(int device,
     for (int i = 0; i < nmp; i++)
         if (mp_level[i] < 0 || mp_level[i] >= nlevels) { orbx_set_error("map point %d: level %d out of range", i, mp_level[i]); return ORBX_ERR_ARG; }
     if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
-    int rc = ORBX_OK;
-    int result[2] = {0, 0};
+    OrbxWorkspace& W = orbx_workspace();
+    int rc = W.bind(device);
+    if (rc != ORBX_OK) return rc;
     ProjArgs A;
     memset(&A, 0, sizeof(A));
-    std::vector<void*> allocs;
-    cudaStream_t s = nullptr;
-    auto up = [&](const void* h, size_t bytes, cudaError_t* ce) -> void* {
-        void* d = nullptr;
-        *ce = cudaMalloc(&d, bytes ? bytes : 4);
-        if (*ce != cudaSuccess) return nullptr;
-        allocs.push_back(d);
-        if (h) *ce = cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s);
-        return d;
-    };
-    cudaError_t ce = cudaSuccess;
-    CUDA_TRYM(cudaSetDevice(device));
-    CUDA_TRYM(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-#define UP(dst, type, src, bytes) do { dst = (type)up(src, bytes, &ce); CUDA_TRYM(ce); } while (0)
-    UP(A.kps, const orbx_keypoint*, kps, sizeof(orbx_keypoint) * (size_t)n);
-    UP(A.desc, const uint4*, desc, 32 * (size_t)n);
-    if (uRight) UP(A.uRight, const float*, uRight, 4 * (size_t)n);
-    UP(A.mp_desc, const uint4*, mp_desc, 32 * (size_t)nmp);
-    UP(A.projx, const float*, mp_projx, 4 * (size_t)nmp);
-    UP(A.projy, const float*, mp_projy, 4 * (size_t)nmp);
-    if (mp_projxr) UP(A.projxr, const float*, mp_projxr, 4 * (size_t)nmp);
-    UP(A.level, const int*, mp_level, 4 * (size_t)nmp);
-    UP(A.viewcos, const float*, mp_viewcos, 4 * (size_t)nmp);
-    if (mp_depth) UP(A.depth, const float*, mp_depth, 4 * (size_t)nmp);
-    UP(A.inview, const uint8_t*, mp_inview, (size_t)nmp);
-    UP(A.assign, int*, assign, 4 * (size_t)n);
-    UP(A.cell_start, int*, nullptr, 4 * (size_t)(GRID_CELLS + 1));
-    UP(A.cell_idx, int*, nullptr, 4 * (size_t)n);
-    UP(A.cand_cnt, int*, nullptr, 4 * (size_t)nmp);
-    UP(A.cand, int*, nullptr, 8 * (size_t)nmp * PROJ_KMAX);
-    UP(A.claim0, int*, nullptr, 4 * (size_t)n);
-    UP(A.claim1, int*, nullptr, 4 * (size_t)n);
-    UP(A.choice, int*, nullptr, 4 * (size_t)nmp);
-    UP(A.result, int*, result, 8);
-#undef UP
+    const size_t N = (size_t)n, M = (size_t)nmp;
+    // inputs (one H2D copy), then the small outputs (one D2H copy), then device-only scratch
+    OrbxCarver c;
+    const size_t o_kps = c.take(N * sizeof(orbx_keypoint)), o_desc = c.take(N * 32), o_ur = c.take(uRight ? N * 4 : 0);
+    const size_t o_md = c.take(M * 32), o_px = c.take(M * 4), o_py = c.take(M * 4), o_pxr = c.take(mp_projxr ? M * 4 : 0);
+    const size_t o_lv = c.take(M * 4), o_vc = c.take(M * 4), o_dp = c.take(mp_depth ? M * 4 : 0), o_iv = c.take(M);
+    const size_t o_assign = c.take(N * 4), o_result = c.take(8);
+    const size_t in_bytes = c.off;
+    const size_t o_cs = c.take(4 * (size_t)(GRID_CELLS + 1)), o_ci = c.take(N * 4), o_cc = c.take(M * 4);
+    const size_t o_cand = c.take(8 * M * PROJ_KMAX), o_c0 = c.take(N * 4), o_c1 = c.take(N * 4), o_ch = c.take(M * 4);
+    rc = W.reserve(c.off, in_bytes);
+    if (rc != ORBX_OK) return rc;
+    char* h = W.h; char* d = W.d;
+    memcpy(h + o_kps, kps, N * sizeof(orbx_keypoint)); memcpy(h + o_desc, desc, N * 32);
+    if (uRight) memcpy(h + o_ur, uRight, N * 4);
+    memcpy(h + o_md, mp_desc, M * 32); memcpy(h + o_px, mp_projx, M * 4); memcpy(h + o_py, mp_projy, M * 4);
+    if (mp_projxr) memcpy(h + o_pxr, mp_projxr, M * 4);
+    memcpy(h + o_lv, mp_level, M * 4); memcpy(h + o_vc, mp_viewcos, M * 4);
+    if (mp_depth) memcpy(h + o_dp, mp_depth, M * 4);
+    memcpy(h + o_iv, mp_inview, M); memcpy(h + o_assign, assign, N * 4);
+    memset(h + o_result, 0, 8);
+    CUDA_TRYW(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, W.s));
+    A.kps = (const orbx_keypoint*)(d + o_kps); A.desc = (const uint4*)(d + o_desc);
+    A.uRight = uRight ? (const float*)(d + o_ur) : nullptr;
+    A.mp_desc = (const uint4*)(d + o_md); A.projx = (const float*)(d + o_px); A.projy = (const float*)(d + o_py);
+    A.projxr = mp_projxr ? (const float*)(d + o_pxr) : nullptr;
+    A.level = (const int*)(d + o_lv); A.viewcos = (const float*)(d + o_vc);
+    A.depth = mp_depth ? (const float*)(d + o_dp) : nullptr; A.inview = (const uint8_t*)(d + o_iv);
+    A.assign = (int*)(d + o_assign); A.result = (int*)(d + o_result);
+    A.cell_start = (int*)(d + o_cs); A.cell_idx = (int*)(d + o_ci); A.cand_cnt = (int*)(d + o_cc); A.cand = (int*)(d + o_cand);
+    A.claim0 = (int*)(d + o_c0); A.claim1 = (int*)(d + o_c1); A.choice = (int*)(d + o_ch);
     A.n = n; A.nmp = nmp;
     A.minX = minX; A.minY = minY;
     A.winv = (float)GRID_COLS / (float)(maxX - minX);                     // src/Frame.cc:292
@@ -323,18 +357,15 @@ extern "C" int orbx_search_by_projection(int device,
         GridArgs g;
         g.kps = A.kps; g.n = n; g.minX = A.minX; g.minY = A.minY; g.winv = A.winv; g.hinv = A.hinv;
         g.cell_start = A.cell_start; g.cell_idx = A.cell_idx;
-        orbx_launch_grid_build(g, s);
+        orbx_launch_grid_build(g, W.s);
     }
-    proj_candidates_kernel<<<(nmp + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32, 0, s>>>(A);
-    proj_resolve_kernel<<<1, 1024, 0, s>>>(A);
-    CUDA_TRYM(cudaGetLastError());
-    CUDA_TRYM(cudaMemcpyAsync(assign, A.assign, 4 * (size_t)n, cudaMemcpyDeviceToHost, s));
-    CUDA_TRYM(cudaMemcpyAsync(result, A.result, 8, cudaMemcpyDeviceToHost, s));
-    CUDA_TRYM(cudaStreamSynchronize(s));
-    if (result[1]) { orbx_set_error("a map point has more than %d candidates", PROJ_KMAX); rc = ORBX_ERR_CAPACITY; }
-    else rc = result[0];
-done:
-    for (void* p : allocs) cudaFree(p);
-    if (s) cudaStreamDestroy(s);
-    return rc;
+    proj_candidates_kernel<<<(nmp + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32, 0, W.s>>>(A);
+    proj_resolve_kernel<<<1, 1024, 0, W.s>>>(A);
+    CUDA_TRYW(cudaGetLastError());
+    CUDA_TRYW(cudaMemcpyAsync(h + o_assign, d + o_assign, in_bytes - o_assign, cudaMemcpyDeviceToHost, W.s));
+    CUDA_TRYW(cudaStreamSynchronize(W.s));
+    memcpy(assign, h + o_assign, N * 4);
+    const int* result = (const int*)(h + o_result);
+    if (result[1]) { orbx_set_error("a map point has more than %d candidates", PROJ_KMAX); return ORBX_ERR_CAPACITY; }
+    return result[0];
 }

@@ -25,3 +25,63 @@ __device__ __forceinline__ int ham256(const uint4& a0, const uint4& a1, const ui
     return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
+
+// ---- per-thread workspace: grow-only device arena + pinned mirror + stream (no cudaMalloc after warm-up) ----
+#define CUDA_TRYW(expr)                                                                        \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            orbx_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return ORBX_ERR_CUDA;                                                              \
+        }                                                                                      \
+    } while (0)
+
+extern "C" int orbx_device_count(void);
+
+struct OrbxWorkspace {
+    int device = -1;
+    cudaStream_t s = nullptr;
+    char* d = nullptr; size_t dcap = 0;     // device arena
+    char* h = nullptr; size_t hcap = 0;     // pinned mirror of the arena's input part / output landing zone
+    ~OrbxWorkspace() { release(); }
+    void release()
+    {
+        if (device < 0) return;
+        if (cudaSetDevice(device) == cudaSuccess) {
+            if (d) cudaFree(d);
+            if (h) cudaFreeHost(h);
+            if (s) cudaStreamDestroy(s);
+        }
+        d = nullptr; h = nullptr; s = nullptr; dcap = hcap = 0; device = -1;
+    }
+    int bind(int dev)
+    {
+        if (dev < 0 || dev >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", dev); return ORBX_ERR_CUDA; }
+        if (device != dev) release();
+        CUDA_TRYW(cudaSetDevice(dev));
+        if (!s) CUDA_TRYW(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+        device = dev;
+        return ORBX_OK;
+    }
+    int reserve(size_t dbytes, size_t hbytes)
+    {
+        if (dbytes > dcap) {
+            if (d) { CUDA_TRYW(cudaStreamSynchronize(s)); CUDA_TRYW(cudaFree(d)); d = nullptr; dcap = 0; }
+            const size_t want = dbytes + dbytes / 2 + (1u << 20);
+            CUDA_TRYW(cudaMalloc((void**)&d, want)); dcap = want;
+        }
+        if (hbytes > hcap) {
+            if (h) { CUDA_TRYW(cudaStreamSynchronize(s)); CUDA_TRYW(cudaFreeHost(h)); h = nullptr; hcap = 0; }
+            const size_t want = hbytes + hbytes / 2 + (1u << 20);
+            CUDA_TRYW(cudaMallocHost((void**)&h, want)); hcap = want;
+        }
+        return ORBX_OK;
+    }
+};
+OrbxWorkspace& orbx_workspace();            // the calling thread's workspace (search.cu)
+
+// lays consecutive 256-byte aligned regions out of one arena
+struct OrbxCarver {
+    size_t off = 0;
+    size_t take(size_t bytes) { const size_t o = off; off = (off + bytes + 255) & ~(size_t)255; return o; }
+};

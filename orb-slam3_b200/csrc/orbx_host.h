@@ -34,6 +34,12 @@ struct orbx_extractor {
     // stereo-match outputs (device), sized out_cap per frame slot
     float* d_uright; float* d_depth;
     int* d_st_scratch;
+    uint32_t* d_st_rows;                 // stereo: row-band index of the right keypoints
+    // frame preparation (prepare.cu): packed rectification maps of this camera and raw frame slots.
+    // Both live outside `allocs`: they survive a change of the extractor geometry.
+    int2* d_map; int map_rows, map_cols;
+    uint8_t* d_raw; size_t raw_bytes;    // raw (unrectified / colour) frames, one slot per frame slot
+    int raw_rows, raw_cols, raw_ch, raw_rgb, raw_pitch;
 };
 
 void orbx_init_tables(orbx_extractor* e);
@@ -41,3 +47,5 @@ int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch
                           std::vector<std::vector<ResizeTapX>>* tapx, std::vector<std::vector<ResizeTapY>>* tapy);
 bool orbx_build_word_taps(const std::vector<ResizeTapX>& TX, int w, int pitch, std::vector<ResizeWord>* out);
 void orbx_set_error(const char* fmt, ...);
+int launch_prepare(orbx_extractor* e, int slot0, int nframes, cudaStream_t s);
+int launch_rectify_pack(const float* mx, const float* my, int rows, int cols, int mstep_floats, int2* out, cudaStream_t s);

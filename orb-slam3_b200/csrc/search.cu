@@ -24,56 +24,13 @@
         }                                                                                      \
     } while (0)
 
-// ---- per-thread workspace ----
+// ---- per-thread workspace (declared in match_internal.h, shared with match.cu) ----
+OrbxWorkspace& orbx_workspace() { static thread_local OrbxWorkspace w; return w; }
 namespace {
-struct Workspace {
-    int device = -1;
-    cudaStream_t s = nullptr;
-    char* d = nullptr; size_t dcap = 0;     // device arena
-    char* h = nullptr; size_t hcap = 0;     // pinned mirror of the arena's input part / output landing zone
-    ~Workspace() { release(); }
-    void release()
-    {
-        if (device < 0) return;
-        if (cudaSetDevice(device) == cudaSuccess) {
-            if (d) cudaFree(d);
-            if (h) cudaFreeHost(h);
-            if (s) cudaStreamDestroy(s);
-        }
-        d = nullptr; h = nullptr; s = nullptr; dcap = hcap = 0; device = -1;
-    }
-    int bind(int dev)
-    {
-        if (dev < 0 || dev >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", dev); return ORBX_ERR_CUDA; }
-        if (device != dev) release();
-        CUDA_TRYS(cudaSetDevice(dev));
-        if (!s) CUDA_TRYS(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-        device = dev;
-        return ORBX_OK;
-    }
-    int reserve(size_t dbytes, size_t hbytes)
-    {
-        if (dbytes > dcap) {
-            if (d) { CUDA_TRYS(cudaStreamSynchronize(s)); CUDA_TRYS(cudaFree(d)); d = nullptr; dcap = 0; }
-            const size_t want = dbytes + dbytes / 2 + (1u << 20);
-            CUDA_TRYS(cudaMalloc((void**)&d, want)); dcap = want;
-        }
-        if (hbytes > hcap) {
-            if (h) { CUDA_TRYS(cudaStreamSynchronize(s)); CUDA_TRYS(cudaFreeHost(h)); h = nullptr; hcap = 0; }
-            const size_t want = hbytes + hbytes / 2 + (1u << 20);
-            CUDA_TRYS(cudaMallocHost((void**)&h, want)); hcap = want;
-        }
-        return ORBX_OK;
-    }
-};
-thread_local Workspace t_ws;
-
-// lays consecutive 256-byte aligned regions out of one arena
-struct Carver {
-    size_t off = 0;
-    size_t take(size_t bytes) { const size_t o = off; off = (off + bytes + 255) & ~(size_t)255; return o; }
-};
-}  // namespace
+typedef OrbxWorkspace Workspace;
+typedef OrbxCarver Carver;
+}
+#define t_ws orbx_workspace()
 
 // ---- windows: GetFeaturesInArea (src/Frame.cc:784-871) + DescriptorDistance for nq queries ----
 struct WinArgs {

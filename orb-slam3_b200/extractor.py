@@ -81,6 +81,68 @@ class ORBextractor:
                                           nkp.ctypes.data, mono.ctypes.data))
         return mono, nkp, kps, desc
 
+    # ---- frame preparation in front of operator(): remap + cvtColor on the device ----
+    def set_rectify_maps(self, mapx, mapy):
+        """M1, M2 of cv::initUndistortRectifyMap(..., CV_32F, ...) (Examples/Stereo/stereo_euroc.cc:117-118); None clears."""
+        if mapx is None:
+            check(self.lib.orbx_set_rectify_maps(self.h, None, None, 0, 0, 0)); self._map_shape = None
+            return
+        mapx = np.ascontiguousarray(mapx, np.float32); mapy = np.ascontiguousarray(mapy, np.float32)
+        assert mapx.shape == mapy.shape and mapx.ndim == 2
+        check(self.lib.orbx_set_rectify_maps(self.h, mapx.ctypes.data, mapy.ctypes.data, mapx.shape[0], mapx.shape[1], mapx.strides[0]))
+        self._map_shape = mapx.shape
+
+    def _prepared_shape(self, src_shape):
+        return getattr(self, "_map_shape", None) or tuple(src_shape[:2])
+
+    def prepare_extract(self, image: np.ndarray, lapping=(0, 0), rgb=False):
+        """cv::remap (stereo_euroc.cc:168) -> cvtColor (Tracking.cc:1264-1290) -> operator(); image HxW or HxWxC u8."""
+        assert image.dtype == np.uint8 and image.ndim in (2, 3) and image.flags.c_contiguous
+        ch = 1 if image.ndim == 2 else image.shape[2]
+        rows, cols = self._prepared_shape(image.shape)
+        cap = self.max_keypoints(rows, cols)
+        kps = np.empty(cap, KP_DTYPE); desc = np.empty((cap, 32), np.uint8)
+        n = C.c_int(0)
+        self._last_shape = (1, rows, cols)
+        mono = check(self.lib.orbx_prepare_extract(self.h, image.ctypes.data, image.shape[0], image.shape[1], ch, int(rgb),
+                                                   image.strides[0], int(lapping[0]), int(lapping[1]),
+                                                   kps.ctypes.data, desc.ctypes.data, cap, C.byref(n)))
+        return mono, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def prepare_extract_batch(self, frames: np.ndarray, lapping=(0, 0), rgb=False, kps=None, desc=None):
+        """frames: [B, rows, cols] or [B, rows, cols, C] uint8.  Returns (mono[B], nkp[B], kps[B,cap], desc[B,cap,32])."""
+        assert frames.dtype == np.uint8 and frames.ndim in (3, 4) and frames.flags.c_contiguous
+        B = frames.shape[0]; ch = 1 if frames.ndim == 3 else frames.shape[3]
+        rows, cols = self._prepared_shape(frames.shape[1:])
+        cap = self.max_keypoints(rows, cols)
+        if kps is None:
+            kps = np.empty((B, cap), KP_DTYPE)
+        if desc is None:
+            desc = np.empty((B, cap, 32), np.uint8)
+        nkp = np.empty(B, np.int32); mono = np.empty(B, np.int32)
+        self._last_shape = (B, rows, cols)
+        check(self.lib.orbx_prepare_extract_batch(self.h, B, frames.ctypes.data, frames.shape[1], frames.shape[2], ch, int(rgb),
+                                                  frames.strides[1], frames.strides[0], int(lapping[0]), int(lapping[1]),
+                                                  kps.ctypes.data, desc.ctypes.data, cap, nkp.ctypes.data, mono.ctypes.data))
+        return mono, nkp, kps, desc
+
+    def prepare_upload(self, frames: np.ndarray, rgb=False):
+        assert frames.dtype == np.uint8 and frames.ndim in (3, 4) and frames.flags.c_contiguous
+        B = frames.shape[0]; ch = 1 if frames.ndim == 3 else frames.shape[3]
+        rows, cols = self._prepared_shape(frames.shape[1:])
+        check(self.lib.orbx_prepare_upload(self.h, B, frames.ctypes.data, frames.shape[1], frames.shape[2], ch, int(rgb),
+                                           frames.strides[1], frames.strides[0]))
+        self._shape = self._last_shape = (B, rows, cols)
+
+    def prepare_resident(self): check(self.lib.orbx_prepare_resident(self.h))
+
+    def prepared(self, frame=0) -> np.ndarray:
+        """imRect / mImGray: the frame operator() saw."""
+        _, rows, cols = self._last_shape
+        out = np.empty((rows, cols), np.uint8)
+        check(self.lib.orbx_get_prepared(self.h, frame, out.ctypes.data, out.strides[0]))
+        return out
+
     # ---- device-resident path (kernel timing) ----
     def reserve(self, rows, cols, batch): check(self.lib.orbx_reserve(self.h, rows, cols, batch))
 

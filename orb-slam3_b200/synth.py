@@ -70,6 +70,40 @@ def synth_stereo_pair(rows: int, cols: int, seed: int, max_disp: int = 40):
     return left, right
 
 
+def synth_rectify_maps(rows: int, cols: int, src_rows: int | None = None, src_cols: int | None = None, seed: int = 0):
+    """CV_32FC1 maps shaped like cv::initUndistortRectifyMap's (Examples/Stereo/stereo_euroc.cc:117-118): a
+    small rotation + radial (k1, k2) distortion about a principal point, in float32 arithmetic.  Near the
+    corners the maps leave the source image (remap's BORDER_CONSTANT taps)."""
+    src_rows = src_rows or rows; src_cols = src_cols or cols
+    rng = np.random.default_rng(seed + 77)
+    fx = np.float32(0.61 * cols); fy = np.float32(0.61 * cols)
+    cx = np.float32(cols / 2 + rng.uniform(-6, 6)); cy = np.float32(rows / 2 + rng.uniform(-6, 6))
+    k1 = np.float32(-0.28 + rng.uniform(-0.02, 0.02)); k2 = np.float32(0.07)
+    th = np.float32(rng.uniform(-0.01, 0.01))
+    y, x = np.mgrid[0:rows, 0:cols].astype(np.float32)
+    xn = (x - cx) / fx; yn = (y - cy) / fy
+    xr = np.cos(th) * xn - np.sin(th) * yn; yr = np.sin(th) * xn + np.cos(th) * yn
+    r2 = xr * xr + yr * yr
+    k = np.float32(1) + k1 * r2 + k2 * r2 * r2
+    sx = np.float32(src_cols / cols); sy = np.float32(src_rows / rows)
+    mapx = ((xr * k * fx + cx) * sx + np.float32(rng.uniform(-1.5, 1.5))).astype(np.float32)
+    mapy = ((yr * k * fy + cy) * sy + np.float32(rng.uniform(-1.5, 1.5))).astype(np.float32)
+    return np.ascontiguousarray(mapx), np.ascontiguousarray(mapy)
+
+
+def synth_color_frame(rows: int, cols: int, seed: int, channels: int = 3) -> np.ndarray:
+    """A colour camera frame: the gray synthetic frame with per-channel gain / offset / noise (alpha = 255)."""
+    g = synth_frame(rows, cols, seed).astype(np.float32)
+    rng = np.random.default_rng(seed + 4242)
+    out = np.empty((rows, cols, channels), np.uint8)
+    for c in range(3):
+        ch = g * np.float32(rng.uniform(0.8, 1.15)) + np.float32(rng.uniform(-12, 12)) + rng.integers(-3, 4, (rows, cols))
+        out[..., c] = np.clip(np.rint(ch), 0, 255).astype(np.uint8)
+    if channels == 4:
+        out[..., 3] = 255
+    return out
+
+
 def synth_map_points(desc: np.ndarray, kps_xy: np.ndarray, octaves: np.ndarray, n: int, seed: int,
                      rows: int, cols: int, nlevels: int = 8):
     """Synthetic map points for SearchByProjection: descriptors of real keypoints with 0..40 random
