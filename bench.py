@@ -227,6 +227,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="bounded CPU-baseline sample")
     ap.add_argument("--ref-frames-per-core", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-legs", action="store_true", help="skip the matching / prepare legs")
     ap.add_argument("--e2e-passes", type=int, default=4, help="host frames per e2e call = passes x batch")
     args = ap.parse_args()
 
@@ -358,6 +359,21 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_oracle_throughput(pkg, rows, cols, nf, lap, args.cpu_seconds)
 
+    # ---------------- matching + frame-preparation legs (rank 0, N=1 only; outside the timed regions) ----------------
+    matching = prepare = None
+    if rank == 0 and world == 1 and not args.no_extra_legs:
+        X.close()
+        sys.path.insert(0, str(ROOT / "tools"))
+        import bench_match as bm
+        pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+        try:
+            matching = {"stereo": bm.stereo_leg(pkg, 256, 10, 2, local_rank), "knn2_1000": bm.knn_leg(pkg, 1000, 20, 3, local_rank),
+                        "knn2_8192": bm.knn_leg(pkg, 8192, 10, 2, local_rank), "search_by_projection_5k": bm.proj_leg(pkg, 20, 3, local_rank)}
+            prepare = bm.prepare_leg(pkg, 256, 2, 4, 2, local_rank, pinned=pin)
+        except Exception as ex:                                  # the headline line must still print
+            matching = matching or {"error": repr(ex)}
+            prepare = prepare or {"error": repr(ex)}
+
     if rank == 0:
         line = {"metric": "ORB extract+describe frames/s @752x480,1000kp", "value": value, "unit": "frames/s",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
@@ -368,7 +384,7 @@ def main():
                                  f"{B * sum(h * w for h, w in level_dims(rows, cols, isf)) * 2 / 1e6:.0f} MB of pyramid/blur planes per step vs 126 MB L2",
                            "partition": "frames sharded across ranks, no collective"},
                 "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
-                "cpu_baseline": cpu, "wall_ms_per_step": wall_ms / args.steps}
+                "cpu_baseline": cpu, "wall_ms_per_step": wall_ms / args.steps, "matching": matching, "prepare": prepare}
         print(json.dumps(line), flush=True)
     X.close()
     if world > 1:

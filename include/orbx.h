@@ -288,6 +288,51 @@ int orbx_search_by_bow(int device, int mode,
                        const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
                        float nnratio, int checkOrientation, int32_t* matches);
 
+/* int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints,
+ * vector<MapPoint*>& vpMatched, int th, float ratioHamming) include/ORBmatcher.h, src/ORBmatcher.cc:549-678, and the
+ * overload with vpPointsKFs / vpMatchedKF, :681-797 (same search; the extra vectors are caller bookkeeping).
+ * Keyframe: kps (mvKeysUn) / desc, bounds, scale factors.  One row per candidate map point: descriptor, projection
+ * uv under Scw (:584-600, host geometry), predicted level (:628), mp_valid = !isBad() && !spAlreadyFound.count(pMP)
+ * && depth > 0 && the distance and viewing-angle gates (:582-625).  KeyFrame::IsInImage (:603) is applied here.
+ * matched (may be NULL): vpMatched[idx] != NULL on entry.  assign[n] out: row of the map point each keypoint newly
+ * receives, -1 = none.  Returns nmatches. */
+int orbx_search_by_projection_sim3(int device,
+                                   const orbx_keypoint* kps, const uint8_t* desc, int n,
+                                   float minX, float maxX, float minY, float maxY,
+                                   const float* scaleFactors, int nlevels,
+                                   int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                   const int32_t* mp_level, const uint8_t* mp_valid,
+                                   float th, float ratioHamming, const uint8_t* matched, int32_t* assign);
+
+/* The search of int ORBmatcher::Fuse(KeyFrame* pKF, const vector<MapPoint*>& vpMapPoints, const float th, const bool bRight)
+ * src/ORBmatcher.cc:1823-2035 (mp_ur != NULL: reprojection gates :1958-1985 against uRight (NULL: mono keyframe) and
+ * invLevelSigma2) and of Fuse(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, float th,
+ * vector<MapPoint*>& vpReplacePoint) :2051-2185 (mp_ur == NULL).  Rows as above; mp_valid folds every gate before
+ * IsInImage (:1861-1903, 1916-1932 / :2078-2117).  best_idx[i]: keypoint row i fuses with (-1: none or distance >
+ * TH_LOW), best_dist[i]: its distance (256: no candidate).  Replace / AddObservation / AddMapPoint (:2001-2026,
+ * 2165-2180) stay with the caller, in row order.  Returns the number of rows with a fuse target. */
+int orbx_fuse(int device,
+              const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+              float minX, float maxX, float minY, float maxY,
+              const float* scaleFactors, const float* invLevelSigma2, int nlevels,
+              int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v, const float* mp_ur,
+              const int32_t* mp_level, const uint8_t* mp_valid, float th,
+              int32_t* best_idx, int32_t* best_dist);
+
+/* int ORBmatcher::SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12, const float& s12,
+ * const cv::Mat& R12, const cv::Mat& t12, const float th) src/ORBmatcher.cc:2201-2434.  Rows 1: per keypoint of KF1
+ * its map point's descriptor, projection into KF2 (:2259-2277), predicted level in KF2 (:2293), valid1 = pMP &&
+ * !vbAlreadyMatched1[i1] && !isBad() && depth > 0 && distance gate; rows 2 the reverse direction.  match12[n1] out:
+ * idx2 of every cross-checked new match (:2415-2431), -1 otherwise.  Returns nFound. */
+int orbx_search_by_sim3(int device,
+                        const orbx_keypoint* kps1, const uint8_t* desc1, int n1,
+                        const orbx_keypoint* kps2, const uint8_t* desc2, int n2,
+                        float minX, float maxX, float minY, float maxY,
+                        const float* scaleFactors, int nlevels,
+                        const uint8_t* mp1_desc, const float* u1in2, const float* v1in2, const int32_t* level1, const uint8_t* valid1,
+                        const uint8_t* mp2_desc, const float* u2in1, const float* v2in1, const int32_t* level2, const uint8_t* valid2,
+                        float th, int32_t* match12);
+
 /* void ORBmatcher::ComputeThreeMaxima(vector<int>* histo, const int L, int&, int&, int&)
  * include/ORBmatcher.h:107, src/ORBmatcher.cc:2863-2905 on the bin sizes (host, no device work). */
 void orbx_three_maxima(const int32_t* sizes, int L, int32_t* ind1, int32_t* ind2, int32_t* ind3);

@@ -160,6 +160,23 @@ int   orc_search_by_projection_keyframe(const orc_grid* g, const orc_keypoint* k
                                         const int32_t* mp_level, const float* mp_angle, const uint8_t* mp_valid,
                                         float th, int ORBdist, int checkOrientation, const uint8_t* cur_held, int32_t* assign);
 
+/* ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th, ratioHamming), src/ORBmatcher.cc:549-678 (and :681-797) */
+int   orc_search_by_projection_sim3(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* sf,
+                                    int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                    const int32_t* mp_level, const uint8_t* mp_valid,
+                                    float th, float ratioHamming, const uint8_t* matched, int32_t* assign);
+/* the search of ORBmatcher::Fuse, src/ORBmatcher.cc:1823-2035 (mp_ur != NULL) and :2051-2185 (mp_ur == NULL) */
+int   orc_fuse(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+               const float* sf, const float* inv_sigma2,
+               int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v, const float* mp_ur,
+               const int32_t* mp_level, const uint8_t* mp_valid, float th, int32_t* best_idx, int32_t* best_dist);
+/* ORBmatcher::SearchBySim3, src/ORBmatcher.cc:2201-2434 */
+int   orc_search_by_sim3(const orc_grid* g1, const orc_keypoint* kps1, const uint8_t* desc1, int n1,
+                         const orc_grid* g2, const orc_keypoint* kps2, const uint8_t* desc2, int n2, const float* sf,
+                         const uint8_t* mp1_desc, const float* u1in2, const float* v1in2, const int32_t* level1, const uint8_t* valid1,
+                         const uint8_t* mp2_desc, const float* u2in1, const float* v2in1, const int32_t* level2, const uint8_t* valid2,
+                         float th, int32_t* match12);
+
 /* ORBmatcher::SearchByBoW (KF,Frame: mode 0, src/ORBmatcher.cc:314-547; KF,KF: mode 1, :955-1105) */
 int   orc_search_by_bow(int mode,
                         const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,

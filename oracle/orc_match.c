@@ -601,3 +601,148 @@ int orc_search_by_projection_keyframe(const orc_grid* g, const orc_keypoint* kps
     hist_free(&H); free(held); free(vIndices2);
     return nmatches;
 }
+
+/* ---- the remaining windowed searches of SURVEY 8a row 16 (loop closing / local mapping) ----
+ * All of them: project a map point into a keyframe (caller geometry: mp_u, mp_v, mp_level = PredictScale,
+ * mp_valid = every gate before KeyFrame::IsInImage), KeyFrame::GetFeaturesInArea(u, v, th*scale[level])
+ * (src/KeyFrame.cc:916-962: no level filter, same grid as the Frame), keypoints at levels
+ * [level-1, level], best Hamming distance, first best wins. */
+
+/* KeyFrame::IsInImage, src/KeyFrame.cc:965-968 */
+static int kf_in_image(const orc_grid* g, float x, float y) { return x >= g->minX && x < g->maxX && y >= g->minY && y < g->maxY; }
+
+/* ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th, ratioHamming), src/ORBmatcher.cc:549-678,
+ * and its twin with vpPointsKFs / vpMatchedKF, :681-797 (same search; the extra vectors are caller bookkeeping).
+ * matched: vpMatched[idx] != NULL on entry (may be NULL); assign[idx] = row of the map point newly matched. */
+int orc_search_by_projection_sim3(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* sf,
+                                  int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                  const int32_t* mp_level, const uint8_t* mp_valid,
+                                  float th, float ratioHamming, const uint8_t* matched, int32_t* assign)
+{
+    int nmatches = 0;
+    uint8_t* held = (uint8_t*)calloc((size_t)(n > 0 ? n : 1), 1);
+    int32_t* vIndices = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; i++) { assign[i] = -1; if (matched) held[i] = matched[i] != 0; }
+    for (int i = 0; i < nmp; i++) {
+        if (!mp_valid[i]) continue;                                           /* :582-594, 610-625 */
+        const float u = mp_u[i], v = mp_v[i];
+        if (!kf_in_image(g, u, v)) continue;                                  /* :603 */
+        const int lvl = mp_level[i];
+        const float radius = th * sf[lvl];                                    /* :631 */
+        const int nc = orc_grid_query(g, kps, u, v, radius, -1, -1, vIndices, n);   /* :634 */
+        if (nc == 0) continue;
+        int bestDist = 256, bestIdx = -1;
+        for (int k = 0; k < nc; k++) {                                        /* :645-664 */
+            const int idx = vIndices[k];
+            if (held[idx]) continue;
+            const int kpLevel = kps[idx].octave;
+            if (kpLevel < lvl - 1 || kpLevel > lvl) continue;
+            const int dist = orc_hamming256(mp_desc + 32 * (size_t)i, desc + 32 * (size_t)idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestIdx >= 0 && bestDist <= TH_LOW * ratioHamming) {              /* :667 (bestIdx = -1 would index vpMatched[-1] there) */
+            assign[bestIdx] = i; held[bestIdx] = 1;
+            nmatches++;
+        }
+    }
+    free(held); free(vIndices);
+    return nmatches;
+}
+
+/* The search of ORBmatcher::Fuse(KeyFrame*, const vector<MapPoint*>&, th, bRight), src/ORBmatcher.cc:1823-2035
+ * (mp_ur != NULL: reprojection gates :1958-1985 with uRight (NULL = mono keyframe, all -1) and invLevelSigma2),
+ * and of Fuse(KeyFrame*, Scw, vpPoints, th, vpReplacePoint), :2051-2185 (mp_ur == NULL: no such gates).
+ * best_idx[i] = keypoint the map point fuses with (-1: none, bestDist > TH_LOW); Replace / AddObservation stay
+ * with the caller.  Returns the number of rows with a fuse target. */
+int orc_fuse(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+             const float* sf, const float* inv_sigma2,
+             int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v, const float* mp_ur,
+             const int32_t* mp_level, const uint8_t* mp_valid, float th, int32_t* best_idx, int32_t* best_dist)
+{
+    int nFused = 0;
+    int32_t* vIndices = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < nmp; i++) {
+        best_idx[i] = -1; best_dist[i] = 256;
+        if (!mp_valid[i]) continue;
+        const float u = mp_u[i], v = mp_v[i];
+        if (!kf_in_image(g, u, v)) continue;                                  /* :1905 / :2096 */
+        const int lvl = mp_level[i];
+        const float radius = th * sf[lvl];                                    /* :1938 / :2124 */
+        const int nc = orc_grid_query(g, kps, u, v, radius, -1, -1, vIndices, n);
+        if (nc == 0) continue;
+        int bestDist = 256, bestIdx = -1;
+        for (int k = 0; k < nc; k++) {
+            const int idx = vIndices[k];
+            const int kpLevel = kps[idx].octave;
+            if (kpLevel < lvl - 1 || kpLevel > lvl) continue;                 /* :1955 / :2143 */
+            if (mp_ur) {
+                const float ex = u - kps[idx].x, ey = v - kps[idx].y;
+                if (uRight && uRight[idx] >= 0) {                             /* :1958-1972 */
+                    const float er = mp_ur[i] - uRight[idx];
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * inv_sigma2[kpLevel] > 7.8) continue;
+                } else {                                                      /* :1974-1985 */
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * inv_sigma2[kpLevel] > 5.99) continue;
+                }
+            }
+            const int dist = orc_hamming256(mp_desc + 32 * (size_t)i, desc + 32 * (size_t)idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        best_dist[i] = bestDist;
+        if (bestDist <= TH_LOW) { best_idx[i] = bestIdx; nFused++; }          /* :1999 / :2163 */
+    }
+    free(vIndices);
+    return nFused;
+}
+
+/* one direction of SearchBySim3 (:2248-2330 / :2333-2412): best keypoint per projected map point, <= TH_HIGH */
+static void sim3_direction(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* sf,
+                           int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                           const int32_t* mp_level, const uint8_t* mp_valid, float th, int32_t* vnMatch)
+{
+    int32_t* vIndices = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < nmp; i++) {
+        vnMatch[i] = -1;
+        if (!mp_valid[i]) continue;
+        const float u = mp_u[i], v = mp_v[i];
+        if (!kf_in_image(g, u, v)) continue;                                  /* :2280 */
+        const int lvl = mp_level[i];
+        const float radius = th * sf[lvl];                                    /* :2296 */
+        const int nc = orc_grid_query(g, kps, u, v, radius, -1, -1, vIndices, n);
+        if (nc == 0) continue;
+        int bestDist = 0x7fffffff, bestIdx = -1;
+        for (int k = 0; k < nc; k++) {
+            const int idx = vIndices[k];
+            if (kps[idx].octave < lvl - 1 || kps[idx].octave > lvl) continue;
+            const int dist = orc_hamming256(mp_desc + 32 * (size_t)i, desc + 32 * (size_t)idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestDist <= TH_HIGH) vnMatch[i] = bestIdx;                        /* :2326 */
+    }
+    free(vIndices);
+}
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th), src/ORBmatcher.cc:2201-2434.
+ * Rows 1 = keypoints of KF1 (their map points projected into KF2), rows 2 the reverse; valid folds the
+ * map point, vbAlreadyMatched, isBad, depth and distance gates.  match12[i1] = idx2 of a cross-checked
+ * new match (:2415-2431) or -1.  Returns nFound. */
+int orc_search_by_sim3(const orc_grid* g1, const orc_keypoint* kps1, const uint8_t* desc1, int n1,
+                       const orc_grid* g2, const orc_keypoint* kps2, const uint8_t* desc2, int n2, const float* sf,
+                       const uint8_t* mp1_desc, const float* u1in2, const float* v1in2, const int32_t* level1, const uint8_t* valid1,
+                       const uint8_t* mp2_desc, const float* u2in1, const float* v2in1, const int32_t* level2, const uint8_t* valid2,
+                       float th, int32_t* match12)
+{
+    int32_t* m1 = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n1 > 0 ? n1 : 1));
+    int32_t* m2 = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n2 > 0 ? n2 : 1));
+    sim3_direction(g2, kps2, desc2, n2, sf, n1, mp1_desc, u1in2, v1in2, level1, valid1, th, m1);
+    sim3_direction(g1, kps1, desc1, n1, sf, n2, mp2_desc, u2in1, v2in1, level2, valid2, th, m2);
+    int nFound = 0;
+    for (int i1 = 0; i1 < n1; i1++) {
+        match12[i1] = -1;
+        const int idx2 = m1[i1];
+        if (idx2 >= 0 && m2[idx2] == i1) { match12[i1] = idx2; nFound++; }
+    }
+    free(m1); free(m2);
+    return nFound;
+}

@@ -108,6 +108,13 @@ class Oracle:
         L.orc_search_for_initialization.restype = C.c_int
         L.orc_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                                     C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.orc_search_by_projection_sim3.restype = C.c_int
+        L.orc_search_by_projection_sim3.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + \
+            [C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_fuse.restype = C.c_int
+        L.orc_fuse.argtypes = [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 6 + [C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_search_by_sim3.restype = C.c_int
+        L.orc_search_by_sim3.argtypes = ([C.c_void_p] * 3 + [C.c_int]) * 2 + [C.c_void_p] + [C.c_void_p] * 10 + [C.c_float, C.c_void_p]
         L.orc_search_by_projection_keyframe.restype = C.c_int
         L.orc_search_by_projection_keyframe.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 6 + \
             [C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
@@ -436,3 +443,48 @@ def search_by_projection_keyframe(grid: Grid, desc, scale_factors, mp: dict, th:
                                                   ma.ctypes.data, mval.ctypes.data, th, int(orb_dist), int(check_orientation),
                                                   _p(held), assign.ctypes.data)
     return nm, assign
+
+
+def search_by_projection_sim3(grid: Grid, desc, scale_factors, mp: dict, th: float, ratio_hamming: float, matched=None):
+    """ORBmatcher::SearchByProjection(KeyFrame*, Scw, ...) (src/ORBmatcher.cc:549, :681).  mp: SoA dict desc,u,v,level,valid."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(grid.kps)
+    assign = np.full(n, -1, np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    held = None if matched is None else np.ascontiguousarray(matched, np.uint8)
+    f = lambda k, t: np.ascontiguousarray(mp[k], t)
+    md, mu, mv, ml, mval = f("desc", np.uint8), f("u", np.float32), f("v", np.float32), f("level", np.int32), f("valid", np.uint8)
+    nm = grid.L.orc_search_by_projection_sim3(grid.g, grid.kps.ctypes.data, desc.ctypes.data, n, sf.ctypes.data, len(mu),
+                                              md.ctypes.data, mu.ctypes.data, mv.ctypes.data, ml.ctypes.data, mval.ctypes.data,
+                                              th, ratio_hamming, _p(held), assign.ctypes.data)
+    return nm, assign
+
+
+def fuse(grid: Grid, desc, uRight, scale_factors, inv_sigma2, mp: dict, th: float):
+    """The search of ORBmatcher::Fuse (src/ORBmatcher.cc:1823, :2051).  mp: desc,u,v,level,valid and optionally ur."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(grid.kps)
+    sf = np.ascontiguousarray(scale_factors, np.float32); isg = np.ascontiguousarray(inv_sigma2, np.float32)
+    ur = None if uRight is None else np.ascontiguousarray(uRight, np.float32)
+    f = lambda k, t: np.ascontiguousarray(mp[k], t)
+    md, mu, mv, ml, mval = f("desc", np.uint8), f("u", np.float32), f("v", np.float32), f("level", np.int32), f("valid", np.uint8)
+    mur = f("ur", np.float32) if mp.get("ur") is not None else None
+    bi = np.empty(len(mu), np.int32); bd = np.empty(len(mu), np.int32)
+    nf = grid.L.orc_fuse(grid.g, grid.kps.ctypes.data, desc.ctypes.data, n, _p(ur), sf.ctypes.data, isg.ctypes.data, len(mu),
+                         md.ctypes.data, mu.ctypes.data, mv.ctypes.data, _p(mur), ml.ctypes.data, mval.ctypes.data, th,
+                         bi.ctypes.data, bd.ctypes.data)
+    return nf, bi, bd
+
+
+def search_by_sim3(grid1: Grid, desc1, grid2: Grid, desc2, scale_factors, rows1: dict, rows2: dict, th: float):
+    """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:2201).  rows1: KF1's map points projected into KF2 (desc,u,v,level,valid)."""
+    desc1 = np.ascontiguousarray(desc1, np.uint8); desc2 = np.ascontiguousarray(desc2, np.uint8)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    n1, n2 = len(grid1.kps), len(grid2.kps)
+    g = lambda r, k, t: np.ascontiguousarray(r[k], t)
+    a = [g(rows1, "desc", np.uint8), g(rows1, "u", np.float32), g(rows1, "v", np.float32), g(rows1, "level", np.int32), g(rows1, "valid", np.uint8)]
+    b = [g(rows2, "desc", np.uint8), g(rows2, "u", np.float32), g(rows2, "v", np.float32), g(rows2, "level", np.int32), g(rows2, "valid", np.uint8)]
+    m12 = np.empty(n1, np.int32)
+    nf = grid1.L.orc_search_by_sim3(grid1.g, grid1.kps.ctypes.data, desc1.ctypes.data, n1, grid2.g, grid2.kps.ctypes.data, desc2.ctypes.data, n2,
+                                    sf.ctypes.data, *[x.ctypes.data for x in a], *[x.ctypes.data for x in b], th, m12.ctypes.data)
+    return nf, m12

@@ -89,6 +89,12 @@ SYMBOLS = {
                                       [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] + [C.c_int] * 4 + [C.c_void_p]),
     "orbx_search_by_bow": (C.c_int, [C.c_int, C.c_int] + ([C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_int]) * 2 +
                            [C.c_float, C.c_int, C.c_void_p]),
+    "orbx_search_by_projection_sim3": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                                                 C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
+    "orbx_fuse": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float,
+                            C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_float, C.c_void_p, C.c_void_p]),
+    "orbx_search_by_sim3": (C.c_int, [C.c_int] + [C.c_void_p, C.c_void_p, C.c_int] * 2 + [C.c_float] * 4 + [C.c_void_p, C.c_int] +
+                            [C.c_void_p] * 10 + [C.c_float, C.c_void_p]),
     "orbx_three_maxima": (None, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 

@@ -220,6 +220,72 @@ struct ORBmatcherGPU {
         return r;
     }
 
+    // Rows of candidate map points projected into a keyframe, as the loop-closing / local-mapping searches visit
+    // them (Scw or the keyframe pose applied on the host): descriptor, projection, predicted level, validity.
+    struct ProjectedPointsSoA {
+        std::vector<uint8_t> desc;                     // n x 32: pMP->GetDescriptor()
+        std::vector<float> u, v;                       // pKF->mpCamera->project(Rcw * p3Dw + tcw)
+        std::vector<float> ur;                         // u - bf * invz (first Fuse form only; empty otherwise)
+        std::vector<int32_t> level;                    // pMP->PredictScale(dist3D, pKF)
+        std::vector<uint8_t> valid;                    // every gate before KeyFrame::IsInImage
+    };
+
+    // int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints,
+    // vector<MapPoint*>& vpMatched, int th, float ratioHamming)  src/ORBmatcher.cc:549-678 (and :681-797).
+    // matched[idx] = vpMatched[idx] != NULL; assign[idx] = row newly matched (the caller stores vpPoints[row] /
+    // vpPointsKFs[row] into vpMatched / vpMatchedKF).
+    int SearchByProjection(const FrameView& KF, const ProjectedPointsSoA& pts, int th, float ratioHamming,
+                           const std::vector<uint8_t>* matched, std::vector<int32_t>& assign, int device = 0) const
+    {
+        const int n = KF.N();
+        assign.assign((size_t)n, -1);
+        const int r = orbx_search_by_projection_sim3(
+            device, KF.kps(), KF.mDescriptors->data, n, KF.mnMinX, KF.mnMaxX, KF.mnMinY, KF.mnMaxY,
+            KF.mvScaleFactors->data(), (int)KF.mvScaleFactors->size(),
+            (int)pts.u.size(), pts.desc.data(), pts.u.data(), pts.v.data(), pts.level.data(), pts.valid.data(),
+            (float)th, ratioHamming, matched ? matched->data() : nullptr, assign.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchByProjection(KeyFrame,Sim3): ") + orbx_last_error());
+        return r;
+    }
+
+    // The search of int ORBmatcher::Fuse(KeyFrame* pKF, const vector<MapPoint*>& vpMapPoints, const float th, const bool
+    // bRight) src/ORBmatcher.cc:1823-2035 (pts.ur filled, mvInvLevelSigma2 given) and of Fuse(KeyFrame* pKF, cv::Mat Scw,
+    // const vector<MapPoint*>& vpPoints, float th, vector<MapPoint*>& vpReplacePoint) :2051-2185 (pts.ur empty).
+    // bestIdx[row] = keypoint the map point fuses with or -1; the caller then walks the rows in order and does
+    // Replace / AddObservation / AddMapPoint / vpReplacePoint exactly as :2001-2026 / :2165-2180.
+    int Fuse(const FrameView& KF, const std::vector<float>* mvInvLevelSigma2, const ProjectedPointsSoA& pts, float th,
+             std::vector<int32_t>& bestIdx, std::vector<int32_t>& bestDist, int device = 0) const
+    {
+        const size_t nmp = pts.u.size();
+        bestIdx.assign(nmp, -1); bestDist.assign(nmp, 256);
+        const bool chi2 = !pts.ur.empty();
+        const int r = orbx_fuse(
+            device, KF.kps(), KF.mDescriptors->data, KF.N(), KF.mvuRight ? KF.mvuRight->data() : nullptr,
+            KF.mnMinX, KF.mnMaxX, KF.mnMinY, KF.mnMaxY, KF.mvScaleFactors->data(),
+            mvInvLevelSigma2 ? mvInvLevelSigma2->data() : nullptr, (int)KF.mvScaleFactors->size(),
+            (int)nmp, pts.desc.data(), pts.u.data(), pts.v.data(), chi2 ? pts.ur.data() : nullptr, pts.level.data(),
+            pts.valid.data(), th, bestIdx.data(), bestDist.data());
+        if (r < 0) throw std::runtime_error(std::string("Fuse: ") + orbx_last_error());
+        return r;
+    }
+
+    // int ORBmatcher::SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12, const float& s12,
+    // const cv::Mat& R12, const cv::Mat& t12, const float th)  src/ORBmatcher.cc:2201-2434.
+    // pts1: KF1's map points projected into KF2 (one row per KF1 keypoint), pts2 the reverse; match12[i1] = idx2 of
+    // every new cross-checked match (the caller sets vpMatches12[i1] = vpMapPoints2[idx2]).
+    int SearchBySim3(const FrameView& KF1, const FrameView& KF2, const ProjectedPointsSoA& pts1, const ProjectedPointsSoA& pts2,
+                     float th, std::vector<int32_t>& match12, int device = 0) const
+    {
+        match12.assign((size_t)KF1.N(), -1);
+        const int r = orbx_search_by_sim3(
+            device, KF1.kps(), KF1.mDescriptors->data, KF1.N(), KF2.kps(), KF2.mDescriptors->data, KF2.N(),
+            KF2.mnMinX, KF2.mnMaxX, KF2.mnMinY, KF2.mnMaxY, KF2.mvScaleFactors->data(), (int)KF2.mvScaleFactors->size(),
+            pts1.desc.data(), pts1.u.data(), pts1.v.data(), pts1.level.data(), pts1.valid.data(),
+            pts2.desc.data(), pts2.u.data(), pts2.v.data(), pts2.level.data(), pts2.valid.data(), th, match12.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchBySim3: ") + orbx_last_error());
+        return r;
+    }
+
     // void ORBmatcher::ComputeThreeMaxima(vector<int>* histo, const int L, int&, int&, int&)
     // include/ORBmatcher.h:107, src/ORBmatcher.cc:2863-2905
     static void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3)

@@ -21,7 +21,7 @@
 // Grid = (query tiles of 128, train splits): one thread per query, the split's train rows broadcast from
 // shared memory; every (split, query) leaves its partial best / second best, knn2_merge_kernel folds the
 // splits in ascending train order (strict '<' keeps the lower train index on ties, as BFMatcher does).
-// The split count is chosen so that the grid covers the 148 SMs about twice even for 1000 x 1000.
+// The split count is chosen so that the grid gives every SM about 8 CTAs when the train set allows (>= 64 rows per split).
 #define KNN_THREADS 128
 #define KNN_TILE 128
 
@@ -80,7 +80,7 @@ extern "C" int orbx_knn2_hamming(int device, const uint8_t* q, int nq, const uin
     int rc = W.bind(device);
     if (rc != ORBX_OK) return rc;
     const int tiles = (nq + KNN_THREADS - 1) / KNN_THREADS;
-    int nsplit = (2 * 148 + tiles - 1) / tiles;                       // cover the SMs about twice
+    int nsplit = (8 * 148 + tiles - 1) / tiles;                       // ~8 CTAs of 128 threads per SM
     const int max_split = nt > 0 ? (nt + 63) / 64 : 1;                // at least 64 train rows per split
     if (nsplit > max_split) nsplit = max_split;
     if (nsplit < 1) nsplit = 1;

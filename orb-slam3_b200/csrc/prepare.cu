@@ -46,15 +46,25 @@ __device__ __forceinline__ uint32_t prepare_pixel(const PrepArgs& A, const uint8
     if (REMAP) {
         const int ix = (int)(short)(m.x & 0xFFFF), iy = m.x >> 16;
         const int fx = m.y & 31, fy = (m.y >> 5) & 31;
-        const int w00 = (32 - fx) * (32 - fy) * 32, w01 = fx * (32 - fy) * 32, w10 = (32 - fx) * fy * 32, w11 = fx * fy * 32;
-        const bool x0 = ix >= 0 && ix < A.scols, x1 = ix + 1 >= 0 && ix + 1 < A.scols;
-        const bool y0 = iy >= 0 && iy < A.srows, y1 = iy + 1 >= 0 && iy + 1 < A.srows;
+        // (sum_k tap_k * w_k * 32 + 2^14) >> 15 == (sum_k tap_k * w_k + 2^9) >> 10 with w = (32-fx | fx) * (32-fy | fy):
+        // two horizontal lerps and one vertical, all exact in int32
         const uint8_t* p = S + (long long)iy * A.spitch + (long long)ix * CH;
+        if ((unsigned)ix < (unsigned)(A.scols - 1) && (unsigned)iy < (unsigned)(A.srows - 1)) {
 #pragma unroll
-        for (int c = 0; c < NC; c++) {
-            const int t00 = (x0 && y0) ? p[c] : 0, t01 = (x1 && y0) ? p[CH + c] : 0;
-            const int t10 = (x0 && y1) ? p[A.spitch + c] : 0, t11 = (x1 && y1) ? p[A.spitch + CH + c] : 0;
-            v[c] = (t00 * w00 + t01 * w01 + t10 * w10 + t11 * w11 + (1 << 14)) >> 15;
+            for (int c = 0; c < NC; c++) {
+                const int top = p[c] * (32 - fx) + p[CH + c] * fx, bot = p[A.spitch + c] * (32 - fx) + p[A.spitch + CH + c] * fx;
+                v[c] = (top * (32 - fy) + bot * fy + 512) >> 10;
+            }
+        } else {                                          // some tap reads the constant border (0)
+            const bool x0 = ix >= 0 && ix < A.scols, x1 = ix + 1 >= 0 && ix + 1 < A.scols;
+            const bool y0 = iy >= 0 && iy < A.srows, y1 = iy + 1 >= 0 && iy + 1 < A.srows;
+#pragma unroll
+            for (int c = 0; c < NC; c++) {
+                const int t00 = (x0 && y0) ? p[c] : 0, t01 = (x1 && y0) ? p[CH + c] : 0;
+                const int t10 = (x0 && y1) ? p[A.spitch + c] : 0, t11 = (x1 && y1) ? p[A.spitch + CH + c] : 0;
+                const int top = t00 * (32 - fx) + t01 * fx, bot = t10 * (32 - fx) + t11 * fx;
+                v[c] = (top * (32 - fy) + bot * fy + 512) >> 10;
+            }
         }
     } else {
         const uint8_t* p = S + (long long)y * A.spitch + (long long)x * CH;

@@ -740,3 +740,253 @@ extern "C" int orbx_search_by_bow(int device, int mode,
     }
     return nmatches;
 }
+
+// ---- the loop-closing / local-mapping searches of SURVEY 8a row 16: best keypoint in a window ----
+//   Fuse(KeyFrame*, const vector<MapPoint*>&, th, bRight)            src/ORBmatcher.cc:1823-2035
+//   Fuse(KeyFrame*, Scw, vpPoints, th, vpReplacePoint)               :2051-2185
+//   SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th)         :2201-2434
+// Every map point's search is independent of the others (nothing the loop mutates is read by the search
+// itself), so the whole decision runs on the device: one warp per projected map point sweeps the window's
+// cells (KeyFrame::GetFeaturesInArea, src/KeyFrame.cc:916-962), keeps keypoints at levels [level-1, level]
+// that pass the optional reprojection gates, and reduces (distance, visiting position) to the first best.
+struct BestArgs {
+    const orbx_keypoint* kps; const uint4* desc; int n; const float* uRight;
+    float minX, minY, winv, hinv;
+    const int* cell_start; const int* cell_idx;
+    int nq; const uint4* q_desc; const float *q_x, *q_y, *q_r, *q_ur; const int* q_lvl;
+    int chi2;                              // reprojection gates of the first Fuse form (:1958-1985)
+    float isig2[ORBX_MAX_LEVELS];
+    int2* best;                            // (idx, dist); idx = -1: no candidate
+};
+
+__global__ void __launch_bounds__(WIN_WARPS * 32)
+best_in_window_kernel(BestArgs A)
+{
+    const int q = blockIdx.x * WIN_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (q >= A.nq) return;
+    const float r = A.q_r[q];
+    int bestDist = INT_MAX, bestIdx = -1, bestPos = INT_MAX;
+    if (r >= 0.f) {
+        const float x = A.q_x[q], y = A.q_y[q];
+        const int lvl = A.q_lvl[q];
+        int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), r), A.winv)));              // src/KeyFrame.cc:924
+        int cx1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, A.minX), r), A.winv)));   // :929
+        const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, A.minY), r), A.hinv)));        // :933
+        const int cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, A.minY), r), A.hinv)));   // :937
+        if (cx0 >= GRID_COLS || cx1 < 0 || cy0 >= GRID_ROWS || cy1 < 0) { cx0 = 1; cx1 = 0; }
+        const uint4 a0 = A.q_desc[2 * q], a1 = A.q_desc[2 * q + 1];
+        const float ur = (A.chi2 && A.q_ur) ? A.q_ur[q] : 0.f;
+        int pos = lane;                                    // visiting position: warp-uniform base + lane
+        for (int ix = cx0; ix <= cx1; ix++)
+            for (int iy = cy0; iy <= cy1; iy++) {
+                const int c = ix * GRID_ROWS + iy;
+                const int b = A.cell_start[c], e = A.cell_start[c + 1];
+                for (int j0 = b; j0 < e; j0 += 32, pos += 32) {
+                    const int j = j0 + lane;
+                    if (j >= e) continue;
+                    const int idx = A.cell_idx[j];
+                    const orbx_keypoint kp = A.kps[idx];
+                    const float dx = __fsub_rn(kp.x, x), dy = __fsub_rn(kp.y, y);
+                    if (!(fabsf(dx) < r && fabsf(dy) < r)) continue;                                       // :955
+                    if (kp.octave < lvl - 1 || kp.octave > lvl) continue;                                  // src/ORBmatcher.cc:1955
+                    if (A.chi2) {
+                        const float ex = __fsub_rn(x, kp.x), ey = __fsub_rn(y, kp.y);
+                        const float kr = A.uRight ? A.uRight[idx] : -1.f;
+                        if (kr >= 0) {                                                                     // :1958-1972
+                            const float er = __fsub_rn(ur, kr);
+                            const float e2 = __fadd_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)), __fmul_rn(er, er));
+                            if ((double)__fmul_rn(e2, A.isig2[kp.octave]) > 7.8) continue;
+                        } else {                                                                           // :1974-1985
+                            const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                            if ((double)__fmul_rn(e2, A.isig2[kp.octave]) > 5.99) continue;
+                        }
+                    }
+                    const int dist = ham256(a0, a1, A.desc[2 * idx], A.desc[2 * idx + 1]);
+                    if (dist < bestDist) { bestDist = dist; bestIdx = idx; bestPos = pos; }
+                }
+            }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const int od = __shfl_xor_sync(0xffffffffu, bestDist, o), oi = __shfl_xor_sync(0xffffffffu, bestIdx, o);
+            const int op = __shfl_xor_sync(0xffffffffu, bestPos, o);
+            if (od < bestDist || (od == bestDist && op < bestPos)) { bestDist = od; bestIdx = oi; bestPos = op; }
+        }
+    }
+    if (lane == 0) A.best[q] = make_int2(bestIdx, bestDist);
+}
+
+namespace {
+struct BestHost {
+    const orbx_keypoint* kps; const uint8_t* desc; int n; const float* uRight;
+    float minX, maxX, minY, maxY;
+    int nq; const uint8_t* q_desc; const float *q_x, *q_y, *q_r, *q_ur; const int32_t* q_lvl;
+    int chi2; const float* isig2; int nlevels;
+};
+
+// one H2D copy, grid build + best_in_window_kernel, one D2H copy of nq (idx, dist) pairs (pinned; valid until the
+// calling thread's next search call)
+int run_best(int device, const BestHost& in, const int2** out)
+{
+    Workspace& W = t_ws;
+    int rc = W.bind(device);
+    if (rc != ORBX_OK) return rc;
+    const size_t n = (size_t)in.n, nq = (size_t)in.nq;
+    Carver c;
+    const size_t o_kps = c.take(n * sizeof(orbx_keypoint)), o_desc = c.take(n * 32), o_ur = c.take(in.uRight ? n * 4 : 0);
+    const size_t o_qd = c.take(nq * 32), o_qx = c.take(nq * 4), o_qy = c.take(nq * 4), o_qr = c.take(nq * 4);
+    const size_t o_qur = c.take(in.q_ur ? nq * 4 : 0), o_ql = c.take(nq * 4);
+    const size_t in_bytes = c.off;
+    const size_t o_best = c.take(nq * 8);
+    const size_t out_end = c.off;
+    const size_t o_cs = c.take((GRID_CELLS + 1) * 4), o_ci = c.take(n * 4);
+    rc = W.reserve(c.off, out_end);
+    if (rc != ORBX_OK) return rc;
+    char* h = W.h; char* d = W.d;
+    memcpy(h + o_kps, in.kps, n * sizeof(orbx_keypoint)); memcpy(h + o_desc, in.desc, n * 32);
+    if (in.uRight) memcpy(h + o_ur, in.uRight, n * 4);
+    memcpy(h + o_qd, in.q_desc, nq * 32); memcpy(h + o_qx, in.q_x, nq * 4); memcpy(h + o_qy, in.q_y, nq * 4);
+    memcpy(h + o_qr, in.q_r, nq * 4); memcpy(h + o_ql, in.q_lvl, nq * 4);
+    if (in.q_ur) memcpy(h + o_qur, in.q_ur, nq * 4);
+    CUDA_TRYS(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, W.s));
+    GridArgs g;
+    g.kps = (const orbx_keypoint*)(d + o_kps); g.n = in.n; g.minX = in.minX; g.minY = in.minY;
+    g.winv = (float)GRID_COLS / (float)(in.maxX - in.minX);
+    g.hinv = (float)GRID_ROWS / (float)(in.maxY - in.minY);
+    g.cell_start = (int*)(d + o_cs); g.cell_idx = (int*)(d + o_ci);
+    orbx_launch_grid_build(g, W.s);
+    BestArgs A;
+    A.kps = g.kps; A.desc = (const uint4*)(d + o_desc); A.n = in.n; A.uRight = in.uRight ? (const float*)(d + o_ur) : nullptr;
+    A.minX = g.minX; A.minY = g.minY; A.winv = g.winv; A.hinv = g.hinv; A.cell_start = g.cell_start; A.cell_idx = g.cell_idx;
+    A.nq = in.nq; A.q_desc = (const uint4*)(d + o_qd); A.q_x = (const float*)(d + o_qx); A.q_y = (const float*)(d + o_qy);
+    A.q_r = (const float*)(d + o_qr); A.q_ur = in.q_ur ? (const float*)(d + o_qur) : nullptr; A.q_lvl = (const int*)(d + o_ql);
+    A.chi2 = in.chi2;
+    for (int l = 0; l < ORBX_MAX_LEVELS; l++) A.isig2[l] = (in.isig2 && l < in.nlevels) ? in.isig2[l] : 0.f;
+    A.best = (int2*)(d + o_best);
+    best_in_window_kernel<<<(in.nq + WIN_WARPS - 1) / WIN_WARPS, WIN_WARPS * 32, 0, W.s>>>(A);
+    CUDA_TRYS(cudaGetLastError());
+    CUDA_TRYS(cudaMemcpyAsync(h + o_best, d + o_best, nq * 8, cudaMemcpyDeviceToHost, W.s));
+    CUDA_TRYS(cudaStreamSynchronize(W.s));
+    *out = (const int2*)(h + o_best);
+    return ORBX_OK;
+}
+
+// window of a projected map point: KeyFrame::IsInImage (src/KeyFrame.cc:965-968), radius th * scale[level]; -1 = no search
+int keyframe_windows(int nmp, const float* mp_u, const float* mp_v, const int32_t* mp_level, const uint8_t* mp_valid,
+                     float minX, float maxX, float minY, float maxY, const float* scaleFactors, int nlevels, float th,
+                     std::vector<float>* q_r)
+{
+    q_r->assign((size_t)nmp, -1.f);
+    for (int i = 0; i < nmp; i++) {
+        if (!mp_valid[i]) continue;
+        if (!(mp_u[i] >= minX && mp_u[i] < maxX && mp_v[i] >= minY && mp_v[i] < maxY)) continue;
+        const int lvl = mp_level[i];
+        if (lvl < 0 || lvl >= nlevels) { orbx_set_error("map point %d: level %d out of range", i, lvl); return ORBX_ERR_ARG; }
+        const float r = th * scaleFactors[lvl];
+        if (r >= 0.f) (*q_r)[i] = r;
+    }
+    return ORBX_OK;
+}
+}  // namespace
+
+extern "C" int orbx_search_by_projection_sim3(int device,
+                                              const orbx_keypoint* kps, const uint8_t* desc, int n,
+                                              float minX, float maxX, float minY, float maxY,
+                                              const float* scaleFactors, int nlevels,
+                                              int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                              const int32_t* mp_level, const uint8_t* mp_valid,
+                                              float th, float ratioHamming, const uint8_t* matched, int32_t* assign)
+{
+    if (bad_frame(kps, desc, n, minX, maxX, minY, maxY) || nmp < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors ||
+        (n > 0 && !assign) || (nmp > 0 && (!mp_desc || !mp_u || !mp_v || !mp_level || !mp_valid))) {
+        orbx_set_error("bad search_by_projection_sim3 arguments"); return ORBX_ERR_ARG;
+    }
+    for (int i = 0; i < n; i++) assign[i] = -1;
+    if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
+    if (n == 0 || nmp == 0) return 0;
+    std::vector<float> q_r;
+    int rc = keyframe_windows(nmp, mp_u, mp_v, mp_level, mp_valid, minX, maxX, minY, maxY, scaleFactors, nlevels, th, &q_r);
+    if (rc != ORBX_OK) return rc;
+    std::vector<int32_t> q_min(nmp), q_max(nmp);
+    for (int i = 0; i < nmp; i++) { q_min[i] = mp_level[i] - 1; q_max[i] = mp_level[i]; }    // :653
+    // bestDist <= TH_LOW * ratioHamming (:667, int against float) <=> bestDist <= floor of the float product
+    const float lim = (float)TH_LOW * ratioHamming;
+    const int maxDist = lim >= 255.f ? 255 : (lim < 0.f ? -1 : (int)floorf(lim));   // 256 = "no candidate"
+    return projection_replay(device, kps, desc, n, nullptr, minX, maxX, minY, maxY, nmp, mp_desc, mp_u, mp_v,
+                             q_r.data(), nullptr, q_min.data(), q_max.data(), nullptr, nullptr, maxDist, 0, matched, assign);
+}
+
+extern "C" int orbx_fuse(int device,
+                         const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+                         float minX, float maxX, float minY, float maxY,
+                         const float* scaleFactors, const float* invLevelSigma2, int nlevels,
+                         int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v, const float* mp_ur,
+                         const int32_t* mp_level, const uint8_t* mp_valid, float th,
+                         int32_t* best_idx, int32_t* best_dist)
+{
+    if (bad_frame(kps, desc, n, minX, maxX, minY, maxY) || nmp < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors ||
+        (mp_ur && !invLevelSigma2) ||
+        (nmp > 0 && (!mp_desc || !mp_u || !mp_v || !mp_level || !mp_valid || !best_idx || !best_dist))) {
+        orbx_set_error("bad fuse arguments"); return ORBX_ERR_ARG;
+    }
+    for (int i = 0; i < nmp; i++) { best_idx[i] = -1; best_dist[i] = 256; }
+    if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
+    if (n == 0 || nmp == 0) return 0;
+    std::vector<float> q_r;
+    int rc = keyframe_windows(nmp, mp_u, mp_v, mp_level, mp_valid, minX, maxX, minY, maxY, scaleFactors, nlevels, th, &q_r);
+    if (rc != ORBX_OK) return rc;
+    BestHost in = {kps, desc, n, uRight, minX, maxX, minY, maxY, nmp, mp_desc, mp_u, mp_v, q_r.data(), mp_ur, mp_level,
+                   mp_ur != nullptr, invLevelSigma2, nlevels};
+    const int2* best = nullptr;
+    rc = run_best(device, in, &best);
+    if (rc != ORBX_OK) return rc;
+    int nFused = 0;
+    for (int i = 0; i < nmp; i++) {
+        if (best[i].x < 0) continue;
+        best_dist[i] = best[i].y;
+        if (best[i].y <= TH_LOW) { best_idx[i] = best[i].x; nFused++; }                // :1999 / :2163
+    }
+    return nFused;
+}
+
+extern "C" int orbx_search_by_sim3(int device,
+                                   const orbx_keypoint* kps1, const uint8_t* desc1, int n1,
+                                   const orbx_keypoint* kps2, const uint8_t* desc2, int n2,
+                                   float minX, float maxX, float minY, float maxY,
+                                   const float* scaleFactors, int nlevels,
+                                   const uint8_t* mp1_desc, const float* u1in2, const float* v1in2, const int32_t* level1, const uint8_t* valid1,
+                                   const uint8_t* mp2_desc, const float* u2in1, const float* v2in1, const int32_t* level2, const uint8_t* valid2,
+                                   float th, int32_t* match12)
+{
+    if (bad_frame(kps1, desc1, n1, minX, maxX, minY, maxY) || bad_frame(kps2, desc2, n2, minX, maxX, minY, maxY) ||
+        nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors || (n1 > 0 && !match12) ||
+        (n1 > 0 && (!mp1_desc || !u1in2 || !v1in2 || !level1 || !valid1)) || (n2 > 0 && (!mp2_desc || !u2in1 || !v2in1 || !level2 || !valid2))) {
+        orbx_set_error("bad search_by_sim3 arguments"); return ORBX_ERR_ARG;
+    }
+    for (int i = 0; i < n1; i++) match12[i] = -1;
+    if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
+    if (n1 == 0 || n2 == 0) return 0;
+    std::vector<float> q_r;
+    // KF1's map points in KF2 (:2248-2330)
+    int rc = keyframe_windows(n1, u1in2, v1in2, level1, valid1, minX, maxX, minY, maxY, scaleFactors, nlevels, th, &q_r);
+    if (rc != ORBX_OK) return rc;
+    BestHost a = {kps2, desc2, n2, nullptr, minX, maxX, minY, maxY, n1, mp1_desc, u1in2, v1in2, q_r.data(), nullptr, level1, 0, nullptr, nlevels};
+    const int2* best = nullptr;
+    rc = run_best(device, a, &best);
+    if (rc != ORBX_OK) return rc;
+    std::vector<int> vnMatch1((size_t)n1, -1), vnMatch2((size_t)n2, -1);
+    for (int i = 0; i < n1; i++) if (best[i].x >= 0 && best[i].y <= TH_HIGH) vnMatch1[i] = best[i].x;   // :2326
+    // KF2's map points in KF1 (:2333-2412)
+    rc = keyframe_windows(n2, u2in1, v2in1, level2, valid2, minX, maxX, minY, maxY, scaleFactors, nlevels, th, &q_r);
+    if (rc != ORBX_OK) return rc;
+    BestHost b = {kps1, desc1, n1, nullptr, minX, maxX, minY, maxY, n2, mp2_desc, u2in1, v2in1, q_r.data(), nullptr, level2, 0, nullptr, nlevels};
+    rc = run_best(device, b, &best);
+    if (rc != ORBX_OK) return rc;
+    for (int i = 0; i < n2; i++) if (best[i].x >= 0 && best[i].y <= TH_HIGH) vnMatch2[i] = best[i].x;
+    int nFound = 0;
+    for (int i1 = 0; i1 < n1; i1++) {                                                   // :2415-2431
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0 && vnMatch2[idx2] == i1) { match12[i1] = idx2; nFound++; }
+    }
+    return nFound;
+}

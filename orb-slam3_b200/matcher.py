@@ -177,6 +177,54 @@ def SearchByBoW(mode: int, kf1: dict, kf2: dict, nnratio: float, check_orientati
     return nm, out
 
 
+def SearchByProjectionSim3(kps, desc, bounds, scale_factors, mp: dict, th: float, ratio_hamming: float, matched=None, device: int = 0):
+    """ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th, ratioHamming) (src/ORBmatcher.cc:549, :681).
+    mp: SoA dict desc,u,v,level,valid.  Returns (nmatches, assign)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE); desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(kps); sf = np.ascontiguousarray(scale_factors, np.float32)
+    assign = np.full(n, -1, np.int32)
+    held = None if matched is None else np.ascontiguousarray(matched, np.uint8)
+    f = lambda k, t: np.ascontiguousarray(mp[k], t)
+    md, mu, mv, ml, mval = f("desc", np.uint8), f("u", np.float32), f("v", np.float32), f("level", np.int32), f("valid", np.uint8)
+    nm = check(binding.load().orbx_search_by_projection_sim3(
+        device, kps.ctypes.data, desc.ctypes.data, n, bounds[0], bounds[1], bounds[2], bounds[3], sf.ctypes.data, len(sf),
+        len(mu), md.ctypes.data, mu.ctypes.data, mv.ctypes.data, ml.ctypes.data, mval.ctypes.data, th, ratio_hamming,
+        _p(held), assign.ctypes.data))
+    return nm, assign
+
+
+def Fuse(kps, desc, uRight, bounds, scale_factors, inv_sigma2, mp: dict, th: float, device: int = 0):
+    """The search of ORBmatcher::Fuse (src/ORBmatcher.cc:1823 with mp['ur'], :2051 without).  Returns (nFused, best_idx, best_dist)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE); desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(kps); sf = np.ascontiguousarray(scale_factors, np.float32); isg = np.ascontiguousarray(inv_sigma2, np.float32)
+    ur = None if uRight is None else np.ascontiguousarray(uRight, np.float32)
+    f = lambda k, t: np.ascontiguousarray(mp[k], t)
+    md, mu, mv, ml, mval = f("desc", np.uint8), f("u", np.float32), f("v", np.float32), f("level", np.int32), f("valid", np.uint8)
+    mur = f("ur", np.float32) if mp.get("ur") is not None else None
+    bi = np.empty(len(mu), np.int32); bd = np.empty(len(mu), np.int32)
+    nf = check(binding.load().orbx_fuse(
+        device, kps.ctypes.data, desc.ctypes.data, n, _p(ur), bounds[0], bounds[1], bounds[2], bounds[3],
+        sf.ctypes.data, isg.ctypes.data, len(sf), len(mu), md.ctypes.data, mu.ctypes.data, mv.ctypes.data, _p(mur),
+        ml.ctypes.data, mval.ctypes.data, th, bi.ctypes.data, bd.ctypes.data))
+    return nf, bi, bd
+
+
+def SearchBySim3(kps1, desc1, kps2, desc2, bounds, scale_factors, rows1: dict, rows2: dict, th: float, device: int = 0):
+    """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:2201).  rows1: KF1's map points projected into KF2.  Returns (nFound, match12)."""
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); desc1 = np.ascontiguousarray(desc1, np.uint8)
+    kps2 = np.ascontiguousarray(kps2, KP_DTYPE); desc2 = np.ascontiguousarray(desc2, np.uint8)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    g = lambda r, k, t: np.ascontiguousarray(r[k], t)
+    a = [g(rows1, "desc", np.uint8), g(rows1, "u", np.float32), g(rows1, "v", np.float32), g(rows1, "level", np.int32), g(rows1, "valid", np.uint8)]
+    b = [g(rows2, "desc", np.uint8), g(rows2, "u", np.float32), g(rows2, "v", np.float32), g(rows2, "level", np.int32), g(rows2, "valid", np.uint8)]
+    m12 = np.full(len(kps1), -1, np.int32)
+    nf = check(binding.load().orbx_search_by_sim3(
+        device, kps1.ctypes.data, desc1.ctypes.data, len(kps1), kps2.ctypes.data, desc2.ctypes.data, len(kps2),
+        bounds[0], bounds[1], bounds[2], bounds[3], sf.ctypes.data, len(sf),
+        *[x.ctypes.data for x in a], *[x.ctypes.data for x in b], th, m12.ctypes.data))
+    return nf, m12
+
+
 def ComputeThreeMaxima(sizes):
     """ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:2863) on the bin sizes."""
     sizes = np.ascontiguousarray(sizes, np.int32)

@@ -235,3 +235,92 @@ def test_search_by_projection_keyframe(pkg, orc, oracle, th, orb_dist, orient, s
     assert nm_o > 100, nm_o
     assert nm_g == nm_o
     assert np.array_equal(as_g, as_o), f"{np.sum(as_g != as_o)} assignments differ"
+
+
+def _projected_rows(pkg, rng, kkps, kdesc, n, rows, cols, with_ur=False):
+    """Map-point rows projected near the keypoints they came from (some far away / outside the image / invalid)."""
+    mp = dict(desc=_flip(rng, kdesc.copy(), 0, 30),
+              u=(kkps["x"] + 3.0 + rng.normal(0, 2.5, n)).astype(np.float32), v=(kkps["y"] - 2.0 + rng.normal(0, 2.5, n)).astype(np.float32),
+              level=np.clip(kkps["octave"] + rng.choice([0, 0, 1], n), 0, 7).astype(np.int32),
+              valid=(rng.random(n) < 0.85).astype(np.uint8))
+    far = rng.random(n) < 0.1
+    mp["u"][far] = rng.uniform(-30, cols + 30, int(far.sum())).astype(np.float32)
+    mp["u"][:3] = [0.0, float(cols), -0.5]              # IsInImage: x >= min && x < max
+    mp["v"][3:6] = [0.0, float(rows), float(rows) - 0.25]
+    if with_ur:
+        mp["ur"] = (mp["u"] - rng.uniform(0, 40, n)).astype(np.float32)
+    return mp
+
+
+@pytest.mark.parametrize("th,ratio,seed,use_held", [(3.0, 1.0, 61, True), (8.0, 1.5, 62, True), (5.0, 0.6, 63, False), (8.0, 6.0, 64, True)])
+def test_search_by_projection_sim3(pkg, orc, oracle, th, ratio, seed, use_held):
+    """LoopClosing: matcher.SearchByProjection(mpCurrentKF, mScw, vpPoints, vpMatched, th, ratioHamming) (:549 and :681)."""
+    rng = np.random.default_rng(seed)
+    rows, cols, n = 480, 752, 1500
+    kkps, kdesc, _, _ = _frame(pkg, rng, n, rows, cols)
+    ckps, cdesc, perm = _moved(pkg, rng, kkps, kdesc, rows, cols)
+    mp = _projected_rows(pkg, rng, kkps, kdesc, n, rows, cols)
+    held = (rng.random(n) < 0.15).astype(np.uint8) if use_held else None
+    bounds = (0.0, float(cols), 0.0, float(rows))
+    g = orc.Grid(oracle, ckps, *bounds)
+    nm_o, as_o = orc.search_by_projection_sim3(g, cdesc, SF, mp, th, ratio, held)
+    nm_g, as_g = pkg.SearchByProjectionSim3(ckps, cdesc, bounds, SF, mp, th, ratio, held)
+    assert nm_o > 50, nm_o
+    assert nm_g == nm_o
+    assert np.array_equal(as_g, as_o), f"{np.sum(as_g != as_o)} assignments differ"
+    if use_held:
+        assert not np.any((as_g >= 0) & (held != 0))
+
+
+@pytest.mark.parametrize("form,stereo,th,seed", [("pose", True, 3.0, 71), ("pose", False, 3.0, 72), ("sim3", False, 4.0, 73), ("pose", True, 10.0, 74)])
+def test_fuse(pkg, orc, oracle, form, stereo, th, seed):
+    """LocalMapping::SearchInNeighbors: matcher.Fuse(pKFi, vpMapPointMatches) (:1823); LoopClosing::SearchAndFuse: Fuse(pKF, Scw, ...) (:2051)."""
+    rng = np.random.default_rng(seed)
+    rows, cols, n = 480, 752, 1800
+    kkps, kdesc, _, _ = _frame(pkg, rng, n, rows, cols, quant=0.5)
+    ckps, cdesc, perm = _moved(pkg, rng, kkps, kdesc, rows, cols)
+    mp = _projected_rows(pkg, rng, kkps, kdesc, n, rows, cols, with_ur=(form == "pose"))
+    uR = None
+    if stereo:
+        uR = np.where(rng.random(n) < 0.6, ckps["x"] - rng.uniform(0, 40, n), -1.0).astype(np.float32)
+    bounds = (0.0, float(cols), 0.0, float(rows))
+    isig2 = (1.0 / SIGMA2).astype(np.float32)
+    g = orc.Grid(oracle, ckps, *bounds)
+    nf_o, bi_o, bd_o = orc.fuse(g, cdesc, uR, SF, isig2, mp, th)
+    nf_g, bi_g, bd_g = pkg.Fuse(ckps, cdesc, uR, bounds, SF, isig2, mp, th)
+    assert nf_o > 30, nf_o
+    assert nf_g == nf_o
+    assert np.array_equal(bi_g, bi_o), f"{np.sum(bi_g != bi_o)} fuse targets differ"
+    assert np.array_equal(bd_g, bd_o)
+
+
+@pytest.mark.parametrize("th,seed", [(7.5, 81), (3.0, 82)])
+def test_search_by_sim3(pkg, orc, oracle, th, seed):
+    """LoopClosing::ComputeSim3: matcher.SearchBySim3(mpCurrentKF, pKF, vpMapPointMatches, s, R, t, 7.5) (:2201)."""
+    rng = np.random.default_rng(seed)
+    rows, cols, n = 480, 752, 1400
+    k1, d1, _, _ = _frame(pkg, rng, n, rows, cols)
+    k2, d2, perm = _moved(pkg, rng, k1, d1, rows, cols, flips=(0, 25))
+    inv = np.empty(n, np.int64); inv[perm] = np.arange(n)          # k2[inv[i]] is the moved copy of k1[i]
+    # rows 1: KF1's map points (descriptor ~ d1) projected where the point sits in KF2, and vice versa
+    rows1 = dict(desc=_flip(rng, d1.copy(), 0, 10), u=(k2["x"][inv] + rng.normal(0, 1.5, n)).astype(np.float32),
+                 v=(k2["y"][inv] + rng.normal(0, 1.5, n)).astype(np.float32),
+                 level=np.clip(k2["octave"][inv] + rng.choice([0, 0, 1], n), 0, 7).astype(np.int32), valid=(rng.random(n) < 0.8).astype(np.uint8))
+    rows2 = dict(desc=_flip(rng, d2.copy(), 0, 10), u=(k1["x"][perm] + rng.normal(0, 1.5, n)).astype(np.float32),
+                 v=(k1["y"][perm] + rng.normal(0, 1.5, n)).astype(np.float32),
+                 level=np.clip(k1["octave"][perm] + rng.choice([0, 0, 1], n), 0, 7).astype(np.int32), valid=(rng.random(n) < 0.8).astype(np.uint8))
+    bounds = (0.0, float(cols), 0.0, float(rows))
+    g1, g2 = orc.Grid(oracle, k1, *bounds), orc.Grid(oracle, k2, *bounds)
+    nf_o, m_o = orc.search_by_sim3(g1, d1, g2, d2, SF, rows1, rows2, th)
+    nf_g, m_g = pkg.SearchBySim3(k1, d1, k2, d2, bounds, SF, rows1, rows2, th)
+    assert nf_o > 100, nf_o
+    assert nf_g == nf_o
+    assert np.array_equal(m_g, m_o), f"{np.sum(m_g != m_o)} matches differ"
+
+
+def test_window_best_empty_inputs(pkg):
+    kps = np.zeros(0, pkg.KP_DTYPE); desc = np.zeros((0, 32), np.uint8)
+    mp = dict(desc=np.zeros((4, 32), np.uint8), u=np.ones(4, np.float32), v=np.ones(4, np.float32), level=np.zeros(4, np.int32), valid=np.ones(4, np.uint8))
+    bounds = (0.0, 100.0, 0.0, 100.0)
+    assert pkg.Fuse(kps, desc, None, bounds, SF, (1 / SIGMA2), mp, 3.0)[0] == 0
+    assert pkg.SearchByProjectionSim3(kps, desc, bounds, SF, mp, 3.0, 1.0)[0] == 0

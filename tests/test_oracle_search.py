@@ -125,3 +125,33 @@ def test_oracle_bow_identity(orc, oracle):
     assert nm == n // 2 and np.array_equal(np.nonzero(m >= 0)[0], np.arange(1, n, 2))
     nm, m = orc.search_by_bow(oracle, 1, kf, half, 0.7, True)         # mode 1 also needs a valid side-2 keypoint
     assert nm == n // 2 and np.all(m[::2] == -1)
+
+
+def test_oracle_fuse_and_sim3_identity(orc, oracle):
+    """Fuse / SearchBySim3 / SearchByProjection(KF, Scw, ...) restatements on a case with a known answer: every
+    map point carries the descriptor of exactly one keypoint and projects onto it -> it must pick that keypoint
+    (distance 0), independent of the grid walk; a brute-force numpy search gives the same best index."""
+    rng = np.random.default_rng(5)
+    kps, desc = _unique_frame(orc, rng, 800)
+    n = len(kps)
+    g = orc.Grid(oracle, kps, 0.0, 752.0, 0.0, 480.0)
+    mp = dict(desc=desc.copy(), u=kps["x"].copy(), v=kps["y"].copy(), level=kps["octave"].astype(np.int32), valid=np.ones(n, np.uint8))
+    isig2 = (1.0 / (SF * SF)).astype(np.float32)
+    inside = (kps["x"] < 752.0) & (kps["y"] < 480.0)
+    nf, bi, bd = orc.fuse(g, desc, None, SF, isig2, mp, 3.0)
+    assert nf == int(inside.sum()) and np.array_equal(bi[inside], np.arange(n)[inside]) and np.all(bd[inside] == 0)
+    mp_ur = dict(mp, ur=(kps["x"] - 5).astype(np.float32))
+    uR = (kps["x"] - 5).astype(np.float32)
+    nf2, bi2, _ = orc.fuse(g, desc, uR, SF, isig2, mp_ur, 3.0)
+    assert nf2 == nf and np.array_equal(bi2, bi)
+    # a right coordinate 10 px off fails the 3-dof gate at level 0 (100 / 1 > 7.8) but not at level 7 (100 / 12.8 = 7.8125 > 7.8 too)
+    uR_bad = (uR + 10).astype(np.float32)
+    nf3, bi3, _ = orc.fuse(g, desc, uR_bad, SF, isig2, mp_ur, 3.0)
+    assert nf3 == 0 and np.all(bi3 == -1)
+    nm, assign = orc.search_by_projection_sim3(g, desc, SF, mp, 3.0, 1.0, None)
+    assert nm == int(inside.sum()) and np.array_equal(assign[inside], np.arange(n)[inside])
+    held = np.zeros(n, np.uint8); held[::2] = 1
+    nm2, assign2 = orc.search_by_projection_sim3(g, desc, SF, mp, 3.0, 0.0, held)      # only distance 0 passes; held keypoints stay free
+    assert np.all(assign2[::2] == -1) and nm2 == int(inside[1::2].sum())
+    nf4, m12 = orc.search_by_sim3(g, desc, g, desc, SF, mp, mp, 7.5)
+    assert nf4 == int(inside.sum()) and np.array_equal(m12[inside], np.arange(n)[inside])
