@@ -288,6 +288,28 @@ int orbx_search_by_bow(int device, int mode,
                        const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
                        float nnratio, int checkOrientation, int32_t* matches);
 
+/* void Tracking::SearchLocalPoints() src/Tracking.cc:3808-3893 in one call: bool
+ * Frame::isInFrustum(MapPoint*, float viewingCosLimit) include/Frame.h, src/Frame.cc:603-711 (Nleft == -1) for every
+ * local map point ON THE DEVICE - pose Rcw (row-major 3x3), tcw, Ow; pinhole fx, fy, cx, cy (src/CameraModels/
+ * Pinhole.cpp:33-37); mbf; logScaleFactor = Frame::mfLogScaleFactor; per point world position, normal, min / max
+ * distance invariance, descriptor, candidate = !isBad() && mnLastFrameSeen != frame id (may be NULL = all) - followed
+ * by ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th, bFarPoints, thFarPoints) src/ORBmatcher.cc:45-168
+ * on the mTrack* fields, which never leave the device in between.  One upload, one download.
+ * assign[n] in/out as orbx_search_by_projection.  out_* (each may be NULL): mbTrackInView, mTrackProjX/Y/XR,
+ * mTrackDepth, mTrackViewCos, mnTrackScaleLevel.  n == 0: isInFrustum only.  Returns nmatches. */
+int orbx_search_local_points(int device,
+                             const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+                             float minX, float maxX, float minY, float maxY,
+                             const float* scaleFactors, int nlevels,
+                             const float* Rcw, const float* tcw, const float* Ow,
+                             float fx, float fy, float cx, float cy, float mbf, float logScaleFactor,
+                             int nmp, const float* mp_pos, const float* mp_normal, const float* mp_min_dist,
+                             const float* mp_max_dist, const uint8_t* mp_desc, const uint8_t* mp_candidate,
+                             float viewingCosLimit, float th, float nnratio, int bFarPoints, float thFarPoints,
+                             int32_t* assign,
+                             uint8_t* out_inview, float* out_projx, float* out_projy, float* out_projxr,
+                             float* out_depth, float* out_viewcos, int32_t* out_level);
+
 /* int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints,
  * vector<MapPoint*>& vpMatched, int th, float ratioHamming) include/ORBmatcher.h, src/ORBmatcher.cc:549-678, and the
  * overload with vpPointsKFs / vpMatchedKF, :681-797 (same search; the extra vectors are caller bookkeeping).

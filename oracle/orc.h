@@ -124,6 +124,13 @@ int   orc_search_by_projection(const orc_grid* g, const orc_keypoint* kps, const
                                float th, float nnratio, int bFarPoints, float thFarPoints,
                                int32_t* assign);
 
+/* Frame::isInFrustum (src/Frame.cc:603-711, Nleft == -1) over a list of map points; see orc_match.c */
+int   orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx, float cy, float mbf,
+                        float minX, float maxX, float minY, float maxY, float logScaleFactor, int nlevels,
+                        int nmp, const float* pos, const float* normal, const float* min_dist, const float* max_dist,
+                        const uint8_t* candidate, float viewingCosLimit,
+                        uint8_t* inview, float* projx, float* projy, float* projxr, float* depth, float* viewcos, int32_t* level);
+
 /* ORBmatcher::ComputeThreeMaxima, src/ORBmatcher.cc:2863-2905 (sizes[i] = histo[i].size()) */
 void  orc_three_maxima(const int* sizes, int L, int* ind1, int* ind2, int* ind3);
 

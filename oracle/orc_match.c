@@ -746,3 +746,60 @@ int orc_search_by_sim3(const orc_grid* g1, const orc_keypoint* kps1, const uint8
     free(m1); free(m2);
     return nFound;
 }
+
+/* ---- Frame::isInFrustum (src/Frame.cc:603-711, branch Nleft == -1) for a list of map points ----
+ * Float arithmetic follows the reference operation by operation: cv::Matx33f * Matx31f accumulates
+ * ((R0*P0 + R1*P1) + R2*P2) in float then adds t; cv::norm(Matx31f) sums the squares in DOUBLE
+ * (normL2Sqr<float, double>) and the square root is rounded to float on assignment; Pinhole::project
+ * (src/CameraModels/Pinhole.cpp:33-37) is fx*x/z + cx; Matx::dot accumulates in float;
+ * MapPoint::PredictScale (src/MapPoint.cc:725-741) is ceil(logf(maxDistance/dist) / mfLogScaleFactor)
+ * clamped to [0, nLevels-1] (std::log(float): TemplatedVocabulary.h imports namespace std).
+ * candidate[i] = the point is tested at all (src/Tracking.cc:3835-3839).  Outputs are the mTrack* fields;
+ * inview[i] = the return value.  Returns the number of points in view (nToMatch). */
+int orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx, float cy, float mbf,
+                      float minX, float maxX, float minY, float maxY, float logScaleFactor, int nlevels,
+                      int nmp, const float* pos, const float* normal, const float* min_dist, const float* max_dist,
+                      const uint8_t* candidate, float viewingCosLimit,
+                      uint8_t* inview, float* projx, float* projy, float* projxr, float* depth, float* viewcos, int32_t* level)
+{
+    int nin = 0;
+    for (int i = 0; i < nmp; i++) {
+        inview[i] = 0; projx[i] = -1; projy[i] = -1; projxr[i] = 0; depth[i] = 0; viewcos[i] = 0; level[i] = 0;   /* :607-609 */
+        if (candidate && !candidate[i]) continue;
+        const float* P = pos + 3 * (size_t)i;
+        float Pc[3];
+        for (int r = 0; r < 3; r++) {
+            float s = 0;
+            for (int k = 0; k < 3; k++) s += Rcw[3 * r + k] * P[k];
+            Pc[r] = s + tcw[r];                                               /* :615 */
+        }
+        double d2 = 0;
+        for (int k = 0; k < 3; k++) { const double v = Pc[k]; d2 += v * v; }
+        const float Pc_dist = (float)sqrt(d2);                                /* :616 */
+        const float PcZ = Pc[2];
+        const float invz = 1.0f / PcZ;
+        if (PcZ < 0.0f) continue;                                             /* :621 */
+        const float u = fx * Pc[0] / PcZ + cx, v = fy * Pc[1] / PcZ + cy;     /* :624 */
+        if (u < minX || u > maxX) continue;
+        if (v < minY || v > maxY) continue;
+        projx[i] = u; projy[i] = v;                                           /* :631-632 */
+        float PO[3];
+        for (int k = 0; k < 3; k++) PO[k] = P[k] - Ow[k];                     /* :637 */
+        double p2 = 0;
+        for (int k = 0; k < 3; k++) { const double w = PO[k]; p2 += w * w; }
+        const float dist = (float)sqrt(p2);
+        if (dist < min_dist[i] || dist > max_dist[i]) continue;               /* :640 */
+        float dot = 0;
+        for (int k = 0; k < 3; k++) dot += PO[k] * normal[3 * (size_t)i + k];
+        const float vc = dot / dist;                                          /* :646 */
+        if (vc < viewingCosLimit) continue;
+        const float ratio = max_dist[i] / dist;                               /* PredictScale */
+        int nScale = (int)ceilf(logf(ratio) / logScaleFactor);
+        if (nScale < 0) nScale = 0; else if (nScale >= nlevels) nScale = nlevels - 1;
+        inview[i] = 1;
+        projxr[i] = u - mbf * invz;                                           /* :657 */
+        depth[i] = Pc_dist; level[i] = nScale; viewcos[i] = vc;
+        nin++;
+    }
+    return nin;
+}

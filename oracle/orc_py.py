@@ -108,6 +108,8 @@ class Oracle:
         L.orc_search_for_initialization.restype = C.c_int
         L.orc_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                                     C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.orc_is_in_frustum.restype = C.c_int
+        L.orc_is_in_frustum.argtypes = [C.c_void_p] * 3 + [C.c_float] * 10 + [C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 7
         L.orc_search_by_projection_sim3.restype = C.c_int
         L.orc_search_by_projection_sim3.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + \
             [C.c_float, C.c_float, C.c_void_p, C.c_void_p]
@@ -488,3 +490,20 @@ def search_by_sim3(grid1: Grid, desc1, grid2: Grid, desc2, scale_factors, rows1:
     nf = grid1.L.orc_search_by_sim3(grid1.g, grid1.kps.ctypes.data, desc1.ctypes.data, n1, grid2.g, grid2.kps.ctypes.data, desc2.ctypes.data, n2,
                                     sf.ctypes.data, *[x.ctypes.data for x in a], *[x.ctypes.data for x in b], th, m12.ctypes.data)
     return nf, m12
+
+
+def is_in_frustum(o: Oracle, pose: dict, cam: dict, bounds, log_sf: float, nlevels: int, pts: dict, cos_limit: float = 0.5):
+    """Frame::isInFrustum (src/Frame.cc:603-711) for every point.  pose: Rcw(3x3), tcw(3), Ow(3); cam: fx, fy, cx, cy, mbf;
+    pts: pos(n,3), normal(n,3), min_dist, max_dist, candidate.  Returns (nToMatch, dict of the mTrack* fields)."""
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    R, t, Ow = f32(pose["Rcw"]).reshape(9), f32(pose["tcw"]), f32(pose["Ow"])
+    pos, nrm, dmin, dmax = f32(pts["pos"]), f32(pts["normal"]), f32(pts["min_dist"]), f32(pts["max_dist"])
+    cand = np.ascontiguousarray(pts["candidate"], np.uint8)
+    n = len(dmin)
+    out = dict(inview=np.empty(n, np.uint8), projx=np.empty(n, np.float32), projy=np.empty(n, np.float32), projxr=np.empty(n, np.float32),
+               depth=np.empty(n, np.float32), viewcos=np.empty(n, np.float32), level=np.empty(n, np.int32))
+    nin = o.L.orc_is_in_frustum(R.ctypes.data, t.ctypes.data, Ow.ctypes.data, cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["mbf"],
+                                bounds[0], bounds[1], bounds[2], bounds[3], log_sf, nlevels, n, pos.ctypes.data, nrm.ctypes.data,
+                                dmin.ctypes.data, dmax.ctypes.data, cand.ctypes.data, cos_limit,
+                                *[out[k].ctypes.data for k in ("inview", "projx", "projy", "projxr", "depth", "viewcos", "level")])
+    return nin, out

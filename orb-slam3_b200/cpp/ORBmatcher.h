@@ -220,6 +220,48 @@ struct ORBmatcherGPU {
         return r;
     }
 
+    // The local map as Tracking::SearchLocalPoints (src/Tracking.cc:3808-3893) walks it: per map point the world
+    // position, mean viewing direction, distance-invariance range, descriptor, and candidate = !isBad() &&
+    // mnLastFrameSeen != mCurrentFrame.mnId.
+    struct LocalMapSoA {
+        std::vector<float> pos, normal;                // n x 3 each: GetWorldPos2(), GetNormal2()
+        std::vector<float> minDistance, maxDistance;   // GetMinDistanceInvariance(), GetMaxDistanceInvariance()
+        std::vector<uint8_t> desc, candidate;          // n x 32 ; n
+    };
+    struct TrackFields {                               // what Frame::isInFrustum leaves in each MapPoint
+        std::vector<uint8_t> mbTrackInView;
+        std::vector<float> mTrackProjX, mTrackProjY, mTrackProjXR, mTrackDepth, mTrackViewCos;
+        std::vector<int32_t> mnTrackScaleLevel;
+        void resize(size_t n)
+        {
+            mbTrackInView.resize(n); mTrackProjX.resize(n); mTrackProjY.resize(n); mTrackProjXR.resize(n);
+            mTrackDepth.resize(n); mTrackViewCos.resize(n); mnTrackScaleLevel.resize(n);
+        }
+    };
+
+    // Frame::isInFrustum (src/Frame.cc:603-711) for the whole local map + SearchByProjection(Frame&, vector<MapPoint*>&,
+    // th, bFarPoints, thFarPoints) (src/ORBmatcher.cc:45-168) in one device round trip.  Rcw row-major 3x3.
+    // assign[i] in: >= 0 when keypoint i already holds a map point with observations; out: row matched.
+    int SearchLocalPoints(const FrameView& F, const float* Rcw, const float* tcw, const float* Ow,
+                          float fx, float fy, float cx, float cy, float mbf, float mfLogScaleFactor,
+                          const LocalMapSoA& map, float viewingCosLimit, float th, bool bFarPoints, float thFarPoints,
+                          std::vector<int32_t>& assign, TrackFields& out, int device = 0) const
+    {
+        const size_t nmp = map.minDistance.size();
+        out.resize(nmp);
+        assign.resize((size_t)F.N(), -1);
+        const int r = orbx_search_local_points(
+            device, F.kps(), F.mDescriptors->data, F.N(), F.mvuRight ? F.mvuRight->data() : nullptr,
+            F.mnMinX, F.mnMaxX, F.mnMinY, F.mnMaxY, F.mvScaleFactors->data(), (int)F.mvScaleFactors->size(),
+            Rcw, tcw, Ow, fx, fy, cx, cy, mbf, mfLogScaleFactor,
+            (int)nmp, map.pos.data(), map.normal.data(), map.minDistance.data(), map.maxDistance.data(), map.desc.data(),
+            map.candidate.empty() ? nullptr : map.candidate.data(), viewingCosLimit, th, mfNNratio, bFarPoints ? 1 : 0, thFarPoints,
+            assign.data(), out.mbTrackInView.data(), out.mTrackProjX.data(), out.mTrackProjY.data(), out.mTrackProjXR.data(),
+            out.mTrackDepth.data(), out.mTrackViewCos.data(), out.mnTrackScaleLevel.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchLocalPoints: ") + orbx_last_error());
+        return r;
+    }
+
     // Rows of candidate map points projected into a keyframe, as the loop-closing / local-mapping searches visit
     // them (Scw or the keyframe pose applied on the host): descriptor, projection, predicted level, validity.
     struct ProjectedPointsSoA {

@@ -369,3 +369,197 @@ extern "C" int orbx_search_by_projection(int device,
     if (result[1]) { orbx_set_error("a map point has more than %d candidates", PROJ_KMAX); return ORBX_ERR_CAPACITY; }
     return result[0];
 }
+
+
+// ---- Tracking::SearchLocalPoints (src/Tracking.cc:3808-3893) in one call: Frame::isInFrustum for every local map
+// point on the device (src/Frame.cc:603-711, Nleft == -1), its mTrack* fields feeding SearchByProjection directly ----
+
+// glibc's logf (sysdeps/ieee754/flt-32/e_logf.c: 16-entry table, degree-3 polynomial in double) restated; checked
+// against this image's libm over all 2 139 095 039 positive finite floats: 0 mismatches, with and without FMA
+// contraction (tools/scratch/logf_glibc_check.c).  MapPoint::PredictScale needs it bit for bit: the level is
+// ceil(logf(ratio) / logScaleFactor).
+__constant__ double c_logf_tab[32] = {
+    0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2, 0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2,
+    0x1.49539f0f010bp+0, -0x1.01eae7f513a67p-2, 0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3,
+    0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3, 0x1.25e227b0b8eap+0, -0x1.1aa2bc79c81p-3,
+    0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4, 0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4,
+    0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5, 0x1p+0, 0x0p+0,
+    0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5, 0x1.ca4b31f026aap-1, 0x1.c5e53aa362eb4p-4,
+    0x1.b2036576afce6p-1, 0x1.526e57720db08p-3, 0x1.9c2d163a1aa2dp-1, 0x1.bc2860d22477p-3,
+    0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2, 0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2};
+
+__device__ float glibc_logf(float x)
+{
+    uint32_t ix = __float_as_uint(x);
+    if (ix == 0x3f800000u) return 0.f;
+    if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) {
+        if (ix * 2 == 0) return -INFINITY;
+        if (ix == 0x7f800000u) return x;
+        if ((ix & 0x80000000u) || ix * 2 >= 0xff000000u) return NAN;
+        ix = __float_as_uint(__fmul_rn(x, 8388608.0f)); ix -= 23u << 23;       // subnormal
+    }
+    const uint32_t tmp = ix - 0x3f330000u;
+    const int i = (tmp >> 19) & 15;
+    const int k = (int)tmp >> 23;
+    const uint32_t iz = ix - (tmp & 0xff800000u);
+    const double invc = c_logf_tab[2 * i], logc = c_logf_tab[2 * i + 1];
+    const double z = (double)__uint_as_float(iz);
+    const double r = __dadd_rn(__dmul_rn(z, invc), -1.0);
+    const double y0 = __dadd_rn(logc, __dmul_rn((double)k, 0x1.62e42fefa39efp-1));
+    const double r2 = __dmul_rn(r, r);
+    double y = __dadd_rn(__dmul_rn(0x1.5575b0be00b6ap-2, r), -0x1.ffffef20a4123p-2);
+    y = __dadd_rn(__dmul_rn(-0x1.00ea348b88334p-2, r2), y);
+    y = __dadd_rn(__dmul_rn(y, r2), __dadd_rn(y0, r));
+    return __double2float_rn(y);
+}
+
+struct FrustumArgs {
+    float R[9], t[3], Ow[3];
+    float fx, fy, cx, cy, mbf;
+    float minX, maxX, minY, maxY, logsf; int nlevels;
+    int nmp; const float* pos; const float* normal; const float* dmin; const float* dmax; const uint8_t* candidate;
+    float cosLimit;
+    uint8_t* inview; float *projx, *projy, *projxr, *depth, *viewcos; int* level;
+};
+
+__global__ void __launch_bounds__(256)
+frustum_kernel(FrustumArgs A)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= A.nmp) return;
+    uint8_t in = 0; float px = -1.f, py = -1.f, pxr = 0.f, dep = 0.f, vcos = 0.f; int lvl = 0;        // :607-609
+    if (!A.candidate || A.candidate[i]) {
+        const float P0 = A.pos[3 * i], P1 = A.pos[3 * i + 1], P2 = A.pos[3 * i + 2];
+        float Pc[3];
+#pragma unroll
+        for (int r = 0; r < 3; r++)                                                                     // cv::Matx33f * Matx31f + t, :615
+            Pc[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(A.R[3 * r], P0), __fmul_rn(A.R[3 * r + 1], P1)), __fmul_rn(A.R[3 * r + 2], P2)), A.t[r]);
+        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(Pc[0], Pc[0]), __dmul_rn(Pc[1], Pc[1])), __dmul_rn(Pc[2], Pc[2]));
+        const float Pc_dist = __double2float_rn(__dsqrt_rn(d2));                                        // cv::norm, :616
+        const float z = Pc[2];
+        do {
+            if (z < 0.0f) break;                                                                        // :621
+            const float invz = __fdiv_rn(1.0f, z);
+            const float u = __fadd_rn(__fdiv_rn(__fmul_rn(A.fx, Pc[0]), z), A.cx);                      // Pinhole::project
+            const float v = __fadd_rn(__fdiv_rn(__fmul_rn(A.fy, Pc[1]), z), A.cy);
+            if (u < A.minX || u > A.maxX) break;
+            if (v < A.minY || v > A.maxY) break;
+            px = u; py = v;                                                                             // :631-632
+            const float O0 = __fsub_rn(P0, A.Ow[0]), O1 = __fsub_rn(P1, A.Ow[1]), O2 = __fsub_rn(P2, A.Ow[2]);
+            const double p2 = __dadd_rn(__dadd_rn(__dmul_rn(O0, O0), __dmul_rn(O1, O1)), __dmul_rn(O2, O2));
+            const float dist = __double2float_rn(__dsqrt_rn(p2));
+            if (dist < A.dmin[i] || dist > A.dmax[i]) break;                                            // :640
+            const float dot = __fadd_rn(__fadd_rn(__fmul_rn(O0, A.normal[3 * i]), __fmul_rn(O1, A.normal[3 * i + 1])), __fmul_rn(O2, A.normal[3 * i + 2]));
+            const float vc = __fdiv_rn(dot, dist);                                                      // :646
+            if (vc < A.cosLimit) break;
+            const float ratio = __fdiv_rn(A.dmax[i], dist);                                             // MapPoint::PredictScale
+            int nScale = (int)ceilf(__fdiv_rn(glibc_logf(ratio), A.logsf));
+            if (nScale < 0) nScale = 0; else if (nScale >= A.nlevels) nScale = A.nlevels - 1;
+            in = 1; pxr = __fsub_rn(u, __fmul_rn(A.mbf, invz)); dep = Pc_dist; lvl = nScale; vcos = vc; // :654-662
+        } while (0);
+    }
+    A.inview[i] = in; A.projx[i] = px; A.projy[i] = py; A.projxr[i] = pxr; A.depth[i] = dep; A.viewcos[i] = vcos; A.level[i] = lvl;
+}
+
+extern "C" int orbx_search_local_points(int device,
+                                        const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+                                        float minX, float maxX, float minY, float maxY,
+                                        const float* scaleFactors, int nlevels,
+                                        const float* Rcw, const float* tcw, const float* Ow,
+                                        float fx, float fy, float cx, float cy, float mbf, float logScaleFactor,
+                                        int nmp, const float* mp_pos, const float* mp_normal, const float* mp_min_dist,
+                                        const float* mp_max_dist, const uint8_t* mp_desc, const uint8_t* mp_candidate,
+                                        float viewingCosLimit, float th, float nnratio, int bFarPoints, float thFarPoints,
+                                        int32_t* assign,
+                                        uint8_t* out_inview, float* out_projx, float* out_projy, float* out_projxr,
+                                        float* out_depth, float* out_viewcos, int32_t* out_level)
+{
+    if (n < 0 || nmp < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors || !(maxX > minX) || !(maxY > minY) ||
+        !Rcw || !tcw || !Ow || (n > 0 && (!kps || !desc || !assign)) ||
+        (nmp > 0 && (!mp_pos || !mp_normal || !mp_min_dist || !mp_max_dist || (n > 0 && !mp_desc)))) {
+        orbx_set_error("bad search_local_points arguments"); return ORBX_ERR_ARG;
+    }
+    if (n >= (1 << 24)) { orbx_set_error("too many keypoints"); return ORBX_ERR_ARG; }
+    OrbxWorkspace& W = orbx_workspace();
+    int rc = W.bind(device);
+    if (rc != ORBX_OK) return rc;
+    if (nmp == 0) return 0;
+    const size_t N = (size_t)n, M = (size_t)nmp;
+    const bool search = n > 0;
+    OrbxCarver c;
+    // inputs
+    const size_t o_kps = c.take(N * sizeof(orbx_keypoint)), o_desc = c.take(N * 32), o_ur = c.take(uRight ? N * 4 : 0);
+    const size_t o_pos = c.take(M * 12), o_nrm = c.take(M * 12), o_dmin = c.take(M * 4), o_dmax = c.take(M * 4);
+    const size_t o_md = c.take(search ? M * 32 : 0), o_cand = c.take(mp_candidate ? M : 0);
+    const size_t in_bytes = c.off;
+    // outputs (one D2H copy): assign, result, then the mTrack* fields
+    const size_t o_assign = c.take(N * 4 + 4), o_result = c.take(8);
+    const size_t o_iv = c.take(M), o_px = c.take(M * 4), o_py = c.take(M * 4), o_pxr = c.take(M * 4), o_dp = c.take(M * 4), o_vc = c.take(M * 4), o_lv = c.take(M * 4);
+    const size_t out_end = c.off;
+    const size_t o_cs = c.take(4 * (size_t)(GRID_CELLS + 1)), o_ci = c.take(N * 4 + 4), o_cc = c.take(M * 4);
+    const size_t o_cl = c.take(search ? 8 * M * PROJ_KMAX : 0), o_c0 = c.take(N * 4 + 4), o_c1 = c.take(N * 4 + 4), o_ch = c.take(M * 4);
+    rc = W.reserve(c.off, out_end);
+    if (rc != ORBX_OK) return rc;
+    char* h = W.h; char* d = W.d;
+    if (search) { memcpy(h + o_kps, kps, N * sizeof(orbx_keypoint)); memcpy(h + o_desc, desc, N * 32); memcpy(h + o_md, mp_desc, M * 32); }
+    if (uRight && search) memcpy(h + o_ur, uRight, N * 4);
+    memcpy(h + o_pos, mp_pos, M * 12); memcpy(h + o_nrm, mp_normal, M * 12);
+    memcpy(h + o_dmin, mp_min_dist, M * 4); memcpy(h + o_dmax, mp_max_dist, M * 4);
+    if (mp_candidate) memcpy(h + o_cand, mp_candidate, M);
+    CUDA_TRYW(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, W.s));
+    if (search) {
+        memcpy(h + o_assign, assign, N * 4); memset(h + o_result, 0, 8);
+        CUDA_TRYW(cudaMemcpyAsync(d + o_assign, h + o_assign, o_iv - o_assign, cudaMemcpyHostToDevice, W.s));
+    }
+    FrustumArgs F;
+    for (int i = 0; i < 9; i++) F.R[i] = Rcw[i];
+    for (int i = 0; i < 3; i++) { F.t[i] = tcw[i]; F.Ow[i] = Ow[i]; }
+    F.fx = fx; F.fy = fy; F.cx = cx; F.cy = cy; F.mbf = mbf;
+    F.minX = minX; F.maxX = maxX; F.minY = minY; F.maxY = maxY; F.logsf = logScaleFactor; F.nlevels = nlevels;
+    F.nmp = nmp; F.pos = (const float*)(d + o_pos); F.normal = (const float*)(d + o_nrm);
+    F.dmin = (const float*)(d + o_dmin); F.dmax = (const float*)(d + o_dmax);
+    F.candidate = mp_candidate ? (const uint8_t*)(d + o_cand) : nullptr;
+    F.cosLimit = viewingCosLimit;
+    F.inview = (uint8_t*)(d + o_iv); F.projx = (float*)(d + o_px); F.projy = (float*)(d + o_py); F.projxr = (float*)(d + o_pxr);
+    F.depth = (float*)(d + o_dp); F.viewcos = (float*)(d + o_vc); F.level = (int*)(d + o_lv);
+    frustum_kernel<<<(nmp + 255) / 256, 256, 0, W.s>>>(F);
+    if (search) {
+        ProjArgs A;
+        memset(&A, 0, sizeof(A));
+        A.kps = (const orbx_keypoint*)(d + o_kps); A.desc = (const uint4*)(d + o_desc);
+        A.uRight = uRight ? (const float*)(d + o_ur) : nullptr;
+        A.mp_desc = (const uint4*)(d + o_md); A.projx = F.projx; A.projy = F.projy; A.projxr = F.projxr;
+        A.level = F.level; A.viewcos = F.viewcos; A.depth = F.depth; A.inview = F.inview;
+        A.assign = (int*)(d + o_assign); A.result = (int*)(d + o_result);
+        A.cell_start = (int*)(d + o_cs); A.cell_idx = (int*)(d + o_ci); A.cand_cnt = (int*)(d + o_cc); A.cand = (int*)(d + o_cl);
+        A.claim0 = (int*)(d + o_c0); A.claim1 = (int*)(d + o_c1); A.choice = (int*)(d + o_ch);
+        A.n = n; A.nmp = nmp;
+        A.minX = minX; A.minY = minY;
+        A.winv = (float)GRID_COLS / (float)(maxX - minX);
+        A.hinv = (float)GRID_ROWS / (float)(maxY - minY);
+        for (int l = 0; l < nlevels; l++) A.sf[l] = scaleFactors[l];
+        A.th = th; A.nnratio = nnratio; A.bFar = bFarPoints; A.thFar = thFarPoints;
+        GridArgs g;
+        g.kps = A.kps; g.n = n; g.minX = A.minX; g.minY = A.minY; g.winv = A.winv; g.hinv = A.hinv;
+        g.cell_start = A.cell_start; g.cell_idx = A.cell_idx;
+        orbx_launch_grid_build(g, W.s);
+        proj_candidates_kernel<<<(nmp + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32, 0, W.s>>>(A);
+        proj_resolve_kernel<<<1, 1024, 0, W.s>>>(A);
+    }
+    CUDA_TRYW(cudaGetLastError());
+    const size_t d2h0 = search ? o_assign : o_iv;
+    CUDA_TRYW(cudaMemcpyAsync(h + d2h0, d + d2h0, out_end - d2h0, cudaMemcpyDeviceToHost, W.s));
+    CUDA_TRYW(cudaStreamSynchronize(W.s));
+    if (out_inview) memcpy(out_inview, h + o_iv, M);
+    if (out_projx) memcpy(out_projx, h + o_px, M * 4);
+    if (out_projy) memcpy(out_projy, h + o_py, M * 4);
+    if (out_projxr) memcpy(out_projxr, h + o_pxr, M * 4);
+    if (out_depth) memcpy(out_depth, h + o_dp, M * 4);
+    if (out_viewcos) memcpy(out_viewcos, h + o_vc, M * 4);
+    if (out_level) memcpy(out_level, h + o_lv, M * 4);
+    if (!search) return 0;
+    memcpy(assign, h + o_assign, N * 4);
+    const int* result = (const int*)(h + o_result);
+    if (result[1]) { orbx_set_error("a map point has more than %d candidates", PROJ_KMAX); return ORBX_ERR_CAPACITY; }
+    return result[0];
+}

@@ -177,6 +177,33 @@ def SearchByBoW(mode: int, kf1: dict, kf2: dict, nnratio: float, check_orientati
     return nm, out
 
 
+def SearchLocalPoints(kps, desc, uRight, bounds, scale_factors, pose: dict, cam: dict, log_sf: float, pts: dict,
+                      cos_limit: float = 0.5, th: float = 1.0, nnratio: float = 0.8, far: bool = False, th_far: float = 0.0,
+                      assign=None, device: int = 0):
+    """Tracking::SearchLocalPoints (src/Tracking.cc:3808-3893): Frame::isInFrustum on the device + SearchByProjection.
+    pose: Rcw, tcw, Ow; cam: fx, fy, cx, cy, mbf; pts: pos(n,3), normal(n,3), min_dist, max_dist, desc, candidate.
+    Returns (nmatches, assign, dict of the mTrack* fields)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE); desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(kps); sf = np.ascontiguousarray(scale_factors, np.float32)
+    assign = np.full(n, -1, np.int32) if assign is None else np.ascontiguousarray(assign, np.int32).copy()
+    ur = None if uRight is None else np.ascontiguousarray(uRight, np.float32)
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    R, t, Ow = f32(pose["Rcw"]).reshape(9), f32(pose["tcw"]), f32(pose["Ow"])
+    pos, nrm, dmin, dmax = f32(pts["pos"]), f32(pts["normal"]), f32(pts["min_dist"]), f32(pts["max_dist"])
+    md = np.ascontiguousarray(pts["desc"], np.uint8)
+    cand = None if pts.get("candidate") is None else np.ascontiguousarray(pts["candidate"], np.uint8)
+    M = len(dmin)
+    out = dict(inview=np.empty(M, np.uint8), projx=np.empty(M, np.float32), projy=np.empty(M, np.float32), projxr=np.empty(M, np.float32),
+               depth=np.empty(M, np.float32), viewcos=np.empty(M, np.float32), level=np.empty(M, np.int32))
+    nm = check(binding.load().orbx_search_local_points(
+        device, kps.ctypes.data, desc.ctypes.data, n, _p(ur), bounds[0], bounds[1], bounds[2], bounds[3], sf.ctypes.data, len(sf),
+        R.ctypes.data, t.ctypes.data, Ow.ctypes.data, cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["mbf"], log_sf,
+        M, pos.ctypes.data, nrm.ctypes.data, dmin.ctypes.data, dmax.ctypes.data, md.ctypes.data, _p(cand),
+        cos_limit, th, nnratio, int(far), th_far, assign.ctypes.data,
+        *[out[k].ctypes.data for k in ("inview", "projx", "projy", "projxr", "depth", "viewcos", "level")]))
+    return nm, assign, out
+
+
 def SearchByProjectionSim3(kps, desc, bounds, scale_factors, mp: dict, th: float, ratio_hamming: float, matched=None, device: int = 0):
     """ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th, ratioHamming) (src/ORBmatcher.cc:549, :681).
     mp: SoA dict desc,u,v,level,valid.  Returns (nmatches, assign)."""

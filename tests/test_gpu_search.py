@@ -324,3 +324,96 @@ def test_window_best_empty_inputs(pkg):
     bounds = (0.0, 100.0, 0.0, 100.0)
     assert pkg.Fuse(kps, desc, None, bounds, SF, (1 / SIGMA2), mp, 3.0)[0] == 0
     assert pkg.SearchByProjectionSim3(kps, desc, bounds, SF, mp, 3.0, 1.0)[0] == 0
+
+
+def _scene(rng, kps, desc, rows, cols, cam, nmp, nlevels=8):
+    """A camera pose and nmp world points: 70 % back-projected from keypoints of the frame at random depths (so that
+    they project onto features), the rest scattered around / behind the camera.  Normals, distance-invariance
+    ranges and descriptors as MapPoint::UpdateNormalAndDepth would leave them, with some made to fail each gate."""
+    th = rng.uniform(-0.2, 0.2, 3)
+    Rx = np.array([[1, 0, 0], [0, np.cos(th[0]), -np.sin(th[0])], [0, np.sin(th[0]), np.cos(th[0])]])
+    Ry = np.array([[np.cos(th[1]), 0, np.sin(th[1])], [0, 1, 0], [-np.sin(th[1]), 0, np.cos(th[1])]])
+    Rz = np.array([[np.cos(th[2]), -np.sin(th[2]), 0], [np.sin(th[2]), np.cos(th[2]), 0], [0, 0, 1]])
+    R = (Rx @ Ry @ Rz).astype(np.float32)
+    t = rng.uniform(-1, 1, 3).astype(np.float32)
+    Ow = (-R.T.astype(np.float64) @ t.astype(np.float64)).astype(np.float32)
+    src = rng.integers(0, len(kps), nmp)
+    z = rng.uniform(1.0, 30.0, nmp)
+    xc = (kps["x"][src] + rng.normal(0, 1.0, nmp) - cam["cx"]) / cam["fx"] * z
+    yc = (kps["y"][src] + rng.normal(0, 1.0, nmp) - cam["cy"]) / cam["fy"] * z
+    Pc = np.stack([xc, yc, z], 1)
+    scatter = rng.random(nmp) < 0.3
+    Pc[scatter] = rng.uniform(-20, 20, (int(scatter.sum()), 3))
+    Pw = ((Pc - t.astype(np.float64)) @ R.astype(np.float64)).astype(np.float32)        # R^T (Pc - t)
+    PO = Pw.astype(np.float64) - Ow.astype(np.float64)
+    dist = np.linalg.norm(PO, axis=1)
+    nrm = PO / np.maximum(dist[:, None], 1e-9) + rng.normal(0, 0.35, (nmp, 3))
+    nrm /= np.linalg.norm(nrm, axis=1)[:, None]
+    flip = rng.random(nmp) < 0.1
+    nrm[flip] *= -1                                                                     # viewing-angle gate
+    lvl_ref = rng.integers(0, nlevels, nmp)
+    dmax = dist * (1.2 ** lvl_ref) * rng.uniform(0.9, 1.3, nmp)
+    dmin = dmax / (1.2 ** (nlevels - 1))
+    bad = rng.random(nmp) < 0.1
+    dmax[bad] = dist[bad] * 0.7                                                         # distance gate
+    d = _flip(rng, desc[src].copy(), 0, 35)
+    pts = dict(pos=Pw, normal=nrm.astype(np.float32), min_dist=dmin.astype(np.float32), max_dist=dmax.astype(np.float32), desc=d,
+               candidate=(rng.random(nmp) < 0.9).astype(np.uint8))
+    return dict(Rcw=R, tcw=t, Ow=Ow), pts
+
+
+@pytest.mark.parametrize("stereo,far,th,seed", [(False, False, 1.0, 91), (True, False, 3.0, 92), (True, True, 5.0, 93), (False, False, 15.0, 94)])
+def test_search_local_points(pkg, orc, oracle, stereo, far, th, seed):
+    """Tracking::SearchLocalPoints: isInFrustum on the device (mTrack* fields bit-exact, incl. PredictScale through the
+    restated glibc logf) feeding SearchByProjection without leaving the device."""
+    rng = np.random.default_rng(seed)
+    rows, cols, n, nmp = 480, 752, 1500, 5000
+    cam = dict(fx=435.2047, fy=435.2047, cx=367.4517, cy=252.2008, mbf=47.90639)
+    kps, desc, _, _ = _frame(pkg, rng, n, rows, cols)
+    pose, pts = _scene(rng, kps, desc, rows, cols, cam, nmp)
+    uR = np.where(rng.random(n) < 0.6, kps["x"] - rng.uniform(0.5, 40, n), -1.0).astype(np.float32) if stereo else None
+    bounds = (0.0, float(cols), 0.0, float(rows))
+    log_sf = float(np.log(np.float32(1.2)).astype(np.float32))
+    pre = np.where(rng.random(n) < 0.1, 7, -1).astype(np.int32)                        # keypoints that already hold a map point
+    nin_o, f_o = orc.is_in_frustum(oracle, pose, cam, bounds, log_sf, 8, pts, 0.5)
+    mp = dict(desc=pts["desc"], projx=f_o["projx"], projy=f_o["projy"], projxr=f_o["projxr"], level=f_o["level"],
+              viewcos=f_o["viewcos"], depth=f_o["depth"], inview=f_o["inview"])
+    g = orc.Grid(oracle, kps, *bounds)
+    nm_o, as_o = orc.search_by_projection(g, desc, uR, SF, mp, th, 0.8, far, 12.0, pre)
+    nm_g, as_g, f_g = pkg.SearchLocalPoints(kps, desc, uR, bounds, SF, pose, cam, log_sf, pts, 0.5, th, 0.8, far, 12.0, pre)
+    assert 500 < nin_o < nmp, nin_o
+    for k in ("inview", "level", "projx", "projy", "projxr", "depth", "viewcos"):
+        assert np.array_equal(f_g[k], f_o[k]), f"{k}: {np.sum(f_g[k] != f_o[k])} differ"
+    assert len(np.unique(f_o["level"][f_o["inview"] != 0])) >= 6
+    assert nm_o > 100, nm_o
+    assert nm_g == nm_o and np.array_equal(as_g, as_o)
+
+
+def test_predict_scale_boundaries(pkg, orc, oracle):
+    """PredictScale on knife edges: max_dist / dist sitting exactly on, one ulp below and one ulp above powers of
+    the scale factor (the ceil of logf(ratio) / logf(1.2f) flips there) - device logf must equal glibc's bit for bit."""
+    log_sf = float(np.log(np.float32(1.2)).astype(np.float32))
+    cam = dict(fx=400.0, fy=400.0, cx=320.0, cy=240.0, mbf=40.0)
+    pose = dict(Rcw=np.eye(3, dtype=np.float32), tcw=np.zeros(3, np.float32), Ow=np.zeros(3, np.float32))
+    base = np.float32(1.2) ** np.arange(0, 9).astype(np.float32)
+    ratios = []
+    for b in base:
+        x = np.float32(b)
+        for _ in range(40):
+            x = np.nextafter(x, np.float32(0))
+        for _ in range(80):
+            ratios.append(x); x = np.nextafter(x, np.float32(np.inf))
+    rng = np.random.default_rng(3)
+    ratios = np.concatenate([np.array(ratios, np.float32), rng.uniform(0.3, 6.0, 20000).astype(np.float32)])
+    m = len(ratios)
+    dist = rng.uniform(2.0, 20.0, m).astype(np.float32)
+    pos = np.zeros((m, 3), np.float32); pos[:, 2] = dist                              # on the optical axis: |P| = dist exactly
+    pts = dict(pos=pos, normal=np.tile(np.array([0, 0, 1], np.float32), (m, 1)), min_dist=np.zeros(m, np.float32),
+               max_dist=(ratios * dist).astype(np.float32), desc=np.zeros((m, 32), np.uint8), candidate=np.ones(m, np.uint8))
+    bounds = (0.0, 640.0, 0.0, 480.0)
+    _, f_o = orc.is_in_frustum(oracle, pose, cam, bounds, log_sf, 8, pts, 0.5)
+    empty = np.zeros(0, pkg.KP_DTYPE)
+    _, _, f_g = pkg.SearchLocalPoints(empty, np.zeros((0, 32), np.uint8), None, bounds, SF, pose, cam, log_sf, pts)
+    assert f_o["inview"].sum() > m // 2
+    assert np.array_equal(f_g["level"], f_o["level"]) and np.array_equal(f_g["inview"], f_o["inview"])
+    assert np.array_equal(f_g["depth"], f_o["depth"])
