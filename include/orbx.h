@@ -310,6 +310,14 @@ int orbx_search_local_points(int device,
                              uint8_t* out_inview, float* out_projx, float* out_projy, float* out_projxr,
                              float* out_depth, float* out_viewcos, int32_t* out_level);
 
+/* void MapPoint::ComputeDistinctiveDescriptors() include/MapPoint.h, src/MapPoint.cc:450-531, for a batch of map
+ * points.  Group p = descriptor rows [start[p], start[p+1]) of `desc` (the observations'
+ * descriptors in the order :463-481 collects them; start[0] == 0).  best_idx[p]: row within the group whose median
+ * distance to the others is least (:505-524), -1 for an empty group; best_median (may be NULL): that median.
+ * The caller copies desc row start[p] + best_idx[p] into mDescriptor (:526-530). */
+int orbx_distinctive_descriptors(int device, int npoints, const int32_t* start, const uint8_t* desc,
+                                 int32_t* best_idx, int32_t* best_median);
+
 /* int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints,
  * vector<MapPoint*>& vpMatched, int th, float ratioHamming) include/ORBmatcher.h, src/ORBmatcher.cc:549-678, and the
  * overload with vpPointsKFs / vpMatchedKF, :681-797 (same search; the extra vectors are caller bookkeeping).

@@ -131,6 +131,9 @@ int   orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, flo
                         const uint8_t* candidate, float viewingCosLimit,
                         uint8_t* inview, float* projx, float* projy, float* projxr, float* depth, float* viewcos, int32_t* level);
 
+/* MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:450-531, batched over CSR groups of descriptors */
+void  orc_distinctive_descriptors(int npoints, const int32_t* start, const uint8_t* desc, int32_t* best_idx, int32_t* best_median);
+
 /* ORBmatcher::ComputeThreeMaxima, src/ORBmatcher.cc:2863-2905 (sizes[i] = histo[i].size()) */
 void  orc_three_maxima(const int* sizes, int L, int* ind1, int* ind2, int* ind3);
 

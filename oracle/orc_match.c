@@ -803,3 +803,28 @@ int orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, float
     }
     return nin;
 }
+
+/* ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:450-531) for a batch of map points ----
+ * Group p = descriptor rows [start[p], start[p+1]) (the observations' descriptors in std::map order, as collected
+ * at :463-481).  best_idx[p] = row (within the group) with the least median distance to the others (:505-524:
+ * sorted row incl. the zero self-distance, element (size_t)(0.5*(N-1)), first least wins), -1 for an empty group. */
+static int cmp_int(const void* a, const void* b) { return *(const int*)a - *(const int*)b; }
+void orc_distinctive_descriptors(int npoints, const int32_t* start, const uint8_t* desc, int32_t* best_idx, int32_t* best_median)
+{
+    for (int p = 0; p < npoints; p++) {
+        const int N = start[p + 1] - start[p];
+        best_idx[p] = -1; best_median[p] = 0x7fffffff;
+        if (N <= 0) continue;
+        const uint8_t* D = desc + 32 * (size_t)start[p];
+        int* v = (int*)malloc(sizeof(int) * (size_t)N);
+        int BestMedian = 0x7fffffff, BestIdx = 0;
+        for (int i = 0; i < N; i++) {
+            for (int j = 0; j < N; j++) v[j] = i == j ? 0 : orc_hamming256(D + 32 * (size_t)i, D + 32 * (size_t)j);
+            qsort(v, (size_t)N, sizeof(int), cmp_int);
+            const int median = v[(size_t)(0.5 * (N - 1))];
+            if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+        }
+        free(v);
+        best_idx[p] = BestIdx; best_median[p] = BestMedian;
+    }
+}

@@ -108,6 +108,8 @@ class Oracle:
         L.orc_search_for_initialization.restype = C.c_int
         L.orc_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                                     C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.orc_distinctive_descriptors.restype = None
+        L.orc_distinctive_descriptors.argtypes = [C.c_int] + [C.c_void_p] * 4
         L.orc_is_in_frustum.restype = C.c_int
         L.orc_is_in_frustum.argtypes = [C.c_void_p] * 3 + [C.c_float] * 10 + [C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 7
         L.orc_search_by_projection_sim3.restype = C.c_int
@@ -507,3 +509,12 @@ def is_in_frustum(o: Oracle, pose: dict, cam: dict, bounds, log_sf: float, nleve
                                 dmin.ctypes.data, dmax.ctypes.data, cand.ctypes.data, cos_limit,
                                 *[out[k].ctypes.data for k in ("inview", "projx", "projy", "projxr", "depth", "viewcos", "level")])
     return nin, out
+
+
+def distinctive_descriptors(o: Oracle, start, desc):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:450-531) per CSR group.  Returns (best_idx, best_median)."""
+    start = np.ascontiguousarray(start, np.int32); desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = len(start) - 1
+    bi = np.empty(n, np.int32); bm = np.empty(n, np.int32)
+    o.L.orc_distinctive_descriptors(n, start.ctypes.data, desc.ctypes.data, bi.ctypes.data, bm.ctypes.data)
+    return bi, bm

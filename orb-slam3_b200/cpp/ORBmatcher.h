@@ -220,6 +220,17 @@ struct ORBmatcherGPU {
         return r;
     }
 
+    // void MapPoint::ComputeDistinctiveDescriptors() src/MapPoint.cc:450-531 for a batch of map points: start is the CSR
+    // offset of each point's observation descriptors in `desc` (rows of 32 bytes); bestIdx[p] = row within group p.
+    static void ComputeDistinctiveDescriptors(const std::vector<int32_t>& start, const std::vector<uint8_t>& desc,
+                                              std::vector<int32_t>& bestIdx, int device = 0)
+    {
+        const int np = start.empty() ? 0 : (int)start.size() - 1;
+        bestIdx.assign((size_t)np, -1);
+        if (orbx_distinctive_descriptors(device, np, start.data(), desc.data(), bestIdx.data(), nullptr) != ORBX_OK)
+            throw std::runtime_error(std::string("ComputeDistinctiveDescriptors: ") + orbx_last_error());
+    }
+
     // The local map as Tracking::SearchLocalPoints (src/Tracking.cc:3808-3893) walks it: per map point the world
     // position, mean viewing direction, distance-invariance range, descriptor, and candidate = !isBad() &&
     // mnLastFrameSeen != mCurrentFrame.mnId.

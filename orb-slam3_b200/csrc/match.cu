@@ -563,3 +563,85 @@ extern "C" int orbx_search_local_points(int device,
     if (result[1]) { orbx_set_error("a map point has more than %d candidates", PROJ_KMAX); return ORBX_ERR_CAPACITY; }
     return result[0];
 }
+
+
+// ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:450-531), batched ----
+// One warp per map point.  For every row i of its N observation descriptors the lanes compute the N distances
+// d(i, .) (XOR + POPC), drop them into a 257-bin histogram in shared memory, and a warp scan finds the element
+// floor(0.5*(N-1)) of the sorted row - its median as the reference takes it; the first row with the least median
+// wins.  Any N; integer pipe + shared-memory atomics.
+#define DD_WARPS 8
+#define DD_BINS 288              // 257 used; 9 bins per lane
+
+__global__ void __launch_bounds__(DD_WARPS * 32)
+distinctive_kernel(int npoints, const int* __restrict__ start, const uint4* __restrict__ desc, int* __restrict__ best_idx, int* __restrict__ best_median)
+{
+    __shared__ int s_hist[DD_WARPS][DD_BINS];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int p = blockIdx.x * DD_WARPS + w;
+    if (p >= npoints) return;
+    const int b = start[p], N = start[p + 1] - b;
+    if (N <= 0) { if (lane == 0) { best_idx[p] = -1; best_median[p] = INT_MAX; } return; }
+    const int k = (N - 1) >> 1;                                               // (size_t)(0.5*(N-1)), :516
+    int* hist = s_hist[w];
+    int BestMedian = INT_MAX, BestIdx = 0;
+    for (int i = 0; i < N; i++) {
+#pragma unroll
+        for (int q = 0; q < 9; q++) hist[lane * 9 + q] = 0;
+        __syncwarp();
+        const uint4 a0 = desc[2 * (size_t)(b + i)], a1 = desc[2 * (size_t)(b + i) + 1];
+        for (int j = lane; j < N; j += 32) {
+            const int d = j == i ? 0 : ham256(a0, a1, desc[2 * (size_t)(b + j)], desc[2 * (size_t)(b + j) + 1]);
+            atomicAdd(&hist[d], 1);
+        }
+        __syncwarp();
+        int c[9], tot = 0;
+#pragma unroll
+        for (int q = 0; q < 9; q++) { c[q] = hist[lane * 9 + q]; tot += c[q]; }
+        int inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+        int before = inc - tot, median = -1;
+        if (before <= k && k < inc) {
+#pragma unroll
+            for (int q = 0; q < 9; q++) { if (median < 0 && k < before + c[q]) median = lane * 9 + q; before += c[q]; }
+        }
+        const unsigned who = __ballot_sync(0xffffffffu, median >= 0);
+        median = __shfl_sync(0xffffffffu, median, __ffs(who) - 1);
+        if (median < BestMedian) { BestMedian = median; BestIdx = i; }        // :518-522
+        __syncwarp();
+    }
+    if (lane == 0) { best_idx[p] = BestIdx; best_median[p] = BestMedian; }
+}
+
+extern "C" int orbx_distinctive_descriptors(int device, int npoints, const int32_t* start, const uint8_t* desc,
+                                            int32_t* best_idx, int32_t* best_median)
+{
+    if (npoints < 0 || (npoints > 0 && (!start || !best_idx))) { orbx_set_error("bad distinctive_descriptors arguments"); return ORBX_ERR_ARG; }
+    if (npoints == 0) return ORBX_OK;
+    if (start[0] != 0) { orbx_set_error("distinctive_descriptors: start[0] must be 0"); return ORBX_ERR_ARG; }
+    for (int p = 0; p < npoints; p++)
+        if (start[p + 1] < start[p]) { orbx_set_error("distinctive_descriptors: start must not decrease"); return ORBX_ERR_ARG; }
+    const size_t total = (size_t)start[npoints];
+    if (total > 0 && !desc) { orbx_set_error("bad distinctive_descriptors arguments"); return ORBX_ERR_ARG; }
+    OrbxWorkspace& W = orbx_workspace();
+    int rc = W.bind(device);
+    if (rc != ORBX_OK) return rc;
+    OrbxCarver c;
+    const size_t o_start = c.take(4 * ((size_t)npoints + 1)), o_desc = c.take(total * 32);
+    const size_t in_bytes = c.off;
+    const size_t o_bi = c.take(4 * (size_t)npoints), o_bm = c.take(4 * (size_t)npoints);
+    rc = W.reserve(c.off, c.off);
+    if (rc != ORBX_OK) return rc;
+    memcpy(W.h + o_start, start, 4 * ((size_t)npoints + 1));
+    if (total) memcpy(W.h + o_desc, desc, total * 32);
+    CUDA_TRYW(cudaMemcpyAsync(W.d, W.h, in_bytes, cudaMemcpyHostToDevice, W.s));
+    distinctive_kernel<<<(npoints + DD_WARPS - 1) / DD_WARPS, DD_WARPS * 32, 0, W.s>>>(
+        npoints, (const int*)(W.d + o_start), (const uint4*)(W.d + o_desc), (int*)(W.d + o_bi), (int*)(W.d + o_bm));
+    CUDA_TRYW(cudaGetLastError());
+    CUDA_TRYW(cudaMemcpyAsync(W.h + o_bi, W.d + o_bi, c.off - o_bi, cudaMemcpyDeviceToHost, W.s));
+    CUDA_TRYW(cudaStreamSynchronize(W.s));
+    memcpy(best_idx, W.h + o_bi, 4 * (size_t)npoints);
+    if (best_median) memcpy(best_median, W.h + o_bm, 4 * (size_t)npoints);
+    return ORBX_OK;
+}

@@ -177,6 +177,16 @@ def SearchByBoW(mode: int, kf1: dict, kf2: dict, nnratio: float, check_orientati
     return nm, out
 
 
+def ComputeDistinctiveDescriptors(start, desc, device: int = 0):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:450-531), batched: CSR groups of descriptors.
+    Returns (best_idx, best_median)."""
+    start = np.ascontiguousarray(start, np.int32); desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = len(start) - 1
+    bi = np.empty(n, np.int32); bm = np.empty(n, np.int32)
+    check(binding.load().orbx_distinctive_descriptors(device, n, start.ctypes.data, desc.ctypes.data, bi.ctypes.data, bm.ctypes.data))
+    return bi, bm
+
+
 def SearchLocalPoints(kps, desc, uRight, bounds, scale_factors, pose: dict, cam: dict, log_sf: float, pts: dict,
                       cos_limit: float = 0.5, th: float = 1.0, nnratio: float = 0.8, far: bool = False, th_far: float = 0.0,
                       assign=None, device: int = 0):

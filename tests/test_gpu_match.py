@@ -103,3 +103,24 @@ def test_search_by_projection(pkg, orc, oracle, th, stereo, far):
     assert nm_g == nm_o
     assert np.array_equal(as_g, as_o), f"{np.sum(as_g != as_o)} assignments differ"
     X.close()
+
+
+@pytest.mark.parametrize("seed,maxn", [(1, 12), (2, 40), (3, 300)])
+def test_distinctive_descriptors(pkg, orc, oracle, seed, maxn):
+    """MapPoint::ComputeDistinctiveDescriptors batched: groups of 0..maxn observation descriptors (ties are frequent:
+    descriptors of a group are a few flips away from one another), best row and its median equal to the oracle's."""
+    rng = np.random.default_rng(seed)
+    npts = 700 if maxn < 100 else 60
+    sizes = rng.integers(0, maxn + 1, npts)
+    sizes[:4] = [0, 1, 2, maxn]
+    start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    base = rng.integers(0, 256, (npts, 32), dtype=np.uint8)
+    desc = np.repeat(base, sizes, axis=0)
+    bits = np.unpackbits(desc, axis=1)
+    flips = rng.random(bits.shape) < rng.choice([0.0, 0.02, 0.1], (len(bits), 1))
+    desc = np.packbits(bits ^ flips.astype(np.uint8), axis=1)
+    bi_o, bm_o = orc.distinctive_descriptors(oracle, start, desc)
+    bi_g, bm_g = pkg.ComputeDistinctiveDescriptors(start, desc)
+    assert np.array_equal(bi_g, bi_o), f"{np.sum(bi_g != bi_o)} best rows differ"
+    assert np.array_equal(bm_g, bm_o)
+    assert bi_o[0] == -1 and bi_o[1] == 0
