@@ -310,6 +310,33 @@ int orbx_search_local_points(int device,
                              uint8_t* out_inview, float* out_projx, float* out_projy, float* out_projxr,
                              float* out_depth, float* out_viewcos, int32_t* out_level);
 
+/* ---- DBoW2 vocabulary transform ---------------------------------------- */
+typedef struct orbx_vocabulary orbx_vocabulary;
+
+/* ORBVocabulary (= DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>, include/ORBVocabulary.h) built from the rows
+ * of its text file exactly as loadFromTextFile does (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1415): header
+ * k, L; row r (node id r+1): parent id, leaf flag, 32 descriptor bytes, weight.  Children keep file order, word
+ * ids number the leaves in file order.  The tree lives on `device`.  TF_IDF weighting / L1 scoring (the ORBvoc.txt
+ * header "10 6 0 0") is what orbx_compute_bow implements. */
+int orbx_vocabulary_create(int device, int k, int L, int nrows, const int32_t* parent, const uint8_t* is_leaf,
+                           const uint8_t* desc, const double* weight, orbx_vocabulary** out);
+void orbx_vocabulary_destroy(orbx_vocabulary* v);
+
+/* TemplatedVocabulary::transform(const TDescriptor& feature, WordId&, WordValue&, NodeId* nid, int levelsup)
+ * TemplatedVocabulary.h:1218-1258 for n features (HOST descriptors, n x 32): word id, word weight and the node at
+ * level L - levelsup of every feature. */
+int orbx_bow_transform(const orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup,
+                       int32_t* word, double* weight, int32_t* node);
+
+/* void Frame::ComputeBoW() src/Frame.cc:905-922 (KeyFrame::ComputeBoW alike) = transform(features, mBowVec, mFeatVec,
+ * levelsup = 4) TemplatedVocabulary.h:1127-1196.  BowVector as ascending (bow_id, bow_val) pairs, L1-normalised
+ * (capacity n each, *nbow entries); FeatureVector as CSR: fv_node[*nfv] ascending, features of node k =
+ * fv_idx[fv_start[k] .. fv_start[k+1]) in insertion order (capacities n, n+1, n) - the layout orbx_search_by_bow and
+ * orbx_search_for_triangulation take. */
+int orbx_compute_bow(const orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup,
+                     int32_t* bow_id, double* bow_val, int* nbow,
+                     int32_t* fv_node, int32_t* fv_start, int32_t* fv_idx, int* nfv);
+
 /* void MapPoint::ComputeDistinctiveDescriptors() include/MapPoint.h, src/MapPoint.cc:450-531, for a batch of map
  * points.  Group p = descriptor rows [start[p], start[p+1]) of `desc` (the observations'
  * descriptors in the order :463-481 collects them; start[0] == 0).  best_idx[p]: row within the group whose median

@@ -134,6 +134,14 @@ int   orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, flo
 /* MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:450-531, batched over CSR groups of descriptors */
 void  orc_distinctive_descriptors(int npoints, const int32_t* start, const uint8_t* desc, int32_t* best_idx, int32_t* best_median);
 
+/* DBoW2 TemplatedVocabulary::transform (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1258 and :1127-1196) behind
+ * Frame::ComputeBoW (src/Frame.cc:905-922); see orc_match.c */
+void  orc_bow_transform(const int32_t* child_start, const int32_t* child_idx, const uint8_t* node_desc,
+                        const double* node_weight, const int32_t* node_word, int L, int levelsup,
+                        int n, const uint8_t* desc, int32_t* word, double* weight, int32_t* node);
+int   orc_bow_vectors(int n, const int32_t* word, const double* weight, const int32_t* node,
+                      int32_t* bow_id, double* bow_val, int32_t* fv_node, int32_t* fv_start, int32_t* fv_idx, int* nfv);
+
 /* ORBmatcher::ComputeThreeMaxima, src/ORBmatcher.cc:2863-2905 (sizes[i] = histo[i].size()) */
 void  orc_three_maxima(const int* sizes, int L, int* ind1, int* ind2, int* ind3);
 

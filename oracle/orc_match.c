@@ -828,3 +828,72 @@ void orc_distinctive_descriptors(int npoints, const int32_t* start, const uint8_
         best_idx[p] = BestIdx; best_median[p] = BestMedian;
     }
 }
+
+/* ---- DBoW2 vocabulary-tree transform behind Frame::ComputeBoW (src/Frame.cc:905-922) ----
+ * TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup), Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1258:
+ * from the root, move to the child with the least FORB::distance (Hamming, FORB.cpp:81-100; first least wins) until a
+ * leaf; nid = the node passed at level L - levelsup (0 = root when that level is <= 0).  Tree as CSR: children of node
+ * i = child_idx[child_start[i] .. child_start[i+1]) in push_back order (loadFromTextFile :1338-1415). */
+void orc_bow_transform(const int32_t* child_start, const int32_t* child_idx, const uint8_t* node_desc,
+                       const double* node_weight, const int32_t* node_word, int L, int levelsup,
+                       int n, const uint8_t* desc, int32_t* word, double* weight, int32_t* node)
+{
+    const int nid_level = L - levelsup;
+    for (int f = 0; f < n; f++) {
+        const uint8_t* feat = desc + 32 * (size_t)f;
+        int nid = 0, final_id = 0, current_level = 0;
+        do {
+            ++current_level;
+            const int b = child_start[final_id], e = child_start[final_id + 1];
+            final_id = child_idx[b];
+            double best_d = orc_hamming256(feat, node_desc + 32 * (size_t)final_id);
+            for (int c = b + 1; c < e; c++) {
+                const int id = child_idx[c];
+                const double d = orc_hamming256(feat, node_desc + 32 * (size_t)id);
+                if (d < best_d) { best_d = d; final_id = id; }
+            }
+            if (current_level == nid_level) nid = final_id;
+        } while (child_start[final_id] != child_start[final_id + 1]);
+        word[f] = node_word[final_id]; weight[f] = node_weight[final_id]; node[f] = nid;
+    }
+}
+
+/* transform(features, BowVector&, FeatureVector&, levelsup) :1127-1196 for TF_IDF weighting and L1 scoring (ORBVocabulary):
+ * v.addWeight(id, w) in feature order for w > 0 (BowVector.cpp:34-46), fv.addFeature(nid, i), then v.normalize(L1)
+ * (BowVector.cpp:62-84, sum in ascending word id).  Flat outputs: (bow_id, bow_val) ascending, FeatureVector as CSR
+ * (fv_node ascending, indices in insertion order).  Returns the number of words; *nfv = number of feature-vector nodes. */
+typedef struct { int32_t key; int32_t i; double w; } bow_item;
+static int cmp_bow(const void* a, const void* b)
+{
+    const bow_item* x = (const bow_item*)a; const bow_item* y = (const bow_item*)b;
+    if (x->key != y->key) return x->key < y->key ? -1 : 1;
+    return x->i - y->i;
+}
+int orc_bow_vectors(int n, const int32_t* word, const double* weight, const int32_t* node,
+                    int32_t* bow_id, double* bow_val, int32_t* fv_node, int32_t* fv_start, int32_t* fv_idx, int* nfv)
+{
+    bow_item* it = (bow_item*)malloc(sizeof(bow_item) * (size_t)(n > 0 ? n : 1));
+    int m = 0;
+    for (int i = 0; i < n; i++) if (weight[i] > 0) { it[m].key = word[i]; it[m].i = i; it[m].w = weight[i]; m++; }
+    qsort(it, (size_t)m, sizeof(bow_item), cmp_bow);
+    int nw = 0;
+    for (int k = 0; k < m; k++) {
+        if (nw > 0 && bow_id[nw - 1] == it[k].key) bow_val[nw - 1] += it[k].w;    /* feature order inside a word */
+        else { bow_id[nw] = it[k].key; bow_val[nw] = it[k].w; nw++; }
+    }
+    double norm = 0.0;
+    for (int k = 0; k < nw; k++) norm += fabs(bow_val[k]);
+    if (norm > 0.0) for (int k = 0; k < nw; k++) bow_val[k] /= norm;
+    m = 0;
+    for (int i = 0; i < n; i++) if (weight[i] > 0) { it[m].key = node[i]; it[m].i = i; it[m].w = 0; m++; }
+    qsort(it, (size_t)m, sizeof(bow_item), cmp_bow);
+    int nn = 0;
+    for (int k = 0; k < m; k++) {
+        if (nn == 0 || fv_node[nn - 1] != it[k].key) { fv_node[nn] = it[k].key; fv_start[nn] = k; nn++; }
+        fv_idx[k] = it[k].i;
+    }
+    fv_start[nn] = m;
+    *nfv = nn;
+    free(it);
+    return nw;
+}

@@ -110,6 +110,10 @@ class Oracle:
                                                     C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.orc_distinctive_descriptors.restype = None
         L.orc_distinctive_descriptors.argtypes = [C.c_int] + [C.c_void_p] * 4
+        L.orc_bow_transform.restype = None
+        L.orc_bow_transform.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 4
+        L.orc_bow_vectors.restype = C.c_int
+        L.orc_bow_vectors.argtypes = [C.c_int] + [C.c_void_p] * 8 + [C.POINTER(C.c_int)]
         L.orc_is_in_frustum.restype = C.c_int
         L.orc_is_in_frustum.argtypes = [C.c_void_p] * 3 + [C.c_float] * 10 + [C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 7
         L.orc_search_by_projection_sim3.restype = C.c_int
@@ -518,3 +522,44 @@ def distinctive_descriptors(o: Oracle, start, desc):
     bi = np.empty(n, np.int32); bm = np.empty(n, np.int32)
     o.L.orc_distinctive_descriptors(n, start.ctypes.data, desc.ctypes.data, bi.ctypes.data, bm.ctypes.data)
     return bi, bm
+
+
+def vocabulary_csr(parent, is_leaf):
+    """Children lists / word ids as TemplatedVocabulary::loadFromTextFile builds them (TemplatedVocabulary.h:1338-1415):
+    node i+1 is row i of the file; children in file order; word ids number the leaves in file order."""
+    parent = np.asarray(parent, np.int64); is_leaf = np.asarray(is_leaf, bool)
+    nn = len(parent) + 1
+    ids = np.arange(1, nn)
+    order = np.argsort(parent, kind="stable")
+    child_idx = ids[order].astype(np.int32)
+    counts = np.bincount(parent, minlength=nn)
+    child_start = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    word = np.zeros(nn, np.int32)
+    word[1:][is_leaf] = np.arange(int(is_leaf.sum()), dtype=np.int32)
+    return child_start, child_idx, word
+
+
+def bow_transform(o: Oracle, voc: dict, desc, levelsup: int = 4):
+    """voc: parent, is_leaf, desc (nn-1 x 32), weight (nn-1), L.  Returns per feature (word, weight, node)."""
+    cs, ci, word = vocabulary_csr(voc["parent"], voc["is_leaf"])
+    nd = np.concatenate([np.zeros((1, 32), np.uint8), np.ascontiguousarray(voc["desc"], np.uint8)])
+    nw = np.concatenate([[0.0], np.asarray(voc["weight"], np.float64)])
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = len(desc)
+    w = np.empty(n, np.int32); wt = np.empty(n, np.float64); nid = np.empty(n, np.int32)
+    o.L.orc_bow_transform(cs.ctypes.data, ci.ctypes.data, nd.ctypes.data, nw.ctypes.data, word.ctypes.data, int(voc["L"]), levelsup,
+                          n, desc.ctypes.data, w.ctypes.data, wt.ctypes.data, nid.ctypes.data)
+    return w, wt, nid
+
+
+def compute_bow(o: Oracle, voc: dict, desc, levelsup: int = 4):
+    """Frame::ComputeBoW (src/Frame.cc:905-922): (bow_id, bow_val, fv_node, fv_start, fv_idx)."""
+    w, wt, nid = bow_transform(o, voc, desc, levelsup)
+    n = len(w)
+    bid = np.empty(n, np.int32); bval = np.empty(n, np.float64)
+    fn = np.empty(n, np.int32); fs = np.empty(n + 1, np.int32); fi = np.empty(n, np.int32)
+    nfv = C.c_int(0)
+    nw = o.L.orc_bow_vectors(n, w.ctypes.data, wt.ctypes.data, nid.ctypes.data, bid.ctypes.data, bval.ctypes.data,
+                             fn.ctypes.data, fs.ctypes.data, fi.ctypes.data, C.byref(nfv))
+    k = nfv.value
+    return bid[:nw].copy(), bval[:nw].copy(), fn[:k].copy(), fs[:k + 1].copy(), fi[:fs[k]].copy()

@@ -89,6 +89,11 @@ SYMBOLS = {
                                       [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p] + [C.c_int] * 4 + [C.c_void_p]),
     "orbx_search_by_bow": (C.c_int, [C.c_int, C.c_int] + ([C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_int]) * 2 +
                            [C.c_float, C.c_int, C.c_void_p]),
+    "orbx_vocabulary_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.POINTER(C.c_void_p)]),
+    "orbx_vocabulary_destroy": (None, [C.c_void_p]),
+    "orbx_bow_transform": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 3),
+    "orbx_compute_bow": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int),
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
     "orbx_distinctive_descriptors": (C.c_int, [C.c_int, C.c_int] + [C.c_void_p] * 4),
     "orbx_search_local_points": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p] + [C.c_float] * 4 + [C.c_void_p, C.c_int] +
                                  [C.c_void_p] * 3 + [C.c_float] * 6 + [C.c_int] + [C.c_void_p] * 6 + [C.c_float] * 3 + [C.c_int, C.c_float] +

@@ -7,7 +7,7 @@ import subprocess
 
 PKG = pathlib.Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
-SOURCES = ["capi.cu", "geometry.cu", "prepare.cu", "pyramid.cu", "fast.cu", "octree.cu", "describe.cu", "stereo.cu", "match.cu", "search.cu"]
+SOURCES = ["capi.cu", "geometry.cu", "prepare.cu", "pyramid.cu", "fast.cu", "octree.cu", "describe.cu", "stereo.cu", "match.cu", "search.cu", "bow.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared"]
 

@@ -6,6 +6,7 @@
 #include <thread>
 
 #include "ORBmatcher.h"
+#include "ORBVocabulary.h"
 
 static cv::Mat synth(int rows, int cols, unsigned seed, int shift)
 {

@@ -177,6 +177,52 @@ def SearchByBoW(mode: int, kf1: dict, kf2: dict, nnratio: float, check_orientati
     return nm, out
 
 
+class ORBVocabulary:
+    """ORBVocabulary (include/ORBVocabulary.h) on the device, built from the rows of its text file
+    (TemplatedVocabulary::loadFromTextFile, Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1415)."""
+
+    def __init__(self, k: int, L: int, parent, is_leaf, desc, weight, device: int = 0):
+        import ctypes as C
+        self.lib = binding.load()
+        parent = np.ascontiguousarray(parent, np.int32); is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); weight = np.ascontiguousarray(weight, np.float64)
+        h = C.c_void_p()
+        check(self.lib.orbx_vocabulary_create(device, k, L, len(parent), parent.ctypes.data, is_leaf.ctypes.data,
+                                              desc.ctypes.data, weight.ctypes.data, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.orbx_vocabulary_destroy(self.h); self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def transform(self, desc, levelsup: int = 4):
+        """Per feature (word id, weight, node id) — TemplatedVocabulary::transform, :1218-1258."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        w = np.empty(n, np.int32); wt = np.empty(n, np.float64); nid = np.empty(n, np.int32)
+        check(self.lib.orbx_bow_transform(self.h, desc.ctypes.data, n, levelsup, w.ctypes.data, wt.ctypes.data, nid.ctypes.data))
+        return w, wt, nid
+
+    def ComputeBoW(self, desc, levelsup: int = 4):
+        """Frame::ComputeBoW (src/Frame.cc:905-922): (bow_id, bow_val, fv_node, fv_start, fv_idx)."""
+        import ctypes as C
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        bid = np.empty(n, np.int32); bval = np.empty(n, np.float64)
+        fn = np.empty(n, np.int32); fs = np.empty(n + 1, np.int32); fi = np.empty(n, np.int32)
+        nb = C.c_int(0); nf = C.c_int(0)
+        check(self.lib.orbx_compute_bow(self.h, desc.ctypes.data, n, levelsup, bid.ctypes.data, bval.ctypes.data, C.byref(nb),
+                                        fn.ctypes.data, fs.ctypes.data, fi.ctypes.data, C.byref(nf)))
+        k = nf.value
+        return bid[:nb.value].copy(), bval[:nb.value].copy(), fn[:k].copy(), fs[:k + 1].copy(), fi[:fs[k]].copy()
+
+
 def ComputeDistinctiveDescriptors(start, desc, device: int = 0):
     """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:450-531), batched: CSR groups of descriptors.
     Returns (best_idx, best_median)."""

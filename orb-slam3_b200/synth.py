@@ -129,5 +129,30 @@ def synth_map_points(desc: np.ndarray, kps_xy: np.ndarray, octaves: np.ndarray, 
                 level=lvl, viewcos=viewcos, depth=depth, inview=inview)
 
 
+def synth_vocabulary(k: int = 10, L: int = 4, seed: int = 0, early_leaves: float = 0.02, stop_words: float = 0.03):
+    """A vocabulary tree shaped like ORBvoc (k-ary, depth L) in the row order of its text file
+    (TemplatedVocabulary.h:1338-1415): child descriptors = parent's with random bit flips (fewer deeper down), idf-like
+    weights, a few stopped words (weight 0) and a few leaves above depth L.  Returns dict(k, L, parent, is_leaf, desc, weight)."""
+    rng = np.random.default_rng(seed + 31337)
+    parent, leaf, desc, weight = [], [], [], []
+    frontier = [(0, np.zeros(256, np.uint8), 0)]          # (node id, descriptor bits, level)
+    frontier[0] = (0, rng.integers(0, 2, 256).astype(np.uint8), 0)
+    nid = 0
+    while frontier:
+        nxt = []
+        for pid, pbits, lvl in frontier:
+            for _ in range(k):
+                nid += 1
+                bits = pbits ^ (rng.random(256) < (0.5 if lvl == 0 else 0.25 / lvl)).astype(np.uint8)
+                is_leaf = lvl + 1 == L or (lvl + 1 >= 2 and rng.random() < early_leaves)
+                parent.append(pid); leaf.append(is_leaf); desc.append(np.packbits(bits))
+                weight.append(0.0 if (is_leaf and rng.random() < stop_words) else float(rng.uniform(0.5, 9.0)))
+                if not is_leaf:
+                    nxt.append((nid, bits, lvl + 1))
+        frontier = nxt
+    return dict(k=k, L=L, parent=np.array(parent, np.int32), is_leaf=np.array(leaf, np.uint8),
+                desc=np.stack(desc).astype(np.uint8), weight=np.array(weight, np.float64))
+
+
 def sha256(a: np.ndarray) -> str:
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()

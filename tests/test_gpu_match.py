@@ -124,3 +124,39 @@ def test_distinctive_descriptors(pkg, orc, oracle, seed, maxn):
     assert np.array_equal(bi_g, bi_o), f"{np.sum(bi_g != bi_o)} best rows differ"
     assert np.array_equal(bm_g, bm_o)
     assert bi_o[0] == -1 and bi_o[1] == 0
+
+
+@pytest.mark.parametrize("k,L,levelsup,seed", [(10, 4, 2, 1), (10, 4, 4, 2), (6, 5, 4, 3), (20, 3, 1, 4)])
+def test_bow_transform(pkg, orc, oracle, k, L, levelsup, seed):
+    """Frame::ComputeBoW: vocabulary-tree descent per feature (word, weight, node at L - levelsup) and the BowVector /
+    FeatureVector built from it, against the oracle's restatement of TemplatedVocabulary::transform."""
+    rng = np.random.default_rng(seed)
+    voc = pkg.synth.synth_vocabulary(k, L, seed)
+    V = pkg.ORBVocabulary(k, L, voc["parent"], voc["is_leaf"], voc["desc"], voc["weight"])
+    leaves = voc["desc"][voc["is_leaf"] != 0]
+    n = 1500
+    desc = leaves[rng.integers(0, len(leaves), n)].copy()
+    bits = np.unpackbits(desc, axis=1)
+    desc = np.packbits(bits ^ (rng.random(bits.shape) < rng.choice([0.0, 0.05, 0.3], (n, 1))).astype(np.uint8), axis=1)
+    desc[:5] = 0                                                    # equal distances to many children: first least wins
+    w_o, wt_o, nid_o = orc.bow_transform(oracle, voc, desc, levelsup)
+    w_g, wt_g, nid_g = V.transform(desc, levelsup)
+    assert np.array_equal(w_g, w_o) and np.array_equal(nid_g, nid_o) and np.array_equal(wt_g, wt_o)
+    assert (wt_o == 0).any() and len(np.unique(w_o)) > 200
+    got = V.ComputeBoW(desc, levelsup)
+    want = orc.compute_bow(oracle, voc, desc, levelsup)
+    for a, b, name in zip(got, want, ("bow_id", "bow_val", "fv_node", "fv_start", "fv_idx")):
+        assert np.array_equal(a, b), name
+    assert abs(got[1].sum() - 1.0) < 1e-12
+    V.close()
+
+
+def test_vocabulary_argument_errors(pkg):
+    import ctypes as C
+    lib = pkg.binding.load()
+    h = C.c_void_p()
+    parent = np.array([0, 0, 5], np.int32); leaf = np.array([1, 1, 1], np.uint8)
+    d = np.zeros((3, 32), np.uint8); w = np.ones(3, np.float64)
+    assert lib.orbx_vocabulary_create(0, 10, 2, 3, parent.ctypes.data, leaf.ctypes.data, d.ctypes.data, w.ctypes.data, C.byref(h)) == pkg.binding.ORBX_ERR_ARG
+    parent = np.array([0, 0, 1], np.int32)                          # node 1 has a child but is flagged as a leaf
+    assert lib.orbx_vocabulary_create(0, 10, 2, 3, parent.ctypes.data, leaf.ctypes.data, d.ctypes.data, w.ctypes.data, C.byref(h)) == pkg.binding.ORBX_ERR_ARG
