@@ -288,6 +288,13 @@ int orbx_search_by_bow(int device, int mode,
                        const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
                        float nnratio, int checkOrientation, int32_t* matches);
 
+/* void Frame::UndistortKeyPoints() src/Frame.cc:924-960: cv::undistortPoints(mat, mat, K, mDistCoef, cv::Mat(), mK)
+ * for the keypoint positions (every other KeyPoint field is copied).  distCoef: k1 k2 p1 p2 [k3] (ncoef = 4 or 5);
+ * distCoef[0] == 0 copies the keypoints (:926-931).  HOST arrays in and out; kps_un may alias kps.  The four image
+ * corners through the same call give Frame::ComputeImageBounds (:978-1009). */
+int orbx_undistort_keypoints(int device, const orbx_keypoint* kps, int n, float fx, float fy, float cx, float cy,
+                             const float* distCoef, int ncoef, orbx_keypoint* kps_un);
+
 /* void Tracking::SearchLocalPoints() src/Tracking.cc:3808-3893 in one call: bool
  * Frame::isInFrustum(MapPoint*, float viewingCosLimit) include/Frame.h, src/Frame.cc:603-711 (Nleft == -1) for every
  * local map point ON THE DEVICE - pose Rcw (row-major 3x3), tcw, Ow; pinhole fx, fy, cx, cy (src/CameraModels/

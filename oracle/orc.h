@@ -69,6 +69,9 @@ void  orc_remap_linear_u8(const uint8_t* src, int srows, int scols, size_t sstep
 /* cvtColor(COLOR_{RGB,BGR,RGBA,BGRA}2GRAY): channels 3 or 4, rgb != 0 when the first channel is R */
 void  orc_cvt_gray_u8(const uint8_t* src, int rows, int cols, size_t sstep, int channels, int rgb,
                       uint8_t* dst, size_t dstep);
+/* cv::undistortPoints(src, dst, K, distCoef, Mat(), K) (Frame::UndistortKeyPoints, src/Frame.cc:924-960); dist = k1 k2 p1 p2 k3 */
+void  orc_undistort_points(const float* xy_in, int n, float fx, float fy, float cx, float cy, const float* dist, float* xy_out);
+
 
 /* ---- ORBextractor (orc_extractor.c) ---- */
 orc_extractor* orc_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);

@@ -61,3 +61,35 @@ void orc_cvt_gray_u8(const uint8_t* src, int rows, int cols, size_t sstep, int c
         }
     }
 }
+
+/* cv::undistortPoints(src, dst, K, distCoef, cv::Mat(), K) as Frame::UndistortKeyPoints calls it (src/Frame.cc:924-960)
+ * and Frame::ComputeImageBounds (:978-1009): OpenCV's cvUndistortPointsInternal restated (double arithmetic, 5 fixed
+ * iterations = TermCriteria(MAX_ITER, 5, 0.01), R = identity, P = K), pinned against cv2 4.13
+ * (tests/test_oracle_vs_cv2.py).  dist: k1, k2, p1, p2, k3 (mDistCoef has 4 or 5 entries; pass k3 = 0 for 4). */
+void orc_undistort_points(const float* xy_in, int n, float fx, float fy, float cx, float cy, const float* dist, float* xy_out)
+{
+    const double dfx = fx, dfy = fy, dcx = cx, dcy = cy;
+    const double ifx = 1. / dfx, ify = 1. / dfy;
+    double k[12] = {0};
+    k[0] = dist[0]; k[1] = dist[1]; k[2] = dist[2]; k[3] = dist[3]; k[4] = dist[4];
+    for (int i = 0; i < n; i++) {
+        double x = xy_in[2 * i], y = xy_in[2 * i + 1];
+        const double u = x, v = y;
+        x = (x - dcx) * ifx;
+        y = (y - dcy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = (u - dcx) * ifx; y = (v - dcy) * ify; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        const double xx = dfx * x + 0.0 * y + dcx, yy = 0.0 * x + dfy * y + dcy;
+        const double ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+        xy_out[2 * i] = (float)(xx * ww);
+        xy_out[2 * i + 1] = (float)(yy * ww);
+    }
+}

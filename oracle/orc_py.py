@@ -56,6 +56,8 @@ class Oracle:
         L.orc_remap_linear_u8.restype = None
         L.orc_remap_linear_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p,
                                           C.c_size_t, C.c_void_p, C.c_int, C.c_int, C.c_size_t]
+        L.orc_undistort_points.restype = None
+        L.orc_undistort_points.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_cvt_gray_u8.restype = None
         L.orc_cvt_gray_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
         L.orc_levels.argtypes = [C.c_void_p]
@@ -181,6 +183,14 @@ class Oracle:
         self.L.orc_cvt_gray_u8(_ptr(src, C.c_void_p), src.shape[0], src.shape[1], src.strides[0], src.shape[2],
                                int(bool(rgb)), _ptr(dst, C.c_void_p), dst.strides[0])
         return dst
+
+    def undistort_points(self, xy: np.ndarray, fx, fy, cx, cy, dist) -> np.ndarray:
+        """cv2.undistortPoints(xy, K, dist, None, K) for n x 2 float32 points; dist = (k1, k2, p1, p2[, k3])."""
+        xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+        d = np.zeros(5, np.float32); d[:len(dist)] = dist
+        out = np.empty_like(xy)
+        self.L.orc_undistort_points(xy.ctypes.data, len(xy), fx, fy, cx, cy, d.ctypes.data, out.ctypes.data)
+        return out
 
     def prepare(self, src: np.ndarray, mapx=None, mapy=None, rgb: bool = False) -> np.ndarray:
         """The frame the extractor sees: remap (stereo_euroc.cc:168) then cvtColor (Tracking.cc:1264-1290)."""

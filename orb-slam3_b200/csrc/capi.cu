@@ -455,7 +455,8 @@ static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* img
     // for upload(k) and download(k-R) (outputs of the slot copied out), download(k) waits for kernels(k).
     int chunk = 128;
     if (const char* cs = getenv("ORBX_CHUNK")) { const int v = atoi(cs); if (v > 0) chunk = v; }
-    if (chunk > B) chunk = B;
+    if (chunk > B / 4 && B >= 4) chunk = B / 4;              // at least 4 chunk slots: upload / kernels / download of
+    if (chunk > B) chunk = B;                                //   neighbouring chunks overlap also for small batches of big frames
     const int R = B / chunk > 0 ? B / chunk : 1;             // chunk slots in the ring
     int ncs = ORBX_NCSTREAMS;
     if (const char* cs_ = getenv("ORBX_STREAMS")) { const int v = atoi(cs_); if (v >= 1 && v <= ORBX_NCSTREAMS) ncs = v; }

@@ -645,3 +645,77 @@ extern "C" int orbx_distinctive_descriptors(int device, int npoints, const int32
     if (best_median) memcpy(best_median, W.h + o_bm, 4 * (size_t)npoints);
     return ORBX_OK;
 }
+
+
+// ---- Frame::UndistortKeyPoints (src/Frame.cc:924-960): cv::undistortPoints(mat, mat, K, mDistCoef, cv::Mat(), mK) ----
+// OpenCV's cvUndistortPointsInternal restated (double arithmetic, 5 fixed iterations = TermCriteria(MAX_ITER, 5, 0.01),
+// R = identity, P = K; k1 k2 p1 p2 k3), non-contracted so that the float results equal cv2's bit for bit
+// (oracle/orc_prepare.c is pinned against cv2 4.13 on 2.4 M values).  One thread per keypoint.
+struct UndistArgs { int n; const orbx_keypoint* in; orbx_keypoint* out; double fx, fy, cx, cy, k[5]; };
+
+__global__ void __launch_bounds__(256)
+undistort_kernel(UndistArgs A)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= A.n) return;
+    orbx_keypoint kp = A.in[i];
+    const double ifx = __ddiv_rn(1.0, A.fx), ify = __ddiv_rn(1.0, A.fy);
+    const double u = (double)kp.x, v = (double)kp.y;
+    double x = __dmul_rn(__dsub_rn(u, A.cx), ifx), y = __dmul_rn(__dsub_rn(v, A.cy), ify);
+    const double x0 = x, y0 = y;
+    const double k0 = A.k[0], k1 = A.k[1], k2 = A.k[2], k3 = A.k[3], k4 = A.k[4];
+#pragma unroll 1
+    for (int j = 0; j < 5; j++) {
+        const double r2 = __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y));
+        // (1 + ((k[7]*r2 + k[6])*r2 + k[5])*r2) with k5..k7 = 0  ==  1 + 0 exactly
+        const double num = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(0.0, r2), 0.0), r2), 0.0), r2));
+        const double den = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(k4, r2), k1), r2), k0), r2));
+        const double icdist = __ddiv_rn(num, den);
+        if (icdist < 0) { x = __dmul_rn(__dsub_rn(u, A.cx), ifx); y = __dmul_rn(__dsub_rn(v, A.cy), ify); break; }
+        // deltaX = 2*k[2]*x*y + k[3]*(r2 + 2*x*x) + k[8]*r2 + k[9]*r2*r2   (k8..k11 = 0)
+        const double dX = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(__dmul_rn(__dmul_rn(2.0, k2), x), y),
+                                                        __dmul_rn(k3, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, x), x)))),
+                                              __dmul_rn(0.0, r2)), __dmul_rn(__dmul_rn(0.0, r2), r2));
+        const double dY = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(k2, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, y), y))),
+                                                        __dmul_rn(__dmul_rn(__dmul_rn(2.0, k3), x), y)),
+                                              __dmul_rn(0.0, r2)), __dmul_rn(__dmul_rn(0.0, r2), r2));
+        x = __dmul_rn(__dsub_rn(x0, dX), icdist);
+        y = __dmul_rn(__dsub_rn(y0, dY), icdist);
+    }
+    const double xx = __dadd_rn(__dadd_rn(__dmul_rn(A.fx, x), __dmul_rn(0.0, y)), A.cx);
+    const double yy = __dadd_rn(__dadd_rn(__dmul_rn(0.0, x), __dmul_rn(A.fy, y)), A.cy);
+    const double ww = __ddiv_rn(1.0, __dadd_rn(__dadd_rn(__dmul_rn(0.0, x), __dmul_rn(0.0, y)), 1.0));
+    kp.x = __double2float_rn(__dmul_rn(xx, ww));
+    kp.y = __double2float_rn(__dmul_rn(yy, ww));
+    A.out[i] = kp;
+}
+
+extern "C" int orbx_undistort_keypoints(int device, const orbx_keypoint* kps, int n, float fx, float fy, float cx, float cy,
+                                        const float* distCoef, int ncoef, orbx_keypoint* kps_un)
+{
+    if (n < 0 || (n > 0 && (!kps || !kps_un)) || !distCoef || (ncoef != 4 && ncoef != 5)) { orbx_set_error("bad undistort_keypoints arguments"); return ORBX_ERR_ARG; }
+    if (n == 0) return ORBX_OK;
+    if (distCoef[0] == 0.0f) {                                   // src/Frame.cc:926-931: mvKeysUn = mvKeys
+        if (kps_un != kps) memcpy(kps_un, kps, sizeof(orbx_keypoint) * (size_t)n);
+        return ORBX_OK;
+    }
+    OrbxWorkspace& W = orbx_workspace();
+    int rc = W.bind(device);
+    if (rc != ORBX_OK) return rc;
+    OrbxCarver c;
+    const size_t o_in = c.take(sizeof(orbx_keypoint) * (size_t)n), o_out = c.take(sizeof(orbx_keypoint) * (size_t)n);
+    rc = W.reserve(c.off, c.off);
+    if (rc != ORBX_OK) return rc;
+    memcpy(W.h + o_in, kps, sizeof(orbx_keypoint) * (size_t)n);
+    CUDA_TRYW(cudaMemcpyAsync(W.d + o_in, W.h + o_in, sizeof(orbx_keypoint) * (size_t)n, cudaMemcpyHostToDevice, W.s));
+    UndistArgs A;
+    A.n = n; A.in = (const orbx_keypoint*)(W.d + o_in); A.out = (orbx_keypoint*)(W.d + o_out);
+    A.fx = fx; A.fy = fy; A.cx = cx; A.cy = cy;
+    for (int i = 0; i < 5; i++) A.k[i] = i < ncoef ? (double)distCoef[i] : 0.0;
+    undistort_kernel<<<(n + 255) / 256, 256, 0, W.s>>>(A);
+    CUDA_TRYW(cudaGetLastError());
+    CUDA_TRYW(cudaMemcpyAsync(W.h + o_out, W.d + o_out, sizeof(orbx_keypoint) * (size_t)n, cudaMemcpyDeviceToHost, W.s));
+    CUDA_TRYW(cudaStreamSynchronize(W.s));
+    memcpy(kps_un, W.h + o_out, sizeof(orbx_keypoint) * (size_t)n);
+    return ORBX_OK;
+}

@@ -18,13 +18,13 @@
 // Latency-bound integer work (no roofline); reported as a share of the step.
 #include "orbx_internal.h"
 
-#define OCT_THREADS 256
 #define OCT_TABLES 23     // int arrays of node_cap entries in the per-CTA node scratch
 
 // exclusive scan of in[0..m) into out[0..m) (out may alias in); returns the total to all threads.
-__device__ int block_scan_excl(const int* in, int* out, int m, int* s_warp)
+template <int NT>
+__device__ int block_scan_excl_t(const int* in, int* out, int m, int* s_warp)
 {
-    const int T = OCT_THREADS;
+    const int T = NT;
     const int chunk = (m + T - 1) / T;
     const int b = min(m, (int)threadIdx.x * chunk), e = min(m, b + chunk);
     int sum = 0;
@@ -40,7 +40,7 @@ __device__ int block_scan_excl(const int* in, int* out, int m, int* s_warp)
     __syncthreads();
     int base = 0, total = 0;
 #pragma unroll
-    for (int w = 0; w < OCT_THREADS / 32; w++) {
+    for (int w = 0; w < NT / 32; w++) {
         const int v = s_warp[w];
         if (w < (int)(threadIdx.x >> 5)) base += v;
         total += v;
@@ -71,34 +71,40 @@ __device__ __forceinline__ int cand_rank(uint32_t key, const LevelGeom& L)
 // Candidate passes are chains of dependent lookups (global label -> shared tables -> shared atomic); four
 // candidates per thread are fetched before any of them is processed so that their global loads overlap.
 #define OCT_UNROLL 4
-template <class F>
-__device__ __forceinline__ void for_cands(const uint32_t* __restrict__ cand, const uint32_t* kcode, int n, F body)
+template <int NT, class F>
+__device__ __forceinline__ void for_cands_t(const uint32_t* __restrict__ cand, const uint32_t* kcode, int n, F body)
 {
-    for (int i0 = threadIdx.x; i0 < n; i0 += OCT_UNROLL * OCT_THREADS) {
+    for (int i0 = threadIdx.x; i0 < n; i0 += OCT_UNROLL * NT) {
         uint32_t key[OCT_UNROLL], code[OCT_UNROLL];
 #pragma unroll
         for (int u = 0; u < OCT_UNROLL; u++) {
-            const int i = i0 + u * OCT_THREADS;
+            const int i = i0 + u * NT;
             key[u] = i < n ? cand[i] : 0u;
             code[u] = (kcode && i < n) ? kcode[i] : 0u;
         }
 #pragma unroll
         for (int u = 0; u < OCT_UNROLL; u++) {
-            const int i = i0 + u * OCT_THREADS;
+            const int i = i0 + u * NT;
             if (i < n) body(i, key[u], (int)code[u]);
         }
     }
 }
 
-template <bool SMEM>
-__global__ void __launch_bounds__(OCT_THREADS)
-octree_kernel(FrameGeom G, DevBuffers D)
+// levels served by one launch (levels of similar table size share a launch: dynamic shared memory is per launch)
+struct OctLevels { int n; int lvl[ORBX_MAX_LEVELS]; };
+
+template <bool SMEM, int NT>
+__global__ void __launch_bounds__(NT)
+octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
 {
+#define OCT_THREADS NT
+#define block_scan_excl block_scan_excl_t<NT>
+#define for_cands for_cands_t<NT>
     extern __shared__ int dyn_smem[];
-    __shared__ int s_warp[OCT_THREADS / 32 + 1];
+    __shared__ int s_warp[NT / 32 + 1];
     __shared__ int s_val[4];
 
-    const int lvl = blockIdx.x, f = blockIdx.y;
+    const int lvl = LV.lvl[blockIdx.x], f = blockIdx.y;
     const LevelGeom& L = G.L[lvl];
     const int tid = threadIdx.x;
     const int cap = L.node_cap;
@@ -294,6 +300,9 @@ octree_kernel(FrameGeom G, DevBuffers D)
         if (nd < nout && (int)KEY_S(k) == best[nd] && cand_rank(k, L) == bestrank[nd]) sel[nd] = k;
     });
     if (tid == 0) D.selcnt[f * G.nlevels + lvl] = nout;
+#undef OCT_THREADS
+#undef block_scan_excl
+#undef for_cands
 }
 
 size_t octree_nodetab_ints(const FrameGeom& G)
@@ -303,16 +312,32 @@ size_t octree_nodetab_ints(const FrameGeom& G)
     return (size_t)mx * OCT_TABLES;
 }
 
+// Levels whose node tables fit 64 KB of shared memory share one launch of 256-thread CTAs (3 per SM).  Larger
+// levels (8000-feature frames: level 0 needs 160 KB) share a launch of 1024-thread CTAs with their tables in shared
+// memory up to 220 KB (one CTA per SM), and levels beyond that a launch with the tables in global memory: their
+// candidate passes (250 k candidates per frame at 4K) are what the step waits for.
+template <bool SMEM, int NT>
+static void launch_group(const FrameGeom& G, const DevBuffers& D, const OctLevels& LV, int nframes, size_t smem, cudaStream_t s)
+{
+    if (smem > 48 * 1024) cudaFuncSetAttribute(octree_kernel<SMEM, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    octree_kernel<SMEM, NT><<<dim3(LV.n, nframes), NT, smem, s>>>(G, D, LV);
+}
+
 int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
-    const size_t need = octree_nodetab_ints(G) * sizeof(int);
-    const dim3 grid(G.nlevels, nframes);
-    if (need <= 64 * 1024) {
-        if (need > 48 * 1024)
-            cudaFuncSetAttribute(octree_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
-        octree_kernel<true><<<grid, OCT_THREADS, need, s>>>(G, D);
-    } else {
-        octree_kernel<false><<<grid, OCT_THREADS, 0, s>>>(G, D);
+    OctLevels small, big, huge;
+    small.n = big.n = huge.n = 0;
+    size_t small_need = 0, big_need = 0;
+    for (int l = 0; l < G.nlevels; l++) {
+        const size_t need = (size_t)G.L[l].node_cap * OCT_TABLES * sizeof(int);
+        if (need <= 64 * 1024) { small.lvl[small.n++] = l; small_need = need > small_need ? need : small_need; }
+        else if (need <= 220 * 1024) { big.lvl[big.n++] = l; big_need = need > big_need ? need : big_need; }
+        else huge.lvl[huge.n++] = l;
     }
-    return 1;
+    int launches = 0;
+    // the long-running launches first: CTAs of the later launches fill the SMs they leave idle
+    if (huge.n) { launch_group<false, 1024>(G, D, huge, nframes, 0, s); launches++; }
+    if (big.n) { launch_group<true, 1024>(G, D, big, nframes, big_need, s); launches++; }
+    if (small.n) { launch_group<true, 256>(G, D, small, nframes, small_need, s); launches++; }
+    return launches;
 }

@@ -233,6 +233,15 @@ def ComputeDistinctiveDescriptors(start, desc, device: int = 0):
     return bi, bm
 
 
+def UndistortKeyPoints(kps, fx, fy, cx, cy, dist_coef, device: int = 0):
+    """Frame::UndistortKeyPoints (src/Frame.cc:924-960): mvKeysUn from mvKeys; dist_coef = (k1, k2, p1, p2[, k3])."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    d = np.ascontiguousarray(dist_coef, np.float32)
+    out = np.empty_like(kps)
+    check(binding.load().orbx_undistort_keypoints(device, kps.ctypes.data, len(kps), fx, fy, cx, cy, d.ctypes.data, len(d), out.ctypes.data))
+    return out
+
+
 def SearchLocalPoints(kps, desc, uRight, bounds, scale_factors, pose: dict, cam: dict, log_sf: float, pts: dict,
                       cos_limit: float = 0.5, th: float = 1.0, nnratio: float = 0.8, far: bool = False, th_far: float = 0.0,
                       assign=None, device: int = 0):

@@ -104,3 +104,22 @@ def test_error_conventions(pkg):
     with pytest.raises(pkg.OrbxError):
         pkg.ORBextractor(1000, nlevels=99)
     X.close()
+
+
+@pytest.mark.parametrize("name,rows,cols,nf", [("C5-4k", 2160, 3840, 8000), ("1080p", 1080, 1920, 4000), ("4k-12000", 2160, 3840, 12000)])
+def test_large_frames_match_oracle(pkg, orc, oracle, name, rows, cols, nf):
+    """C5-shaped frames: the level-0 quadtree tables exceed 64 KB of shared memory (own launch of 1024-thread CTAs,
+    tables in shared memory up to 220 KB - C5: 160 KB - and in global memory beyond: 12000 features)."""
+    img = pkg.synth.synth_frame(rows, cols, 17)
+    E = orc.Extractor(nf, oracle=oracle)
+    mono_o, kps_o, desc_o = E(img, (0, 0))
+    X = pkg.ORBextractor(nf)
+    mono_g, kps_g, desc_g = X(img, (0, 0))
+    for l in range(8):
+        sel_g, ang_g = X.level_keys(l, 1)
+        sel_o, ang_o = E.level_selected(l)
+        assert np.array_equal(sel_g, _cand_arr(sel_o)), f"quadtree selection level {l}"
+        assert np.array_equal(ang_g, ang_o)
+    assert mono_g == mono_o and len(kps_g) == len(kps_o) >= nf
+    assert np.array_equal(kps_g, kps_o) and np.array_equal(desc_g, desc_o)
+    X.close()

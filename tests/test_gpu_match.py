@@ -160,3 +160,24 @@ def test_vocabulary_argument_errors(pkg):
     assert lib.orbx_vocabulary_create(0, 10, 2, 3, parent.ctypes.data, leaf.ctypes.data, d.ctypes.data, w.ctypes.data, C.byref(h)) == pkg.binding.ORBX_ERR_ARG
     parent = np.array([0, 0, 1], np.int32)                          # node 1 has a child but is flagged as a leaf
     assert lib.orbx_vocabulary_create(0, 10, 2, 3, parent.ctypes.data, leaf.ctypes.data, d.ctypes.data, w.ctypes.data, C.byref(h)) == pkg.binding.ORBX_ERR_ARG
+
+
+@pytest.mark.parametrize("ncoef,seed", [(4, 1), (5, 2)])
+def test_undistort_keypoints(pkg, oracle, ncoef, seed):
+    """Frame::UndistortKeyPoints on the device: positions bit-exact against the oracle (itself pinned to cv2), every
+    other KeyPoint field untouched; k1 == 0 is the identity."""
+    rng = np.random.default_rng(seed)
+    n = 3000
+    kps = np.zeros(n, pkg.KP_DTYPE)
+    kps["x"] = rng.uniform(0, 752, n); kps["y"] = rng.uniform(0, 480, n)
+    kps["octave"] = rng.integers(0, 8, n); kps["angle"] = rng.uniform(0, 360, n); kps["response"] = rng.integers(7, 200, n); kps["size"] = 31; kps["class_id"] = -1
+    cam = (458.654, 457.296, 367.215, 248.375)                        # EuRoC cam0 (Examples/Monocular/EuRoC.yaml)
+    dist = np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.01][:ncoef], np.float32)
+    un = pkg.UndistortKeyPoints(kps, *cam, dist)
+    want = oracle.undistort_points(np.stack([kps["x"], kps["y"]], 1), *cam, dist)
+    assert np.array_equal(un["x"], want[:, 0]) and np.array_equal(un["y"], want[:, 1])
+    assert np.abs(un["x"] - kps["x"]).max() > 1.0
+    for f in ("size", "angle", "response", "octave", "class_id"):
+        assert np.array_equal(un[f], kps[f])
+    dist0 = dist.copy(); dist0[0] = 0
+    assert np.array_equal(pkg.UndistortKeyPoints(kps, *cam, dist0), kps)

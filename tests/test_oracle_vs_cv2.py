@@ -98,3 +98,23 @@ def test_prepare_primitives(oracle, channels):
             assert np.array_equal(oracle.gray(src, rgb), cv2.cvtColor(src, codes[(channels, rgb)]))
             ref = cv2.cvtColor(cv2.remap(src, m1, m2, cv2.INTER_LINEAR), codes[(channels, rgb)])
             assert np.array_equal(oracle.prepare(src, m1, m2, rgb), ref)
+
+
+def test_undistort_points(oracle):
+    """cv::undistortPoints(src, dst, K, dist, Mat(), K) as Frame::UndistortKeyPoints calls it (src/Frame.cc:938): the
+    restatement of cvUndistortPointsInternal equals the wheel bit for bit (4- and 5-coefficient models, incl. points
+    outside the image and the image corners of ComputeImageBounds)."""
+    rng = np.random.default_rng(0)
+    for case in range(4):
+        fx, fy = np.float32(rng.uniform(180, 900)), np.float32(rng.uniform(180, 900))
+        cx, cy = np.float32(rng.uniform(300, 400)), np.float32(rng.uniform(200, 280))
+        dist = np.array([rng.uniform(-0.35, 0.1), rng.uniform(-0.1, 0.15), rng.uniform(-2e-3, 2e-3), rng.uniform(-2e-3, 2e-3),
+                         rng.uniform(-0.05, 0.05)], np.float32)
+        if case % 2 == 0:
+            dist = dist[:4]
+        K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+        xy = np.stack([rng.uniform(-20, 772, 50000), rng.uniform(-20, 500, 50000)], 1).astype(np.float32)
+        xy[:4] = [[0, 0], [752, 0], [0, 480], [752, 480]]
+        ref = cv2.undistortPoints(xy.reshape(-1, 1, 2), K, dist, None, K).reshape(-1, 2)
+        got = oracle.undistort_points(xy, float(fx), float(fy), float(cx), float(cy), dist)
+        assert np.array_equal(ref.view(np.uint32), got.view(np.uint32))
