@@ -41,7 +41,7 @@ knn2_partial_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict
         __syncthreads();
 #pragma unroll 4
         for (int j = 0; j < m; j++) {
-            const int d = ham256(a0, a1, s_t[2 * j], s_t[2 * j + 1]);
+            const int d = ham256_csa(a0, a1, s_t[2 * j], s_t[2 * j + 1]);
             if (d < b0) { b1 = b0; i1 = i0; b0 = d; i0 = j0 + j; }     // ties keep the lower train index
             else if (d < b1) { b1 = d; i1 = j0 + j; }
         }

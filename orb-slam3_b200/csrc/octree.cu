@@ -281,24 +281,37 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     }
 
     // ---- best response per node; ties go to the first keypoint in the reference's vector order
-    // (:1005-1030), i.e. the smallest canonical rank (cell row, cell col, y, x) ----
-    int* best = aA;
+    // (:1005-1030), i.e. the smallest canonical rank (cell row, cell col, y, x).  The rank determines the
+    // keypoint (cand_rank is invertible), so the winner is rebuilt from (score, rank) by a node pass: ONE
+    // candidate pass when score and rank pack into 32 bits (<= 1024 cells: score << 24 | inverted rank),
+    // two otherwise ----
+    unsigned* best = reinterpret_cast<unsigned*>(aA);
     int* bestrank = aB;
-    for (int i = tid; i < size; i += OCT_THREADS) { best[i] = 0; bestrank[i] = 0x7FFFFFFF; }
-    __syncthreads();
-    for_cands(cand, kcode, n, [&](int, uint32_t k, int code) { atomicMax(&best[code >> 2], (int)KEY_S(k)); });
-    __syncthreads();
-    for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
-        const int nd = code >> 2;
-        if ((int)KEY_S(k) == best[nd]) atomicMin(&bestrank[nd], cand_rank(k, L));
-    });
-    __syncthreads();
     uint32_t* sel = D.sel + (long long)f * G.sel_per_frame + L.sel_base;
     const int nout = min(size, L.sel_cap);
-    for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
-        const int nd = code >> 2;
-        if (nd < nout && (int)KEY_S(k) == best[nd] && cand_rank(k, L) == bestrank[nd]) sel[nd] = k;
-    });
+    const bool packed = L.nCols * L.nRows <= 1024;
+    for (int i = tid; i < size; i += OCT_THREADS) { best[i] = 0u; bestrank[i] = 0x7FFFFFFF; }
+    __syncthreads();
+    if (packed) {
+        for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
+            atomicMax(&best[code >> 2], (KEY_S(k) << 24) | (0xFFFFFFu - (uint32_t)cand_rank(k, L)));
+        });
+    } else {
+        for_cands(cand, kcode, n, [&](int, uint32_t k, int code) { atomicMax(&best[code >> 2], KEY_S(k)); });
+        __syncthreads();
+        for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
+            const int nd = code >> 2;
+            if (KEY_S(k) == best[nd]) atomicMin(&bestrank[nd], cand_rank(k, L));
+        });
+    }
+    __syncthreads();
+    for (int nd = tid; nd < nout; nd += OCT_THREADS) {
+        const uint32_t score = packed ? best[nd] >> 24 : best[nd];
+        const int rank = packed ? (int)(0xFFFFFFu - (best[nd] & 0xFFFFFFu)) : bestrank[nd];
+        const int cell = rank >> 14, ci = cell / L.nCols, cj = cell - ci * L.nCols;
+        const int X3 = cj * L.wCell + (rank & 127), Y3 = ci * L.hCell + ((rank >> 7) & 127);
+        sel[nd] = MAKE_KEY(X3 + 3, Y3 + 3, score);
+    }
     if (tid == 0) D.selcnt[f * G.nlevels + lvl] = nout;
 #undef OCT_THREADS
 #undef block_scan_excl
