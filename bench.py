@@ -368,7 +368,8 @@ def main():
         pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
         try:
             matching = {"stereo": bm.stereo_leg(pkg, 256, 10, 2, local_rank), "knn2_1000": bm.knn_leg(pkg, 1000, 20, 3, local_rank),
-                        "knn2_8192": bm.knn_leg(pkg, 8192, 10, 2, local_rank), "search_by_projection_5k": bm.proj_leg(pkg, 20, 3, local_rank)}
+                        "knn2_8192": bm.knn_leg(pkg, 8192, 10, 2, local_rank), "search_by_projection_5k": bm.proj_leg(pkg, 20, 3, local_rank),
+                        "latency": bm.latency_leg(pkg, 100, 10, local_rank)}
             prepare = bm.prepare_leg(pkg, 256, 2, 4, 2, local_rank, pinned=pin)
         except Exception as ex:                                  # the headline line must still print
             matching = matching or {"error": repr(ex)}

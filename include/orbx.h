@@ -288,6 +288,24 @@ int orbx_search_by_bow(int device, int mode,
                        const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
                        float nnratio, int checkOrientation, int32_t* matches);
 
+/* int ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, const float th, const bool
+ * bFarPoints, const float thFarPoints) src/ORBmatcher.cc:45-239 for a two-camera rig (F.Nleft != -1; the TUM-VI
+ * stereo-fisheye configuration of BASELINE config C3).  Left keypoints mvKeys[0..nL), right keypoints mvKeysRight
+ * [0..nR); desc = F.mDescriptors ((nL + nR) x 32, left rows first); leftToRight / rightToLeft = mvLeftToRightMatch /
+ * mvRightToLeftMatch (-1: none); per map point the fields Frame::isInFrustum leaves for each camera
+ * (mbTrackInView[R], mTrackProjX/Y[R], mnTrackScaleLevel[R] (right: -1 allowed), mTrackViewCos[R]) and mTrackDepth.
+ * assign[nL + nR] in/out = F.mvpMapPoints as map-point rows (right keypoints at nL + i); >= 0 on entry: the keypoint
+ * holds a map point with observations.  Returns nmatches (left + right increments, :155-165, :222-231). */
+int orbx_search_by_projection_rig(int device,
+                                  const orbx_keypoint* kpsL, int nL, const orbx_keypoint* kpsR, int nR, const uint8_t* desc,
+                                  const int32_t* leftToRight, const int32_t* rightToLeft,
+                                  float minX, float maxX, float minY, float maxY,
+                                  const float* scaleFactors, int nlevels,
+                                  int nmp, const uint8_t* mp_desc, const float* mp_depth,
+                                  const uint8_t* inviewL, const float* projxL, const float* projyL, const int32_t* levelL, const float* viewcosL,
+                                  const uint8_t* inviewR, const float* projxR, const float* projyR, const int32_t* levelR, const float* viewcosR,
+                                  float th, float nnratio, int bFarPoints, float thFarPoints, int32_t* assign);
+
 /* void Frame::UndistortKeyPoints() src/Frame.cc:924-960: cv::undistortPoints(mat, mat, K, mDistCoef, cv::Mat(), mK)
  * for the keypoint positions (every other KeyPoint field is copied).  distCoef: k1 k2 p1 p2 [k3] (ncoef = 4 or 5);
  * distCoef[0] == 0 copies the keypoints (:926-931).  HOST arrays in and out; kps_un may alias kps.  The four image

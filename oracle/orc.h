@@ -145,6 +145,15 @@ void  orc_bow_transform(const int32_t* child_start, const int32_t* child_idx, co
 int   orc_bow_vectors(int n, const int32_t* word, const double* weight, const int32_t* node,
                       int32_t* bow_id, double* bow_val, int32_t* fv_node, int32_t* fv_start, int32_t* fv_idx, int* nfv);
 
+/* ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, ...) src/ORBmatcher.cc:45-239, branch Nleft != -1 (two-camera rig) */
+int   orc_search_by_projection_rig(const orc_grid* gL, const orc_keypoint* kpsL, int nL,
+                                   const orc_grid* gR, const orc_keypoint* kpsR, int nR,
+                                   const uint8_t* desc, const int32_t* l2r, const int32_t* r2l, const float* sf,
+                                   int nmp, const uint8_t* mp_desc, const float* mp_depth,
+                                   const uint8_t* inviewL, const float* projxL, const float* projyL, const int32_t* levelL, const float* viewcosL,
+                                   const uint8_t* inviewR, const float* projxR, const float* projyR, const int32_t* levelR, const float* viewcosR,
+                                   float th, float nnratio, int bFarPoints, float thFarPoints, int32_t* assign);
+
 /* ORBmatcher::ComputeThreeMaxima, src/ORBmatcher.cc:2863-2905 (sizes[i] = histo[i].size()) */
 void  orc_three_maxima(const int* sizes, int L, int* ind1, int* ind2, int* ind3);
 

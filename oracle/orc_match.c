@@ -897,3 +897,78 @@ int orc_bow_vectors(int n, const int32_t* word, const double* weight, const int3
     free(it);
     return nw;
 }
+
+/* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints), src/ORBmatcher.cc:45-239,
+ * branch F.Nleft != -1 (two-camera rig, e.g. the TUM-VI stereo-fisheye configuration): left keypoints mvKeys / mGrid,
+ * right keypoints mvKeysRight / mGridRight (right-local indices), descriptor rows and mvpMapPoints indexed left first
+ * then right (+ Nleft), mvLeftToRightMatch / mvRightToLeftMatch from ComputeStereoFishEyeMatches.  Per map point the
+ * left fields (mbTrackInView, mTrackProjX/Y, mnTrackScaleLevel, mTrackViewCos) and the right ones (...R).
+ * Quirks kept: a failed ratio test on the left side `continue`s past the right side (:148-149); the right radius is
+ * not multiplied by th (:173 has no bFactor); a stereo partner is overwritten without the "already held" test
+ * (:155-159, :222-226).  assign[nL + nR] in/out (>= 0 on entry: holds a map point with observations). */
+int orc_search_by_projection_rig(const orc_grid* gL, const orc_keypoint* kpsL, int nL,
+                                 const orc_grid* gR, const orc_keypoint* kpsR, int nR,
+                                 const uint8_t* desc, const int32_t* l2r, const int32_t* r2l, const float* sf,
+                                 int nmp, const uint8_t* mp_desc, const float* mp_depth,
+                                 const uint8_t* inviewL, const float* projxL, const float* projyL, const int32_t* levelL, const float* viewcosL,
+                                 const uint8_t* inviewR, const float* projxR, const float* projyR, const int32_t* levelR, const float* viewcosR,
+                                 float th, float nnratio, int bFarPoints, float thFarPoints, int32_t* assign)
+{
+    int nmatches = 0;
+    const int bFactor = th != 1.0;
+    const int cap = (nL > nR ? nL : nR) + 1;
+    int32_t* vIndices = (int32_t*)malloc(sizeof(int32_t) * (size_t)cap);
+    for (int iMP = 0; iMP < nmp; iMP++) {
+        if (!inviewL[iMP] && !inviewR[iMP]) continue;                         /* :54 */
+        if (bFarPoints && mp_depth[iMP] > thFarPoints) continue;              /* :57 */
+        const uint8_t* MPd = mp_desc + 32 * (size_t)iMP;
+        if (inviewL[iMP]) {                                                   /* :63-167 */
+            const int lvl = levelL[iMP];
+            float r = viewcosL[iMP] > 0.998 ? 2.5f : 4.0f;
+            if (bFactor) r *= th;
+            const int nc = orc_grid_query(gL, kpsL, projxL[iMP], projyL[iMP], r * sf[lvl], lvl - 1, lvl, vIndices, cap);
+            if (nc > 0) {
+                int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+                for (int k = 0; k < nc; k++) {
+                    const int idx = vIndices[k];
+                    if (assign[idx] >= 0) continue;
+                    const int dist = orc_hamming256(MPd, desc + 32 * (size_t)idx);
+                    if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = kpsL[idx].octave; bestIdx = idx; }
+                    else if (dist < bestDist2) { bestLevel2 = kpsL[idx].octave; bestDist2 = dist; }
+                }
+                if (bestDist <= TH_HIGH) {
+                    if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;       /* skips the right side too */
+                    if (bestLevel != bestLevel2 || bestDist <= nnratio * bestDist2) {
+                        assign[bestIdx] = iMP;
+                        if (l2r[bestIdx] != -1) { assign[l2r[bestIdx] + nL] = iMP; nmatches++; }    /* :155-159 */
+                        nmatches++;
+                    }
+                }
+            }
+        }
+        if (inviewR[iMP]) {                                                   /* :170-236 */
+            const int lvl = levelR[iMP];
+            if (lvl != -1) {
+                const float r = viewcosR[iMP] > 0.998 ? 2.5f : 4.0f;
+                const int nc = orc_grid_query(gR, kpsR, projxR[iMP], projyR[iMP], r * sf[lvl], lvl - 1, lvl, vIndices, cap);
+                if (nc == 0) continue;
+                int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+                for (int k = 0; k < nc; k++) {
+                    const int idx = vIndices[k];
+                    if (assign[idx + nL] >= 0) continue;
+                    const int dist = orc_hamming256(MPd, desc + 32 * (size_t)(idx + nL));
+                    if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = kpsR[idx].octave; bestIdx = idx; }
+                    else if (dist < bestDist2) { bestLevel2 = kpsR[idx].octave; bestDist2 = dist; }
+                }
+                if (bestDist <= TH_HIGH) {
+                    if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+                    if (r2l[bestIdx] != -1) { assign[r2l[bestIdx]] = iMP; nmatches++; }             /* :222-226 */
+                    assign[bestIdx + nL] = iMP;
+                    nmatches++;
+                }
+            }
+        }
+    }
+    free(vIndices);
+    return nmatches;
+}

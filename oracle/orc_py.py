@@ -116,6 +116,9 @@ class Oracle:
         L.orc_bow_transform.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 4
         L.orc_bow_vectors.restype = C.c_int
         L.orc_bow_vectors.argtypes = [C.c_int] + [C.c_void_p] * 8 + [C.POINTER(C.c_int)]
+        L.orc_search_by_projection_rig.restype = C.c_int
+        L.orc_search_by_projection_rig.argtypes = [C.c_void_p, C.c_void_p, C.c_int] * 2 + [C.c_void_p] * 4 + [C.c_int] + [C.c_void_p] * 12 + \
+            [C.c_float, C.c_float, C.c_int, C.c_float, C.c_void_p]
         L.orc_is_in_frustum.restype = C.c_int
         L.orc_is_in_frustum.argtypes = [C.c_void_p] * 3 + [C.c_float] * 10 + [C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 7
         L.orc_search_by_projection_sim3.restype = C.c_int
@@ -573,3 +576,22 @@ def compute_bow(o: Oracle, voc: dict, desc, levelsup: int = 4):
                              fn.ctypes.data, fs.ctypes.data, fi.ctypes.data, C.byref(nfv))
     k = nfv.value
     return bid[:nw].copy(), bval[:nw].copy(), fn[:k].copy(), fs[:k + 1].copy(), fi[:fs[k]].copy()
+
+
+def search_by_projection_rig(gridL: Grid, gridR: Grid, desc, l2r, r2l, scale_factors, mp: dict, th: float, nnratio: float,
+                             far: bool = False, th_far: float = 0.0, assign=None):
+    """SearchByProjection(Frame&, vector<MapPoint*>&, ...) for Nleft != -1 (src/ORBmatcher.cc:45-239).
+    mp: desc, depth, and per side inview / projx / projy / level / viewcos with suffix L or R."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    nL, nR = len(gridL.kps), len(gridR.kps)
+    assign = np.full(nL + nR, -1, np.int32) if assign is None else np.ascontiguousarray(assign, np.int32).copy()
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    l2r = np.ascontiguousarray(l2r, np.int32); r2l = np.ascontiguousarray(r2l, np.int32)
+    f = lambda k, t: np.ascontiguousarray(mp[k], t)
+    args = [f("desc", np.uint8), f("depth", np.float32)]
+    for s in ("L", "R"):
+        args += [f("inview" + s, np.uint8), f("projx" + s, np.float32), f("projy" + s, np.float32), f("level" + s, np.int32), f("viewcos" + s, np.float32)]
+    nm = gridL.L.orc_search_by_projection_rig(gridL.g, gridL.kps.ctypes.data, nL, gridR.g, gridR.kps.ctypes.data, nR, desc.ctypes.data,
+                                              l2r.ctypes.data, r2l.ctypes.data, sf.ctypes.data, len(args[1]), *[a.ctypes.data for a in args],
+                                              th, nnratio, int(far), th_far, assign.ctypes.data)
+    return nm, assign

@@ -11,4 +11,4 @@ from .extractor import ORBextractor, DescriptorDistance  # noqa: F401
 from .matcher import (ComputeStereoMatches, knn2_hamming, SearchByProjection, SearchByProjectionFrame,  # noqa: F401
                       SearchByProjectionKeyFrame,
                       SearchForInitialization, SearchForTriangulation, SearchByBoW, GetFeaturesInArea,
-                      SearchLocalPoints, UndistortKeyPoints, ComputeDistinctiveDescriptors, ORBVocabulary, SearchByProjectionSim3, Fuse, SearchBySim3, ComputeThreeMaxima)
+                      SearchLocalPoints, SearchByProjectionRig, UndistortKeyPoints, ComputeDistinctiveDescriptors, ORBVocabulary, SearchByProjectionSim3, Fuse, SearchBySim3, ComputeThreeMaxima)

@@ -95,6 +95,9 @@ SYMBOLS = {
     "orbx_compute_bow": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int),
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
     "orbx_distinctive_descriptors": (C.c_int, [C.c_int, C.c_int] + [C.c_void_p] * 4),
+    "orbx_search_by_projection_rig": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p] +
+                                      [C.c_float] * 4 + [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 12 +
+                                      [C.c_float, C.c_float, C.c_int, C.c_float, C.c_void_p]),
     "orbx_undistort_keypoints": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int, C.c_void_p]),
     "orbx_search_local_points": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p] + [C.c_float] * 4 + [C.c_void_p, C.c_int] +
                                  [C.c_void_p] * 3 + [C.c_float] * 6 + [C.c_int] + [C.c_void_p] * 6 + [C.c_float] * 3 + [C.c_int, C.c_float] +

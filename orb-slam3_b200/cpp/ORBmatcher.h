@@ -220,6 +220,37 @@ struct ORBmatcherGPU {
         return r;
     }
 
+    // The two-camera rig form (F.Nleft != -1) of SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints,
+    // thFarPoints), src/ORBmatcher.cc:45-239: the fields Frame::isInFrustum leaves per camera, SoA.
+    struct RigMapPointsSoA {
+        std::vector<uint8_t> desc;                                   // n x 32
+        std::vector<float> depth;                                    // mTrackDepth
+        std::vector<uint8_t> inView, inViewR;                        // mbTrackInView, mbTrackInViewR
+        std::vector<float> projX, projY, viewCos, projXR, projYR, viewCosR;
+        std::vector<int32_t> level, levelR;                          // mnTrackScaleLevel, mnTrackScaleLevelR (-1 allowed)
+    };
+    // mvKeys / mvKeysRight / mDescriptors (left rows first) / mvLeftToRightMatch / mvRightToLeftMatch of the frame;
+    // assign = F.mvpMapPoints as rows of `mp` (>= 0 on entry: holds a map point with observations), right keypoints at Nleft + i.
+    int SearchByProjection(const std::vector<cv::KeyPoint>& mvKeys, const std::vector<cv::KeyPoint>& mvKeysRight, const cv::Mat& mDescriptors,
+                           const std::vector<int>& mvLeftToRightMatch, const std::vector<int>& mvRightToLeftMatch,
+                           float mnMinX, float mnMaxX, float mnMinY, float mnMaxY, const std::vector<float>& mvScaleFactors,
+                           const RigMapPointsSoA& mp, float th, bool bFarPoints, float thFarPoints,
+                           std::vector<int32_t>& assign, int device = 0) const
+    {
+        static_assert(sizeof(int) == sizeof(int32_t), "int is 32 bits");
+        const int nL = (int)mvKeys.size(), nR = (int)mvKeysRight.size();
+        assign.resize((size_t)(nL + nR), -1);
+        const int r = orbx_search_by_projection_rig(
+            device, reinterpret_cast<const orbx_keypoint*>(mvKeys.data()), nL, reinterpret_cast<const orbx_keypoint*>(mvKeysRight.data()), nR,
+            mDescriptors.data, mvLeftToRightMatch.data(), mvRightToLeftMatch.data(), mnMinX, mnMaxX, mnMinY, mnMaxY,
+            mvScaleFactors.data(), (int)mvScaleFactors.size(), (int)mp.depth.size(), mp.desc.data(), mp.depth.data(),
+            mp.inView.data(), mp.projX.data(), mp.projY.data(), mp.level.data(), mp.viewCos.data(),
+            mp.inViewR.data(), mp.projXR.data(), mp.projYR.data(), mp.levelR.data(), mp.viewCosR.data(),
+            th, mfNNratio, bFarPoints ? 1 : 0, thFarPoints, assign.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchByProjection(rig): ") + orbx_last_error());
+        return r;
+    }
+
     // void MapPoint::ComputeDistinctiveDescriptors() src/MapPoint.cc:450-531 for a batch of map points: start is the CSR
     // offset of each point's observation descriptors in `desc` (rows of 32 bytes); bestIdx[p] = row within group p.
     static void ComputeDistinctiveDescriptors(const std::vector<int32_t>& start, const std::vector<uint8_t>& desc,

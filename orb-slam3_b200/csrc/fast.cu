@@ -20,6 +20,7 @@
 //      candidate's canonical rank (cell row, cell col, y, x), i.e. the reference's vector order.
 // Integer work on the ALU pipe (~55 lane-ops per pixel); HBM traffic = one read of the level.
 #include "orbx_internal.h"
+#include <cstdlib>
 #include <vector>
 
 #define FAST_WARPS 4
@@ -361,10 +362,14 @@ int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out, int* warp_w
 int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
     cudaMemsetAsync(D.candcnt, 0, sizeof(int) * (size_t)nframes * G.nlevels, s);
-    if (G.fast_smem > 48 * 1024)
-        cudaFuncSetAttribute(fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G.fast_smem);
+    int smem = G.fast_smem;
+    // experiment hook: ORBX_FAST_SMEM pads the CTA's shared memory, i.e. caps the FAST CTAs per SM
+    static const int pad = [] { const char* e = getenv("ORBX_FAST_SMEM"); return e ? atoi(e) : 0; }();
+    if (pad > smem) smem = pad;
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     const dim3 grid((G.bands_per_frame + FAST_WARPS - 1) / FAST_WARPS, nframes);
-    fast_band_kernel<<<grid, FAST_THREADS, G.fast_smem, s>>>(G, D);
+    fast_band_kernel<<<grid, FAST_THREADS, smem, s>>>(G, D);
     return 1;
 }
 

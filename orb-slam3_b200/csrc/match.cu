@@ -189,6 +189,7 @@ proj_candidates_kernel(ProjArgs A)
     int cnt = 0;
     bool live = A.inview[iMP] != 0;                                       // :54
     if (A.bFar && A.depth[iMP] > A.thFar) live = false;                    // :57
+    if (live && A.level[iMP] < 0) live = false;                            // mnTrackScaleLevelR == -1, :172
     if (live) {
         const int lvl = A.level[iMP];
         float r = ((double)A.viewcos[iMP] > 0.998) ? 2.5f : 4.0f;          // RadiusByViewingCos :242-249
@@ -718,4 +719,185 @@ extern "C" int orbx_undistort_keypoints(int device, const orbx_keypoint* kps, in
     CUDA_TRYW(cudaStreamSynchronize(W.s));
     memcpy(kps_un, W.h + o_out, sizeof(orbx_keypoint) * (size_t)n);
     return ORBX_OK;
+}
+
+
+// ---- SearchByProjection(Frame&, vector<MapPoint*>&, ...) for a two-camera rig (F.Nleft != -1), src/ORBmatcher.cc:45-239 ----
+// Candidate lists per side by proj_candidates_kernel (left: mvKeys / mGrid, right: mvKeysRight / mGridRight with
+// right-local indices; the right radius is not scaled by th, :173).  rig_resolve_kernel replays the sequential
+// bookkeeping as the same fixpoint as proj_resolve_kernel over rows (2*iMP: left side, 2*iMP+1: right side): a row
+// skips keypoints written by an earlier row; an accepted row writes its keypoint AND overwrites the keypoint's stereo
+// partner (mvLeftToRightMatch / mvRightToLeftMatch, :155-159, :222-226); a failed left ratio test skips the right side
+// (:148-149).  A keypoint ends up with its LAST writer.
+struct RigArgs {
+    int nL, nR, nmp;
+    const int* candL; const int* cntL; const int* candR; const int* cntR;
+    const int* l2r; const int* r2l;
+    float nnratio;
+    int* assign;                 // nL + nR, in/out
+    int* claim0; int* claim1;    // first writer row per keypoint (iteration t-1 / t)
+    int* last;                   // last writer row per keypoint
+    int* choice;                 // 2 per map point
+    int* result;
+};
+
+__device__ __forceinline__ int rig_pick(const int* c, int nc, const int* prev, int off, int row, int skipIdx, float nnratio, bool* ratioFail)
+{
+    int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+    for (int k = 0; k < nc; k++) {
+        const int idx = c[2 * k] & 0xFFFFFF, oct = c[2 * k] >> 24, dist = c[2 * k + 1];
+        if (prev[idx + off] < row || idx == skipIdx) continue;             // already holds a map point
+        if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = idx; }
+        else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
+    }
+    *ratioFail = false;
+    if (bestDist <= TH_HIGH) {
+        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) { *ratioFail = true; return -1; }
+        return bestIdx;
+    }
+    return -1;
+}
+
+__global__ void __launch_bounds__(1024)
+rig_resolve_kernel(RigArgs A)
+{
+    __shared__ int s_changed, s_matches;
+    const int tid = threadIdx.x;
+    const int n = A.nL + A.nR;
+    int* prev = A.claim0; int* next = A.claim1;
+    for (int i = tid; i < n; i += 1024) prev[i] = A.assign[i] >= 0 ? -1 : INT_MAX;
+    for (int i = tid; i < 2 * A.nmp; i += 1024) A.choice[i] = -2;
+    __syncthreads();
+    for (int iter = 0; iter <= A.nmp + 1; iter++) {
+        if (tid == 0) { s_changed = 0; s_matches = 0; }
+        for (int i = tid; i < n; i += 1024) { next[i] = A.assign[i] >= 0 ? -1 : INT_MAX; A.last[i] = -1; }
+        __syncthreads();
+        int changed = 0, matches = 0;
+        for (int i = tid; i < A.nmp; i += 1024) {
+            bool fail = false;
+            const int chL = rig_pick(A.candL + (long long)i * PROJ_KMAX * 2, A.cntL[i], prev, 0, 2 * i, -1, A.nnratio, &fail);
+            int partner = -1;
+            if (chL >= 0) {
+                atomicMin(&next[chL], 2 * i); atomicMax(&A.last[chL], 2 * i);
+                partner = A.l2r[chL];
+                if (partner != -1) { atomicMin(&next[partner + A.nL], 2 * i); atomicMax(&A.last[partner + A.nL], 2 * i); matches++; }
+                matches++;
+            }
+            int chR = -1;
+            if (!fail) {                                                   // a failed left ratio test `continue`s past the right side
+                bool failR = false;
+                chR = rig_pick(A.candR + (long long)i * PROJ_KMAX * 2, A.cntR[i], prev, A.nL, 2 * i + 1, partner, A.nnratio, &failR);
+                if (chR >= 0) {
+                    const int p = A.r2l[chR];
+                    if (p != -1) { atomicMin(&next[p], 2 * i + 1); atomicMax(&A.last[p], 2 * i + 1); matches++; }
+                    atomicMin(&next[chR + A.nL], 2 * i + 1); atomicMax(&A.last[chR + A.nL], 2 * i + 1);
+                    matches++;
+                }
+            }
+            if (chL != A.choice[2 * i] || chR != A.choice[2 * i + 1]) { changed = 1; A.choice[2 * i] = chL; A.choice[2 * i + 1] = chR; }
+        }
+        if (changed) atomicOr(&s_changed, 1);
+        if (matches) atomicAdd(&s_matches, matches);
+        __syncthreads();
+        int* t = prev; prev = next; next = t;
+        const int ch = s_changed;
+        __syncthreads();
+        if (!ch) break;
+    }
+    for (int i = tid; i < n; i += 1024) if (A.last[i] >= 0) A.assign[i] = A.last[i] >> 1;
+    if (tid == 0) A.result[0] = s_matches;
+}
+
+extern "C" int orbx_search_by_projection_rig(int device,
+                                             const orbx_keypoint* kpsL, int nL, const orbx_keypoint* kpsR, int nR, const uint8_t* desc,
+                                             const int32_t* leftToRight, const int32_t* rightToLeft,
+                                             float minX, float maxX, float minY, float maxY,
+                                             const float* scaleFactors, int nlevels,
+                                             int nmp, const uint8_t* mp_desc, const float* mp_depth,
+                                             const uint8_t* inviewL, const float* projxL, const float* projyL, const int32_t* levelL, const float* viewcosL,
+                                             const uint8_t* inviewR, const float* projxR, const float* projyR, const int32_t* levelR, const float* viewcosR,
+                                             float th, float nnratio, int bFarPoints, float thFarPoints, int32_t* assign)
+{
+    if (nL < 0 || nR < 0 || nmp < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors || !(maxX > minX) || !(maxY > minY) ||
+        (nL > 0 && (!kpsL || !leftToRight)) || (nR > 0 && (!kpsR || !rightToLeft)) || (nL + nR > 0 && (!desc || !assign)) ||
+        (nmp > 0 && (!mp_desc || !inviewL || !projxL || !projyL || !levelL || !viewcosL || !inviewR || !projxR || !projyR || !levelR || !viewcosR)) ||
+        (bFarPoints && !mp_depth)) {
+        orbx_set_error("bad search_by_projection_rig arguments"); return ORBX_ERR_ARG;
+    }
+    if (nL + nR >= (1 << 24)) { orbx_set_error("too many keypoints"); return ORBX_ERR_ARG; }
+    if (nL + nR == 0 || nmp == 0) return 0;
+    for (int i = 0; i < nmp; i++) {
+        if (inviewL[i] && (levelL[i] < 0 || levelL[i] >= nlevels)) { orbx_set_error("map point %d: level %d out of range", i, levelL[i]); return ORBX_ERR_ARG; }
+        if (inviewR[i] && (levelR[i] < -1 || levelR[i] >= nlevels)) { orbx_set_error("map point %d: right level %d out of range", i, levelR[i]); return ORBX_ERR_ARG; }
+    }
+    for (int i = 0; i < nL; i++) if (leftToRight[i] < -1 || leftToRight[i] >= nR) { orbx_set_error("mvLeftToRightMatch[%d] out of range", i); return ORBX_ERR_ARG; }
+    for (int i = 0; i < nR; i++) if (rightToLeft[i] < -1 || rightToLeft[i] >= nL) { orbx_set_error("mvRightToLeftMatch[%d] out of range", i); return ORBX_ERR_ARG; }
+    OrbxWorkspace& W = orbx_workspace();
+    int rc = W.bind(device);
+    if (rc != ORBX_OK) return rc;
+    const size_t NL = (size_t)nL, NR = (size_t)nR, N = NL + NR, M = (size_t)nmp;
+    OrbxCarver c;
+    const size_t o_kl = c.take(NL * sizeof(orbx_keypoint)), o_kr = c.take(NR * sizeof(orbx_keypoint)), o_desc = c.take(N * 32);
+    const size_t o_l2r = c.take(NL * 4), o_r2l = c.take(NR * 4);
+    const size_t o_md = c.take(M * 32), o_dp = c.take(mp_depth ? M * 4 : 0);
+    size_t o_iv[2], o_px[2], o_py[2], o_lv[2], o_vc[2];
+    for (int sd = 0; sd < 2; sd++) { o_iv[sd] = c.take(M); o_px[sd] = c.take(M * 4); o_py[sd] = c.take(M * 4); o_lv[sd] = c.take(M * 4); o_vc[sd] = c.take(M * 4); }
+    const size_t o_assign = c.take(N * 4), o_result = c.take(8);
+    const size_t in_bytes = c.off;
+    size_t o_cs[2], o_ci[2], o_cc[2], o_cl[2];
+    for (int sd = 0; sd < 2; sd++) { o_cs[sd] = c.take(4 * (size_t)(GRID_CELLS + 1)); o_ci[sd] = c.take((sd ? NR : NL) * 4 + 4); o_cc[sd] = c.take(M * 4); o_cl[sd] = c.take(8 * M * PROJ_KMAX); }
+    const size_t o_c0 = c.take(N * 4), o_c1 = c.take(N * 4), o_last = c.take(N * 4), o_ch = c.take(M * 8);
+    rc = W.reserve(c.off, in_bytes);
+    if (rc != ORBX_OK) return rc;
+    char* h = W.h; char* d = W.d;
+    if (nL) { memcpy(h + o_kl, kpsL, NL * sizeof(orbx_keypoint)); memcpy(h + o_l2r, leftToRight, NL * 4); }
+    if (nR) { memcpy(h + o_kr, kpsR, NR * sizeof(orbx_keypoint)); memcpy(h + o_r2l, rightToLeft, NR * 4); }
+    memcpy(h + o_desc, desc, N * 32); memcpy(h + o_md, mp_desc, M * 32);
+    if (mp_depth) memcpy(h + o_dp, mp_depth, M * 4);
+    const uint8_t* iv[2] = {inviewL, inviewR}; const float* px[2] = {projxL, projxR}; const float* py[2] = {projyL, projyR};
+    const int32_t* lv[2] = {levelL, levelR}; const float* vc[2] = {viewcosL, viewcosR};
+    for (int sd = 0; sd < 2; sd++) {
+        memcpy(h + o_iv[sd], iv[sd], M); memcpy(h + o_px[sd], px[sd], M * 4); memcpy(h + o_py[sd], py[sd], M * 4);
+        memcpy(h + o_lv[sd], lv[sd], M * 4); memcpy(h + o_vc[sd], vc[sd], M * 4);
+    }
+    memcpy(h + o_assign, assign, N * 4); memset(h + o_result, 0, 8);
+    CUDA_TRYW(cudaMemcpyAsync(d, h, in_bytes, cudaMemcpyHostToDevice, W.s));
+    for (int sd = 0; sd < 2; sd++) {
+        const int n = sd ? nR : nL;
+        ProjArgs A;
+        memset(&A, 0, sizeof(A));
+        A.kps = (const orbx_keypoint*)(d + (sd ? o_kr : o_kl)); A.desc = (const uint4*)(d + o_desc + (sd ? NL * 32 : 0));
+        A.uRight = nullptr;                                                   // the stereo gate is for Nleft == -1 only, :105
+        A.mp_desc = (const uint4*)(d + o_md); A.projx = (const float*)(d + o_px[sd]); A.projy = (const float*)(d + o_py[sd]);
+        A.level = (const int*)(d + o_lv[sd]); A.viewcos = (const float*)(d + o_vc[sd]);
+        A.depth = mp_depth ? (const float*)(d + o_dp) : nullptr; A.inview = (const uint8_t*)(d + o_iv[sd]);
+        A.result = (int*)(d + o_result);
+        A.cell_start = (int*)(d + o_cs[sd]); A.cell_idx = (int*)(d + o_ci[sd]); A.cand_cnt = (int*)(d + o_cc[sd]); A.cand = (int*)(d + o_cl[sd]);
+        A.n = n; A.nmp = nmp;
+        A.minX = minX; A.minY = minY;
+        A.winv = (float)GRID_COLS / (float)(maxX - minX);
+        A.hinv = (float)GRID_ROWS / (float)(maxY - minY);
+        for (int l = 0; l < nlevels; l++) A.sf[l] = scaleFactors[l];
+        A.th = sd ? 1.0f : th;                                                // :173: no bFactor on the right side
+        A.nnratio = nnratio; A.bFar = bFarPoints; A.thFar = thFarPoints;
+        GridArgs g;
+        g.kps = A.kps; g.n = n; g.minX = A.minX; g.minY = A.minY; g.winv = A.winv; g.hinv = A.hinv;
+        g.cell_start = A.cell_start; g.cell_idx = A.cell_idx;
+        orbx_launch_grid_build(g, W.s);
+        proj_candidates_kernel<<<(nmp + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32, 0, W.s>>>(A);
+    }
+    RigArgs R;
+    R.nL = nL; R.nR = nR; R.nmp = nmp;
+    R.candL = (const int*)(d + o_cl[0]); R.cntL = (const int*)(d + o_cc[0]); R.candR = (const int*)(d + o_cl[1]); R.cntR = (const int*)(d + o_cc[1]);
+    R.l2r = (const int*)(d + o_l2r); R.r2l = (const int*)(d + o_r2l); R.nnratio = nnratio;
+    R.assign = (int*)(d + o_assign); R.claim0 = (int*)(d + o_c0); R.claim1 = (int*)(d + o_c1); R.last = (int*)(d + o_last);
+    R.choice = (int*)(d + o_ch); R.result = (int*)(d + o_result);
+    rig_resolve_kernel<<<1, 1024, 0, W.s>>>(R);
+    CUDA_TRYW(cudaGetLastError());
+    CUDA_TRYW(cudaMemcpyAsync(h + o_assign, d + o_assign, in_bytes - o_assign, cudaMemcpyDeviceToHost, W.s));
+    CUDA_TRYW(cudaStreamSynchronize(W.s));
+    memcpy(assign, h + o_assign, N * 4);
+    const int* result = (const int*)(h + o_result);
+    if (result[1]) { orbx_set_error("a map point has more than %d candidates", PROJ_KMAX); return ORBX_ERR_CAPACITY; }
+    return result[0];
 }

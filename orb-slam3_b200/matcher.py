@@ -233,6 +233,27 @@ def ComputeDistinctiveDescriptors(start, desc, device: int = 0):
     return bi, bm
 
 
+def SearchByProjectionRig(kpsL, kpsR, desc, l2r, r2l, bounds, scale_factors, mp: dict, th: float, nnratio: float,
+                          far: bool = False, th_far: float = 0.0, assign=None, device: int = 0):
+    """ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, ...) for Nleft != -1 (src/ORBmatcher.cc:45-239).
+    mp: desc, depth and per side inview / projx / projy / level / viewcos with suffix L or R.  Returns (nmatches, assign)."""
+    kpsL = np.ascontiguousarray(kpsL, KP_DTYPE); kpsR = np.ascontiguousarray(kpsR, KP_DTYPE)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    nL, nR = len(kpsL), len(kpsR)
+    assign = np.full(nL + nR, -1, np.int32) if assign is None else np.ascontiguousarray(assign, np.int32).copy()
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    l2r = np.ascontiguousarray(l2r, np.int32); r2l = np.ascontiguousarray(r2l, np.int32)
+    f = lambda k, t: np.ascontiguousarray(mp[k], t)
+    args = [f("desc", np.uint8), f("depth", np.float32)]
+    for s in ("L", "R"):
+        args += [f("inview" + s, np.uint8), f("projx" + s, np.float32), f("projy" + s, np.float32), f("level" + s, np.int32), f("viewcos" + s, np.float32)]
+    nm = check(binding.load().orbx_search_by_projection_rig(
+        device, kpsL.ctypes.data, nL, kpsR.ctypes.data, nR, desc.ctypes.data, l2r.ctypes.data, r2l.ctypes.data,
+        bounds[0], bounds[1], bounds[2], bounds[3], sf.ctypes.data, len(sf), len(args[1]), *[a.ctypes.data for a in args],
+        th, nnratio, int(far), th_far, assign.ctypes.data))
+    return nm, assign
+
+
 def UndistortKeyPoints(kps, fx, fy, cx, cy, dist_coef, device: int = 0):
     """Frame::UndistortKeyPoints (src/Frame.cc:924-960): mvKeysUn from mvKeys; dist_coef = (k1, k2, p1, p2[, k3])."""
     kps = np.ascontiguousarray(kps, KP_DTYPE)

@@ -417,3 +417,43 @@ def test_predict_scale_boundaries(pkg, orc, oracle):
     assert f_o["inview"].sum() > m // 2
     assert np.array_equal(f_g["level"], f_o["level"]) and np.array_equal(f_g["inview"], f_o["inview"])
     assert np.array_equal(f_g["depth"], f_o["depth"])
+
+
+@pytest.mark.parametrize("th,far,seed,preheld", [(1.0, False, 101, 0.0), (3.0, False, 102, 0.1), (5.0, True, 103, 0.1), (15.0, False, 104, 0.3)])
+def test_search_by_projection_rig(pkg, orc, oracle, th, far, seed, preheld):
+    """C3: SearchByProjection(Frame&, vector<MapPoint*>&, ...) on a two-camera rig (Nleft != -1): left and right keypoint
+    sets, stereo partners overwritten, a failed left ratio test skipping the right side, right radius without th."""
+    rng = np.random.default_rng(seed)
+    rows = cols = 512
+    nL, nR, nmp = 1000, 950, 5000
+    kL, dL, pool, _ = _frame(pkg, rng, nL, rows, cols)
+    kR, dR, _, _ = _frame(pkg, rng, nR, rows, cols, pool=pool)
+    desc = np.concatenate([dL, dR])
+    # stereo partners (ComputeStereoFishEyeMatches): a random partial matching
+    l2r = np.full(nL, -1, np.int32); r2l = np.full(nR, -1, np.int32)
+    pairs = min(nL, nR) // 3
+    li = rng.choice(nL, pairs, replace=False); ri = rng.choice(nR, pairs, replace=False)
+    l2r[li] = ri; r2l[ri] = li
+    srcL = rng.integers(0, nL, nmp); srcR = rng.integers(0, nR, nmp)
+    mp = dict(desc=_flip(rng, np.where((rng.random(nmp) < 0.5)[:, None], dL[srcL], dR[srcR]), 0, 30),
+              depth=rng.uniform(0.5, 30.0, nmp).astype(np.float32))
+    for s, k, src in (("L", kL, srcL), ("R", kR, srcR)):
+        near = rng.random(nmp) < 0.7
+        mp["projx" + s] = np.where(near, k["x"][src] + rng.normal(0, 2, nmp), rng.uniform(0, cols, nmp)).astype(np.float32)
+        mp["projy" + s] = np.where(near, k["y"][src] + rng.normal(0, 2, nmp), rng.uniform(0, rows, nmp)).astype(np.float32)
+        mp["level" + s] = np.clip(k["octave"][src] + rng.integers(0, 2, nmp), 0, 7).astype(np.int32)
+        mp["viewcos" + s] = np.where(rng.random(nmp) < 0.5, 0.9, 0.999).astype(np.float32)
+        mp["inview" + s] = (rng.random(nmp) < 0.6).astype(np.uint8)
+    mp["levelR"][rng.random(nmp) < 0.05] = -1                                     # mnTrackScaleLevelR == -1, :172
+    pre = np.where(rng.random(nL + nR) < preheld, 3, -1).astype(np.int32)
+    bounds = (0.0, float(cols), 0.0, float(rows))
+    gL, gR = orc.Grid(oracle, kL, *bounds), orc.Grid(oracle, kR, *bounds)
+    nm_o, as_o = orc.search_by_projection_rig(gL, gR, desc, l2r, r2l, SF, mp, th, 0.8, far, 12.0, pre)
+    nm_g, as_g = pkg.SearchByProjectionRig(kL, kR, desc, l2r, r2l, bounds, SF, mp, th, 0.8, far, 12.0, pre)
+    assert nm_o > 300, nm_o
+    assert nm_g == nm_o
+    assert np.array_equal(as_g, as_o), f"{np.sum(as_g != as_o)} assignments differ"
+    # a pre-held keypoint can only change through a partner overwrite
+    changed = (pre >= 0) & (as_o != pre)
+    partners = np.concatenate([r2l >= 0, l2r >= 0]) if False else np.concatenate([l2r >= 0, r2l >= 0])
+    assert not np.any(changed & ~partners)

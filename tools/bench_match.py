@@ -138,6 +138,30 @@ def prepare_leg(pkg, B=256, passes=2, reps=5, warm=2, device=0, pinned=None):
             "e2e_frames_per_s_plain_extract": BE / (ms_plain * 1e-3)}
 
 
+def latency_leg(pkg, reps=200, warm=20, device=0):
+    """What a SLAM front-end sees per frame: ONE 752x480 frame through operator() (host image in, host keypoints +
+    descriptors out), and one stereo pair (two extractors on two host threads, src/Frame.cc:132-137, then
+    ComputeStereoMatches with mvuRight / mvDepth back on the host)."""
+    import threading
+    cfg = pkg.synth.CONFIGS["C2"]
+    rows, cols = cfg["rows"], cfg["cols"]
+    mbf, mb = cfg["mbf"], cfg["mbf"] / cfg["fx"]
+    L, R = pkg.synth.synth_stereo_pair(rows, cols, 7)
+    X1 = pkg.ORBextractor(1000, device=device)
+    ms_mono = wall(lambda: X1(L, (0, 1000)), reps, warm)
+    X1.close()
+    XL, XR = pkg.ORBextractor(cfg["nfeatures"], device=device), pkg.ORBextractor(cfg["nfeatures"], device=device)
+
+    def pair():
+        t = threading.Thread(target=lambda: XR(R, (0, 0)))
+        t.start(); XL(L, (0, 0)); t.join()
+        pkg.ComputeStereoMatches(XL, XR, mb, mbf, frame=0)
+    ms_pair = wall(pair, reps, warm)
+    XL.close(); XR.close()
+    return {"mono_frame_ms": ms_mono, "stereo_pair_ms": ms_pair,
+            "note": "single 752x480 frame through orbx_extract (host in/out); stereo pair = two extractor threads + orbx_stereo_match"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--pairs", type=int, default=256)
@@ -151,7 +175,8 @@ def main():
            "C3_knn2_1000": knn_leg(pkg, 1000, reps, warm),
            "knn2_8192": knn_leg(pkg, 8192, reps, warm),
            "C3_search_by_projection": proj_leg(pkg, reps, warm),
-           "prepare": prepare_leg(pkg, 64 if args.quick else 256, 2, 1 if args.quick else 5, 1 if args.quick else 2)}
+           "prepare": prepare_leg(pkg, 64 if args.quick else 256, 2, 1 if args.quick else 5, 1 if args.quick else 2),
+           "latency": latency_leg(pkg, 10 if args.quick else 200, 2 if args.quick else 20)}
     print(json.dumps(out))
 
 
