@@ -18,7 +18,17 @@
 // Latency-bound integer work (no roofline); reported as a share of the step.
 #include "orbx_internal.h"
 
-#define OCT_TABLES 23     // int arrays of node_cap entries in the per-CTA node scratch
+#define OCT_TABLES 25     // int arrays of node_cap entries in the per-CTA node scratch
+// "Fast rounds": the subdivision GEOMETRY of the reference's quadtree does not depend on the data (a node's children
+// are its four quadrants, ceil-halved) - only which nodes exist and when the splitting stops does.  So ONE candidate
+// pass bins every candidate by its path through the implicit tree down to depth OCT_HDEPTH; the per-child counts a
+// round needs are then table lookups, and the per-round candidate pass disappears as long as no node deeper than
+// OCT_HDEPTH has to split (dense frames: never - 4^5 nodes per root exceed every per-level quota).  A level that does
+// go deeper (few, clustered keypoints) materialises the per-candidate node labels once and continues with the
+// relabel-per-round scheme.  Shared-memory variant only, <= OCT_HROOTS root nodes.
+#define OCT_HDEPTH 5
+#define OCT_HROOTS 4
+#define OCT_HNODES 1365   // (4^(OCT_HDEPTH+1) - 1) / 3 implicit nodes per root
 
 // exclusive scan of in[0..m) into out[0..m) (out may alias in); returns the total to all threads.
 template <int NT>
@@ -118,6 +128,12 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     int* CC[2] = {T + 6 * cap, T + 10 * cap};    // keypoints per child (4 per node)
     int* NP4 = T + 14 * cap;                     // (old node, child) -> new list position
     int* aA = T + 18 * cap; int* aB = T + 19 * cap; int* aC = T + 20 * cap; int* aD = T + 21 * cap; int* aE = T + 22 * cap;
+    int* PD[2] = {T + 23 * cap, T + 24 * cap};   // depth << 24 | path of the node in the implicit tree (fast rounds)
+    int* Hh = T + OCT_TABLES * cap;              // per implicit node: candidates inside (later: list-position markers)
+    bool fast = SMEM && L.nIni <= OCT_HROOTS;
+    const int nI = L.nIni;
+    // first bin of depth d: nI * (4^d - 1) / 3
+#define HOFF(d) (nI * (((1 << (2 * (d))) - 1) / 3))
 
     const int n = min(D.candcnt[f * G.nlevels + lvl], L.cand_cap);   // compacted (unordered) by fast_band_kernel
     const int N = L.N;
@@ -129,12 +145,41 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
         BX[0][i] = x0 | (x1 << 16); BY[0][i] = H << 16; CN[0][i] = 0;
     }
     __syncthreads();
-    for_cands(cand, nullptr, n, [&](int i, uint32_t k, int) {
-        int r = (int)__fdiv_rn((float)KEY_X(k), L.hX);               // vpIniNodes[kp.pt.x/hX], :740
-        r = min(r, L.nIni - 1);
-        kcode[i] = 4 * r;
-        atomicAdd(&CN[0][r], 1);
-    });
+    if (fast) {
+        for (int i = tid; i < nI * OCT_HNODES; i += OCT_THREADS) Hh[i] = 0;
+        __syncthreads();
+        int* Hd = Hh + HOFF(OCT_HDEPTH);
+        for_cands(cand, nullptr, n, [&](int i, uint32_t k, int) {
+            int r = (int)__fdiv_rn((float)KEY_X(k), L.hX);           // vpIniNodes[kp.pt.x/hX], :740
+            r = min(r, L.nIni - 1);
+            const int x = KEY_X(k), y = KEY_Y(k);
+            int x0 = (int)__fmul_rn(L.hX, (float)r), x1 = (int)__fmul_rn(L.hX, (float)(r + 1)), y0 = 0, y1 = H;
+            int path = r;
+#pragma unroll
+            for (int d = 0; d < OCT_HDEPTH; d++) {                   // DivideNode geometry, :602-661
+                const int mx = x0 + ((x1 - x0 + 1) >> 1), my = y0 + ((y1 - y0 + 1) >> 1);
+                const int cx = x >= mx, cy = y >= my;
+                path = 4 * path + 2 * cy + cx;
+                x0 = cx ? mx : x0; x1 = cx ? x1 : mx; y0 = cy ? my : y0; y1 = cy ? y1 : my;
+            }
+            kcode[i] = path;
+            atomicAdd(&Hd[path], 1);
+        });
+        __syncthreads();
+        for (int d = OCT_HDEPTH - 1; d >= 0; d--) {
+            int* Hp = Hh + HOFF(d); const int* Hc = Hh + HOFF(d + 1);
+            for (int q = tid; q < (nI << (2 * d)); q += OCT_THREADS) Hp[q] = Hc[4 * q] + Hc[4 * q + 1] + Hc[4 * q + 2] + Hc[4 * q + 3];
+            __syncthreads();
+        }
+        for (int i = tid; i < nI; i += OCT_THREADS) CN[0][i] = Hh[i];
+    } else {
+        for_cands(cand, nullptr, n, [&](int i, uint32_t k, int) {
+            int r = (int)__fdiv_rn((float)KEY_X(k), L.hX);           // vpIniNodes[kp.pt.x/hX], :740
+            r = min(r, L.nIni - 1);
+            kcode[i] = 4 * r;
+            atomicAdd(&CN[0][r], 1);
+        });
+    }
     __syncthreads();
     for (int i = tid; i < L.nIni; i += OCT_THREADS) aA[i] = CN[0][i] > 0;
     __syncthreads();
@@ -142,7 +187,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     for (int i = tid; i < L.nIni; i += OCT_THREADS) {
         const int p = aB[i];
         if (CN[0][i] > 0) {
-            BX[1][p] = BX[0][i]; BY[1][p] = BY[0][i]; CN[1][p] = CN[0][i];
+            BX[1][p] = BX[0][i]; BY[1][p] = BY[0][i]; CN[1][p] = CN[0][i]; PD[1][p] = i;     // depth 0, path = root index
             *reinterpret_cast<int4*>(CC[1] + 4 * p) = make_int4(0, 0, 0, 0);
         }
         *reinterpret_cast<int4*>(NP4 + 4 * i) = make_int4(p, p, p, p);
@@ -155,11 +200,50 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
 
 #pragma unroll 1
     while (more) {
-        // ---- candidate step: relabel, child inside the new node, next round's per-child counts ----
-        {
+        bool materialise = false;
+        if (fast) {
+            if (finish) break;                                             // no labels to refresh: the winner pass looks nodes up
+            // ---- fast round: per-child counts of the expandable nodes straight from the implicit-tree bins ----
+            if (tid == 0) s_val[2] = 0;
+            __syncthreads();
+            const int* cn = CN[cur]; int* cc = CC[cur]; const int* pd = PD[cur];
+            int deep = 0;
+            for (int i = tid; i < size; i += OCT_THREADS) {
+                if (cn[i] > 1) {
+                    const int d = pd[i] >> 24, q = pd[i] & 0xFFFFFF;
+                    if (d >= OCT_HDEPTH) deep = 1;
+                    else {
+                        const int* Hc = Hh + HOFF(d + 1) + 4 * q;
+                        *reinterpret_cast<int4*>(cc + 4 * i) = make_int4(Hc[0], Hc[1], Hc[2], Hc[3]);
+                    }
+                }
+            }
+            if (deep) s_val[2] = 1;
+            __syncthreads();
+            if (s_val[2]) {
+                // a node below the binned depth has to split: mark every list node in the bins (-1 - position), let each
+                // candidate find its node, and continue with per-round relabelling
+                fast = false; materialise = true;
+                for (int i = tid; i < size; i += OCT_THREADS) {
+                    Hh[HOFF(pd[i] >> 24) + (pd[i] & 0xFFFFFF)] = -1 - i;
+                    *reinterpret_cast<int4*>(cc + 4 * i) = make_int4(0, 0, 0, 0);
+                }
+                __syncthreads();
+            }
+        }
+        if (!fast) {
+            // ---- candidate step: relabel, child inside the new node, next round's per-child counts ----
             const int* bx = BX[cur]; const int* by = BY[cur]; const int* cn = CN[cur]; int* cc = CC[cur];
             for_cands(cand, kcode, n, [&](int i, uint32_t k, int code) {
-                const int p = NP4[code];
+                int p;
+                if (materialise) {
+                    p = 0;
+#pragma unroll
+                    for (int d = 0; d <= OCT_HDEPTH; d++) {
+                        const int v = Hh[HOFF(d) + (code >> (2 * (OCT_HDEPTH - d)))];
+                        if (v < 0) { p = -1 - v; break; }
+                    }
+                } else p = NP4[code];
                 int c = 0;
                 if (!finish && cn[p] > 1) {
                     c = child_of(KEY_X(k), KEY_Y(k), bx[p], by[p]);
@@ -167,9 +251,9 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
                 }
                 kcode[i] = 4 * p + c;
             });
+            __syncthreads();
+            if (finish) break;
         }
-        __syncthreads();
-        if (finish) break;
         // ---- node step ----
         const int prevSize = size;
         const int nxt = cur ^ 1;
@@ -242,8 +326,8 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
         if (tid == 0) s_val[1] = 0;
         __syncthreads();
         {
-            const int* bxo = BX[cur]; const int* byo = BY[cur];
-            int* bxn = BX[nxt]; int* byn = BY[nxt]; int* cnn = CN[nxt]; int* ccn = CC[nxt];
+            const int* bxo = BX[cur]; const int* byo = BY[cur]; const int* pdo = PD[cur];
+            int* bxn = BX[nxt]; int* byn = BY[nxt]; int* cnn = CN[nxt]; int* ccn = CC[nxt]; int* pdn = PD[nxt];
             int myexp = 0;
             for (int i = tid; i < size; i += OCT_THREADS) {
                 const int bx = bxo[i], by = byo[i];
@@ -253,6 +337,11 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
                     const int mx = x0 + ((x1 - x0 + 1) >> 1), my = y0 + ((y1 - y0 + 1) >> 1);
                     const int4 c4 = *reinterpret_cast<const int4*>(cc + 4 * i);
                     int4 np = make_int4(0, 0, 0, 0);
+                    const int pdc = pdo[i] + (1 << 24) + 3 * (pdo[i] & 0xFFFFFF);      // depth + 1, path * 4 (+ child below)
+                    if (c4.w > 0) pdn[p] = pdc + 3;
+                    if (c4.z > 0) pdn[p + (c4.w > 0)] = pdc + 2;
+                    if (c4.y > 0) pdn[p + (c4.w > 0) + (c4.z > 0)] = pdc + 1;
+                    if (c4.x > 0) pdn[p + (c4.w > 0) + (c4.z > 0) + (c4.y > 0)] = pdc;
                     if (c4.w > 0) { bxn[p] = mx | (x1 << 16); byn[p] = my | (y1 << 16); cnn[p] = c4.w; np.w = p;
                                     *reinterpret_cast<int4*>(ccn + 4 * p) = make_int4(0, 0, 0, 0); p++; myexp += c4.w > 1; }
                     if (c4.z > 0) { bxn[p] = x0 | (mx << 16); byn[p] = my | (y1 << 16); cnn[p] = c4.z; np.z = p;
@@ -264,7 +353,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
                     *reinterpret_cast<int4*>(NP4 + 4 * i) = np;
                 } else {
                     p = totalNe + aC[i];
-                    bxn[p] = bx; byn[p] = by; cnn[p] = cn[i];
+                    bxn[p] = bx; byn[p] = by; cnn[p] = cn[i]; pdn[p] = pdo[i];
                     *reinterpret_cast<int4*>(ccn + 4 * p) = make_int4(0, 0, 0, 0);
                     *reinterpret_cast<int4*>(NP4 + 4 * i) = make_int4(p, p, p, p);
                 }
@@ -290,17 +379,30 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     uint32_t* sel = D.sel + (long long)f * G.sel_per_frame + L.sel_base;
     const int nout = min(size, L.sel_cap);
     const bool packed = L.nCols * L.nRows <= 1024;
-    for (int i = tid; i < size; i += OCT_THREADS) { best[i] = 0u; bestrank[i] = 0x7FFFFFFF; }
+    for (int i = tid; i < size; i += OCT_THREADS) {
+        best[i] = 0u; bestrank[i] = 0x7FFFFFFF;
+        if (fast) Hh[HOFF(PD[cur][i] >> 24) + (PD[cur][i] & 0xFFFFFF)] = -1 - i;      // list-position markers
+    }
     __syncthreads();
+    auto node_of = [&](int code) -> int {
+        if (!fast) return code >> 2;
+        int p = 0;
+#pragma unroll
+        for (int d = 0; d <= OCT_HDEPTH; d++) {
+            const int v = Hh[HOFF(d) + (code >> (2 * (OCT_HDEPTH - d)))];
+            if (v < 0) { p = -1 - v; break; }
+        }
+        return p;
+    };
     if (packed) {
         for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
-            atomicMax(&best[code >> 2], (KEY_S(k) << 24) | (0xFFFFFFu - (uint32_t)cand_rank(k, L)));
+            atomicMax(&best[node_of(code)], (KEY_S(k) << 24) | (0xFFFFFFu - (uint32_t)cand_rank(k, L)));
         });
     } else {
-        for_cands(cand, kcode, n, [&](int, uint32_t k, int code) { atomicMax(&best[code >> 2], KEY_S(k)); });
+        for_cands(cand, kcode, n, [&](int, uint32_t k, int code) { atomicMax(&best[node_of(code)], KEY_S(k)); });
         __syncthreads();
         for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
-            const int nd = code >> 2;
+            const int nd = node_of(code);
             if (KEY_S(k) == best[nd]) atomicMin(&bestrank[nd], cand_rank(k, L));
         });
     }
@@ -316,6 +418,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
 #undef OCT_THREADS
 #undef block_scan_excl
 #undef for_cands
+#undef HOFF
 }
 
 size_t octree_nodetab_ints(const FrameGeom& G)
@@ -342,7 +445,7 @@ int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStre
     small.n = big.n = huge.n = 0;
     size_t small_need = 0, big_need = 0;
     for (int l = 0; l < G.nlevels; l++) {
-        const size_t need = (size_t)G.L[l].node_cap * OCT_TABLES * sizeof(int);
+        const size_t need = ((size_t)G.L[l].node_cap * OCT_TABLES + (G.L[l].nIni <= OCT_HROOTS ? G.L[l].nIni * OCT_HNODES : 0)) * sizeof(int);
         if (need <= 64 * 1024) { small.lvl[small.n++] = l; small_need = need > small_need ? need : small_need; }
         else if (need <= 220 * 1024) { big.lvl[big.n++] = l; big_need = need > big_need ? need : big_need; }
         else huge.lvl[huge.n++] = l;
