@@ -44,30 +44,28 @@ UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 def profiled_traffic(stage, frames_per_launch):
     """dram__bytes_read.sum + dram__bytes_write.sum of the stage's kernel from the newest committed full-set
-    ncu summary (profiles/*_full_summary.csv, captured at 512 frames per launch), scaled to this launch."""
+    ncu summary that holds that kernel (profiles/*_full_summary.csv), scaled to this launch's frame count."""
     import csv
-    files = sorted((ROOT / "profiles").glob("*_full_summary.csv"))
-    if not files:
-        return None, None
-    f = files[-1]
-    rows = list(csv.reader(open(f)))
-    hdr = rows[0]
-    cols = {}
-    for i, h in enumerate(hdr):
-        for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-            if h.startswith(key):
-                cols[key] = (i, UNIT.get(h[h.index("[") + 1:h.index("]")], None))
-    if len(cols) != 2 or any(u is None for _, u in cols.values()):
-        return None, None
-    tot = 0.0; frames = None
-    for r in rows[1:]:
-        if r[1].strip() == STAGE_KERNEL[stage]:
-            tot += sum(float(r[i]) * u for i, u in cols.values())
-            g = [int(x) for x in r[2].strip("()").split(",")]
-            frames = max(g[1], g[2]) if stage != "pyramid" else g[2]
-    if tot == 0.0 or not frames:
-        return None, None
-    return tot * frames_per_launch / frames, f"{f.name} ({frames} frames per launch, scaled to {frames_per_launch})"
+    for f in sorted((ROOT / "profiles").glob("*_full_summary.csv"), reverse=True):
+        rows = list(csv.reader(open(f)))
+        hdr = rows[0]
+        cols = {}
+        for i, h in enumerate(hdr):
+            for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                if h.startswith(key):
+                    cols[key] = (i, UNIT.get(h[h.index("[") + 1:h.index("]")], None))
+        if len(cols) != 2 or any(u is None for _, u in cols.values()):
+            continue
+        tot = 0.0; frames = None
+        for r in rows[1:]:
+            if r[1].strip() == STAGE_KERNEL[stage]:
+                tot += sum(float(r[i]) * u for i, u in cols.values())
+                g = [int(x) for x in r[2].strip("()").split(",")]
+                frames = max(g[1], g[2]) if stage != "pyramid" else g[2]
+        if tot == 0.0 or not frames:
+            continue                                    # a capture of other kernels (matching legs)
+        return tot * frames_per_launch / frames, f"{f.name} ({frames} frames per launch, scaled to {frames_per_launch})"
+    return None, None
 
 
 def algorithmic_bytes(rows, cols, isf, nkp_mean):

@@ -123,3 +123,30 @@ def test_large_frames_match_oracle(pkg, orc, oracle, name, rows, cols, nf):
     assert mono_g == mono_o and len(kps_g) == len(kps_o) >= nf
     assert np.array_equal(kps_g, kps_o) and np.array_equal(desc_g, desc_o)
     X.close()
+
+
+@pytest.mark.parametrize("npatch,patch,nf,seed", [(20, 24, 2000, 1), (6, 48, 1000, 2), (40, 15, 3000, 3)])
+def test_clustered_keypoints_deep_quadtree(pkg, orc, oracle, npatch, patch, nf, seed):
+    """Corners only inside a few small noisy patches of an otherwise flat frame, fewer than the per-level quota: the
+    quadtree has to split down to single keypoints, far below the depth its candidate bins cover (fast rounds ->
+    materialise the labels -> relabel per round); selection, order and descriptors must still equal the oracle's.
+    (One single patch would not do: the reference stops as soon as a round leaves the node count unchanged.)"""
+    rows, cols = 480, 752
+    rng = np.random.default_rng(seed)
+    img = np.full((rows, cols), 90, np.uint8)
+    for _ in range(npatch):
+        blk = rng.integers(0, 2, (patch // 3 + 1, patch // 3 + 1)).astype(np.uint8) * 120 + 40
+        tex = np.kron(blk, np.ones((3, 3), np.uint8))
+        y0, x0 = int(rng.integers(30, rows - 30 - patch)), int(rng.integers(30, cols - 30 - patch))
+        img[y0:y0 + patch, x0:x0 + patch] = tex[:patch, :patch]
+    X = pkg.ORBextractor(nf)
+    E = orc.Extractor(nf, oracle=oracle)
+    mg, kg, dg = X(img, (0, 0))
+    mo, ko, do = E(img, (0, 0))
+    assert 500 < len(ko) < nf
+    for l in range(8):
+        sel_g, _ = X.level_keys(l, 1)
+        sel_o, _ = E.level_selected(l)
+        assert np.array_equal(sel_g, _cand_arr(sel_o)), f"quadtree selection level {l}"
+    assert mg == mo and np.array_equal(kg, ko) and np.array_equal(dg, do)
+    X.close()
