@@ -175,6 +175,17 @@ int orbx_stereo_match_batch(orbx_extractor* eL, orbx_extractor* eR, float mb, fl
 /* resident variant (results stay on device; for kernel timing) */
 int orbx_stereo_match_resident(orbx_extractor* eL, orbx_extractor* eR, float mb, float mbf);
 
+/* The stereo Frame constructor's extraction + matching in ONE call: the two ExtractORB threads (src/Frame.cc:132-137,
+ * both with vLappingArea {0,0}) and ComputeStereoMatches (:154, src/Frame.cc:1027-1276).  Both extractions run
+ * concurrently on the two handles' streams, the match is queued behind them, one host wait.  HOST images in (CV_8UC1,
+ * row steps stepL / stepR), HOST results out: cap keypoints / descriptors per eye, uRight / depth for the left
+ * keypoints (mvuRight, mvDepth).  nL / nR: keypoints found.  Pyramids and results stay resident as after orbx_extract. */
+int orbx_extract_stereo(orbx_extractor* eL, orbx_extractor* eR, const uint8_t* imgL, size_t stepL,
+                        const uint8_t* imgR, size_t stepR, int rows, int cols,
+                        orbx_keypoint* kpsL, uint8_t* descL, int* nL,
+                        orbx_keypoint* kpsR, uint8_t* descR, int* nR, int cap,
+                        float mb, float mbf, float* uRight, float* depth);
+
 /* cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, k=2) as used by Frame::ComputeStereoFishEyeMatches
  * src/Frame.cc:1440-1480 (matcher at src/Frame.cc:48).  HOST descriptors in, out_idx/out_dist
  * [nq][2] out (missing neighbour = -1); ties by ascending train index. */

@@ -65,6 +65,9 @@ SYMBOLS = {
     "orbx_stereo_match": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int]),
     "orbx_stereo_match_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int]),
     "orbx_stereo_match_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_float]),
+    "orbx_extract_stereo": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int, C.c_int,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                      C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
     "orbx_knn2_hamming": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "orbx_search_by_projection": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
                                             C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int,

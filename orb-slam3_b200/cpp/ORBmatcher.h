@@ -36,6 +36,35 @@ struct ORBmatcherGPU {
             throw std::runtime_error(std::string("ComputeStereoMatches: ") + orbx_last_error());
     }
 
+    // The stereo Frame constructor's hot part as one call (src/Frame.cc:132-137: threadLeft / threadRight ExtractORB with
+    // vLappingArea {0,0}; :143 N = mvKeys.size(); :154 ComputeStereoMatches): both eyes are extracted concurrently on the
+    // device and the match is queued behind them - one host wait instead of two thread joins and a third call.
+    static void ExtractStereo(ORBextractor& left, ORBextractor& right, const cv::Mat& imLeft, const cv::Mat& imRight,
+                              std::vector<cv::KeyPoint>& mvKeys, cv::Mat& mDescriptors,
+                              std::vector<cv::KeyPoint>& mvKeysRight, cv::Mat& mDescriptorsRight,
+                              float mb, float mbf, std::vector<float>& mvuRight, std::vector<float>& mvDepth)
+    {
+        const int cap = orbx_max_keypoints(left.handle(), imLeft.rows, imLeft.cols);
+        if (cap < 0) throw std::runtime_error(std::string("ExtractStereo: ") + orbx_last_error());
+        mvKeys.resize((size_t)cap); mvKeysRight.resize((size_t)cap);
+        std::vector<uint8_t> dl((size_t)cap * 32), dr((size_t)cap * 32);
+        mvuRight.assign((size_t)cap, -1.0f); mvDepth.assign((size_t)cap, -1.0f);
+        int nL = 0, nR = 0;
+        if (orbx_extract_stereo(left.handle(), right.handle(), imLeft.data, imLeft.step, imRight.data, imRight.step,
+                                imLeft.rows, imLeft.cols, reinterpret_cast<orbx_keypoint*>(mvKeys.data()), dl.data(), &nL,
+                                reinterpret_cast<orbx_keypoint*>(mvKeysRight.data()), dr.data(), &nR, cap, mb, mbf,
+                                mvuRight.data(), mvDepth.data()) != ORBX_OK)
+            throw std::runtime_error(std::string("ExtractStereo: ") + orbx_last_error());
+        mvKeys.resize((size_t)nL); mvKeysRight.resize((size_t)nR);
+        mvuRight.resize((size_t)nL); mvDepth.resize((size_t)nL);
+        auto fill = [](cv::Mat& D, const std::vector<uint8_t>& src, int n) {
+            if (n == 0) { D.release(); return; }
+            ORBX_MAT_CREATE(D, n, 32);
+            for (int i = 0; i < n; i++) std::memcpy(D.ptr(i), src.data() + (size_t)i * 32, 32);
+        };
+        fill(mDescriptors, dl, nL); fill(mDescriptorsRight, dr, nR);
+    }
+
     // cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, matches, 2) of ComputeStereoFishEyeMatches, src/Frame.cc:1458
     static void KnnMatch2(const cv::Mat& q, const cv::Mat& t, std::vector<int>& idx, std::vector<int>& dist, int device = 0)
     {

@@ -56,6 +56,7 @@ extern "C" int orbx_create(int nfeatures, float scaleFactor, int nlevels, int in
     e->device = device; e->reserved = false; e->profiling = false; e->launches = 0; e->last_nframes = 0;
     e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr; e->d_st_rows = nullptr;
     e->h_counts = nullptr; e->h_counts_cap = 0;
+    e->h_in = e->h_land = nullptr; e->h_in_cap = e->h_land_cap = 0;
     e->d_map = nullptr; e->map_rows = e->map_cols = 0;
     e->d_raw = nullptr; e->raw_bytes = 0; e->raw_rows = e->raw_cols = e->raw_ch = e->raw_rgb = e->raw_pitch = 0;
     memset(&e->G, 0, sizeof(e->G)); memset(&e->D, 0, sizeof(e->D));
@@ -107,6 +108,8 @@ extern "C" void orbx_destroy(orbx_extractor* e)
     for (int i = 0; i < ORBX_NCSTREAMS; i++) { cudaStreamDestroy(e->cstream[i]); cudaEventDestroy(e->ev_join[i]); }
     cudaEventDestroy(e->ev_fork);
     if (e->h_counts) cudaFreeHost(e->h_counts);
+    if (e->h_in) cudaFreeHost(e->h_in);
+    if (e->h_land) cudaFreeHost(e->h_land);
     cudaStreamDestroy(e->stream_h2d); cudaStreamDestroy(e->stream_d2h);
     cudaStreamDestroy(e->stream);
     delete e;
@@ -418,6 +421,125 @@ static int prepare_begin(orbx_extractor* e, const uint8_t* imgs, int src_rows, i
     return 0;
 }
 
+// One chunk, few frames (the per-frame call of a SLAM front end): everything on the handle's stream, host side kept off
+// the critical path.  Frames go through a pinned staging buffer (one host memcpy, then a truly asynchronous H2D copy
+// that the first kernels queue behind), results land in a pinned zone by two asynchronous D2H copies, ONE stream
+// synchronise, then only the nkp valid rows are copied into the caller's (pageable) arrays.
+#define ORBX_LAND_MAX (4u << 20)
+static bool orbx_no_land()
+{
+    static const bool v = [] { const char* c = getenv("ORBX_NO_LAND"); return c && atoi(c) != 0; }();
+    return v;
+}
+
+static int pinned_reserve(uint8_t** p, size_t* cap, size_t need)
+{
+    if (need <= *cap) return 0;
+    if (*p) cudaFreeHost(*p);
+    *p = nullptr; *cap = 0;
+    CUDA_TRY(cudaHostAlloc((void**)p, need, cudaHostAllocDefault));
+    *cap = need;
+    return 0;
+}
+
+// stage the frames, upload, run the pipeline: all asynchronous on the handle's stream
+static int small_enqueue(orbx_extractor* e, int nframes, const uint8_t* imgs, size_t step, size_t frame_stride, int lap0, int lap1)
+{
+    const FrameGeom& G = e->G;
+    const size_t pitch = (size_t)(G.cols + 15) / 16 * 16, fbytes = pitch * G.rows;
+    const uint8_t* src_all = imgs;
+    size_t sstep = step, sstride = frame_stride;
+    cudaPointerAttributes pa;
+    const bool pinned = cudaPointerGetAttributes(&pa, imgs) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    if (!pinned) {                                       // a caller that keeps its frames in pinned memory skips the staging copy
+        cudaGetLastError();
+        int r = pinned_reserve(&e->h_in, &e->h_in_cap, fbytes * nframes);
+        if (r) return r;
+        for (int f = 0; f < nframes; f++) {
+            const uint8_t* src = imgs + (size_t)f * frame_stride;
+            uint8_t* dst = e->h_in + (size_t)f * fbytes;
+            if (step == pitch) memcpy(dst, src, fbytes);
+            else for (int y = 0; y < G.rows; y++) memcpy(dst + (size_t)y * pitch, src + (size_t)y * step, G.cols);
+        }
+        src_all = e->h_in; sstep = pitch; sstride = fbytes;
+    }
+    int r = upload_frames(e, 0, nframes, src_all, sstep, sstride, e->stream);
+    if (r) return r;
+    r = run_pipeline(e, 0, nframes, lap0, lap1, e->stream);
+    if (r) return r;
+    e->last_nframes = nframes;
+    return 0;
+}
+
+// results -> the pinned landing zone {keypoints | descriptors | extra}, asynchronous on the handle's stream
+static int small_download(orbx_extractor* e, int nframes, size_t extra_bytes)
+{
+    const int oc = e->G.out_cap;
+    const size_t kb = (size_t)nframes * oc * sizeof(orbx_keypoint), db = (size_t)nframes * oc * 32;
+    if (e->h_counts_cap < 2 * (size_t)nframes) {
+        if (e->h_counts) cudaFreeHost(e->h_counts);
+        e->h_counts = nullptr; e->h_counts_cap = 0;
+        CUDA_TRY(cudaHostAlloc((void**)&e->h_counts, sizeof(int) * 2 * (size_t)nframes, cudaHostAllocDefault));
+        e->h_counts_cap = 2 * (size_t)nframes;
+    }
+    int r = pinned_reserve(&e->h_land, &e->h_land_cap, kb + db + extra_bytes);
+    if (r) return r;
+    cudaStream_t st = e->stream;
+    CUDA_TRY(cudaMemcpyAsync(e->h_counts, e->D.counts, sizeof(int) * 2 * nframes, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(e->h_land, e->D.kps, kb, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(e->h_land + kb, e->D.desc, db, cudaMemcpyDeviceToHost, st));
+    return 0;
+}
+
+// after the stream synchronise: counts and the valid rows into the caller's arrays
+static int small_finish(orbx_extractor* e, int nframes, orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono)
+{
+    const int oc = e->G.out_cap;
+    const size_t kb = (size_t)nframes * oc * sizeof(orbx_keypoint);
+    const int* counts = e->h_counts;
+    int rc = ORBX_OK;
+    for (int f = 0; f < nframes; f++) {
+        const int n = counts[2 * f];
+        if (nkp) nkp[f] = n;
+        if (mono) mono[f] = counts[2 * f + 1];
+        if (n > cap) rc = ORBX_ERR_CAPACITY;
+        const int m = n < cap ? n : cap;
+        memcpy(kps + (size_t)f * cap, e->h_land + (size_t)f * oc * sizeof(orbx_keypoint), (size_t)m * sizeof(orbx_keypoint));
+        memcpy(desc + (size_t)f * cap * 32, e->h_land + kb + (size_t)f * oc * 32, (size_t)m * 32);
+    }
+    if (rc) orbx_set_error("keypoint capacity %d too small", cap);
+    return rc;
+}
+
+static int extract_small(orbx_extractor* e, int nframes, const uint8_t* imgs, size_t step, size_t frame_stride,
+                         int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono)
+{
+    int r = small_enqueue(e, nframes, imgs, step, frame_stride, lap0, lap1);
+    if (r) return r;
+    r = small_download(e, nframes, 0);
+    if (r) return r;
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    collect_stage_times(e);
+    return small_finish(e, nframes, kps, desc, cap, nkp, mono);
+}
+
+// lazy sizing of the handle for rows x cols frames: bound the device footprint to ~8 GB
+static int ensure_reserved(orbx_extractor* e, int rows, int cols, int nframes)
+{
+    if (e->reserved && e->G.rows == rows && e->G.cols == cols) return 0;
+    FrameGeom G;
+    std::vector<std::vector<ResizeTapX>> tx; std::vector<std::vector<ResizeTapY>> ty;
+    int r = orbx_compute_geometry(e, rows, cols, 1, &G, &tx, &ty);
+    if (r) { orbx_set_error("image %dx%d too small for %d pyramid levels (35-px cell grid)", cols, rows, e->nlevels); return r; }
+    long long per = (long long)rows * ((cols + 127) / 128 * 128) + G.keys_per_frame * 12;
+    for (int l = 0; l < G.nlevels; l++) per += 2 * G.L[l].plane_bytes;
+    long long b = (8LL << 30) / per;
+    if (b < 1) b = 1;
+    if (b > nframes) b = nframes;
+    if (b > 512) b = 512;
+    return orbx_reserve(e, rows, cols, (int)b);
+}
+
 static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* imgs, int rows, int cols,
                               size_t step, size_t frame_stride, int lap0, int lap1,
                               orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono, bool raw)
@@ -425,22 +547,8 @@ static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* img
     if (!e) { orbx_set_error("null handle"); return ORBX_ERR_ARG; }
     if (!imgs || rows <= 0 || cols <= 0 || nframes <= 0) { orbx_set_error("empty image"); return ORBX_EMPTY_IMAGE; }
     if (!kps || !desc || cap <= 0 || (!raw && step < (size_t)cols)) { orbx_set_error("bad output buffers / step"); return ORBX_ERR_ARG; }
-    int r;
-    if (!(e->reserved && e->G.rows == rows && e->G.cols == cols)) {
-        // lazy sizing: bound the device footprint to ~8 GB
-        FrameGeom G;
-        std::vector<std::vector<ResizeTapX>> tx; std::vector<std::vector<ResizeTapY>> ty;
-        r = orbx_compute_geometry(e, rows, cols, 1, &G, &tx, &ty);
-        if (r) { orbx_set_error("image %dx%d too small for %d pyramid levels (35-px cell grid)", cols, rows, e->nlevels); return r; }
-        long long per = (long long)rows * ((cols + 127) / 128 * 128) + G.keys_per_frame * 12;
-        for (int l = 0; l < G.nlevels; l++) per += 2 * G.L[l].plane_bytes;
-        long long b = (8LL << 30) / per;
-        if (b < 1) b = 1;
-        if (b > nframes) b = nframes;
-        if (b > 512) b = 512;
-        r = orbx_reserve(e, rows, cols, (int)b);
-        if (r) return r;
-    }
+    int r = ensure_reserved(e, rows, cols, nframes);
+    if (r) return r;
     CUDA_TRY(cudaSetDevice(e->device));
     const int B = e->G.batch;
     int rc = ORBX_OK;
@@ -477,6 +585,8 @@ static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* img
         e->h_counts_cap = 2 * (size_t)nframes;
     }
     int* counts = e->h_counts;
+    if (!multi && !raw && (size_t)nframes * e->G.out_cap * (sizeof(orbx_keypoint) + 32) <= ORBX_LAND_MAX && !orbx_no_land())
+        return extract_small(e, nframes, imgs, step, frame_stride, lap0, lap1, kps, desc, cap, nkp, mono);
     cudaStream_t up = multi ? e->stream_h2d : e->stream, dn = multi ? e->stream_d2h : e->stream;
     for (int k = 0; k < nchunks; k++) {
         const int fr0 = k * chunk, n = nframes - fr0 < chunk ? nframes - fr0 : chunk;
@@ -635,6 +745,52 @@ extern "C" int orbx_extract(orbx_extractor* e, const uint8_t* img, int rows, int
     if (nkp) *nkp = n;
     if (r < 0) return r;
     return mono;
+}
+
+// The stereo Frame constructor's hot part in ONE call (src/Frame.cc:132-137 two ExtractORB threads, :154
+// ComputeStereoMatches): both extractions run concurrently on the two handles' streams, the match is queued behind them,
+// the right eye's results travel back while the match kernels run; the host blocks once.
+extern "C" int orbx_extract_stereo(orbx_extractor* eL, orbx_extractor* eR, const uint8_t* imgL, size_t stepL,
+                                   const uint8_t* imgR, size_t stepR, int rows, int cols,
+                                   orbx_keypoint* kpsL, uint8_t* descL, int* nL,
+                                   orbx_keypoint* kpsR, uint8_t* descR, int* nR, int cap,
+                                   float mb, float mbf, float* uRight, float* depth)
+{
+    if (nL) *nL = 0;
+    if (nR) *nR = 0;
+    if (!eL || !eR || eL == eR) { orbx_set_error("two distinct extractor handles needed"); return ORBX_ERR_ARG; }
+    if (!imgL || !imgR || rows <= 0 || cols <= 0) { orbx_set_error("empty image"); return ORBX_EMPTY_IMAGE; }
+    if (!kpsL || !descL || !kpsR || !descR || !uRight || !depth || cap <= 0 || stepL < (size_t)cols || stepR < (size_t)cols) {
+        orbx_set_error("bad output buffers / step"); return ORBX_ERR_ARG;
+    }
+    if (eL->device != eR->device) { orbx_set_error("left/right extractors live on different devices"); return ORBX_ERR_ARG; }
+    int r = ensure_reserved(eL, rows, cols, 1);
+    if (!r) r = ensure_reserved(eR, rows, cols, 1);
+    if (r) return r;
+    CUDA_TRY(cudaSetDevice(eL->device));
+    r = small_enqueue(eL, 1, imgL, stepL, stepL * (size_t)rows, 0, 0);
+    if (!r) r = small_enqueue(eR, 1, imgR, stepR, stepR * (size_t)rows, 0, 0);
+    if (!r) r = orbx_stereo_match_resident(eL, eR, mb, mbf);       // orders eL's stream behind eR's pipeline
+    if (r) return r;
+    const int oc = eL->G.out_cap;
+    r = small_download(eR, 1, 0);
+    if (!r) r = small_download(eL, 1, 2 * sizeof(float) * (size_t)oc);
+    if (r) return r;
+    float* su = reinterpret_cast<float*>(eL->h_land + (size_t)oc * (sizeof(orbx_keypoint) + 32));
+    CUDA_TRY(cudaMemcpyAsync(su, eL->d_uright, sizeof(float) * oc, cudaMemcpyDeviceToHost, eL->stream));
+    CUDA_TRY(cudaMemcpyAsync(su + oc, eL->d_depth, sizeof(float) * oc, cudaMemcpyDeviceToHost, eL->stream));
+    CUDA_TRY(cudaStreamSynchronize(eR->stream));
+    int monoR = 0, monoL = 0, cR = 0, cL = 0;
+    const int rcR = small_finish(eR, 1, kpsR, descR, cap, &cR, &monoR);
+    CUDA_TRY(cudaStreamSynchronize(eL->stream));
+    collect_stage_times(eL);
+    const int rcL = small_finish(eL, 1, kpsL, descL, cap, &cL, &monoL);
+    if (nL) *nL = cL;
+    if (nR) *nR = cR;
+    const int m = cL < cap ? cL : cap;
+    memcpy(uRight, su, sizeof(float) * (size_t)m);
+    memcpy(depth, su + oc, sizeof(float) * (size_t)m);
+    return rcL ? rcL : rcR;
 }
 
 extern "C" int orbx_get_pyramid_level(orbx_extractor* e, int frame, int level, int padded,

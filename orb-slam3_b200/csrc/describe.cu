@@ -10,63 +10,72 @@ __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9
 // assemble: final row of every selected keypoint (mono ascending / lapping-area descending,
 // src/ORBextractor.cc:1589,1633-1655) + all KeyPoint fields except the angle.
 // ------------------------------------------------------------------------------------------------
-#define ASM_THREADS 256
+#define ASM_THREADS 512
 
+// One CTA per frame walks the selected keypoints of all levels as ONE list (level-major = the reference's order) in
+// chunks of ASM_THREADS: a frame of 1000 keypoints is two chunks (two dependent global loads deep), not one chunk per level.
 __global__ void __launch_bounds__(ASM_THREADS)
 assemble_kernel(FrameGeom G, DevBuffers D, float lap0, float lap1)
 {
     __shared__ int s_warp[ASM_THREADS / 32];
+    __shared__ int s_pref[ORBX_MAX_LEVELS + 1];
+    orbx_pdl_prologue();
     const int f = blockIdx.x, tid = threadIdx.x;
-    const int* selcnt = D.selcnt + f * G.nlevels;
-    int total = 0;
-    for (int l = 0; l < G.nlevels; l++) total += selcnt[l];
+    if (tid == 0) {
+        const int* selcnt = D.selcnt + f * G.nlevels;
+        int a = 0;
+        for (int l = 0; l < G.nlevels; l++) { s_pref[l] = a; a += selcnt[l]; }
+        s_pref[G.nlevels] = a;
+    }
+    __syncthreads();
+    const int total = s_pref[G.nlevels];
     int nLap = 0, nMono = 0;       // running counts in reference order
     orbx_keypoint* kps = D.kps + (long long)f * G.out_cap;
-    for (int l = 0; l < G.nlevels; l++) {
-        const LevelGeom& L = G.L[l];
-        const uint32_t* sel = D.sel + (long long)f * G.sel_per_frame + L.sel_base;
-        int* outidx = D.outidx + (long long)f * G.sel_per_frame + L.sel_base;
-        const int n = selcnt[l];
-        for (int base = 0; base < n; base += ASM_THREADS) {
-            const int i = base + tid;
-            float x = 0.f, y = 0.f;
-            uint32_t key = 0;
-            int flag = 0, valid = i < n;
-            if (valid) {
-                key = sel[i];
-                x = (float)(KEY_X(key) + ORBX_MINB);                 // :1167
-                y = (float)(KEY_Y(key) + ORBX_MINB);
-                if (l != 0) { x = __fmul_rn(x, L.scale); y = __fmul_rn(y, L.scale); }   // :1639-1642
-                flag = (x >= lap0 && x <= lap1);                      // :1644
-            }
-            // block exclusive scan of flag
-            const unsigned bal = __ballot_sync(0xffffffffu, flag);
-            const int lane = tid & 31, warp = tid >> 5;
-            if (lane == 0) s_warp[warp] = __popc(bal);
-            __syncthreads();
-            int before = __popc(bal & ((1u << lane) - 1)), tot = 0;
-            for (int w = 0; w < ASM_THREADS / 32; w++) { if (w < warp) before += s_warp[w]; tot += s_warp[w]; }
-            const int nvalid = min(ASM_THREADS, n - base);
-            if (valid) {
-                const int lapBefore = nLap + before;
-                const int monoBefore = nMono + (i - base) - before;
-                const int dst = flag ? (total - 1 - lapBefore) : monoBefore;
-                outidx[i] = dst;
-                orbx_keypoint kp;
-                kp.x = x; kp.y = y; kp.size = L.patch_size; kp.angle = -1.f;
-                kp.response = (float)KEY_S(key); kp.octave = l; kp.class_id = -1;
-                kps[dst] = kp;
-            }
-            nLap += tot; nMono += nvalid - tot;
-            __syncthreads();
+    for (int base = 0; base < total; base += ASM_THREADS) {
+        const int g = base + tid;
+        const int valid = g < total;
+        float x = 0.f, y = 0.f;
+        uint32_t key = 0;
+        int flag = 0, l = 0, i = 0;
+        if (valid) {
+            while (g >= s_pref[l + 1]) l++;
+            i = g - s_pref[l];
+            const LevelGeom& L = G.L[l];
+            key = D.sel[(long long)f * G.sel_per_frame + L.sel_base + i];
+            x = (float)(KEY_X(key) + ORBX_MINB);                 // :1167
+            y = (float)(KEY_Y(key) + ORBX_MINB);
+            if (l != 0) { x = __fmul_rn(x, L.scale); y = __fmul_rn(y, L.scale); }   // :1639-1642
+            flag = (x >= lap0 && x <= lap1);                      // :1644
         }
+        // block exclusive scan of flag
+        const unsigned bal = __ballot_sync(0xffffffffu, flag);
+        const int lane = tid & 31, warp = tid >> 5;
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        int before = __popc(bal & ((1u << lane) - 1)), tot = 0;
+#pragma unroll
+        for (int w = 0; w < ASM_THREADS / 32; w++) { const int v = s_warp[w]; if (w < warp) before += v; tot += v; }
+        const int nvalid = min(ASM_THREADS, total - base);
+        if (valid) {
+            const LevelGeom& L = G.L[l];
+            const int lapBefore = nLap + before;
+            const int monoBefore = nMono + tid - before;
+            const int dst = flag ? (total - 1 - lapBefore) : monoBefore;
+            D.outidx[(long long)f * G.sel_per_frame + L.sel_base + i] = dst;
+            orbx_keypoint kp;
+            kp.x = x; kp.y = y; kp.size = L.patch_size; kp.angle = -1.f;
+            kp.response = (float)KEY_S(key); kp.octave = l; kp.class_id = -1;
+            kps[dst] = kp;
+        }
+        nLap += tot; nMono += nvalid - tot;
+        __syncthreads();
     }
     if (tid == 0) { D.counts[2 * f] = total; D.counts[2 * f + 1] = nMono; }
 }
 
 int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int lap0, int lap1, cudaStream_t s)
 {
-    assemble_kernel<<<nframes, ASM_THREADS, 0, s>>>(G, D, (float)lap0, (float)lap1);
+    orbx_launch(assemble_kernel, dim3(nframes), dim3(ASM_THREADS), 0, s, G, D, (float)lap0, (float)lap1);
     return 1;
 }
 
@@ -124,6 +133,7 @@ __device__ __forceinline__ uint32_t blur_hword(uint32_t El, uint32_t Ol, uint32_
 __global__ void __launch_bounds__(32 * BL_BY, BL_MINB)
 blur_kernel(FrameGeom G)
 {
+    orbx_pdl_prologue();
     const int lane = threadIdx.x, warp = threadIdx.y;
     // all levels in one launch: blockIdx.x enumerates (level, row-strip group, column block)
     int lvl = 0, bid = blockIdx.x;
@@ -182,7 +192,7 @@ void blur_plan(FrameGeom& G)
 
 int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
-    blur_kernel<<<dim3(G.blur_end[G.nlevels - 1], nframes), dim3(32, BL_BY), 0, s>>>(G);
+    orbx_launch(blur_kernel, dim3(G.blur_end[G.nlevels - 1], nframes), dim3(32, BL_BY), 0, s, G);
     (void)D;
     return 1;
 }
@@ -293,6 +303,7 @@ describe_kernel(FrameGeom G, DevBuffers D)
 {
     __shared__ uint32_t s_patch[DESC_WARPS][DESC_ROWS * DESC_PW];
     __shared__ uint32_t s_raw[DESC_WARPS][ORBX_PATCH * 9];
+    orbx_pdl_prologue();
     const int f = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int slot0 = (blockIdx.x * DESC_WARPS + warp) * DESC_KPW;
@@ -421,6 +432,6 @@ describe_kernel(FrameGeom G, DevBuffers D)
 int launch_describe(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
     const dim3 grid((G.sel_per_frame + DESC_WARPS * DESC_KPW - 1) / (DESC_WARPS * DESC_KPW), nframes);
-    describe_kernel<<<grid, DESC_WARPS * 32, 0, s>>>(G, D);
+    orbx_launch(describe_kernel, grid, dim3(DESC_WARPS * 32), 0, s, G, D);
     return 1;
 }

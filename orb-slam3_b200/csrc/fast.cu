@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINBLOCKS)
 fast_band_kernel(FrameGeom G, DevBuffers D)
 {
     extern __shared__ uint32_t s_dyn[];               // per warp: S words [ihmax][32], then 32 lane-private u16 survivor lists
+    orbx_pdl_prologue();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int item = blockIdx.x * FAST_WARPS + warp;
     if (item >= G.bands_per_frame) return;            // warps are independent: no block-level barrier below
@@ -361,7 +362,7 @@ int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out, int* warp_w
 
 int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
-    cudaMemsetAsync(D.candcnt, 0, sizeof(int) * (size_t)nframes * G.nlevels, s);
+    // D.candcnt was zeroed by pyr_level0_kernel
     int smem = G.fast_smem;
     // experiment hook: ORBX_FAST_SMEM pads the CTA's shared memory, i.e. caps the FAST CTAs per SM
     static const int pad = [] { const char* e = getenv("ORBX_FAST_SMEM"); return e ? atoi(e) : 0; }();
@@ -369,7 +370,7 @@ int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream
     if (smem > 48 * 1024)
         cudaFuncSetAttribute(fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     const dim3 grid((G.bands_per_frame + FAST_WARPS - 1) / FAST_WARPS, nframes);
-    fast_band_kernel<<<grid, FAST_THREADS, smem, s>>>(G, D);
+    orbx_launch(fast_band_kernel, grid, dim3(FAST_THREADS), (size_t)smem, s, G, D);
     return 1;
 }
 

@@ -17,6 +17,7 @@
 // y, x) since the FAST kernel emits candidates unordered.
 // Latency-bound integer work (no roofline); reported as a share of the step.
 #include "orbx_internal.h"
+#include <cstdlib>
 
 #define OCT_TABLES 25     // int arrays of node_cap entries in the per-CTA node scratch
 // "Fast rounds": the subdivision GEOMETRY of the reference's quadtree does not depend on the data (a node's children
@@ -114,6 +115,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     __shared__ int s_warp[NT / 32 + 1];
     __shared__ int s_val[4];
 
+    orbx_pdl_prologue();
     const int lvl = LV.lvl[blockIdx.x], f = blockIdx.y;
     const LevelGeom& L = G.L[lvl];
     const int tid = threadIdx.x;
@@ -432,11 +434,12 @@ size_t octree_nodetab_ints(const FrameGeom& G)
 // levels (8000-feature frames: level 0 needs 160 KB) share a launch of 1024-thread CTAs with their tables in shared
 // memory up to 220 KB (one CTA per SM), and levels beyond that a launch with the tables in global memory: their
 // candidate passes (250 k candidates per frame at 4K) are what the step waits for.
+#define OCT_NT_FEW 512
 template <bool SMEM, int NT>
 static void launch_group(const FrameGeom& G, const DevBuffers& D, const OctLevels& LV, int nframes, size_t smem, cudaStream_t s)
 {
     if (smem > 48 * 1024) cudaFuncSetAttribute(octree_kernel<SMEM, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    octree_kernel<SMEM, NT><<<dim3(LV.n, nframes), NT, smem, s>>>(G, D, LV);
+    orbx_launch(octree_kernel<SMEM, NT>, dim3(LV.n, nframes), dim3(NT), smem, s, G, D, LV);
 }
 
 int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
@@ -454,6 +457,14 @@ int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStre
     // the long-running launches first: CTAs of the later launches fill the SMs they leave idle
     if (huge.n) { launch_group<false, 1024>(G, D, huge, nframes, 0, s); launches++; }
     if (big.n) { launch_group<true, 1024>(G, D, big, nframes, big_need, s); launches++; }
-    if (small.n) { launch_group<true, 256>(G, D, small, nframes, small_need, s); launches++; }
+    if (small.n) {
+        // few CTAs in flight (single frames): the candidate passes of level 0 are the critical path, wider CTAs shorten them
+        static const int nt_env = [] { const char* e = getenv("ORBX_OCT_NT"); return e ? atoi(e) : 0; }();
+        const int nt = nt_env ? nt_env : (small.n * nframes <= 148 ? OCT_NT_FEW : 256);
+        if (nt == 1024) launch_group<true, 1024>(G, D, small, nframes, small_need, s);
+        else if (nt == 512) launch_group<true, 512>(G, D, small, nframes, small_need, s);
+        else launch_group<true, 256>(G, D, small, nframes, small_need, s);
+        launches++;
+    }
     return launches;
 }

@@ -21,6 +21,10 @@ struct orbx_extractor {
     cudaStream_t stream_h2d, stream_d2h;   // copy engines of the chunked extract_batch pipeline
     std::vector<cudaEvent_t> ev_up, ev_done, ev_down;
     int* h_counts; size_t h_counts_cap;    // pinned {nkp, mono} staging (a pageable target would make the D2H copy synchronous)
+    // single-chunk calls (one frame / a few frames): pinned staging of the input frames and a pinned landing zone for
+    // {keypoints, descriptors}: with pageable user buffers every cudaMemcpyAsync is a synchronous staged copy
+    uint8_t* h_in; size_t h_in_cap;
+    uint8_t* h_land; size_t h_land_cap;
     bool reserved;
     FrameGeom G;
     DevBuffers D;

@@ -6,6 +6,7 @@
 // hot path only writes the interior; the border is produced on demand (orbx_get_pyramid_level).
 // HBM-bound: algorithmic bytes per frame = read sum(L0..L6) + write sum(L1..L7).
 #include "orbx_internal.h"
+#include <cstdlib>
 
 __device__ __forceinline__ int reflect101(int i, int n)
 {
@@ -23,8 +24,14 @@ __device__ __forceinline__ int reflect101(int i, int n)
 template <bool ALIGNED>
 __global__ void __launch_bounds__(256)
 pyr_level0_kernel(const uint8_t* __restrict__ in, int in_pitch, long long in_frame_bytes,
-                  uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h)
+                  uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h,
+                  int* __restrict__ candcnt, int nlevels)
 {
+    orbx_pdl_prologue();
+    // the per-level candidate counters FAST appends to start at zero (one thread per frame; saves a memset node
+    // between the pyramid and FAST launches)
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.y == 0 && threadIdx.x < nlevels)
+        candcnt[blockIdx.z * nlevels + threadIdx.x] = 0;
     const int qi = blockIdx.x * blockDim.x + threadIdx.x;     // 16-byte group of the image row
     const int y = blockIdx.y * blockDim.y + threadIdx.y - PYR_HALO;
     if (y >= h + PYR_HALO || qi * 16 >= w) return;
@@ -99,12 +106,16 @@ __device__ __forceinline__ HRow4 pyr_hrow_fast(const uint8_t* __restrict__ S, co
     return r;
 }
 
-#define PYRF_ROWS 8
+// PYRF_ROWS output rows per thread: 8 for batches (one horizontal pass serves ~1.2 output rows), 2 when a launch holds
+// only a few frames - there the serial chain of dependent row loads per thread IS the launch's duration (8 rows: 8-10 us
+// per level for a single 752x480 frame, 2 rows: a third of that), and the redundant horizontal passes cost nothing
+template <int PYRF_ROWS>
 __global__ void __launch_bounds__(256)
 pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long pplane_bytes,
                        uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h,
                        const ResizeWord* __restrict__ tapw, const ResizeTapY* __restrict__ tapy)
 {
+    orbx_pdl_prologue();
     const int wi = ORBX_XOFF / 4 - 1 + blockIdx.x * blockDim.x + threadIdx.x; // interior words + one halo word per side
     if (wi > (ORBX_XOFF + w + 3) / 4) return;
     const int Y0 = (blockIdx.y * blockDim.y + threadIdx.y) * PYRF_ROWS - PYR_HALO;   // image row (interior + halo rows)
@@ -209,6 +220,13 @@ pyr_resize_kernel(const uint8_t* __restrict__ prev, int ppitch, long long pplane
     }
 }
 
+// experiment hook: ORBX_PYR_ROWS=2 / 8 forces one variant for every batch size
+static int pyr_rows_override()
+{
+    static const int v = [] { const char* e = getenv("ORBX_PYR_ROWS"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
 int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
     int launches = 0;
@@ -218,18 +236,24 @@ int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStr
             const dim3 block(64, 4);
             const dim3 grid(((L.w + 15) / 16 + block.x - 1) / block.x, (L.h + 2 * PYR_HALO + block.y - 1) / block.y, nframes);
             if ((D.in_pitch & 15) == 0 && ((uintptr_t)D.input & 15) == 0)
-                pyr_level0_kernel<true><<<grid, block, 0, s>>>(D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
-                                                               L.pyr, L.pitch, L.plane_bytes, L.w, L.h);
+                orbx_launch(pyr_level0_kernel<true>, grid, block, 0, s, D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
+                            L.pyr, L.pitch, L.plane_bytes, L.w, L.h, D.candcnt, G.nlevels);
             else
-                pyr_level0_kernel<false><<<grid, block, 0, s>>>(D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
-                                                                L.pyr, L.pitch, L.plane_bytes, L.w, L.h);
+                orbx_launch(pyr_level0_kernel<false>, grid, block, 0, s, D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
+                            L.pyr, L.pitch, L.plane_bytes, L.w, L.h, D.candcnt, G.nlevels);
         } else if (L.tapw) {
             const LevelGeom& P = G.L[l - 1];
             const dim3 block(64, 4);
-            const dim3 grid(((L.w + 3) / 4 + 2 + block.x - 1) / block.x,
-                            (L.h + 2 * PYR_HALO + block.y * PYRF_ROWS - 1) / (block.y * PYRF_ROWS), nframes);
-            pyr_resize_fast_kernel<<<grid, block, 0, s>>>(P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch, L.plane_bytes,
-                                                          L.w, L.h, L.tapw, L.tapy);
+            const int gx = ((L.w + 3) / 4 + 2 + block.x - 1) / block.x;
+            const int gy8 = (L.h + 2 * PYR_HALO + block.y * 8 - 1) / (block.y * 8);
+            if (pyr_rows_override() ? pyr_rows_override() == 8 : (long long)gx * gy8 * nframes >= 4 * 148) {
+                orbx_launch(pyr_resize_fast_kernel<8>, dim3(gx, gy8, nframes), block, 0, s, P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch,
+                                                                                  L.plane_bytes, L.w, L.h, L.tapw, L.tapy);
+            } else {
+                const int gy2 = (L.h + 2 * PYR_HALO + block.y * 2 - 1) / (block.y * 2);
+                orbx_launch(pyr_resize_fast_kernel<2>, dim3(gx, gy2, nframes), block, 0, s, P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch,
+                                                                                  L.plane_bytes, L.w, L.h, L.tapw, L.tapy);
+            }
         } else {
             // generic path (taps of a word do not fit 8 source bytes); it also writes the border
             const LevelGeom& P = G.L[l - 1];

@@ -24,6 +24,28 @@ def ComputeStereoMatches(extL, extR, mb: float, mbf: float, frame: int | None = 
     return uR, depth
 
 
+def ExtractStereo(extL, extR, imL: np.ndarray, imR: np.ndarray, mb: float, mbf: float):
+    """The stereo Frame constructor's hot part (src/Frame.cc:132-137 two ExtractORB threads + :154 ComputeStereoMatches)
+    as one call: returns (kpsL, descL, kpsR, descR, mvuRight, mvDepth)."""
+    import ctypes as C
+    for im in (imL, imR):
+        assert im.dtype == np.uint8 and im.ndim == 2 and im.strides[1] == 1, "CV_8UC1 expected"
+    assert imL.shape == imR.shape
+    rows, cols = imL.shape
+    cap = extL.max_keypoints(rows, cols)
+    kL = np.empty(cap, KP_DTYPE); dL = np.empty((cap, 32), np.uint8)
+    kR = np.empty(cap, KP_DTYPE); dR = np.empty((cap, 32), np.uint8)
+    uR = np.empty(cap, np.float32); depth = np.empty(cap, np.float32)
+    nL = C.c_int(0); nR = C.c_int(0)
+    check(binding.load().orbx_extract_stereo(extL.h, extR.h, imL.ctypes.data, imL.strides[0], imR.ctypes.data, imR.strides[0],
+                                             rows, cols, kL.ctypes.data, dL.ctypes.data, C.byref(nL),
+                                             kR.ctypes.data, dR.ctypes.data, C.byref(nR), cap, mb, mbf,
+                                             uR.ctypes.data, depth.ctypes.data))
+    extL._last_shape = extR._last_shape = (1, rows, cols)
+    a, b = nL.value, nR.value
+    return kL[:a].copy(), dL[:a].copy(), kR[:b].copy(), dR[:b].copy(), uR[:a].copy(), depth[:a].copy()
+
+
 def extL_shape(ext):
     return ext._last_shape[1:]
 

@@ -51,6 +51,46 @@ def test_stereo_single_frame_api(pkg, orc, oracle):
     XL.close(); XR.close()
 
 
+@pytest.mark.parametrize("cfg,seed,strided", [("C2", 5, False), ("C4", 9, True)])
+def test_extract_stereo_one_call(pkg, orc, oracle, cfg, seed, strided):
+    """orbx_extract_stereo (both eyes + ComputeStereoMatches in one call) == the oracle, and the handles are left in
+    the same state as after separate calls (a following ComputeStereoMatches gives the same answer).  Repeated on the
+    same handles with another pair; strided (non-continuous) input rows."""
+    c = pkg.synth.CONFIGS[cfg]
+    nf = c["nfeatures"]; mbf = c["mbf"]; mb = mbf / c["fx"]
+    XL, XR = pkg.ORBextractor(nf), pkg.ORBextractor(nf)
+    EL, ER = orc.Extractor(nf, oracle=oracle), orc.Extractor(nf, oracle=oracle)
+    for rep in range(2):
+        l, r = pkg.synth.synth_stereo_pair(c["rows"], c["cols"], seed + rep)
+        if strided:
+            big = np.zeros((2, c["rows"], c["cols"] + 24), np.uint8)
+            big[0, :, :c["cols"]] = l; big[1, :, :c["cols"]] = r
+            lv, rv = big[0, :, :c["cols"]], big[1, :, :c["cols"]]
+        else:
+            lv, rv = l, r
+        kl, dl, kr, dr, uR, depth = pkg.ExtractStereo(XL, XR, lv, rv, mb, mbf)
+        _, ko, do = EL(l); _, kro, dro = ER(r)
+        assert np.array_equal(kl, ko) and np.array_equal(dl, do) and np.array_equal(kr, kro) and np.array_equal(dr, dro)
+        u_o, d_o, _, _ = orc.stereo_match(EL, ER, ko, do, kro, dro, mb, mbf)
+        assert np.array_equal(uR, u_o) and np.array_equal(depth, d_o)
+        assert (u_o >= 0).sum() > 100
+        u2, d2 = pkg.ComputeStereoMatches(XL, XR, mb, mbf, frame=0)
+        assert np.array_equal(u2[:len(kl)], u_o) and np.array_equal(d2[:len(kl)], d_o)
+    XL.close(); XR.close()
+
+
+def test_extract_stereo_errors(pkg):
+    XL, XR = pkg.ORBextractor(500), pkg.ORBextractor(500)
+    im = pkg.synth.synth_frame(480, 752, 3)
+    with pytest.raises(pkg.OrbxError) as ei:
+        pkg.ExtractStereo(XL, XL, im, im, 0.11, 47.9)            # the same handle twice
+    assert ei.value.code == pkg.binding.ORBX_ERR_ARG
+    with pytest.raises(pkg.OrbxError) as ei:
+        pkg.ExtractStereo(XL, XR, im, im, 0.0, 47.9)             # mb must be positive
+    assert ei.value.code == pkg.binding.ORBX_ERR_ARG
+    XL.close(); XR.close()
+
+
 def test_stereo_state_errors(pkg):
     XL, XR = pkg.ORBextractor(1200), pkg.ORBextractor(1200)
     XL._last_shape = (1, 480, 752)

@@ -1,0 +1,40 @@
+#!/usr/bin/env python
+"""Single-frame latency probe: a handful of orbx_extract calls on ONE 752x480 frame (host in, host out).
+Run plain for wall-clock per call, or under `ncu --metrics gpu__time_duration.sum` for the per-kernel list
+of a one-frame call (grids are tiny there: launch latency and serial kernel tails dominate)."""
+import importlib, json, sys, time
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+pkg = importlib.import_module("orb-slam3_b200")
+
+
+def main():
+    reps = int(sys.argv[1]) if len(sys.argv) > 1 else 200
+    img = pkg.synth.synth_frame(480, 752, 7)
+    X = pkg.ORBextractor(1000)
+    for _ in range(5):
+        X(img, (0, 1000))
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter(); X(img, (0, 1000)); ts.append(time.perf_counter() - t0)
+    ts.sort()
+    print(json.dumps({"reps": reps, "median_ms": ts[len(ts) // 2] * 1e3, "p10_ms": ts[len(ts) // 10] * 1e3,
+                      "p90_ms": ts[(len(ts) * 9) // 10] * 1e3}))
+    X.close()
+    c = pkg.synth.CONFIGS["C2"]
+    l, r = pkg.synth.synth_stereo_pair(c["rows"], c["cols"], 7)
+    XL, XR = pkg.ORBextractor(c["nfeatures"]), pkg.ORBextractor(c["nfeatures"])
+    mb = c["mbf"] / c["fx"]
+    for _ in range(5):
+        pkg.ExtractStereo(XL, XR, l, r, mb, c["mbf"])
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter(); pkg.ExtractStereo(XL, XR, l, r, mb, c["mbf"]); ts.append(time.perf_counter() - t0)
+    ts.sort()
+    print(json.dumps({"stereo_one_call_median_ms": ts[len(ts) // 2] * 1e3, "p10_ms": ts[len(ts) // 10] * 1e3,
+                      "p90_ms": ts[(len(ts) * 9) // 10] * 1e3}))
+    XL.close(); XR.close()
+
+
+if __name__ == "__main__":
+    main()
