@@ -57,6 +57,7 @@ extern "C" int orbx_create(int nfeatures, float scaleFactor, int nlevels, int in
     e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr; e->d_st_rows = nullptr;
     e->h_counts = nullptr; e->h_counts_cap = 0;
     e->h_in = e->h_land = nullptr; e->h_in_cap = e->h_land_cap = 0;
+    e->graph_exec = nullptr; e->graph_launches = 0;
     e->d_map = nullptr; e->map_rows = e->map_cols = 0;
     e->d_raw = nullptr; e->raw_bytes = 0; e->raw_rows = e->raw_cols = e->raw_ch = e->raw_rgb = e->raw_pitch = 0;
     memset(&e->G, 0, sizeof(e->G)); memset(&e->D, 0, sizeof(e->D));
@@ -85,6 +86,7 @@ extern "C" int orbx_create(int nfeatures, float scaleFactor, int nlevels, int in
 static void free_device(orbx_extractor* e)
 {
     cudaSetDevice(e->device);
+    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }   // it holds the old pointers
     for (void* p : e->allocs) cudaFree(p);
     e->allocs.clear();
     e->reserved = false;
@@ -442,6 +444,38 @@ static int pinned_reserve(uint8_t** p, size_t* cap, size_t need)
     return 0;
 }
 
+// run_pipeline on frame slots [0, nframes) of the handle's stream through a cached CUDA graph
+static bool orbx_no_graph()
+{
+    static const bool v = [] { const char* c = getenv("ORBX_NO_GRAPH"); return c && atoi(c) != 0; }();
+    return v;
+}
+
+static int run_pipeline_graph(orbx_extractor* e, int nframes, int lap0, int lap1)
+{
+    if (e->profiling || orbx_no_graph()) return run_pipeline(e, 0, nframes, lap0, lap1, e->stream);
+    const int key[4] = {nframes, lap0, lap1, e->D.in_pitch};
+    if (!e->graph_exec || memcmp(key, e->graph_key, sizeof(key)) != 0) {
+        if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+        cudaGraph_t g = nullptr;
+        CUDA_TRY(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+        const long long l0 = e->launches;
+        const int r = run_pipeline(e, 0, nframes, lap0, lap1, e->stream);
+        const cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
+        e->graph_launches = (int)(e->launches - l0);
+        e->launches = l0;
+        if (r) { if (g) cudaGraphDestroy(g); return r; }
+        CUDA_TRY(ce);
+        const cudaError_t ci = cudaGraphInstantiate(&e->graph_exec, g, 0);
+        cudaGraphDestroy(g);
+        CUDA_TRY(ci);
+        memcpy(e->graph_key, key, sizeof(key));
+    }
+    CUDA_TRY(cudaGraphLaunch(e->graph_exec, e->stream));
+    e->launches += e->graph_launches;
+    return 0;
+}
+
 // stage the frames, upload, run the pipeline: all asynchronous on the handle's stream
 static int small_enqueue(orbx_extractor* e, int nframes, const uint8_t* imgs, size_t step, size_t frame_stride, int lap0, int lap1)
 {
@@ -465,7 +499,7 @@ static int small_enqueue(orbx_extractor* e, int nframes, const uint8_t* imgs, si
     }
     int r = upload_frames(e, 0, nframes, src_all, sstep, sstride, e->stream);
     if (r) return r;
-    r = run_pipeline(e, 0, nframes, lap0, lap1, e->stream);
+    r = run_pipeline_graph(e, nframes, lap0, lap1);
     if (r) return r;
     e->last_nframes = nframes;
     return 0;

@@ -23,6 +23,9 @@ struct orbx_extractor {
     int* h_counts; size_t h_counts_cap;    // pinned {nkp, mono} staging (a pageable target would make the D2H copy synchronous)
     // single-chunk calls (one frame / a few frames): pinned staging of the input frames and a pinned landing zone for
     // {keypoints, descriptors}: with pageable user buffers every cudaMemcpyAsync is a synchronous staged copy
+    // the pipeline of a single-chunk call as an instantiated CUDA graph (one graph launch instead of 14 kernel launches);
+    // valid for one {frames, lapping area, input pitch} and the current device buffers
+    cudaGraphExec_t graph_exec; int graph_key[4]; int graph_launches;
     uint8_t* h_in; size_t h_in_cap;
     uint8_t* h_land; size_t h_land_cap;
     bool reserved;

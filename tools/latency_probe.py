@@ -20,6 +20,16 @@ def main():
     ts.sort()
     print(json.dumps({"reps": reps, "median_ms": ts[len(ts) // 2] * 1e3, "p10_ms": ts[len(ts) // 10] * 1e3,
                       "p90_ms": ts[(len(ts) * 9) // 10] * 1e3}))
+    # host-side cost of queueing the launches vs the GPU time of the pipeline (frame already resident)
+    X.upload(img[None])
+    for _ in range(5):
+        X.run_resident((0, 1000)); X.sync()
+    enq, tot = [], []
+    for _ in range(reps):
+        t0 = time.perf_counter(); X.run_resident((0, 1000)); t1 = time.perf_counter(); X.sync(); t2 = time.perf_counter()
+        enq.append(t1 - t0); tot.append(t2 - t0)
+    enq.sort(); tot.sort()
+    print(json.dumps({"resident_enqueue_median_ms": enq[len(enq) // 2] * 1e3, "resident_total_median_ms": tot[len(tot) // 2] * 1e3}))
     X.close()
     c = pkg.synth.CONFIGS["C2"]
     l, r = pkg.synth.synth_stereo_pair(c["rows"], c["cols"], 7)
