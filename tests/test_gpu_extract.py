@@ -150,3 +150,26 @@ def test_clustered_keypoints_deep_quadtree(pkg, orc, oracle, npatch, patch, nf, 
         assert np.array_equal(sel_g, _cand_arr(sel_o)), f"quadtree selection level {l}"
     assert mg == mo and np.array_equal(kg, ko) and np.array_equal(dg, do)
     X.close()
+
+
+def test_single_frame_path_state_changes(pkg, orc, oracle):
+    """The one-chunk path caches a CUDA graph of the pipeline per {frames, lapping area, input pitch, buffers}: calls
+    that change any of them (other lapping area, strided rows, another image size = re-reserve, a batch call in
+    between, a two-frame call) must re-capture and still equal the oracle."""
+    X = pkg.ORBextractor(800)
+    E = orc.Extractor(800, oracle=oracle)
+    a = pkg.synth.synth_frame(480, 752, 61)
+    b = pkg.synth.synth_frame(376, 620, 62)
+    wide = np.zeros((480, 800), np.uint8); wide[:, :752] = pkg.synth.synth_frame(480, 752, 63)
+    seq = [(a, (0, 0)), (a, (200, 400)), (a, (200, 400)), (wide[:, :752], (200, 400)), (b, (0, 0)), (a, (0, 1000)), (b, (100, 300))]
+    for k, (img, lap) in enumerate(seq):
+        mg, kg, dg = X(img, lap)
+        mo, ko, do = E(np.ascontiguousarray(img), lap)
+        assert mg == mo and np.array_equal(kg, ko) and np.array_equal(dg, do), f"call {k}"
+        if k == 2:          # a batch in between (same size: the buffers stay, the resident frames change)
+            fr = np.stack([pkg.synth.synth_frame(480, 752, 70 + i) for i in range(3)])
+            mono, nkp, kps, desc = X.extract_batch(fr, (0, 0))
+            for i in range(3):
+                mo, ko, do = E(fr[i], (0, 0))
+                assert mono[i] == mo and np.array_equal(kps[i, :nkp[i]], ko) and np.array_equal(desc[i, :nkp[i]], do)
+    X.close()

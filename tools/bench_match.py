@@ -157,9 +157,11 @@ def latency_leg(pkg, reps=200, warm=20, device=0):
         t.start(); XL(L, (0, 0)); t.join()
         pkg.ComputeStereoMatches(XL, XR, mb, mbf, frame=0)
     ms_pair = wall(pair, reps, warm)
+    ms_one = wall(lambda: pkg.ExtractStereo(XL, XR, L, R, mb, mbf), reps, warm)
     XL.close(); XR.close()
-    return {"mono_frame_ms": ms_mono, "stereo_pair_ms": ms_pair,
-            "note": "single 752x480 frame through orbx_extract (host in/out); stereo pair = two extractor threads + orbx_stereo_match"}
+    return {"mono_frame_ms": ms_mono, "stereo_pair_ms": ms_pair, "stereo_pair_one_call_ms": ms_one,
+            "note": "single 752x480 frame through orbx_extract (host in/out); stereo pair = two extractor threads + "
+                    "orbx_stereo_match; one call = orbx_extract_stereo"}
 
 
 def main():
