@@ -155,10 +155,12 @@ pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long p
     const int nr = min(PYRF_ROWS, h + PYR_HALO - Y0);
 #pragma unroll 2
     for (int rr = 0; rr < nr; rr++) {
-        const ResizeTapY ty = tapy[ORBX_EDGE + Y0 + rr];       // the tap table is indexed by padded row
-        const HRow4 h0 = (ty.s0 == have) ? hl : pyr_hrow_fast(base + (long long)ty.s0 * ppitch, t, sel);
-        const HRow4 h1 = (ty.s1 == ty.s0) ? h0 : pyr_hrow_fast(base + (long long)ty.s1 * ppitch, t, sel);
-        const uint32_t b0 = (uint32_t)ty.b0, b1 = (uint32_t)ty.b1;
+        // the tap table is indexed by padded row; one 8-byte load (source rows and coefficients are non-negative)
+        const uint2 tv = __ldg(reinterpret_cast<const uint2*>(tapy + ORBX_EDGE + Y0) + rr);
+        const int s0 = (int)(tv.x & 0xFFFFu), s1 = (int)(tv.x >> 16);
+        const HRow4 h0 = (s0 == have) ? hl : pyr_hrow_fast(base + (uint32_t)(s0 * ppitch), t, sel);
+        const HRow4 h1 = (s1 == s0) ? h0 : pyr_hrow_fast(base + (uint32_t)(s1 * ppitch), t, sel);
+        const uint32_t b0 = tv.y & 0xFFFFu, b1 = tv.y >> 16;
         // ((b0*h0)>>16) + ((b1*h1)>>16) + 2 for two pixels per register: PRMT gathers the upper halves of
         // the products (each < 2^27), the sums stay below 2^11 per 16-bit lane; result byte = bits 2..9
         const uint32_t A01 = __byte_perm(b0 * (uint32_t)h0.h[0], b0 * (uint32_t)h0.h[1], 0x7632);
@@ -167,7 +169,7 @@ pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long p
         const uint32_t B23 = __byte_perm(b1 * (uint32_t)h1.h[2], b1 * (uint32_t)h1.h[3], 0x7632);
         const uint32_t S01 = A01 + B01 + 0x00020002u, S23 = A23 + B23 + 0x00020002u;
         dst[rr * pw] = __byte_perm(S01 >> 2, S23 >> 2, 0x6420);
-        hl = h1; have = ty.s1;
+        hl = h1; have = s1;
     }
 }
 
