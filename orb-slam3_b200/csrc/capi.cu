@@ -203,6 +203,15 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
         if (!rc) rc |= dev_alloc(e, &db, bands.size());
         if (!rc) CUDA_TRY(cudaMemcpy(db, bands.data(), bands.size() * sizeof(BandDesc), cudaMemcpyHostToDevice));
         D.bands = db;
+        std::vector<StripDesc> strips;
+        G.strip_ctas = rc ? 0 : fast_build_strips(G, &strips);
+        D.strips = nullptr;
+        if (G.strip_ctas > 0) {
+            StripDesc* ds = nullptr;
+            rc |= dev_alloc(e, &ds, strips.size());
+            if (!rc) CUDA_TRY(cudaMemcpy(ds, strips.data(), strips.size() * sizeof(StripDesc), cudaMemcpyHostToDevice));
+            D.strips = ds;
+        }
     }
     if (!rc) rc |= dev_alloc(e, &D.cand, B * G.cand_per_frame);
     if (!rc) rc |= dev_alloc(e, &D.candnode, B * G.cand_per_frame);

@@ -21,6 +21,7 @@
 // Integer work on the ALU pipe (~55 lane-ops per pixel); HBM traffic = one read of the level.
 #include "orbx_internal.h"
 #include <cstdlib>
+#include <algorithm>
 #include <vector>
 
 #define FAST_WARPS 4
@@ -325,6 +326,240 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Strip variant.  fast_band_kernel gives a warp a run of WHOLE cells (<= 128 px): at cell widths of 35-42 px that is
+// 3 cells = 27-32 of the 32 lanes, and some 2-cell items (18 lanes) - 74 % lane utilisation on 752x480.  Here a GROUP
+// of whole cells spans up to FAST_WARPS * 128 px and is cut into 128-px strips that ignore the cell boundaries, one
+// warp each, side by side in one CTA (88 % utilisation).  What crosses a strip edge goes through shared memory behind
+// two block barriers: the 3x3 NMS reads the edge column of the neighbouring warp's score tile, and the per-cell
+// "any survivor >= iniThFAST" flags of the retry rule (:1118-1125) are per CTA (one array per group, indexed by the
+// cell column), set by every lane for its own pixels.  Phases A / B1 are those of fast_band_kernel.
+// ------------------------------------------------------------------------------------------------
+#define FS_MAXCOLS 128                 // cell columns per level the flag arrays hold
+
+__global__ void __launch_bounds__(FAST_THREADS, FAST_MINBLOCKS)
+fast_strip_kernel(FrameGeom G, DevBuffers D)
+{
+    extern __shared__ uint32_t s_dyn[];               // per warp: S words [ihmax + 2][32], then the lane-private survivor lists
+    __shared__ uint32_t s_ini[FAST_WARPS][FS_MAXCOLS];
+    orbx_pdl_prologue();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const StripDesc sd = D.strips[blockIdx.x * FAST_WARPS + warp];
+    const bool live = sd.lvl >= 0;
+    const int f = blockIdx.y;
+    const LevelGeom& L = G.L[live ? sd.lvl : 0];
+    const int Hr = L.maxBY - ORBX_MINB, Wr = L.maxBX - ORBX_MINB;
+    const int ys = ORBX_MINB + sd.ci * L.hCell + 3;
+    const int ye = ORBX_MINB + min(sd.ci * L.hCell + L.hCell + 6, Hr) - 3;
+    const int xs = sd.gxs, xe = sd.gxe;               // the group's scored columns
+    const int ih = live ? ye - ys : 0;
+    const int xa = (xs & ~3) + 128 * sd.k;            // word aligned (XOFF and the pitch are multiples of 4)
+    const int nw = live ? min(32, (xe - xa + 3) >> 2) : 1;
+    const bool active = live && lane < nw;
+    const int wi = lane < nw ? lane : nw - 1;
+    const int x = xa + 4 * wi;
+    uint32_t* s_tile = s_dyn + warp * G.fast_warp_words;
+#pragma unroll
+    for (int c = lane; c < FS_MAXCOLS; c += 32) s_ini[warp][c] = 0;
+
+    // ---------------- phase A: score tile ----------------
+    if (live) {
+        const uint32_t* p0 = reinterpret_cast<const uint32_t*>(
+            L.pyr + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + ys - 3) * L.pitch + ORBX_XOFF + x);
+        const int pw = L.pitch >> 2;
+        const int klast = ih + 5;
+        uint32_t W[7][8];
+#pragma unroll
+        for (int i = 0; i < 6; i++) { const uint32_t* p = p0 + i * pw; fast_fill_row(W[i], __ldg(p - 1), __ldg(p), __ldg(p + 1)); }
+        uint32_t pf[7][3];
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            const uint32_t* pn = p0 + min(6 + i, klast) * pw;
+            pf[(6 + i) % 7][0] = __ldg(pn - 1); pf[(6 + i) % 7][1] = __ldg(pn); pf[(6 + i) % 7][2] = __ldg(pn + 1);
+        }
+        uint32_t* out = s_tile + wi;
+#define FAST_STEP(PH)                                                                              \
+        if (rb + PH < ih) {                                                                        \
+            const int r = rb + PH;                                                                 \
+            fast_fill_row(W[(PH + 6) % 7], pf[(PH + 6) % 7][0], pf[(PH + 6) % 7][1], pf[(PH + 6) % 7][2]); \
+            { const uint32_t* pn = p0 + min(r + 9, klast) * pw;                                    \
+              pf[(PH + 9) % 7][0] = __ldg(pn - 1); pf[(PH + 9) % 7][1] = __ldg(pn); pf[(PH + 9) % 7][2] = __ldg(pn + 1); } \
+            const uint32_t sw = fast_score_word<PH>(W);                                            \
+            if (active) out[r * 32] = sw;                                                          \
+        }
+#pragma unroll 1
+        for (int rb = 0; rb < ih; rb += 7) {
+            FAST_STEP(0) FAST_STEP(1) FAST_STEP(2) FAST_STEP(3) FAST_STEP(4) FAST_STEP(5) FAST_STEP(6)
+        }
+#undef FAST_STEP
+        // two zero rows under the tile: the NMS loop below runs whole 3-row steps without a row guard
+        s_tile[ih * 32 + lane] = 0;
+        s_tile[(ih + 1) * 32 + lane] = 0;
+    }
+    __syncthreads();                                  // every tile of the CTA is complete, the flags are cleared
+
+    // ---------------- phase B1: 3x3 NMS inside each cell, survivors appended to the list ----------------
+    int cq[4];                                        // cell column of each of the thread's 4 pixels
+    uint32_t ML_e = 0, MR_e = 0, ML_o = 0, MR_o = 0, V_e = 0, V_o = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const int xp = x + q;
+        const bool valid = active && xp >= xs && xp < xe;
+        const int X3 = xp - ORBX_MINB - 3;
+        const int j = valid ? X3 / L.wCell : 0;
+        const int xin = X3 - j * L.wCell;
+        const int cend = ORBX_MINB + min(j * L.wCell + L.wCell + 6, Wr) - 3;      // end of cell j's interior
+        const bool lok = valid && xin > 0, rok = valid && xp + 1 < cend;
+        cq[q] = j;
+        const uint32_t ln = (q & 2) ? 0xFFFF0000u : 0x0000FFFFu;
+        if (q & 1) { if (lok) ML_o |= ln; if (rok) MR_o |= ln; if (valid) V_o |= ln & 0xFF00FF00u; }
+        else       { if (lok) ML_e |= ln; if (rok) MR_e |= ln; if (valid) V_e |= ln & 0xFF00FF00u; }
+    }
+    const int iniTh = G.iniTh, minTh = min(G.minTh, G.iniTh);
+    const uint32_t thr = (uint32_t)(((minTh - 1) << 8) | 0xFF) * 0x00010001u;
+    const uint32_t* mylist = s_tile + (ih + 2) * 32 + lane;
+    int cnt = 0;
+    if (live) {
+        // across a strip edge the neighbour column is word 31 / word 0 of the adjacent warp's tile (same cell row, same
+        // ih); at the group's ends it lies outside every cell interior and is masked: those lanes re-read their own word
+        const uint32_t* pm = s_tile + wi;
+        const uint32_t* pl = wi > 0 ? pm - 1 : (sd.k > 0 ? s_tile - G.fast_warp_words + 31 : pm);
+        const uint32_t* pr = wi + 1 < nw ? pm + 1 : ((wi == 31 && sd.k + 1 < sd.nstrips) ? s_tile + G.fast_warp_words : pm);
+        uint32_t R[3][4];
+        const uint32_t wa0 = (uint32_t)__cvta_generic_to_shared(mylist);
+        uint32_t wa = wa0, rr = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) R[0][k] = 0;
+        nms_fill(R[1], pl[0], pm[0], pr[0]);
+#define NMS_STEP(PH)                                                                                        \
+        {                                                                                                   \
+            nms_fill(R[(PH + 2) % 3], pl[(PH + 1) * 32], pm[(PH + 1) * 32], pr[(PH + 1) * 32]);             \
+            uint32_t te, to;                                                                                \
+            nms_row<PH>(R, thr, ML_e, MR_e, ML_o, MR_o, V_e, V_o, te, to);                                  \
+            const uint32_t fl = __vminu2(te, 0x00010001u) + 2u * __vminu2(to, 0x00010001u);                 \
+            list_push(wa, fl, fl | (rr + PH * 256u));                                                       \
+        }
+#pragma unroll 1
+        for (int rb = 0; rb < ih; rb += 3) {
+            NMS_STEP(0) NMS_STEP(1) NMS_STEP(2)
+            pl += 96; pm += 96; pr += 96; rr += 768u;
+        }
+#undef NMS_STEP
+        cnt = (int)((wa - wa0) >> 7);
+    }
+    __syncwarp();
+
+    // ---------------- phase B2: per-cell retry rule (:1118-1125) and emission ----------------
+    const int xrel = xa - ORBX_MINB + 4 * wi, yrel = ys - ORBX_MINB;
+    const uint32_t* srow = s_tile + wi;
+    uint32_t* ini = s_ini[live ? sd.first : 0];       // the group's flags: cell column -> a survivor >= iniTh exists
+    for (int i = 0; i < cnt; i++) {
+        const uint32_t e = mylist[i * 32];
+        const uint32_t sw = srow[((e >> 8) & 127u) * 32];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint32_t bit = (e >> ((q & 1) + (q & 2) * 8)) & 1u;
+            if (bit && ((sw >> (8 * q)) & 255u) >= (uint32_t)iniTh) ini[cq[q]] = 1u;
+        }
+    }
+    __syncthreads();                                  // the flags of every group of the CTA are final
+    if (!live) return;
+    uint32_t zq = 0;                                  // bit q: the cell of pixel q has no survivor >= iniTh
+#pragma unroll
+    for (int q = 0; q < 4; q++) if (ini[cq[q]] == 0u) zq |= 1u << q;
+    int mine = 0;
+    for (int i = 0; i < cnt; i++) {
+        const uint32_t e = mylist[i * 32];
+        const uint32_t sw = srow[((e >> 8) & 127u) * 32];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint32_t bit = (e >> ((q & 1) + (q & 2) * 8)) & 1u;
+            mine += (int)(bit & ((((sw >> (8 * q)) & 255u) >= (uint32_t)iniTh ? 1u : 0u) | (zq >> q)));
+        }
+    }
+    const int total = __reduce_add_sync(0xffffffffu, mine);
+    if (total == 0) return;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(&D.candcnt[f * G.nlevels + sd.lvl], total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    uint32_t* out = D.cand + (long long)f * G.cand_per_frame + L.cand_base + base;
+    const uint32_t lt = (1u << lane) - 1u;
+    const int maxcnt = __reduce_max_sync(0xffffffffu, cnt);
+    for (int i = 0; i < maxcnt; i++) {
+        const uint32_t e = i < cnt ? mylist[i * 32] : 0u;
+        const uint32_t r = (e >> 8) & 127u;
+        const uint32_t sw = srow[r * 32];
+        bool em[4];
+        int c = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint32_t sc = (sw >> (8 * q)) & 255u;
+            const bool bit = (e >> ((q & 1) + (q & 2) * 8)) & 1u;
+            em[q] = bit && (sc >= (uint32_t)iniTh || ((zq >> q) & 1u));
+            c += em[q];
+        }
+        const uint32_t b1 = __ballot_sync(0xffffffffu, c >= 1), b2 = __ballot_sync(0xffffffffu, c >= 2),
+                       b3 = __ballot_sync(0xffffffffu, c >= 3);
+        int pos = __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+            if (em[q]) out[pos++] = MAKE_KEY(xrel + q, yrel + r, (sw >> (8 * q)) & 255u);
+        out += __popc(b1) + __popc(b2) + __popc(b3);
+    }
+}
+
+// Work items of the strip kernel: per level and cell row, greedy runs of whole valid cells spanning <= FAST_WARPS * 128
+// px ("groups"), each cut into 128-px strips; the groups are packed into CTAs of FAST_WARPS warps (largest first, first
+// fit).  Returns the CTAs per frame; 0 when the geometry does not fit (the band kernel serves it then).
+int fast_build_strips(const FrameGeom& G, std::vector<StripDesc>* out)
+{
+    struct Group { int lvl, ci, xs, xe, n; };
+    std::vector<Group> groups;
+    out->clear();
+    for (int l = 0; l < G.nlevels; l++) {
+        const LevelGeom& L = G.L[l];
+        const int Wr = L.maxBX - ORBX_MINB, Hr = L.maxBY - ORBX_MINB;
+        if (L.nCols > FS_MAXCOLS || L.maxBX > 32000) return 0;
+        int ncv = 0, nrv = 0;
+        while (ncv < L.nCols && ncv * L.wCell <= Wr - 7) ncv++;
+        while (nrv < L.nRows && nrv * L.hCell <= Hr - 7) nrv++;
+        auto xs_of = [&](int j0) { return ORBX_MINB + j0 * L.wCell + 3; };
+        auto xe_of = [&](int j1) { return ORBX_MINB + ((j1 - 1) * L.wCell + L.wCell + 6 < Wr ? (j1 - 1) * L.wCell + L.wCell + 6 : Wr) - 3; };
+        auto span = [&](int j0, int j1) { return xe_of(j1) - (xs_of(j0) & ~3); };
+        for (int i = 0; i < nrv; i++) {
+            int j0 = 0;
+            while (j0 < ncv) {
+                int j1 = j0 + 1;
+                while (j1 < ncv && span(j0, j1 + 1) <= FAST_WARPS * 128) j1++;
+                const int sp = span(j0, j1);
+                if (sp > FAST_WARPS * 128 || sp <= 0) return 0;
+                groups.push_back({l, i, xs_of(j0), xe_of(j1), (sp + 127) / 128});
+                j0 = j1;
+            }
+        }
+    }
+    std::stable_sort(groups.begin(), groups.end(), [](const Group& a, const Group& b) { return a.n > b.n; });
+    std::vector<int> used;                         // warps taken per CTA
+    std::vector<std::vector<StripDesc>> ctas;
+    for (const Group& g : groups) {
+        size_t c = 0;
+        while (c < used.size() && used[c] + g.n > FAST_WARPS) c++;
+        if (c == used.size()) { used.push_back(0); ctas.emplace_back(); }
+        for (int k = 0; k < g.n; k++) {
+            StripDesc sd; sd.lvl = (short)g.lvl; sd.ci = (short)g.ci; sd.gxs = (short)g.xs; sd.gxe = (short)g.xe;
+            sd.k = (short)k; sd.first = (short)used[c]; sd.nstrips = (short)g.n; sd.pad = 0;
+            ctas[c].push_back(sd);
+        }
+        used[c] += g.n;
+    }
+    for (auto& v : ctas) {
+        StripDesc none = {}; none.lvl = -1;
+        while ((int)v.size() < FAST_WARPS) v.push_back(none);
+        out->insert(out->end(), v.begin(), v.end());
+    }
+    return (int)ctas.size();
+}
+
 // FAST work items of one frame: per level and cell row, runs of whole cells spanning <= 128 px (one warp,
 // 4 px per lane).  Cells the reference skips (:1085,1102: iniX >= maxBorderX-6, iniY >= maxBorderY-3, or
 // narrower than the 7-px FAST footprint) are left out.  Returns the kernel's dynamic shared memory and
@@ -369,6 +604,13 @@ int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream
     if (pad > smem) smem = pad;
     if (smem > 48 * 1024)
         cudaFuncSetAttribute(fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    static const bool strips = [] { const char* e = getenv("ORBX_FAST_STRIPS"); return !e || atoi(e) != 0; }();
+    if (strips && G.strip_ctas > 0) {
+        if (smem > 48 * 1024)
+            cudaFuncSetAttribute(fast_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        orbx_launch(fast_strip_kernel, dim3(G.strip_ctas, nframes), dim3(FAST_THREADS), (size_t)smem, s, G, D);
+        return 1;
+    }
     const dim3 grid((G.bands_per_frame + FAST_WARPS - 1) / FAST_WARPS, nframes);
     orbx_launch(fast_band_kernel, grid, dim3(FAST_THREADS), (size_t)smem, s, G, D);
     return 1;

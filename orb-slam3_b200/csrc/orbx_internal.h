@@ -81,8 +81,14 @@ struct LevelGeom {
 // one FAST work item (one warp): the interiors of cells [cj0, cj1) of cell row ci of level lvl (<= 128 px wide)
 struct BandDesc { short lvl, ci, cj0, cj1; };
 
+// one FAST work item of the strip kernel (one warp): 128-px strip k of a GROUP = the interiors of a run of whole cells
+// of cell row ci, [gxs, gxe) in level coordinates; the nstrips warps of a group sit side by side in one CTA starting
+// at warp `first`.  lvl < 0: empty slot.
+struct StripDesc { short lvl, ci, gxs, gxe, k, first, nstrips, pad; };
+
 struct FrameGeom {
     int nlevels;
+    int strip_ctas;           // CTAs per frame of fast_strip_kernel (0: use fast_band_kernel)
     int bands_per_frame;      // FAST band segments per frame (DevBuffers::bands)
     int fast_smem;            // dynamic shared memory of fast_band_kernel (bytes)
     int fast_warp_words;      // ... of which 32-bit words per warp
@@ -103,6 +109,7 @@ struct DevBuffers {
     int in_pitch;             // row stride of the frames currently resident (the caller's stride when packed)
     int in_pitch_cap;         // largest row stride the staging buffer is sized for
     const BandDesc* bands;    // [bands_per_frame] FAST work units (same for every frame)
+    const StripDesc* strips;  // [strip_ctas * 4] work units of the strip kernel
     uint32_t* cand;           // [batch][cand_per_frame]
     uint32_t* candnode;       // [batch][cand_per_frame]  quadtree scratch: node of each candidate
     int* nodetab;             // quadtree scratch: node tables
@@ -129,6 +136,7 @@ int launch_describe(const FrameGeom& G, const DevBuffers& D, int nframes, cudaSt
 #ifdef __cplusplus
 #include <vector>
 int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out, int* warp_words);   // returns the kernel's dynamic smem bytes
+int fast_build_strips(const FrameGeom& G, std::vector<StripDesc>* out);                   // returns the CTAs per frame, 0 if unsupported
 #endif
 size_t octree_nodetab_ints(const FrameGeom& G);   // ints of node scratch per frame
 void octree_assign_node_offsets(FrameGeom& G);
