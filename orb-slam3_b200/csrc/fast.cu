@@ -606,7 +606,7 @@ int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream
         cudaFuncSetAttribute(fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     static const bool strips = [] { const char* e = getenv("ORBX_FAST_STRIPS"); return !e || atoi(e) != 0; }();
     if (strips && G.strip_ctas > 0) {
-        if (smem > 48 * 1024)
+        if (smem + (int)sizeof(uint32_t) * FAST_WARPS * FS_MAXCOLS > 48 * 1024)      // static flags + dynamic tiles
             cudaFuncSetAttribute(fast_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         orbx_launch(fast_strip_kernel, dim3(G.strip_ctas, nframes), dim3(FAST_THREADS), (size_t)smem, s, G, D);
         return 1;

@@ -173,3 +173,26 @@ def test_single_frame_path_state_changes(pkg, orc, oracle):
                 mo, ko, do = E(fr[i], (0, 0))
                 assert mono[i] == mo and np.array_equal(kps[i, :nkp[i]], ko) and np.array_equal(desc[i, :nkp[i]], do)
     X.close()
+
+
+@pytest.mark.parametrize("cfg", ["C3", "C4"])
+def test_fresh_process_per_geometry(cfg):
+    """Function attributes (opt-in shared memory) stick to the process: a geometry whose shared-memory need sits just
+    under 48 KB only worked when another geometry had raised the limit before.  Each config in its own process."""
+    import subprocess, sys, os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import importlib, sys, numpy as np\n"
+        f"sys.path.insert(0, {root!r})\n"
+        "pkg = importlib.import_module('orb-slam3_b200')\n"
+        "from oracle import orc_py as orc\n"
+        f"c = pkg.synth.CONFIGS[{cfg!r}]\n"
+        "fr = np.stack([pkg.synth.synth_frame(c['rows'], c['cols'], 90 + i) for i in range(8)])\n"
+        "X = pkg.ORBextractor(c['nfeatures']); E = orc.Extractor(c['nfeatures'])\n"
+        "mono, nkp, kps, desc = X.extract_batch(fr, (0, 0))\n"
+        "for i in (0, 7):\n"
+        "    mo, ko, do = E(fr[i], (0, 0))\n"
+        "    assert len(ko) > 100 and np.array_equal(kps[i, :nkp[i]], ko) and np.array_equal(desc[i, :nkp[i]], do)\n"
+        "print('ok')\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
