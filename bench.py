@@ -38,7 +38,7 @@ def level_dims(rows, cols, isf):
     return [(int(np.rint(np.float32(rows) * s)), int(np.rint(np.float32(cols) * s))) for s in isf]
 
 
-STAGE_KERNEL = {"pyramid": "pyr_resize_fast_kernel", "fast": "fast_band_kernel", "blur": "blur_kernel"}
+STAGE_KERNEL = {"pyramid": "pyr_resize_fast_kernel", "fast": "fast_strip_kernel", "blur": "blur_kernel"}
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 
@@ -58,7 +58,7 @@ def profiled_traffic(stage, frames_per_launch):
             continue
         tot = 0.0; frames = None
         for r in rows[1:]:
-            if r[1].strip() == STAGE_KERNEL[stage]:
+            if STAGE_KERNEL[stage] in r[1]:                 # template instances carry "void ...<...>" around the name
                 tot += sum(float(r[i]) * u for i, u in cols.values())
                 g = [int(x) for x in r[2].strip("()").split(",")]
                 frames = max(g[1], g[2]) if stage != "pyramid" else g[2]
