@@ -261,7 +261,7 @@ int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStr
                             L.pyr, L.pitch, L.plane_bytes, L.w, L.h, D.candcnt, G.nlevels);
         } else if (L.tapw) {
             const LevelGeom& P = G.L[l - 1];
-            const dim3 block(64, 4);
+            const dim3 block(32, 8);        // one warp per 32 words: the partial warp at the right edge wastes less than a 64-wide block
             const int gx = ((L.w + 3) / 4 + 2 + block.x - 1) / block.x;
             const int gy8 = (L.h + 2 * PYR_HALO + block.y * 8 - 1) / (block.y * 8);
             if (pyr_rows_override() ? pyr_rows_override() == 8 : (long long)gx * gy8 * nframes >= 4 * 148) {
