@@ -79,6 +79,26 @@ def test_extract_stereo_one_call(pkg, orc, oracle, cfg, seed, strided):
     XL.close(); XR.close()
 
 
+def test_extract_stereo_flat_frames(pkg, orc, oracle):
+    """No keypoints in one or both eyes (src/Frame.cc:145 returns before ComputeStereoMatches): empty results, no
+    error, and the handles still work afterwards."""
+    c = pkg.synth.CONFIGS["C2"]
+    mbf = c["mbf"]; mb = mbf / c["fx"]
+    flat = np.full((c["rows"], c["cols"]), 77, np.uint8)
+    l, r = pkg.synth.synth_stereo_pair(c["rows"], c["cols"], 15)
+    XL, XR = pkg.ORBextractor(600), pkg.ORBextractor(600)
+    kl, dl, kr, dr, uR, depth = pkg.ExtractStereo(XL, XR, flat, flat, mb, mbf)
+    assert len(kl) == 0 and len(kr) == 0 and len(uR) == 0 and dl.shape == (0, 32)
+    kl, dl, kr, dr, uR, depth = pkg.ExtractStereo(XL, XR, l, flat, mb, mbf)        # nothing to match against
+    assert len(kl) > 100 and len(kr) == 0 and np.all(uR == -1) and np.all(depth == -1)
+    kl, dl, kr, dr, uR, depth = pkg.ExtractStereo(XL, XR, l, r, mb, mbf)
+    EL, ER = orc.Extractor(600, oracle=oracle), orc.Extractor(600, oracle=oracle)
+    _, ko, do = EL(l); _, kro, dro = ER(r)
+    u_o, d_o, _, _ = orc.stereo_match(EL, ER, ko, do, kro, dro, mb, mbf)
+    assert np.array_equal(kl, ko) and np.array_equal(uR, u_o) and np.array_equal(depth, d_o)
+    XL.close(); XR.close()
+
+
 def test_extract_stereo_errors(pkg):
     XL, XR = pkg.ORBextractor(500), pkg.ORBextractor(500)
     im = pkg.synth.synth_frame(480, 752, 3)
