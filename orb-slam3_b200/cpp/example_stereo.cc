@@ -3,6 +3,7 @@
 //   g++ -O2 -std=c++17 orb-slam3_b200/cpp/example_stereo.cc -Lorb-slam3_b200 -lorbx -Wl,-rpath,$PWD/orb-slam3_b200 -o example_stereo
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
 #include <thread>
 
 #include "ORBmatcher.h"
@@ -96,7 +97,32 @@ int main()
         const int nBoW = matcherBoW.SearchByBoW(K1, K2, false, bowMatches);
         std::printf("second view: %zu kps; SearchForInitialization %d, SearchByProjection(Frame,Frame) %d, SearchForTriangulation %d, "
                     "SearchByBoW %d\n", mvKeys2.size(), nIni, nProj, nTri, nBoW);
-        return (matched > 0 && nIni > 0 && nProj > 0 && nTri > 0 && nBoW > 0 && (int)vMatchedPairs.size() == nTri) ? 0 : 2;
+        // --- the same stereo frame through the one-call entry: identical results ---
+        std::vector<cv::KeyPoint> k1, k2;
+        cv::Mat d1, d2;
+        std::vector<float> u1, z1;
+        ORBmatcherGPU::ExtractStereo(left, right, imLeft, imRight, k1, d1, k2, d2, mb, mbf, u1, z1);
+        bool same = k1.size() == mvKeys.size() && k2.size() == mvKeysRight.size() && u1 == mvuRight && z1 == mvDepth;
+        for (size_t i = 0; same && i < k1.size(); i++)
+            same = std::memcmp(&k1[i], &mvKeys[i], sizeof(cv::KeyPoint)) == 0 && std::memcmp(d1.ptr((int)i), mDescriptors.ptr((int)i), 32) == 0;
+        // --- what the C++ caller waits per frame (host cv::Mat in, host vectors out) ---
+        auto ms = [](auto&& fn, int reps) {
+            for (int i = 0; i < 10; i++) fn();
+            const auto t0 = std::chrono::steady_clock::now();
+            for (int i = 0; i < reps; i++) fn();
+            return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() / reps;
+        };
+        const double tMono = ms([&] { left(imLeft, cv::Mat(), mvKeys, mDescriptors, vLapping); }, 200);
+        const double tThreads = ms([&] {
+            std::thread a([&] { left(imLeft, cv::Mat(), mvKeys, mDescriptors, vLapping); });
+            std::thread b([&] { right(imRight, cv::Mat(), mvKeysRight, mDescriptorsRight, vLapping); });
+            a.join(); b.join();
+            ORBmatcherGPU::ComputeStereoMatches(left, right, (int)mvKeys.size(), mb, mbf, mvuRight, mvDepth);
+        }, 200);
+        const double tOne = ms([&] { ORBmatcherGPU::ExtractStereo(left, right, imLeft, imRight, k1, d1, k2, d2, mb, mbf, u1, z1); }, 200);
+        std::printf("one-call stereo identical: %s; latency per frame: mono operator() %.3f ms, stereo (two threads + "
+                    "ComputeStereoMatches) %.3f ms, stereo (ExtractStereo) %.3f ms\n", same ? "yes" : "NO", tMono, tThreads, tOne);
+        return (matched > 0 && nIni > 0 && nProj > 0 && nTri > 0 && nBoW > 0 && (int)vMatchedPairs.size() == nTri && same) ? 0 : 2;
     } catch (const std::exception& e) {
         std::fprintf(stderr, "error: %s\n", e.what());
         return 1;

@@ -33,3 +33,5 @@ def test_shim_example_runs_on_gpu(tmp_path, built_lib):
     r = subprocess.run([str(exe)], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "stereo matches" in r.stdout and "SearchForTriangulation" in r.stdout
+    assert "one-call stereo identical: yes" in r.stdout
+    print(r.stdout)
