@@ -57,7 +57,7 @@ extern "C" int orbx_create(int nfeatures, float scaleFactor, int nlevels, int in
     e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr; e->d_st_rows = nullptr;
     e->h_counts = nullptr; e->h_counts_cap = 0;
     e->h_in = e->h_land = nullptr; e->h_in_cap = e->h_land_cap = 0;
-    e->graph_exec = nullptr; e->graph_launches = 0;
+    e->graph_exec = nullptr; e->graph_launches = 0; e->dag_ready = false;
     e->d_map = nullptr; e->map_rows = e->map_cols = 0;
     e->d_raw = nullptr; e->raw_bytes = 0; e->raw_rows = e->raw_cols = e->raw_ch = e->raw_rgb = e->raw_pitch = 0;
     memset(&e->G, 0, sizeof(e->G)); memset(&e->D, 0, sizeof(e->D));
@@ -109,6 +109,8 @@ extern "C" void orbx_destroy(orbx_extractor* e)
     for (cudaEvent_t ev : e->ev_down) cudaEventDestroy(ev);
     for (int i = 0; i < ORBX_NCSTREAMS; i++) { cudaStreamDestroy(e->cstream[i]); cudaEventDestroy(e->ev_join[i]); }
     cudaEventDestroy(e->ev_fork);
+    if (e->dag_ready)
+        for (int l = 0; l < ORBX_MAX_LEVELS; l++) { cudaStreamDestroy(e->dag_stream[l]); cudaEventDestroy(e->dag_ev[l]); cudaEventDestroy(e->dag_done[l]); }
     if (e->h_counts) cudaFreeHost(e->h_counts);
     if (e->h_in) cudaFreeHost(e->h_in);
     if (e->h_land) cudaFreeHost(e->h_land);
@@ -204,7 +206,7 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
         if (!rc) CUDA_TRY(cudaMemcpy(db, bands.data(), bands.size() * sizeof(BandDesc), cudaMemcpyHostToDevice));
         D.bands = db;
         std::vector<StripDesc> strips;
-        G.strip_ctas = rc ? 0 : fast_build_strips(G, &strips);
+        G.strip_ctas = rc ? 0 : fast_build_strips(G, &strips, G.strip_lvl_cta);
         D.strips = nullptr;
         if (G.strip_ctas > 0) {
             StripDesc* ds = nullptr;
@@ -460,6 +462,37 @@ static bool orbx_no_graph()
     return v;
 }
 
+// The pipeline of frame slots [0, nframes) as a DAG (only ever CAPTURED into a graph): the levels' FAST + quadtree
+// kernels hang off the pyramid chain level by level on their own streams instead of waiting for the whole pyramid, the
+// blur runs beside them.  Critical path of one 752x480 frame: level 0 -> FAST(0) -> quadtree(0) -> assemble -> describe.
+static int run_pipeline_dag(orbx_extractor* e, int nframes, int lap0, int lap1)
+{
+    FrameGeom G; DevBuffers D;
+    slot_view(e, 0, &G, &D);
+    cudaStream_t s = e->stream;
+    for (int l = 0; l < G.nlevels; l++) {
+        e->launches += launch_pyramid_level(G, D, nframes, l, s);
+        CUDA_TRY(cudaEventRecord(e->dag_ev[l], s));
+        cudaStream_t b = e->dag_stream[l];
+        CUDA_TRY(cudaStreamWaitEvent(b, e->dag_ev[l], 0));
+        e->launches += launch_fast(G, D, nframes, b, l);
+        e->launches += launch_octree(G, D, nframes, b, l);
+        CUDA_TRY(cudaEventRecord(e->dag_done[l], b));
+    }
+    e->launches += launch_blur(G, D, nframes, s);
+    for (int l = 0; l < G.nlevels; l++) CUDA_TRY(cudaStreamWaitEvent(s, e->dag_done[l], 0));
+    e->launches += launch_assemble(G, D, nframes, lap0, lap1, s);
+    e->launches += launch_describe(G, D, nframes, s);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+static bool orbx_no_dag()
+{
+    static const bool v = [] { const char* c = getenv("ORBX_NO_DAG"); return c && atoi(c) != 0; }();
+    return v;
+}
+
 static int run_pipeline_graph(orbx_extractor* e, int nframes, int lap0, int lap1)
 {
     if (e->profiling || orbx_no_graph()) return run_pipeline(e, 0, nframes, lap0, lap1, e->stream);
@@ -467,9 +500,18 @@ static int run_pipeline_graph(orbx_extractor* e, int nframes, int lap0, int lap1
     if (!e->graph_exec || memcmp(key, e->graph_key, sizeof(key)) != 0) {
         if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
         cudaGraph_t g = nullptr;
+        const bool dag = fast_per_level(e->G) && !orbx_no_dag() && nframes * e->G.nlevels <= 64;
+        if (dag && !e->dag_ready) {                       // branch streams / events exist before the capture starts
+            for (int l = 0; l < ORBX_MAX_LEVELS; l++) {
+                CUDA_TRY(cudaStreamCreateWithFlags(&e->dag_stream[l], cudaStreamNonBlocking));
+                CUDA_TRY(cudaEventCreateWithFlags(&e->dag_ev[l], cudaEventDisableTiming));
+                CUDA_TRY(cudaEventCreateWithFlags(&e->dag_done[l], cudaEventDisableTiming));
+            }
+            e->dag_ready = true;
+        }
         CUDA_TRY(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
         const long long l0 = e->launches;
-        const int r = run_pipeline(e, 0, nframes, lap0, lap1, e->stream);
+        const int r = dag ? run_pipeline_dag(e, nframes, lap0, lap1) : run_pipeline(e, 0, nframes, lap0, lap1, e->stream);
         const cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
         e->graph_launches = (int)(e->launches - l0);
         e->launches = l0;

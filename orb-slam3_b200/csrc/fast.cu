@@ -338,13 +338,13 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
 #define FS_MAXCOLS 128                 // cell columns per level the flag arrays hold
 
 __global__ void __launch_bounds__(FAST_THREADS, FAST_MINBLOCKS)
-fast_strip_kernel(FrameGeom G, DevBuffers D)
+fast_strip_kernel(FrameGeom G, DevBuffers D, int cta0)
 {
     extern __shared__ uint32_t s_dyn[];               // per warp: S words [ihmax + 2][32], then the lane-private survivor lists
     __shared__ uint32_t s_ini[FAST_WARPS][FS_MAXCOLS];
     orbx_pdl_prologue();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const StripDesc sd = D.strips[blockIdx.x * FAST_WARPS + warp];
+    const StripDesc sd = D.strips[(cta0 + blockIdx.x) * FAST_WARPS + warp];
     const bool live = sd.lvl >= 0;
     const int f = blockIdx.y;
     const LevelGeom& L = G.L[live ? sd.lvl : 0];
@@ -511,7 +511,7 @@ fast_strip_kernel(FrameGeom G, DevBuffers D)
 // Work items of the strip kernel: per level and cell row, greedy runs of whole valid cells spanning <= FAST_WARPS * 128
 // px ("groups"), each cut into 128-px strips; the groups are packed into CTAs of FAST_WARPS warps (largest first, first
 // fit).  Returns the CTAs per frame; 0 when the geometry does not fit (the band kernel serves it then).
-int fast_build_strips(const FrameGeom& G, std::vector<StripDesc>* out)
+int fast_build_strips(const FrameGeom& G, std::vector<StripDesc>* out, int* lvl_cta)
 {
     struct Group { int lvl, ci, xs, xe, n; };
     std::vector<Group> groups;
@@ -538,26 +538,39 @@ int fast_build_strips(const FrameGeom& G, std::vector<StripDesc>* out)
             }
         }
     }
-    std::stable_sort(groups.begin(), groups.end(), [](const Group& a, const Group& b) { return a.n > b.n; });
-    std::vector<int> used;                         // warps taken per CTA
-    std::vector<std::vector<StripDesc>> ctas;
-    for (const Group& g : groups) {
-        size_t c = 0;
-        while (c < used.size() && used[c] + g.n > FAST_WARPS) c++;
-        if (c == used.size()) { used.push_back(0); ctas.emplace_back(); }
-        for (int k = 0; k < g.n; k++) {
-            StripDesc sd; sd.lvl = (short)g.lvl; sd.ci = (short)g.ci; sd.gxs = (short)g.xs; sd.gxe = (short)g.xe;
-            sd.k = (short)k; sd.first = (short)used[c]; sd.nstrips = (short)g.n; sd.pad = 0;
-            ctas[c].push_back(sd);
+    // first fit of the groups of [lo, hi) (largest first) into CTAs appended to *out; returns the CTAs added
+    auto pack = [&](std::vector<Group> gs) {
+        std::stable_sort(gs.begin(), gs.end(), [](const Group& a, const Group& b) { return a.n > b.n; });
+        std::vector<int> used;                         // warps taken per CTA
+        std::vector<std::vector<StripDesc>> ctas;
+        for (const Group& g : gs) {
+            size_t c = 0;
+            while (c < used.size() && used[c] + g.n > FAST_WARPS) c++;
+            if (c == used.size()) { used.push_back(0); ctas.emplace_back(); }
+            for (int k = 0; k < g.n; k++) {
+                StripDesc sd; sd.lvl = (short)g.lvl; sd.ci = (short)g.ci; sd.gxs = (short)g.xs; sd.gxe = (short)g.xe;
+                sd.k = (short)k; sd.first = (short)used[c]; sd.nstrips = (short)g.n; sd.pad = 0;
+                ctas[c].push_back(sd);
+            }
+            used[c] += g.n;
         }
-        used[c] += g.n;
+        for (auto& v : ctas) {
+            StripDesc none = {}; none.lvl = -1;
+            while ((int)v.size() < FAST_WARPS) v.push_back(none);
+            out->insert(out->end(), v.begin(), v.end());
+        }
+        return (int)ctas.size();
+    };
+    const int total = pack(groups);                    // plan 1: all levels packed together (batches)
+    int at = total;                                    // plan 2: level by level (the per-level launches of a single-frame graph)
+    for (int l = 0; l < G.nlevels; l++) {
+        std::vector<Group> gl;
+        for (const Group& g : groups) if (g.lvl == l) gl.push_back(g);
+        lvl_cta[l] = at;
+        at += pack(gl);
     }
-    for (auto& v : ctas) {
-        StripDesc none = {}; none.lvl = -1;
-        while ((int)v.size() < FAST_WARPS) v.push_back(none);
-        out->insert(out->end(), v.begin(), v.end());
-    }
-    return (int)ctas.size();
+    lvl_cta[G.nlevels] = at;
+    return total;
 }
 
 // FAST work items of one frame: per level and cell row, runs of whole cells spanning <= 128 px (one warp,
@@ -595,7 +608,16 @@ int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out, int* warp_w
     return FAST_WARPS * *warp_words * 4;
 }
 
-int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
+static bool fast_strips_enabled()
+{
+    static const bool strips = [] { const char* e = getenv("ORBX_FAST_STRIPS"); return !e || atoi(e) != 0; }();
+    return strips;
+}
+
+// per-level launches (launch_fast(..., level)) exist for the strip kernel only
+bool fast_per_level(const FrameGeom& G) { return fast_strips_enabled() && G.strip_ctas > 0; }
+
+int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s, int level)
 {
     // D.candcnt was zeroed by pyr_level0_kernel
     int smem = G.fast_smem;
@@ -604,11 +626,16 @@ int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream
     if (pad > smem) smem = pad;
     if (smem > 48 * 1024)
         cudaFuncSetAttribute(fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    static const bool strips = [] { const char* e = getenv("ORBX_FAST_STRIPS"); return !e || atoi(e) != 0; }();
-    if (strips && G.strip_ctas > 0) {
+    if (fast_per_level(G)) {
         if (smem + (int)sizeof(uint32_t) * FAST_WARPS * FS_MAXCOLS > 48 * 1024)      // static flags + dynamic tiles
             cudaFuncSetAttribute(fast_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        orbx_launch(fast_strip_kernel, dim3(G.strip_ctas, nframes), dim3(FAST_THREADS), (size_t)smem, s, G, D);
+        if (level >= 0) {
+            const int c0 = G.strip_lvl_cta[level], nc = G.strip_lvl_cta[level + 1] - c0;
+            if (nc <= 0) return 0;
+            orbx_launch(fast_strip_kernel, dim3(nc, nframes), dim3(FAST_THREADS), (size_t)smem, s, G, D, c0);
+            return 1;
+        }
+        orbx_launch(fast_strip_kernel, dim3(G.strip_ctas, nframes), dim3(FAST_THREADS), (size_t)smem, s, G, D, 0);
         return 1;
     }
     const dim3 grid((G.bands_per_frame + FAST_WARPS - 1) / FAST_WARPS, nframes);

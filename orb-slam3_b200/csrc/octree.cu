@@ -442,12 +442,13 @@ static void launch_group(const FrameGeom& G, const DevBuffers& D, const OctLevel
     orbx_launch(octree_kernel<SMEM, NT>, dim3(LV.n, nframes), dim3(NT), smem, s, G, D, LV);
 }
 
-int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
+int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s, int level)
 {
     OctLevels small, big, huge;
     small.n = big.n = huge.n = 0;
     size_t small_need = 0, big_need = 0;
     for (int l = 0; l < G.nlevels; l++) {
+        if (level >= 0 && l != level) continue;
         const size_t need = ((size_t)G.L[l].node_cap * OCT_TABLES + (G.L[l].nIni <= OCT_HROOTS ? G.L[l].nIni * OCT_HNODES : 0)) * sizeof(int);
         if (need <= 64 * 1024) { small.lvl[small.n++] = l; small_need = need > small_need ? need : small_need; }
         else if (need <= 220 * 1024) { big.lvl[big.n++] = l; big_need = need > big_need ? need : big_need; }

@@ -26,6 +26,8 @@ struct orbx_extractor {
     // the pipeline of a single-chunk call as an instantiated CUDA graph (one graph launch instead of 14 kernel launches);
     // valid for one {frames, lapping area, input pitch} and the current device buffers
     cudaGraphExec_t graph_exec; int graph_key[4]; int graph_launches;
+    // per-level branches of that graph: FAST and the quadtree of level l start as soon as pyramid level l exists
+    cudaStream_t dag_stream[ORBX_MAX_LEVELS]; cudaEvent_t dag_ev[ORBX_MAX_LEVELS], dag_done[ORBX_MAX_LEVELS]; bool dag_ready;
     uint8_t* h_in; size_t h_in_cap;
     uint8_t* h_land; size_t h_land_cap;
     bool reserved;

@@ -89,6 +89,7 @@ struct StripDesc { short lvl, ci, gxs, gxe, k, first, nstrips, pad; };
 struct FrameGeom {
     int nlevels;
     int strip_ctas;           // CTAs per frame of fast_strip_kernel (0: use fast_band_kernel)
+    int strip_lvl_cta[ORBX_MAX_LEVELS + 1];   // second, level-major plan behind the first: CTAs [lvl_cta[l], lvl_cta[l+1]) serve level l
     int bands_per_frame;      // FAST band segments per frame (DevBuffers::bands)
     int fast_smem;            // dynamic shared memory of fast_band_kernel (bytes)
     int fast_warp_words;      // ... of which 32-bit words per warp
@@ -128,15 +129,17 @@ struct DevBuffers {
 int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
 void blur_plan(FrameGeom& G);           // fills blur_end[]
 void pyramid_fill_border(const LevelGeom& L, int frame, cudaStream_t s);   // mvImagePyramid border on demand
-int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
-int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
+bool fast_per_level(const FrameGeom& G);
+int launch_pyramid_level(const FrameGeom& G, const DevBuffers& D, int nframes, int l, cudaStream_t s);
+int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s, int level = -1);     // level >= 0: that level only
+int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s, int level = -1);
 int launch_assemble(const FrameGeom& G, const DevBuffers& D, int nframes, int lap0, int lap1, cudaStream_t s);
 int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
 int launch_describe(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
 #ifdef __cplusplus
 #include <vector>
 int fast_build_bands(const FrameGeom& G, std::vector<BandDesc>* out, int* warp_words);   // returns the kernel's dynamic smem bytes
-int fast_build_strips(const FrameGeom& G, std::vector<StripDesc>* out);                   // returns the CTAs per frame, 0 if unsupported
+int fast_build_strips(const FrameGeom& G, std::vector<StripDesc>* out, int* lvl_cta);     // returns the CTAs per frame, 0 if unsupported
 #endif
 size_t octree_nodetab_ints(const FrameGeom& G);   // ints of node scratch per frame
 void octree_assign_node_offsets(FrameGeom& G);

@@ -245,10 +245,9 @@ static int pyr_rows_override()
     return v;
 }
 
-int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
+int launch_pyramid_level(const FrameGeom& G, const DevBuffers& D, int nframes, int l, cudaStream_t s)
 {
-    int launches = 0;
-    for (int l = 0; l < G.nlevels; l++) {
+    {
         const LevelGeom& L = G.L[l];
         if (l == 0) {
             const dim3 block(64, 4);
@@ -281,7 +280,13 @@ int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStr
             pyr_resize_kernel<<<rgrid, rblock, 0, s>>>(P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch, L.plane_bytes,
                                                        L.prow, L.tapx, L.tapy);
         }
-        launches++;
     }
+    return 1;
+}
+
+int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
+{
+    int launches = 0;
+    for (int l = 0; l < G.nlevels; l++) launches += launch_pyramid_level(G, D, nframes, l, s);
     return launches;
 }
