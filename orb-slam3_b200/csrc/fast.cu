@@ -337,13 +337,17 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
 // ------------------------------------------------------------------------------------------------
 #define FS_MAXCOLS 128                 // cell columns per level the flag arrays hold
 
-__global__ void __launch_bounds__(FAST_THREADS, FAST_MINBLOCKS)
+// HALVES = 2 (launches of a few frames, where one warp walking a whole cell row IS the kernel's duration): two warps
+// per strip, warp w and w + FAST_WARPS share strip slot w - rows [0, r0) and [r0, ih) of the same score tile, r0 a
+// multiple of 3 (the NMS loop's step), each with its own half of the survivor list.
+template <int HALVES>
+__global__ void __launch_bounds__(FAST_THREADS * HALVES, HALVES == 1 ? FAST_MINBLOCKS : 2)
 fast_strip_kernel(FrameGeom G, DevBuffers D, int cta0)
 {
     extern __shared__ uint32_t s_dyn[];               // per warp: S words [ihmax + 2][32], then the lane-private survivor lists
     __shared__ uint32_t s_ini[FAST_WARPS][FS_MAXCOLS];
     orbx_pdl_prologue();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = (threadIdx.x >> 5) & (FAST_WARPS - 1), half = threadIdx.x >> 7;
     const StripDesc sd = D.strips[(cta0 + blockIdx.x) * FAST_WARPS + warp];
     const bool live = sd.lvl >= 0;
     const int f = blockIdx.y;
@@ -359,15 +363,22 @@ fast_strip_kernel(FrameGeom G, DevBuffers D, int cta0)
     const int wi = lane < nw ? lane : nw - 1;
     const int x = xa + 4 * wi;
     uint32_t* s_tile = s_dyn + warp * G.fast_warp_words;
+    // this warp's rows [ra, rb_end) of the tile
+    const int r0 = HALVES == 2 ? 3 * ((ih + 5) / 6) : ih;
+    const int ra = half ? r0 : 0, re = half ? ih : min(r0, ih);
+    if (half == 0) {
 #pragma unroll
-    for (int c = lane; c < FS_MAXCOLS; c += 32) s_ini[warp][c] = 0;
+        for (int c = lane; c < FS_MAXCOLS; c += 32) s_ini[warp][c] = 0;
+    }
 
     // ---------------- phase A: score tile ----------------
     if (live) {
-        const uint32_t* p0 = reinterpret_cast<const uint32_t*>(
-            L.pyr + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + ys - 3) * L.pitch + ORBX_XOFF + x);
         const int pw = L.pitch >> 2;
-        const int klast = ih + 5;
+        // window rows are counted from the first row this warp scores
+        const uint32_t* p0 = reinterpret_cast<const uint32_t*>(
+            L.pyr + (long long)f * L.plane_bytes + (long long)(ORBX_YOFF + ys - 3 + ra) * L.pitch + ORBX_XOFF + x);
+        const int nrow = re - ra;
+        const int klast = nrow + 5;
         uint32_t W[7][8];
 #pragma unroll
         for (int i = 0; i < 6; i++) { const uint32_t* p = p0 + i * pw; fast_fill_row(W[i], __ldg(p - 1), __ldg(p), __ldg(p + 1)); }
@@ -377,9 +388,9 @@ fast_strip_kernel(FrameGeom G, DevBuffers D, int cta0)
             const uint32_t* pn = p0 + min(6 + i, klast) * pw;
             pf[(6 + i) % 7][0] = __ldg(pn - 1); pf[(6 + i) % 7][1] = __ldg(pn); pf[(6 + i) % 7][2] = __ldg(pn + 1);
         }
-        uint32_t* out = s_tile + wi;
+        uint32_t* out = s_tile + ra * 32 + wi;
 #define FAST_STEP(PH)                                                                              \
-        if (rb + PH < ih) {                                                                        \
+        if (rb + PH < nrow) {                                                                        \
             const int r = rb + PH;                                                                 \
             fast_fill_row(W[(PH + 6) % 7], pf[(PH + 6) % 7][0], pf[(PH + 6) % 7][1], pf[(PH + 6) % 7][2]); \
             { const uint32_t* pn = p0 + min(r + 9, klast) * pw;                                    \
@@ -388,13 +399,15 @@ fast_strip_kernel(FrameGeom G, DevBuffers D, int cta0)
             if (active) out[r * 32] = sw;                                                          \
         }
 #pragma unroll 1
-        for (int rb = 0; rb < ih; rb += 7) {
+        for (int rb = 0; rb < nrow; rb += 7) {
             FAST_STEP(0) FAST_STEP(1) FAST_STEP(2) FAST_STEP(3) FAST_STEP(4) FAST_STEP(5) FAST_STEP(6)
         }
 #undef FAST_STEP
         // two zero rows under the tile: the NMS loop below runs whole 3-row steps without a row guard
-        s_tile[ih * 32 + lane] = 0;
-        s_tile[(ih + 1) * 32 + lane] = 0;
+        if (half == HALVES - 1) {
+            s_tile[ih * 32 + lane] = 0;
+            s_tile[(ih + 1) * 32 + lane] = 0;
+        }
     }
     __syncthreads();                                  // every tile of the CTA is complete, the flags are cleared
 
@@ -417,19 +430,20 @@ fast_strip_kernel(FrameGeom G, DevBuffers D, int cta0)
     }
     const int iniTh = G.iniTh, minTh = min(G.minTh, G.iniTh);
     const uint32_t thr = (uint32_t)(((minTh - 1) << 8) | 0xFF) * 0x00010001u;
-    const uint32_t* mylist = s_tile + (ih + 2) * 32 + lane;
+    const uint32_t* mylist = s_tile + (ih + 2 + ra) * 32 + lane;     // the second half appends behind the first half's rows
     int cnt = 0;
-    if (live) {
+    if (live && ra < re) {
         // across a strip edge the neighbour column is word 31 / word 0 of the adjacent warp's tile (same cell row, same
         // ih); at the group's ends it lies outside every cell interior and is masked: those lanes re-read their own word
-        const uint32_t* pm = s_tile + wi;
-        const uint32_t* pl = wi > 0 ? pm - 1 : (sd.k > 0 ? s_tile - G.fast_warp_words + 31 : pm);
-        const uint32_t* pr = wi + 1 < nw ? pm + 1 : ((wi == 31 && sd.k + 1 < sd.nstrips) ? s_tile + G.fast_warp_words : pm);
+        const uint32_t* pm = s_tile + ra * 32 + wi;
+        const uint32_t* pl = wi > 0 ? pm - 1 : (sd.k > 0 ? pm - G.fast_warp_words + 31 : pm);
+        const uint32_t* pr = wi + 1 < nw ? pm + 1 : ((wi == 31 && sd.k + 1 < sd.nstrips) ? pm + G.fast_warp_words - 31 : pm);
         uint32_t R[3][4];
         const uint32_t wa0 = (uint32_t)__cvta_generic_to_shared(mylist);
-        uint32_t wa = wa0, rr = 0;
+        uint32_t wa = wa0, rr = (uint32_t)ra * 256u;
 #pragma unroll
         for (int k = 0; k < 4; k++) R[0][k] = 0;
+        if (ra > 0) nms_fill(R[0], pl[-32], pm[-32], pr[-32]);         // the row above belongs to the first half
         nms_fill(R[1], pl[0], pm[0], pr[0]);
 #define NMS_STEP(PH)                                                                                        \
         {                                                                                                   \
@@ -440,7 +454,7 @@ fast_strip_kernel(FrameGeom G, DevBuffers D, int cta0)
             list_push(wa, fl, fl | (rr + PH * 256u));                                                       \
         }
 #pragma unroll 1
-        for (int rb = 0; rb < ih; rb += 3) {
+        for (int rb = ra; rb < re; rb += 3) {
             NMS_STEP(0) NMS_STEP(1) NMS_STEP(2)
             pl += 96; pm += 96; pr += 96; rr += 768u;
         }
@@ -451,7 +465,7 @@ fast_strip_kernel(FrameGeom G, DevBuffers D, int cta0)
 
     // ---------------- phase B2: per-cell retry rule (:1118-1125) and emission ----------------
     const int xrel = xa - ORBX_MINB + 4 * wi, yrel = ys - ORBX_MINB;
-    const uint32_t* srow = s_tile + wi;
+    const uint32_t* srow = s_tile + wi;        // list entries carry absolute tile rows
     uint32_t* ini = s_ini[live ? sd.first : 0];       // the group's flags: cell column -> a survivor >= iniTh exists
     for (int i = 0; i < cnt; i++) {
         const uint32_t e = mylist[i * 32];
@@ -627,15 +641,18 @@ int launch_fast(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream
     if (smem > 48 * 1024)
         cudaFuncSetAttribute(fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (fast_per_level(G)) {
+        const bool two = nframes * G.nlevels <= 64;        // few frames: two warps per strip
         if (smem + (int)sizeof(uint32_t) * FAST_WARPS * FS_MAXCOLS > 48 * 1024)      // static flags + dynamic tiles
-            cudaFuncSetAttribute(fast_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            cudaFuncSetAttribute(two ? fast_strip_kernel<2> : fast_strip_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (level >= 0) {
             const int c0 = G.strip_lvl_cta[level], nc = G.strip_lvl_cta[level + 1] - c0;
             if (nc <= 0) return 0;
-            orbx_launch(fast_strip_kernel, dim3(nc, nframes), dim3(FAST_THREADS), (size_t)smem, s, G, D, c0);
+            if (two) orbx_launch(fast_strip_kernel<2>, dim3(nc, nframes), dim3(2 * FAST_THREADS), (size_t)smem, s, G, D, c0);
+            else orbx_launch(fast_strip_kernel<1>, dim3(nc, nframes), dim3(FAST_THREADS), (size_t)smem, s, G, D, c0);
             return 1;
         }
-        orbx_launch(fast_strip_kernel, dim3(G.strip_ctas, nframes), dim3(FAST_THREADS), (size_t)smem, s, G, D, 0);
+        if (two) orbx_launch(fast_strip_kernel<2>, dim3(G.strip_ctas, nframes), dim3(2 * FAST_THREADS), (size_t)smem, s, G, D, 0);
+        else orbx_launch(fast_strip_kernel<1>, dim3(G.strip_ctas, nframes), dim3(FAST_THREADS), (size_t)smem, s, G, D, 0);
         return 1;
     }
     const dim3 grid((G.bands_per_frame + FAST_WARPS - 1) / FAST_WARPS, nframes);
