@@ -1,0 +1,44 @@
+#!/bin/sh
+# oracle/build_ref.sh — TEST INFRASTRUCTURE.  Compiles the UNMODIFIED reference sources of the hot path,
+# where they lie under /root/reference, against the OpenCV stand-in in oracle/cvshim/ and writes the
+# libraries into oracle/_ref/ (git-ignored, travels to the GPU box with the snapshot).
+# Never runs the reference's own build system (cmake + OpenCV + Eigen + Pangolin are not in this image).
+#
+#   libref.so         ORBextractor.cc, system allocator (literal pointer tie-break, src/ORBextractor.cc:927)
+#   libref_seq.so     same, operator new = creation-ordered arena (the canonical tie-break)
+#   libref_native.so  libref.so built the way the reference's CMakeLists.txt:10-13 builds it
+#                     (-O3 -march=native there; here -march=x86-64-v3 = AVX2+FMA, because the library is
+#                     built in this container and must run on the GPU box's unknown host CPU: host FMA
+#                     contraction allowed) — the timed CPU baseline
+set -e
+HERE="$(cd "$(dirname "$0")" && pwd)"
+REF="${ORB_REFERENCE_ROOT:-/root/reference}"
+OUT="$HERE/_ref"
+if [ ! -f "$REF/src/ORBextractor.cc" ]; then
+    echo "build_ref.sh: $REF/src/ORBextractor.cc not found (expected on the GPU box: prebuilt oracle/_ref is used)"
+    exit 0
+fi
+mkdir -p "$OUT"
+CXX="${CXX:-g++}"
+CC="${CC:-gcc}"
+COMMON="-O3 -fPIC -w -I$HERE/cvshim -I$REF/include -I$HERE"
+CANON="-ffp-contract=off"
+LINK="-shared -Wl,-Bsymbolic -lm -lpthread"
+
+$CC -O3 -fPIC -std=c11 $CANON -c "$HERE/orc_prims.c" -o "$OUT/orc_prims.o"
+$CC -O3 -fPIC -std=c11 -march=x86-64-v3 -c "$HERE/orc_prims.c" -o "$OUT/orc_prims_native.o"
+
+$CXX -std=c++14 $COMMON $CANON -c "$REF/src/ORBextractor.cc" -o "$OUT/ORBextractor.o"
+$CXX -std=c++14 $COMMON $CANON -c "$HERE/ref_wrap.cc" -o "$OUT/ref_wrap.o"
+$CXX -o "$OUT/libref.so" "$OUT/ORBextractor.o" "$OUT/ref_wrap.o" "$OUT/orc_prims.o" $LINK
+
+$CXX -std=c++14 $COMMON $CANON -DREF_SEQ_ALLOC -c "$HERE/ref_wrap.cc" -o "$OUT/ref_wrap_seq.o"
+$CXX -o "$OUT/libref_seq.so" "$OUT/ORBextractor.o" "$OUT/ref_wrap_seq.o" "$OUT/orc_prims.o" $LINK
+
+$CXX -std=c++14 $COMMON -march=x86-64-v3 -c "$REF/src/ORBextractor.cc" -o "$OUT/ORBextractor_native.o"
+$CXX -std=c++14 $COMMON -march=x86-64-v3 -c "$HERE/ref_wrap.cc" -o "$OUT/ref_wrap_native.o"
+$CXX -o "$OUT/libref_native.so" "$OUT/ORBextractor_native.o" "$OUT/ref_wrap_native.o" "$OUT/orc_prims_native.o" $LINK
+
+rm -f "$OUT"/*.o
+sha256sum "$REF/src/ORBextractor.cc" "$REF/include/ORBextractor.h" > "$OUT/SOURCES.sha256" 2>/dev/null || true
+echo "build_ref.sh: built $(ls "$OUT"/*.so | wc -l) libraries in $OUT"

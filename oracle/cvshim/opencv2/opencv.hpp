@@ -1,0 +1,422 @@
+/*
+ * oracle/cvshim/opencv2/opencv.hpp — TEST INFRASTRUCTURE ONLY.
+ *
+ * A minimal stand-in for the slice of the OpenCV C++ API that the reference's hot-path sources use, so
+ * that the UNMODIFIED files under /root/reference/src (ORBextractor.cc) compile with g++ in an image
+ * that has no OpenCV C++ headers or libraries (only the cv2 Python wheel).  The container types (Mat
+ * with ROI views, KeyPoint, Point_, Size, Rect, Range, InputArray/OutputArray) are written here; the
+ * pixel primitives the reference calls (resize, copyMakeBorder, FAST, GaussianBlur, fastAtan2, cvRound)
+ * forward to oracle/orc_prims.c, which is pinned bit-exact against the real OpenCV 4.13
+ * (tests/test_oracle_vs_cv2.py, tests/golden/).
+ *
+ * Built only by oracle/build_ref.sh into oracle/_ref/; nothing in the product links or includes it.
+ * Semantics follow the OpenCV 4.x documentation of each call; only what the reference reaches is
+ * implemented, anything else aborts loudly (cvshim_fail).
+ */
+#pragma once
+#include <algorithm>
+#include <cassert>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../orc.h"
+
+#define CV_8U 0
+#define CV_8UC1 0
+#define CV_32S 4
+#define CV_32F 5
+#define CV_64F 6
+#define CV_32FC1 5
+#define CV_PI 3.1415926535897932384626433832795
+
+typedef unsigned char uchar;
+
+namespace cv {
+
+typedef ::uchar uchar;
+
+[[noreturn]] inline void cvshim_fail(const char* what)
+{
+    std::fprintf(stderr, "cvshim: unsupported use: %s\n", what);
+    std::abort();
+}
+
+/* cvRound: round half to even (SSE cvtss2si / cvtsd2si in OpenCV builds for x86). */
+inline int cvRound(float v) { return (int)lrintf(v); }
+inline int cvRound(double v) { return (int)lrint(v); }
+inline int cvRound(int v) { return v; }
+inline int cvFloor(double v) { int i = (int)v; return i - (i > v); }
+inline int cvFloor(float v) { int i = (int)v; return i - (i > v); }
+inline int cvCeil(double v) { int i = (int)v; return i + (i < v); }
+inline int cvCeil(float v) { int i = (int)v; return i + (i < v); }
+inline float fastAtan2(float y, float x) { return orc_fast_atan2(y, x); }
+
+template <typename T> inline T saturate_cast(float v) { return (T)v; }
+template <> inline int saturate_cast<int>(float v) { return cvRound(v); }
+template <typename T> inline T saturate_cast(double v) { return (T)v; }
+template <> inline int saturate_cast<int>(double v) { return cvRound(v); }
+template <typename T> inline T saturate_cast(int v) { return (T)v; }
+
+template <typename T> struct Point_ {
+    T x, y;
+    Point_() : x(0), y(0) {}
+    Point_(T _x, T _y) : x(_x), y(_y) {}
+    template <typename U> Point_(const Point_<U>& p) : x(saturate_cast<T>(p.x)), y(saturate_cast<T>(p.y)) {}
+};
+/* core/types.hpp: a *= b  ->  saturate_cast<T>(a.x * b) per component */
+template <typename T> inline Point_<T>& operator*=(Point_<T>& a, float b)
+{
+    a.x = saturate_cast<T>(a.x * b);
+    a.y = saturate_cast<T>(a.y * b);
+    return a;
+}
+template <typename T> inline Point_<T>& operator*=(Point_<T>& a, double b)
+{
+    a.x = saturate_cast<T>(a.x * b);
+    a.y = saturate_cast<T>(a.y * b);
+    return a;
+}
+template <typename T> inline Point_<T>& operator*=(Point_<T>& a, int b)
+{
+    a.x = saturate_cast<T>(a.x * b);
+    a.y = saturate_cast<T>(a.y * b);
+    return a;
+}
+template <typename T> inline Point_<T> operator+(const Point_<T>& a, const Point_<T>& b) { return Point_<T>(a.x + b.x, a.y + b.y); }
+template <typename T> inline Point_<T> operator-(const Point_<T>& a, const Point_<T>& b) { return Point_<T>(a.x - b.x, a.y - b.y); }
+template <typename T> inline bool operator==(const Point_<T>& a, const Point_<T>& b) { return a.x == b.x && a.y == b.y; }
+typedef Point_<int> Point2i;
+typedef Point_<int> Point;
+typedef Point_<float> Point2f;
+typedef Point_<double> Point2d;
+
+template <typename T> struct Size_ {
+    T width, height;
+    Size_() : width(0), height(0) {}
+    Size_(T w, T h) : width(w), height(h) {}
+};
+typedef Size_<int> Size;
+
+template <typename T> struct Rect_ {
+    T x, y, width, height;
+    Rect_() : x(0), y(0), width(0), height(0) {}
+    Rect_(T _x, T _y, T w, T h) : x(_x), y(_y), width(w), height(h) {}
+};
+typedef Rect_<int> Rect;
+
+struct Range {
+    int start, end;
+    Range() : start(0), end(0) {}
+    Range(int s, int e) : start(s), end(e) {}
+};
+
+/* cv::KeyPoint: 28 bytes, the layout the product's ABI mirrors (include/orbx.h). */
+struct KeyPoint {
+    Point2f pt;
+    float size;
+    float angle;
+    float response;
+    int octave;
+    int class_id;
+    KeyPoint() : pt(0, 0), size(0), angle(-1), response(0), octave(0), class_id(-1) {}
+    KeyPoint(Point2f _pt, float _size, float _angle = -1, float _response = 0, int _octave = 0, int _class_id = -1)
+        : pt(_pt), size(_size), angle(_angle), response(_response), octave(_octave), class_id(_class_id) {}
+    KeyPoint(float x, float y, float _size, float _angle = -1, float _response = 0, int _octave = 0, int _class_id = -1)
+        : pt(x, y), size(_size), angle(_angle), response(_response), octave(_octave), class_id(_class_id) {}
+};
+static_assert(sizeof(KeyPoint) == 28, "cv::KeyPoint layout");
+
+enum BorderTypes { BORDER_CONSTANT = 0, BORDER_REPLICATE = 1, BORDER_REFLECT = 2, BORDER_WRAP = 3, BORDER_REFLECT_101 = 4,
+                   BORDER_REFLECT101 = 4, BORDER_DEFAULT = 4, BORDER_ISOLATED = 16 };
+enum InterpolationFlags { INTER_NEAREST = 0, INTER_LINEAR = 1, INTER_CUBIC = 2, INTER_AREA = 3 };
+enum NormTypes { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4, NORM_HAMMING = 6 };
+
+inline int cvshim_elem_size(int type)
+{
+    switch (type) {
+    case CV_8U: return 1;
+    case CV_32S: case CV_32F: return 4;
+    case CV_64F: return 8;
+    default: cvshim_fail("Mat type");
+    }
+}
+
+struct MatStep {
+    size_t v;
+    MatStep() : v(0) {}
+    operator size_t() const { return v; }
+    MatStep& operator=(size_t s) { v = s; return *this; }
+};
+
+class Mat;
+class _InputArray;
+class _OutputArray;
+typedef const _InputArray& InputArray;
+typedef const _OutputArray& OutputArray;
+
+/* Reference-counted 2-D buffer with ROI views (the cv::Mat subset the reference touches). */
+class Mat {
+public:
+    int rows, cols;
+    uchar* data;
+    MatStep step;
+
+    Mat() : rows(0), cols(0), data(nullptr), type_(CV_8U), ref_(nullptr), datastart_(nullptr), wrows_(0), wcols_(0) {}
+    Mat(int r, int c, int type) : Mat() { create(r, c, type); }
+    Mat(Size sz, int type) : Mat() { create(sz.height, sz.width, type); }
+    /* user-owned data (no reference counting), as cv::Mat(rows, cols, type, void* data, step) */
+    Mat(int r, int c, int type, void* ext, size_t st = 0) : Mat()
+    {
+        rows = r; cols = c; type_ = type; data = (uchar*)ext;
+        step = st ? st : (size_t)c * cvshim_elem_size(type);
+        datastart_ = data; wrows_ = r; wcols_ = c;
+    }
+    Mat(const Mat& m) : rows(m.rows), cols(m.cols), data(m.data), step(m.step), type_(m.type_), ref_(m.ref_),
+                        datastart_(m.datastart_), wrows_(m.wrows_), wcols_(m.wcols_)
+    {
+        if (ref_) ++*ref_;
+    }
+    Mat& operator=(const Mat& m)
+    {
+        if (this != &m) {
+            if (m.ref_) ++*m.ref_;
+            release();
+            rows = m.rows; cols = m.cols; data = m.data; step = m.step; type_ = m.type_; ref_ = m.ref_;
+            datastart_ = m.datastart_; wrows_ = m.wrows_; wcols_ = m.wcols_;
+        }
+        return *this;
+    }
+    ~Mat() { release(); }
+
+    /* pixel buffers come from malloc, never operator new: the creation-order build of oracle/_ref replaces
+     * operator new with a per-call arena (oracle/ref_wrap.cc) and mvImagePyramid outlives the call */
+    void release()
+    {
+        if (ref_ && --*ref_ == 0) {
+            std::free(datastart_);
+            std::free(ref_);
+        }
+        rows = cols = 0; data = nullptr; ref_ = nullptr; datastart_ = nullptr; wrows_ = wcols_ = 0; step = 0;
+    }
+    /* cv::Mat::create: keeps the buffer when shape and type already match (also for ROI views) */
+    void create(int r, int c, int type)
+    {
+        if (data && rows == r && cols == c && type_ == type) return;
+        release();
+        if (r <= 0 || c <= 0) { type_ = type; return; }
+        rows = r; cols = c; type_ = type;
+        step = (size_t)c * cvshim_elem_size(type);
+        datastart_ = (uchar*)std::malloc((size_t)r * step + 64);
+        ref_ = (int*)std::malloc(sizeof(int));
+        *ref_ = 1;
+        data = datastart_; wrows_ = r; wcols_ = c;
+    }
+    void create(Size sz, int type) { create(sz.height, sz.width, type); }
+
+    int type() const { return type_; }
+    int depth() const { return type_; }
+    int channels() const { return 1; }
+    bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
+    size_t elemSize() const { return (size_t)cvshim_elem_size(type_); }
+    size_t step1() const { return step.v / elemSize(); }
+    Size size() const { return Size(cols, rows); }
+    size_t total() const { return (size_t)rows * cols; }
+    bool isContinuous() const { return rows <= 1 || step.v == (size_t)cols * elemSize(); }
+    bool isSubmatrix() const { return rows != wrows_ || cols != wcols_; }
+    /* position of this view inside the allocation it was cut from */
+    void locateROI(Size& whole, Point& ofs) const
+    {
+        whole = Size(wcols_, wrows_);
+        size_t d = (size_t)(data - datastart_);
+        ofs.y = step.v ? (int)(d / step.v) : 0;
+        ofs.x = step.v ? (int)((d - (size_t)ofs.y * step.v) / elemSize()) : 0;
+    }
+
+    Mat operator()(const Rect& r) const
+    {
+        if (r.x < 0 || r.y < 0 || r.x + r.width > cols || r.y + r.height > rows) cvshim_fail("Mat ROI out of range");
+        Mat m(*this);
+        m.data = data + (size_t)r.y * step.v + (size_t)r.x * elemSize();
+        m.rows = r.height; m.cols = r.width;
+        return m;
+    }
+    Mat operator()(const Range& rr, const Range& cr) const { return (*this)(Rect(cr.start, rr.start, cr.end - cr.start, rr.end - rr.start)); }
+    Mat rowRange(int a, int b) const { return (*this)(Rect(0, a, cols, b - a)); }
+    Mat colRange(int a, int b) const { return (*this)(Rect(a, 0, b - a, rows)); }
+    Mat rowRange(const Range& r) const { return rowRange(r.start, r.end); }
+    Mat colRange(const Range& r) const { return colRange(r.start, r.end); }
+    Mat row(int y) const { return rowRange(y, y + 1); }
+    Mat col(int x) const { return colRange(x, x + 1); }
+
+    Mat clone() const
+    {
+        Mat m;
+        copyToMat(m);
+        return m;
+    }
+    void copyToMat(Mat& dst) const
+    {
+        dst.create(rows, cols, type_);
+        const size_t w = (size_t)cols * elemSize();
+        for (int y = 0; y < rows; y++) std::memmove(dst.data + (size_t)y * dst.step.v, data + (size_t)y * step.v, w);
+    }
+    inline void copyTo(OutputArray dst) const;
+
+    uchar* ptr(int y = 0) { return data + (size_t)y * step.v; }
+    const uchar* ptr(int y = 0) const { return data + (size_t)y * step.v; }
+    template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step.v); }
+    template <typename T> const T* ptr(int y = 0) const { return (const T*)(data + (size_t)y * step.v); }
+    template <typename T> T& at(int y, int x) { return ((T*)(data + (size_t)y * step.v))[x]; }
+    template <typename T> const T& at(int y, int x) const { return ((const T*)(data + (size_t)y * step.v))[x]; }
+
+    static Mat zeros(int r, int c, int type)
+    {
+        Mat m(r, c, type);
+        for (int y = 0; y < r; y++) std::memset(m.ptr(y), 0, (size_t)c * m.elemSize());
+        return m;
+    }
+
+private:
+    int type_;
+    int* ref_;
+    uchar* datastart_;
+    int wrows_, wcols_;
+};
+
+class _InputArray {
+public:
+    _InputArray() : m_(nullptr) {}
+    _InputArray(const Mat& m) : m_(const_cast<Mat*>(&m)) {}
+    Mat getMat() const { return m_ ? *m_ : Mat(); }
+    bool empty() const { return !m_ || m_->empty(); }
+protected:
+    Mat* m_;
+};
+class _OutputArray : public _InputArray {
+public:
+    _OutputArray() {}
+    _OutputArray(Mat& m) { m_ = &m; }
+    _OutputArray(const Mat& m) { m_ = const_cast<Mat*>(&m); }
+    void release() const { if (m_) m_->release(); }
+    void create(int r, int c, int type) const { if (m_) m_->create(r, c, type); }
+    void create(Size sz, int type) const { if (m_) m_->create(sz, type); }
+    Mat& getMatRef() const { return *m_; }
+};
+inline void Mat::copyTo(OutputArray dst) const { copyToMat(dst.getMatRef()); }
+inline const _InputArray& noArray() { static _InputArray n; return n; }
+
+/* ---- pixel primitives: forward to the cv2-pinned restatements in oracle/orc_prims.c ---- */
+
+inline void resize(InputArray _src, OutputArray _dst, Size dsize, double fx = 0, double fy = 0, int interpolation = INTER_LINEAR)
+{
+    Mat src = _src.getMat();
+    if (src.type() != CV_8UC1 || interpolation != INTER_LINEAR || fx != 0 || fy != 0) cvshim_fail("resize: only u8 INTER_LINEAR with dsize");
+    _dst.create(dsize, src.type());
+    Mat dst = _dst.getMat();
+    orc_resize_linear_u8(src.data, src.rows, src.cols, src.step, dst.data, dst.rows, dst.cols, dst.step);
+}
+
+/* copyMakeBorder, BORDER_REFLECT_101 with or without BORDER_ISOLATED.  Without ISOLATED a source that is a
+ * view takes real pixels from its parent where they exist (core/src/copy.cpp: locateROI + border shrink). */
+inline void copyMakeBorder(InputArray _src, OutputArray _dst, int top, int bottom, int left, int right, int borderType)
+{
+    Mat src = _src.getMat();
+    if (src.type() != CV_8UC1 || (borderType & ~BORDER_ISOLATED) != BORDER_REFLECT_101) cvshim_fail("copyMakeBorder: only u8 REFLECT_101");
+    int dtop = 0, dbottom = 0, dleft = 0, dright = 0;
+    if (src.isSubmatrix() && !(borderType & BORDER_ISOLATED)) {
+        Size whole; Point ofs;
+        src.locateROI(whole, ofs);
+        dtop = std::min(ofs.y, top);
+        dbottom = std::min(whole.height - src.rows - ofs.y, bottom);
+        dleft = std::min(ofs.x, left);
+        dright = std::min(whole.width - src.cols - ofs.x, right);
+    }
+    _dst.create(src.rows + top + bottom, src.cols + left + right, src.type());
+    Mat dst = _dst.getMat();
+    /* effective source = the view grown by the real pixels around it */
+    const uchar* es = src.data - (size_t)dtop * src.step - dleft;
+    const int er = src.rows + dtop + dbottom, ec = src.cols + dleft + dright;
+    const int etop = top - dtop, eleft = left - dleft;
+    if (er < 2 || ec < 2) cvshim_fail("copyMakeBorder: image too small");
+    std::vector<int> xmap(dst.cols);
+    for (int x = 0; x < dst.cols; x++) {
+        int sx = x - eleft;
+        while (sx < 0 || sx >= ec) sx = sx < 0 ? -sx : 2 * (ec - 1) - sx;
+        xmap[x] = sx;
+    }
+    /* interior rows first (memmove: src may live inside dst), then the mirrored columns and rows from dst itself */
+    for (int y = 0; y < er; y++) {
+        const uchar* s = es + (size_t)y * src.step;
+        uchar* d = dst.ptr(y + etop);
+        if (d + eleft != s) std::memmove(d + eleft, s, (size_t)ec);
+    }
+    for (int y = 0; y < er; y++) {
+        uchar* d = dst.ptr(y + etop);
+        for (int x = 0; x < eleft; x++) d[x] = d[eleft + xmap[x]];
+        for (int x = eleft + ec; x < dst.cols; x++) d[x] = d[eleft + xmap[x]];
+    }
+    for (int y = 0; y < dst.rows; y++) {
+        int sy = y - etop;
+        if (sy >= 0 && sy < er) continue;
+        while (sy < 0 || sy >= er) sy = sy < 0 ? -sy : 2 * (er - 1) - sy;
+        std::memcpy(dst.ptr(y), dst.ptr(sy + etop), (size_t)dst.cols);
+    }
+}
+
+/* cv::FAST(image, keypoints, threshold, nonmaxSuppression) — TYPE_9_16; KeyPoint(x, y, 7.f, -1, score) */
+inline void FAST(InputArray _img, std::vector<KeyPoint>& keypoints, int threshold, bool nonmaxSuppression = true)
+{
+    Mat img = _img.getMat();
+    if (img.type() != CV_8UC1) cvshim_fail("FAST: only u8");
+    keypoints.clear();
+    if (img.rows < 7 || img.cols < 7) return;
+    /* scratch from malloc, not operator new (see Mat::release) */
+    static thread_local orc_cand* buf = nullptr;
+    static thread_local int bufcap = 0;
+    const int cap = img.rows * img.cols;
+    if (bufcap < cap) { std::free(buf); buf = (orc_cand*)std::malloc(sizeof(orc_cand) * (size_t)cap); bufcap = cap; }
+    const int n = orc_fast9_16(img.data, img.rows, img.cols, img.step, threshold, nonmaxSuppression ? 1 : 0, buf, cap);
+    keypoints.reserve(n);
+    for (int i = 0; i < n; i++) keypoints.push_back(KeyPoint((float)buf[i].x, (float)buf[i].y, 7.f, -1, (float)buf[i].score));
+}
+
+/* cv::GaussianBlur — only the call the reference makes: 7x7, sigma 2, u8, REFLECT_101, on a standalone Mat */
+inline void GaussianBlur(InputArray _src, OutputArray _dst, Size ksize, double sigmaX, double sigmaY = 0, int borderType = BORDER_DEFAULT)
+{
+    Mat src = _src.getMat();
+    if (src.type() != CV_8UC1 || ksize.width != 7 || ksize.height != 7 || sigmaX != 2 || sigmaY != 2 ||
+        (borderType & ~BORDER_ISOLATED) != BORDER_REFLECT_101)
+        cvshim_fail("GaussianBlur: only u8 7x7 sigma 2 REFLECT_101");
+    if (src.isSubmatrix() && !(borderType & BORDER_ISOLATED)) cvshim_fail("GaussianBlur on a view without BORDER_ISOLATED");
+    _dst.create(src.rows, src.cols, src.type());
+    Mat dst = _dst.getMat();
+    if (dst.data == src.data) {
+        Mat tmp = src.clone();
+        orc_gaussian7x7_s2(tmp.data, tmp.rows, tmp.cols, tmp.step, dst.data, dst.step);
+    } else {
+        orc_gaussian7x7_s2(src.data, src.rows, src.cols, src.step, dst.data, dst.step);
+    }
+}
+
+/* features2d KeyPointsFilter::retainBest (keypoint.cpp): keep the n strongest plus everything tied with
+ * the n-th.  Reached only from the reference's dead ComputeKeyPointsOld; present so that the file links. */
+struct KeyPointsFilter {
+    static void retainBest(std::vector<KeyPoint>& keypoints, int n_points)
+    {
+        if (n_points >= 0 && keypoints.size() > (size_t)n_points) {
+            if (n_points == 0) { keypoints.clear(); return; }
+            std::nth_element(keypoints.begin(), keypoints.begin() + n_points - 1, keypoints.end(),
+                             [](const KeyPoint& a, const KeyPoint& b) { return a.response > b.response; });
+            const float ambiguous = keypoints[n_points - 1].response;
+            auto new_end = std::partition(keypoints.begin() + n_points, keypoints.end(),
+                                          [ambiguous](const KeyPoint& k) { return k.response >= ambiguous; });
+            keypoints.resize(new_end - keypoints.begin());
+        }
+    }
+};
+
+} // namespace cv
