@@ -192,6 +192,20 @@ int orbx_extract_stereo(orbx_extractor* eL, orbx_extractor* eR, const uint8_t* i
 int orbx_knn2_hamming(int device, const uint8_t* q, int nq, const uint8_t* t, int nt,
                       int32_t* out_idx, int32_t* out_dist);
 
+/* orbx_knn2_hamming for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same result as orbx_knn2_hamming, but d_q / d_t / d_out_idx / d_out_dist are the caller's DEVICE buffers
+ * (descriptors 16-byte aligned; outputs [nq][2] int32), the kernels are queued on `stream` (a cudaStream_t; NULL =
+ * the default stream) and the call returns WITHOUT synchronising.  It calls no cudaMalloc / cudaFree / allocating
+ * routine: the per-split partial table lives in a static 4 MiB device array that every GPU loading the library holds
+ * until exit.  nq > ORBX_KNN2_NOALLOC_MAX_QUERIES -> ORBX_ERR_CAPACITY (nt is not limited).  The first call on a device
+ * resolves the array's device address (cudaGetSymbolAddress): make it outside a capture, nq = 0 does only that.
+ * All calls on a device share the array; it keeps the last call's contents, none of which a later call reads before
+ * writing.  Calls that OVERLAP on the GPU (different streams or host threads) race on it: serialise them. */
+#define ORBX_KNN2_NOALLOC_MAX_QUERIES 16384
+int orbx_knn2_hamming_noalloc(int device, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt,
+                              int32_t* d_out_idx, int32_t* d_out_dist, void* stream);
+
 /* int ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints)
  * include/ORBmatcher.h:46, src/ORBmatcher.cc:45-168 (F.Nleft == -1 branch: mono / rectified stereo).
  * Frame side: n keypoints (undistorted, mvKeysUn), descriptors, optional uRight (NULL for mono),

@@ -69,6 +69,7 @@ SYMBOLS = {
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                       C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
     "orbx_knn2_hamming": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "orbx_knn2_hamming_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "orbx_search_by_projection": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
                                             C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int,
                                             C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -6,6 +6,7 @@
 #include "match_internal.h"
 #include <climits>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #define CUDA_TRYM(expr)                                                                        \
@@ -105,6 +106,66 @@ extern "C" int orbx_knn2_hamming(int device, const uint8_t* q, int nq, const uin
     CUDA_TRYW(cudaStreamSynchronize(W.s));
     memcpy(out_idx, W.h + o_idx, (size_t)nq * 8);
     memcpy(out_dist, W.h + o_dist, (size_t)nq * 8);
+    return ORBX_OK;
+}
+
+// ---- brute-force 2-NN without any allocation (no counterpart in the reference) ----
+// Same two kernels as orbx_knn2_hamming, but the (split, query) partial table lives in a file-scope device array
+// instead of the grow-only workspace arena, and descriptors / results are the CALLER's device buffers: the entry
+// point calls no cudaMalloc / cudaFree / cudaMallocHost and creates no stream.  For callers that cannot allocate:
+// code under CUDA graph capture, tight serving loops, harnesses that forbid it.
+// The array is shared by every call on a device and keeps the last call's contents.  Nothing in it has to start at
+// zero: knn2_merge_kernel reads exactly the nsplit x nq entries that the knn2_partial_kernel launch in front of it
+// (same stream) has written in this call.  Calls that overlap on the GPU (two streams, two host threads) RACE on it.
+#define KNN2_NOALLOC_MAX_QUERIES 16384                       // = ORBX_KNN2_NOALLOC_MAX_QUERIES (include/orbx.h)
+#define KNN2_NOALLOC_PARTIALS (16 * KNN2_NOALLOC_MAX_QUERIES) // int4 entries: 4 MiB per GPU that loads the library
+static __device__ __align__(256) int4 g_knn2_noalloc_scratch[KNN2_NOALLOC_PARTIALS];
+
+#define KNN2_NOALLOC_MAX_DEVICES 64
+static int4* g_knn2_noalloc_ptr[KNN2_NOALLOC_MAX_DEVICES];   // device address of the array, per device (host code
+static std::mutex g_knn2_noalloc_mutex;                      // must not pass the symbol itself to a kernel)
+
+// set-up, once per device, with that device current
+static int knn2_noalloc_scratch(int device, int4** out)
+{
+    std::lock_guard<std::mutex> lock(g_knn2_noalloc_mutex);
+    if (!g_knn2_noalloc_ptr[device]) {
+        int4* p = nullptr;
+        CUDA_TRYW(cudaGetSymbolAddress((void**)&p, g_knn2_noalloc_scratch));
+        if (!p) { orbx_set_error("cudaGetSymbolAddress returned a null scratch address on device %d", device); return ORBX_ERR_CUDA; }
+        g_knn2_noalloc_ptr[device] = p;
+    }
+    *out = g_knn2_noalloc_ptr[device];
+    return ORBX_OK;
+}
+
+extern "C" int orbx_knn2_hamming_noalloc(int device, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt,
+                                         int32_t* d_out_idx, int32_t* d_out_dist, void* stream)
+{
+    if (nq < 0 || nt < 0 || (nq > 0 && (!d_q || !d_out_idx || !d_out_dist)) || (nt > 0 && !d_t)) { orbx_set_error("bad knn2 arguments"); return ORBX_ERR_ARG; }
+    if (nq > KNN2_NOALLOC_MAX_QUERIES) {
+        orbx_set_error("orbx_knn2_hamming_noalloc: %d query descriptors exceed the fixed scratch (max %d); use orbx_knn2_hamming", nq, KNN2_NOALLOC_MAX_QUERIES);
+        return ORBX_ERR_CAPACITY;
+    }
+    if (((uintptr_t)d_q | (uintptr_t)d_t) & 15) { orbx_set_error("orbx_knn2_hamming_noalloc: descriptor arrays must be 16-byte aligned"); return ORBX_ERR_ARG; }
+    if (device < 0 || device >= orbx_device_count() || device >= KNN2_NOALLOC_MAX_DEVICES) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
+    CUDA_TRYW(cudaSetDevice(device));
+    int4* part = nullptr;
+    const int rc = knn2_noalloc_scratch(device, &part);
+    if (rc != ORBX_OK) return rc;
+    if (nq == 0) return ORBX_OK;                                      // set-up only (call once outside a capture)
+    const int tiles = (nq + KNN_THREADS - 1) / KNN_THREADS;
+    int nsplit = (8 * 148 + tiles - 1) / tiles;                       // same split rule as orbx_knn2_hamming ...
+    const int max_split = nt > 0 ? (nt + 63) / 64 : 1;
+    if (nsplit > max_split) nsplit = max_split;
+    if (nsplit > KNN2_NOALLOC_PARTIALS / nq) nsplit = KNN2_NOALLOC_PARTIALS / nq;   // ... capped by the scratch (>= 16)
+    if (nsplit < 1) nsplit = 1;
+    const int per_split = nt > 0 ? (nt + nsplit - 1) / nsplit : 1;
+    nsplit = nt > 0 ? (nt + per_split - 1) / per_split : 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    knn2_partial_kernel<<<dim3(tiles, nsplit), KNN_THREADS, 0, s>>>((const uint4*)d_q, nq, (const uint4*)d_t, nt, per_split, part);
+    knn2_merge_kernel<<<tiles, KNN_THREADS, 0, s>>>(part, nq, nsplit, d_out_idx, d_out_dist);
+    CUDA_TRYW(cudaGetLastError());
     return ORBX_OK;
 }
 
