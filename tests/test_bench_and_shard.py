@@ -26,7 +26,9 @@ def test_reference_arm_json_contract():
     assert len(lines) == 1
     j = json.loads(lines[0])
     assert REQUIRED <= set(j) and j["impl"] == "reference" and j["unit"] == "frames/s" and j["value"] > 0
-    assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1
+    assert j["cpu_baseline"]["kind"] in ("reference", "port") and j["cpu_baseline"]["cores"] >= 1
+    if (ROOT / "oracle" / "_ref" / "libref_native.so").exists():
+        assert j["cpu_baseline"]["kind"] == "reference" and j["cpu_baseline"]["port_vs_cv2"] > 0
     assert j["e2e"]["h2d_bytes_per_step"] == 0 and j["e2e"]["value"] == j["value"]
     assert "752x480" in j["config"]["workload"] and j["vs_baseline"] is None
 
