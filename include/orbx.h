@@ -169,7 +169,10 @@ int orbx_hamming256(const void* a, const void* b);
  * eL and eR (frame slot `frame` of each).  uRight/depth: N_left floats (mvuRight, mvDepth). */
 int orbx_stereo_match(orbx_extractor* eL, orbx_extractor* eR, int frame, float mb, float mbf,
                       float* uRight, float* depth, int cap);
-/* batch twin: all frames of the last extract; outputs at uRight + f*cap, depth + f*cap. */
+/* batch twin: all frames of the last extract; outputs at uRight + f*cap, depth + f*cap.  The frames of a batch stay
+ * resident (frame f in device slot f) as long as the batch fits the handle's frame slots (up to 512, bounded by an
+ * 8 GB footprint); a larger batch reuses the slots chunk by chunk and leaves NOTHING resident: this call, the
+ * per-frame variant, orbx_get_pyramid_level and the debug getters then return ORBX_ERR_STATE. */
 int orbx_stereo_match_batch(orbx_extractor* eL, orbx_extractor* eR, float mb, float mbf,
                             float* uRight, float* depth, int cap);
 /* resident variant (results stay on device; for kernel timing) */

@@ -74,6 +74,7 @@ extern "C" int orbx_create(int nfeatures, float scaleFactor, int nlevels, int in
     if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->stream_d2h, cudaStreamNonBlocking);
     for (int i = 0; i <= ORBX_NSTAGES && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->ev[i]);
     for (int i = 0; i < 2 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->tev[i]);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->join_ev, cudaEventDisableTiming);
     if (ce != cudaSuccess) {
         orbx_set_error("CUDA init failed: %s", cudaGetErrorString(ce));
         delete e;
@@ -104,6 +105,7 @@ extern "C" void orbx_destroy(orbx_extractor* e)
     if (e->d_raw) cudaFree(e->d_raw);
     for (int i = 0; i <= ORBX_NSTAGES; i++) cudaEventDestroy(e->ev[i]);
     for (int i = 0; i < 2; i++) cudaEventDestroy(e->tev[i]);
+    cudaEventDestroy(e->join_ev);
     for (cudaEvent_t ev : e->ev_up) cudaEventDestroy(ev);
     for (cudaEvent_t ev : e->ev_done) cudaEventDestroy(ev);
     for (cudaEvent_t ev : e->ev_down) cudaEventDestroy(ev);
@@ -167,6 +169,7 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     D.in_pitch = (cols + 15) / 16 * 16;
     D.in_pitch_cap = D.in_pitch + 64;
     int rc = 0;
+    bool geometry_error = false;
     rc |= dev_alloc(e, &D.input, B * rows * D.in_pitch_cap + 64);
     for (int l = 0; l < G.nlevels && !rc; l++) {
         rc |= dev_alloc(e, &G.L[l].pyr, B * G.L[l].plane_bytes);
@@ -199,7 +202,7 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     {
         std::vector<BandDesc> bands;
         G.fast_smem = fast_build_bands(G, &bands, &G.fast_warp_words);
-        if (G.fast_smem < 0) { orbx_set_error("cell rows taller than 127 px are not supported"); rc |= ORBX_ERR_GEOMETRY; G.fast_smem = 0; }
+        if (G.fast_smem < 0) { orbx_set_error("cell rows taller than 127 px are not supported"); geometry_error = true; rc |= ORBX_ERR_GEOMETRY; G.fast_smem = 0; }
         G.bands_per_frame = (int)bands.size();
         BandDesc* db = nullptr;
         if (!rc) rc |= dev_alloc(e, &db, bands.size());
@@ -228,7 +231,11 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     if (!rc) rc |= dev_alloc(e, &D.counts, B * 2);
     if (!rc) rc |= dev_alloc(e, &e->d_uright, B * G.out_cap);
     if (!rc) rc |= dev_alloc(e, &e->d_depth, B * G.out_cap);
-    if (rc) { free_device(e); return ORBX_ERR_CUDA; }
+    if (rc) { free_device(e); return geometry_error ? ORBX_ERR_GEOMETRY : ORBX_ERR_CUDA; }   // keep the cause
+    // a slot that no call has written yet reads as "no keypoints" (stereo / getters on a partly used batch)
+    CUDA_TRY(cudaMemsetAsync(D.counts, 0, sizeof(*D.counts) * B * 2, e->stream));
+    CUDA_TRY(cudaMemsetAsync(D.selcnt, 0, sizeof(*D.selcnt) * B * G.nlevels, e->stream));
+    CUDA_TRY(cudaMemsetAsync(D.candcnt, 0, sizeof(*D.candcnt) * B * G.nlevels, e->stream));
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     e->G = G; e->D = D; e->reserved = true;
     return ORBX_OK;
@@ -611,7 +618,7 @@ static int extract_small(orbx_extractor* e, int nframes, const uint8_t* imgs, si
 // lazy sizing of the handle for rows x cols frames: bound the device footprint to ~8 GB
 static int ensure_reserved(orbx_extractor* e, int rows, int cols, int nframes)
 {
-    if (e->reserved && e->G.rows == rows && e->G.cols == cols) return 0;
+    if (e->reserved && e->G.rows == rows && e->G.cols == cols && (e->G.batch >= nframes || e->G.batch >= e->batch_limit)) return 0;
     FrameGeom G;
     std::vector<std::vector<ResizeTapX>> tx; std::vector<std::vector<ResizeTapY>> ty;
     int r = orbx_compute_geometry(e, rows, cols, 1, &G, &tx, &ty);
@@ -620,8 +627,10 @@ static int ensure_reserved(orbx_extractor* e, int rows, int cols, int nframes)
     for (int l = 0; l < G.nlevels; l++) per += 2 * G.L[l].plane_bytes;
     long long b = (8LL << 30) / per;
     if (b < 1) b = 1;
-    if (b > nframes) b = nframes;
     if (b > 512) b = 512;
+    e->batch_limit = (int)b;                                 // a later, larger batch grows the slots up to here
+    if (b > nframes) b = nframes;
+    if (e->reserved && e->G.rows == rows && e->G.cols == cols && b < e->G.batch) b = e->G.batch;
     return orbx_reserve(e, rows, cols, (int)b);
 }
 
@@ -648,9 +657,14 @@ static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* img
     // for upload(k) and download(k-R) (outputs of the slot copied out), download(k) waits for kernels(k).
     int chunk = 128;
     if (const char* cs = getenv("ORBX_CHUNK")) { const int v = atoi(cs); if (v > 0) chunk = v; }
-    if (chunk > B / 4 && B >= 4) chunk = B / 4;              // at least 4 chunk slots: upload / kernels / download of
-    if (chunk > B) chunk = B;                                //   neighbouring chunks overlap also for small batches of big frames
-    const int R = B / chunk > 0 ? B / chunk : 1;             // chunk slots in the ring
+    // at least 4 chunks: upload / kernels / download of neighbouring chunks overlap also for small batches of big frames
+    const bool laps = nframes > B;                           // more frames than device slots: the slots are reused
+    const int span = laps ? B : nframes;
+    if (chunk > (span + 3) / 4) chunk = (span + 3) / 4;
+    if (chunk < 1) chunk = 1;
+    // A batch that fits keeps frame f in slot f: chunk k sits at slot offset k*chunk and the last one may be short, so
+    // ceil(span/chunk) chunk slots never reach past slot B.  A lapping batch cycles through the floor(B/chunk) whole ones.
+    const int R = laps ? (B / chunk > 0 ? B / chunk : 1) : (span + chunk - 1) / chunk;
     int ncs = ORBX_NCSTREAMS;
     if (const char* cs_ = getenv("ORBX_STREAMS")) { const int v = atoi(cs_); if (v >= 1 && v <= ORBX_NCSTREAMS) ncs = v; }
     while (R % ncs) ncs--;                                   // a slot must always be served by the same compute stream
@@ -704,7 +718,9 @@ static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* img
     }
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     collect_stage_times(e);
-    e->last_nframes = nframes < B ? nframes : B;           // resident pyramids / outputs: the last pass over the slots
+    // resident pyramids / outputs (orbx_stereo_match_batch, orbx_get_pyramid_level, the debug getters): every frame of a
+    // batch that fits; a lapping batch leaves a mix of passes in the slots, so nothing is reported resident
+    e->last_nframes = laps ? 0 : nframes;
     for (int f = 0; f < nframes; f++) {
         if (nkp) nkp[f] = counts[2 * f];
         if (mono) mono[f] = counts[2 * f + 1];

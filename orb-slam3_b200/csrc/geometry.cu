@@ -74,7 +74,6 @@ int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch
         const float scale = e->isf[l];
         L.w = cv_round_f((float)cols * scale);                        // :1669
         L.h = cv_round_f((float)rows * scale);
-        if (L.w + 2 * ORBX_EDGE > 4096 + 2 * ORBX_MINB + 6 && false) return ORBX_ERR_GEOMETRY;
         L.pitch = align_up(ORBX_XOFF + L.w + ORBX_EDGE, 128);
         L.prow = L.h + 2 * ORBX_EDGE;
         L.plane_bytes = (long long)L.pitch * L.prow;
@@ -99,7 +98,6 @@ int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch
         const int mx = (L.N + 3 > 4 * L.nIni ? L.N + 3 : 4 * L.nIni);
         L.sel_cap = mx;
         L.node_cap = align_up(mx + 1, 4);
-        if (L.node_cap > 4096) return ORBX_ERR_GEOMETRY;              // quadtree sort key holds a 12-bit list position
         L.sel_base = sel;
         sel += L.sel_cap;
         L.scale = e->sf[l];

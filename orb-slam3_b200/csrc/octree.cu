@@ -284,22 +284,32 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
             }
             __syncthreads();
         } else {
-            // ordered phase (:909-992): expandable nodes by (size desc, creation desc == position asc)
+            // ordered phase (:909-992): expandable nodes by (size desc, creation desc == position asc).  The compacted
+            // list e = 0..E-1 of expandable nodes is in list order, so "position asc" is "e asc": the sort key is the bare
+            // count, ties go to the smaller e - no bit field limits the list length or the count.  NP4 is free between the
+            // candidate step and the table build: it maps e back to the list position.
             for (int i = tid; i < size; i += OCT_THREADS) { aA[i] = cn[i] > 1; aB[i] = -1; }
             __syncthreads();
             const int E = block_scan_excl(aA, aD, size, s_warp);
             for (int i = tid; i < size; i += OCT_THREADS)
-                if (cn[i] > 1) aC[aD[i]] = (min(cn[i], 0x7FFFF) << 12) | (4095 - i);      // sort key
+                if (cn[i] > 1) { aC[aD[i]] = cn[i]; NP4[aD[i]] = i; }
             __syncthreads();
             for (int e = tid; e < E; e += OCT_THREADS) {
                 const int my = aC[e];
                 int r = 0, j = 0;
+                const int e4 = e & ~3;
+                for (; j < e4; j += 4) {                                     // in front of e: ties rank first
+                    const int4 k4 = *reinterpret_cast<const int4*>(aC + j);
+                    r += (k4.x >= my) + (k4.y >= my) + (k4.z >= my) + (k4.w >= my);
+                }
+                for (; j < e; j++) r += aC[j] >= my;
+                for (j = e + 1; j < E && (j & 3); j++) r += aC[j] > my;      // behind e: only larger counts
                 for (; j + 4 <= E; j += 4) {
                     const int4 k4 = *reinterpret_cast<const int4*>(aC + j);
                     r += (k4.x > my) + (k4.y > my) + (k4.z > my) + (k4.w > my);
                 }
                 for (; j < E; j++) r += aC[j] > my;
-                const int i = 4095 - (my & 4095);
+                const int i = NP4[e];
                 const int4 c4 = *reinterpret_cast<const int4*>(cc + 4 * i);
                 aD[r] = i;                                                   // node processed r-th
                 aE[r] = (c4.x > 0) + (c4.y > 0) + (c4.z > 0) + (c4.w > 0);  // its non-empty children

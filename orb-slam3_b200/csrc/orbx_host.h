@@ -36,10 +36,12 @@ struct orbx_extractor {
     std::vector<void*> allocs;           // every cudaMalloc of this handle
     cudaEvent_t ev[ORBX_NSTAGES + 1];
     cudaEvent_t tev[2];                  // stopwatch (orbx_timer_start/stop)
+    cudaEvent_t join_ev;                 // stereo: orders the left handle's stream behind this (right) handle's
     bool profiling;
     float stage_ms[ORBX_NSTAGES + 1];    // [ORBX_NSTAGES] = total
     long long launches;
     int last_nframes;                    // frames processed by the last run (valid pyramids / outputs)
+    int batch_limit = 512;               // most frame slots ensure_reserved may give this geometry (8 GB bound)
     // stereo-match outputs (device), sized out_cap per frame slot
     float* d_uright; float* d_depth;
     int* d_st_scratch;

@@ -353,7 +353,7 @@ extern "C" int orbx_stereo_match_resident(orbx_extractor* eL, orbx_extractor* eR
     if (r) return r;
     if (cudaSetDevice(eL->device) != cudaSuccess) { orbx_set_error("cudaSetDevice failed"); return ORBX_ERR_CUDA; }
     // order after both extractions: the right handle has its own stream
-    cudaEvent_t ev = eR->ev[ORBX_NSTAGES];
+    cudaEvent_t ev = eR->join_ev;                 // not a profiling event: eR's stage times stay intact
     cudaEventRecord(ev, eR->stream);
     cudaStreamWaitEvent(eL->stream, ev, 0);
     const int nf = eL->last_nframes;

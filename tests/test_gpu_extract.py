@@ -75,6 +75,36 @@ def test_batch_equals_single(pkg, orc, oracle):
     X.close()
 
 
+def test_batch_larger_than_device_slots(pkg, orc, oracle):
+    """More frames than the handle keeps slots for (512): the slots are reused chunk by chunk.  Host results must be
+    right for every frame; nothing is reported resident afterwards (ORBX_ERR_STATE instead of another frame's data)."""
+    rows, cols, nf, n = 256, 320, 300, 530
+    base = np.stack([pkg.synth.synth_frame(rows, cols, 300 + s, bands=False) for s in range(7)])
+    frames = np.ascontiguousarray(base[np.arange(n) % 7])
+    X = pkg.ORBextractor(nf)
+    mono, nkp, kps, desc = X.extract_batch(frames, (0, 0))
+    E = orc.Extractor(nf, oracle=oracle)
+    ref = [E(base[i], (0, 0)) for i in range(7)]
+    assert min(len(r[1]) for r in ref) > 20
+    for f in range(n):
+        m, k, d = ref[f % 7]
+        assert mono[f] == m and nkp[f] == len(k), f"frame {f}"
+        assert np.array_equal(kps[f, :nkp[f]], k) and np.array_equal(desc[f, :nkp[f]], d), f"frame {f}"
+    with pytest.raises(pkg.OrbxError) as ei:
+        X.pyramid_level(0, frame=0)
+    assert ei.value.code == pkg.binding.ORBX_ERR_STATE
+    # a batch that fits is resident again, frame f in slot f
+    mono, nkp, kps, desc = X.extract_batch(frames[:13], (0, 0))
+    for f in (0, 5, 12):
+        assert np.array_equal(X.pyramid_level(2, frame=f), E_level(E, base[f % 7], 2))
+    X.close()
+
+
+def E_level(E, img, level):
+    E(img, (0, 0))
+    return E.level_plane(level)[19:-19, 19:-19]
+
+
 def test_flat_and_low_texture_frames(pkg, orc, oracle):
     """Empty cells, minThFAST retries and levels with no keypoints at all."""
     rows, cols = 480, 752
@@ -123,6 +153,43 @@ def test_large_frames_match_oracle(pkg, orc, oracle, name, rows, cols, nf):
     assert mono_g == mono_o and len(kps_g) == len(kps_o) >= nf
     assert np.array_equal(kps_g, kps_o) and np.array_equal(desc_g, desc_o)
     X.close()
+
+
+def test_ini_extractor_of_c5_40000_features(pkg, orc, oracle):
+    """The mono "Ini" extractor is 5 x nFeatures (reference src/Tracking.cc:1113): C5's 8000 features -> 40 000, level-0
+    quota 8687 > 4093, which the quadtree's packed sort key used to refuse (ORBX_ERR_GEOMETRY)."""
+    img = pkg.synth.synth_frame(2160, 3840, 23)
+    nf = 40000
+    E = orc.Extractor(nf, oracle=oracle)
+    mono_o, kps_o, desc_o = E(img, (0, 1000))
+    X = pkg.ORBextractor(nf)
+    assert X.features_per_level()[0] > 4093
+    mono_g, kps_g, desc_g = X(img, (0, 1000))
+    for l in range(8):
+        sel_g, ang_g = X.level_keys(l, 1)
+        sel_o, ang_o = E.level_selected(l)
+        assert np.array_equal(sel_g, _cand_arr(sel_o)), f"quadtree selection level {l}"
+    assert mono_g == mono_o and len(kps_g) == len(kps_o) >= nf
+    assert np.array_equal(kps_g, kps_o) and np.array_equal(desc_g, desc_o)
+    X.close()
+
+
+def test_equal_count_ties_in_the_ordered_phase(pkg, orc, oracle):
+    """A regular dot pattern: many quadtree nodes hold the SAME number of candidates when the ordered final phase
+    (:909-992) starts, so the split order is decided by the tie-break (count desc, then list position)."""
+    rows, cols = 480, 752
+    img = np.full((rows, cols), 60, np.uint8)
+    for y in range(28, rows - 28, 12):
+        for x in range(28, cols - 28, 12):
+            img[y:y + 3, x:x + 3] = 200
+    for nf in (300, 1000, 2500):
+        X = pkg.ORBextractor(nf)
+        E = orc.Extractor(nf, oracle=oracle)
+        mg, kg, dg = X(img, (0, 0))
+        mo, ko, do = E(img, (0, 0))
+        assert len(ko) > 100
+        assert mg == mo and np.array_equal(kg, ko) and np.array_equal(dg, do), nf
+        X.close()
 
 
 @pytest.mark.parametrize("npatch,patch,nf,seed", [(20, 24, 2000, 1), (6, 48, 1000, 2), (40, 15, 3000, 3)])

@@ -37,6 +37,35 @@ def test_stereo_kitti(pkg, orc, oracle):
     assert _stereo_case(pkg, orc, oracle, "C4", 21, nframes=2) > 300
 
 
+@pytest.mark.parametrize("nframes", [9, 11])
+def test_stereo_batch_odd_sizes_stay_resident(pkg, orc, oracle, nframes):
+    """Batch sizes that do not divide into equal chunks (9 = 3+3+3, 11 = 3+3+3+2): every frame must sit in its own
+    device slot after orbx_extract_batch, for orbx_stereo_match_batch and the pyramid getter alike."""
+    assert _stereo_case(pkg, orc, oracle, "C2", 40 + nframes, nframes=nframes) > 100 * nframes
+
+
+def test_stereo_after_handle_growth(pkg, orc, oracle):
+    """A handle first used for ONE frame must serve a later 6-pair batch with all pairs resident (the slots grow)."""
+    c = pkg.synth.CONFIGS["C2"]
+    rows, cols, nf = c["rows"], c["cols"], c["nfeatures"]
+    mbf = c["mbf"]; mb = mbf / c["fx"]
+    XL, XR = pkg.ORBextractor(nf), pkg.ORBextractor(nf)
+    l0, r0 = pkg.synth.synth_stereo_pair(rows, cols, 70)
+    XL(l0); XR(r0)
+    pairs = [pkg.synth.synth_stereo_pair(rows, cols, 71 + i) for i in range(6)]
+    L = np.stack([p[0] for p in pairs]); R = np.stack([p[1] for p in pairs])
+    _, nL, kL, dL = XL.extract_batch(L, (0, 0))
+    _, nR, kR, dR = XR.extract_batch(R, (0, 0))
+    uR, depth = pkg.ComputeStereoMatches(XL, XR, mb, mbf, frame=None)
+    EL, ER = orc.Extractor(nf, oracle=oracle), orc.Extractor(nf, oracle=oracle)
+    for f in (0, 5):
+        _, kl, dl = EL(L[f], (0, 0)); _, kr, dr = ER(R[f], (0, 0))
+        u_o, d_o, _, _ = orc.stereo_match(EL, ER, kl, dl, kr, dr, mb, mbf)
+        assert np.array_equal(uR[f, :nL[f]], u_o) and np.array_equal(depth[f, :nL[f]], d_o)
+        assert np.array_equal(XL.pyramid_level(3, frame=f), EL.level_plane(3)[19:-19, 19:-19])
+    XL.close(); XR.close()
+
+
 def test_stereo_single_frame_api(pkg, orc, oracle):
     c = pkg.synth.CONFIGS["C2"]
     l, r = pkg.synth.synth_stereo_pair(c["rows"], c["cols"], 5)
