@@ -447,6 +447,69 @@ int orbx_search_by_sim3(int device,
  * include/ORBmatcher.h:107, src/ORBmatcher.cc:2863-2905 on the bin sizes (host, no device work). */
 void orbx_three_maxima(const int32_t* sizes, int L, int32_t* ind1, int32_t* ind2, int32_t* ind3);
 
+/* ---- two-camera rig (Frame::Nleft != -1: KannalaBrandt stereo, e.g. TUM-VI = config C3) ----------------------- */
+
+/* int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono)
+ * include/ORBmatcher.h:50, src/ORBmatcher.cc:2469-2711, branch CurrentFrame.Nleft != -1 (left half :2540-2601, right
+ * half :2610-2684).  kpsL = mvKeys (nL = Nleft), kpsR = mvKeysRight (nR); desc / cur_held / assign are indexed like
+ * mvpMapPoints and mDescriptors: left keypoint i at i, right keypoint j at nL + j.  Per last-frame point the caller
+ * supplies the projection into the left camera (last_u, last_v; :2516) and that of Trl * x3Dc (last_ur, last_vr;
+ * :2613-2616), invzc, the octave the reference picks at :2530, the last keypoint's angle (:2583-2585), valid = pMP &&
+ * !mvbOutlier, obs = Observations() > 0.  Returns nmatches. */
+int orbx_search_by_projection_frame_rig(int device,
+                                        const orbx_keypoint* kpsL, int nL, const orbx_keypoint* kpsR, int nR, const uint8_t* desc,
+                                        float minX, float maxX, float minY, float maxY,
+                                        const float* scaleFactors, int nlevels,
+                                        int nlast, const uint8_t* last_desc, const float* last_u, const float* last_v,
+                                        const float* last_ur, const float* last_vr,
+                                        const float* last_invz, const int32_t* last_octave, const float* last_angle,
+                                        const uint8_t* last_valid, const uint8_t* last_obs,
+                                        float th, int bForward, int bBackward, int checkOrientation,
+                                        const uint8_t* cur_held, int32_t* assign);
+
+/* int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>&), src/ORBmatcher.cc:314-547, branch
+ * F.Nleft != -1 (:386-430, :455-486): Frame rows < nleft2 are left-camera keypoints, the rest right-camera ones
+ * (kps2 carries mvKeys / mvKeysRight angles accordingly, kps1 the keyframe's, :437-448).  Otherwise as
+ * orbx_search_by_bow(mode 0).  matches[n2] out. */
+int orbx_search_by_bow_rig(int device,
+                           const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,
+                           const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                           const orbx_keypoint* kps2, const uint8_t* desc2, int n2, int nleft2,
+                           const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                           float nnratio, int checkOrientation, int32_t* matches);
+
+/* The triangulation searches whose geometric test is the camera model's own code (KannalaBrandt8: an SVD
+ * triangulation, src/CameraModels/KannalaBrandt8.cpp:350-457), which stays the caller's:
+ *   overload 0  SearchForTriangulation   include/ORBmatcher.h:74, src/ORBmatcher.cc:1107-1386, branch pKF1->mpCamera2 &&
+ *               pKF2->mpCamera2 (:1252-1279; verdict = pCamera1->epipolarConstrain(pCamera2, kp1, kp2, R12, t12, ...))
+ *   overload 1  SearchForTriangulation_  include/ORBmatcher.h:77, :1388-1630, same branch (epipolarConstrain_)
+ *   overload 2  SearchForTriangulation(..., vector<cv::Mat>& vMatchedPoints)  include/ORBmatcher.h:80, :1632-1821
+ *               (verdict = pCamera1->matchAndtriangulate(...), :1729; caller src/Tracking.cc:4739)
+ * `verdict(user, idx1, idx2)` (non-zero = accepted) is called from the calling thread in exactly the reference's call
+ * order: per KF1 keypoint in FeatureVector order, for the KF2 keypoints under the same node with no map point, not
+ * matched before (overload 0 only), dist <= TH_LOW and dist <= the best accepted so far.  A callback that stores its
+ * 3-D point per idx1 on acceptance reproduces vMatchedPoints.  bOnlyStereo (overloads 0, 1) yields no match with a rig
+ * (:1194); bCoarse accepts without calling.  has_mp1 / has_mp2: the keypoint already holds a map point.  matches12[n1]. */
+typedef int (*orbx_pair_verdict_fn)(void* user, int idx1, int idx2);
+int orbx_search_for_triangulation_cb(int device, int overload,
+                                     const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
+                                     const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                                     const orbx_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* has_mp2,
+                                     const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                                     int bOnlyStereo, int bCoarse, int checkOrientation,
+                                     orbx_pair_verdict_fn verdict, void* user, int32_t* matches12);
+
+/* void Frame::ComputeStereoFishEyeMatches() include/Frame.h:304, src/Frame.cc:1440-1480, up to the triangulation gate:
+ * knnMatch(k = 2) between rows [monoLeft, nL) of eL's and rows [monoRight, nR) of eR's descriptors of frame slot
+ * `frame` - the matrices the two preceding orbx_extract calls left ON THE DEVICE (nL / nR = their keypoint counts,
+ * monoLeft / monoRight = their return values, :1445-1446) - and Lowe's ratio test d0 < d1 * 0.7 (:1465).
+ * l2r[nL] / r2l[nR] out: candidate mvLeftToRightMatch / mvRightToLeftMatch in full-frame indices (-1 = none; the
+ * caller applies TriangulateMatches > 0.0001, :1471); best_dist[nL] (may be NULL) the winning distance.
+ * Returns the number of pairs that pass the ratio test (descMatches). */
+int orbx_stereo_fisheye_match(orbx_extractor* eL, orbx_extractor* eR, int frame, int nL, int monoLeft, int nR, int monoRight,
+                              int32_t* l2r, int32_t* r2l, int32_t* best_dist);
+
+
 #ifdef __cplusplus
 }
 #endif

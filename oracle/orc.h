@@ -215,6 +215,32 @@ int   orc_search_by_bow(int mode,
                         const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
                         float nnratio, int checkOrientation, int32_t* matches);
 
+/* ---- two-camera rig branches, callback-driven triangulation searches, fisheye stereo (orc_match.c, bottom) ---- */
+typedef int (*orc_pair_verdict_fn)(void* user, int idx1, int idx2);
+int   orc_search_by_projection_frame_rig(const orc_grid* gL, const orc_keypoint* kpsL, int nL,
+                                         const orc_grid* gR, const orc_keypoint* kpsR, int nR,
+                                         const uint8_t* desc, const float* sf,
+                                         int nlast, const uint8_t* last_desc, const float* last_u, const float* last_v,
+                                         const float* last_ur, const float* last_vr,
+                                         const float* last_invz, const int32_t* last_octave, const float* last_angle,
+                                         const uint8_t* last_valid, const uint8_t* last_obs,
+                                         float th, int bForward, int bBackward, int checkOrientation,
+                                         const uint8_t* cur_held, int32_t* assign);
+int   orc_search_by_bow_rig(const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,
+                            const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                            const orc_keypoint* kps2, const uint8_t* desc2, int n2, int nleft2,
+                            const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                            float nnratio, int checkOrientation, int32_t* matches);
+int   orc_search_for_triangulation_cb(int overload,
+                                      const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
+                                      const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                                      const orc_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* has_mp2,
+                                      const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                                      int bOnlyStereo, int bCoarse, int checkOrientation,
+                                      orc_pair_verdict_fn verdict, void* user, int32_t* matches12);
+int   orc_stereo_fisheye_match(const uint8_t* descL, int nL, int monoLeft, const uint8_t* descR, int nR, int monoRight,
+                               int32_t* l2r, int32_t* r2l, int32_t* dist_out);
+
 #ifdef __cplusplus
 }
 #endif

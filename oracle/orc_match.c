@@ -972,3 +972,244 @@ int orc_search_by_projection_rig(const orc_grid* gL, const orc_keypoint* kpsL, i
     free(vIndices);
     return nmatches;
 }
+
+/* ===== two-camera rig (Nleft != -1) branches and the callback-driven triangulation searches ===== */
+
+/* ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono), src/ORBmatcher.cc:2469-2711,
+ * branch CurrentFrame.Nleft != -1 (KannalaBrandt stereo rig, config C3).  Keypoints: kpsL = mvKeys (nL = Nleft, grid gL =
+ * mGrid), kpsR = mvKeysRight (nR, grid gR = mGridRight); desc / cur_held / assign are indexed like mvpMapPoints:
+ * left keypoint i at i, right keypoint j at nL + j.  Per last-frame point the caller supplies both projections:
+ * (last_u, last_v) into the left camera (:2516) and (last_ur, last_vr) of Trl * x3Dc (:2613-2616), plus invzc, octave
+ * (:2530, picks mvKeys / mvKeysRight of the LAST frame), the last keypoint's angle, valid = pMP && !outlier, obs.
+ * Quirks kept: a point whose LEFT window is empty skips its right half as well (`continue`, :2541); there is no stereo
+ * gate (Nleft != -1, :2556) and no image-bounds test on the right projection. */
+int orc_search_by_projection_frame_rig(const orc_grid* gL, const orc_keypoint* kpsL, int nL,
+                                       const orc_grid* gR, const orc_keypoint* kpsR, int nR,
+                                       const uint8_t* desc, const float* sf,
+                                       int nlast, const uint8_t* last_desc, const float* last_u, const float* last_v,
+                                       const float* last_ur, const float* last_vr,
+                                       const float* last_invz, const int32_t* last_octave, const float* last_angle,
+                                       const uint8_t* last_valid, const uint8_t* last_obs,
+                                       float th, int bForward, int bBackward, int checkOrientation,
+                                       const uint8_t* cur_held, int32_t* assign)
+{
+    const int n = nL + nR;
+    int nmatches = 0;
+    rot_hist H; hist_init(&H);
+    const float factor = HISTO_LENGTH / 360.0f;                               /* :2480 */
+    uint8_t* held = (uint8_t*)calloc((size_t)(n > 0 ? n : 1), 1);
+    int32_t* vIndices2 = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; i++) { assign[i] = -1; if (cur_held) held[i] = cur_held[i] != 0; }
+    for (int i = 0; i < nlast; i++) {
+        if (!last_valid[i]) continue;                                         /* :2503-2506 */
+        if (last_invz[i] < 0) continue;                                       /* :2515 */
+        const float u = last_u[i], v = last_v[i];
+        if (u < gL->minX || u > gL->maxX) continue;                           /* :2520-2523 */
+        if (v < gL->minY || v > gL->maxY) continue;
+        const int nLastOctave = last_octave[i];
+        const float radius = th * sf[nLastOctave];                            /* :2529 */
+        int nc;
+        if (bForward) nc = orc_grid_query(gL, kpsL, u, v, radius, nLastOctave, -1, vIndices2, n);
+        else if (bBackward) nc = orc_grid_query(gL, kpsL, u, v, radius, 0, nLastOctave, vIndices2, n);
+        else nc = orc_grid_query(gL, kpsL, u, v, radius, nLastOctave - 1, nLastOctave + 1, vIndices2, n);
+        if (nc == 0) continue;                                                /* :2541: also skips the right camera */
+        int bestDist = 256, bestIdx2 = -1;
+        for (int k = 0; k < nc; k++) {                                        /* :2548-2574 */
+            const int i2 = vIndices2[k];
+            if (held[i2]) continue;
+            const int dist = orc_hamming256(last_desc + 32 * (size_t)i, desc + 32 * (size_t)i2);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {                                            /* :2576-2601 */
+            assign[bestIdx2] = i;
+            held[bestIdx2] = last_obs[i] != 0;
+            nmatches++;
+            if (checkOrientation) hist_push(&H, hist_bin(last_angle[i], kpsL[bestIdx2].angle, factor), bestIdx2);
+        }
+        /* right camera, :2610-2684 */
+        const float ur = last_ur[i], vr = last_vr[i];
+        if (bForward) nc = orc_grid_query(gR, kpsR, ur, vr, radius, nLastOctave, -1, vIndices2, n);
+        else if (bBackward) nc = orc_grid_query(gR, kpsR, ur, vr, radius, 0, nLastOctave, vIndices2, n);
+        else nc = orc_grid_query(gR, kpsR, ur, vr, radius, nLastOctave - 1, nLastOctave + 1, vIndices2, n);
+        bestDist = 256; bestIdx2 = -1;
+        for (int k = 0; k < nc; k++) {
+            const int i2 = vIndices2[k];
+            if (held[i2 + nL]) continue;                                      /* :2640-2642 */
+            const int dist = orc_hamming256(last_desc + 32 * (size_t)i, desc + 32 * (size_t)(i2 + nL));
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {                                            /* :2658-2683 */
+            assign[bestIdx2 + nL] = i;
+            held[bestIdx2 + nL] = last_obs[i] != 0;
+            nmatches++;
+            if (checkOrientation) hist_push(&H, hist_bin(last_angle[i], kpsR[bestIdx2].angle, factor), bestIdx2 + nL);
+        }
+    }
+    if (checkOrientation) {                                                   /* :2686-2708 */
+        int ind1, ind2, ind3;
+        orc_three_maxima(H.n, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int b = 0; b < HISTO_LENGTH; b++)
+            if (b != ind1 && b != ind2 && b != ind3)
+                for (int j = 0; j < H.n[b]; j++) { assign[H.v[b][j]] = -1; nmatches--; }
+    }
+    hist_free(&H); free(held); free(vIndices2);
+    return nmatches;
+}
+
+/* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&), src/ORBmatcher.cc:314-547, branch F.Nleft != -1:
+ * Frame rows < nleft2 are left-camera keypoints, the others right-camera ones; best / second are kept per camera
+ * (:380-430).  Quirks kept: the right-camera match is only considered when the LEFT best passed TH_LOW (:431, the block
+ * at :455 is nested in it) and ignores its own ratio test (`|| true`, :457).  kps1 / kps2 carry the angles the reference
+ * picks (:437-448, :459-470: mvKeys / mvKeysRight by index).  matches[n2] out: KF keypoint per Frame keypoint. */
+int orc_search_by_bow_rig(const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,
+                          const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                          const orc_keypoint* kps2, const uint8_t* desc2, int n2, int nleft2,
+                          const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                          float nnratio, int checkOrientation, int32_t* matches)
+{
+    int nmatches = 0;
+    rot_hist H; hist_init(&H);
+    const float factor = HISTO_LENGTH / 360.0f;                               /* :334 */
+    uint8_t* matched2 = (uint8_t*)calloc((size_t)(n2 > 0 ? n2 : 1), 1);
+    for (int i = 0; i < n2; i++) matches[i] = -1;
+    int a = 0, b = 0;
+    while (a < nn1 && b < nn2) {
+        if (fv1_node[a] < fv2_node[b]) { a++; continue; }
+        if (fv1_node[a] > fv2_node[b]) { b++; continue; }
+        for (int p1 = fv1_start[a]; p1 < fv1_start[a + 1]; p1++) {
+            const int idx1 = fv1_idx[p1];
+            if (!valid1[idx1]) continue;                                      /* :343-349 */
+            int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+            int bestDist1R = 256, bestIdxFR = -1, bestDist2R = 256;
+            for (int p2 = fv2_start[b]; p2 < fv2_start[b + 1]; p2++) {
+                const int idx2 = fv2_idx[p2];
+                if (matched2[idx2]) continue;                                 /* :390 */
+                const int dist = orc_hamming256(desc1 + 32 * (size_t)idx1, desc2 + 32 * (size_t)idx2);
+                if (idx2 < nleft2 && dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = idx2; }
+                else if (idx2 < nleft2 && dist < bestDist2) bestDist2 = dist;
+                if (idx2 >= nleft2 && dist < bestDist1R) { bestDist2R = bestDist1R; bestDist1R = dist; bestIdxFR = idx2; }
+                else if (idx2 >= nleft2 && dist < bestDist2R) bestDist2R = dist;
+            }
+            if (bestDist1 <= TH_LOW) {                                        /* :431 */
+                if ((float)bestDist1 < nnratio * (float)bestDist2) {          /* :433 */
+                    matches[bestIdxF] = idx1; matched2[bestIdxF] = 1;
+                    if (checkOrientation) hist_push(&H, hist_bin(kps1[idx1].angle, kps2[bestIdxF].angle, factor), bestIdxF);
+                    nmatches++;
+                }
+                if (bestDist1R <= TH_LOW) {                                   /* :455-457: ratio test disabled by `|| true` */
+                    matches[bestIdxFR] = idx1; matched2[bestIdxFR] = 1;
+                    if (checkOrientation) hist_push(&H, hist_bin(kps1[idx1].angle, kps2[bestIdxFR].angle, factor), bestIdxFR);
+                    nmatches++;
+                }
+            }
+        }
+        a++; b++;
+    }
+    if (checkOrientation) {                                                   /* :520-544 */
+        int ind1, ind2, ind3;
+        orc_three_maxima(H.n, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int bi = 0; bi < HISTO_LENGTH; bi++) {
+            if (bi == ind1 || bi == ind2 || bi == ind3) continue;
+            for (int j = 0; j < H.n[bi]; j++) { matches[H.v[bi][j]] = -1; nmatches--; }
+        }
+    }
+    hist_free(&H); free(matched2);
+    return nmatches;
+}
+
+/* The triangulation searches whose geometric verdict is the camera model's own (caller-side) code:
+ *   overload 0  SearchForTriangulation  src/ORBmatcher.cc:1107-1386, branch pKF1->mpCamera2 && pKF2->mpCamera2
+ *               (verdict = pCamera1->epipolarConstrain(...) with the Rll/Rlr/Rrl/Rrr pose picked at :1252-1279)
+ *   overload 1  SearchForTriangulation_ :1388-1630, same branch (epipolarConstrain_)
+ *   overload 2  SearchForTriangulation(..., vector<cv::Mat>& vMatchedPoints) :1632-1821
+ *               (verdict = pCamera1->matchAndtriangulate(...), which also yields the 3-D point)
+ * verdict(user, idx1, idx2) is called exactly where the reference calls the camera model: for the candidates of idx1 in
+ * FeatureVector order that pass `!vbMatched2 && !pMP2`, `dist <= TH_LOW && dist <= bestDist`.  With a rig bStereo1 /
+ * bStereo2 are false (:1194, :1222), so bOnlyStereo leaves no candidate and the epipole gate (:1241) is off.
+ * Differences kept: overload 0 marks vbMatched2 (:1297) and un-marks it in the histogram filter (:1362), 1 and 2 never
+ * mark it; the histogram factor is 30/360 in overload 0 and 1/30 in 1 and 2 (:1166 / :1441 / :1666); bCoarse accepts
+ * without asking (overloads 0, 1). */
+int orc_search_for_triangulation_cb(int overload,
+                                    const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
+                                    const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                                    const orc_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* has_mp2,
+                                    const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                                    int bOnlyStereo, int bCoarse, int checkOrientation,
+                                    orc_pair_verdict_fn verdict, void* user, int32_t* matches12)
+{
+    int nmatches = 0;
+    rot_hist H; hist_init(&H);
+    const float factor = overload == 0 ? HISTO_LENGTH / 360.0f : 1.0f / HISTO_LENGTH;
+    uint8_t* vbMatched2 = (uint8_t*)calloc((size_t)(n2 > 0 ? n2 : 1), 1);
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    int a = 0, b = 0;
+    while (a < nn1 && b < nn2) {
+        if (fv1_node[a] < fv2_node[b]) { a++; continue; }
+        if (fv1_node[a] > fv2_node[b]) { b++; continue; }
+        for (int p1 = fv1_start[a]; p1 < fv1_start[a + 1]; p1++) {
+            const int idx1 = fv1_idx[p1];
+            if (has_mp1[idx1]) continue;                                      /* :1188-1192 / :1682-1684 */
+            if (overload != 2 && bOnlyStereo) continue;                       /* :1194-1198: bStereo1 is false with a rig */
+            int bestDist = TH_LOW, bestIdx2 = -1;
+            for (int p2 = fv2_start[b]; p2 < fv2_start[b + 1]; p2++) {
+                const int idx2 = fv2_idx[p2];
+                if (vbMatched2[idx2] || has_mp2[idx2]) continue;              /* :1218 / :1701 */
+                const int dist = orc_hamming256(desc1 + 32 * (size_t)idx1, desc2 + 32 * (size_t)idx2);
+                if (dist > TH_LOW || dist > bestDist) continue;               /* :1231 / :1707 */
+                int ok;
+                if (overload != 2 && bCoarse) ok = 1;                         /* :1282 `|| bCoarse` */
+                else ok = verdict(user, idx1, idx2) != 0;
+                if (ok) { bestIdx2 = idx2; bestDist = dist; }
+            }
+            if (bestIdx2 >= 0) {
+                matches12[idx1] = bestIdx2;
+                if (overload == 0) vbMatched2[bestIdx2] = 1;                  /* :1297 */
+                nmatches++;
+                if (checkOrientation) hist_push(&H, hist_bin(kps1[idx1].angle, kps2[bestIdx2].angle, factor), idx1);
+            }
+        }
+        a++; b++;
+    }
+    if (checkOrientation) {
+        int ind1, ind2, ind3;
+        orc_three_maxima(H.n, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int bi = 0; bi < HISTO_LENGTH; bi++) {
+            if (bi == ind1 || bi == ind2 || bi == ind3) continue;
+            for (int j = 0; j < H.n[bi]; j++) {
+                if (overload == 0) vbMatched2[matches12[H.v[bi][j]]] = 0;     /* :1362 */
+                matches12[H.v[bi][j]] = -1; nmatches--;
+            }
+        }
+    }
+    hist_free(&H); free(vbMatched2);
+    return nmatches;
+}
+
+/* Frame::ComputeStereoFishEyeMatches, src/Frame.cc:1440-1480, up to the triangulation: the descriptors of the lapping
+ * area are the rows [monoLeft, nL) / [monoRight, nR) of the two extractors' outputs (:1445-1446); BFMatcher knnMatch k=2
+ * (:1458); Lowe ratio 0.7 (:1465: size >= 2 && d0 < d1 * 0.7).  l2r[nL] / r2l[nR] out = mvLeftToRightMatch /
+ * mvRightToLeftMatch candidates in FULL-frame indices (:1477-1478 before the triangulation gate), -1 elsewhere.
+ * Later matches overwrite earlier ones exactly as the loop at :1463 does.  Returns the number of ratio-test survivors. */
+int orc_stereo_fisheye_match(const uint8_t* descL, int nL, int monoLeft, const uint8_t* descR, int nR, int monoRight,
+                             int32_t* l2r, int32_t* r2l, int32_t* dist_out)
+{
+    for (int i = 0; i < nL; i++) { l2r[i] = -1; if (dist_out) dist_out[i] = -1; }
+    for (int i = 0; i < nR; i++) r2l[i] = -1;
+    const int nq = nL - monoLeft, nt = nR - monoRight;
+    if (nq <= 0 || nt <= 0) return 0;
+    int32_t* idx = (int32_t*)malloc(sizeof(int32_t) * 2 * (size_t)nq);
+    int32_t* dst = (int32_t*)malloc(sizeof(int32_t) * 2 * (size_t)nq);
+    orc_bf_knn2(descL + 32 * (size_t)monoLeft, nq, descR + 32 * (size_t)monoRight, nt, idx, dst);
+    int good = 0;
+    for (int q = 0; q < nq; q++) {
+        if (idx[2 * q] < 0 || idx[2 * q + 1] < 0) continue;                   /* (*it).size() >= 2 */
+        if ((double)dst[2 * q] < (double)dst[2 * q + 1] * 0.7) {              /* float distance * double 0.7, :1465 */
+            const int iL = q + monoLeft, iR = idx[2 * q] + monoRight;
+            l2r[iL] = iR; r2l[iR] = iL;
+            if (dist_out) dist_out[iL] = dst[2 * q];
+            good++;
+        }
+    }
+    free(idx); free(dst);
+    return good;
+}

@@ -595,3 +595,82 @@ def search_by_projection_rig(gridL: Grid, gridR: Grid, desc, l2r, r2l, scale_fac
                                               l2r.ctypes.data, r2l.ctypes.data, sf.ctypes.data, len(args[1]), *[a.ctypes.data for a in args],
                                               th, nnratio, int(far), th_far, assign.ctypes.data)
     return nm, assign
+
+
+# ---- two-camera rig branches, callback-driven triangulation searches, fisheye stereo (orc_match.c, bottom) ----
+VERDICT_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int)
+
+
+def _kf_args(k, with_valid_key):
+    kps = np.ascontiguousarray(k["kps"], KP_DTYPE); desc = np.ascontiguousarray(k["desc"], np.uint8)
+    flag = None if k.get(with_valid_key) is None else np.ascontiguousarray(k[with_valid_key], np.uint8)
+    fn, fs, fi = (np.ascontiguousarray(k[x], np.int32) for x in ("fv_node", "fv_start", "fv_idx"))
+    return kps, desc, flag, fn, fs, fi
+
+
+def search_by_projection_frame_rig(gridL: Grid, gridR: Grid, desc, scale_factors, last: dict, th: float,
+                                   forward: bool, backward: bool, check_orientation: bool = True, cur_held=None):
+    """last: SoA dict desc,u,v,ur,vr,invz,octave,angle,valid,obs.  Returns (nmatches, assign[nL + nR])."""
+    L = gridL.L
+    L.orc_search_by_projection_frame_rig.restype = C.c_int
+    L.orc_search_by_projection_frame_rig.argtypes = [C.c_void_p, C.c_void_p, C.c_int] * 2 + [C.c_void_p, C.c_void_p, C.c_int] + \
+        [C.c_void_p] * 10 + [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    desc = np.ascontiguousarray(desc, np.uint8)
+    nL, nR = len(gridL.kps), len(gridR.kps)
+    assign = np.full(nL + nR, -1, np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    held = None if cur_held is None else np.ascontiguousarray(cur_held, np.uint8)
+    f = lambda k, t: np.ascontiguousarray(last[k], t)
+    ld = f("desc", np.uint8)
+    lu, lv, lur, lvr, lz = (f(k, np.float32) for k in ("u", "v", "ur", "vr", "invz"))
+    lo, la, lval, lobs = f("octave", np.int32), f("angle", np.float32), f("valid", np.uint8), f("obs", np.uint8)
+    nm = L.orc_search_by_projection_frame_rig(gridL.g, gridL.kps.ctypes.data, nL, gridR.g, gridR.kps.ctypes.data, nR,
+                                              desc.ctypes.data, sf.ctypes.data, len(lu), ld.ctypes.data, lu.ctypes.data, lv.ctypes.data,
+                                              lur.ctypes.data, lvr.ctypes.data, lz.ctypes.data, lo.ctypes.data, la.ctypes.data,
+                                              lval.ctypes.data, lobs.ctypes.data, th, int(forward), int(backward),
+                                              int(check_orientation), _p(held), assign.ctypes.data)
+    return nm, assign
+
+
+def search_by_bow_rig(o: Oracle, kf1: dict, kf2: dict, nleft2: int, nnratio: float, check_orientation: bool = True):
+    L = o.L
+    L.orc_search_by_bow_rig.restype = C.c_int
+    L.orc_search_by_bow_rig.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                        C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                        C.c_float, C.c_int, C.c_void_p]
+    a, b = _kf_args(kf1, "valid"), _kf_args(kf2, "valid")
+    out = np.full(len(b[0]), -1, np.int32)
+    nm = L.orc_search_by_bow_rig(a[0].ctypes.data, a[1].ctypes.data, len(a[0]), a[2].ctypes.data, a[3].ctypes.data, a[4].ctypes.data,
+                                 a[5].ctypes.data, len(a[3]), b[0].ctypes.data, b[1].ctypes.data, len(b[0]), int(nleft2),
+                                 b[3].ctypes.data, b[4].ctypes.data, b[5].ctypes.data, len(b[3]), nnratio, int(check_orientation),
+                                 out.ctypes.data)
+    return nm, out
+
+
+def search_for_triangulation_cb(o: Oracle, overload: int, kf1: dict, kf2: dict, verdict, only_stereo=False, coarse=False,
+                                check_orientation=True):
+    """verdict(idx1, idx2) -> bool, a Python callable.  kfN: dict kps, desc, has_mp, fv_node, fv_start, fv_idx."""
+    L = o.L
+    L.orc_search_for_triangulation_cb.restype = C.c_int
+    L.orc_search_for_triangulation_cb.argtypes = [C.c_int] + [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int] * 2 + \
+        [C.c_int, C.c_int, C.c_int, VERDICT_FN, C.c_void_p, C.c_void_p]
+    a, b = _kf_args(kf1, "has_mp"), _kf_args(kf2, "has_mp")
+    m12 = np.full(len(a[0]), -1, np.int32)
+    cb = VERDICT_FN(lambda user, i1, i2: int(bool(verdict(i1, i2))))
+    args = []
+    for k in (a, b):
+        args += [k[0].ctypes.data, k[1].ctypes.data, len(k[0]), k[2].ctypes.data, k[3].ctypes.data, k[4].ctypes.data, k[5].ctypes.data, len(k[3])]
+    nm = L.orc_search_for_triangulation_cb(int(overload), *args, int(only_stereo), int(coarse), int(check_orientation), cb, None, m12.ctypes.data)
+    return nm, m12
+
+
+def stereo_fisheye_match(o: Oracle, descL, monoLeft: int, descR, monoRight: int):
+    """Frame::ComputeStereoFishEyeMatches up to the triangulation gate.  Returns (good, l2r, r2l, best_dist)."""
+    L = o.L
+    L.orc_stereo_fisheye_match.restype = C.c_int
+    L.orc_stereo_fisheye_match.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    descL = np.ascontiguousarray(descL, np.uint8); descR = np.ascontiguousarray(descR, np.uint8)
+    l2r = np.full(len(descL), -1, np.int32); r2l = np.full(len(descR), -1, np.int32); bd = np.full(len(descL), -1, np.int32)
+    good = L.orc_stereo_fisheye_match(descL.ctypes.data, len(descL), int(monoLeft), descR.ctypes.data, len(descR), int(monoRight),
+                                      l2r.ctypes.data, r2l.ctypes.data, bd.ctypes.data)
+    return good, l2r, r2l, bd

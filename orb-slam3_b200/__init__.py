@@ -11,4 +11,5 @@ from .extractor import ORBextractor, DescriptorDistance  # noqa: F401
 from .matcher import (ComputeStereoMatches, ExtractStereo, knn2_hamming, SearchByProjection, SearchByProjectionFrame,  # noqa: F401
                       SearchByProjectionKeyFrame,
                       SearchForInitialization, SearchForTriangulation, SearchByBoW, GetFeaturesInArea,
-                      SearchLocalPoints, SearchByProjectionRig, UndistortKeyPoints, ComputeDistinctiveDescriptors, ORBVocabulary, SearchByProjectionSim3, Fuse, SearchBySim3, ComputeThreeMaxima)
+                      SearchLocalPoints, SearchByProjectionRig, UndistortKeyPoints, ComputeDistinctiveDescriptors, ORBVocabulary, SearchByProjectionSim3, Fuse, SearchBySim3, ComputeThreeMaxima,
+                      SearchByProjectionFrameRig, SearchByBoWRig, SearchForTriangulationCb, ComputeStereoFishEyeMatches)

@@ -3,6 +3,7 @@
 // the device sees SoA PODs.
 #pragma once
 #include <stdexcept>
+#include <type_traits>
 #include <string>
 #include <utility>
 #include <vector>
@@ -277,6 +278,91 @@ struct ORBmatcherGPU {
             mp.inViewR.data(), mp.projXR.data(), mp.projYR.data(), mp.levelR.data(), mp.viewCosR.data(),
             th, mfNNratio, bFarPoints ? 1 : 0, thFarPoints, assign.data());
         if (r < 0) throw std::runtime_error(std::string("SearchByProjection(rig): ") + orbx_last_error());
+        return r;
+    }
+
+    // ---- two-camera rig (Nleft != -1) forms of the other guided searches ----
+
+    // Rows of the last frame for the rig form of SearchByProjection(Frame&, const Frame&, th, bMono): as LastFrameSoA plus
+    // the projection of Trl * x3Dc into the right camera (src/ORBmatcher.cc:2613-2616).
+    struct LastFrameRigSoA : LastFrameSoA { std::vector<float> ur, vr; };
+
+    // int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono), CurrentFrame.Nleft != -1
+    // (src/ORBmatcher.cc:2469-2711; right camera :2610-2684).  mDescriptors holds the left rows first (as Frame does, :2647);
+    // assign[i] / assign[Nleft + j] = row of `last` now held by left keypoint i / right keypoint j.
+    int SearchByProjection(const std::vector<cv::KeyPoint>& mvKeys, const std::vector<cv::KeyPoint>& mvKeysRight, const cv::Mat& mDescriptors,
+                           float mnMinX, float mnMaxX, float mnMinY, float mnMaxY, const std::vector<float>& mvScaleFactors,
+                           const LastFrameRigSoA& last, float th, bool bForward, bool bBackward,
+                           const std::vector<uint8_t>* curHeld, std::vector<int32_t>& assign, int device = 0) const
+    {
+        const int nL = (int)mvKeys.size(), nR = (int)mvKeysRight.size();
+        assign.assign((size_t)(nL + nR), -1);
+        const int r = orbx_search_by_projection_frame_rig(
+            device, reinterpret_cast<const orbx_keypoint*>(mvKeys.data()), nL, reinterpret_cast<const orbx_keypoint*>(mvKeysRight.data()), nR,
+            mDescriptors.data, mnMinX, mnMaxX, mnMinY, mnMaxY, mvScaleFactors.data(), (int)mvScaleFactors.size(),
+            (int)last.u.size(), last.desc.data(), last.u.data(), last.v.data(), last.ur.data(), last.vr.data(), last.invz.data(),
+            last.octave.data(), last.angle.data(), last.valid.data(), last.obs.data(), th, bForward ? 1 : 0, bBackward ? 1 : 0,
+            mbCheckOrientation ? 1 : 0, curHeld ? curHeld->data() : nullptr, assign.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchByProjection(Frame,Frame) rig: ") + orbx_last_error());
+        return r;
+    }
+
+    // int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>&) with F.Nleft != -1 (src/ORBmatcher.cc:386-430,
+    // :455-486).  KF2.mvKeysUn must point at the Frame's keypoints in mvpMapPoints order: mvKeys rows first, then mvKeysRight
+    // (the angles :442-448 reads); Nleft = F.Nleft.
+    int SearchByBoWRig(const KeyFrameView& KF1, const KeyFrameView& F, int Nleft, std::vector<int32_t>& matches, int device = 0) const
+    {
+        const int n1 = (int)KF1.mvKeysUn->size(), n2 = (int)F.mvKeysUn->size();
+        matches.assign((size_t)n2, -1);
+        const int r = orbx_search_by_bow_rig(
+            device, reinterpret_cast<const orbx_keypoint*>(KF1.mvKeysUn->data()), KF1.mDescriptors->data, n1, KF1.hasMapPoint.data(),
+            KF1.fvNode.data(), KF1.fvStart.data(), KF1.fvIdx.data(), (int)KF1.fvNode.size(),
+            reinterpret_cast<const orbx_keypoint*>(F.mvKeysUn->data()), F.mDescriptors->data, n2, Nleft,
+            F.fvNode.data(), F.fvStart.data(), F.fvIdx.data(), (int)F.fvNode.size(), mfNNratio, mbCheckOrientation ? 1 : 0, matches.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchByBoW rig: ") + orbx_last_error());
+        return r;
+    }
+
+    // The triangulation searches whose geometric test belongs to the camera model (a KannalaBrandt8 rig):
+    //   overload 0: SearchForTriangulation (include/ORBmatcher.h:74, src/ORBmatcher.cc:1107) with pKF1->mpCamera2 && pKF2->mpCamera2:
+    //               verdict(idx1, idx2) = pCamera1->epipolarConstrain(pCamera2, kp1, kp2, R12, t12, sigma1, sigma2) with the
+    //               camera / pose pair of :1252-1279 (bRight1 = idx1 >= NLeft, bRight2 = idx2 >= NLeft)
+    //   overload 1: SearchForTriangulation_ (:1388), epipolarConstrain_
+    //   overload 2: SearchForTriangulation(..., vector<cv::Mat>& vMatchedPoints) (:1632): verdict = matchAndtriangulate(...);
+    //               let it remember x3D per idx1 when it accepts to rebuild vMatchedPoints (:1733-1735, :1815)
+    // Verdict is any callable bool(int idx1, int idx2); it is invoked in the reference's call order from this thread.
+    template <class Verdict>
+    int SearchForTriangulation(int overload, const KeyFrameView& KF1, const KeyFrameView& KF2, Verdict&& verdict,
+                               std::vector<std::pair<size_t, size_t>>& vMatchedPairs, bool bOnlyStereo, bool bCoarse = false, int device = 0) const
+    {
+        const int n1 = (int)KF1.mvKeysUn->size(), n2 = (int)KF2.mvKeysUn->size();
+        std::vector<int32_t> m12((size_t)n1, -1);
+        auto thunk = [](void* u, int i1, int i2) -> int { return (*static_cast<typename std::remove_reference<Verdict>::type*>(u))(i1, i2) ? 1 : 0; };
+        const int r = orbx_search_for_triangulation_cb(
+            device, overload, reinterpret_cast<const orbx_keypoint*>(KF1.mvKeysUn->data()), KF1.mDescriptors->data, n1, KF1.hasMapPoint.data(),
+            KF1.fvNode.data(), KF1.fvStart.data(), KF1.fvIdx.data(), (int)KF1.fvNode.size(),
+            reinterpret_cast<const orbx_keypoint*>(KF2.mvKeysUn->data()), KF2.mDescriptors->data, n2, KF2.hasMapPoint.data(),
+            KF2.fvNode.data(), KF2.fvStart.data(), KF2.fvIdx.data(), (int)KF2.fvNode.size(),
+            bOnlyStereo ? 1 : 0, bCoarse ? 1 : 0, mbCheckOrientation ? 1 : 0, thunk, &verdict, m12.data());
+        if (r < 0) throw std::runtime_error(std::string("SearchForTriangulation(rig / matchAndtriangulate): ") + orbx_last_error());
+        vMatchedPairs.clear();
+        vMatchedPairs.reserve((size_t)r);
+        for (int i = 0; i < n1; i++)
+            if (m12[(size_t)i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m12[(size_t)i]));
+        return r;
+    }
+
+    // void Frame::ComputeStereoFishEyeMatches(), include/Frame.h:304, src/Frame.cc:1440-1480, up to the triangulation gate, on
+    // the descriptors the two ExtractORB calls (src/Frame.cc:1363-1366) left on the device: left / right are the two
+    // extractor objects, Nleft / Nright the keypoint counts, monoLeft / monoRight the values operator() returned.
+    // Fills the CANDIDATE mvLeftToRightMatch / mvRightToLeftMatch (the caller keeps a pair iff TriangulateMatches > 0.0001, :1471).
+    static int ComputeStereoFishEyeMatches(ORBextractor& left, ORBextractor& right, int Nleft, int monoLeft, int Nright, int monoRight,
+                                           std::vector<int>& mvLeftToRightMatch, std::vector<int>& mvRightToLeftMatch)
+    {
+        mvLeftToRightMatch.assign((size_t)Nleft, -1); mvRightToLeftMatch.assign((size_t)Nright, -1);
+        const int r = orbx_stereo_fisheye_match(left.handle(), right.handle(), 0, Nleft, monoLeft, Nright, monoRight,
+                                                mvLeftToRightMatch.data(), mvRightToLeftMatch.data(), nullptr);
+        if (r < 0) throw std::runtime_error(std::string("ComputeStereoFishEyeMatches: ") + orbx_last_error());
         return r;
     }
 

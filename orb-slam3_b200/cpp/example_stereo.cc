@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <chrono>
+#include <cmath>
 #include <thread>
 
 #include "ORBmatcher.h"
@@ -27,6 +28,12 @@ static cv::Mat synth(int rows, int cols, unsigned seed, int shift)
             m.ptr(y)[x] = (uint8_t)(s / 9);
         }
     return m;
+}
+
+static ORB_SLAM3::ORBmatcherGPU::KeyFrameView K1nomp(ORB_SLAM3::ORBmatcherGPU::KeyFrameView k)
+{
+    k.hasMapPoint.assign(k.hasMapPoint.size(), 0);
+    return k;
 }
 
 int main()
@@ -97,6 +104,42 @@ int main()
         const int nBoW = matcherBoW.SearchByBoW(K1, K2, false, bowMatches);
         std::printf("second view: %zu kps; SearchForInitialization %d, SearchByProjection(Frame,Frame) %d, SearchForTriangulation %d, "
                     "SearchByBoW %d\n", mvKeys2.size(), nIni, nProj, nTri, nBoW);
+        // --- two-camera rig (KannalaBrandt stereo, Frame::Nleft != -1): the fisheye Frame constructor's sequence ---
+        {
+            std::vector<int> lapRig = {100, 600};                   // vLappingArea of the two fisheye cameras
+            std::vector<cv::KeyPoint> kL, kR;
+            cv::Mat dL, dR;
+            const int monoLeft = left(imLeft, cv::Mat(), kL, dL, lapRig);        // src/Frame.cc:1363-1366 (two threads there)
+            const int monoRight = right(imRight, cv::Mat(), kR, dR, lapRig);
+            std::vector<int> l2r, r2l;
+            const int nFish = ORBmatcherGPU::ComputeStereoFishEyeMatches(left, right, (int)kL.size(), monoLeft, (int)kR.size(), monoRight, l2r, r2l);
+            // Frame keypoints in mvpMapPoints order (left rows, then right rows) for the rig searches
+            std::vector<cv::KeyPoint> kAll(kL); kAll.insert(kAll.end(), kR.begin(), kR.end());
+            cv::Mat dAll; ORBX_MAT_CREATE(dAll, (int)kAll.size(), 32);
+            for (int i = 0; i < dL.rows; i++) std::memcpy(dAll.ptr(i), dL.ptr(i), 32);
+            for (int i = 0; i < dR.rows; i++) std::memcpy(dAll.ptr(dL.rows + i), dR.ptr(i), 32);
+            ORBmatcherGPU::KeyFrameView FR = {&kAll, &dAll, nullptr, std::vector<uint8_t>(kAll.size(), 0), {0}, {0, (int32_t)kAll.size()}, {}, &sf, &sigma2};
+            for (size_t i = 0; i < kAll.size(); i++) FR.fvIdx.push_back((int32_t)i);
+            std::vector<int32_t> bowRig;
+            const int nBoWRig = matcherBoW.SearchByBoWRig(K1, FR, (int)kL.size(), bowRig);
+            ORBmatcherGPU::LastFrameRigSoA lastRig;
+            static_cast<ORBmatcherGPU::LastFrameSoA&>(lastRig) = last;
+            lastRig.ur = last.u; lastRig.vr = last.v;
+            for (float& u : lastRig.ur) u -= 20.f;
+            std::vector<int32_t> assignRig;
+            const int nProjRig = matcherIni.SearchByProjection(kL, kR, dAll, 0.f, (float)cols, 0.f, (float)rows, sf, lastRig, 15.f, false, false,
+                                                               nullptr, assignRig);
+            // SearchForTriangulation with the camera model's own test as a callable (here: rows within 2 px)
+            int asked = 0;
+            auto verdict = [&](int i1, int i2) { asked++; return std::fabs(mvKeys[(size_t)i1].pt.y - kAll[(size_t)i2].pt.y) < 2.f; };
+            std::vector<std::pair<size_t, size_t>> pairsRig;
+            const int nTriRig = matcherTri.SearchForTriangulation(0, K1nomp(K1), FR, verdict, pairsRig, false);
+            std::printf("rig: fisheye stereo candidates %d (monoLeft %d, monoRight %d), SearchByBoW %d, SearchByProjection(Frame,Frame) %d, "
+                        "SearchForTriangulation %d (%d verdict calls)\n", nFish, monoLeft, monoRight, nBoWRig, nProjRig, nTriRig, asked);
+            if (nFish <= 0 || nBoWRig <= 0 || nProjRig <= 0 || nTriRig <= 0 || asked < nTriRig) return 3;
+            left(imLeft, cv::Mat(), mvKeys, mDescriptors, vLapping);             // restore the resident state used below
+            right(imRight, cv::Mat(), mvKeysRight, mDescriptorsRight, vLapping);
+        }
         // --- the same stereo frame through the one-call entry: identical results ---
         std::vector<cv::KeyPoint> k1, k2;
         cv::Mat d1, d2;

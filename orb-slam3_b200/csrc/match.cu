@@ -109,6 +109,86 @@ extern "C" int orbx_knn2_hamming(int device, const uint8_t* q, int nq, const uin
     return ORBX_OK;
 }
 
+// ---- Frame::ComputeStereoFishEyeMatches on the descriptors the two extractions left on the device ----
+// src/Frame.cc:1440-1480 up to the triangulation: rows [monoLeft, nL) x [monoRight, nR) of the two handles' resident
+// descriptor matrices (:1445-1446), knnMatch k = 2 (:1458), Lowe ratio (:1465; float distance * DOUBLE 0.7).
+__global__ void __launch_bounds__(KNN_THREADS)
+fisheye_ratio_kernel(const int4* __restrict__ part, int nq, int nsplit, int monoLeft, int monoRight, int* __restrict__ l2r, int* __restrict__ r2l,
+                     int* __restrict__ dist_out, int* __restrict__ good)
+{
+    const int i = blockIdx.x * KNN_THREADS + threadIdx.x;
+    int ok = 0;
+    if (i < nq) {
+        int b0 = 1 << 30, b1 = 1 << 30, i0 = -1, i1 = -1;
+        for (int s = 0; s < nsplit; s++) {                             // as knn2_merge_kernel
+            const int4 p = part[(size_t)s * nq + i];
+            if (p.y >= 0) { if (p.x < b0) { b1 = b0; i1 = i0; b0 = p.x; i0 = p.y; } else if (p.x < b1) { b1 = p.x; i1 = p.y; } }
+            if (p.w >= 0) { if (p.z < b0) { b1 = b0; i1 = i0; b0 = p.z; i0 = p.w; } else if (p.z < b1) { b1 = p.z; i1 = p.w; } }
+        }
+        if (i0 >= 0 && i1 >= 0 && (double)b0 < __dmul_rn((double)b1, 0.7)) {   // (*it).size() >= 2 && d0 < d1 * 0.7
+            l2r[i + monoLeft] = i0 + monoRight;
+            dist_out[i + monoLeft] = b0;
+            atomicMax(&r2l[i0 + monoRight], i + monoLeft);              // the loop at :1463 runs in query order: the last writer wins
+            ok = 1;
+        }
+    }
+    const int n = __syncthreads_count(ok);
+    if (threadIdx.x == 0 && n) atomicAdd(good, n);
+}
+
+__global__ void fill_minus1_kernel(int* p, int n) { const int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) p[i] = -1; }
+
+extern "C" int orbx_stereo_fisheye_match(orbx_extractor* eL, orbx_extractor* eR, int frame, int nL, int monoLeft, int nR, int monoRight,
+                                         int32_t* l2r, int32_t* r2l, int32_t* best_dist)
+{
+    if (!eL || !eR || !eL->reserved || !eR->reserved || eL->last_nframes <= 0 || eL->last_nframes != eR->last_nframes) {
+        orbx_set_error("fisheye stereo match needs a preceding extract of the same number of frames on both handles"); return ORBX_ERR_STATE;
+    }
+    if (eL->device != eR->device) { orbx_set_error("left/right extractors live on different devices"); return ORBX_ERR_ARG; }
+    if (frame < 0 || frame >= eL->last_nframes || nL < 0 || nR < 0 || monoLeft < 0 || monoRight < 0 || monoLeft > nL || monoRight > nR ||
+        nL > eL->G.out_cap || nR > eR->G.out_cap || (nL > 0 && !l2r) || (nR > 0 && !r2l)) {
+        orbx_set_error("bad fisheye stereo arguments (frame %d, nL %d, monoLeft %d, nR %d, monoRight %d)", frame, nL, monoLeft, nR, monoRight); return ORBX_ERR_ARG;
+    }
+    OrbxWorkspace& W = orbx_workspace();
+    int rc = W.bind(eL->device);
+    if (rc != ORBX_OK) return rc;
+    const int nq = nL - monoLeft, nt = nR - monoRight;
+    for (int i = 0; i < nL; i++) { l2r[i] = -1; if (best_dist) best_dist[i] = -1; }
+    for (int i = 0; i < nR; i++) r2l[i] = -1;
+    if (nq <= 0 || nt <= 0) return 0;
+    const int tiles = (nq + KNN_THREADS - 1) / KNN_THREADS;
+    int nsplit = (8 * 148 + tiles - 1) / tiles;
+    const int max_split = (nt + 63) / 64;
+    if (nsplit > max_split) nsplit = max_split;
+    if (nsplit < 1) nsplit = 1;
+    const int per_split = (nt + nsplit - 1) / nsplit;
+    nsplit = (nt + per_split - 1) / per_split;
+    OrbxCarver c;
+    const size_t o_l2r = c.take((size_t)nL * 4), o_dist = c.take((size_t)nL * 4), o_r2l = c.take((size_t)nR * 4), o_good = c.take(4);
+    const size_t out_end = c.off;
+    const size_t o_part = c.take((size_t)nsplit * nq * sizeof(int4));
+    rc = W.reserve(c.off, out_end);
+    if (rc != ORBX_OK) return rc;
+    // order behind both extractions (each handle has its own stream)
+    CUDA_TRYW(cudaEventRecord(eL->join_ev, eL->stream)); CUDA_TRYW(cudaStreamWaitEvent(W.s, eL->join_ev, 0));
+    CUDA_TRYW(cudaEventRecord(eR->join_ev, eR->stream)); CUDA_TRYW(cudaStreamWaitEvent(W.s, eR->join_ev, 0));
+    const int nfill = (int)(out_end / 4);
+    fill_minus1_kernel<<<(nfill + 255) / 256, 256, 0, W.s>>>((int*)W.d, nfill);
+    CUDA_TRYW(cudaMemsetAsync(W.d + o_good, 0, 4, W.s));
+    const uint8_t* dL = eL->D.desc + ((size_t)frame * eL->G.out_cap + monoLeft) * 32;
+    const uint8_t* dR = eR->D.desc + ((size_t)frame * eR->G.out_cap + monoRight) * 32;
+    knn2_partial_kernel<<<dim3(tiles, nsplit), KNN_THREADS, 0, W.s>>>((const uint4*)dL, nq, (const uint4*)dR, nt, per_split, (int4*)(W.d + o_part));
+    fisheye_ratio_kernel<<<tiles, KNN_THREADS, 0, W.s>>>((const int4*)(W.d + o_part), nq, nsplit, monoLeft, monoRight,
+                                                          (int*)(W.d + o_l2r), (int*)(W.d + o_r2l), (int*)(W.d + o_dist), (int*)(W.d + o_good));
+    CUDA_TRYW(cudaGetLastError());
+    CUDA_TRYW(cudaMemcpyAsync(W.h, W.d, out_end, cudaMemcpyDeviceToHost, W.s));
+    CUDA_TRYW(cudaStreamSynchronize(W.s));
+    memcpy(l2r, W.h + o_l2r, (size_t)nL * 4);
+    memcpy(r2l, W.h + o_r2l, (size_t)nR * 4);
+    if (best_dist) memcpy(best_dist, W.h + o_dist, (size_t)nL * 4);
+    return *(const int*)(W.h + o_good);
+}
+
 // ---- brute-force 2-NN without any allocation (no counterpart in the reference) ----
 // Same two kernels as orbx_knn2_hamming, but the (split, query) partial table lives in a file-scope device array
 // instead of the grow-only workspace arena, and descriptors / results are the CALLER's device buffers: the entry

@@ -119,7 +119,8 @@ struct TriArgs {
     float sf2[ORBX_MAX_LEVELS], sigma2_2[ORBX_MAX_LEVELS];
     float epx, epy, F[9];
     int bOnlyStereo, bCoarse;
-    int mode;                        // 0: SearchForTriangulation gates, 1: SearchByBoW (ratio-bounded distances)
+    int mode;                        // 0: SearchForTriangulation gates, 1: SearchByBoW (ratio-bounded distances),
+                                     // 2: dist <= TH_LOW only (rig / callback triangulation: geometry is the caller's)
     float nnratio;
     int* it_base; int* it_cnt;
     int2* cand; int cap;             // (idx2 | epi_ok << 30, dist)
@@ -161,7 +162,7 @@ tri_candidates_kernel(TriArgs A)
                 if (A.bOnlyStereo && !bStereo2) ok = false;                                  // :1224-1226
                 if (ok) {
                     dist = ham256(a0, a1, A.desc2[2 * idx2], A.desc2[2 * idx2 + 1]);
-                    if (A.mode == 0) { if (dist > TH_LOW) ok = false; }                      // :1231
+                    if (A.mode == 0 || A.mode == 2) { if (dist > TH_LOW) ok = false; }       // :1231 (mode 2: the verdict is the caller's)
                     // SearchByBoW accepts best1 <= TH_LOW when best1 < ratio * best2 (:431-433): a distance with
                     // ratio * d > TH_LOW can neither win nor make that test fail, so it need not be reported
                     else { epi = 1; if (__fmul_rn(A.nnratio, (float)dist) > (float)TH_LOW) ok = false; }
@@ -990,3 +991,256 @@ extern "C" int orbx_search_by_sim3(int device,
     }
     return nFound;
 }
+
+// ---- two-camera rig (Nleft != -1) branches: config C3's KannalaBrandt stereo set-up ----
+
+// SearchByProjection(Frame& Current, const Frame& Last, th, bMono), src/ORBmatcher.cc:2469-2711, CurrentFrame.Nleft != -1.
+// Two window sweeps (left grid over mvKeys, right grid over mvKeysRight with the right projections) and one host replay
+// over rows 0..nlast-1 in order: left half (:2540-2601), then right half (:2610-2684) - skipped together with the left
+// one when the left WINDOW is empty (`continue`, :2541).
+extern "C" int orbx_search_by_projection_frame_rig(int device,
+                                                   const orbx_keypoint* kpsL, int nL, const orbx_keypoint* kpsR, int nR, const uint8_t* desc,
+                                                   float minX, float maxX, float minY, float maxY,
+                                                   const float* scaleFactors, int nlevels,
+                                                   int nlast, const uint8_t* last_desc, const float* last_u, const float* last_v,
+                                                   const float* last_ur, const float* last_vr,
+                                                   const float* last_invz, const int32_t* last_octave, const float* last_angle,
+                                                   const uint8_t* last_valid, const uint8_t* last_obs,
+                                                   float th, int bForward, int bBackward, int checkOrientation,
+                                                   const uint8_t* cur_held, int32_t* assign)
+{
+    const int n = nL + nR;
+    if (nL < 0 || nR < 0 || (nL > 0 && !kpsL) || (nR > 0 && !kpsR) || (n > 0 && (!desc || !assign)) || !(maxX > minX) || !(maxY > minY) ||
+        nlast < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors ||
+        (nlast > 0 && (!last_desc || !last_u || !last_v || !last_ur || !last_vr || !last_invz || !last_octave || !last_angle || !last_valid || !last_obs))) {
+        orbx_set_error("bad search_by_projection_frame_rig arguments"); return ORBX_ERR_ARG;
+    }
+    for (int i = 0; i < n; i++) assign[i] = -1;
+    if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
+    if (n == 0 || nlast == 0) return 0;
+    std::vector<float> q_r(nlast);
+    std::vector<int32_t> q_min(nlast), q_max(nlast);
+    for (int i = 0; i < nlast; i++) {
+        q_r[i] = -1.f; q_min[i] = -1; q_max[i] = -1;
+        if (!last_valid[i]) continue;                                             // :2503-2506
+        if (last_invz[i] < 0) continue;                                           // :2515
+        if (last_u[i] < minX || last_u[i] > maxX) continue;                       // :2520-2523 (left projection only)
+        if (last_v[i] < minY || last_v[i] > maxY) continue;
+        const int oct = last_octave[i];
+        if (oct < 0 || oct >= nlevels) { orbx_set_error("last-frame point %d: octave %d out of range", i, oct); return ORBX_ERR_ARG; }
+        q_r[i] = th * scaleFactors[oct];                                          // :2529 / :2620
+        if (!(q_r[i] >= 0.f)) { q_r[i] = -1.f; continue; }
+        if (bForward) { q_min[i] = oct; q_max[i] = -1; }
+        else if (bBackward) { q_min[i] = 0; q_max[i] = oct; }
+        else { q_min[i] = oct - 1; q_max[i] = oct + 1; }
+    }
+    // the results of run_windows live in the calling thread's pinned workspace: keep the left sweep before the right one
+    std::vector<int> cntL(nlast, 0), baseL(nlast, 0);
+    std::vector<int2> candL;
+    if (nL > 0) {
+        WinHost in = {kpsL, desc, nL, nullptr, minX, maxX, minY, maxY, nlast, last_desc, last_u, last_v, q_r.data(), nullptr, q_min.data(), q_max.data()};
+        WinResult R;
+        const int rc = run_windows(device, in, &R);
+        if (rc != ORBX_OK) return rc;
+        cntL.assign(R.cnt, R.cnt + nlast); baseL.assign(R.base, R.base + nlast);
+        candL.assign(R.cand, R.cand + R.total);
+    }
+    WinResult RR = {nullptr, nullptr, nullptr, 0};
+    if (nR > 0) {
+        WinHost in = {kpsR, desc + 32 * (size_t)nL, nR, nullptr, minX, maxX, minY, maxY, nlast, last_desc, last_ur, last_vr, q_r.data(), nullptr,
+                      q_min.data(), q_max.data()};
+        const int rc = run_windows(device, in, &RR);
+        if (rc != ORBX_OK) return rc;
+    }
+    int nmatches = 0;
+    RotHist H(HISTO_LENGTH / 360.0f);                                             // :2480
+    std::vector<uint8_t> held(n, 0);
+    if (cur_held) for (int i = 0; i < n; i++) held[i] = cur_held[i] != 0;
+    for (int i = 0; i < nlast; i++) {
+        if (cntL[i] == 0) continue;                                               // :2541
+        {
+            const int2* c = candL.data() + baseL[i];
+            int bestDist = 256, bestIdx2 = -1;
+            for (int k = 0; k < cntL[i]; k++) {
+                if (held[c[k].x]) continue;                                       // :2552-2554
+                if (c[k].y < bestDist) { bestDist = c[k].y; bestIdx2 = c[k].x; }
+            }
+            if (bestDist <= TH_HIGH) {
+                assign[bestIdx2] = i; held[bestIdx2] = last_obs[i] != 0; nmatches++;
+                if (checkOrientation) H.push(last_angle[i], kpsL[bestIdx2].angle, bestIdx2);
+            }
+        }
+        if (nR > 0 && RR.cnt[i] > 0) {
+            const int2* c = RR.cand + RR.base[i];
+            int bestDist = 256, bestIdx2 = -1;
+            for (int k = 0; k < RR.cnt[i]; k++) {
+                if (held[c[k].x + nL]) continue;                                  // :2640-2642
+                if (c[k].y < bestDist) { bestDist = c[k].y; bestIdx2 = c[k].x; }
+            }
+            if (bestDist <= TH_HIGH) {
+                assign[bestIdx2 + nL] = i; held[bestIdx2 + nL] = last_obs[i] != 0; nmatches++;
+                if (checkOrientation) H.push(last_angle[i], kpsR[bestIdx2].angle, bestIdx2 + nL);
+            }
+        }
+    }
+    if (checkOrientation) {                                                       // :2686-2708
+        int i1, i2, i3;
+        H.top3(&i1, &i2, &i3);
+        for (int b = 0; b < HISTO_LENGTH; b++)
+            if (b != i1 && b != i2 && b != i3)
+                for (int v : H.bin[b]) { assign[v] = -1; nmatches--; }
+    }
+    return nmatches;
+}
+
+// SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&), src/ORBmatcher.cc:314-547, F.Nleft != -1: the pair sweep is that
+// of orbx_search_by_bow(mode 0); the replay keeps best / second per camera (:380-430), accepts the right-camera match
+// only inside the left one's TH_LOW test and without a ratio test of its own (:431, :455-457).
+extern "C" int orbx_search_by_bow_rig(int device,
+                                      const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* valid1,
+                                      const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                                      const orbx_keypoint* kps2, const uint8_t* desc2, int n2, int nleft2,
+                                      const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                                      float nnratio, int checkOrientation, int32_t* matches)
+{
+    if (n1 < 0 || n2 < 0 || nn1 < 0 || nn2 < 0 || nleft2 < 0 || nleft2 > n2 || (n2 > 0 && !matches) ||
+        (n1 > 0 && (!kps1 || !desc1 || !valid1)) || (n2 > 0 && (!kps2 || !desc2)) ||
+        (nn1 > 0 && (!fv1_node || !fv1_start || !fv1_idx)) || (nn2 > 0 && (!fv2_node || !fv2_start || !fv2_idx))) {
+        orbx_set_error("bad search_by_bow_rig arguments"); return ORBX_ERR_ARG;
+    }
+    for (int i = 0; i < n2; i++) matches[i] = -1;
+    if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
+    if (n1 == 0 || n2 == 0 || nn1 == 0 || nn2 == 0) return 0;
+    const int len1 = fv1_start[nn1], len2 = fv2_start[nn2];
+    for (int i = 0; i < len1; i++) if (fv1_idx[i] < 0 || fv1_idx[i] >= n1) { orbx_set_error("fv1_idx[%d] out of range", i); return ORBX_ERR_ARG; }
+    for (int i = 0; i < len2; i++) if (fv2_idx[i] < 0 || fv2_idx[i] >= n2) { orbx_set_error("fv2_idx[%d] out of range", i); return ORBX_ERR_ARG; }
+    std::vector<int4> items;
+    items.reserve(len1);
+    merge_feature_vectors(fv1_node, fv1_start, fv1_idx, nn1, fv2_node, fv2_start, nn2, [&](int idx1) { return valid1[idx1] != 0; }, &items);
+    const int nitems = (int)items.size();
+    if (nitems == 0) return 0;
+    std::vector<uint8_t> skip2((size_t)n2, 0);
+    // a distance with ratio * d > TH_LOW can neither be accepted (left: best1 <= TH_LOW and best1 < ratio * best2; right:
+    // best1R <= TH_LOW) nor make the left ratio test fail, so the pair sweep need not report it.  For ratio > 1 that bound
+    // would drop right-camera candidates <= TH_LOW: report everything then.
+    PairHost in = {kps1, desc1, n1, nullptr, kps2, desc2, n2, nullptr, skip2.data(), fv2_idx, len2, items.data(), nitems,
+                   nullptr, nullptr, 0, nullptr, nullptr, 0, 0, 1, nnratio > 1.f ? 1.f : nnratio};
+    PairResult R;
+    {
+        const int rc = run_pairs(device, in, &R);
+        if (rc != ORBX_OK) return rc;
+    }
+    int nmatches = 0;
+    RotHist H(HISTO_LENGTH / 360.0f);                                             // :334
+    std::vector<uint8_t> taken2((size_t)n2, 0);
+    for (int it = 0; it < nitems; it++) {
+        const int idx1 = items[it].x;
+        const int2* c = R.cand + R.base[it];
+        int bestDist1 = 256, bestDist2 = 256, bestIdxF = -1, bestDist1R = 256, bestDist2R = 256, bestIdxFR = -1;
+        for (int k = 0; k < R.cnt[it]; k++) {                                     // :386-430
+            const int idx2 = c[k].x & 0x3FFFFFFF, dist = c[k].y;
+            if (taken2[idx2]) continue;
+            if (idx2 < nleft2) {
+                if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = idx2; }
+                else if (dist < bestDist2) bestDist2 = dist;
+            } else {
+                if (dist < bestDist1R) { bestDist2R = bestDist1R; bestDist1R = dist; bestIdxFR = idx2; }
+                else if (dist < bestDist2R) bestDist2R = dist;
+            }
+        }
+        (void)bestDist2R;
+        if (bestDist1 <= TH_LOW) {                                                // :431
+            if ((float)bestDist1 < nnratio * (float)bestDist2) {                  // :433
+                matches[bestIdxF] = idx1; taken2[bestIdxF] = 1;
+                if (checkOrientation) H.push(kps1[idx1].angle, kps2[bestIdxF].angle, bestIdxF);
+                nmatches++;
+            }
+            if (bestDist1R <= TH_LOW) {                                           // :455-457 (`|| true`)
+                matches[bestIdxFR] = idx1; taken2[bestIdxFR] = 1;
+                if (checkOrientation) H.push(kps1[idx1].angle, kps2[bestIdxFR].angle, bestIdxFR);
+                nmatches++;
+            }
+        }
+    }
+    if (checkOrientation) {                                                       // :520-544
+        int i1, i2, i3;
+        H.top3(&i1, &i2, &i3);
+        for (int b = 0; b < HISTO_LENGTH; b++) {
+            if (b == i1 || b == i2 || b == i3) continue;
+            for (int v : H.bin[b]) { matches[v] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+// The triangulation searches whose geometric verdict is the camera model's own (caller-side) code - see the
+// declaration in include/orbx.h for the three overloads.  The device sweeps every (KF1 keypoint, KF2 keypoint) pair
+// under a common vocabulary node and keeps those with !pMP2 and dist <= TH_LOW, in FeatureVector order; the replay
+// asks `verdict` exactly where the reference calls epipolarConstrain / matchAndtriangulate (dist <= bestDist so far).
+extern "C" int orbx_search_for_triangulation_cb(int device, int overload,
+                                                const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
+                                                const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
+                                                const orbx_keypoint* kps2, const uint8_t* desc2, int n2, const uint8_t* has_mp2,
+                                                const int32_t* fv2_node, const int32_t* fv2_start, const int32_t* fv2_idx, int nn2,
+                                                int bOnlyStereo, int bCoarse, int checkOrientation,
+                                                orbx_pair_verdict_fn verdict, void* user, int32_t* matches12)
+{
+    if (overload < 0 || overload > 2 || n1 < 0 || n2 < 0 || nn1 < 0 || nn2 < 0 || (n1 > 0 && (!kps1 || !desc1 || !has_mp1 || !matches12)) ||
+        (n2 > 0 && (!kps2 || !desc2 || !has_mp2)) || (nn1 > 0 && (!fv1_node || !fv1_start || !fv1_idx)) ||
+        (nn2 > 0 && (!fv2_node || !fv2_start || !fv2_idx)) || (!verdict && !(bCoarse && overload != 2))) {
+        orbx_set_error("bad search_for_triangulation_cb arguments"); return ORBX_ERR_ARG;
+    }
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    if (device < 0 || device >= orbx_device_count()) { orbx_set_error("CUDA device %d not available; no CPU path", device); return ORBX_ERR_CUDA; }
+    if (n1 == 0 || n2 == 0 || nn1 == 0 || nn2 == 0) return 0;
+    if (overload != 2 && bOnlyStereo) return 0;                                   // bStereo1 is false with a rig: every idx1 is skipped (:1194-1198)
+    const int len1 = fv1_start[nn1], len2 = fv2_start[nn2];
+    for (int i = 0; i < len1; i++) if (fv1_idx[i] < 0 || fv1_idx[i] >= n1) { orbx_set_error("fv1_idx[%d] out of range", i); return ORBX_ERR_ARG; }
+    for (int i = 0; i < len2; i++) if (fv2_idx[i] < 0 || fv2_idx[i] >= n2) { orbx_set_error("fv2_idx[%d] out of range", i); return ORBX_ERR_ARG; }
+    std::vector<int4> items;
+    items.reserve(len1);
+    merge_feature_vectors(fv1_node, fv1_start, fv1_idx, nn1, fv2_node, fv2_start, nn2, [&](int idx1) { return !has_mp1[idx1]; }, &items);
+    const int nitems = (int)items.size();
+    if (nitems == 0) return 0;
+    PairHost in = {kps1, desc1, n1, nullptr, kps2, desc2, n2, nullptr, has_mp2, fv2_idx, len2, items.data(), nitems,
+                   nullptr, nullptr, 0, nullptr, nullptr, 0, 0, 2, 0.f};
+    PairResult R;
+    {
+        const int rc = run_pairs(device, in, &R);
+        if (rc != ORBX_OK) return rc;
+    }
+    // the candidate lists live in the calling thread's workspace, which `verdict` may reuse (another orbx call): copy them
+    const std::vector<int> base(R.base, R.base + nitems), cnt(R.cnt, R.cnt + nitems);
+    const std::vector<int2> cand(R.cand, R.cand + R.total);
+    int nmatches = 0;
+    RotHist H(overload == 0 ? HISTO_LENGTH / 360.0f : 1.0f / HISTO_LENGTH);       // :1166 / :1441 / :1666
+    std::vector<uint8_t> vbMatched2(n2, 0);
+    for (int it = 0; it < nitems; it++) {
+        const int idx1 = items[it].x;
+        const int2* c = cand.data() + base[it];
+        int bestDist = TH_LOW, bestIdx2 = -1;
+        for (int k = 0; k < cnt[it]; k++) {
+            const int idx2 = c[k].x & 0x3FFFFFFF, dist = c[k].y;
+            if (vbMatched2[idx2]) continue;                                       // :1218
+            if (dist > bestDist) continue;                                        // :1231 / :1707
+            const bool ok = (overload != 2 && bCoarse) ? true : verdict(user, idx1, idx2) != 0;   // :1282 / :1729
+            if (ok) { bestIdx2 = idx2; bestDist = dist; }
+        }
+        if (bestIdx2 >= 0) {
+            matches12[idx1] = bestIdx2;
+            if (overload == 0) vbMatched2[bestIdx2] = 1;                          // :1297 only
+            nmatches++;
+            if (checkOrientation) H.push(kps1[idx1].angle, kps2[bestIdx2].angle, idx1);
+        }
+    }
+    if (checkOrientation) {
+        int i1, i2, i3;
+        H.top3(&i1, &i2, &i3);
+        for (int b = 0; b < HISTO_LENGTH; b++) {
+            if (b == i1 || b == i2 || b == i3) continue;
+            for (int v : H.bin[b]) { matches12[v] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+

@@ -3,6 +3,8 @@
 on the C ABI (include/orbx.h).  All compute happens in liborbx.so on the GPU."""
 from __future__ import annotations
 
+import ctypes as C
+
 import numpy as np
 
 from . import binding
@@ -366,3 +368,71 @@ def ComputeThreeMaxima(sizes):
     out = np.zeros(3, np.int32)
     binding.load().orbx_three_maxima(sizes.ctypes.data, len(sizes), out[0:].ctypes.data, out[1:].ctypes.data, out[2:].ctypes.data)
     return tuple(int(v) for v in out)
+
+
+# ---- two-camera rig (Frame::Nleft != -1) branches, callback-driven triangulation searches, fisheye stereo ----
+VERDICT_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int)
+
+
+def _kf_args(k, flag_key):
+    kps = np.ascontiguousarray(k["kps"], KP_DTYPE); desc = np.ascontiguousarray(k["desc"], np.uint8)
+    flag = None if k.get(flag_key) is None else np.ascontiguousarray(k[flag_key], np.uint8)
+    fn, fs, fi = (np.ascontiguousarray(k[x], np.int32) for x in ("fv_node", "fv_start", "fv_idx"))
+    return kps, desc, flag, fn, fs, fi
+
+
+def SearchByProjectionFrameRig(kpsL, kpsR, desc, bounds, scale_factors, last: dict, th: float, forward: bool, backward: bool,
+                               check_orientation: bool = True, cur_held=None, device: int = 0):
+    """ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th, bMono), CurrentFrame.Nleft != -1
+    (src/ORBmatcher.cc:2469-2711).  last: SoA dict desc,u,v,ur,vr,invz,octave,angle,valid,obs.  Returns (nmatches, assign)."""
+    kpsL = np.ascontiguousarray(kpsL, KP_DTYPE); kpsR = np.ascontiguousarray(kpsR, KP_DTYPE)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(kpsL) + len(kpsR)
+    assign = np.full(n, -1, np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    held = None if cur_held is None else np.ascontiguousarray(cur_held, np.uint8)
+    f = lambda k, t: np.ascontiguousarray(last[k], t)
+    ld = f("desc", np.uint8)
+    lu, lv, lur, lvr, lz = (f(k, np.float32) for k in ("u", "v", "ur", "vr", "invz"))
+    lo, la, lval, lobs = f("octave", np.int32), f("angle", np.float32), f("valid", np.uint8), f("obs", np.uint8)
+    nm = check(binding.load().orbx_search_by_projection_frame_rig(
+        device, kpsL.ctypes.data, len(kpsL), kpsR.ctypes.data, len(kpsR), desc.ctypes.data, bounds[0], bounds[1], bounds[2], bounds[3],
+        sf.ctypes.data, len(sf), len(lu), ld.ctypes.data, lu.ctypes.data, lv.ctypes.data, lur.ctypes.data, lvr.ctypes.data, lz.ctypes.data,
+        lo.ctypes.data, la.ctypes.data, lval.ctypes.data, lobs.ctypes.data, th, int(forward), int(backward), int(check_orientation),
+        _p(held), assign.ctypes.data))
+    return nm, assign
+
+
+def SearchByBoWRig(kf1: dict, kf2: dict, nleft2: int, nnratio: float, check_orientation: bool = True, device: int = 0):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) with F.Nleft != -1 (src/ORBmatcher.cc:314-547).  Returns (nmatches, matches[n2])."""
+    a, b = _kf_args(kf1, "valid"), _kf_args(kf2, "valid")
+    out = np.full(len(b[0]), -1, np.int32)
+    nm = check(binding.load().orbx_search_by_bow_rig(
+        device, a[0].ctypes.data, a[1].ctypes.data, len(a[0]), a[2].ctypes.data, a[3].ctypes.data, a[4].ctypes.data, a[5].ctypes.data, len(a[3]),
+        b[0].ctypes.data, b[1].ctypes.data, len(b[0]), int(nleft2), b[3].ctypes.data, b[4].ctypes.data, b[5].ctypes.data, len(b[3]),
+        nnratio, int(check_orientation), out.ctypes.data))
+    return nm, out
+
+
+def SearchForTriangulationCb(overload: int, kf1: dict, kf2: dict, verdict, only_stereo: bool = False, coarse: bool = False,
+                             check_orientation: bool = True, device: int = 0):
+    """SearchForTriangulation / SearchForTriangulation_ with a two-camera rig (overload 0 / 1) and the matchAndtriangulate
+    overload (2), src/ORBmatcher.cc:1107 / :1388 / :1632.  verdict(idx1, idx2) -> bool is the camera model's test."""
+    a, b = _kf_args(kf1, "has_mp"), _kf_args(kf2, "has_mp")
+    m12 = np.full(len(a[0]), -1, np.int32)
+    cb = VERDICT_FN(lambda user, i1, i2: int(bool(verdict(i1, i2))))
+    args = []
+    for k in (a, b):
+        args += [k[0].ctypes.data, k[1].ctypes.data, len(k[0]), k[2].ctypes.data, k[3].ctypes.data, k[4].ctypes.data, k[5].ctypes.data, len(k[3])]
+    nm = check(binding.load().orbx_search_for_triangulation_cb(device, int(overload), *args, int(only_stereo), int(coarse),
+                                                               int(check_orientation), C.cast(cb, C.c_void_p), None, m12.ctypes.data))
+    return nm, m12
+
+
+def ComputeStereoFishEyeMatches(XL, XR, nL: int, monoLeft: int, nR: int, monoRight: int, frame: int = 0):
+    """Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1440-1480) up to the triangulation gate, on the descriptors the two
+    extractors left on the device.  Returns (descMatches, l2r[nL], r2l[nR], best_dist[nL])."""
+    l2r = np.full(nL, -1, np.int32); r2l = np.full(nR, -1, np.int32); bd = np.full(nL, -1, np.int32)
+    good = check(binding.load().orbx_stereo_fisheye_match(XL.h, XR.h, int(frame), int(nL), int(monoLeft), int(nR), int(monoRight),
+                                                          l2r.ctypes.data, r2l.ctypes.data, bd.ctypes.data))
+    return good, l2r, r2l, bd

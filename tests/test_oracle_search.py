@@ -155,3 +155,103 @@ def test_oracle_fuse_and_sim3_identity(orc, oracle):
     assert np.all(assign2[::2] == -1) and nm2 == int(inside[1::2].sum())
     nf4, m12 = orc.search_by_sim3(g, desc, g, desc, SF, mp, mp, 7.5)
     assert nf4 == int(inside.sum()) and np.array_equal(m12[inside], np.arange(n)[inside])
+
+
+# ---- the two-camera rig / callback restatements: answers known by construction or from the Nleft == -1 restatement ----
+
+def _one_node_fv(n):
+    return dict(fv_node=np.array([3], np.int32), fv_start=np.array([0, n], np.int32), fv_idx=np.arange(n, dtype=np.int32))
+
+
+def test_oracle_rig_frame_identity_and_empty_left_window(orc, oracle):
+    rng = np.random.default_rng(5)
+    kL, dL = _unique_frame(orc, rng, 300)
+    kR, dR = _unique_frame(orc, rng, 200)
+    desc = np.concatenate([dL, dR])
+    b = (0.0, 752.0, 0.0, 480.0)
+    gL, gR = orc.Grid(oracle, kL, *b), orc.Grid(oracle, kR, *b)
+    # rows = the left keypoints themselves, projected exactly; right projections hit right keypoint i % 200
+    last = dict(desc=dL, u=kL["x"], v=kL["y"], ur=kR["x"][np.arange(300) % 200], vr=kR["y"][np.arange(300) % 200],
+                invz=np.full(300, 0.1, np.float32), octave=np.zeros(300, np.int32), angle=kL["angle"],
+                valid=np.ones(300, np.uint8), obs=np.ones(300, np.uint8))
+    nm, a = orc.search_by_projection_frame_rig(gL, gR, desc, SF, last, 3.0, False, False, False, None)
+    assert np.array_equal(a[:300], np.arange(300))                  # every left keypoint takes its own row
+    # random right descriptors: a right keypoint is only accepted when its distance <= TH_HIGH; count consistent
+    assert nm == 300 + int(np.sum(a[300:] >= 0))
+    # the Nleft == -1 restatement agrees on the left half when there is no right camera
+    e = np.zeros(0, orc.KP_DTYPE)
+    nm1, a1 = orc.search_by_projection_frame_rig(gL, orc.Grid(oracle, e, *b), dL, SF, last, 3.0, False, False, True, None)
+    lastm = {k: v for k, v in last.items() if k not in ("ur", "vr")}
+    nm0, a0 = orc.search_by_projection_frame(gL, dL, None, SF, lastm, 3.0, 0.0, False, False, True, None)
+    assert nm1 == nm0 and np.array_equal(a1, a0)
+    # rows whose LEFT window is empty never reach the right camera (:2541), even with a perfect right match
+    last2 = dict(last); last2["desc"] = dR[np.arange(300) % 200]
+    last2["u"] = np.full(300, 751.0, np.float32); last2["v"] = np.full(300, 479.0, np.float32)
+    nm2, a2 = orc.search_by_projection_frame_rig(gL, gR, desc, SF, last2, 3.0, False, False, False, None)
+    assert nm2 == 0 and np.all(a2 == -1)
+
+
+def test_oracle_rig_bow_quirks(orc, oracle):
+    rng = np.random.default_rng(6)
+    n = 60
+    k1, d1 = _unique_frame(orc, rng, n)
+    # Frame: left rows = exact copies of the keyframe descriptors, right rows = copies with 3 flipped bits
+    dR = d1.copy(); dR[:, 0] ^= 0x07
+    k2 = np.concatenate([k1, k1]); d2 = np.concatenate([d1, dR])
+    kf1 = dict(kps=k1, desc=d1, valid=np.ones(n, np.uint8), **_one_node_fv(n))
+    kf2 = dict(kps=k2, desc=d2, valid=None, **_one_node_fv(2 * n))
+    nm, m = orc.search_by_bow_rig(oracle, kf1, kf2, n, 0.7, False)
+    assert nm == 2 * n and np.array_equal(m[:n], np.arange(n)) and np.array_equal(m[n:], np.arange(n))
+    # with nleft2 == n2 (no right rows) it is the Nleft == -1 branch
+    nm_a, m_a = orc.search_by_bow_rig(oracle, kf1, kf2, 2 * n, 0.7, True)
+    nm_b, m_b = orc.search_by_bow(oracle, 0, kf1, kf2, 0.7, True)
+    assert nm_a == nm_b and np.array_equal(m_a, m_b)
+    # left best fails TH_LOW (random left rows) -> the right match is not even considered (:431 encloses :455)
+    d2b = np.concatenate([rng.integers(0, 256, (n, 32), dtype=np.uint8), dR])
+    nm_c, m_c = orc.search_by_bow_rig(oracle, kf1, dict(kf2, desc=d2b), n, 0.7, False)
+    assert nm_c == 0 and np.all(m_c == -1)
+    # right match ignores its own ratio test (`|| true`): two identical right rows per keyframe keypoint still match
+    d2c = np.concatenate([d1, dR, dR]); k2c = np.concatenate([k1, k1, k1])
+    nm_d, m_d = orc.search_by_bow_rig(oracle, kf1, dict(kps=k2c, desc=d2c, valid=None, **_one_node_fv(3 * n)), n, 0.7, False)
+    assert np.array_equal(m_d[n:2 * n], np.arange(n)) and nm_d == 2 * n
+
+
+def test_oracle_triangulation_callback_order_and_overloads(orc, oracle):
+    rng = np.random.default_rng(7)
+    n = 80
+    k1, d1 = _unique_frame(orc, rng, n)
+    d2 = d1.copy(); d2[:, 1] ^= 0x01                               # every pair (i, i) at distance 1, others ~128
+    kf1 = dict(kps=k1, desc=d1, has_mp=np.zeros(n, np.uint8), **_one_node_fv(n))
+    kf2 = dict(kps=k1, desc=d2, has_mp=np.zeros(n, np.uint8), **_one_node_fv(n))
+    calls = []
+    nm, m = orc.search_for_triangulation_cb(oracle, 0, kf1, kf2, lambda a, b: calls.append((a, b)) or True, False, False, False)
+    assert nm == n and np.array_equal(m, np.arange(n))
+    assert calls == [(i, i) for i in range(n)]                     # only pairs with dist <= TH_LOW reach the camera model
+    # overload 0 marks vbMatched2: with identical KF2 rows the first idx1 takes idx2 = 0 ... overload 1 / 2 do not mark
+    d2s = np.repeat(d1[:1], n, axis=0); d1s = np.repeat(d1[:1], n, axis=0)
+    a = dict(kf1, desc=d1s); b = dict(kf2, desc=d2s)
+    _, m0 = orc.search_for_triangulation_cb(oracle, 0, a, b, lambda i, j: True, False, False, False)
+    _, m1 = orc.search_for_triangulation_cb(oracle, 1, a, b, lambda i, j: True, False, False, False)
+    _, m2 = orc.search_for_triangulation_cb(oracle, 2, a, b, lambda i, j: True, False, False, False)
+    assert np.array_equal(m0, np.arange(n)[::-1])                 # `dist > bestDist` keeps the LAST equal candidate, then marks it
+    assert np.all(m1 == n - 1) and np.all(m2 == n - 1)
+    # bOnlyStereo: nothing with a rig (overloads 0, 1); ignored by overload 2
+    assert orc.search_for_triangulation_cb(oracle, 0, kf1, kf2, lambda i, j: True, True, False, False)[0] == 0
+    assert orc.search_for_triangulation_cb(oracle, 2, kf1, kf2, lambda i, j: True, True, False, False)[0] == n
+
+
+def test_oracle_fisheye_ratio(orc, oracle):
+    rng = np.random.default_rng(8)
+    dL = rng.integers(0, 256, (50, 32), dtype=np.uint8)
+    dR = np.concatenate([rng.integers(0, 256, (7, 32), dtype=np.uint8), dL[10:]])     # right row 7 + k == left row 10 + k
+    good, l2r, r2l, bd = orc.stereo_fisheye_match(oracle, dL, 10, dR, 7)
+    assert good == 40 and np.all(l2r[:10] == -1) and np.array_equal(l2r[10:], np.arange(7, 47)) and np.all(bd[10:] == 0)
+    assert np.all(r2l[:7] == -1) and np.array_equal(r2l[7:], np.arange(10, 50))
+    # fewer than two train rows: knnMatch returns one neighbour, the size() >= 2 test fails
+    good, l2r, _, _ = orc.stereo_fisheye_match(oracle, dL, 10, dR[:8], 7)
+    assert good == 0 and np.all(l2r == -1)
+    # double 0.7: d0 = 7, d1 = 10 -> 7 < 7.000000000000001 is false only if the product rounds to 7.0; pin the arithmetic
+    q = np.zeros((1, 32), np.uint8)
+    t = np.zeros((2, 32), np.uint8); t[0, 0] = 0x7F; t[1, 0] = 0xFF; t[1, 1] = 0x03
+    good, l2r, _, _ = orc.stereo_fisheye_match(oracle, q, 0, t, 0)
+    assert good == int(float(7) < float(10) * 0.7)
