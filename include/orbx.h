@@ -87,6 +87,16 @@ int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t* imgs, int 
                        size_t step, size_t frame_stride, int lap0, int lap1,
                        orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono);
 
+/* One HOST batch spread over several devices (no reference analogue beyond the two extraction threads of
+ * src/Frame.cc:132-137; BASELINE north_star: frame batches partitioned across the GPUs of one box, no collective).
+ * handles[0..ndev): extractors created with the same parameters on the devices to use (distinct handles; several may
+ * share a device).  Frames are split into contiguous ranges - the first nframes % ndev handles take one more - each
+ * driven by its own host thread through orbx_extract_batch; outputs are written in frame order exactly as
+ * orbx_extract_batch writes them.  Returns the first failing range's status. */
+int orbx_extract_batch_multi(orbx_extractor* const* handles, int ndev, int nframes, const uint8_t* imgs, int rows, int cols,
+                             size_t step, size_t frame_stride, int lap0, int lap1,
+                             orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono);
+
 /* ---- frame preparation in front of operator() ------------------------- */
 
 /* cv::initUndistortRectifyMap(..., CV_32F, M1, M2) maps of this extractor's camera

@@ -7,7 +7,7 @@ The directory name contains a hyphen, so import it through `_pkg.load()` at the 
 """
 from . import binding, synth  # noqa: F401
 from .binding import KP_DTYPE, OrbxError  # noqa: F401
-from .extractor import ORBextractor, DescriptorDistance  # noqa: F401
+from .extractor import ORBextractor, DescriptorDistance, extract_batch_multi  # noqa: F401
 from .matcher import (ComputeStereoMatches, ExtractStereo, knn2_hamming, SearchByProjection, SearchByProjectionFrame,  # noqa: F401
                       SearchByProjectionKeyFrame,
                       SearchForInitialization, SearchForTriangulation, SearchByBoW, GetFeaturesInArea,

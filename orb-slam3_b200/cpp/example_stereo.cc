@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <chrono>
 #include <cmath>
+#include <memory>
 #include <thread>
 
 #include "ORBmatcher.h"
@@ -139,6 +140,36 @@ int main()
             if (nFish <= 0 || nBoWRig <= 0 || nProjRig <= 0 || nTriRig <= 0 || asked < nTriRig) return 3;
             left(imLeft, cv::Mat(), mvKeys, mDescriptors, vLapping);             // restore the resident state used below
             right(imRight, cv::Mat(), mvKeysRight, mDescriptorsRight, vLapping);
+        }
+        // --- one host batch over several extractor handles (one per GPU on a multi-GPU box): results in frame order ---
+        {
+            int ndevs = orbx_device_count();
+            std::vector<std::unique_ptr<ORBextractor>> ex;
+            std::vector<orbx_extractor*> hs;
+            const int nh = ndevs > 1 ? ndevs : 2;                   // a single-GPU box: two handles on device 0
+            for (int d = 0; d < nh; d++) { ex.emplace_back(new ORBextractor(1200, 1.2f, 8, 20, 7, d % ndevs)); hs.push_back(ex.back()->handle()); }
+            const int nfr = 2 * nh + 1;
+            std::vector<uint8_t> batch((size_t)nfr * rows * cols);
+            for (int f = 0; f < nfr; f++) {
+                const cv::Mat& src = (f & 1) ? imRight : imLeft;
+                for (int y = 0; y < rows; y++) std::memcpy(batch.data() + ((size_t)f * rows + y) * cols, src.ptr(y), (size_t)cols);
+            }
+            const int cap = orbx_max_keypoints(hs[0], rows, cols);
+            std::vector<orbx_keypoint> bk((size_t)nfr * cap);
+            std::vector<uint8_t> bd((size_t)nfr * cap * 32);
+            std::vector<int> bn((size_t)nfr), bm((size_t)nfr);
+            if (orbx_extract_batch_multi(hs.data(), nh, nfr, batch.data(), rows, cols, (size_t)cols, (size_t)rows * cols, 0, 0,
+                                         bk.data(), bd.data(), cap, bn.data(), bm.data()) != ORBX_OK)
+                throw std::runtime_error(std::string("extract_batch_multi: ") + orbx_last_error());
+            bool ok = true;
+            for (int f = 0; f < nfr && ok; f++) {
+                const std::vector<cv::KeyPoint>& rk = (f & 1) ? mvKeysRight : mvKeys;
+                const cv::Mat& rd = (f & 1) ? mDescriptorsRight : mDescriptors;
+                ok = bn[(size_t)f] == (int)rk.size() && std::memcmp(&bk[(size_t)f * cap], rk.data(), rk.size() * sizeof(cv::KeyPoint)) == 0;
+                for (int i = 0; ok && i < rd.rows; i++) ok = std::memcmp(&bd[((size_t)f * cap + i) * 32], rd.ptr(i), 32) == 0;
+            }
+            std::printf("multi-device batch: %d frames over %d handles on %d device(s): %s\n", nfr, nh, ndevs, ok ? "identical to operator()" : "MISMATCH");
+            if (!ok) return 4;
         }
         // --- the same stereo frame through the one-call entry: identical results ---
         std::vector<cv::KeyPoint> k1, k2;

@@ -7,6 +7,8 @@
 #include <cstring>
 #include <cstdlib>
 #include <algorithm>
+#include <string>
+#include <thread>
 
 static thread_local char g_err[512] = "";
 
@@ -735,6 +737,45 @@ extern "C" int orbx_extract_batch(orbx_extractor* e, int nframes, const uint8_t*
                                   orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono)
 {
     return extract_batch_impl(e, nframes, imgs, rows, cols, step, frame_stride, lap0, lap1, kps, desc, cap, nkp, mono, false);
+}
+
+// ---- one host batch over several devices (north_star: "partitioning frame batches across the 8 GPUs of one box with
+// per-GPU CUDA streams"; the reference's only analogue is the two extraction threads of src/Frame.cc:132-137) ----
+// handles[d] may live on any device (several on one device are allowed).  Frames are split into contiguous ranges, the
+// first nframes % ndev handles take one frame more (the rule of orb-slam3_b200/shard.py); every range is driven by its
+// own host thread through orbx_extract_batch, results land in the caller's arrays in frame order.  No collective, no
+// device-to-device traffic: frames are independent.
+extern "C" int orbx_extract_batch_multi(orbx_extractor* const* handles, int ndev, int nframes, const uint8_t* imgs, int rows, int cols,
+                                        size_t step, size_t frame_stride, int lap0, int lap1,
+                                        orbx_keypoint* kps, uint8_t* desc, int cap, int* nkp, int* mono)
+{
+    if (!handles || ndev <= 0) { orbx_set_error("no extractor handles"); return ORBX_ERR_ARG; }
+    for (int d = 0; d < ndev; d++) {
+        if (!handles[d]) { orbx_set_error("handle %d is null", d); return ORBX_ERR_ARG; }
+        for (int k = 0; k < d; k++) if (handles[k] == handles[d]) { orbx_set_error("handle %d is used twice: a handle is not re-entrant", d); return ORBX_ERR_ARG; }
+    }
+    if (!imgs || rows <= 0 || cols <= 0 || nframes <= 0) { orbx_set_error("empty image"); return ORBX_EMPTY_IMAGE; }
+    if (!kps || !desc || cap <= 0 || !nkp || !mono || step < (size_t)cols) { orbx_set_error("bad output buffers / step"); return ORBX_ERR_ARG; }
+    std::vector<int> rc((size_t)ndev, ORBX_OK);
+    std::vector<std::string> msg((size_t)ndev);
+    std::vector<std::thread> th;
+    const int q = nframes / ndev, r = nframes % ndev;
+    int f0 = 0;
+    for (int d = 0; d < ndev; d++) {
+        const int n = q + (d < r ? 1 : 0);
+        if (n == 0) continue;
+        const int first = f0;
+        th.emplace_back([=, &rc, &msg] {
+            rc[(size_t)d] = orbx_extract_batch(handles[d], n, imgs + (size_t)first * frame_stride, rows, cols, step, frame_stride, lap0, lap1,
+                                              kps + (size_t)first * cap, desc + (size_t)first * cap * 32, cap, nkp + first, mono + first);
+            if (rc[(size_t)d] != ORBX_OK) msg[(size_t)d] = orbx_last_error();       // the message is thread-local: carry it over
+        });
+        f0 += n;
+    }
+    for (std::thread& t : th) t.join();
+    for (int d = 0; d < ndev; d++)
+        if (rc[(size_t)d] != ORBX_OK) { orbx_set_error("device range %d: %s", d, msg[(size_t)d].c_str()); return rc[(size_t)d]; }
+    return ORBX_OK;
 }
 
 // ---- frame preparation in front of operator(): remap + cvtColor on the device (prepare.cu) ----

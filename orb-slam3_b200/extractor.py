@@ -196,3 +196,23 @@ def DescriptorDistance(a: np.ndarray, b: np.ndarray) -> int:
     """ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:2911-2931)."""
     a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
     return binding.load().orbx_hamming256(a.ctypes.data, b.ctypes.data)
+
+
+def extract_batch_multi(extractors, frames: np.ndarray, lapping=(0, 0)):
+    """One host batch over several extractor handles / devices (orbx_extract_batch_multi): contiguous frame ranges, one
+    host thread per handle, results in frame order.  Returns (mono[B], nkp[B], kps[B,cap], desc[B,cap,32])."""
+    assert frames.dtype == np.uint8 and frames.ndim == 3 and frames.flags.c_contiguous and len(extractors) > 0
+    B, rows, cols = frames.shape
+    cap = extractors[0].max_keypoints(rows, cols)
+    kps = np.empty((B, cap), KP_DTYPE); desc = np.empty((B, cap, 32), np.uint8)
+    nkp = np.empty(B, np.int32); mono = np.empty(B, np.int32)
+    hs = (C.c_void_p * len(extractors))(*[x.h for x in extractors])
+    check(binding.load().orbx_extract_batch_multi(hs, len(extractors), B, frames.ctypes.data, rows, cols, frames.strides[1], frames.strides[0],
+                                                  int(lapping[0]), int(lapping[1]), kps.ctypes.data, desc.ctypes.data, cap,
+                                                  nkp.ctypes.data, mono.ctypes.data))
+    per = B // len(extractors); rem = B % len(extractors)
+    for d, x in enumerate(extractors):
+        n = per + (1 if d < rem else 0)
+        if n:
+            x._last_shape = (n, rows, cols)
+    return mono, nkp, kps, desc

@@ -263,3 +263,31 @@ def test_fresh_process_per_geometry(cfg):
         "print('ok')\n")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("nhandles,nframes", [(2, 7), (3, 3), (4, 2), (1, 5)])
+def test_extract_batch_multi(pkg, orc, oracle, nhandles, nframes):
+    """One host batch over several handles (one per device where the box has them, else several on device 0): frame ranges
+    of unequal length, fewer frames than handles; results in frame order and equal to the oracle."""
+    import ctypes
+    ndev = pkg.binding.load().orbx_device_count()
+    rows, cols, nf = 376, 620, 600
+    frames = np.stack([pkg.synth.synth_frame(rows, cols, 800 + s, bands=(s % 2 == 0)) for s in range(nframes)])
+    X = [pkg.ORBextractor(nf, device=d % ndev) for d in range(nhandles)]
+    mono, nkp, kps, desc = pkg.extract_batch_multi(X, frames, (0, 0))
+    E = orc.Extractor(nf, oracle=oracle)
+    for f in range(nframes):
+        m, k, d = E(frames[f], (0, 0))
+        assert mono[f] == m and nkp[f] == len(k) > 100, f
+        assert np.array_equal(kps[f, :nkp[f]], k) and np.array_equal(desc[f, :nkp[f]], d), f
+    # each handle keeps ITS range resident: frame 0 of handle 0 is frame 0 of the batch
+    E(frames[0], (0, 0))
+    assert np.array_equal(X[0].pyramid_level(1, frame=0), E.level_plane(1)[19:-19, 19:-19])
+    # the same handle twice is refused (a handle is not re-entrant)
+    L = pkg.binding.load()
+    hs = (ctypes.c_void_p * 2)(X[0].h, X[0].h)
+    rc = L.orbx_extract_batch_multi(hs, 2, nframes, frames.ctypes.data, rows, cols, cols, rows * cols, 0, 0,
+                                    kps.ctypes.data, desc.ctypes.data, kps.shape[1], nkp.ctypes.data, mono.ctypes.data)
+    assert rc == pkg.binding.ORBX_ERR_ARG
+    for x in X:
+        x.close()
