@@ -92,6 +92,7 @@ static void free_device(orbx_extractor* e)
     if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }   // it holds the old pointers
     for (void* p : e->allocs) cudaFree(p);
     e->allocs.clear();
+    if (e->reserved && e->D.blur_maps) { blur_tma_destroy(e->D.blur_maps); e->D.blur_maps = nullptr; }
     e->reserved = false;
     e->last_nframes = 0;
     e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr; e->d_st_rows = nullptr;
@@ -239,6 +240,7 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     CUDA_TRY(cudaMemsetAsync(D.selcnt, 0, sizeof(*D.selcnt) * B * G.nlevels, e->stream));
     CUDA_TRY(cudaMemsetAsync(D.candcnt, 0, sizeof(*D.candcnt) * B * G.nlevels, e->stream));
     CUDA_TRY(cudaStreamSynchronize(e->stream));
+    D.blur_maps = blur_tma_create(G); D.slot0 = 0;
     e->G = G; e->D = D; e->reserved = true;
     return ORBX_OK;
 }
@@ -269,6 +271,7 @@ static int upload_frames(orbx_extractor* e, int slot0, int nframes, const uint8_
 static void slot_view(const orbx_extractor* e, int s0, FrameGeom* Go, DevBuffers* Do)
 {
     *Go = e->G; *Do = e->D;
+    Do->slot0 = s0;
     const FrameGeom& G = e->G;
     const size_t s = (size_t)s0;
     for (int l = 0; l < G.nlevels; l++) { Go->L[l].pyr += s * G.L[l].plane_bytes; Go->L[l].blur += s * G.L[l].plane_bytes; }

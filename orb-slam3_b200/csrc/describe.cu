@@ -191,18 +191,184 @@ blur_kernel(FrameGeom G)
 #undef BLUR_ROW
 }
 
+// ------------------------------------------------------------------------------------------------
+// TMA variant of the blur (north_star: "staged through shared memory/TMA tiles"): the same arithmetic, but the
+// CTA's input tile - 128 output rows + 6 halo rows of the 128-byte column block - arrives in shared memory by ONE
+// cp.async.bulk.tensor.2d issued by one thread (SASS: UTMALDG) behind an mbarrier, instead of 32 lanes x 38 LDG per warp
+// through a 7-deep register ring.  What it removes: the ring registers, the L2 prefetches and the per-row global
+// address arithmetic; what stays: one LDS per word-row where there was one LDG, and the whole ALU work.
+// Opt-in (ORBX_BLUR_TMA=1): measured on a B200 in DESIGN.md section 5.
+// ------------------------------------------------------------------------------------------------
+#include <cuda.h>
+#define BT_ROWS (BL_BY * BL_RT + 2 * HALO_ROWS_BLUR)      // 134 tile rows
+#define BT_WORDS 36                                       // 144-byte tile rows: 128 bytes + up to 12 of alignment slack
+struct BlurMaps { CUtensorMap map[ORBX_MAX_LEVELS]; };
+
+// tile t of a launch = (frame, level, row group, column block); input box coordinates and the level
+__device__ __forceinline__ int blur_tma_tile(const FrameGeom& G, int t, int per_frame, int slot0, int* f, int* bx, int* y0c, int* cx, int* cy)
+{
+    int bid = t, lvl = 0;
+    if (per_frame > 0) { *f = t / per_frame; bid = t - *f * per_frame; }      // persistent form: linear tile index
+    else *f = blockIdx.y;                                                      // one tile per CTA: grid = (tiles per frame, frames)
+    while (bid >= G.blur_tma_end[lvl]) lvl++;
+    if (lvl > 0) bid -= G.blur_tma_end[lvl - 1];
+    const LevelGeom& L = G.L[lvl];
+    const int nbx = (L.w + 4 * BL_OUTW - 1) / (4 * BL_OUTW);
+    const int by = bid / nbx;
+    *bx = bid - by * nbx;
+    *y0c = by * BL_BY * BL_RT;
+    // the box must start on a 16-byte address (an unaligned start traps with "illegal instruction",
+    // tools/scratch/tma_probe2.cu): start at the aligned address below the left halo word, 144 bytes wide
+    *cx = (ORBX_XOFF + *bx * 4 * BL_OUTW - 4) & ~15;
+    *cy = (slot0 + *f) * L.prow + ORBX_YOFF + *y0c - HALO_ROWS_BLUR;          // row in the stack of planes
+    return lvl;
+}
+
+// STAGES = 1: one tile per CTA (grid = tiles).  STAGES = 2: persistent CTAs walk the tiles with stride gridDim.x and a
+// two-deep shared-memory ring - thread 0 issues the copy of tile k+1 before the CTA computes tile k.
+template <int STAGES>
+__global__ void __launch_bounds__(32 * BL_BY, STAGES == 1 ? BL_MINB : 5)
+blur_tma_kernel(FrameGeom G, const __grid_constant__ BlurMaps M, int slot0, int per_frame, int total)
+{
+    __shared__ __align__(128) uint32_t tile[STAGES][BT_ROWS + 2][BT_WORDS];   // 136 x 144 B: every stage starts on a 128-byte address (TMA destination)
+    __shared__ __align__(8) uint64_t mbar[STAGES];
+    orbx_pdl_prologue();
+    const int lane = threadIdx.x, warp = threadIdx.y;
+    const bool leader = lane == 0 && warp == 0;
+    if (leader) {
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((uint32_t)__cvta_generic_to_shared(&mbar[s])));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int t, int stage) {
+        int f, bx, y0c, cx, cy;
+        const int lvl = blur_tma_tile(G, t, per_frame, slot0, &f, &bx, &y0c, &cx, &cy);
+        const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar[stage]);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mb), "r"((uint32_t)(BT_ROWS * BT_WORDS * 4)) : "memory");
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                     :: "r"((uint32_t)__cvta_generic_to_shared(&tile[stage][0][0])), "l"(reinterpret_cast<uint64_t>(&M.map[lvl])), "r"(cx), "r"(cy), "r"(mb)
+                     : "memory");
+    };
+    if (STAGES == 1) per_frame = 0;
+    int t = blockIdx.x;
+    if (leader && t < total) issue(t, 0);
+#pragma unroll 1
+    for (int k = 0; t < total; k++, t += gridDim.x) {
+        const int stage = STAGES == 1 ? 0 : (k & 1);
+        if (STAGES == 2 && leader && t + (int)gridDim.x < total) issue(t + gridDim.x, stage ^ 1);   // that buffer was released by the barrier below
+        int f, bx, y0c, cx, cy;
+        const int lvl = blur_tma_tile(G, t, per_frame, slot0, &f, &bx, &y0c, &cx, &cy);
+        const LevelGeom& L = G.L[lvl];
+        {   // every thread waits for the tile; the stage's barrier completes once per use: phase = use count & 1
+            const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar[stage]);
+            const uint32_t phase = STAGES == 1 ? 0u : (uint32_t)((k >> 1) & 1);
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                             : "=r"(done) : "r"(mb), "r"(phase) : "memory");
+        }
+        const int pitch = L.pitch, w = L.w, h = L.h;
+        const int y0 = y0c + warp * BL_RT;
+        if (y0 < h) {                                          // warp-uniform
+            const int wi = bx * BL_OUTW - 1 + lane;
+            const int pw = pitch >> 2;
+            const int nr = min(BL_RT, h - y0);
+            const long long plane = (long long)f * L.plane_bytes + (long long)ORBX_YOFF * pitch + ORBX_XOFF;
+            uint32_t* q = reinterpret_cast<uint32_t*>(L.blur + plane) + (long long)y0 * pw + wi;
+            const bool colvalid = lane >= 1 && lane <= BL_OUTW && wi * 4 < w;
+            const int woff = ((ORBX_XOFF + bx * 4 * BL_OUTW - 4) & 15) >> 2;   // words between the box start and the left halo word (1 or 3)
+            const uint32_t* src = &tile[stage][warp * BL_RT][woff + lane];      // tile row 0 of this warp = image row y0 - 3
+            uint32_t WE[7], WO[7];
+#define BT_ROW(SLOT, R)                                                                   \
+            {   const uint32_t raw = src[(R) * BT_WORDS];                                 \
+                WE[SLOT] = __byte_perm(raw, 0u, 0x4240); WO[SLOT] = __byte_perm(raw, 0u, 0x4341); }
+            BT_ROW(0, 0) BT_ROW(1, 1) BT_ROW(2, 2) BT_ROW(3, 3) BT_ROW(4, 4) BT_ROW(5, 5)
+#define BT_STEP(PH)                                                     \
+            {   BT_ROW((PH + 6) % 7, rb + PH + 6)                       \
+                uint32_t VE, VO;                                        \
+                blur_vcol<PH>(WE, WO, VE, VO);                          \
+                const uint32_t El = __shfl_up_sync(0xffffffffu, VE, 1), Ol = __shfl_up_sync(0xffffffffu, VO, 1);     \
+                const uint32_t Er = __shfl_down_sync(0xffffffffu, VE, 1), Or = __shfl_down_sync(0xffffffffu, VO, 1); \
+                const uint32_t vw = blur_hword(El, Ol, VE, VO, Er, Or); \
+                if (colvalid && rb + PH < nr) *q = vw;                  \
+                q += pw;                                                \
+            }
+            // rows past the strip stay inside the tile only for rb + PH + 6 < 38: the last (partial) step group is guarded
+#pragma unroll 1
+            for (int rb = 0; rb < nr; rb += 7) {
+                if (rb + 12 < BL_RT + 2 * HALO_ROWS_BLUR) {
+                    BT_STEP(0) BT_STEP(1) BT_STEP(2) BT_STEP(3) BT_STEP(4) BT_STEP(5) BT_STEP(6)
+                } else {                                       // rb = 28: rows 28..31 only (tile rows up to 37)
+                    BT_STEP(0) BT_STEP(1) BT_STEP(2) BT_STEP(3)
+                }
+            }
+#undef BT_STEP
+#undef BT_ROW
+        }
+        if (STAGES == 2) __syncthreads();                      // every warp is done with this stage's buffer
+    }
+}
+
+typedef CUresult (*orbx_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                        const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                        CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+const void* blur_tma_create(const FrameGeom& G)
+{
+    static orbx_tmap_encode_fn enc = [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) fn = nullptr;
+        return (orbx_tmap_encode_fn)fn;
+    }();
+    if (!enc) return nullptr;
+    BlurMaps* M = new BlurMaps();
+    for (int l = 0; l < G.nlevels; l++) {
+        const LevelGeom& L = G.L[l];
+        // the planes of all frame slots stacked: rows of `pitch` bytes, prow rows per slot
+        const cuuint64_t dims[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.prow * (cuuint64_t)G.batch};
+        const cuuint64_t strides[1] = {(cuuint64_t)L.pitch};
+        const cuuint32_t box[2] = {(cuuint32_t)(BT_WORDS * 4), (cuuint32_t)BT_ROWS};
+        const cuuint32_t estr[2] = {1u, 1u};
+        if (enc(&M->map[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void*)L.pyr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+            delete M;
+            return nullptr;
+        }
+    }
+    return M;
+}
+
+void blur_tma_destroy(const void* maps) { delete static_cast<const BlurMaps*>(maps); }
+
 void blur_plan(FrameGeom& G)
 {
-    int run = 0;
+    int run = 0, run_tma = 0;
     for (int l = 0; l < G.nlevels; l++) {
-        run += ((G.L[l].w + 4 * BL_OUTW - 1) / (4 * BL_OUTW)) * ((G.L[l].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
+        const int nbx = (G.L[l].w + 4 * BL_OUTW - 1) / (4 * BL_OUTW);
+        run += nbx * ((G.L[l].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
         G.blur_end[l] = run;
+        run_tma += nbx * ((G.L[l].h + BL_BY * BL_RT - 1) / (BL_BY * BL_RT));
+        G.blur_tma_end[l] = run_tma;
     }
 }
 
 int launch_blur(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s)
 {
     static const bool pf = [] { const char* e = getenv("ORBX_BLUR_PF"); return !e || atoi(e) != 0; }();
+    // ORBX_BLUR_TMA: 0 = register-ring kernel, 1 = one TMA tile per CTA, 2 = persistent CTAs with a two-deep TMA ring
+    static const int tma = [] { const char* e = getenv("ORBX_BLUR_TMA"); return e ? atoi(e) : 1; }();
+    if (tma && D.blur_maps) {
+        const int per_frame = G.blur_tma_end[G.nlevels - 1], total = per_frame * nframes;
+        if (tma == 2) {
+            const int grid = total < 148 * 5 ? total : 148 * 5;
+            orbx_launch(blur_tma_kernel<2>, dim3(grid), dim3(32, BL_BY), 0, s, G, *static_cast<const BlurMaps*>(D.blur_maps), D.slot0, per_frame, total);
+        } else {
+            orbx_launch(blur_tma_kernel<1>, dim3(per_frame, nframes), dim3(32, BL_BY), 0, s, G, *static_cast<const BlurMaps*>(D.blur_maps), D.slot0, per_frame, per_frame);
+        }
+        return 1;
+    }
     orbx_launch(pf ? blur_kernel<true> : blur_kernel<false>, dim3(G.blur_end[G.nlevels - 1], nframes), dim3(32, BL_BY), 0, s, G);
     (void)D;
     return 1;

@@ -102,6 +102,7 @@ struct FrameGeom {
     int out_cap;
     int iniTh, minTh;
     int blur_end[ORBX_MAX_LEVELS];   // cumulative blur CTAs per frame up to and including level l
+    int blur_tma_end[ORBX_MAX_LEVELS];   // same for the TMA variant (128-row tiles)
     LevelGeom L[ORBX_MAX_LEVELS];
 };
 
@@ -123,11 +124,15 @@ struct DevBuffers {
     orbx_keypoint* kps;       // [batch][out_cap]
     uint8_t* desc;            // [batch][out_cap][32]
     int* counts;              // [batch][2] = {nkp, mono}
+    const void* blur_maps;    // HOST pointer: BlurMaps (TMA tensor maps of the pyramid planes, describe.cu) or NULL
+    int slot0;                // first frame slot of this view (TMA coordinates are absolute)
 };
 
 // kernel launchers (each returns the number of kernel launches it issued)
 int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s);
-void blur_plan(FrameGeom& G);           // fills blur_end[]
+void blur_plan(FrameGeom& G);           // fills blur_end[] (and blur_tma_end[])
+const void* blur_tma_create(const FrameGeom& G);   // tensor maps over the level planes (NULL: TMA path unavailable)
+void blur_tma_destroy(const void* maps);
 void pyramid_fill_border(const LevelGeom& L, int frame, cudaStream_t s);   // mvImagePyramid border on demand
 bool fast_per_level(const FrameGeom& G);
 int launch_pyramid_level(const FrameGeom& G, const DevBuffers& D, int nframes, int l, cudaStream_t s);
