@@ -499,7 +499,8 @@ int orbx_search_by_bow_rig(int device,
  * order: per KF1 keypoint in FeatureVector order, for the KF2 keypoints under the same node with no map point, not
  * matched before (overload 0 only), dist <= TH_LOW and dist <= the best accepted so far.  A callback that stores its
  * 3-D point per idx1 on acceptance reproduces vMatchedPoints.  bOnlyStereo (overloads 0, 1) yields no match with a rig
- * (:1194); bCoarse accepts without calling.  has_mp1 / has_mp2: the keypoint already holds a map point.  matches12[n1]. */
+ * (:1194); with bCoarse the callback is still invoked (`A || bCoarse` evaluates A first) and its answer ignored - pass
+ * verdict = NULL to skip it.  has_mp1 / has_mp2: the keypoint already holds a map point.  matches12[n1]. */
 typedef int (*orbx_pair_verdict_fn)(void* user, int idx1, int idx2);
 int orbx_search_for_triangulation_cb(int device, int overload,
                                      const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,

@@ -39,6 +39,14 @@ $CXX -std=c++14 $COMMON -march=x86-64-v3 -c "$REF/src/ORBextractor.cc" -o "$OUT/
 $CXX -std=c++14 $COMMON -march=x86-64-v3 -c "$HERE/ref_wrap.cc" -o "$OUT/ref_wrap_native.o"
 $CXX -o "$OUT/libref_native.so" "$OUT/ORBextractor_native.o" "$OUT/ref_wrap_native.o" "$OUT/orc_prims_native.o" $LINK
 
+# libref_match.so: the UNMODIFIED src/ORBmatcher.cc over oracle/refshim's Frame / KeyFrame / MapPoint / camera doubles
+# (force-included in front of it; they define the include guards of the real headers) and the restated grid of orc_match.c
+$CC -O3 -fPIC -std=c11 $CANON -c "$HERE/orc_match.c" -o "$OUT/orc_match.o"
+MATCH="-I$HERE/refshim -I$REF -include $HERE/refshim/ref_stubs.h"
+$CXX -std=c++14 $COMMON $CANON $MATCH -c "$REF/src/ORBmatcher.cc" -o "$OUT/ORBmatcher.o"
+$CXX -std=c++14 $COMMON $CANON $MATCH -c "$HERE/ref_match_wrap.cc" -o "$OUT/ref_match_wrap.o"
+$CXX -o "$OUT/libref_match.so" "$OUT/ORBmatcher.o" "$OUT/ref_match_wrap.o" "$OUT/orc_match.o" "$OUT/orc_prims.o" $LINK
+
 rm -f "$OUT"/*.o
-sha256sum "$REF/src/ORBextractor.cc" "$REF/include/ORBextractor.h" > "$OUT/SOURCES.sha256" 2>/dev/null || true
+sha256sum "$REF/src/ORBextractor.cc" "$REF/include/ORBextractor.h" "$REF/src/ORBmatcher.cc" "$REF/include/ORBmatcher.h" > "$OUT/SOURCES.sha256" 2>/dev/null || true
 echo "build_ref.sh: built $(ls "$OUT"/*.so | wc -l) libraries in $OUT"

@@ -94,6 +94,13 @@ typedef Point_<int> Point;
 typedef Point_<float> Point2f;
 typedef Point_<double> Point2d;
 
+template <typename T> struct Point3_ {
+    T x, y, z;
+    Point3_() : x(0), y(0), z(0) {}
+    Point3_(T _x, T _y, T _z) : x(_x), y(_y), z(_z) {}
+};
+typedef Point3_<float> Point3f;
+
 template <typename T> struct Size_ {
     T width, height;
     Size_() : width(0), height(0) {}
@@ -273,6 +280,36 @@ public:
     template <typename T> T& at(int y, int x) { return ((T*)(data + (size_t)y * step.v))[x]; }
     template <typename T> const T& at(int y, int x) const { return ((const T*)(data + (size_t)y * step.v))[x]; }
 
+    /* single-index access on a row or column vector */
+    template <typename T> T& at(int i) { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+    template <typename T> const T& at(int i) const { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+
+    /* ---- CV_32F matrix algebra (only what ORBmatcher.cc's pose arithmetic needs) ---- */
+    Mat t() const
+    {
+        if (type_ != CV_32F) cvshim_fail("Mat::t type");
+        Mat m(cols, rows, CV_32F);
+        for (int y = 0; y < rows; y++)
+            for (int x = 0; x < cols; x++) m.at<float>(x, y) = at<float>(y, x);
+        return m;
+    }
+    /* cv::Mat::dot: double accumulation over all elements */
+    double dot(const Mat& b) const
+    {
+        if (type_ != CV_32F || b.type_ != CV_32F || rows != b.rows || cols != b.cols) cvshim_fail("Mat::dot");
+        double s = 0;
+        for (int y = 0; y < rows; y++)
+            for (int x = 0; x < cols; x++) s += (double)at<float>(y, x) * b.at<float>(y, x);
+        return s;
+    }
+    static Mat eye(int r, int c, int type)
+    {
+        Mat m = zeros(r, c, type);
+        if (type != CV_32F) cvshim_fail("Mat::eye type");
+        for (int i = 0; i < (r < c ? r : c); i++) m.at<float>(i, i) = 1.f;
+        return m;
+    }
+
     static Mat zeros(int r, int c, int type)
     {
         Mat m(r, c, type);
@@ -286,6 +323,137 @@ private:
     uchar* datastart_;
     int wrows_, wcols_;
 };
+
+/* CV_32F matrix product: cv::gemm accumulates every output element in DOUBLE for float inputs of these small sizes
+ * (core/src/matmul.simd.hpp GEMMSingleMul<float,double>) and rounds once. */
+inline Mat operator*(const Mat& a, const Mat& b)
+{
+    if (a.type() != CV_32F || b.type() != CV_32F || a.cols != b.rows) cvshim_fail("Mat * Mat");
+    Mat m(a.rows, b.cols, CV_32F);
+    for (int y = 0; y < a.rows; y++)
+        for (int x = 0; x < b.cols; x++) {
+            double s = 0;
+            for (int k = 0; k < a.cols; k++) s += (double)a.at<float>(y, k) * (double)b.at<float>(k, x);
+            m.at<float>(y, x) = (float)s;
+        }
+    return m;
+}
+inline Mat cvshim_ew(const Mat& a, const Mat& b, int sign)
+{
+    if (a.type() != CV_32F || b.type() != CV_32F || a.rows != b.rows || a.cols != b.cols) cvshim_fail("Mat +- Mat");
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; y++)
+        for (int x = 0; x < a.cols; x++) m.at<float>(y, x) = sign > 0 ? a.at<float>(y, x) + b.at<float>(y, x) : a.at<float>(y, x) - b.at<float>(y, x);
+    return m;
+}
+inline Mat operator+(const Mat& a, const Mat& b) { return cvshim_ew(a, b, +1); }
+inline Mat operator-(const Mat& a, const Mat& b) { return cvshim_ew(a, b, -1); }
+inline Mat operator-(const Mat& a)
+{
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; y++)
+        for (int x = 0; x < a.cols; x++) m.at<float>(y, x) = -a.at<float>(y, x);
+    return m;
+}
+inline Mat operator*(const Mat& a, double s)
+{
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; y++)
+        for (int x = 0; x < a.cols; x++) m.at<float>(y, x) = (float)(a.at<float>(y, x) * s);
+    return m;
+}
+inline Mat operator*(double s, const Mat& a) { return a * s; }
+inline Mat operator/(const Mat& a, double s)
+{
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; y++)
+        for (int x = 0; x < a.cols; x++) m.at<float>(y, x) = (float)(a.at<float>(y, x) / s);
+    return m;
+}
+/* cv::norm(Mat) on CV_32F: L2 with double accumulation */
+inline double norm(const Mat& a)
+{
+    if (a.type() != CV_32F) cvshim_fail("norm(a): only CV_32F");
+    double s = 0;
+    for (int y = 0; y < a.rows; y++)
+        for (int x = 0; x < a.cols; x++) s += (double)a.at<float>(y, x) * (double)a.at<float>(y, x);
+    return std::sqrt(s);
+}
+
+/* Fixed-size matrices: cv::Matx arithmetic is plain float (core/matx.hpp accumulates in _Tp). */
+template <typename T, int M, int N> struct Matx {
+    T val[M * N];
+    Matx() { for (int i = 0; i < M * N; i++) val[i] = T(0); }
+    Matx(T a, T b, T c) { static_assert(M * N == 3, "Matx3"); val[0] = a; val[1] = b; val[2] = c; }
+    Matx(T a, T b, T c, T d, T e, T f, T g, T h, T i)
+    {
+        static_assert(M * N == 9, "Matx9");
+        val[0] = a; val[1] = b; val[2] = c; val[3] = d; val[4] = e; val[5] = f; val[6] = g; val[7] = h; val[8] = i;
+    }
+    T& operator()(int i, int j) { return val[i * N + j]; }
+    const T& operator()(int i, int j) const { return val[i * N + j]; }
+    T& operator()(int i) { return val[i]; }
+    const T& operator()(int i) const { return val[i]; }
+    Matx<T, N, M> t() const
+    {
+        Matx<T, N, M> r;
+        for (int i = 0; i < M; i++)
+            for (int j = 0; j < N; j++) r(j, i) = (*this)(i, j);
+        return r;
+    }
+    T dot(const Matx<T, M, N>& b) const
+    {
+        T s = 0;
+        for (int i = 0; i < M * N; i++) s += val[i] * b.val[i];
+        return s;
+    }
+};
+template <typename T, int M, int N, int L> inline Matx<T, M, L> operator*(const Matx<T, M, N>& a, const Matx<T, N, L>& b)
+{
+    Matx<T, M, L> r;
+    for (int i = 0; i < M; i++)
+        for (int j = 0; j < L; j++) {
+            T s = 0;
+            for (int k = 0; k < N; k++) s += a(i, k) * b(k, j);
+            r(i, j) = s;
+        }
+    return r;
+}
+template <typename T, int M, int N> inline Matx<T, M, N> operator+(const Matx<T, M, N>& a, const Matx<T, M, N>& b)
+{
+    Matx<T, M, N> r;
+    for (int i = 0; i < M * N; i++) r.val[i] = a.val[i] + b.val[i];
+    return r;
+}
+template <typename T, int M, int N> inline Matx<T, M, N> operator-(const Matx<T, M, N>& a, const Matx<T, M, N>& b)
+{
+    Matx<T, M, N> r;
+    for (int i = 0; i < M * N; i++) r.val[i] = a.val[i] - b.val[i];
+    return r;
+}
+template <typename T, int M, int N> inline Matx<T, M, N> operator-(const Matx<T, M, N>& a)
+{
+    Matx<T, M, N> r;
+    for (int i = 0; i < M * N; i++) r.val[i] = -a.val[i];
+    return r;
+}
+template <typename T, int M, int N> inline Matx<T, M, N> operator*(const Matx<T, M, N>& a, float s)
+{
+    Matx<T, M, N> r;
+    for (int i = 0; i < M * N; i++) r.val[i] = a.val[i] * s;
+    return r;
+}
+template <typename T, int M, int N> inline Matx<T, M, N> operator*(float s, const Matx<T, M, N>& a) { return a * s; }
+typedef Matx<float, 3, 3> Matx33f;
+typedef Matx<float, 3, 1> Matx31f;
+typedef Matx<float, 4, 4> Matx44f;
+/* cv::norm(Matx): sqrt of the sum of squares accumulated in double (normL2Sqr<_Tp, double>) */
+template <typename T, int M, int N> inline double norm(const Matx<T, M, N>& a)
+{
+    double s = 0;
+    for (int i = 0; i < M * N; i++) s += (double)a.val[i] * (double)a.val[i];
+    return std::sqrt(s);
+}
 
 class _InputArray {
 public:

@@ -112,6 +112,7 @@ void  orc_stereo_match(const orc_extractor* eL, const orc_extractor* eR,
 typedef struct orc_grid orc_grid;
 orc_grid* orc_grid_build(const orc_keypoint* kps, int n, float minX, float maxX, float minY, float maxY);
 void  orc_grid_destroy(orc_grid* g);
+void  orc_grid_bounds(const orc_grid* g, float* out4);
 int   orc_grid_query(const orc_grid* g, const orc_keypoint* kps, float x, float y, float r,
                      int minLevel, int maxLevel, int32_t* out, int cap);
 

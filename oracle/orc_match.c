@@ -1127,8 +1127,8 @@ int orc_search_by_bow_rig(const orc_keypoint* kps1, const uint8_t* desc1, int n1
  * FeatureVector order that pass `!vbMatched2 && !pMP2`, `dist <= TH_LOW && dist <= bestDist`.  With a rig bStereo1 /
  * bStereo2 are false (:1194, :1222), so bOnlyStereo leaves no candidate and the epipole gate (:1241) is off.
  * Differences kept: overload 0 marks vbMatched2 (:1297) and un-marks it in the histogram filter (:1362), 1 and 2 never
- * mark it; the histogram factor is 30/360 in overload 0 and 1/30 in 1 and 2 (:1166 / :1441 / :1666); bCoarse accepts
- * without asking (overloads 0, 1). */
+ * mark it; the histogram factor is 30/360 in overload 0 and 1/30 in 1 and 2 (:1166 / :1441 / :1666); with bCoarse
+ * (overloads 0, 1) the camera model is still asked - `A || bCoarse` evaluates A first - and its answer ignored. */
 int orc_search_for_triangulation_cb(int overload,
                                     const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
                                     const int32_t* fv1_node, const int32_t* fv1_start, const int32_t* fv1_idx, int nn1,
@@ -1156,9 +1156,9 @@ int orc_search_for_triangulation_cb(int overload,
                 if (vbMatched2[idx2] || has_mp2[idx2]) continue;              /* :1218 / :1701 */
                 const int dist = orc_hamming256(desc1 + 32 * (size_t)idx1, desc2 + 32 * (size_t)idx2);
                 if (dist > TH_LOW || dist > bestDist) continue;               /* :1231 / :1707 */
-                int ok;
-                if (overload != 2 && bCoarse) ok = 1;                         /* :1282 `|| bCoarse` */
-                else ok = verdict(user, idx1, idx2) != 0;
+                /* :1282 `epipolarConstrain(...) || bCoarse`: the camera model is asked FIRST, bCoarse only overrides its answer */
+                int ok = verdict ? verdict(user, idx1, idx2) != 0 : 0;
+                if (overload != 2 && bCoarse) ok = 1;
                 if (ok) { bestIdx2 = idx2; bestDist = dist; }
             }
             if (bestIdx2 >= 0) {
@@ -1213,3 +1213,6 @@ int orc_stereo_fisheye_match(const uint8_t* descL, int nL, int monoLeft, const u
     free(idx); free(dst);
     return good;
 }
+
+/* bounds of a grid (mnMinX, mnMaxX, mnMinY, mnMaxY) - for oracle/ref_match_wrap.cc, which fills the Frame doubles */
+void orc_grid_bounds(const orc_grid* g, float* out4) { out4[0] = g->minX; out4[1] = g->maxX; out4[2] = g->minY; out4[3] = g->maxY; }

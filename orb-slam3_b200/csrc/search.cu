@@ -1223,7 +1223,9 @@ extern "C" int orbx_search_for_triangulation_cb(int device, int overload,
             const int idx2 = c[k].x & 0x3FFFFFFF, dist = c[k].y;
             if (vbMatched2[idx2]) continue;                                       // :1218
             if (dist > bestDist) continue;                                        // :1231 / :1707
-            const bool ok = (overload != 2 && bCoarse) ? true : verdict(user, idx1, idx2) != 0;   // :1282 / :1729
+            // :1282 `epipolarConstrain(...) || bCoarse` evaluates the camera model first: it is asked even when bCoarse overrides it
+            bool ok = verdict ? verdict(user, idx1, idx2) != 0 : false;                           // :1282 / :1729
+            if (overload != 2 && bCoarse) ok = true;
             if (ok) { bestIdx2 = idx2; bestDist = dist; }
         }
         if (bestIdx2 >= 0) {
