@@ -106,6 +106,7 @@ template <typename T> struct Size_ {
     Size_() : width(0), height(0) {}
     Size_(T w, T h) : width(w), height(h) {}
 };
+template <typename T> inline bool operator==(const Size_<T>& a, const Size_<T>& b) { return a.width == b.width && a.height == b.height; }
 typedef Size_<int> Size;
 
 template <typename T> struct Rect_ {

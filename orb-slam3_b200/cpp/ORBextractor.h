@@ -16,7 +16,7 @@
 #include "../../include/orbx.h"
 
 #ifdef ORBX_WITH_OPENCV
-#include <opencv2/core.hpp>
+#include <opencv2/opencv.hpp>       // as the reference's include/ORBextractor.h:24
 #else
 namespace cv {
 struct Point2f { float x, y; };
@@ -31,6 +31,7 @@ struct Mat {                        // CV_8UC1 only: what the hot path exchanges
     Mat(int r, int c, uint8_t* ext, size_t st) : rows(r), cols(c), step(st), data(ext) {}
     void create(int r, int c) { rows = r; cols = c; step = (size_t)c; storage.assign((size_t)r * c, 0); data = storage.data(); }
     void release() { rows = cols = 0; step = 0; data = nullptr; storage.clear(); }
+    void shrinkRows(int r) { rows = r; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     uint8_t* ptr(int r) { return data + (size_t)r * step; }
     const uint8_t* ptr(int r) const { return data + (size_t)r * step; }
@@ -40,8 +41,10 @@ struct Mat {                        // CV_8UC1 only: what the hot path exchanges
 
 #ifdef ORBX_WITH_OPENCV
 #define ORBX_MAT_CREATE(m, r, c) (m).create((r), (c), CV_8U)
+#define ORBX_MAT_SHRINK(m, r) ((m) = (m).rowRange(0, (r)))      // a view of the first r rows: no copy
 #else
 #define ORBX_MAT_CREATE(m, r, c) (m).create((r), (c))
+#define ORBX_MAT_SHRINK(m, r) (m).shrinkRows(r)
 #endif
 
 static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint layout");
@@ -69,27 +72,39 @@ public:
 
     // include/ORBextractor.h:57-59, src/ORBextractor.cc:1534-1659.  The mask is ignored (as in the
     // reference); outputs are resized by the callee; returns monoIndex, -1 for an empty image.
+    // The descriptor matrix is created with the capacity, filled by the library in place and cut to the
+    // keypoint count as a row-range view: no second host pass over the descriptors.
+#ifdef ORBX_WITH_OPENCV
+    int operator()(cv::InputArray _image, cv::InputArray _mask, std::vector<cv::KeyPoint>& _keypoints,
+                   cv::OutputArray _descriptors, std::vector<int>& vLappingArea)
+    {
+        (void)_mask;
+        if (_image.empty()) return -1;                                      // :1538
+        cv::Mat image = _image.getMat();
+        assert(image.type() == CV_8UC1);                                    // :1544
+        cv::Mat descriptors;
+        const int mono = extract(image, _keypoints, descriptors, vLappingArea);
+        if (descriptors.empty()) _descriptors.release();                    // :1570-1572
+        else descriptors.copyTo(_descriptors);                              // shares nothing with the capacity buffer the view came from
+        return mono;
+    }
+    // the overload Frame::ExtractORB reaches when it passes plain cv::Mat objects (src/Frame.cc:482-492): fills the
+    // caller's Mat in place
+    int operator()(const cv::Mat& image, const cv::Mat& /*mask*/, std::vector<cv::KeyPoint>& keypoints,
+                   cv::Mat& descriptors, std::vector<int>& vLappingArea)
+    {
+        if (image.empty()) return -1;
+        assert(image.type() == CV_8UC1);
+        return extract(image, keypoints, descriptors, vLappingArea);
+    }
+#else
     int operator()(const cv::Mat& image, const cv::Mat& /*mask*/, std::vector<cv::KeyPoint>& keypoints,
                    cv::Mat& descriptors, std::vector<int>& vLappingArea)
     {
         if (image.empty()) return -1;                                       // :1538
-        assert(vLappingArea.size() >= 2);
-        const int cap = orbx_max_keypoints(h_, image.rows, image.cols);
-        if (cap < 0) throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
-        keypoints.resize((size_t)cap);
-        scratch_.resize((size_t)cap * 32);
-        int n = 0;
-        const int mono = orbx_extract(h_, image.data, image.rows, image.cols, image.step, vLappingArea[0], vLappingArea[1],
-                                      reinterpret_cast<orbx_keypoint*>(keypoints.data()), scratch_.data(), cap, &n);
-        if (mono < 0) throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
-        keypoints.resize((size_t)n);                                        // :1587
-        if (n == 0) descriptors.release();                                  // :1570-1572
-        else {
-            ORBX_MAT_CREATE(descriptors, n, 32);                            // :1577 (CV_8U)
-            for (int i = 0; i < n; i++) std::memcpy(descriptors.ptr(i), scratch_.data() + (size_t)i * 32, 32);
-        }
-        return mono;
+        return extract(image, keypoints, descriptors, vLappingArea);
     }
+#endif
 
     // include/ORBextractor.h:61-81
     int GetLevels() { return orbx_levels(h_); }
@@ -166,7 +181,34 @@ public:
 
     orbx_extractor* handle() { return h_; }
 
+    // include/ORBextractor.h:83: `std::vector<cv::Mat> mvImagePyramid`, which only Frame::ComputeStereoMatches reads
+    // (src/Frame.cc:1051,1168,1194) - replaced by ORBmatcherGPU::ComputeStereoMatches on the device-resident pyramid.
+    // Callers that still want the member: SetKeepHostPyramid(true) makes every operator() call copy the 8 levels out.
+    std::vector<cv::Mat> mvImagePyramid;
+    void SetKeepHostPyramid(bool on) { keep_host_pyramid_ = on; }
+
 protected:
+    int extract(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, cv::Mat& descriptors, std::vector<int>& vLappingArea)
+    {
+        assert(vLappingArea.size() >= 2);
+        const int cap = orbx_max_keypoints(h_, image.rows, image.cols);
+        if (cap < 0) throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        keypoints.resize((size_t)cap);
+        ORBX_MAT_CREATE(descriptors, cap, 32);                              // :1577 (CV_8U), at capacity
+        int n = 0;
+        const int mono = orbx_extract(h_, image.data, image.rows, image.cols, image.step, vLappingArea[0], vLappingArea[1],
+                                      reinterpret_cast<orbx_keypoint*>(keypoints.data()), descriptors.data, cap, &n);
+        if (mono < 0) throw std::runtime_error(std::string("ORBextractor: ") + orbx_last_error());
+        keypoints.resize((size_t)n);                                        // :1587
+        if (n == 0) descriptors.release();                                  // :1570-1572
+        else ORBX_MAT_SHRINK(descriptors, n);
+        if (keep_host_pyramid_) {
+            mvImagePyramid.resize((size_t)orbx_levels(h_));
+            for (int l = 0; l < (int)mvImagePyramid.size(); l++) mvImagePyramid[(size_t)l] = GetPyramidLevel(l);
+        }
+        return mono;
+    }
+    bool keep_host_pyramid_ = false;
     orbx_extractor* h_ = nullptr;
     std::vector<uint8_t> scratch_;
     int rect_rows_ = 0, rect_cols_ = 0, prep_rows_ = 0, prep_cols_ = 0;
