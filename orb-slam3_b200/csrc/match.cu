@@ -250,7 +250,9 @@ extern "C" int orbx_knn2_hamming_noalloc(int device, const uint8_t* d_q, int nq,
 }
 
 // ---- frame grid + SearchByProjection ----
-#define PROJ_KMAX 256
+#define PROJ_KMAX0 256            // first capacity of a map point's candidate list; grown on demand (t_proj_kmax)
+static thread_local int t_proj_kmax = PROJ_KMAX0;
+#define ORBX_RETRY_KMAX (-1000)   // private: a candidate list overflowed, t_proj_kmax was raised, run again
 
 struct ProjArgs {
     const orbx_keypoint* kps; const uint4* desc; int n; const float* uRight;
@@ -262,7 +264,8 @@ struct ProjArgs {
     int* cell_start;      // GRID_CELLS + 1
     int* cell_idx;        // n
     int* cand_cnt;        // nmp
-    int* cand;            // nmp * PROJ_KMAX * 2 : (idx | octave << 24, dist)
+    int* cand;            // nmp * kmax * 2 : (idx | octave << 24, dist)
+    int kmax;             // capacity of one list
     int* assign;          // n (in/out)
     int* claim0; int* claim1;   // n
     int* choice;          // nmp
@@ -345,7 +348,7 @@ proj_candidates_kernel(ProjArgs A)
         if (cx0 >= GRID_COLS || cx1 < 0 || cy0 >= GRID_ROWS || cy1 < 0) { cx0 = 1; cx1 = 0; }
         const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);        // :828
         const uint4 a0 = A.mp_desc[2 * iMP], a1 = A.mp_desc[2 * iMP + 1];
-        int* out = A.cand + (long long)iMP * PROJ_KMAX * 2;
+        int* out = A.cand + (long long)iMP * A.kmax * 2;
         for (int ix = cx0; ix <= cx1; ix++)
             for (int iy = cy0; iy <= cy1; iy++) {
                 const int c = ix * GRID_ROWS + iy;
@@ -373,14 +376,14 @@ proj_candidates_kernel(ProjArgs A)
                     const unsigned bal = __ballot_sync(0xffffffffu, ok);
                     if (ok) {
                         const int p = cnt + __popc(bal & ((1u << lane) - 1));
-                        if (p < PROJ_KMAX) { out[2 * p] = idx | (oct << 24); out[2 * p + 1] = dist; }
+                        if (p < A.kmax) { out[2 * p] = idx | (oct << 24); out[2 * p + 1] = dist; }
                     }
                     cnt += __popc(bal);
                 }
             }
     }
     if (lane == 0) {
-        if (cnt > PROJ_KMAX) { A.result[1] = 1; cnt = PROJ_KMAX; }
+        if (cnt > A.kmax) { atomicMax(&A.result[1], cnt); cnt = A.kmax; }      // the host re-runs with room for the longest list
         A.cand_cnt[iMP] = cnt;
     }
 }
@@ -404,7 +407,7 @@ proj_resolve_kernel(ProjArgs A)
         __syncthreads();
         int changed = 0, matches = 0;
         for (int i = tid; i < A.nmp; i += 1024) {
-            const int* c = A.cand + (long long)i * PROJ_KMAX * 2;
+            const int* c = A.cand + (long long)i * A.kmax * 2;
             const int nc = A.cand_cnt[i];
             int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
             for (int k = 0; k < nc; k++) {                                 // :100-141
@@ -433,7 +436,7 @@ proj_resolve_kernel(ProjArgs A)
     if (tid == 0) A.result[0] = s_matches;
 }
 
-extern "C" int orbx_search_by_projection(int device,
+static int orbx_search_by_projection_once(int device,
                                          const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
                                          float minX, float maxX, float minY, float maxY,
                                          const float* scaleFactors, int nlevels,
@@ -442,6 +445,7 @@ extern "C" int orbx_search_by_projection(int device,
                                          const float* mp_depth, const uint8_t* mp_inview,
                                          float th, float nnratio, int bFarPoints, float thFarPoints, int32_t* assign)
 {
+    const int kmax = t_proj_kmax;
     if (n < 0 || nmp < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors || !(maxX > minX) || !(maxY > minY) ||
         (n > 0 && (!kps || !desc || !assign)) ||
         (nmp > 0 && (!mp_desc || !mp_projx || !mp_projy || !mp_level || !mp_viewcos || !mp_inview)) ||
@@ -467,7 +471,7 @@ extern "C" int orbx_search_by_projection(int device,
     const size_t o_assign = c.take(N * 4), o_result = c.take(8);
     const size_t in_bytes = c.off;
     const size_t o_cs = c.take(4 * (size_t)(GRID_CELLS + 1)), o_ci = c.take(N * 4), o_cc = c.take(M * 4);
-    const size_t o_cand = c.take(8 * M * PROJ_KMAX), o_c0 = c.take(N * 4), o_c1 = c.take(N * 4), o_ch = c.take(M * 4);
+    const size_t o_cand = c.take(8 * M * (size_t)kmax), o_c0 = c.take(N * 4), o_c1 = c.take(N * 4), o_ch = c.take(M * 4);
     rc = W.reserve(c.off, in_bytes);
     if (rc != ORBX_OK) return rc;
     char* h = W.h; char* d = W.d;
@@ -486,7 +490,7 @@ extern "C" int orbx_search_by_projection(int device,
     A.projxr = mp_projxr ? (const float*)(d + o_pxr) : nullptr;
     A.level = (const int*)(d + o_lv); A.viewcos = (const float*)(d + o_vc);
     A.depth = mp_depth ? (const float*)(d + o_dp) : nullptr; A.inview = (const uint8_t*)(d + o_iv);
-    A.assign = (int*)(d + o_assign); A.result = (int*)(d + o_result);
+    A.assign = (int*)(d + o_assign); A.result = (int*)(d + o_result); A.kmax = kmax;
     A.cell_start = (int*)(d + o_cs); A.cell_idx = (int*)(d + o_ci); A.cand_cnt = (int*)(d + o_cc); A.cand = (int*)(d + o_cand);
     A.claim0 = (int*)(d + o_c0); A.claim1 = (int*)(d + o_c1); A.choice = (int*)(d + o_ch);
     A.n = n; A.nmp = nmp;
@@ -506,10 +510,29 @@ extern "C" int orbx_search_by_projection(int device,
     CUDA_TRYW(cudaGetLastError());
     CUDA_TRYW(cudaMemcpyAsync(h + o_assign, d + o_assign, in_bytes - o_assign, cudaMemcpyDeviceToHost, W.s));
     CUDA_TRYW(cudaStreamSynchronize(W.s));
-    memcpy(assign, h + o_assign, N * 4);
     const int* result = (const int*)(h + o_result);
-    if (result[1]) { orbx_set_error("a map point has more than %d candidates", PROJ_KMAX); return ORBX_ERR_CAPACITY; }
+    if (result[1] > kmax) { t_proj_kmax = (result[1] + 63) / 64 * 64; return ORBX_RETRY_KMAX; }   // nothing of the caller's was touched yet
+    memcpy(assign, h + o_assign, N * 4);
     return result[0];
+}
+
+extern "C" int orbx_search_by_projection(int device,
+                                         const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+                                         float minX, float maxX, float minY, float maxY,
+                                         const float* scaleFactors, int nlevels,
+                                         int nmp, const uint8_t* mp_desc, const float* mp_projx, const float* mp_projy,
+                                         const float* mp_projxr, const int32_t* mp_level, const float* mp_viewcos,
+                                         const float* mp_depth, const uint8_t* mp_inview,
+                                         float th, float nnratio, int bFarPoints, float thFarPoints, int32_t* assign)
+{
+    // a map point whose window holds more keypoints than the candidate lists have room for makes the pass report the
+    // longest list; the lists are regrown (per calling thread, kept) and the pass repeated - the reference has no such limit
+    for (int attempt = 0; attempt < 4; attempt++) {
+        const int r = orbx_search_by_projection_once(device, kps, desc, n, uRight, minX, maxX, minY, maxY, scaleFactors, nlevels, nmp, mp_desc, mp_projx, mp_projy, mp_projxr, mp_level, mp_viewcos, mp_depth, mp_inview, th, nnratio, bFarPoints, thFarPoints, assign);
+        if (r != ORBX_RETRY_KMAX) return r;
+    }
+    orbx_set_error("candidate lists kept overflowing");
+    return ORBX_ERR_CAPACITY;
 }
 
 
@@ -603,7 +626,7 @@ frustum_kernel(FrustumArgs A)
     A.inview[i] = in; A.projx[i] = px; A.projy[i] = py; A.projxr[i] = pxr; A.depth[i] = dep; A.viewcos[i] = vcos; A.level[i] = lvl;
 }
 
-extern "C" int orbx_search_local_points(int device,
+static int orbx_search_local_points_once(int device,
                                         const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
                                         float minX, float maxX, float minY, float maxY,
                                         const float* scaleFactors, int nlevels,
@@ -616,6 +639,7 @@ extern "C" int orbx_search_local_points(int device,
                                         uint8_t* out_inview, float* out_projx, float* out_projy, float* out_projxr,
                                         float* out_depth, float* out_viewcos, int32_t* out_level)
 {
+    const int kmax = t_proj_kmax;
     if (n < 0 || nmp < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors || !(maxX > minX) || !(maxY > minY) ||
         !Rcw || !tcw || !Ow || (n > 0 && (!kps || !desc || !assign)) ||
         (nmp > 0 && (!mp_pos || !mp_normal || !mp_min_dist || !mp_max_dist || (n > 0 && !mp_desc)))) {
@@ -639,7 +663,7 @@ extern "C" int orbx_search_local_points(int device,
     const size_t o_iv = c.take(M), o_px = c.take(M * 4), o_py = c.take(M * 4), o_pxr = c.take(M * 4), o_dp = c.take(M * 4), o_vc = c.take(M * 4), o_lv = c.take(M * 4);
     const size_t out_end = c.off;
     const size_t o_cs = c.take(4 * (size_t)(GRID_CELLS + 1)), o_ci = c.take(N * 4 + 4), o_cc = c.take(M * 4);
-    const size_t o_cl = c.take(search ? 8 * M * PROJ_KMAX : 0), o_c0 = c.take(N * 4 + 4), o_c1 = c.take(N * 4 + 4), o_ch = c.take(M * 4);
+    const size_t o_cl = c.take(search ? 8 * M * (size_t)kmax : 0), o_c0 = c.take(N * 4 + 4), o_c1 = c.take(N * 4 + 4), o_ch = c.take(M * 4);
     rc = W.reserve(c.off, out_end);
     if (rc != ORBX_OK) return rc;
     char* h = W.h; char* d = W.d;
@@ -672,7 +696,7 @@ extern "C" int orbx_search_local_points(int device,
         A.uRight = uRight ? (const float*)(d + o_ur) : nullptr;
         A.mp_desc = (const uint4*)(d + o_md); A.projx = F.projx; A.projy = F.projy; A.projxr = F.projxr;
         A.level = F.level; A.viewcos = F.viewcos; A.depth = F.depth; A.inview = F.inview;
-        A.assign = (int*)(d + o_assign); A.result = (int*)(d + o_result);
+        A.assign = (int*)(d + o_assign); A.result = (int*)(d + o_result); A.kmax = kmax;
         A.cell_start = (int*)(d + o_cs); A.cell_idx = (int*)(d + o_ci); A.cand_cnt = (int*)(d + o_cc); A.cand = (int*)(d + o_cl);
         A.claim0 = (int*)(d + o_c0); A.claim1 = (int*)(d + o_c1); A.choice = (int*)(d + o_ch);
         A.n = n; A.nmp = nmp;
@@ -692,6 +716,7 @@ extern "C" int orbx_search_local_points(int device,
     const size_t d2h0 = search ? o_assign : o_iv;
     CUDA_TRYW(cudaMemcpyAsync(h + d2h0, d + d2h0, out_end - d2h0, cudaMemcpyDeviceToHost, W.s));
     CUDA_TRYW(cudaStreamSynchronize(W.s));
+    if (search && ((const int*)(h + o_result))[1] > kmax) { t_proj_kmax = (((const int*)(h + o_result))[1] + 63) / 64 * 64; return ORBX_RETRY_KMAX; }
     if (out_inview) memcpy(out_inview, h + o_iv, M);
     if (out_projx) memcpy(out_projx, h + o_px, M * 4);
     if (out_projy) memcpy(out_projy, h + o_py, M * 4);
@@ -700,10 +725,33 @@ extern "C" int orbx_search_local_points(int device,
     if (out_viewcos) memcpy(out_viewcos, h + o_vc, M * 4);
     if (out_level) memcpy(out_level, h + o_lv, M * 4);
     if (!search) return 0;
-    memcpy(assign, h + o_assign, N * 4);
     const int* result = (const int*)(h + o_result);
-    if (result[1]) { orbx_set_error("a map point has more than %d candidates", PROJ_KMAX); return ORBX_ERR_CAPACITY; }
+    if (result[1] > kmax) { t_proj_kmax = (result[1] + 63) / 64 * 64; return ORBX_RETRY_KMAX; }   // nothing of the caller's was touched yet
+    memcpy(assign, h + o_assign, N * 4);
     return result[0];
+}
+
+extern "C" int orbx_search_local_points(int device,
+                                        const orbx_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+                                        float minX, float maxX, float minY, float maxY,
+                                        const float* scaleFactors, int nlevels,
+                                        const float* Rcw, const float* tcw, const float* Ow,
+                                        float fx, float fy, float cx, float cy, float mbf, float logScaleFactor,
+                                        int nmp, const float* mp_pos, const float* mp_normal, const float* mp_min_dist,
+                                        const float* mp_max_dist, const uint8_t* mp_desc, const uint8_t* mp_candidate,
+                                        float viewingCosLimit, float th, float nnratio, int bFarPoints, float thFarPoints,
+                                        int32_t* assign,
+                                        uint8_t* out_inview, float* out_projx, float* out_projy, float* out_projxr,
+                                        float* out_depth, float* out_viewcos, int32_t* out_level)
+{
+    // a map point whose window holds more keypoints than the candidate lists have room for makes the pass report the
+    // longest list; the lists are regrown (per calling thread, kept) and the pass repeated - the reference has no such limit
+    for (int attempt = 0; attempt < 4; attempt++) {
+        const int r = orbx_search_local_points_once(device, kps, desc, n, uRight, minX, maxX, minY, maxY, scaleFactors, nlevels, Rcw, tcw, Ow, fx, fy, cx, cy, mbf, logScaleFactor, nmp, mp_pos, mp_normal, mp_min_dist, mp_max_dist, mp_desc, mp_candidate, viewingCosLimit, th, nnratio, bFarPoints, thFarPoints, assign, out_inview, out_projx, out_projy, out_projxr, out_depth, out_viewcos, out_level);
+        if (r != ORBX_RETRY_KMAX) return r;
+    }
+    orbx_set_error("candidate lists kept overflowing");
+    return ORBX_ERR_CAPACITY;
 }
 
 
@@ -874,7 +922,7 @@ struct RigArgs {
     int nL, nR, nmp;
     const int* candL; const int* cntL; const int* candR; const int* cntR;
     const int* l2r; const int* r2l;
-    float nnratio;
+    float nnratio; int kmax;
     int* assign;                 // nL + nR, in/out
     int* claim0; int* claim1;    // first writer row per keypoint (iteration t-1 / t)
     int* last;                   // last writer row per keypoint
@@ -916,7 +964,7 @@ rig_resolve_kernel(RigArgs A)
         int changed = 0, matches = 0;
         for (int i = tid; i < A.nmp; i += 1024) {
             bool fail = false;
-            const int chL = rig_pick(A.candL + (long long)i * PROJ_KMAX * 2, A.cntL[i], prev, 0, 2 * i, -1, A.nnratio, &fail);
+            const int chL = rig_pick(A.candL + (long long)i * A.kmax * 2, A.cntL[i], prev, 0, 2 * i, -1, A.nnratio, &fail);
             int partner = -1;
             if (chL >= 0) {
                 atomicMin(&next[chL], 2 * i); atomicMax(&A.last[chL], 2 * i);
@@ -927,7 +975,7 @@ rig_resolve_kernel(RigArgs A)
             int chR = -1;
             if (!fail) {                                                   // a failed left ratio test `continue`s past the right side
                 bool failR = false;
-                chR = rig_pick(A.candR + (long long)i * PROJ_KMAX * 2, A.cntR[i], prev, A.nL, 2 * i + 1, partner, A.nnratio, &failR);
+                chR = rig_pick(A.candR + (long long)i * A.kmax * 2, A.cntR[i], prev, A.nL, 2 * i + 1, partner, A.nnratio, &failR);
                 if (chR >= 0) {
                     const int p = A.r2l[chR];
                     if (p != -1) { atomicMin(&next[p], 2 * i + 1); atomicMax(&A.last[p], 2 * i + 1); matches++; }
@@ -949,7 +997,7 @@ rig_resolve_kernel(RigArgs A)
     if (tid == 0) A.result[0] = s_matches;
 }
 
-extern "C" int orbx_search_by_projection_rig(int device,
+static int orbx_search_by_projection_rig_once(int device,
                                              const orbx_keypoint* kpsL, int nL, const orbx_keypoint* kpsR, int nR, const uint8_t* desc,
                                              const int32_t* leftToRight, const int32_t* rightToLeft,
                                              float minX, float maxX, float minY, float maxY,
@@ -959,6 +1007,7 @@ extern "C" int orbx_search_by_projection_rig(int device,
                                              const uint8_t* inviewR, const float* projxR, const float* projyR, const int32_t* levelR, const float* viewcosR,
                                              float th, float nnratio, int bFarPoints, float thFarPoints, int32_t* assign)
 {
+    const int kmax = t_proj_kmax;
     if (nL < 0 || nR < 0 || nmp < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !scaleFactors || !(maxX > minX) || !(maxY > minY) ||
         (nL > 0 && (!kpsL || !leftToRight)) || (nR > 0 && (!kpsR || !rightToLeft)) || (nL + nR > 0 && (!desc || !assign)) ||
         (nmp > 0 && (!mp_desc || !inviewL || !projxL || !projyL || !levelL || !viewcosL || !inviewR || !projxR || !projyR || !levelR || !viewcosR)) ||
@@ -986,7 +1035,7 @@ extern "C" int orbx_search_by_projection_rig(int device,
     const size_t o_assign = c.take(N * 4), o_result = c.take(8);
     const size_t in_bytes = c.off;
     size_t o_cs[2], o_ci[2], o_cc[2], o_cl[2];
-    for (int sd = 0; sd < 2; sd++) { o_cs[sd] = c.take(4 * (size_t)(GRID_CELLS + 1)); o_ci[sd] = c.take((sd ? NR : NL) * 4 + 4); o_cc[sd] = c.take(M * 4); o_cl[sd] = c.take(8 * M * PROJ_KMAX); }
+    for (int sd = 0; sd < 2; sd++) { o_cs[sd] = c.take(4 * (size_t)(GRID_CELLS + 1)); o_ci[sd] = c.take((sd ? NR : NL) * 4 + 4); o_cc[sd] = c.take(M * 4); o_cl[sd] = c.take(8 * M * (size_t)kmax); }
     const size_t o_c0 = c.take(N * 4), o_c1 = c.take(N * 4), o_last = c.take(N * 4), o_ch = c.take(M * 8);
     rc = W.reserve(c.off, in_bytes);
     if (rc != ORBX_OK) return rc;
@@ -1012,7 +1061,7 @@ extern "C" int orbx_search_by_projection_rig(int device,
         A.mp_desc = (const uint4*)(d + o_md); A.projx = (const float*)(d + o_px[sd]); A.projy = (const float*)(d + o_py[sd]);
         A.level = (const int*)(d + o_lv[sd]); A.viewcos = (const float*)(d + o_vc[sd]);
         A.depth = mp_depth ? (const float*)(d + o_dp) : nullptr; A.inview = (const uint8_t*)(d + o_iv[sd]);
-        A.result = (int*)(d + o_result);
+        A.result = (int*)(d + o_result); A.kmax = kmax;
         A.cell_start = (int*)(d + o_cs[sd]); A.cell_idx = (int*)(d + o_ci[sd]); A.cand_cnt = (int*)(d + o_cc[sd]); A.cand = (int*)(d + o_cl[sd]);
         A.n = n; A.nmp = nmp;
         A.minX = minX; A.minY = minY;
@@ -1030,15 +1079,35 @@ extern "C" int orbx_search_by_projection_rig(int device,
     RigArgs R;
     R.nL = nL; R.nR = nR; R.nmp = nmp;
     R.candL = (const int*)(d + o_cl[0]); R.cntL = (const int*)(d + o_cc[0]); R.candR = (const int*)(d + o_cl[1]); R.cntR = (const int*)(d + o_cc[1]);
-    R.l2r = (const int*)(d + o_l2r); R.r2l = (const int*)(d + o_r2l); R.nnratio = nnratio;
+    R.l2r = (const int*)(d + o_l2r); R.r2l = (const int*)(d + o_r2l); R.nnratio = nnratio; R.kmax = kmax;
     R.assign = (int*)(d + o_assign); R.claim0 = (int*)(d + o_c0); R.claim1 = (int*)(d + o_c1); R.last = (int*)(d + o_last);
     R.choice = (int*)(d + o_ch); R.result = (int*)(d + o_result);
     rig_resolve_kernel<<<1, 1024, 0, W.s>>>(R);
     CUDA_TRYW(cudaGetLastError());
     CUDA_TRYW(cudaMemcpyAsync(h + o_assign, d + o_assign, in_bytes - o_assign, cudaMemcpyDeviceToHost, W.s));
     CUDA_TRYW(cudaStreamSynchronize(W.s));
-    memcpy(assign, h + o_assign, N * 4);
     const int* result = (const int*)(h + o_result);
-    if (result[1]) { orbx_set_error("a map point has more than %d candidates", PROJ_KMAX); return ORBX_ERR_CAPACITY; }
+    if (result[1] > kmax) { t_proj_kmax = (result[1] + 63) / 64 * 64; return ORBX_RETRY_KMAX; }   // nothing of the caller's was touched yet
+    memcpy(assign, h + o_assign, N * 4);
     return result[0];
+}
+
+extern "C" int orbx_search_by_projection_rig(int device,
+                                             const orbx_keypoint* kpsL, int nL, const orbx_keypoint* kpsR, int nR, const uint8_t* desc,
+                                             const int32_t* leftToRight, const int32_t* rightToLeft,
+                                             float minX, float maxX, float minY, float maxY,
+                                             const float* scaleFactors, int nlevels,
+                                             int nmp, const uint8_t* mp_desc, const float* mp_depth,
+                                             const uint8_t* inviewL, const float* projxL, const float* projyL, const int32_t* levelL, const float* viewcosL,
+                                             const uint8_t* inviewR, const float* projxR, const float* projyR, const int32_t* levelR, const float* viewcosR,
+                                             float th, float nnratio, int bFarPoints, float thFarPoints, int32_t* assign)
+{
+    // a map point whose window holds more keypoints than the candidate lists have room for makes the pass report the
+    // longest list; the lists are regrown (per calling thread, kept) and the pass repeated - the reference has no such limit
+    for (int attempt = 0; attempt < 4; attempt++) {
+        const int r = orbx_search_by_projection_rig_once(device, kpsL, nL, kpsR, nR, desc, leftToRight, rightToLeft, minX, maxX, minY, maxY, scaleFactors, nlevels, nmp, mp_desc, mp_depth, inviewL, projxL, projyL, levelL, viewcosL, inviewR, projxR, projyR, levelR, viewcosR, th, nnratio, bFarPoints, thFarPoints, assign);
+        if (r != ORBX_RETRY_KMAX) return r;
+    }
+    orbx_set_error("candidate lists kept overflowing");
+    return ORBX_ERR_CAPACITY;
 }

@@ -194,6 +194,33 @@ def test_search_by_projection(pkg, orc, oracle, th, stereo, far):
     X.close()
 
 
+def test_search_by_projection_long_candidate_lists(pkg, orc, oracle):
+    """th = 15 right after relocalisation on a dense frame: a map point's window holds far more than the 256 keypoints the
+    candidate lists start with; the reference has no limit, the lists are regrown and the pass repeated."""
+    rng = np.random.default_rng(17)
+    rows, cols, n = 480, 752, 6000
+    kps = np.zeros(n, pkg.KP_DTYPE)
+    kps["x"] = rng.uniform(250, 500, n).astype(np.float32); kps["y"] = rng.uniform(150, 330, n).astype(np.float32)   # a crowded region
+    kps["octave"] = rng.choice(8, n, p=[.3, .22, .16, .12, .08, .06, .04, .02]); kps["angle"] = 0; kps["class_id"] = -1
+    desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    sf = np.cumprod(np.concatenate([[1.0], np.full(7, 1.2)])).astype(np.float32)
+    m = 800
+    src = rng.integers(0, n, m)
+    mp = dict(desc=desc[src] ^ (rng.random((m, 32)) < 0.03).astype(np.uint8),
+              projx=(kps["x"][src] + rng.normal(0, 4, m)).astype(np.float32), projy=(kps["y"][src] + rng.normal(0, 4, m)).astype(np.float32),
+              projxr=np.zeros(m, np.float32), level=np.clip(kps["octave"][src] + 1, 0, 7).astype(np.int32),
+              viewcos=np.full(m, 0.9, np.float32), depth=np.full(m, 5.0, np.float32), inview=np.ones(m, np.uint8))
+    b = (0.0, float(cols), 0.0, float(rows))
+    g = orc.Grid(oracle, kps, *b)
+    longest = max(len(g.query(float(mp["projx"][i]), float(mp["projy"][i]), 4.0 * 15.0 * float(sf[mp["level"][i]]), int(mp["level"][i]) - 1, int(mp["level"][i])))
+                  for i in range(0, m, 16))
+    assert longest > 600                                   # well past the initial capacity
+    for _ in range(2):                                     # second call: the grown lists are kept
+        nm_o, as_o = orc.search_by_projection(g, desc, None, sf, mp, 15.0, 0.8, False, 0.0, None)
+        nm_g, as_g = pkg.SearchByProjection(kps, desc, None, b, sf, mp, 15.0, 0.8, False, 0.0, None)
+        assert nm_o > 100 and nm_g == nm_o and np.array_equal(as_g, as_o)
+
+
 @pytest.mark.parametrize("seed,maxn", [(1, 12), (2, 40), (3, 300)])
 def test_distinctive_descriptors(pkg, orc, oracle, seed, maxn):
     """MapPoint::ComputeDistinctiveDescriptors batched: groups of 0..maxn observation descriptors (ties are frequent:
