@@ -39,7 +39,7 @@ def level_dims(rows, cols, isf):
     return [(int(np.rint(np.float32(rows) * s)), int(np.rint(np.float32(cols) * s))) for s in isf]
 
 
-STAGE_KERNEL = {"pyramid": "pyr_resize_fast_kernel", "fast": "fast_strip_kernel", "blur": "blur_kernel"}
+STAGE_KERNEL = {"pyramid": "pyr_resize_fast_kernel", "fast": "fast_strip_kernel", "blur": "blur_"}     # blur_tma_kernel / blur_kernel
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 
