@@ -58,6 +58,7 @@ def profiled_traffic(stage, frames_per_launch):
         if len(cols) != 2 or any(u is None for _, u in cols.values()):
             continue
         tot = 0.0; frames = None
+        steps = max(1, sum(1 for r in rows[1:] if "describe_kernel" in r[1]))   # a capture may hold several steps
         for r in rows[1:]:
             if STAGE_KERNEL[stage] in r[1]:                 # template instances carry "void ...<...>" around the name
                 tot += sum(float(r[i]) * u for i, u in cols.values())
@@ -65,7 +66,7 @@ def profiled_traffic(stage, frames_per_launch):
                 frames = max(g[1], g[2]) if stage != "pyramid" else g[2]
         if tot == 0.0 or not frames:
             continue                                    # a capture of other kernels (matching legs)
-        return tot * frames_per_launch / frames, f"{f.name} ({frames} frames per launch, scaled to {frames_per_launch})"
+        return tot / steps * frames_per_launch / frames, f"{f.name} ({frames} frames per launch, scaled to {frames_per_launch})"
     return None, None
 
 

@@ -986,10 +986,10 @@ extern "C" int orbx_debug_level_keys(orbx_extractor* e, int frame, int level, in
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     if (!out) return n;
     const int m = n < cap ? n : cap;
-    std::vector<uint32_t> keys((size_t)m);
-    const uint32_t* src = stage == 0 ? e->D.cand + (size_t)frame * G.cand_per_frame + L.cand_base
+    std::vector<orbx_key_t> keys((size_t)m);
+    const orbx_key_t* src = stage == 0 ? e->D.cand + (size_t)frame * G.cand_per_frame + L.cand_base
                                      : e->D.sel + (size_t)frame * G.sel_per_frame + L.sel_base;
-    if (m > 0) CUDA_TRY(cudaMemcpyAsync(keys.data(), src, sizeof(uint32_t) * m, cudaMemcpyDeviceToHost, e->stream));
+    if (m > 0) CUDA_TRY(cudaMemcpyAsync(keys.data(), src, sizeof(orbx_key_t) * m, cudaMemcpyDeviceToHost, e->stream));
     if (m > 0 && stage == 1 && angles)
         CUDA_TRY(cudaMemcpyAsync(angles, e->D.angle + (size_t)frame * G.sel_per_frame + L.sel_base, sizeof(float) * m,
                                  cudaMemcpyDeviceToHost, e->stream));
@@ -997,12 +997,12 @@ extern "C" int orbx_debug_level_keys(orbx_extractor* e, int frame, int level, in
     if (stage == 0) {
         // the device list is unordered; present it in the reference's vToDistributeKeys order
         // (cell row-major, raster inside a cell) = ascending canonical rank, as the quadtree sees it
-        auto rank = [&L](uint32_t k) {
+        auto rank = [&L](orbx_key_t k) {
             const int X3 = (int)KEY_X(k) - 3, Y3 = (int)KEY_Y(k) - 3;
             const int cj = X3 / L.wCell, ci = Y3 / L.hCell;
             return ((ci * L.nCols + cj) << 14) | ((Y3 - ci * L.hCell) << 7) | (X3 - cj * L.wCell);
         };
-        std::sort(keys.begin(), keys.end(), [&](uint32_t a, uint32_t b) { return rank(a) < rank(b); });
+        std::sort(keys.begin(), keys.end(), [&](orbx_key_t a, orbx_key_t b) { return rank(a) < rank(b); });
     }
     for (int i = 0; i < m; i++) {
         out[3 * i] = (int32_t)KEY_X(keys[i]); out[3 * i + 1] = (int32_t)KEY_Y(keys[i]); out[3 * i + 2] = (int32_t)KEY_S(keys[i]);

@@ -35,7 +35,7 @@ assemble_kernel(FrameGeom G, DevBuffers D, float lap0, float lap1)
         const int g = base + tid;
         const int valid = g < total;
         float x = 0.f, y = 0.f;
-        uint32_t key = 0;
+        orbx_key_t key = 0;
         int flag = 0, l = 0, i = 0;
         if (valid) {
             while (g >= s_pref[l + 1]) l++;
@@ -519,7 +519,7 @@ describe_kernel(FrameGeom G, DevBuffers D)
         for (int l = 1; l < G.nlevels; l++) if (slot >= G.L[l].sel_base) lvl = l;
         const LevelGeom& L = G.L[lvl];
         if (slot - L.sel_base >= D.selcnt[f * G.nlevels + lvl]) continue;
-        const uint32_t key = D.sel[(long long)f * G.sel_per_frame + slot];
+        const orbx_key_t key = D.sel[(long long)f * G.sel_per_frame + slot];
         const int x = KEY_X(key) + ORBX_MINB, y = KEY_Y(key) + ORBX_MINB;
         const int pw = L.pitch >> 2;
 

@@ -300,7 +300,7 @@ fast_band_kernel(FrameGeom G, DevBuffers D)
     // quadtree nodes more often than a lane-major order would give).  Up to three pixels of a 4-px row can be
     // strict 3x3 maxima of their cells (two on either side of a cell boundary plus one two pixels away):
     // three ballots rank the lanes.
-    uint32_t* out = D.cand + (long long)f * G.cand_per_frame + L.cand_base + base;
+    orbx_key_t* out = D.cand + (long long)f * G.cand_per_frame + L.cand_base + base;
     const uint32_t lt = (1u << lane) - 1u;
     const int maxcnt = __reduce_max_sync(0xffffffffu, cnt);
     for (int i = 0; i < maxcnt; i++) {
@@ -496,7 +496,7 @@ fast_strip_kernel(FrameGeom G, DevBuffers D, int cta0)
     int base = 0;
     if (lane == 0) base = atomicAdd(&D.candcnt[f * G.nlevels + sd.lvl], total);
     base = __shfl_sync(0xffffffffu, base, 0);
-    uint32_t* out = D.cand + (long long)f * G.cand_per_frame + L.cand_base + base;
+    orbx_key_t* out = D.cand + (long long)f * G.cand_per_frame + L.cand_base + base;
     const uint32_t lt = (1u << lane) - 1u;
     const int maxcnt = __reduce_max_sync(0xffffffffu, cnt);
     for (int i = 0; i < maxcnt; i++) {

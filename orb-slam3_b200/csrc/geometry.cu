@@ -80,7 +80,7 @@ int orbx_compute_geometry(const orbx_extractor* e, int rows, int cols, int batch
         L.maxBX = L.w - ORBX_EDGE + 3; L.maxBY = L.h - ORBX_EDGE + 3;   // :1055-1056
         const float width = (float)(L.maxBX - ORBX_MINB), height = (float)(L.maxBY - ORBX_MINB);
         if (width < 35.f || height < 35.f) return ORBX_ERR_GEOMETRY;   // nCols/nRows would be 0 (:1064-1068 divide by zero)
-        if (L.maxBX - ORBX_MINB > 4095 || L.maxBY - ORBX_MINB > 4095) return ORBX_ERR_GEOMETRY;   // packed key range
+        if (L.maxBX - ORBX_MINB > 32767 || L.maxBY - ORBX_MINB > 32767) return ORBX_ERR_GEOMETRY;   // 16-bit node bounds / resize taps
         L.nCols = (int)(width / 35.f); L.nRows = (int)(height / 35.f);
         L.wCell = (int)ceilf(width / L.nCols); L.hCell = (int)ceilf(height / L.nRows);
         L.cell_base = cells;

@@ -62,7 +62,7 @@ __device__ int block_scan_excl_t(const int* in, int* out, int m, int* s_warp)
     return total;
 }
 
-// node bounds are packed lo | hi << 16 (coordinates relative to minBorder, < 4096)
+// node bounds are packed lo | hi << 16 (coordinates relative to minBorder, < 32768)
 __device__ __forceinline__ int child_of(int x, int y, int bx, int by)
 {
     const int x0 = bx & 0xFFFF, x1 = bx >> 16, y0 = by & 0xFFFF, y1 = by >> 16;
@@ -72,7 +72,7 @@ __device__ __forceinline__ int child_of(int x, int y, int bx, int by)
 }
 
 // position of a candidate in the reference's vToDistributeKeys order (cell row-major, raster inside a cell)
-__device__ __forceinline__ int cand_rank(uint32_t key, const LevelGeom& L)
+__device__ __forceinline__ int cand_rank(orbx_key_t key, const LevelGeom& L)
 {
     const int X3 = (int)KEY_X(key) - 3, Y3 = (int)KEY_Y(key) - 3;
     const int cj = X3 / L.wCell, ci = Y3 / L.hCell;
@@ -83,14 +83,14 @@ __device__ __forceinline__ int cand_rank(uint32_t key, const LevelGeom& L)
 // candidates per thread are fetched before any of them is processed so that their global loads overlap.
 #define OCT_UNROLL 4
 template <int NT, class F>
-__device__ __forceinline__ void for_cands_t(const uint32_t* __restrict__ cand, const uint32_t* kcode, int n, F body)
+__device__ __forceinline__ void for_cands_t(const orbx_key_t* __restrict__ cand, const uint32_t* kcode, int n, F body)
 {
     for (int i0 = threadIdx.x; i0 < n; i0 += OCT_UNROLL * NT) {
-        uint32_t key[OCT_UNROLL], code[OCT_UNROLL];
+        orbx_key_t key[OCT_UNROLL]; uint32_t code[OCT_UNROLL];
 #pragma unroll
         for (int u = 0; u < OCT_UNROLL; u++) {
             const int i = i0 + u * NT;
-            key[u] = i < n ? cand[i] : 0u;
+            key[u] = i < n ? cand[i] : (orbx_key_t)0;
             code[u] = (kcode && i < n) ? kcode[i] : 0u;
         }
 #pragma unroll
@@ -121,7 +121,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     const int tid = threadIdx.x;
     const int cap = L.node_cap;
 
-    const uint32_t* __restrict__ cand = D.cand + (long long)f * G.cand_per_frame + L.cand_base;
+    const orbx_key_t* __restrict__ cand = D.cand + (long long)f * G.cand_per_frame + L.cand_base;
     uint32_t* kcode = D.candnode + (long long)f * G.cand_per_frame + L.cand_base;     // 4*node + child
     int* T = SMEM ? dyn_smem : (D.nodetab + ((long long)f * G.nlevels + lvl) * D.nodetab_per_frame);
     int* BX[2] = {T, T + 3 * cap};               // x0 | x1 << 16
@@ -151,7 +151,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
         for (int i = tid; i < nI * OCT_HNODES; i += OCT_THREADS) Hh[i] = 0;
         __syncthreads();
         int* Hd = Hh + HOFF(OCT_HDEPTH);
-        for_cands(cand, nullptr, n, [&](int i, uint32_t k, int) {
+        for_cands(cand, nullptr, n, [&](int i, orbx_key_t k, int) {
             int r = (int)__fdiv_rn((float)KEY_X(k), L.hX);           // vpIniNodes[kp.pt.x/hX], :740
             r = min(r, L.nIni - 1);
             const int x = KEY_X(k), y = KEY_Y(k);
@@ -175,7 +175,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
         }
         for (int i = tid; i < nI; i += OCT_THREADS) CN[0][i] = Hh[i];
     } else {
-        for_cands(cand, nullptr, n, [&](int i, uint32_t k, int) {
+        for_cands(cand, nullptr, n, [&](int i, orbx_key_t k, int) {
             int r = (int)__fdiv_rn((float)KEY_X(k), L.hX);           // vpIniNodes[kp.pt.x/hX], :740
             r = min(r, L.nIni - 1);
             kcode[i] = 4 * r;
@@ -236,7 +236,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
         if (!fast) {
             // ---- candidate step: relabel, child inside the new node, next round's per-child counts ----
             const int* bx = BX[cur]; const int* by = BY[cur]; const int* cn = CN[cur]; int* cc = CC[cur];
-            for_cands(cand, kcode, n, [&](int i, uint32_t k, int code) {
+            for_cands(cand, kcode, n, [&](int i, orbx_key_t k, int code) {
                 int p;
                 if (materialise) {
                     p = 0;
@@ -388,7 +388,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     // two otherwise ----
     unsigned* best = reinterpret_cast<unsigned*>(aA);
     int* bestrank = aB;
-    uint32_t* sel = D.sel + (long long)f * G.sel_per_frame + L.sel_base;
+    orbx_key_t* sel = D.sel + (long long)f * G.sel_per_frame + L.sel_base;
     const int nout = min(size, L.sel_cap);
     const bool packed = L.nCols * L.nRows <= 1024;
     for (int i = tid; i < size; i += OCT_THREADS) {
@@ -407,13 +407,13 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
         return p;
     };
     if (packed) {
-        for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
+        for_cands(cand, kcode, n, [&](int, orbx_key_t k, int code) {
             atomicMax(&best[node_of(code)], (KEY_S(k) << 24) | (0xFFFFFFu - (uint32_t)cand_rank(k, L)));
         });
     } else {
-        for_cands(cand, kcode, n, [&](int, uint32_t k, int code) { atomicMax(&best[node_of(code)], KEY_S(k)); });
+        for_cands(cand, kcode, n, [&](int, orbx_key_t k, int code) { atomicMax(&best[node_of(code)], KEY_S(k)); });
         __syncthreads();
-        for_cands(cand, kcode, n, [&](int, uint32_t k, int code) {
+        for_cands(cand, kcode, n, [&](int, orbx_key_t k, int code) {
             const int nd = node_of(code);
             if (KEY_S(k) == best[nd]) atomicMin(&bestrank[nd], cand_rank(k, L));
         });

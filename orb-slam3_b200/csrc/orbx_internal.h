@@ -30,10 +30,13 @@
 #define ORBX_HALF_PATCH 15
 #define ORBX_PATCH 31
 
-#define KEY_X(k) (((k) >> 8) & 0xFFFu)
-#define KEY_Y(k) ((k) >> 20)
-#define KEY_S(k) ((k) & 0xFFu)
-#define MAKE_KEY(x, y, s) (((uint32_t)(y) << 20) | ((uint32_t)(x) << 8) | (uint32_t)(s))
+// candidate / selected-keypoint key: y (16 bits) | x (16 bits) | FAST score (8 bits), coordinates relative to minBorder.
+// 64-bit words: 12-bit coordinates in a 32-bit key stopped at level planes of 4111 px.
+typedef uint64_t orbx_key_t;
+#define KEY_X(k) ((uint32_t)((k) >> 8) & 0xFFFFu)
+#define KEY_Y(k) ((uint32_t)((k) >> 24) & 0xFFFFu)
+#define KEY_S(k) ((uint32_t)(k) & 0xFFu)
+#define MAKE_KEY(x, y, s) (((orbx_key_t)(uint32_t)(y) << 24) | ((orbx_key_t)(uint32_t)(x) << 8) | (orbx_key_t)(uint32_t)(s))
 
 struct ResizeTapX { short s0, s1, a0, a1; };   // source cols (clipped) and 11-bit coefficients
 struct ResizeTapY { short s0, s1, b0, b1; };
@@ -112,11 +115,11 @@ struct DevBuffers {
     int in_pitch_cap;         // largest row stride the staging buffer is sized for
     const BandDesc* bands;    // [bands_per_frame] FAST work units (same for every frame)
     const StripDesc* strips;  // [strip_ctas * 4] work units of the strip kernel
-    uint32_t* cand;           // [batch][cand_per_frame]
+    orbx_key_t* cand;         // [batch][cand_per_frame]
     uint32_t* candnode;       // [batch][cand_per_frame]  quadtree scratch: node of each candidate
     int* nodetab;             // quadtree scratch: node tables
     long long nodetab_per_frame;
-    uint32_t* sel;            // [batch][sel_per_frame]
+    orbx_key_t* sel;          // [batch][sel_per_frame]
     int* selcnt;              // [batch][nlevels]
     int* candcnt;             // [batch][nlevels]
     float* angle;             // [batch][sel_per_frame]

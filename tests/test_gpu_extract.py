@@ -174,6 +174,29 @@ def test_ini_extractor_of_c5_40000_features(pkg, orc, oracle):
     X.close()
 
 
+@pytest.mark.parametrize("rows,cols,nf", [(600, 5000, 3000), (4500, 2400, 6000)])
+def test_frames_wider_or_taller_than_4111_px(pkg, orc, oracle, rows, cols, nf):
+    """A level plane beyond 4095 px of keypoint region (5000-px-wide / 4500-px-tall frames): the 12-bit coordinates of the
+    32-bit candidate key used to refuse these (ORBX_ERR_GEOMETRY); keys are 64-bit words with 16-bit coordinates now.
+    (A tall frame must keep width / height >= 0.5: below that the reference's nIni = round(width / height) is 0 and it
+    divides by zero, src/ORBextractor.cc:695-698.)"""
+    img = pkg.synth.synth_frame(rows, cols, 29)
+    E = orc.Extractor(nf, oracle=oracle)
+    mono_o, kps_o, desc_o = E(img, (0, 0))
+    X = pkg.ORBextractor(nf)
+    mono_g, kps_g, desc_g = X(img, (0, 0))
+    for l in range(8):
+        assert np.array_equal(X.pyramid_level(l, padded=True), E.level_plane(l)), f"pyramid level {l}"
+        assert np.array_equal(X.level_keys(l, 0), _cand_arr(E.level_candidates(l))), f"FAST candidates level {l}"
+        sel_g, ang_g = X.level_keys(l, 1)
+        sel_o, ang_o = E.level_selected(l)
+        assert np.array_equal(sel_g, _cand_arr(sel_o)), f"quadtree selection level {l}"
+    assert max(kps_o["x"].max(), kps_o["y"].max()) > 4200
+    assert mono_g == mono_o and len(kps_g) == len(kps_o)
+    assert np.array_equal(kps_g, kps_o) and np.array_equal(desc_g, desc_o)
+    X.close()
+
+
 def test_equal_count_ties_in_the_ordered_phase(pkg, orc, oracle):
     """A regular dot pattern: many quadtree nodes hold the SAME number of candidates when the ordered final phase
     (:909-992) starts, so the split order is decided by the tie-break (count desc, then list position)."""

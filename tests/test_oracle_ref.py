@@ -40,6 +40,7 @@ CASES = [
     ("ini-5x", 480, 752, 5000, (0, 1000), 8, True),
     ("small", 256, 320, 300, (0, 0), 9, True),
     ("1080p", 1080, 1920, 4000, (0, 0), 17, True),
+    ("wide-5000", 600, 5000, 3000, (0, 0), 29, True),
 ]
 
 
