@@ -19,8 +19,13 @@ if [ ! -f "$REF/src/ORBextractor.cc" ]; then
     exit 0
 fi
 mkdir -p "$OUT"
-CXX="${CXX:-g++}"
-CC="${CC:-gcc}"
+# the system compiler, not $CXX: this image exports CXX=/opt/gcc/bin/g++, a wrapper that links libstdc++ STATICALLY; a private
+# copy of the iostream / locale state inside a dlopen'ed library crashes once the process also holds the shared libstdc++
+# (numpy and torch load it).  ORB_REF_CXX / ORB_REF_CC override.
+CXX="${ORB_REF_CXX:-g++}"
+CC="${ORB_REF_CC:-gcc}"
+[ -x /usr/bin/g++ ] && [ -z "$ORB_REF_CXX" ] && CXX=/usr/bin/g++
+[ -x /usr/bin/gcc ] && [ -z "$ORB_REF_CC" ] && CC=/usr/bin/gcc
 COMMON="-O3 -fPIC -w -I$HERE/cvshim -I$REF/include -I$HERE"
 CANON="-ffp-contract=off"
 LINK="-shared -Wl,-Bsymbolic -lm -lpthread"
@@ -46,6 +51,20 @@ MATCH="-I$HERE/refshim -I$REF -include $HERE/refshim/ref_stubs.h"
 $CXX -std=c++14 $COMMON $CANON $MATCH -c "$REF/src/ORBmatcher.cc" -o "$OUT/ORBmatcher.o"
 $CXX -std=c++14 $COMMON $CANON $MATCH -c "$HERE/ref_match_wrap.cc" -o "$OUT/ref_match_wrap.o"
 $CXX -o "$OUT/libref_match.so" "$OUT/ORBmatcher.o" "$OUT/ref_match_wrap.o" "$OUT/orc_match.o" "$OUT/orc_prims.o" $LINK
+
+# libref_bow.so: the reference's vendored, UNMODIFIED DBoW2 (Thirdparty/DBoW2) - ORBVocabulary::loadFromTextFile / transform
+DBOW="$REF/Thirdparty/DBoW2"
+if [ -f "$DBOW/DBoW2/TemplatedVocabulary.h" ]; then
+    BOW="-O3 -fPIC -w $CANON -I$HERE/cvshim -I$HERE/boostshim -I$DBOW"
+    BOWOBJ=""
+    for f in DBoW2/BowVector DBoW2/FORB DBoW2/FeatureVector DBoW2/ScoringObject DUtils/Random DUtils/Timestamp; do
+        o="$OUT/dbow_$(basename $f).o"
+        $CXX -std=c++14 $BOW -c "$DBOW/$f.cpp" -o "$o"
+        BOWOBJ="$BOWOBJ $o"
+    done
+    $CXX -std=c++14 $BOW -c "$HERE/ref_bow_wrap.cc" -o "$OUT/ref_bow_wrap.o"
+    $CXX -o "$OUT/libref_bow.so" $BOWOBJ "$OUT/ref_bow_wrap.o" "$OUT/orc_prims.o" $LINK
+fi
 
 rm -f "$OUT"/*.o
 sha256sum "$REF/src/ORBextractor.cc" "$REF/include/ORBextractor.h" "$REF/src/ORBmatcher.cc" "$REF/include/ORBmatcher.h" > "$OUT/SOURCES.sha256" 2>/dev/null || true

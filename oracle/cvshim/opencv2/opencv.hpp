@@ -35,6 +35,9 @@
 
 typedef unsigned char uchar;
 
+#include <stdexcept>
+#include <string>
+#include <sstream>      /* the real core.hpp pulls it in; the vendored DBoW2 relies on that */
 namespace cv {
 
 typedef ::uchar uchar;
@@ -587,5 +590,36 @@ struct KeyPointsFilter {
         }
     }
 };
+
+/* persistence (core/persistence.hpp): the vendored DBoW2's YAML save / load (TemplatedVocabulary.h:1456-1620) are virtual
+ * members and must compile; ORB-SLAM3 only ever calls loadFromTextFile (plain fstream), so these throw if reached. */
+class FileNode {
+public:
+    FileNode operator[](const char*) const { unreachable(); return FileNode(); }
+    FileNode operator[](const std::string&) const { unreachable(); return FileNode(); }
+    FileNode operator[](int) const { unreachable(); return FileNode(); }
+    size_t size() const { unreachable(); return 0; }
+    operator int() const { unreachable(); return 0; }
+    operator float() const { unreachable(); return 0.f; }
+    operator double() const { unreachable(); return 0.0; }
+    operator std::string() const { unreachable(); return std::string(); }
+private:
+    static void unreachable() { throw std::runtime_error("cvshim: cv::FileStorage is not implemented (YAML vocabulary path is unused)"); }
+};
+class FileStorage {
+public:
+    enum Mode { READ = 0, WRITE = 1 };
+    FileStorage() {}
+    FileStorage(const std::string&, int) {}
+    bool isOpened() const { return false; }
+    void release() {}
+    FileNode operator[](const char*) const { return FileNode()["x"]; }
+    FileNode operator[](const std::string&) const { return FileNode()["x"]; }
+};
+template <class T> inline FileStorage& operator<<(FileStorage& fs, const T&)
+{
+    throw std::runtime_error("cvshim: cv::FileStorage is not implemented (YAML vocabulary path is unused)");
+    return fs;
+}
 
 } // namespace cv

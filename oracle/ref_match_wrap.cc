@@ -425,3 +425,189 @@ int ref_search_for_triangulation_cb(int overload,
 }
 
 } // extern "C"
+
+namespace {
+
+cv::Mat identity4()
+{
+    cv::Mat T = cv::Mat::eye(4, 4, CV_32F);
+    return T;
+}
+
+/* a map point the reference's pose arithmetic (identity pose, camera double (x, y, z) -> (x, y)) projects to pixel (u, v)
+ * at depth z, passing the distance (:610-617) and viewing-angle (:621-624) gates: normal = the viewing ray itself */
+MapPoint* projected_point(Pool& pool, int index, const uint8_t* desc, float u, float v, float z, int level, int nobs = 1)
+{
+    MapPoint* p = pool.make(index, desc, nobs);
+    p->mWorldPos = point3(u, v, z);
+    p->mNormal = point3(u, v, z);
+    p->mfMinDistance = 0.f; p->mfMaxDistance = 3.0e38f;
+    p->predicted_level = level;
+    return p;
+}
+
+void fill_keyframe(KeyFrame& K, const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* sf, GeometricCamera* cam)
+{
+    K.N = n; K.Nleft = -1; K.NLeft = -1;
+    K.mvKeysUn = keys(kps, n); K.mvKeys = K.mvKeysUn; K.mDescriptors = desc_matrix(desc, n);
+    K.mvuRight.assign((size_t)n, -1.f);
+    K.mpCamera = cam; K.Tcw = identity4(); K.Trl = identity4();
+    set_levels(K, sf); set_bounds(K, g); K.grid = const_cast<orc_grid*>(g);
+    K.mvpMapPoints.assign((size_t)n, nullptr);
+}
+
+} // namespace
+
+extern "C" {
+
+/* ORBmatcher::SearchByProjection(Frame&, KeyFrame*, const set<MapPoint*>&, th, ORBdist), src/ORBmatcher.cc:2723-2862;
+ * arguments as orc_search_by_projection_keyframe */
+int ref_search_by_projection_keyframe(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* sf,
+                                      int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                      const int32_t* mp_level, const float* mp_angle, const uint8_t* mp_valid,
+                                      float th, int ORBdist, int checkOrientation, const uint8_t* cur_held, int32_t* assign)
+{
+    Frame Cur; KeyFrame K; Pool pool; GeometricCamera cam;
+    Cur.N = n; Cur.Nleft = -1; Cur.mvKeysUn = keys(kps, n); Cur.mvKeys = Cur.mvKeysUn; Cur.mDescriptors = desc_matrix(desc, n);
+    Cur.mvuRight.assign((size_t)n, -1.f); Cur.mpCamera = &cam; Cur.mTcw = identity4();
+    set_levels(Cur, sf); set_bounds(Cur, g); Cur.grid = const_cast<orc_grid*>(g);
+    Cur.mvpMapPoints.assign((size_t)n, nullptr);
+    for (int i = 0; i < n; i++) if (cur_held && cur_held[i]) Cur.mvpMapPoints[i] = pool.make(-2, nullptr, 1);
+    K.N = nmp; K.mvKeysUn.resize((size_t)nmp); K.mvpMapPoints.assign((size_t)nmp, nullptr);
+    std::set<MapPoint*> already;
+    for (int i = 0; i < nmp; i++) {
+        K.mvKeysUn[i].angle = mp_angle[i];
+        /* invalid rows alternate between the three ways the reference skips a keyframe keypoint (:2746-2750) */
+        if (!mp_valid[i] && i % 3 == 0) continue;                                        /* pMP == NULL */
+        MapPoint* p = projected_point(pool, i, mp_desc + 32 * (size_t)i, mp_u[i], mp_v[i], 1.f, mp_level[i]);
+        if (!mp_valid[i]) { if (i % 3 == 1) p->mbBad = true; else already.insert(p); }
+        K.mvpMapPoints[i] = p;
+    }
+    K.mvKeys = K.mvKeysUn;
+    ORBmatcher m(0.9f, checkOrientation != 0);
+    const int r = m.SearchByProjection(Cur, &K, already, th, ORBdist);
+    for (int i = 0; i < n; i++) {
+        MapPoint* p = Cur.mvpMapPoints[i];
+        assign[i] = (p && p->index >= 0) ? p->index : -1;
+    }
+    return r;
+}
+
+/* ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th, ratioHamming), src/ORBmatcher.cc:549-678, and (every
+ * second call) its twin with vpPointsKFs / vpMatchedKF, :681-797; arguments as orc_search_by_projection_sim3 */
+int ref_search_by_projection_sim3(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* sf,
+                                  int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v,
+                                  const int32_t* mp_level, const uint8_t* mp_valid,
+                                  float th, float ratioHamming, const uint8_t* matched, int32_t* assign)
+{
+    static int flip = 0;
+    KeyFrame K, other; Pool pool; GeometricCamera cam;
+    fill_keyframe(K, g, kps, desc, n, sf, &cam);
+    std::vector<MapPoint*> vpPoints((size_t)nmp), vpMatched((size_t)n, nullptr);
+    std::vector<KeyFrame*> vpPointsKFs((size_t)nmp, &other), vpMatchedKF((size_t)n, nullptr);
+    for (int i = 0; i < n; i++) if (matched && matched[i]) vpMatched[i] = pool.make(-2, nullptr, 1);
+    for (int i = 0; i < nmp; i++) {
+        MapPoint* p = projected_point(pool, i, mp_desc + 32 * (size_t)i, mp_u[i], mp_v[i], 1.f, mp_level[i]);
+        if (!mp_valid[i]) p->mbBad = true;                                               /* :582 */
+        vpPoints[i] = p;
+    }
+    ORBmatcher m(0.9f, true);
+    cv::Mat Scw = identity4();
+    const int r = (flip++ & 1) ? m.SearchByProjection(&K, Scw, vpPoints, vpPointsKFs, vpMatched, vpMatchedKF, (int)th, ratioHamming)
+                               : m.SearchByProjection(&K, Scw, vpPoints, vpMatched, (int)th, ratioHamming);
+    for (int i = 0; i < n; i++) {
+        MapPoint* p = vpMatched[i];
+        assign[i] = (p && p->index >= 0) ? p->index : -1;
+    }
+    return r;
+}
+
+/* ORBmatcher::Fuse(KeyFrame*, const vector<MapPoint*>&, th, bRight = false), src/ORBmatcher.cc:1823-2035 (mp_ur != NULL), and
+ * Fuse(KeyFrame*, Scw, vpPoints, th, vpReplacePoint), :2051-2185 (mp_ur == NULL); arguments as orc_fuse.
+ * The first form computes ur = uv.x - bf * invz itself (:1912): the double uses bf = 1 and the depth z = 1 / (mp_u - mp_ur), so
+ * every valid row must satisfy mp_u - fl(1 / z) == mp_ur in float arithmetic (disparities that are powers of two do); -1000
+ * otherwise.  best_dist is not observable through the reference's interface: rows come back as -1.
+ * best_idx is read from what the reference did to the map: AddObservation(pKF, bestIdx) for the first point that lands on a
+ * keypoint, Replace(the point already there) for the later ones (the doubles' observation counts make that the branch taken). */
+int ref_fuse(const orc_grid* g, const orc_keypoint* kps, const uint8_t* desc, int n, const float* uRight,
+             const float* sf, const float* inv_sigma2,
+             int nmp, const uint8_t* mp_desc, const float* mp_u, const float* mp_v, const float* mp_ur,
+             const int32_t* mp_level, const uint8_t* mp_valid, float th, int32_t* best_idx, int32_t* best_dist)
+{
+    KeyFrame K; Pool pool; GeometricCamera cam;
+    fill_keyframe(K, g, kps, desc, n, sf, &cam);
+    if (uRight) K.mvuRight.assign(uRight, uRight + n);
+    if (inv_sigma2) K.mvInvLevelSigma2.assign(inv_sigma2, inv_sigma2 + 8);
+    K.mbf = 1.f;
+    std::vector<MapPoint*> vp((size_t)nmp, nullptr);
+    for (int i = 0; i < nmp; i++) {
+        best_idx[i] = -1; best_dist[i] = -1;
+        if (!mp_valid[i] && mp_ur && i % 3 == 0) continue;                               /* !pMP, :1864 (first form only) */
+        float z = 1.f;
+        if (mp_ur && mp_valid[i]) {
+            const float d = mp_u[i] - mp_ur[i];
+            if (!(d > 0.f)) return -1000;
+            z = 1.f / d;
+            const float invz = 1 / z;
+            const float ur = mp_u[i] - 1.f * invz;
+            if (ur != mp_ur[i]) return -1000;
+        }
+        MapPoint* p = projected_point(pool, i, mp_desc + 32 * (size_t)i, mp_u[i], mp_v[i], z, mp_level[i], /*nobs=*/1);
+        if (!mp_valid[i]) { if (i % 3 == 1 || !mp_ur) p->mbBad = true; else p->obs[&K] = std::make_pair(0, -1); }   /* isBad / IsInKeyFrame */
+        vp[i] = p;
+    }
+    ORBmatcher m(0.9f, true);
+    int r;
+    std::vector<MapPoint*> vpReplace((size_t)nmp, nullptr);
+    if (mp_ur) r = m.Fuse(&K, vp, th, false);
+    else { cv::Mat Scw = identity4(); r = m.Fuse(&K, Scw, vp, th, vpReplace); }
+    for (int i = 0; i < nmp; i++) {
+        MapPoint* p = vp[i];
+        if (!p || !mp_valid[i]) continue;
+        MapPoint* there = mp_ur ? p->replaced : vpReplace[i];
+        if (there) {                                                                     /* landed on an occupied keypoint */
+            auto it = there->obs.find(&K);
+            best_idx[i] = it == there->obs.end() ? -2 : it->second.first;
+        } else {
+            auto it = p->obs.find(&K);
+            if (it != p->obs.end()) best_idx[i] = it->second.first;
+        }
+    }
+    return r;
+}
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th), src/ORBmatcher.cc:2201-2434; arguments as orc_search_by_sim3 */
+int ref_search_by_sim3(const orc_grid* g1, const orc_keypoint* kps1, const uint8_t* desc1, int n1,
+                       const orc_grid* g2, const orc_keypoint* kps2, const uint8_t* desc2, int n2, const float* sf,
+                       const uint8_t* mp1_desc, const float* u1in2, const float* v1in2, const int32_t* level1, const uint8_t* valid1,
+                       const uint8_t* mp2_desc, const float* u2in1, const float* v2in1, const int32_t* level2, const uint8_t* valid2,
+                       float th, int32_t* match12)
+{
+    KeyFrame K1, K2; Pool pool; GeometricCamera cam;
+    fill_keyframe(K1, g1, kps1, desc1, n1, sf, &cam);
+    fill_keyframe(K2, g2, kps2, desc2, n2, sf, &cam);
+    std::vector<MapPoint*> vpMatches12((size_t)n1, nullptr);
+    for (int i = 0; i < n1; i++) {
+        if (!valid1[i] && i % 3 == 0) continue;                                          /* !pMP, :2262 */
+        MapPoint* p = projected_point(pool, i, mp1_desc + 32 * (size_t)i, u1in2[i], v1in2[i], 1.f, level1[i]);
+        if (!valid1[i]) { if (i % 3 == 1) p->mbBad = true; else vpMatches12[i] = pool.make(-2, nullptr, 1); }   /* isBad / vbAlreadyMatched1 */
+        K1.mvpMapPoints[i] = p;
+    }
+    for (int i = 0; i < n2; i++) {
+        if (!valid2[i] && i % 2 == 0) continue;
+        MapPoint* p = projected_point(pool, i, mp2_desc + 32 * (size_t)i, u2in1[i], v2in1[i], 1.f, level2[i]);
+        if (!valid2[i]) p->mbBad = true;
+        K2.mvpMapPoints[i] = p;
+    }
+    ORBmatcher m(0.9f, true);
+    const float s12 = 1.f;
+    cv::Mat R12 = cv::Mat::eye(3, 3, CV_32F), t12 = cv::Mat::zeros(3, 1, CV_32F);
+    const int r = m.SearchBySim3(&K1, &K2, vpMatches12, s12, R12, t12, th);
+    for (int i = 0; i < n1; i++) {
+        MapPoint* p = vpMatches12[i];
+        match12[i] = (p && p->index >= 0) ? p->index : -1;
+    }
+    return r;
+}
+
+} // extern "C"

@@ -37,7 +37,8 @@ public:
         if (n1 != 0 || n2 != 0) throw std::runtime_error("ORBVocabulary: only L1_NORM scoring / TF_IDF weighting (ORBvoc.txt) is implemented");
         std::vector<int32_t> parent; std::vector<uint8_t> leaf, desc; std::vector<double> weight;
         while (std::getline(f, s)) {
-            if (s.empty()) continue;
+            if (s.empty()) continue;      // the reference's `while(!f.eof())` turns a trailing empty line into one more node built from
+                                          // uninitialised locals (pid, nIsLeaf of the previous row in practice); not reproduced
             std::stringstream sn(s);
             int pid = 0, isLeaf = 0; double w = 0;
             sn >> pid >> isLeaf;

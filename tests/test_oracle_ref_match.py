@@ -308,3 +308,118 @@ def test_search_for_triangulation_callback(orc, oracle, refo, overload, only_ste
     assert a[0] == b[0] and np.array_equal(a[1], b[1]), f"{np.sum(a[1] != b[1])} matches differ"
     assert ca == cb, "the reference asks the camera model for other pairs / in another order"
     assert "orc_search_for_triangulation_cb" in refo.L.routed
+
+
+# ---- the loop-closing / relocalisation / local-mapping searches (second half) ----
+
+from test_gpu_search import _projected_rows
+
+
+@pytest.mark.parametrize("th,orb_dist,orient,seed", [(10.0, 100, True, 51), (3.0, 64, True, 52), (10.0, 100, False, 53)])
+def test_search_by_projection_keyframe(orc, oracle, refo, th, orb_dist, orient, seed):
+    """ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:2723-2862 (Relocalization)."""
+    rng = np.random.default_rng(seed)
+    rows, cols, n = 480, 752, 1500
+    kkps, kdesc, _, _ = _frame(orc, rng, n, rows, cols)
+    ckps, cdesc, perm = _moved(orc, rng, kkps, kdesc, rows, cols)
+    mp = dict(desc=_flip(rng, kdesc.copy(), 0, 10),
+              u=(kkps["x"] + 4.0 + rng.normal(0, 2, n)).astype(np.float32), v=(kkps["y"] - 3.0 + rng.normal(0, 2, n)).astype(np.float32),
+              level=np.clip(kkps["octave"] + rng.choice([-1, 0, 0, 1], n), 0, 7).astype(np.int32), angle=kkps["angle"],
+              valid=(rng.random(n) < 0.8).astype(np.uint8))
+    mp["u"][:4] = [0.0, float(cols), -0.5, float(cols) + 0.5]        # the frame's bounds are inclusive here (:2761-2764)
+    held = (rng.random(n) < 0.1).astype(np.uint8)
+    b = (0.0, float(cols), 0.0, float(rows))
+    out = [orc.search_by_projection_keyframe(orc.Grid(o, ckps, *b), cdesc, SF, mp, th, orb_dist, orient, held) for o in (oracle, refo)]
+    assert out[0][0] == out[1][0] > 100 and np.array_equal(out[0][1], out[1][1])
+    assert "orc_search_by_projection_keyframe" in refo.L.routed
+
+
+@pytest.mark.parametrize("th,ratio,seed,use_held", [(3.0, 1.0, 61, True), (8.0, 1.5, 62, True), (5.0, 0.6, 63, False), (8.0, 5.0, 64, True),
+                                                    (3.0, 1.0, 65, True)])
+def test_search_by_projection_sim3(orc, oracle, refo, th, ratio, seed, use_held):
+    """ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th, ratioHamming), src/ORBmatcher.cc:549-678, and the
+    vpPointsKFs / vpMatchedKF twin :681-797 (the wrapper alternates between the two overloads from call to call).
+    ratioHamming stays below 256 / TH_LOW = 5.12: above it a map point without any candidate at its level passes
+    `bestDist <= TH_LOW * ratioHamming` with bestIdx = -1 and the reference writes vpMatched[-1] (:667-670; it aborts here). The
+    restatement and the product skip such a row (tests/test_gpu_search.py runs ratio 6.0)."""
+    rng = np.random.default_rng(seed)
+    rows, cols, n = 480, 752, 1500
+    kkps, kdesc, _, _ = _frame(orc, rng, n, rows, cols)
+    ckps, cdesc, perm = _moved(orc, rng, kkps, kdesc, rows, cols)
+    mp = _projected_rows(orc, rng, kkps, kdesc, n, rows, cols)
+    held = (rng.random(n) < 0.15).astype(np.uint8) if use_held else None
+    b = (0.0, float(cols), 0.0, float(rows))
+    out = [orc.search_by_projection_sim3(orc.Grid(o, ckps, *b), cdesc, SF, mp, th, ratio, held) for o in (oracle, refo)]
+    assert out[0][0] == out[1][0] > 50 and np.array_equal(out[0][1], out[1][1])
+    assert "orc_search_by_projection_sim3" in refo.L.routed
+
+
+def _exact_disparity_rows(rng, mp, n):
+    """ur = u - d with d a power of two: the reference recomputes ur = uv.x - bf * (1 / z) from the depth (:1912), and the
+    double's z = 1 / d must reproduce ur in float arithmetic; rows where it would not are taken out (valid = 0)."""
+    d = (2.0 ** rng.integers(-2, 6, n)).astype(np.float32)
+    u = mp["u"].astype(np.float32)
+    ur = (u - d).astype(np.float32)
+    dd = (u - ur).astype(np.float32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        z = (np.float32(1) / dd).astype(np.float32)
+        back = (u - (np.float32(1) / z).astype(np.float32)).astype(np.float32)
+    ok = (dd > 0) & (back == ur)
+    mp["ur"] = ur
+    mp["valid"] = (mp["valid"].astype(bool) & ok).astype(np.uint8)
+    return mp
+
+
+@pytest.mark.parametrize("form,stereo,th,seed", [("pose", True, 3.0, 71), ("pose", False, 3.0, 72), ("sim3", False, 4.0, 73), ("pose", True, 10.0, 74),
+                                                 ("sim3", False, 10.0, 75)])
+def test_fuse(orc, oracle, refo, form, stereo, th, seed):
+    """ORBmatcher::Fuse(KeyFrame*, vpMapPoints, th, bRight) src/ORBmatcher.cc:1823-2035 and Fuse(KeyFrame*, Scw, vpPoints, th,
+    vpReplacePoint) :2051-2185.  The fuse target of every row is read back from what the reference did to the map
+    (AddObservation / Replace / vpReplacePoint); the reference does not expose bestDist, so distances are checked on the oracle's side."""
+    rng = np.random.default_rng(seed)
+    rows, cols, n = 480, 752, 1800
+    kkps, kdesc, _, _ = _frame(orc, rng, n, rows, cols, quant=0.5)
+    ckps, cdesc, perm = _moved(orc, rng, kkps, kdesc, rows, cols)
+    mp = _projected_rows(orc, rng, kkps, kdesc, n, rows, cols)
+    if form == "pose":
+        mp = _exact_disparity_rows(rng, mp, n)
+    src, dst = rng.integers(0, n, 60), rng.integers(0, n, 60)      # twin rows: two map points that fuse with the same keypoint
+    for k in mp:
+        mp[k][dst] = mp[k][src]
+    uR = None
+    if stereo:
+        uR = np.where(rng.random(n) < 0.6, ckps["x"] - rng.uniform(0, 40, n), -1.0).astype(np.float32)
+    b = (0.0, float(cols), 0.0, float(rows))
+    isig2 = (1.0 / SIGMA2).astype(np.float32)
+    nf_o, bi_o, bd_o = orc.fuse(orc.Grid(oracle, ckps, *b), cdesc, uR, SF, isig2, mp, th)
+    nf_r, bi_r, _ = orc.fuse(orc.Grid(refo, ckps, *b), cdesc, uR, SF, isig2, mp, th)
+    assert nf_r != -1000
+    assert nf_o == nf_r > 30
+    assert np.array_equal(bi_o, bi_r), f"{np.sum(bi_o != bi_r)} fuse targets differ"
+    # several rows land on the same keypoint (the Replace branch of the reference): make sure the case occurred
+    hit = bi_o[bi_o >= 0]
+    assert len(hit) > len(np.unique(hit))
+    for i in np.flatnonzero(bi_o >= 0)[:200]:
+        assert bd_o[i] == int(np.unpackbits(mp["desc"][i] ^ cdesc[bi_o[i]]).sum()) <= 50
+    assert "orc_fuse" in refo.L.routed
+
+
+@pytest.mark.parametrize("th,seed", [(7.5, 81), (3.0, 82), (7.5, 83)])
+def test_search_by_sim3(orc, oracle, refo, th, seed):
+    """ORBmatcher::SearchBySim3, src/ORBmatcher.cc:2201-2434 (both projection directions and the cross-check)."""
+    rng = np.random.default_rng(seed)
+    rows, cols, n = 480, 752, 1400
+    k1, d1, _, _ = _frame(orc, rng, n, rows, cols)
+    k2, d2, perm = _moved(orc, rng, k1, d1, rows, cols, flips=(0, 25))
+    inv = np.empty(n, np.int64); inv[perm] = np.arange(n)
+    rows1 = dict(desc=_flip(rng, d1.copy(), 0, 10), u=(k2["x"][inv] + rng.normal(0, 1.5, n)).astype(np.float32),
+                 v=(k2["y"][inv] + rng.normal(0, 1.5, n)).astype(np.float32),
+                 level=np.clip(k2["octave"][inv] + rng.choice([0, 0, 1], n), 0, 7).astype(np.int32), valid=(rng.random(n) < 0.8).astype(np.uint8))
+    rows2 = dict(desc=_flip(rng, d2.copy(), 0, 10), u=(k1["x"][perm] + rng.normal(0, 1.5, n)).astype(np.float32),
+                 v=(k1["y"][perm] + rng.normal(0, 1.5, n)).astype(np.float32),
+                 level=np.clip(k1["octave"][perm] + rng.choice([0, 0, 1], n), 0, 7).astype(np.int32), valid=(rng.random(n) < 0.8).astype(np.uint8))
+    rows1["u"][:3] = [0.0, float(cols), -0.5]
+    b = (0.0, float(cols), 0.0, float(rows))
+    out = [orc.search_by_sim3(orc.Grid(o, k1, *b), d1, orc.Grid(o, k2, *b), d2, SF, rows1, rows2, th) for o in (oracle, refo)]
+    assert out[0][0] == out[1][0] > 100 and np.array_equal(out[0][1], out[1][1])
+    assert "orc_search_by_sim3" in refo.L.routed
