@@ -354,8 +354,9 @@ int orbx_undistort_keypoints(int device, const orbx_keypoint* kps, int n, float 
 /* void Tracking::SearchLocalPoints() src/Tracking.cc:3808-3893 in one call: bool
  * Frame::isInFrustum(MapPoint*, float viewingCosLimit) include/Frame.h, src/Frame.cc:603-711 (Nleft == -1) for every
  * local map point ON THE DEVICE - pose Rcw (row-major 3x3), tcw, Ow; pinhole fx, fy, cx, cy (src/CameraModels/
- * Pinhole.cpp:33-37); mbf; logScaleFactor = Frame::mfLogScaleFactor; per point world position, normal, min / max
- * distance invariance, descriptor, candidate = !isBad() && mnLastFrameSeen != frame id (may be NULL = all) - followed
+ * Pinhole.cpp:33-37); mbf; logScaleFactor = Frame::mfLogScaleFactor; per point world position, normal, the map point's
+ * mfMinDistance / mfMaxDistance AS STORED (the 0.8 / 1.2 of GetMin/MaxDistanceInvariance, src/MapPoint.cc:668-681, are applied here;
+ * MapPoint::PredictScale :725-741 divides the stored mfMaxDistance), descriptor, candidate = !isBad() && mnLastFrameSeen != frame id (may be NULL = all) - followed
  * by ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th, bFarPoints, thFarPoints) src/ORBmatcher.cc:45-168
  * on the mTrack* fields, which never leave the device in between.  One upload, one download.
  * assign[n] in/out as orbx_search_by_projection.  out_* (each may be NULL): mbTrackInView, mTrackProjX/Y/XR,

@@ -64,6 +64,20 @@ if [ -f "$DBOW/DBoW2/TemplatedVocabulary.h" ]; then
     done
     $CXX -std=c++14 $BOW -c "$HERE/ref_bow_wrap.cc" -o "$OUT/ref_bow_wrap.o"
     $CXX -o "$OUT/libref_bow.so" $BOWOBJ "$OUT/ref_bow_wrap.o" "$OUT/orc_prims.o" $LINK
+
+    # libref_frame.so: the UNMODIFIED src/Frame.cc with the real include/Frame.h, ORBextractor.cc and the vendored DBoW2; doubles of
+    # the IMU / camera / map-point headers in oracle/refshim_frame (force-included); the oracle's C primitives behind the OpenCV
+    # stand-in's undistortPoints / BFMatcher / FAST / resize / GaussianBlur
+    FRAME="-I$HERE/boostshim -I$HERE/refshim_frame -I$REF -I$REF/include/CameraModels -I$DBOW -include $HERE/refshim_frame/ref_frame_stubs.h"
+    $CXX -std=c++14 $COMMON $CANON $FRAME -c "$REF/src/Frame.cc" -o "$OUT/Frame.o"
+    $CXX -std=c++14 $COMMON $CANON $FRAME -c "$HERE/ref_frame_wrap.cc" -o "$OUT/ref_frame_wrap.o"
+    ORCOBJ=""
+    for f in orc_extractor orc_octree orc_detect orc_prepare; do
+        $CC -O3 -fPIC -std=c11 $CANON -c "$HERE/$f.c" -o "$OUT/$f.o"
+        ORCOBJ="$ORCOBJ $OUT/$f.o"
+    done
+    $CXX -o "$OUT/libref_frame.so" "$OUT/Frame.o" "$OUT/ref_frame_wrap.o" "$OUT/ORBextractor.o" $BOWOBJ \
+        "$OUT/orc_match.o" "$OUT/orc_prims.o" $ORCOBJ $LINK
 fi
 
 rm -f "$OUT"/*.o

@@ -37,6 +37,7 @@ typedef unsigned char uchar;
 
 #include <stdexcept>
 #include <string>
+#include <climits>
 #include <sstream>      /* the real core.hpp pulls it in; the vendored DBoW2 relies on that */
 namespace cv {
 
@@ -321,6 +322,10 @@ public:
         return m;
     }
 
+    /* Frame::UndistortKeyPoints reshapes its N x 2 point list to N x 1 two-channel and back (src/Frame.cc:950-953): the
+     * stand-in keeps point lists as N x 2 one-channel throughout (undistortPoints below takes them that way) */
+    Mat reshape(int) const { return *this; }
+
 private:
     int type_;
     int* ref_;
@@ -394,6 +399,18 @@ template <typename T, int M, int N> struct Matx {
         static_assert(M * N == 9, "Matx9");
         val[0] = a; val[1] = b; val[2] = c; val[3] = d; val[4] = e; val[5] = f; val[6] = g; val[7] = h; val[8] = i;
     }
+    Matx(T a, T b, T c, T d, T e, T f, T g, T h, T i, T j, T k, T l)
+    {
+        static_assert(M * N == 12, "Matx12");
+        val[0] = a; val[1] = b; val[2] = c; val[3] = d; val[4] = e; val[5] = f; val[6] = g; val[7] = h; val[8] = i; val[9] = j; val[10] = k; val[11] = l;
+    }
+    template <int M1, int N1> Matx<T, M1, N1> get_minor(int i0, int j0) const
+    {
+        Matx<T, M1, N1> r;
+        for (int i = 0; i < M1; i++)
+            for (int j = 0; j < N1; j++) r(i, j) = (*this)(i0 + i, j0 + j);
+        return r;
+    }
     T& operator()(int i, int j) { return val[i * N + j]; }
     const T& operator()(int i, int j) const { return val[i * N + j]; }
     T& operator()(int i) { return val[i]; }
@@ -451,6 +468,7 @@ template <typename T, int M, int N> inline Matx<T, M, N> operator*(float s, cons
 typedef Matx<float, 3, 3> Matx33f;
 typedef Matx<float, 3, 1> Matx31f;
 typedef Matx<float, 4, 4> Matx44f;
+typedef Matx<float, 3, 4> Matx34f;
 /* cv::norm(Matx): sqrt of the sum of squares accumulated in double (normL2Sqr<_Tp, double>) */
 template <typename T, int M, int N> inline double norm(const Matx<T, M, N>& a)
 {
@@ -589,6 +607,119 @@ struct KeyPointsFilter {
             keypoints.resize(new_end - keypoints.begin());
         }
     }
+};
+
+/* ---- what src/Frame.cc needs on top of the extractor / matcher subset ---- */
+
+/* cv::norm(a, b, NORM_L1) on CV_8U windows (the SAD of Frame::ComputeStereoMatches, src/Frame.cc:1197): integer sum, returned as double */
+inline double norm(const Mat& a, const Mat& b, int normType)
+{
+    if (normType != NORM_L1 || a.type() != CV_8U || b.type() != CV_8U || a.rows != b.rows || a.cols != b.cols) cvshim_fail("norm(a, b): only NORM_L1 on CV_8U");
+    long s = 0;
+    for (int y = 0; y < a.rows; y++) {
+        const uchar* pa = a.ptr(y); const uchar* pb = b.ptr(y);
+        for (int x = 0; x < a.cols; x++) s += pa[x] > pb[x] ? pa[x] - pb[x] : pb[x] - pa[x];
+    }
+    return (double)s;
+}
+
+/* cv::Mat_<float>(r, c) << a, b, c  (src/Frame.cc:1321) */
+template <typename T> struct cvshim_type;
+template <> struct cvshim_type<float> { enum { value = CV_32F }; };
+template <> struct cvshim_type<double> { enum { value = CV_64F }; };
+template <> struct cvshim_type<uchar> { enum { value = CV_8U }; };
+template <> struct cvshim_type<int> { enum { value = CV_32S }; };
+template <typename T> class Mat_ : public Mat {
+public:
+    Mat_() {}
+    Mat_(int r, int c) : Mat(r, c, cvshim_type<T>::value) {}
+};
+template <typename T> class MatCommaInitializer_ {
+public:
+    MatCommaInitializer_(const Mat_<T>& m) : m_(m), i_(0) {}
+    template <typename V> MatCommaInitializer_<T>& operator,(V v)
+    {
+        m_.template at<T>(i_ / m_.cols, i_ % m_.cols) = (T)v; i_++;
+        return *this;
+    }
+    operator Mat() const { return m_; }
+    operator Mat_<T>() const { return m_; }
+private:
+    Mat_<T> m_; int i_;
+};
+template <typename T, typename V> inline MatCommaInitializer_<T> operator<<(const Mat_<T>& m, V v)
+{
+    MatCommaInitializer_<T> ci(m);
+    return (ci, v);
+}
+
+inline void hconcat(const Mat& a, const Mat& b, Mat& dst)
+{
+    if (a.rows != b.rows || a.type() != b.type()) cvshim_fail("hconcat");
+    Mat m(a.rows, a.cols + b.cols, a.type());
+    for (int y = 0; y < a.rows; y++) {
+        std::memcpy(m.ptr(y), a.ptr(y), (size_t)a.cols * a.elemSize());
+        std::memcpy(m.ptr(y) + (size_t)a.cols * a.elemSize(), b.ptr(y), (size_t)b.cols * b.elemSize());
+    }
+    dst = m;
+}
+inline void vconcat(const Mat& a, const Mat& b, Mat& dst)
+{
+    if ((a.cols != b.cols && !a.empty() && !b.empty()) || a.type() != b.type()) cvshim_fail("vconcat");
+    const int cols = a.empty() ? b.cols : a.cols;
+    Mat m(a.rows + b.rows, cols, a.type());
+    for (int y = 0; y < a.rows; y++) std::memcpy(m.ptr(y), a.ptr(y), (size_t)cols * a.elemSize());
+    for (int y = 0; y < b.rows; y++) std::memcpy(m.ptr(a.rows + y), b.ptr(y), (size_t)cols * b.elemSize());
+    dst = m;
+}
+
+/* cv::undistortPoints(src, dst, K, distCoeffs, R = empty, P) for N x 2 CV_32F point lists with P == K, 4 or 5 coefficients:
+ * orc_undistort_points (oracle/orc_prepare.c), pinned against cv2.undistortPoints in tests/test_oracle_vs_cv2.py */
+extern "C" void orc_undistort_points(const float* xy_in, int n, float fx, float fy, float cx, float cy, const float* dist, float* xy_out);
+inline void undistortPoints(const Mat& src, Mat& dst, const Mat& K, const Mat& distCoeffs, const Mat& R, const Mat& P)
+{
+    if (src.type() != CV_32F || src.cols != 2 || !src.isContinuous() || !R.empty()) cvshim_fail("undistortPoints: N x 2 CV_32F, R empty");
+    if (K.type() != CV_32F || P.type() != CV_32F) cvshim_fail("undistortPoints: K, P CV_32F");
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++)
+            if (K.at<float>(i, j) != P.at<float>(i, j)) cvshim_fail("undistortPoints: P != K");
+    float d[5] = {0, 0, 0, 0, 0};
+    const int nd = (int)distCoeffs.total();
+    if (nd != 4 && nd != 5) cvshim_fail("undistortPoints: 4 or 5 distortion coefficients");
+    for (int i = 0; i < nd; i++) d[i] = distCoeffs.at<float>(i);
+    Mat out(src.rows, 2, CV_32F);
+    orc_undistort_points(src.ptr<float>(), src.rows, K.at<float>(0, 0), K.at<float>(1, 1), K.at<float>(0, 2), K.at<float>(1, 2), d, out.ptr<float>());
+    dst = out;
+}
+
+/* features2d: cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, matches, 2) = orc_bf_knn2 (oracle/orc_prims.c), pinned against
+ * cv2.BFMatcher.knnMatch incl. its tie order in tests/test_oracle_vs_cv2.py */
+struct DMatch {
+    int queryIdx, trainIdx, imgIdx; float distance;
+    DMatch() : queryIdx(-1), trainIdx(-1), imgIdx(-1), distance(3.4e38f) {}
+    DMatch(int q, int t, float d) : queryIdx(q), trainIdx(t), imgIdx(0), distance(d) {}
+};
+extern "C" void orc_bf_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* out_idx, int32_t* out_dist);
+class BFMatcher {
+public:
+    explicit BFMatcher(int normType = NORM_L2, bool crossCheck = false) : norm_(normType) { (void)crossCheck; }
+    void knnMatch(const Mat& q, const Mat& t, std::vector<std::vector<DMatch> >& matches, int k) const
+    {
+        if (norm_ != NORM_HAMMING || k != 2) cvshim_fail("BFMatcher: only NORM_HAMMING, k = 2");
+        matches.clear();
+        const int nq = q.rows, nt = t.rows;
+        if (nq == 0) return;
+        if (q.cols != 32 || (nt > 0 && t.cols != 32) || !q.isContinuous() || (nt > 0 && !t.isContinuous())) cvshim_fail("BFMatcher: 32-byte continuous rows");
+        matches.resize((size_t)nq);
+        if (nt == 0) return;
+        std::vector<int32_t> idx((size_t)nq * 2), dist((size_t)nq * 2);
+        orc_bf_knn2(q.ptr(), nq, t.ptr(), nt, idx.data(), dist.data());
+        for (int i = 0; i < nq; i++)
+            for (int j = 0; j < 2; j++)
+                if (idx[2 * i + j] >= 0) matches[(size_t)i].push_back(DMatch(i, idx[2 * i + j], (float)dist[2 * i + j]));
+    }
+private:
+    int norm_;
 };
 
 /* persistence (core/persistence.hpp): the vendored DBoW2's YAML save / load (TemplatedVocabulary.h:1456-1620) are virtual

@@ -788,12 +788,12 @@ int orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, float
         double p2 = 0;
         for (int k = 0; k < 3; k++) { const double w = PO[k]; p2 += w * w; }
         const float dist = (float)sqrt(p2);
-        if (dist < min_dist[i] || dist > max_dist[i]) continue;               /* :640 */
+        if (dist < 0.8f * min_dist[i] || dist > 1.2f * max_dist[i]) continue; /* :647-656; GetMin/MaxDistanceInvariance, src/MapPoint.cc:668-681 */
         float dot = 0;
         for (int k = 0; k < 3; k++) dot += PO[k] * normal[3 * (size_t)i + k];
         const float vc = dot / dist;                                          /* :646 */
         if (vc < viewingCosLimit) continue;
-        const float ratio = max_dist[i] / dist;                               /* PredictScale */
+        const float ratio = max_dist[i] / dist;                               /* PredictScale: mfMaxDistance itself, src/MapPoint.cc:730 */
         int nScale = (int)ceilf(logf(ratio) / logScaleFactor);
         if (nScale < 0) nScale = 0; else if (nScale >= nlevels) nScale = nlevels - 1;
         inview[i] = 1;

@@ -382,7 +382,7 @@ struct ORBmatcherGPU {
     // mnLastFrameSeen != mCurrentFrame.mnId.
     struct LocalMapSoA {
         std::vector<float> pos, normal;                // n x 3 each: GetWorldPos2(), GetNormal2()
-        std::vector<float> minDistance, maxDistance;   // GetMinDistanceInvariance(), GetMaxDistanceInvariance()
+        std::vector<float> minDistance, maxDistance;   // mfMinDistance, mfMaxDistance as stored (= GetMin/MaxDistanceInvariance() / 0.8f, / 1.2f)
         std::vector<uint8_t> desc, candidate;          // n x 32 ; n
     };
     struct TrackFields {                               // what Frame::isInFrustum leaves in each MapPoint

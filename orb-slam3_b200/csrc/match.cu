@@ -613,11 +613,11 @@ frustum_kernel(FrustumArgs A)
             const float O0 = __fsub_rn(P0, A.Ow[0]), O1 = __fsub_rn(P1, A.Ow[1]), O2 = __fsub_rn(P2, A.Ow[2]);
             const double p2 = __dadd_rn(__dadd_rn(__dmul_rn(O0, O0), __dmul_rn(O1, O1)), __dmul_rn(O2, O2));
             const float dist = __double2float_rn(__dsqrt_rn(p2));
-            if (dist < A.dmin[i] || dist > A.dmax[i]) break;                                            // :640
+            if (dist < __fmul_rn(0.8f, A.dmin[i]) || dist > __fmul_rn(1.2f, A.dmax[i])) break;          // :647-656, src/MapPoint.cc:668-681
             const float dot = __fadd_rn(__fadd_rn(__fmul_rn(O0, A.normal[3 * i]), __fmul_rn(O1, A.normal[3 * i + 1])), __fmul_rn(O2, A.normal[3 * i + 2]));
             const float vc = __fdiv_rn(dot, dist);                                                      // :646
             if (vc < A.cosLimit) break;
-            const float ratio = __fdiv_rn(A.dmax[i], dist);                                             // MapPoint::PredictScale
+            const float ratio = __fdiv_rn(A.dmax[i], dist);                                             // MapPoint::PredictScale: the RAW mfMaxDistance
             int nScale = (int)ceilf(__fdiv_rn(glibc_logf(ratio), A.logsf));
             if (nScale < 0) nScale = 0; else if (nScale >= A.nlevels) nScale = A.nlevels - 1;
             in = 1; pxr = __fsub_rn(u, __fmul_rn(A.mbf, invz)); dep = Pc_dist; lvl = nScale; vcos = vc; // :654-662

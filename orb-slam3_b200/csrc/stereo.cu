@@ -303,7 +303,9 @@ static int fill_args(orbx_extractor* eL, orbx_extractor* eR, float mb, float mbf
         orbx_set_error("left/right extractors differ in device, image size or parameters");
         return ORBX_ERR_ARG;
     }
-    if (!(mb > 0.f)) { orbx_set_error("mb must be > 0"); return ORBX_ERR_ARG; }
+    // mb == 0 is accepted: maxD = mbf / 0 = +inf, no upper disparity bound - what the reference's rectified-stereo constructor
+    // effectively runs with (it calls ComputeStereoMatches, src/Frame.cc:137, before it assigns mb, :163)
+    if (!(mb >= 0.f)) { orbx_set_error("mb must be >= 0"); return ORBX_ERR_ARG; }
     if (!eL->d_st_scratch) {
         void* q = nullptr;
         if (cudaMalloc(&q, sizeof(int) * (size_t)eL->G.batch * eL->G.out_cap) != cudaSuccess) {

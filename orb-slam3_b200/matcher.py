@@ -291,7 +291,7 @@ def SearchLocalPoints(kps, desc, uRight, bounds, scale_factors, pose: dict, cam:
                       cos_limit: float = 0.5, th: float = 1.0, nnratio: float = 0.8, far: bool = False, th_far: float = 0.0,
                       assign=None, device: int = 0):
     """Tracking::SearchLocalPoints (src/Tracking.cc:3808-3893): Frame::isInFrustum on the device + SearchByProjection.
-    pose: Rcw, tcw, Ow; cam: fx, fy, cx, cy, mbf; pts: pos(n,3), normal(n,3), min_dist, max_dist, desc, candidate.
+    pose: Rcw, tcw, Ow; cam: fx, fy, cx, cy, mbf; pts: pos(n,3), normal(n,3), min_dist, max_dist (mfMinDistance / mfMaxDistance as stored), desc, candidate.
     Returns (nmatches, assign, dict of the mTrack* fields)."""
     kps = np.ascontiguousarray(kps, KP_DTYPE); desc = np.ascontiguousarray(desc, np.uint8)
     n = len(kps); sf = np.ascontiguousarray(scale_factors, np.float32)

@@ -6,10 +6,10 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _stereo_case(pkg, orc, oracle, cfg, seed, nframes=1):
+def _stereo_case(pkg, orc, oracle, cfg, seed, nframes=1, mb=None):
     c = pkg.synth.CONFIGS[cfg]
     rows, cols, nf = c["rows"], c["cols"], c["nfeatures"]
-    mbf = c["mbf"]; mb = mbf / c["fx"]
+    mbf = c["mbf"]; mb = mbf / c["fx"] if mb is None else mb
     pairs = [pkg.synth.synth_stereo_pair(rows, cols, seed + i) for i in range(nframes)]
     L = np.stack([p[0] for p in pairs]); R = np.stack([p[1] for p in pairs])
     XL, XR = pkg.ORBextractor(nf), pkg.ORBextractor(nf)
@@ -35,6 +35,12 @@ def test_stereo_euroc(pkg, orc, oracle):
 
 def test_stereo_kitti(pkg, orc, oracle):
     assert _stereo_case(pkg, orc, oracle, "C4", 21, nframes=2) > 300
+
+
+def test_stereo_unbounded_disparity(pkg, orc, oracle):
+    """mb = 0: maxD = mbf / mb = +inf.  This is what the reference's rectified-stereo constructor effectively runs with - it calls
+    ComputeStereoMatches (src/Frame.cc:137) before it assigns mb (:163); tests/test_oracle_ref_frame.py::test_stereo_constructor_end_to_end."""
+    assert _stereo_case(pkg, orc, oracle, "C4", 23, nframes=2, mb=0.0) > 300
 
 
 @pytest.mark.parametrize("nframes", [9, 11])
@@ -135,7 +141,7 @@ def test_extract_stereo_errors(pkg):
         pkg.ExtractStereo(XL, XL, im, im, 0.11, 47.9)            # the same handle twice
     assert ei.value.code == pkg.binding.ORBX_ERR_ARG
     with pytest.raises(pkg.OrbxError) as ei:
-        pkg.ExtractStereo(XL, XR, im, im, 0.0, 47.9)             # mb must be positive
+        pkg.ExtractStereo(XL, XR, im, im, -0.1, 47.9)            # mb must be >= 0 (0 = no upper disparity bound)
     assert ei.value.code == pkg.binding.ORBX_ERR_ARG
     XL.close(); XR.close()
 
