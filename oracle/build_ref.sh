@@ -80,6 +80,12 @@ if [ -f "$DBOW/DBoW2/TemplatedVocabulary.h" ]; then
         "$OUT/orc_match.o" "$OUT/orc_prims.o" $ORCOBJ $LINK
 fi
 
+# libref_mp.so: the UNMODIFIED src/MapPoint.cc with the real include/MapPoint.h over doubles of KeyFrame / Frame / Map
+MP="-I$HERE/boostshim -I$HERE/refshim_mp -I$REF -include $HERE/refshim_mp/ref_mp_stubs.h"
+$CXX -std=c++14 $COMMON $CANON $MP -c "$REF/src/MapPoint.cc" -o "$OUT/MapPoint.o"
+$CXX -std=c++14 $COMMON $CANON $MP -c "$HERE/ref_mp_wrap.cc" -o "$OUT/ref_mp_wrap.o"
+$CXX -o "$OUT/libref_mp.so" "$OUT/MapPoint.o" "$OUT/ref_mp_wrap.o" "$OUT/orc_match.o" "$OUT/orc_prims.o" $LINK
+
 rm -f "$OUT"/*.o
-sha256sum "$REF/src/ORBextractor.cc" "$REF/include/ORBextractor.h" "$REF/src/ORBmatcher.cc" "$REF/include/ORBmatcher.h" > "$OUT/SOURCES.sha256" 2>/dev/null || true
+sha256sum "$REF/src/ORBextractor.cc" "$REF/include/ORBextractor.h" "$REF/src/ORBmatcher.cc" "$REF/include/ORBmatcher.h" "$REF/src/Frame.cc" "$REF/include/Frame.h" "$REF/src/MapPoint.cc" "$REF/include/MapPoint.h" "$REF/Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h" "$REF/Thirdparty/DBoW2/DBoW2/FORB.cpp" > "$OUT/SOURCES.sha256" 2>/dev/null || true
 echo "build_ref.sh: built $(ls "$OUT"/*.so | wc -l) libraries in $OUT"

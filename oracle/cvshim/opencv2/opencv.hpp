@@ -404,6 +404,7 @@ template <typename T, int M, int N> struct Matx {
         static_assert(M * N == 12, "Matx12");
         val[0] = a; val[1] = b; val[2] = c; val[3] = d; val[4] = e; val[5] = f; val[6] = g; val[7] = h; val[8] = i; val[9] = j; val[10] = k; val[11] = l;
     }
+    static Matx zeros() { return Matx(); }
     template <int M1, int N1> Matx<T, M1, N1> get_minor(int i0, int j0) const
     {
         Matx<T, M1, N1> r;
