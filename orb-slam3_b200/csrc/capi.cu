@@ -112,6 +112,7 @@ extern "C" void orbx_destroy(orbx_extractor* e)
     for (cudaEvent_t ev : e->ev_up) cudaEventDestroy(ev);
     for (cudaEvent_t ev : e->ev_done) cudaEventDestroy(ev);
     for (cudaEvent_t ev : e->ev_down) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : e->ev_piece) cudaEventDestroy(ev);
     for (int i = 0; i < ORBX_NCSTREAMS; i++) { cudaStreamDestroy(e->cstream[i]); cudaEventDestroy(e->ev_join[i]); }
     cudaEventDestroy(e->ev_fork);
     if (e->dag_ready)
@@ -692,29 +693,60 @@ static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* img
     if (!multi && !raw && (size_t)nframes * e->G.out_cap * (sizeof(orbx_keypoint) + 32) <= ORBX_LAND_MAX && !orbx_no_land())
         return extract_small(e, nframes, imgs, step, frame_stride, lap0, lap1, kps, desc, cap, nkp, mono);
     cudaStream_t up = multi ? e->stream_h2d : e->stream, dn = multi ? e->stream_d2h : e->stream;
+    // Ramp: the upload of the first chunk and the kernels + download of the last one have nothing to overlap with, so those two
+    // chunks are cut into pieces of 1/8, 1/8, 1/4, 1/2 (mirrored at the end) that move through the same slot one behind the
+    // other: only 1/8 of a chunk is exposed at either end of a call (C1: 0.9 ms -> 0.1 ms of a 16 ms call of 2048 frames).
+    bool ramp = false;                                       // measured on B200: 124.5 k vs 125.9 k frames/s without (C1) - off
+    if (const char* rs = getenv("ORBX_RAMP")) ramp = multi && !e->profiling && atoi(rs) != 0;
+    while (ramp && (int)e->ev_piece.size() < 8) {
+        cudaEvent_t a;
+        CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        e->ev_piece.push_back(a);
+    }
     for (int k = 0; k < nchunks; k++) {
         const int fr0 = k * chunk, n = nframes - fr0 < chunk ? nframes - fr0 : chunk;
         const int slot = k % R, s0 = slot * chunk;
         cudaStream_t cs = (multi && !e->profiling) ? e->cstream[k % ncs] : e->stream;   // chunk slot k%R is always served by the same stream
+        int pc[4] = {n, 0, 0, 0}, np = 1;
+        if (ramp && n >= 32 && (k == 0 || k == nchunks - 1)) {
+            const int h = n / 2, q = n / 4, o = n / 8, rest = n - h - q - o;
+            if (k == 0) { pc[0] = rest; pc[1] = o; pc[2] = q; pc[3] = h; }
+            else { pc[0] = h; pc[1] = q; pc[2] = o; pc[3] = rest; }
+            np = 4;
+        }
         if (multi && k >= R) CUDA_TRY(cudaStreamWaitEvent(up, e->ev_done[slot], 0));
-        r = raw ? upload_raw(e, s0, n, imgs + (size_t)fr0 * frame_stride, step, frame_stride, up)
-                : upload_frames(e, s0, n, imgs + (size_t)fr0 * frame_stride, step, frame_stride, up);
-        if (r) return r;
-        if (multi) {
-            CUDA_TRY(cudaEventRecord(e->ev_up[slot], up));
-            CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_up[slot], 0));
-            if (k >= R) CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_down[slot], 0));
+        if (multi && k >= R) CUDA_TRY(cudaStreamWaitEvent(cs, e->ev_down[slot], 0));
+        for (int j = 0, off = 0; j < np; off += pc[j], j++) {
+            const int pn = pc[j], pf = fr0 + off, ps = s0 + off;
+            static const bool skip_h2d = getenv("ORBX_DIAG_NO_H2D") != nullptr, skip_d2h = getenv("ORBX_DIAG_NO_D2H") != nullptr;   // diagnostics
+            r = skip_h2d ? 0 : raw ? upload_raw(e, ps, pn, imgs + (size_t)pf * frame_stride, step, frame_stride, up)
+                    : upload_frames(e, ps, pn, imgs + (size_t)pf * frame_stride, step, frame_stride, up);
+            if (r) return r;
+            if (multi) {
+                cudaEvent_t evu = np > 1 ? e->ev_piece[(size_t)(2 * j)] : e->ev_up[slot];
+                CUDA_TRY(cudaEventRecord(evu, up));
+                CUDA_TRY(cudaStreamWaitEvent(cs, evu, 0));
+            }
+            if (raw) e->launches += launch_prepare(e, ps, pn, cs);   // remap + gray into the slot's frames
+            static const bool skip_kernels = getenv("ORBX_DIAG_COPIES_ONLY") != nullptr;   // diagnostic: the ring's copy rate alone
+            r = skip_kernels ? 0 : run_pipeline(e, ps, pn, lap0, lap1, cs);
+            if (r) return r;
+            if (multi) {
+                cudaEvent_t evd = np > 1 ? e->ev_piece[(size_t)(2 * j + 1)] : e->ev_done[slot];
+                CUDA_TRY(cudaEventRecord(evd, cs));
+                CUDA_TRY(cudaStreamWaitEvent(dn, evd, 0));
+            }
+            r = skip_d2h ? (int)cudaMemcpyAsync(counts + 2 * (size_t)pf, e->D.counts + 2 * ps, sizeof(int) * 2 * pn, cudaMemcpyDeviceToHost, dn)
+                         : download_results(e, ps, pn, kps + (size_t)pf * cap, desc + (size_t)pf * cap * 32, cap, counts + 2 * (size_t)pf, dn);
+            if (r) return r;
         }
-        if (raw) e->launches += launch_prepare(e, s0, n, cs);   // remap + gray into the slot's frames
-        r = run_pipeline(e, s0, n, lap0, lap1, cs);
-        if (r) return r;
         if (multi) {
-            CUDA_TRY(cudaEventRecord(e->ev_done[slot], cs));
-            CUDA_TRY(cudaStreamWaitEvent(dn, e->ev_done[slot], 0));
+            if (np > 1) {                                     // the slot's own events mark the end of its last piece
+                CUDA_TRY(cudaEventRecord(e->ev_up[slot], up));
+                CUDA_TRY(cudaEventRecord(e->ev_done[slot], cs));
+            }
+            CUDA_TRY(cudaEventRecord(e->ev_down[slot], dn));
         }
-        r = download_results(e, s0, n, kps + (size_t)fr0 * cap, desc + (size_t)fr0 * cap * 32, cap, counts + 2 * (size_t)fr0, dn);
-        if (r) return r;
-        if (multi) CUDA_TRY(cudaEventRecord(e->ev_down[slot], dn));
     }
     if (multi) {
         // callers (timer, stereo match) order against the handle's stream: join the copy streams into it

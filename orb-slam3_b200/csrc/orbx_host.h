@@ -19,7 +19,7 @@ struct orbx_extractor {
     cudaStream_t cstream[ORBX_NCSTREAMS];  // compute streams: sub-batches run concurrently so kernel tails overlap
     cudaEvent_t ev_fork, ev_join[ORBX_NCSTREAMS];
     cudaStream_t stream_h2d, stream_d2h;   // copy engines of the chunked extract_batch pipeline
-    std::vector<cudaEvent_t> ev_up, ev_done, ev_down;
+    std::vector<cudaEvent_t> ev_up, ev_done, ev_down, ev_piece;   // ev_piece: upload / kernel events of the ramp pieces of a call's first and last chunk
     int* h_counts; size_t h_counts_cap;    // pinned {nkp, mono} staging (a pageable target would make the D2H copy synchronous)
     // single-chunk calls (one frame / a few frames): pinned staging of the input frames and a pinned landing zone for
     // {keypoints, descriptors}: with pageable user buffers every cudaMemcpyAsync is a synchronous staged copy
