@@ -631,9 +631,11 @@ static int ensure_reserved(orbx_extractor* e, int rows, int cols, int nframes)
     if (r) { orbx_set_error("image %dx%d too small for %d pyramid levels (35-px cell grid)", cols, rows, e->nlevels); return r; }
     long long per = (long long)rows * ((cols + 127) / 128 * 128) + G.keys_per_frame * 12;
     for (int l = 0; l < G.nlevels; l++) per += 2 * G.L[l].plane_bytes;
-    long long b = (8LL << 30) / per;
+    long long maxslots = 512, budget = 8LL << 30;
+    if (const char* sl = getenv("ORBX_SLOTS")) { const long long v = atoll(sl); if (v >= 1 && v <= 8192) { maxslots = v; budget = 64LL << 30; } }
+    long long b = budget / per;
     if (b < 1) b = 1;
-    if (b > 512) b = 512;
+    if (b > maxslots) b = maxslots;
     e->batch_limit = (int)b;                                 // a later, larger batch grows the slots up to here
     if (b > nframes) b = nframes;
     if (e->reserved && e->G.rows == rows && e->G.cols == cols && b < e->G.batch) b = e->G.batch;

@@ -20,6 +20,19 @@ def main():
     ts.sort()
     print(json.dumps({"reps": reps, "median_ms": ts[len(ts) // 2] * 1e3, "p10_ms": ts[len(ts) // 10] * 1e3,
                       "p90_ms": ts[(len(ts) * 9) // 10] * 1e3}))
+    # the same call with the frame in pinned host memory (no staging copy inside the call)
+    try:
+        import torch
+        pimg = torch.from_numpy(img.copy()).pin_memory().numpy()
+        for _ in range(5):
+            X(pimg, (0, 1000))
+        tp = []
+        for _ in range(reps):
+            t0 = time.perf_counter(); X(pimg, (0, 1000)); tp.append(time.perf_counter() - t0)
+        tp.sort()
+        print(json.dumps({"pinned_input_median_ms": tp[len(tp) // 2] * 1e3, "p10_ms": tp[len(tp) // 10] * 1e3}))
+    except Exception as ex:                              # torch is plumbing here, not a dependency of the probe
+        print(json.dumps({"pinned_input": f"skipped: {ex}"}))
     # host-side cost of queueing the launches vs the GPU time of the pipeline (frame already resident)
     X.upload(img[None])
     for _ in range(5):
