@@ -272,7 +272,7 @@ static int upload_frames(orbx_extractor* e, int slot0, int nframes, const uint8_
 static void slot_view(const orbx_extractor* e, int s0, FrameGeom* Go, DevBuffers* Do)
 {
     *Go = e->G; *Do = e->D;
-    Do->slot0 = s0;
+    Do->slot0 = s0; Do->zc_input = nullptr; Do->zc_pitch = 0; Do->zc_frame_bytes = 0;
     const FrameGeom& G = e->G;
     const size_t s = (size_t)s0;
     for (int l = 0; l < G.nlevels; l++) { Go->L[l].pyr += s * G.L[l].plane_bytes; Go->L[l].blur += s * G.L[l].plane_bytes; }
@@ -285,10 +285,12 @@ static void slot_view(const orbx_extractor* e, int s0, FrameGeom* Go, DevBuffers
 }
 
 // the whole extraction pipeline on frame slots [0, nframes), asynchronous on the handle's stream
-static int run_pipeline(orbx_extractor* e, int slot0, int nframes, int lap0, int lap1, cudaStream_t s)
+static int run_pipeline(orbx_extractor* e, int slot0, int nframes, int lap0, int lap1, cudaStream_t s,
+                        const uint8_t* zc_input = nullptr, size_t zc_step = 0, size_t zc_frame_stride = 0)
 {
     FrameGeom G; DevBuffers D;
     slot_view(e, slot0, &G, &D);
+    D.zc_input = zc_input; D.zc_pitch = (int)zc_step; D.zc_frame_bytes = (long long)zc_frame_stride;
     const bool prof = e->profiling && s == e->stream;
     if (prof) cudaEventRecord(e->ev[0], s);
     e->launches += launch_pyramid(G, D, nframes, s);
@@ -698,6 +700,15 @@ static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* img
     // Ramp: the upload of the first chunk and the kernels + download of the last one have nothing to overlap with, so those two
     // chunks are cut into pieces of 1/8, 1/8, 1/4, 1/2 (mirrored at the end) that move through the same slot one behind the
     // other: only 1/8 of a chunk is exposed at either end of a call (C1: 0.9 ms -> 0.1 ms of a 16 ms call of 2048 frames).
+    // Zero-copy experiment (ORBX_ZEROCOPY=1): frames in mapped pinned host memory are read by the level-0 kernel itself, no copy engine
+    bool zerocopy = false; const uint8_t* zc_base = nullptr;
+    if (const char* zs = getenv("ORBX_ZEROCOPY")) {
+        cudaPointerAttributes pa;
+        if (atoi(zs) != 0 && !raw && multi && cudaPointerGetAttributes(&pa, imgs) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer) {
+            zerocopy = true; zc_base = (const uint8_t*)pa.devicePointer;
+        }
+        cudaGetLastError();
+    }
     bool ramp = false;                                       // measured on B200: 124.5 k vs 125.9 k frames/s without (C1) - off
     if (const char* rs = getenv("ORBX_RAMP")) ramp = multi && !e->profiling && atoi(rs) != 0;
     while (ramp && (int)e->ev_piece.size() < 8) {
@@ -721,7 +732,7 @@ static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* img
         for (int j = 0, off = 0; j < np; off += pc[j], j++) {
             const int pn = pc[j], pf = fr0 + off, ps = s0 + off;
             static const bool skip_h2d = getenv("ORBX_DIAG_NO_H2D") != nullptr, skip_d2h = getenv("ORBX_DIAG_NO_D2H") != nullptr;   // diagnostics
-            r = skip_h2d ? 0 : raw ? upload_raw(e, ps, pn, imgs + (size_t)pf * frame_stride, step, frame_stride, up)
+            r = (skip_h2d || zerocopy) ? 0 : raw ? upload_raw(e, ps, pn, imgs + (size_t)pf * frame_stride, step, frame_stride, up)
                     : upload_frames(e, ps, pn, imgs + (size_t)pf * frame_stride, step, frame_stride, up);
             if (r) return r;
             if (multi) {
@@ -731,7 +742,8 @@ static int extract_batch_impl(orbx_extractor* e, int nframes, const uint8_t* img
             }
             if (raw) e->launches += launch_prepare(e, ps, pn, cs);   // remap + gray into the slot's frames
             static const bool skip_kernels = getenv("ORBX_DIAG_COPIES_ONLY") != nullptr;   // diagnostic: the ring's copy rate alone
-            r = skip_kernels ? 0 : run_pipeline(e, ps, pn, lap0, lap1, cs);
+            r = skip_kernels ? 0 : zerocopy ? run_pipeline(e, ps, pn, lap0, lap1, cs, zc_base + (size_t)pf * frame_stride, step, frame_stride)
+                                            : run_pipeline(e, ps, pn, lap0, lap1, cs);
             if (r) return r;
             if (multi) {
                 cudaEvent_t evd = np > 1 ? e->ev_piece[(size_t)(2 * j + 1)] : e->ev_done[slot];

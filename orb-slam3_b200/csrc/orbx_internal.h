@@ -129,6 +129,8 @@ struct DevBuffers {
     int* counts;              // [batch][2] = {nkp, mono}
     const void* blur_maps;    // HOST pointer: BlurMaps (TMA tensor maps of the pyramid planes, describe.cu) or NULL
     int slot0;                // first frame slot of this view (TMA coordinates are absolute)
+    const uint8_t* zc_input;  // != NULL: level 0 reads the frames from here (mapped pinned host memory) instead of `input`
+    int zc_pitch; long long zc_frame_bytes;
 };
 
 // kernel launchers (each returns the number of kernel launches it issued)

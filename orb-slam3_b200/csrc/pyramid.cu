@@ -252,11 +252,14 @@ int launch_pyramid_level(const FrameGeom& G, const DevBuffers& D, int nframes, i
         if (l == 0) {
             const dim3 block(64, 4);
             const dim3 grid(((L.w + 15) / 16 + block.x - 1) / block.x, (L.h + 2 * PYR_HALO + block.y - 1) / block.y, nframes);
-            if ((D.in_pitch & 15) == 0 && ((uintptr_t)D.input & 15) == 0)
-                orbx_launch(pyr_level0_kernel<true>, grid, block, 0, s, D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
+            const uint8_t* in = D.zc_input ? D.zc_input : D.input;
+            const int ip = D.zc_input ? D.zc_pitch : D.in_pitch;
+            const long long ifb = D.zc_input ? D.zc_frame_bytes : (long long)D.in_pitch * G.rows;
+            if ((ip & 15) == 0 && (ifb & 15) == 0 && ((uintptr_t)in & 15) == 0)
+                orbx_launch(pyr_level0_kernel<true>, grid, block, 0, s, in, ip, ifb,
                             L.pyr, L.pitch, L.plane_bytes, L.w, L.h, D.candcnt, G.nlevels);
             else
-                orbx_launch(pyr_level0_kernel<false>, grid, block, 0, s, D.input, D.in_pitch, (long long)D.in_pitch * G.rows,
+                orbx_launch(pyr_level0_kernel<false>, grid, block, 0, s, in, ip, ifb,
                             L.pyr, L.pitch, L.plane_bytes, L.w, L.h, D.candcnt, G.nlevels);
         } else if (L.tapw) {
             const LevelGeom& P = G.L[l - 1];
