@@ -93,6 +93,7 @@ static void free_device(orbx_extractor* e)
     for (void* p : e->allocs) cudaFree(p);
     e->allocs.clear();
     if (e->reserved && e->D.blur_maps) { blur_tma_destroy(e->D.blur_maps); e->D.blur_maps = nullptr; }
+    if (e->reserved && e->D.pyr_maps) { pyr_tma_destroy(e->D.pyr_maps); e->D.pyr_maps = nullptr; }
     e->reserved = false;
     e->last_nframes = 0;
     e->d_uright = e->d_depth = nullptr; e->d_st_scratch = nullptr; e->d_st_rows = nullptr;
@@ -242,6 +243,7 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
     CUDA_TRY(cudaMemsetAsync(D.candcnt, 0, sizeof(*D.candcnt) * B * G.nlevels, e->stream));
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     D.blur_maps = blur_tma_create(G); D.slot0 = 0;
+    D.pyr_maps = pyr_tma_create(G);
     e->G = G; e->D = D; e->reserved = true;
     return ORBX_OK;
 }

@@ -128,6 +128,7 @@ struct DevBuffers {
     uint8_t* desc;            // [batch][out_cap][32]
     int* counts;              // [batch][2] = {nkp, mono}
     const void* blur_maps;    // HOST pointer: BlurMaps (TMA tensor maps of the pyramid planes, describe.cu) or NULL
+    const void* pyr_maps;     // HOST pointer: PyrMaps (pyramid.cu; ORBX_PYR_TMA=0 disables) or NULL
     int slot0;                // first frame slot of this view (TMA coordinates are absolute)
     const uint8_t* zc_input;  // != NULL: level 0 reads the frames from here (mapped pinned host memory) instead of `input`
     int zc_pitch; long long zc_frame_bytes;
@@ -138,6 +139,8 @@ int launch_pyramid(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStr
 void blur_plan(FrameGeom& G);           // fills blur_end[] (and blur_tma_end[])
 const void* blur_tma_create(const FrameGeom& G);   // tensor maps over the level planes (NULL: TMA path unavailable)
 void blur_tma_destroy(const void* maps);
+const void* pyr_tma_create(const FrameGeom& G);
+void pyr_tma_destroy(const void* maps);
 void pyramid_fill_border(const LevelGeom& L, int frame, cudaStream_t s);   // mvImagePyramid border on demand
 bool fast_per_level(const FrameGeom& G);
 int launch_pyramid_level(const FrameGeom& G, const DevBuffers& D, int nframes, int l, cudaStream_t s);

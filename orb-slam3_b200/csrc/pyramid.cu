@@ -173,6 +173,134 @@ pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long p
     }
 }
 
+// ---- TMA variant of the fast resize (default; ORBX_PYR_TMA=0 selects the global-memory kernel above) ----
+// Same thread mapping and arithmetic as pyr_resize_fast_kernel<8, *>, but the source rows of the CTA's 64 output rows x 128
+// pixels come from ONE cp.async.bulk.tensor.2d tile (SASS: UTMALDG) of PT_ROWS x PT_BYTES behind an mbarrier: the row loop
+// reads shared memory (3 LDS per source row) instead of global memory, the L2 prefetch and the 64-bit address arithmetic go.
+#include <cuda.h>
+#define PT_ROWS 82            // 64 output rows * 1.2 + taps + the reflected halo rows
+#define PT_BYTES 192          // 32 words * 4 px * 1.2 + 12 tap bytes + 15 alignment bytes, multiple of 16
+struct PyrMaps { CUtensorMap map[ORBX_MAX_LEVELS]; };
+
+__device__ __forceinline__ HRow4 pyr_hrow_smem(const uint8_t* S, uint32_t shift, const uint32_t (&a01)[4], const uint32_t (&sel)[4])
+{
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(S);
+    const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+    const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
+    HRow4 r;
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        r.h[k] = (int)(__dp2a_lo(a01[k], __byte_perm(lo, hi, sel[k]), 0u) >> 4);
+    return r;
+}
+
+__global__ void __launch_bounds__(256)
+pyr_resize_tma_kernel(const __grid_constant__ PyrMaps M, int lvl_src, int slot0, int src_prow,
+                      uint8_t* __restrict__ out, int pitch, long long plane_bytes, int w, int h,
+                      const ResizeWord* __restrict__ tapw, const ResizeTapY* __restrict__ tapy)
+{
+    __shared__ __align__(128) uint8_t tile[PT_ROWS * PT_BYTES];
+    __shared__ __align__(8) uint64_t mbar;
+    __shared__ int s_org[2];
+    orbx_pdl_prologue();
+    const int lane = threadIdx.x, ty = threadIdx.y;
+    const int wi = ORBX_XOFF / 4 - 1 + blockIdx.x * 32 + lane;             // interior words + one halo word per side
+    const bool colvalid = wi <= (ORBX_XOFF + w + 3) / 4;
+    const int Y0c = blockIdx.y * 64 - PYR_HALO, Y0 = Y0c + ty * 8;
+    const int f = blockIdx.z;
+    ResizeWord t;
+    {
+        const int wl = colvalid ? wi : ORBX_XOFF / 4;                        // any valid table row
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(tapw + wl)), b = __ldg(reinterpret_cast<const uint4*>(tapw + wl) + 1);
+        t.wb = (int)a.x; t.shift = a.y; t.sels = a.z; t.a01[0] = a.w; t.a01[1] = b.x; t.a01[2] = b.y; t.a01[3] = b.z;
+    }
+    if (ty == 0) {
+        // tile origin: leftmost tap word of the warp (16-byte aligned down: TMA box start), first source row of the CTA's rows
+        const int wbmin = __reduce_min_sync(0xffffffffu, colvalid ? t.wb : 0x7fffffff);
+        if (lane == 0) {
+            const int xs = (ORBX_XOFF + wbmin) & ~15;                       // byte column inside the padded plane row
+            // first source row: the CTA's first image row, or - bottom CTA - the reflected halo row h + 2 -> h - 4 (the top halo reflects downwards)
+            const int ys = min((int)tapy[ORBX_EDGE + max(Y0c, 0)].s0, (int)tapy[ORBX_EDGE + min(Y0c + 63, h + PYR_HALO - 1)].s0);
+            s_org[0] = xs - ORBX_XOFF; s_org[1] = ys;
+            const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mb));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mb), "r"((uint32_t)(PT_ROWS * PT_BYTES)) : "memory");
+            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                         :: "r"((uint32_t)__cvta_generic_to_shared(tile)), "l"(reinterpret_cast<uint64_t>(&M.map[lvl_src])),
+                            "r"(xs), "r"((slot0 + f) * src_prow + ORBX_YOFF + ys), "r"(mb) : "memory");
+        }
+    }
+    __syncthreads();                                                        // barrier initialised, origin published
+    if (!colvalid || Y0 >= h + PYR_HALO) return;
+    uint32_t sel[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) sel[k] = (t.sels >> (8 * k)) & 0xFFu;
+    const uint8_t* base = tile + (t.wb - s_org[0]) - s_org[1] * PT_BYTES;   // source row s -> base + s * PT_BYTES
+    uint32_t* dst = reinterpret_cast<uint32_t*>(out + (long long)f * plane_bytes + (long long)(ORBX_YOFF + Y0) * pitch) + wi;
+    const int pw = pitch >> 2;
+    {
+        const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar);
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(done) : "r"(mb), "r"(0u) : "memory");
+    }
+    int have = -1;
+    HRow4 hl;
+#pragma unroll
+    for (int k = 0; k < 4; k++) hl.h[k] = 0;
+    const int nr = min(8, h + PYR_HALO - Y0);
+#pragma unroll 2
+    for (int rr = 0; rr < nr; rr++) {
+        const uint2 tv = __ldg(reinterpret_cast<const uint2*>(tapy + ORBX_EDGE + Y0) + rr);
+        const int s0 = (int)(tv.x & 0xFFFFu), s1 = (int)(tv.x >> 16);
+        const HRow4 h0 = (s0 == have) ? hl : pyr_hrow_smem(base + s0 * PT_BYTES, t.shift, t.a01, sel);
+        const HRow4 h1 = (s1 == s0) ? h0 : pyr_hrow_smem(base + s1 * PT_BYTES, t.shift, t.a01, sel);
+        const uint32_t b0 = tv.y & 0xFFFFu, b1 = tv.y >> 16;
+        const uint32_t A01 = __byte_perm(b0 * (uint32_t)h0.h[0], b0 * (uint32_t)h0.h[1], 0x7632);
+        const uint32_t A23 = __byte_perm(b0 * (uint32_t)h0.h[2], b0 * (uint32_t)h0.h[3], 0x7632);
+        const uint32_t B01 = __byte_perm(b1 * (uint32_t)h1.h[0], b1 * (uint32_t)h1.h[1], 0x7632);
+        const uint32_t B23 = __byte_perm(b1 * (uint32_t)h1.h[2], b1 * (uint32_t)h1.h[3], 0x7632);
+        const uint32_t S01 = A01 + B01 + 0x00020002u, S23 = A23 + B23 + 0x00020002u;
+        dst[rr * pw] = __byte_perm(S01 >> 2, S23 >> 2, 0x6420);
+        hl = h1; have = s1;
+    }
+}
+
+typedef CUresult (*pyr_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                       const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                       CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+const void* pyr_tma_create(const FrameGeom& G)
+{
+    static const bool want = [] { const char* e = getenv("ORBX_PYR_TMA"); return !e || atoi(e) != 0; }();   // default on: 0.544 -> 0.463 ms per 512 C1 frames
+    if (!want) return nullptr;
+    static pyr_tmap_encode_fn enc = [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) fn = nullptr;
+        return (pyr_tmap_encode_fn)fn;
+    }();
+    if (!enc) return nullptr;
+    PyrMaps* M = new PyrMaps();
+    for (int l = 0; l < G.nlevels; l++) {
+        const LevelGeom& L = G.L[l];
+        const cuuint64_t dims[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.prow * (cuuint64_t)G.batch};
+        const cuuint64_t strides[1] = {(cuuint64_t)L.pitch};
+        const cuuint32_t box[2] = {(cuuint32_t)PT_BYTES, (cuuint32_t)PT_ROWS};
+        const cuuint32_t estr[2] = {1u, 1u};
+        if (enc(&M->map[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void*)L.pyr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+            delete M;
+            return nullptr;
+        }
+    }
+    return M;
+}
+
+void pyr_tma_destroy(const void* maps) { delete static_cast<const PyrMaps*>(maps); }
+
 // level l>0 from level l-1.  OpenCV HResizeLinear/VResizeLinear u8 arithmetic (see oracle/orc_prims.c):
 //   H = S[s0]*a0 + S[s1]*a1 ;  dst = (((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2
 // A thread owns one 32-bit word (4 px) of PYR_ROWS consecutive padded rows: the 4 horizontal taps are
@@ -266,7 +394,10 @@ int launch_pyramid_level(const FrameGeom& G, const DevBuffers& D, int nframes, i
             const dim3 block(32, 8);        // one warp per 32 words: the partial warp at the right edge wastes less than a 64-wide block
             const int gx = ((L.w + 3) / 4 + 2 + block.x - 1) / block.x;
             const int gy8 = (L.h + 2 * PYR_HALO + block.y * 8 - 1) / (block.y * 8);
-            if (pyr_rows_override() ? pyr_rows_override() == 8 : (long long)gx * gy8 * nframes >= 4 * 148) {
+            if (D.pyr_maps && (long long)gx * gy8 * nframes >= 4 * 148) {
+                orbx_launch(pyr_resize_tma_kernel, dim3(gx, gy8, nframes), block, 0, s, *static_cast<const PyrMaps*>(D.pyr_maps), l - 1, D.slot0, P.prow,
+                            L.pyr, L.pitch, L.plane_bytes, L.w, L.h, L.tapw, L.tapy);
+            } else if (pyr_rows_override() ? pyr_rows_override() == 8 : (long long)gx * gy8 * nframes >= 4 * 148) {
                 static const bool pf = [] { const char* e = getenv("ORBX_PYR_PF"); return !e || atoi(e) != 0; }();
                 orbx_launch(pf ? pyr_resize_fast_kernel<8, true> : pyr_resize_fast_kernel<8, false>, dim3(gx, gy8, nframes), block, 0, s, P.pyr, P.pitch, P.plane_bytes, L.pyr, L.pitch,
                                                                                   L.plane_bytes, L.w, L.h, L.tapw, L.tapy);
