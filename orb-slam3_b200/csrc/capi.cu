@@ -198,6 +198,25 @@ extern "C" int orbx_reserve(orbx_extractor* e, int rows, int cols, int max_batch
                     rc |= dev_alloc(e, &dw, tw.size());
                     if (!rc) CUDA_TRY(cudaMemcpy(dw, tw.data(), tw.size() * sizeof(ResizeWord), cudaMemcpyHostToDevice));
                     G.L[l].tapw = dw;
+                    // does the TMA resize tile hold the sources of every CTA (32 words x 64 rows) of this level?
+                    const int wlast = (ORBX_XOFF + G.L[l].w + 3) / 4, HALO = 3;
+                    bool ok = true;
+                    for (int w0 = ORBX_XOFF / 4 - 1; w0 <= wlast && ok; w0 += 32) {
+                        int lo = 1 << 30, hi = 0;
+                        for (int wi = w0; wi < w0 + 32 && wi <= wlast; wi++) { lo = std::min(lo, tw[wi].wb); hi = std::max(hi, tw[wi].wb + 12); }
+                        const int start = ((ORBX_XOFF + lo) & ~15) - ORBX_XOFF;
+                        if (lo < -ORBX_XOFF || hi - start > PT_BYTES) ok = false;
+                    }
+                    for (int y0 = -HALO; y0 < G.L[l].h + HALO && ok; y0 += 64) {
+                        int lo = 1 << 30, hi = 0;
+                        for (int y = y0; y < y0 + 64 && y < G.L[l].h + HALO; y++) {
+                            const ResizeTapY& t = ty[l][ORBX_EDGE + y];
+                            lo = std::min(lo, (int)t.s0); hi = std::max(hi, (int)t.s1);
+                        }
+                        const int first = std::min((int)ty[l][ORBX_EDGE + std::max(y0, 0)].s0, (int)ty[l][ORBX_EDGE + std::min(y0 + 63, G.L[l].h + HALO - 1)].s0);
+                        if (lo < first || hi - first + 1 > PT_ROWS) ok = false;
+                    }
+                    G.L[l].pyr_tma_ok = ok ? 1 : 0;
                 }
             }
         }

@@ -51,7 +51,11 @@ struct ResizeWord {
     uint32_t pad;
 };
 
+#define PT_ROWS 82            // TMA resize tile: 64 output rows * 1.2 + taps + the reflected halo rows
+#define PT_BYTES 192          // 32 words * 4 px * 1.2 + 12 tap bytes + 15 alignment bytes, multiple of 16
+
 struct LevelGeom {
+    int pyr_tma_ok;           // the TMA resize tile (PT_ROWS x PT_BYTES) covers every CTA's source rows / tap bytes of this level
     int w, h;                 // level image size (cols, rows)
     int pitch, prow;          // plane row pitch (bytes) and padded row count (h + 38)
     long long plane_bytes;    // pitch * prow

@@ -178,8 +178,8 @@ pyr_resize_fast_kernel(const uint8_t* __restrict__ prev, int ppitch, long long p
 // pixels come from ONE cp.async.bulk.tensor.2d tile (SASS: UTMALDG) of PT_ROWS x PT_BYTES behind an mbarrier: the row loop
 // reads shared memory (3 LDS per source row) instead of global memory, the L2 prefetch and the 64-bit address arithmetic go.
 #include <cuda.h>
-#define PT_ROWS 82            // 64 output rows * 1.2 + taps + the reflected halo rows
-#define PT_BYTES 192          // 32 words * 4 px * 1.2 + 12 tap bytes + 15 alignment bytes, multiple of 16
+// PT_ROWS / PT_BYTES (orbx_internal.h): the tile holds the sources of 64 rows x 32 words at scale factors up to ~1.25; the host
+// checks every level's tap tables against them (LevelGeom::pyr_tma_ok) and falls back to the global-memory kernel otherwise
 struct PyrMaps { CUtensorMap map[ORBX_MAX_LEVELS]; };
 
 __device__ __forceinline__ HRow4 pyr_hrow_smem(const uint8_t* S, uint32_t shift, const uint32_t (&a01)[4], const uint32_t (&sel)[4])
@@ -394,7 +394,7 @@ int launch_pyramid_level(const FrameGeom& G, const DevBuffers& D, int nframes, i
             const dim3 block(32, 8);        // one warp per 32 words: the partial warp at the right edge wastes less than a 64-wide block
             const int gx = ((L.w + 3) / 4 + 2 + block.x - 1) / block.x;
             const int gy8 = (L.h + 2 * PYR_HALO + block.y * 8 - 1) / (block.y * 8);
-            if (D.pyr_maps && (long long)gx * gy8 * nframes >= 4 * 148) {
+            if (D.pyr_maps && L.pyr_tma_ok && (long long)gx * gy8 * nframes >= 4 * 148) {
                 orbx_launch(pyr_resize_tma_kernel, dim3(gx, gy8, nframes), block, 0, s, *static_cast<const PyrMaps*>(D.pyr_maps), l - 1, D.slot0, P.prow,
                             L.pyr, L.pitch, L.plane_bytes, L.w, L.h, L.tapw, L.tapy);
             } else if (pyr_rows_override() ? pyr_rows_override() == 8 : (long long)gx * gy8 * nframes >= 4 * 148) {

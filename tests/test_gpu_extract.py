@@ -197,6 +197,25 @@ def test_frames_wider_or_taller_than_4111_px(pkg, orc, oracle, rows, cols, nf):
     X.close()
 
 
+@pytest.mark.parametrize("sf,nlevels,ini,mn", [(1.1, 8, 20, 7), (1.25, 6, 20, 7), (1.3, 5, 15, 5), (1.5, 4, 20, 7), (2.0, 3, 25, 10)])
+def test_other_scale_factors_and_thresholds(pkg, orc, oracle, sf, nlevels, ini, mn):
+    """ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST) away from the YAML defaults, batched (so that the
+    batch variants of every kernel run): scale factors beyond ~1.25 do not fit the TMA resize tile (host check,
+    LevelGeom::pyr_tma_ok) and beyond ~1.33 not the 8-byte tap window either - both fallbacks must give the same bytes."""
+    frames = np.stack([pkg.synth.synth_frame(480, 752, 60 + i) for i in range(24)])
+    X = pkg.ORBextractor(900, sf, nlevels, ini, mn)
+    E = orc.Extractor(900, sf, nlevels, ini, mn, oracle=oracle)
+    _, n, k, d = X.extract_batch(frames, (0, 0))
+    for f in (0, 7, 23):
+        mo, ko, do = E(frames[f], (0, 0))
+        assert len(ko) > 300
+        assert n[f] == len(ko) and np.array_equal(k[f, :n[f]], ko) and np.array_equal(d[f, :n[f]], do), (sf, f)
+        if f == 23:
+            for l in range(nlevels):
+                assert np.array_equal(X.pyramid_level(l, frame=f), E.level_plane(l)[19:-19, 19:-19]), f"pyramid level {l}"
+    X.close()
+
+
 def test_equal_count_ties_in_the_ordered_phase(pkg, orc, oracle):
     """A regular dot pattern: many quadtree nodes hold the SAME number of candidates when the ordered final phase
     (:909-992) starts, so the split order is decided by the tie-break (count desc, then list position)."""
