@@ -176,7 +176,10 @@ int orbx_hamming256(const void* a, const void* b);
 
 /* void Frame::ComputeStereoMatches()  include/Frame.h:114, src/Frame.cc:1027-1276.
  * Uses the keypoints, descriptors and pyramids left on the device by the preceding extract calls on
- * eL and eR (frame slot `frame` of each).  uRight/depth: N_left floats (mvuRight, mvDepth). */
+ * eL and eR (frame slot `frame` of each).  uRight/depth: N_left floats (mvuRight, mvDepth).
+ * mb = Frame::mb (baseline in metres; minZ, so maxD = mbf / mb, :1081-1084), mb >= 0.  NOTE: the reference's rectified-stereo
+ * constructor calls ComputeStereoMatches (:137) BEFORE it assigns mb = mbf / fx (:163), i.e. with an uninitialised member; pass
+ * mb = mbf / fx for the intended bound, or mb = 0 (maxD = +inf, no upper disparity bound) for what a zero-filled Frame computes. */
 int orbx_stereo_match(orbx_extractor* eL, orbx_extractor* eR, int frame, float mb, float mbf,
                       float* uRight, float* depth, int cap);
 /* batch twin: all frames of the last extract; outputs at uRight + f*cap, depth + f*cap.  The frames of a batch stay
