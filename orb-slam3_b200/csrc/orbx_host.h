@@ -18,6 +18,10 @@ struct orbx_extractor {
     cudaStream_t stream;
     cudaStream_t cstream[ORBX_NCSTREAMS];  // compute streams: sub-batches run concurrently so kernel tails overlap
     cudaEvent_t ev_fork, ev_join[ORBX_NCSTREAMS];
+    // side streams: the blur of a sub-batch runs beside its FAST / quadtree / assemble (it only needs the pyramid); one per compute
+    // stream plus one for the handle's own stream, created on first use
+    cudaStream_t bstream[ORBX_NCSTREAMS + 1] = {};
+    cudaEvent_t ev_pyr[ORBX_NCSTREAMS + 1] = {}, ev_blur[ORBX_NCSTREAMS + 1] = {};
     cudaStream_t stream_h2d, stream_d2h;   // copy engines of the chunked extract_batch pipeline
     std::vector<cudaEvent_t> ev_up, ev_done, ev_down, ev_piece;   // ev_piece: upload / kernel events of the ramp pieces of a call's first and last chunk
     int* h_counts; size_t h_counts_cap;    // pinned {nkp, mono} staging (a pageable target would make the D2H copy synchronous)
