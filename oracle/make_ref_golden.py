@@ -70,6 +70,23 @@ def main():
     np.savez_compressed(out / "ref_stereo_c2.npz", seed=11, mb=mb, mbf=mbf, left_sha=sha(L), right_sha=sha(Rimg), kps_left=kl, kps_right=kr,
                         desc_left_sha=sha(dl), desc_right_sha=sha(dr), uRight=uR, depth=depth, reference_sources=sources_sha())
     print("stereo", int((uR >= 0).sum()), "matches of", len(kl))
+    # guided searches through the compiled, unmodified src/ORBmatcher.cc (oracle/_ref/libref_match.so): inputs from tests/search_cases.py
+    sys.path.insert(0, str(ROOT / "tests"))
+    import copy
+    import orc_py
+    import search_cases
+    from test_oracle_ref_match import _Proxy
+    orc_py.build()
+    oracle = orc_py.Oracle()
+    refo = copy.copy(oracle)
+    refo.L = _Proxy(oracle.L, C.CDLL(str(ROOT / "oracle" / "_ref" / "libref_match.so")))
+    for name, make in search_cases.CASES.items():
+        c = make(orc_py)
+        count, arr = search_cases.run_oracle(name, orc_py, refo, c)
+        assert any(r.startswith("orc_") for r in refo.L.routed)
+        np.savez_compressed(out / f"ref_search_{name}.npz", inputs_sha=search_cases.digest(c), count=count, result=arr,
+                            routed=np.array(sorted(refo.L.routed)), reference_sources=sources_sha())
+        print(name, count)
 
 
 if __name__ == "__main__":

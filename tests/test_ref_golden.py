@@ -83,3 +83,31 @@ def test_gpu_reproduces_reference_stereo(pkg):
     assert np.array_equal(np.asarray(uR).reshape(-1)[:n].view(np.uint32), g["uRight"].view(np.uint32))
     assert np.array_equal(np.asarray(depth).reshape(-1)[:n].view(np.uint32), g["depth"].view(np.uint32))
     XL.close(); XR.close()
+
+
+# ---- guided searches: vectors produced by the compiled, unmodified src/ORBmatcher.cc (inputs: tests/search_cases.py) ----
+import search_cases
+
+SEARCHES = sorted(search_cases.CASES)
+
+
+def _search_golden(name, mod):
+    g = np.load(GOLD / f"ref_search_{name}.npz")
+    c = search_cases.CASES[name](mod)
+    assert search_cases.digest(c) == str(g["inputs_sha"]), "the input builders changed: regenerate with oracle/make_ref_golden.py"
+    return g, c
+
+
+@pytest.mark.parametrize("name", SEARCHES)
+def test_oracle_reproduces_reference_search(orc, oracle, name):
+    g, c = _search_golden(name, orc)
+    count, arr = search_cases.run_oracle(name, orc, oracle, c)
+    assert count == int(g["count"]) > 100 and np.array_equal(arr, g["result"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", SEARCHES)
+def test_gpu_reproduces_reference_search(pkg, name):
+    g, c = _search_golden(name, pkg)
+    count, arr = search_cases.run_gpu(name, pkg, c)
+    assert count == int(g["count"]) and np.array_equal(arr, g["result"]), f"{np.sum(arr != g['result'])} entries differ from the reference's"
