@@ -116,7 +116,9 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     __shared__ int s_val[4];
 
     orbx_pdl_prologue();
-    const int lvl = LV.lvl[blockIdx.x], f = blockIdx.y;
+    // blockIdx.x = frame (dispatched first), blockIdx.y = level in the group's order (largest level first): the long level-0 CTAs of
+    // ALL frames start before any small level does, so the launch ends with short CTAs instead of waiting for a late level-0 one
+    const int lvl = LV.lvl[blockIdx.y], f = blockIdx.x;
     const LevelGeom& L = G.L[lvl];
     const int tid = threadIdx.x;
     const int cap = L.node_cap;
@@ -449,7 +451,7 @@ template <bool SMEM, int NT>
 static void launch_group(const FrameGeom& G, const DevBuffers& D, const OctLevels& LV, int nframes, size_t smem, cudaStream_t s)
 {
     if (smem > 48 * 1024) cudaFuncSetAttribute(octree_kernel<SMEM, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    orbx_launch(octree_kernel<SMEM, NT>, dim3(LV.n, nframes), dim3(NT), smem, s, G, D, LV);
+    orbx_launch(octree_kernel<SMEM, NT>, dim3(nframes, LV.n), dim3(NT), smem, s, G, D, LV);
 }
 
 int launch_octree(const FrameGeom& G, const DevBuffers& D, int nframes, cudaStream_t s, int level)
