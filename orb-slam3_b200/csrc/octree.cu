@@ -114,6 +114,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     extern __shared__ int dyn_smem[];
     __shared__ int s_warp[NT / 32 + 1];
     __shared__ int s_val[4];
+    __shared__ int s_thr[OCT_HROOTS + 1], s_rx[OCT_HROOTS + 1];
 
     orbx_pdl_prologue();
     // blockIdx.x = frame (dispatched first), blockIdx.y = level in the group's order (largest level first): the long level-0 CTAs of
@@ -151,13 +152,23 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     __syncthreads();
     if (fast) {
         for (int i = tid; i < nI * OCT_HNODES; i += OCT_THREADS) Hh[i] = 0;
+        // root of a keypoint = min((int)(x / hX), nIni - 1) (:740) without a division per candidate: x is an integer and the quotient
+        // is monotone, so root r <=> s_thr[r] <= x < s_thr[r + 1] with s_thr[i] = the smallest x whose float quotient reaches i
+        if (tid <= nI) {
+            s_rx[tid] = (int)__fmul_rn(L.hX, (float)tid);                   // root bounds, :698-731
+            int c = (int)ceilf(__fmul_rn(L.hX, (float)tid));
+            while (c > 0 && (int)__fdiv_rn((float)(c - 1), L.hX) >= tid) c--;
+            while ((int)__fdiv_rn((float)c, L.hX) < tid) c++;
+            s_thr[tid] = (tid == 0) ? 0 : (tid == nI ? 0x7FFFFFFF : c);
+        }
         __syncthreads();
         int* Hd = Hh + HOFF(OCT_HDEPTH);
         for_cands(cand, nullptr, n, [&](int i, orbx_key_t k, int) {
-            int r = (int)__fdiv_rn((float)KEY_X(k), L.hX);           // vpIniNodes[kp.pt.x/hX], :740
-            r = min(r, L.nIni - 1);
             const int x = KEY_X(k), y = KEY_Y(k);
-            int x0 = (int)__fmul_rn(L.hX, (float)r), x1 = (int)__fmul_rn(L.hX, (float)(r + 1)), y0 = 0, y1 = H;
+            int r = 0;
+#pragma unroll
+            for (int q = 1; q < OCT_HROOTS; q++) r += (q < nI) && (x >= s_thr[q]);
+            int x0 = s_rx[r], x1 = s_rx[r + 1], y0 = 0, y1 = H;
             int path = r;
 #pragma unroll
             for (int d = 0; d < OCT_HDEPTH; d++) {                   // DivideNode geometry, :602-661
@@ -243,7 +254,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
                 if (materialise) {
                     p = 0;
 #pragma unroll
-                    for (int d = 0; d <= OCT_HDEPTH; d++) {
+                    for (int d = OCT_HDEPTH; d >= 0; d--) {
                         const int v = Hh[HOFF(d) + (code >> (2 * (OCT_HDEPTH - d)))];
                         if (v < 0) { p = -1 - v; break; }
                     }
@@ -402,8 +413,8 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
         if (!fast) return code >> 2;
         int p = 0;
 #pragma unroll
-        for (int d = 0; d <= OCT_HDEPTH; d++) {
-            const int v = Hh[HOFF(d) + (code >> (2 * (OCT_HDEPTH - d)))];
+        for (int d = OCT_HDEPTH; d >= 0; d--) {       // deepest first: the final nodes sit near the bottom of the binned tree, and
+            const int v = Hh[HOFF(d) + (code >> (2 * (OCT_HDEPTH - d)))];      // exactly one node on a candidate's path holds a marker
             if (v < 0) { p = -1 - v; break; }
         }
         return p;
