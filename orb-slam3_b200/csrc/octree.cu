@@ -72,10 +72,12 @@ __device__ __forceinline__ int child_of(int x, int y, int bx, int by)
 }
 
 // position of a candidate in the reference's vToDistributeKeys order (cell row-major, raster inside a cell)
-__device__ __forceinline__ int cand_rank(orbx_key_t key, const LevelGeom& L)
+// The two divisions by the cell size are multiplications by ceil(2^32 / d) (mw, mh; one division per thread at kernel start): exact for
+// x < 2^16 and 2 <= d <= 128, since x * (ceil(2^32 / d) * d - 2^32) < 2^16 * 128 < 2^32.
+__device__ __forceinline__ int cand_rank(orbx_key_t key, const LevelGeom& L, uint32_t mw, uint32_t mh)
 {
     const int X3 = (int)KEY_X(key) - 3, Y3 = (int)KEY_Y(key) - 3;
-    const int cj = X3 / L.wCell, ci = Y3 / L.hCell;
+    const int cj = (int)__umulhi((uint32_t)X3, mw), ci = (int)__umulhi((uint32_t)Y3, mh);
     return ((ci * L.nCols + cj) << 14) | ((Y3 - ci * L.hCell) << 7) | (X3 - cj * L.wCell);
 }
 
@@ -400,6 +402,7 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     // candidate pass when score and rank pack into 32 bits (<= 1024 cells: score << 24 | inverted rank),
     // two otherwise ----
     unsigned* best = reinterpret_cast<unsigned*>(aA);
+    const uint32_t mw = 0xFFFFFFFFu / (uint32_t)L.wCell + 1u, mh = 0xFFFFFFFFu / (uint32_t)L.hCell + 1u;   // ceil(2^32 / cell size); cells are 35..127 px
     int* bestrank = aB;
     orbx_key_t* sel = D.sel + (long long)f * G.sel_per_frame + L.sel_base;
     const int nout = min(size, L.sel_cap);
@@ -421,14 +424,14 @@ octree_kernel(FrameGeom G, DevBuffers D, OctLevels LV)
     };
     if (packed) {
         for_cands(cand, kcode, n, [&](int, orbx_key_t k, int code) {
-            atomicMax(&best[node_of(code)], (KEY_S(k) << 24) | (0xFFFFFFu - (uint32_t)cand_rank(k, L)));
+            atomicMax(&best[node_of(code)], (KEY_S(k) << 24) | (0xFFFFFFu - (uint32_t)cand_rank(k, L, mw, mh)));
         });
     } else {
         for_cands(cand, kcode, n, [&](int, orbx_key_t k, int code) { atomicMax(&best[node_of(code)], KEY_S(k)); });
         __syncthreads();
         for_cands(cand, kcode, n, [&](int, orbx_key_t k, int code) {
             const int nd = node_of(code);
-            if (KEY_S(k) == best[nd]) atomicMin(&bestrank[nd], cand_rank(k, L));
+            if (KEY_S(k) == best[nd]) atomicMin(&bestrank[nd], cand_rank(k, L, mw, mh));
         });
     }
     __syncthreads();
