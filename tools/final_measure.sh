@@ -14,7 +14,7 @@ python tools/bench_match.py > $O/${T}_match.log 2>&1
 python tools/bench_search.py > $O/${T}_search.log 2>&1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file $O/${T}_launches_raw.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $O/${T}_ncu_launch.log 2>&1
-ncu --set full --import-source on --clock-control none \
-    -k regex:'pyr_resize|fast_strip|octree_kernel|blur_tma|describe_kernel|assemble' --launch-skip 39 -c 26 -f -o $O/${T}_full \
-    python bench.py --batch 32 --steps 2 --warmup 3 --no-cpu-baseline > $O/${T}_ncu_full.log 2>&1
+# one warm resident step of 128 frames (4 compute streams x 32 frames = 52 launches): skip the first three steps, capture half of the fourth
+ncu --set full --import-source on --clock-control none --launch-skip 156 -c 26 -f -o $O/${T}_full \
+    python tools/profile_step.py 128 4 > $O/${T}_ncu_full.log 2>&1
 tail -2 $O/${T}_pytest.log; cat $O/${T}_smoke.log | tail -1; tail -1 $O/${T}_bench.log | cut -c1-300
